@@ -1,0 +1,96 @@
+// Shared device/host helpers for the sm_100a kernel library.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+namespace cml {
+
+// ---- error plumbing -------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what, const char* file, int line);
+int sm_count();          // multiprocessors of the current device (cached per device)
+int current_device();
+
+#define CML_CUDA(expr)                                                        \
+  do {                                                                        \
+    int _rc = ::cml::check_cuda((expr), #expr, __FILE__, __LINE__);           \
+    if (_rc) return _rc;                                                      \
+  } while (0)
+
+#define CML_REQUIRE(cond, code, ...)                                          \
+  do {                                                                        \
+    if (!(cond)) {                                                            \
+      ::cml::set_error(__VA_ARGS__);                                          \
+      return (code);                                                          \
+    }                                                                         \
+  } while (0)
+
+#define CML_LAUNCH_CHECK() CML_CUDA(cudaGetLastError())
+
+enum : int {
+  CML_OK = 0,
+  CML_EINVAL = 22,     // bad argument
+  CML_E2BIG = 7,       // size beyond a stated maximum
+  CML_ENOTSUP = 95,
+};
+
+// ---- warp helpers ------------------------------------------------------------------------------
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (scratch: 32 floats of shared memory).
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  v = warp_sum(v);
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float t = (threadIdx.x < nw) ? scratch[threadIdx.x] : 0.f;
+  if (wid == 0) {
+    t = warp_sum(t);
+    if (lane == 0) scratch[0] = t;
+  }
+  __syncthreads();
+  t = scratch[0];
+  __syncthreads();
+  return t;
+}
+
+__host__ __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ __forceinline__ long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
+
+// 128-bit streaming loads that do not pollute L1 (single-use data).
+__device__ __forceinline__ int4 ld_stream(const int4* p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+}  // namespace cml

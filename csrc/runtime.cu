@@ -1,0 +1,81 @@
+// Error plumbing and device queries shared by every launcher in libcml_b200.so.
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+
+#include "cml_b200.h"
+#include "common.cuh"
+
+namespace cml {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what, const char* file, int line) {
+  if (e == cudaSuccess) return 0;
+  set_error("%s:%d: %s -> %s (%s)", file, line, what, cudaGetErrorName(e), cudaGetErrorString(e));
+  return 1000 + static_cast<int>(e);
+}
+
+int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+int sm_count() {
+  static int cache[64];
+  static std::once_flag once;
+  std::call_once(once, [] { memset(cache, 0, sizeof(cache)); });
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return 148;
+  if (cache[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev] = n;
+  }
+  return cache[dev];
+}
+
+}  // namespace cml
+
+extern "C" {
+
+const char* cml_last_error(void) { return cml::g_err; }
+
+int cml_version(void) { return 100; }
+
+int cml_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* total_mem) {
+  cudaDeviceProp prop;
+  CML_CUDA(cudaGetDeviceProperties(&prop, cml::current_device()));
+  if (sm_count) *sm_count = prop.multiProcessorCount;
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  if (total_mem) *total_mem = static_cast<long long>(prop.totalGlobalMem);
+  return 0;
+}
+
+// Overwrites `bytes` of `buf` so that whatever the caller timed before is evicted from the 126 MB L2.
+__global__ void l2_flush_kernel(int4* buf, size_t n16, int v) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n16; i += stride) buf[i] = make_int4(v, v, v, v);
+}
+
+int cml_l2_flush(void* buf, size_t bytes, void* stream) {
+  const size_t n16 = bytes / 16;
+  if (n16 == 0) return 0;
+  static int counter = 0;
+  l2_flush_kernel<<<cml::sm_count() * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<int4*>(buf), n16, ++counter);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+/* Public C ABI of libcml_b200.so - the sm_100a kernel library of consensusml_b200.
+ *
+ * Conventions
+ *  - every function returns 0 on success; on failure cml_last_error() describes the problem
+ *    (1000 + cudaError_t for CUDA runtime errors, errno-style codes for argument errors);
+ *  - pointers are DEVICE pointers unless the name says host; `stream` is a cudaStream_t passed as void*;
+ *  - no function synchronises the device; none allocates device memory unless documented - work
+ *    buffers ("scratch") are supplied by the caller and sized with the matching *_scratch_bytes().
+ *
+ * Each block cites the place in the reference (3ickey/ConsensusML, paths relative to the repository
+ * root) whose CPU library call the kernel replaces.
+ */
+#ifndef CML_B200_H
+#define CML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ------------------------------------------------------------------------------------ */
+const char* cml_last_error(void);
+int cml_version(void);
+int cml_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* total_mem);
+/* Overwrite `bytes` of `buf` (use > 126 MB) to evict L2 between timed iterations. */
+int cml_l2_flush(void* buf, size_t bytes, void* stream);
+
+/* ---- K6/K13: batched glmnet-style logistic lasso / elastic-net path ---------------------------------
+ * Replaces glmnet()/cv.glmnet() (composite_code/rnotebook/cml_targetaml_seanalysis.Rmd:94-101,110;
+ * JSmith_code/Differential_Expression_and_Lasso.Rmd:344-378).  One warp fits one replicate's whole
+ * lambda path; replicates (CV folds, bootstraps, exclusion sets) share xt and differ in w / ju.
+ *   xt  [p][n_pad] feature-major fp32, zero padded;  y [n_pad] (y_stride 0) or [B][n_pad];
+ *   w   [B][n_pad] observation weights, 0 = sample left out;  ju [p] (stride 0) / [B][p] / NULL;
+ *   vp  [p] penalty factors or NULL;  lam [nlam] descending.
+ * Outputs use glmnet's compressed form: m_out[B][nx] = features in order of entry,
+ * ca_out[B][nlam][nx] = their coefficients (first kin_out[b][l] entries valid), plus the linear
+ * predictor of every sample eta_out[B][nlam][n_pad] (may be NULL).  jerr_out follows glmnet:
+ * 0 ok, <0 no convergence / active list overflow at that lambda, >0 fatal.                           */
+int cml_lognet_n_pad(int n);                                /* padded sample count, -1 if n > 1024 */
+int cml_lognet_grid(int B, int n_pad);
+size_t cml_lognet_scratch_bytes(int B, int n_pad, int p);
+int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
+                    long long y_stride, const float* w, const unsigned char* ju, long long ju_stride,
+                    const float* vp, const float* lam, float alpha, float thresh, int intercept, int kopt,
+                    int maxit, void* scratch, size_t scratch_bytes, int* m_out, float* ca_out, int* kin_out,
+                    float* a0_out, float* dev_out, float* eta_out, float* nulldev_out, int* npasses_out,
+                    int* lmu_out, int* jerr_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CML_B200_H */
