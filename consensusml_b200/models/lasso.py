@@ -222,34 +222,25 @@ def stability_selection(x: torch.Tensor, y: torch.Tensor, lam: np.ndarray, *, n_
     The north-star configuration ("1000 bootstrap replicates x elastic-net alpha grid", BASELINE.json
     config 5).  Bootstrap multiplicities enter as integer observation weights, so every replicate is one
     more row of the weight matrix in the same launch.  Returns ``freq[alpha, L, p]`` and ``max_freq[p]``."""
+    from ..ops.replicate import replicate_weights
     n, p = x.shape
-    rng = np.random.default_rng(seed)
     dev = x.device
-    packed = K.pack_design(x) if x.is_cuda else None
+    if x.is_cuda:
+        packed = K.pack_design(x)
+        n_pad = packed[1]
+    else:
+        packed, n_pad = None, n
     L = len(lam)
     freq = torch.zeros(len(alphas), L, p, dtype=torch.float32, device=dev)
+    mode = "bootstrap" if subsample is None else "subsample"
+    k = 0 if subsample is None else max(2, int(round(subsample * n)))
     for ai, alpha in enumerate(alphas):
         done = 0
         while done < n_boot:
             nb = min(batch, n_boot - done)
-            if subsample is None:
-                idx = rng.integers(0, n, size=(nb, n))
-                w = np.zeros((nb, n))
-                np.add.at(w, (np.arange(nb)[:, None], idx), 1.0)
-            else:
-                k = max(2, int(round(subsample * n)))
-                w = np.zeros((nb, n))
-                for b in range(nb):
-                    w[b, rng.choice(n, k, replace=False)] = 1.0
-            pb = K.lognet_path(x, y, torch.as_tensor(w, device=dev), lam, alpha=alpha, want_eta=False,
-                               packed=packed, nx=nx)
-            nxx = pb.coef.shape[2]
-            valid = torch.arange(nxx, device=dev)[None, None, :] < pb.kin[:, :, None]
-            sel = ((pb.coef != 0) & valid).to(torch.float32)          # [nb, L, nx]
-            idxs = pb.active.long()[:, None, :].expand(-1, L, -1)      # [nb, L, nx]
-            acc = torch.zeros(L, p, dtype=torch.float32, device=dev)
-            acc.scatter_add_(1, idxs.permute(1, 0, 2).reshape(L, -1), sel.permute(1, 0, 2).reshape(L, -1))
-            freq[ai] += acc
+            w = replicate_weights(nb, n, mode=mode, k=k, seed=seed + 7919 * ai, device=dev, n_pad=n_pad, rep0=done)
+            K.lognet_path(x, y, w[:, :n], lam, alpha=alpha, want_eta=False, packed=packed, nx=nx, freq_out=freq[ai],
+                          padded_weights=w if x.is_cuda else None, want_coef=False)
             done += nb
         freq[ai] /= n_boot
     return {"freq": freq, "max_freq": freq.amax(dim=(0, 1)), "alphas": torch.tensor(list(alphas)), "lam": torch.as_tensor(lam)}

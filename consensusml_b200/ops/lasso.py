@@ -88,11 +88,13 @@ def lognet_path(x: torch.Tensor, y: torch.Tensor, weights: torch.Tensor, lam, *,
                 intercept: bool = False, modified_newton: bool = False, thresh: float = 1e-7,
                 maxit: int = 100000, nx: Optional[int] = None, feature_mask: Optional[torch.Tensor] = None,
                 penalty_factor: Optional[torch.Tensor] = None, want_eta: bool = True,
-                packed: Optional[tuple] = None) -> PathBatch:
+                packed: Optional[tuple] = None, freq_out: Optional[torch.Tensor] = None,
+                padded_weights: Optional[torch.Tensor] = None, want_coef: bool = True) -> PathBatch:
     """Fit B replicate paths that share the design matrix.
 
     x : [n, p] samples x genes;  y : [n] in {0,1} (or [B, n]);  weights : [B, n] (0 leaves a sample out);
-    lam : descending lambda grid;  feature_mask : [p] or [B, p] bool (False = gene excluded).
+    lam : descending lambda grid;  feature_mask : [p] or [B, p] bool (False = gene excluded);
+    freq_out : optional [L, p] fp32 accumulator of selection counts (stability selection).
     """
     if weights.dim() == 1:
         weights = weights[None, :]
@@ -106,14 +108,20 @@ def lognet_path(x: torch.Tensor, y: torch.Tensor, weights: torch.Tensor, lam, *,
     if penalty_factor is not None:
         pf = penalty_factor.to(torch.float64).clamp_min(0)
         penalty_factor = pf * p / pf.sum()
+    if freq_out is not None and (tuple(freq_out.shape) != (L, p) or freq_out.dtype != torch.float32):
+        raise ValueError("freq_out must be a float32 [L, p] tensor")
     if x.is_cuda:
         return _path_cuda(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
-                          feature_mask, penalty_factor, want_eta, packed)
-    return _path_host(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
-                      feature_mask, penalty_factor, want_eta)
+                          feature_mask, penalty_factor, want_eta, packed, freq_out, padded_weights, want_coef)
+    out = _path_host(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
+                     feature_mask, penalty_factor, want_eta)
+    if freq_out is not None:
+        freq_out += (out._dense_all != 0).sum(0).to(freq_out.dtype)
+    return out
 
 
-def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx, fmask, vp, want_eta, packed):
+def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx, fmask, vp, want_eta, packed,
+               freq_out=None, padded_weights=None, want_coef=True):
     lib = _native.cuda()
     dev = x.device
     B, n = weights.shape
@@ -125,8 +133,11 @@ def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx,
         xt, n_pad = pack_design(x)
     f32 = dict(dtype=torch.float32, device=dev)
     i32 = dict(dtype=torch.int32, device=dev)
-    wp = torch.zeros(B, n_pad, **f32)
-    wp[:, :n] = weights.to(**f32)
+    if padded_weights is not None and tuple(padded_weights.shape) == (B, n_pad) and padded_weights.dtype == torch.float32:
+        wp = padded_weights.contiguous()          # already in the kernel's layout: no copy
+    else:
+        wp = torch.zeros(B, n_pad, **f32)
+        wp[:, :n] = weights.to(**f32)
     if y.dim() == 1:
         yp = torch.zeros(n_pad, **f32)
         yp[:n] = y.to(**f32)
@@ -145,8 +156,8 @@ def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx,
     lib.cml_lognet_scratch_bytes.restype = ctypes.c_size_t
     sbytes = lib.cml_lognet_scratch_bytes(B, n_pad, p)
     scratch = torch.empty(sbytes, dtype=torch.uint8, device=dev)
-    m_out = torch.zeros(B, nx, **i32)
-    ca = torch.zeros(B, L, nx, **f32)
+    m_out = torch.zeros(B, nx, **i32) if want_coef else None
+    ca = torch.empty(B, L, nx, **f32) if want_coef else None       # entries >= kin[b, l] are never read
     kin = torch.zeros(B, L, **i32)
     a0 = torch.zeros(B, L, **f32)
     devr = torch.zeros(B, L, **f32)
@@ -160,8 +171,12 @@ def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx,
         B, n, n_pad, p, L, nx, P(xt), P(yp), ctypes.c_longlong(y_stride), P(wp), P(ju),
         ctypes.c_longlong(ju_stride), P(vpt), P(lam_t), ctypes.c_float(alpha), ctypes.c_float(thresh),
         int(bool(intercept)), int(bool(kopt)), int(maxit), P(scratch), ctypes.c_size_t(sbytes), P(m_out), P(ca),
-        P(kin), P(a0), P(devr), P(eta), P(nulldev), P(npasses), P(lmu), P(jerr), _native.stream_ptr())
+        P(kin), P(a0), P(devr), P(eta), P(freq_out), P(nulldev), P(npasses), P(lmu), P(jerr), _native.stream_ptr())
     _native.check(rc, "cml_lognet_path")
+    if not want_coef:
+        m_out = torch.zeros(B, 0, **i32)
+        ca = torch.zeros(B, L, 0, **f32)
+        kin = torch.zeros_like(kin)
     return PathBatch(m_out, ca, kin, a0, devr, eta[:, :, :n] if eta is not None else None, nulldev, npasses, lmu,
                      jerr, lam_t, p)
 
@@ -233,5 +248,7 @@ def _path_host(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx,
                 eta[b] = coef[b, :, :k] @ xs[:, active[b, :k]].T
         eta += a0[:, :, None]
     t = lambda a, dt=torch.float64: torch.as_tensor(a, dtype=dt)
-    return PathBatch(t(active, torch.int32), t(coef), t(kin, torch.int32), t(a0), t(dev), t(eta) if eta is not None else None,
-                     t(nulldev), t(npasses, torch.int32), t(lmu, torch.int32), t(jerr, torch.int32), t(lam_np), p)
+    out = PathBatch(t(active, torch.int32), t(coef), t(kin, torch.int32), t(a0), t(dev), t(eta) if eta is not None else None,
+                    t(nulldev), t(npasses, torch.int32), t(lmu, torch.int32), t(jerr, torch.int32), t(lam_np), p)
+    out._dense_all = torch.as_tensor(beta)
+    return out

@@ -50,6 +50,7 @@ struct LognetParams {
   float* a0_out;              // [B][nlam]
   float* dev_out;             // [B][nlam]
   float* eta_out;             // [B][nlam][n_pad] or null
+  float* freq_out;            // [nlam][p] selection counts accumulated over the batch, or null
   float* nulldev_out;         // [B]
   int* npasses_out;           // [B]
   int* lmu_out;               // [B]
@@ -447,7 +448,13 @@ lognet_path_kernel(const LognetParams P) {
 
       // ---- record this lambda
       const size_t row = (size_t)rep * P.nlam + ilm;
-      for (int l = lane; l < W.nin; l += 32) P.ca_out[row * P.nx + l] = W.b[W.m[l]];
+      for (int l = lane; l < W.nin; l += 32) {
+        const int k = W.m[l];
+        const float bk = W.b[k];
+        if (P.ca_out) P.ca_out[row * P.nx + l] = bk;
+        // stability selection: how many replicates of this batch picked gene k at this lambda
+        if (P.freq_out && bk != 0.f) atomicAdd(P.freq_out + (size_t)ilm * P.p + k, 1.f);
+      }
       float dacc = 0.f;
 #pragma unroll
       for (int j = 0; j < NPL; ++j) {
@@ -481,7 +488,8 @@ lognet_path_kernel(const LognetParams P) {
       lmu = ilm + 1;
       if (W.xmz <= vmin) break;
     }
-    for (int l = lane; l < W.nin; l += 32) P.m_out[(size_t)rep * P.nx + l] = W.m[l];
+    if (P.m_out)
+      for (int l = lane; l < W.nin; l += 32) P.m_out[(size_t)rep * P.nx + l] = W.m[l];
     if (lane == 0) {
       P.npasses_out[rep] = W.nlp;
       P.lmu_out[rep] = lmu;
@@ -532,8 +540,8 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
                     long long y_stride, const float* w, const unsigned char* ju, long long ju_stride,
                     const float* vp, const float* lam, float alpha, float thresh, int intercept, int kopt,
                     int maxit, void* scratch, size_t scratch_bytes, int* m_out, float* ca_out, int* kin_out,
-                    float* a0_out, float* dev_out, float* eta_out, float* nulldev_out, int* npasses_out,
-                    int* lmu_out, int* jerr_out, void* stream) {
+                    float* a0_out, float* dev_out, float* eta_out, float* freq_out, float* nulldev_out,
+                    int* npasses_out, int* lmu_out, int* jerr_out, void* stream) {
   using namespace cml;
   CML_REQUIRE(B > 0 && n > 0 && p > 0 && nlam > 0 && nx > 0, CML_EINVAL, "cml_lognet_path: empty problem");
   CML_REQUIRE(n_pad == cml_lognet_n_pad(n) || (n_pad % 32 == 0 && n_pad >= n && cml_lognet_n_pad(n_pad) == n_pad),
@@ -546,7 +554,7 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
               p, nx, n_pad, smem);
   LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, ju, ju_stride, vp, lam, alpha, thresh, intercept,
                  kopt, maxit, static_cast<float*>(scratch), m_out, ca_out, kin_out, a0_out, dev_out, eta_out,
-                 nulldev_out, npasses_out, lmu_out, jerr_out};
+                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (n_pad / 32) {
     case 1: return launch<1>(P, grid, smem, st);

@@ -36,7 +36,9 @@ int cml_l2_flush(void* buf, size_t bytes, void* stream);
  *   vp  [p] penalty factors or NULL;  lam [nlam] descending.
  * Outputs use glmnet's compressed form: m_out[B][nx] = features in order of entry,
  * ca_out[B][nlam][nx] = their coefficients (first kin_out[b][l] entries valid), plus the linear
- * predictor of every sample eta_out[B][nlam][n_pad] (may be NULL).  jerr_out follows glmnet:
+ * predictor of every sample eta_out[B][nlam][n_pad] (may be NULL) and, for stability selection,
+ * freq_out[nlam][p] += 1 for every (replicate, lambda) at which gene k is non-zero (may be NULL; the
+ * caller zeroes it).  jerr_out follows glmnet:
  * 0 ok, <0 no convergence / active list overflow at that lambda, >0 fatal.                           */
 int cml_lognet_n_pad(int n);                                /* padded sample count, -1 if n > 1024 */
 int cml_lognet_grid(int B, int n_pad);
@@ -45,8 +47,16 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
                     long long y_stride, const float* w, const unsigned char* ju, long long ju_stride,
                     const float* vp, const float* lam, float alpha, float thresh, int intercept, int kopt,
                     int maxit, void* scratch, size_t scratch_bytes, int* m_out, float* ca_out, int* kin_out,
-                    float* a0_out, float* dev_out, float* eta_out, float* nulldev_out, int* npasses_out,
-                    int* lmu_out, int* jerr_out, void* stream);
+                    float* a0_out, float* dev_out, float* eta_out, float* freq_out, float* nulldev_out,
+                    int* npasses_out, int* lmu_out, int* jerr_out, void* stream);
+
+/* ---- K13: replicate batching --------------------------------------------------------------------
+ * Weight rows for bootstrap (mode 0), k-of-n subsample (mode 1) and repeated k-fold (mode 2, k = folds)
+ * replicates, generated on the device with a counter-based RNG.  Replaces the sequential refit loops
+ * inside cv.glmnet / caret (cml_targetaml_seanalysis.Rmd:98-101; VikasP/AML.R:241-245).
+ *   w [B][n_pad] out;  rep0 = index of the first replicate (continues a stream across batches).    */
+int cml_replicate_weights(float* w, int B, int n, int n_pad, unsigned long long seed, int mode, int k,
+                          int rep0, void* stream);
 
 #ifdef __cplusplus
 }

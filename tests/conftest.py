@@ -1,0 +1,42 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "slow: takes more than a few seconds on CPU")
+    # the host library is needed by the CPU oracles; build it once up front
+    from consensusml_b200 import _build
+    _build.build_host()
+
+
+def pytest_collection_modifyitems(config, items):
+    import torch
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def aml():
+    from consensusml_b200 import datasets
+    return datasets.load_target_aml()
+
+
+@pytest.fixture(scope="session")
+def glmnet_oracle():
+    from consensusml_b200 import datasets
+    return datasets.glmnet_oracle()
+
+
+REFERENCE_DIR = os.environ.get("CML_REFERENCE_DIR", "/root/reference")
+needs_reference = pytest.mark.skipif(not os.path.isdir(REFERENCE_DIR), reason="reference tree not mounted")
