@@ -54,8 +54,42 @@ def cuda() -> ctypes.CDLL:
                         "run `python -m consensusml_b200._build`") from exc
             lib = ctypes.CDLL(str(_build.CUDA_LIB))
             lib.cml_last_error.restype = ctypes.c_char_p
+            _declare(lib)
             _cuda = lib
         return _cuda
+
+
+_I, _LL, _SZ, _F, _D, _P, _ULL = (ctypes.c_int, ctypes.c_longlong, ctypes.c_size_t, ctypes.c_float, ctypes.c_double,
+                                 ctypes.c_void_p, ctypes.c_ulonglong)
+
+# Explicit signatures: without them ctypes passes every Python int as a 32-bit C int, which corrupts
+# size_t / long long / pointer-sized arguments.
+_SIGNATURES = {
+    "cml_l2_flush": ([_P, _SZ, _P], _I),
+    "cml_device_info": ([_P, _P, _P, _P], _I),
+    "cml_lognet_n_pad": ([_I], _I),
+    "cml_lognet_grid": ([_I, _I], _I),
+    "cml_lognet_scratch_bytes": ([_I, _I, _I], _SZ),
+    "cml_lognet_path": ([_I] * 6 + [_P, _P, _LL, _P, _P, _LL, _P, _P, _F, _F, _I, _I, _I, _P, _SZ] + [_P] * 11 + [_P], _I),
+    "cml_replicate_weights": ([_P, _I, _I, _I, _ULL, _I, _I, _I, _P], _I),
+}
+
+
+def _declare(lib) -> None:
+    for name, (args, res) in _SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            continue
+        fn.argtypes = args
+        fn.restype = res
+
+
+def register_signature(name: str, args, res=ctypes.c_int) -> None:
+    """Used by op modules to declare the C signature of the entry points they bind."""
+    _SIGNATURES[name] = (list(args), res)
+    if _cuda is not None:
+        _declare(_cuda)
 
 
 def check(code: int, what: str) -> None:

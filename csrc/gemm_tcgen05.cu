@@ -1,0 +1,334 @@
+// tcgen05 / TMEM / TMA GEMM core:  C[M,N] = epilogue( A[M,K] . B[N,K]^T ),  bf16 operands, fp32 accumulate.
+//
+// Every GEMM-shaped op of the framework goes through this one kernel:
+//   * SVM Gram / RBF kernel matrix  K(i,j) = exp(-gamma |x_i - x_j|^2)      (e1071::svm, reference:
+//     composite_code/rnotebook/cml_targetaml_seanalysis.Rmd:151-154,166-169; BuieRProj/KM_WHATEVER.Rmd:234-237)
+//   * Spearman / Pearson correlation matrices of standardised ranks          (cor(method="spearman"),
+//     cml_targetaml_seanalysis.Rmd:895,910,979,984)
+//   * random-forest proximity = one-hot(leaf) . one-hot(leaf)^T              (randomForest(proximity=TRUE), :1037-1050)
+//   * replicate-batched lasso gradient  X^T . R                              (glmnet inner loop, :94-101)
+//   * k-means / hclust distance blocks.
+// The reference delegates all of these to CPU libraries; nothing in it is a GEMM kernel.
+//
+// Structure (one CTA per SM, persistent over output tiles, 192 threads):
+//   warp 0     : TMA producer - cp.async.bulk.tensor 2-D boxes (64 bf16 x 128 rows, 128B swizzle) of A and B
+//                into a STAGES-deep shared-memory ring, completion on `full` mbarriers;
+//   warp 1     : allocates TMEM, then a single thread issues tcgen05.mma (M=128, N=BN, K=16, cta_group::1)
+//                straight from the swizzled tiles via shared-memory descriptors; tcgen05.commit releases
+//                ring slots (`empty`) and publishes finished accumulators (`tmem_full`);
+//   warps 2..5 : epilogue - tcgen05.ld the fp32 accumulator (32 lanes x 32 columns per warp per load), apply
+//                the fused epilogue (scale | RBF exponent with row/column squared norms), store to global.
+//                Two accumulator stages in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
+// The B operand may be spread over several "sources" (one tensor map + norm vector each).  With one source
+// it is a plain GEMM; with the sources being the symmetric-memory buffers of the NVLink peers it is the fused
+// all-gather -> GEMM: the TMA engine pulls peer tiles over NVLink directly into shared memory, so no
+// gathered copy of X is ever materialised (see consensusml_b200/parallel/fused.py).
+#include <cuda_bf16.h>
+
+#include <cmath>
+#include <cstring>
+#include <mutex>
+
+#include "cml_b200.h"
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace cml {
+
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+int make_tmap_bf16_k64(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_tiled();
+  CML_REQUIRE(enc != nullptr, CML_ENOTSUP, "cuTensorMapEncodeTiled is not available from this driver");
+  CML_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0, CML_EINVAL,
+              "TMA operand must be 16-byte aligned with a row pitch that is a multiple of 16 bytes (ld=%lld)", ld);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CML_REQUIRE(r == CUDA_SUCCESS, 2000 + static_cast<int>(r), "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return 0;
+}
+
+namespace {
+
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int kMaxSrc = 8;
+constexpr int kThreads = 192;
+
+enum Epilogue : int { EPI_SCALE = 0, EPI_RBF = 1, EPI_SQDIST = 2 };
+
+struct GemmParams {
+  CUtensorMap map_a;
+  CUtensorMap map_b[kMaxSrc];
+  const float* norm_b[kMaxSrc];   // squared row norms of every B source (RBF / distance epilogues)
+  const float* norm_a;
+  float* c;
+  long long ldc;
+  int M, N, K;
+  int n_src, rows_per_src;        // B row j of the logical [N][K] operand lives in source j / rows_per_src
+  int epilogue;
+  float alpha;                    // SCALE: multiplier;  RBF: gamma
+  int tiles_m, tiles_n_per_src;
+};
+
+template <int BN, int STAGES>
+struct SmemLayout {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarrierBytes = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int kTotal = STAGES * kStageBytes + kBarrierBytes + 1024;   // +1024: manual alignment slack
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_constant__ GemmParams P) {
+  using L = SmemLayout<BN, STAGES>;
+  using namespace sm100;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;              // SWIZZLE_128B tiles need 1024-byte alignment
+  uint8_t* gen_base = smem_raw + (base - raw);
+  const uint32_t bar0 = base + STAGES * L::kStageBytes;
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + 2 + s); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen_base + STAGES * L::kStageBytes + (2 * STAGES + 4) * 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = (P.K + BK - 1) / BK;
+  const int tiles_n = P.tiles_n_per_src * P.n_src;
+  const int num_tiles = P.tiles_m * tiles_n;
+  constexpr uint32_t kTmemCols = 2 * BN;                     // two accumulator stages (power of two: 256 / 512)
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&P.map_a);
+    for (int s = 0; s < P.n_src; ++s) prefetch_tensormap(&P.map_b[s]);
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+        const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
+          mbar_arrive_expect_tx(full_bar(stage), L::kStageBytes);
+          tma_load_2d(sa, &P.map_a, full_bar(stage), kb * BK, m_blk * BM);
+          tma_load_2d(sb, &P.map_b[src], full_bar(stage), kb * BK, n_loc * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);          // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);                 // TMA bytes have landed
+          tc_fence_after();
+          const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
+          const uint64_t adesc = umma_desc_k_sw128(sa), bdesc = umma_desc_k_sw128(sb);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle atom: +2 in the (>>4) address field
+            umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(empty_bar(stage));                     // slot reusable once these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));                         // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps (TMEM -> registers -> global) =====================
+    const int quarter = warp & 3;                            // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+      const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      const int row = m_blk * BM + quarter * 32 + lane;
+      const int col_src0 = n_loc * BN;                       // column offset inside the source
+      const int rows_here = min(P.rows_per_src, P.N - src * P.rows_per_src);
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      float na = 0.f;
+      if (P.epilogue != EPI_SCALE && row < P.M) na = __ldg(P.norm_a + row);
+      const float* nb = P.norm_b[src];
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN + c0, v);
+        const int cs = col_src0 + c0;                        // first column of this chunk within the source
+        if (row < P.M && cs < rows_here) {
+          float* out = P.c + (size_t)row * P.ldc + (size_t)src * P.rows_per_src + cs;
+          const int nvalid = min(32, rows_here - cs);
+          if (P.epilogue == EPI_SCALE) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= P.alpha;
+          } else {
+            const float g = (P.epilogue == EPI_RBF) ? -P.alpha * 1.4426950408889634f : 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float nbj = (j < nvalid) ? __ldg(nb + cs + j) : 0.f;
+              const float d2 = fmaxf(na + nbj - 2.f * v[j], 0.f);
+              v[j] = (P.epilogue == EPI_RBF) ? exp2f(g * d2) : d2;
+            }
+          }
+          if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int j = 0; j < nvalid; ++j) out[j] = v[j];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+template <int BN, int STAGES>
+int launch_gemm(const GemmParams& P, cudaStream_t st) {
+  using L = SmemLayout<BN, STAGES>;
+  auto kern = gemm_tn_kernel<BN, STAGES>;
+  CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+  const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  kern<<<grid, kThreads, L::kTotal, st>>>(P);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// fp32 row-major -> bf16 row-major with zero-padded pitch, fused with the squared row norm of the
+// ROUNDED values (so that the RBF epilogue's |a|^2 + |b|^2 - 2ab is exactly consistent with the MMA inputs).
+__global__ void to_bf16_rownorm_kernel(const float* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y,
+                                       long long ldy, float* __restrict__ norm, int rows, int cols, float shift,
+                                       const float* __restrict__ col_shift, const float* __restrict__ col_scale) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float* xr = x + (size_t)warp * ldx;
+  __nv_bfloat16* yr = y + (size_t)warp * ldy;
+  float s = 0.f;
+  for (int j = lane; j < ldy; j += 32) {
+    float v = 0.f;
+    if (j < cols) {
+      v = xr[j] - shift;
+      if (col_shift) v -= col_shift[j];
+      if (col_scale) v *= col_scale[j];
+    }
+    const __nv_bfloat16 b = __float2bfloat16_rn(v);
+    yr[j] = b;
+    const float f = __bfloat162float(b);
+    s = fmaf(f, f, s);
+  }
+  s = warp_sum(s);
+  if (lane == 0 && norm) norm[warp] = s;
+}
+
+}  // namespace
+}  // namespace cml
+
+extern "C" {
+
+int cml_to_bf16_rownorm(const float* x, long long ldx, void* y_bf16, long long ldy, float* norm, int rows, int cols,
+                        float shift, const float* col_shift, const float* col_scale, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(rows > 0 && cols > 0 && ldy >= cols && ldy % 8 == 0, CML_EINVAL,
+              "cml_to_bf16_rownorm: ldy=%lld must be >= cols=%d and a multiple of 8", ldy, cols);
+  const int wpb = 8;
+  to_bf16_rownorm_kernel<<<ceil_div(rows, wpb), wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, ldx, static_cast<__nv_bfloat16*>(y_bf16), ldy, norm, rows, cols, shift, col_shift, col_scale);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// C[M][N] (fp32, pitch ldc) = epilogue(A . B^T).  A: bf16 [M][lda]; B source s: bf16 [rows_s][ldb] at b_ptrs[s]
+// holding logical rows [s*rows_per_src, ...).  epilogue 0: alpha*acc; 1: exp(-alpha*(na+nb-2acc)); 2: na+nb-2acc.
+int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const void* const* b_ptrs, int n_src,
+                     int rows_per_src, long long ldb, float* c, long long ldc, int epilogue, float alpha,
+                     const float* norm_a, const float* const* norm_b_ptrs, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(M > 0 && N > 0 && K > 0, CML_EINVAL, "cml_gemm_tn_bf16: empty problem");
+  CML_REQUIRE(n_src >= 1 && n_src <= kMaxSrc, CML_EINVAL, "cml_gemm_tn_bf16: n_src=%d out of range 1..%d", n_src, kMaxSrc);
+  CML_REQUIRE(epilogue >= 0 && epilogue <= 2, CML_EINVAL, "cml_gemm_tn_bf16: unknown epilogue %d", epilogue);
+  CML_REQUIRE(epilogue == EPI_SCALE || (norm_a && norm_b_ptrs), CML_EINVAL, "cml_gemm_tn_bf16: distance epilogues need row norms");
+  CML_REQUIRE((long long)n_src * rows_per_src >= N, CML_EINVAL, "cml_gemm_tn_bf16: sources cover %lld rows < N=%d",
+              (long long)n_src * rows_per_src, N);
+  GemmParams P;
+  memset(&P, 0, sizeof(P));
+  const int BN = 128;
+  int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
+  if (rc) return rc;
+  for (int s = 0; s < n_src; ++s) {
+    const long long rows_s = (long long)N - (long long)s * rows_per_src < rows_per_src ? (long long)N - (long long)s * rows_per_src
+                                                                                      : rows_per_src;
+    CML_REQUIRE(rows_s > 0, CML_EINVAL, "cml_gemm_tn_bf16: source %d is empty", s);
+    rc = make_tmap_bf16_k64(&P.map_b[s], b_ptrs[s], rows_s, K, ldb, BN);
+    if (rc) return rc;
+    P.norm_b[s] = norm_b_ptrs ? norm_b_ptrs[s] : nullptr;
+  }
+  P.norm_a = norm_a;
+  P.c = c;
+  P.ldc = ldc;
+  P.M = M; P.N = N; P.K = K;
+  P.n_src = n_src;
+  P.rows_per_src = rows_per_src;
+  P.epilogue = epilogue;
+  P.alpha = alpha;
+  P.tiles_m = ceil_div(M, BM);
+  P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
+  return launch_gemm<128, 6>(P, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -58,6 +58,23 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
 int cml_replicate_weights(float* w, int B, int n, int n_pad, unsigned long long seed, int mode, int k,
                           int rep0, void* stream);
 
+/* ---- K7/K11: tcgen05 GEMM core -----------------------------------------------------------------
+ * C[M][N] (fp32, pitch ldc) = epilogue(A . B^T), bf16 operands, fp32 TMEM accumulation, TMA-fed.
+ * Replaces the kernel-matrix evaluation inside e1071::svm (cml_targetaml_seanalysis.Rmd:151-154,166-169),
+ * cor(method="spearman") (:895,910,979,984) and randomForest's proximity (:1037-1050).
+ *   a          bf16 [M][lda] (lda = K, multiple of 8, zero padded)
+ *   b_ptrs[s]  bf16 [rows_per_src][ldb] holding logical rows [s*rows_per_src, ...) of B; n_src <= 8.
+ *              The pointers may be peer (NVLink-mapped) addresses: that is the fused all-gather -> GEMM.
+ *   epilogue   0: alpha*acc   1: exp(-alpha*(norm_a[i]+norm_b[j]-2acc))   2: norm_a[i]+norm_b[j]-2acc
+ * b_ptrs / norm_b_ptrs are HOST arrays of device pointers.                                            */
+int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const void* const* b_ptrs, int n_src,
+                     int rows_per_src, long long ldb, float* c, long long ldc, int epilogue, float alpha,
+                     const float* norm_a, const float* const* norm_b_ptrs, void* stream);
+/* fp32 [rows][ldx] -> bf16 [rows][ldy] (zero padded) with optional (x - shift - col_shift[j]) * col_scale[j],
+ * plus squared row norms of the rounded values.                                                       */
+int cml_to_bf16_rownorm(const float* x, long long ldx, void* y_bf16, long long ldy, float* norm, int rows, int cols,
+                        float shift, const float* col_shift, const float* col_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
