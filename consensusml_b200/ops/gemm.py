@@ -82,11 +82,12 @@ def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optiona
         zz = x if z is None else z
         d2 = torch.cdist(x.double(), zz.double()) ** 2
         return torch.exp(-gamma * d2).to(x.dtype)
-    xa, na = to_bf16_rows(x.float())
+    shift = float(x.mean())            # distances are shift-invariant; centring shrinks the norms that cancel
+    xa, na = to_bf16_rows(x.float(), shift=shift)
     if z is None:
         xb, nb = xa, na
     else:
-        xb, nb = to_bf16_rows(z.float())
+        xb, nb = to_bf16_rows(z.float(), shift=shift)
     return gemm_tn(xa, [xb], xb.shape[0], epilogue=EPI_RBF, alpha=gamma, norm_a=na, norm_b=[nb])
 
 

@@ -92,11 +92,12 @@ struct Warp {
 
   // One coordinate step; returns true when the coefficient moved.
   __device__ __forceinline__ bool cd(int k, const float (&x)[NPL], float al1, float al2, float& dlx) {
+    // scalar state first: these global loads then overlap the dot product and its butterfly reduction
+    const float bk = b[k], xvk = xv[k], pk = vpk(k);
     float g = 0.f;
 #pragma unroll
     for (int j = 0; j < NPL; ++j) g = fmaf(r[j], x[j], g);
     g = warp_sum(g);
-    const float bk = b[k], xvk = xv[k], pk = vpk(k);
     const float u = g + xvk * bk;
     const float au = fabsf(u) - pk * al1;
     const float nb = au > 0.f ? copysignf(au, u) / (xvk + pk * al2) : 0.f;
@@ -132,25 +133,39 @@ struct Warp {
   // Returns false on active-list overflow.
   __device__ bool sweep_screened(float al1, float al2, float& dlx) {
     const int pw = (P.p + 31) >> 5;
-    for (int wd = 0; wd < pw; ++wd) {
-      unsigned bits = ixx[wd];
-      while (bits) {
-        const int k = (wd << 5) + __ffs(bits) - 1;
-        bits &= bits - 1;
-        float x[NPL];
-        load_col(k, x);
-        const bool was_in = bit(inm, k);
-        if (cd(k, x, al1, al2, dlx) && !was_in) {
-          if (nin >= P.nx) return false;
-          __syncwarp();   // every lane has read the membership word before lane 0 rewrites it
-          if (lane == 0) {
-            inm[k >> 5] |= 1u << (k & 31);
-            m[nin] = k;
-          }
-          ++nin;
-          __syncwarp();
-        }
+    // walk the set bits in feature order with the NEXT column already in flight
+    int wd = 0;
+    unsigned bits = 0u;
+    auto next_feature = [&]() -> int {
+      while (bits == 0u) {
+        if (wd >= pw) return -1;
+        bits = ixx[wd++];
       }
+      const int k = ((wd - 1) << 5) + __ffs(bits) - 1;
+      bits &= bits - 1;
+      return k;
+    };
+    int k = next_feature();
+    if (k < 0) return true;
+    float xc[NPL], xn[NPL];
+    load_col(k, xc);
+    while (k >= 0) {
+      const int kn = next_feature();
+      if (kn >= 0) load_col(kn, xn);
+      const bool was_in = bit(inm, k);
+      if (cd(k, xc, al1, al2, dlx) && !was_in) {
+        if (nin >= P.nx) return false;
+        __syncwarp();   // every lane has read the membership word before lane 0 rewrites it
+        if (lane == 0) {
+          inm[k >> 5] |= 1u << (k & 31);
+          m[nin] = k;
+        }
+        ++nin;
+        __syncwarp();
+      }
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) xc[j] = xn[j];
+      k = kn;
     }
     return true;
   }
