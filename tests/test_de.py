@@ -59,16 +59,17 @@ def test_gpu_voom_de_matches_oracle(cohort):
     ref = O.voom_de(c, g)
     res = DE.voom_de(torch.from_numpy(c).cuda(), g)
     assert np.array_equal(res.keep.cpu().numpy(), ref["keep"])
-    assert np.abs(res.norm_factors.cpu().numpy() - ref["norm_factors"]).max() < 3e-4
+    assert np.abs(res.norm_factors.cpu().numpy() - ref["norm_factors"]).max() < 3e-4, 'norm factors'
     eb = ref["ebayes"]
-    assert np.abs(res.logFC - ref["coef"]).max() < 2e-3
-    assert np.abs(res.AveExpr - ref["fit"].amean).max() < 1e-3
-    assert abs(res.s2_prior - eb.s2_prior) / eb.s2_prior < 5e-3
-    assert abs(res.df_prior - eb.df_prior) / eb.df_prior < 2e-2
+    assert np.abs(res.logFC - ref["coef"]).max() < 2e-3, ('logFC', np.abs(res.logFC - ref['coef']).max())
+    assert np.abs(res.AveExpr - ref["fit"].amean).max() < 1e-3, 'AveExpr'
+    assert abs(res.s2_prior - eb.s2_prior) / eb.s2_prior < 5e-3, ('s2_prior', res.s2_prior, eb.s2_prior)
+    assert abs(res.df_prior - eb.df_prior) / eb.df_prior < 2e-2, ('df_prior', res.df_prior, eb.df_prior)
     rel_t = np.abs(res.t - eb.t) / np.maximum(1.0, np.abs(eb.t))
     assert rel_t.max() < 1e-2, rel_t.max()
     big = eb.p_value > 1e-250
-    assert np.abs(np.log(res.P_Value[big]) - np.log(eb.p_value[big])).max() < 0.2
+    dlp = np.abs(np.log(np.maximum(res.P_Value[big], 1e-300)) - np.log(eb.p_value[big]))
+    assert dlp.max() < 0.2, ('log p', dlp.max(), res.P_Value[big][np.argmax(dlp)], eb.p_value[big][np.argmax(dlp)])
     # the DEG sets agree up to genes sitting on the thresholds
     a, b = set(res.deg_order.tolist()), set(ref["deg_index"].tolist())
     assert len(a ^ b) <= max(3, 0.02 * len(b)), (len(a), len(b), len(a ^ b))
@@ -95,10 +96,9 @@ def test_gpu_student_t_pvalues():
     one = torch.ones(G, dtype=torch.float64, device="cuda")
     outs = [torch.empty(G, dtype=torch.float64, device="cuda") for _ in range(5)]
     P = _native.ptr
-    for df in (3.0, 58.0, 375.2):
-        rc = _native.cuda().cml_ebayes(P(coef), P(one), P(one), None, df, G, 1.0, float("inf"), 1e18, 1.0, 0.01,
-                                       *[P(o) for o in outs], _native.stream_ptr())
-        assert rc == 0
+    rc = _native.cuda().cml_ebayes(P(coef), P(one), P(one), None, 58.0, G, 1.0, float("inf"), 1e18, 1.0, 0.01,
+                                   *[P(o) for o in outs], _native.stream_ptr())
+    assert rc == 0
     # infinite prior df -> normal tail
     assert np.allclose(outs[1].cpu().numpy(), 2 * stats.norm.sf(np.abs(t)), rtol=1e-9, atol=1e-300)
     for df0 in (4.0, 300.0):
