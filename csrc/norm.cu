@@ -48,32 +48,36 @@ __global__ void cpm_count_kernel(const int* __restrict__ counts, int G, int S, c
 }
 
 // ---------------------------------------------------------------------------------------- radix select
-__device__ __forceinline__ unsigned fkey(float f) {   // order-preserving float -> uint
-  const unsigned u = __float_as_uint(f);
-  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+// Keys are order-preserving 64-bit images of doubles, so M/A values compare exactly as they do in the float64
+// oracle (float keys would reorder near-ties at the trim boundaries and move the factor by ~1e-3).
+using Key = unsigned long long;
+constexpr Key kKeyMax = ~0ull;
+__device__ __forceinline__ Key dkey(double f) {
+  const Key u = (Key)__double_as_longlong(f);
+  return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
 }
-__device__ __forceinline__ float fkey_inv(unsigned k) {
-  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+__device__ __forceinline__ double dkey_inv(Key k) {
+  return __longlong_as_double((long long)((k & 0x8000000000000000ull) ? (k & 0x7fffffffffffffffull) : ~k));
 }
 
 constexpr int kSelThreads = 512;
 
-// k-th smallest (1-based) key among the valid elements produced by `gen(g, &key)`.
+// k-th smallest (1-based) key among the valid elements produced by `gen(g, &key)`: MSB-first, 8 bits a pass.
 template <typename Gen>
-__device__ unsigned block_radix_select(int G, int k, Gen gen, unsigned* hist /*256*/, unsigned* bcast /*2*/) {
-  unsigned prefix = 0, mask = 0;
+__device__ Key block_radix_select(int G, int k, Gen gen, unsigned* hist /*256*/, unsigned* bcast /*2*/) {
+  Key prefix = 0, mask = 0;
   int remaining = k;
-  for (int shift = 24; shift >= 0; shift -= 8) {
+  for (int shift = 56; shift >= 0; shift -= 8) {
     for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
     __syncthreads();
     for (int g = threadIdx.x; g < G; g += blockDim.x) {
-      unsigned key;
-      if (gen(g, key) && (key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+      Key key;
+      if (gen(g, key) && (key & mask) == prefix) atomicAdd(&hist[(unsigned)(key >> shift) & 255u], 1u);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
       int acc = 0, b = 0;
-      for (; b < 256; ++b) {
+      for (; b < 255; ++b) {
         if (acc + (int)hist[b] >= remaining) break;
         acc += hist[b];
       }
@@ -81,8 +85,8 @@ __device__ unsigned block_radix_select(int G, int k, Gen gen, unsigned* hist /*2
       bcast[1] = remaining - acc;
     }
     __syncthreads();
-    prefix |= bcast[0] << shift;
-    mask |= 255u << shift;
+    prefix |= (Key)bcast[0] << shift;
+    mask |= (Key)255u << shift;
     remaining = (int)bcast[1];
     __syncthreads();
   }
@@ -91,14 +95,14 @@ __device__ unsigned block_radix_select(int G, int k, Gen gen, unsigned* hist /*2
 
 // count(<key), count(==key) and the smallest key strictly greater / largest key strictly smaller
 template <typename Gen>
-__device__ void block_rank_stats(int G, unsigned key0, Gen gen, int* sh_i /*2*/, unsigned* sh_u /*2*/, int& less,
-                                 int& equal, unsigned& next_up, unsigned& next_down) {
-  if (threadIdx.x == 0) { sh_i[0] = 0; sh_i[1] = 0; sh_u[0] = 0xffffffffu; sh_u[1] = 0u; }
+__device__ void block_rank_stats(int G, Key key0, Gen gen, int* sh_i /*2*/, Key* sh_u /*2*/, int& less, int& equal,
+                                 Key& next_up, Key& next_down) {
+  if (threadIdx.x == 0) { sh_i[0] = 0; sh_i[1] = 0; sh_u[0] = kKeyMax; sh_u[1] = 0ull; }
   __syncthreads();
   int l = 0, e = 0;
-  unsigned up = 0xffffffffu, dn = 0u;
+  Key up = kKeyMax, dn = 0ull;
   for (int g = threadIdx.x; g < G; g += blockDim.x) {
-    unsigned key;
+    Key key;
     if (!gen(g, key)) continue;
     l += key < key0;
     e += key == key0;
@@ -123,15 +127,15 @@ __device__ void block_rank_stats(int G, unsigned key0, Gen gen, int* sh_i /*2*/,
 // Smallest value whose average rank >= lo  /  largest value whose average rank <= hi  (as keys).
 template <typename Gen>
 __device__ void trim_thresholds(int G, int n, double lo, double hi, Gen gen, unsigned* hist, unsigned* bc, int* sh_i,
-                                unsigned* sh_u, unsigned& key_lo, unsigned& key_hi) {
+                                Key* sh_u, Key& key_lo, Key& key_hi) {
   int kl = (int)lo; kl = max(1, min(n, kl));
   int kh = (int)hi; kh = max(1, min(n, kh));
   int less, equal;
-  unsigned up, dn;
-  unsigned k0 = block_radix_select(G, kl, gen, hist, bc);
+  Key up, dn;
+  const Key k0 = block_radix_select(G, kl, gen, hist, bc);
   block_rank_stats(G, k0, gen, sh_i, sh_u, less, equal, up, dn);
   key_lo = ((double)less + (equal + 1) * 0.5 >= lo) ? k0 : up;
-  unsigned k1 = block_radix_select(G, kh, gen, hist, bc);
+  const Key k1 = block_radix_select(G, kh, gen, hist, bc);
   block_rank_stats(G, k1, gen, sh_i, sh_u, less, equal, up, dn);
   key_hi = ((double)less + (equal + 1) * 0.5 <= hi) ? k1 : dn;
 }
@@ -141,23 +145,24 @@ __device__ void trim_thresholds(int G, int n, double lo, double hi, Gen gen, uns
 __global__ void __launch_bounds__(kSelThreads) quantile75_kernel(const int* __restrict__ counts, int G, int S,
                                                                   const unsigned char* __restrict__ rowmask, int n_rows,
                                                                   const double* __restrict__ lib, double* __restrict__ f75) {
-  __shared__ unsigned hist[256], bc[2], sh_u[2];
+  __shared__ unsigned hist[256], bc[2];
+  __shared__ Key sh_u[2];
   __shared__ int sh_i[2];
   const int s = blockIdx.x;
-  auto gen = [&](int g, unsigned& key) {
+  auto gen = [&](int g, Key& key) {
     if (rowmask && !rowmask[g]) return false;
-    key = fkey((float)max(counts[(size_t)g * S + s], 0));   // counts order == count/lib order within a sample
+    key = dkey((double)max(counts[(size_t)g * S + s], 0));   // counts order == count/lib order within a sample
     return true;
   };
   const double h = (n_rows - 1) * 0.75;
   const int k = (int)floor(h) + 1;                           // 1-based lower order statistic
-  const unsigned key_a = block_radix_select(G, k, gen, hist, bc);
+  const Key key_a = block_radix_select(G, k, gen, hist, bc);
   int less, equal;
-  unsigned up, dn;
+  Key up, dn;
   block_rank_stats(G, key_a, gen, sh_i, sh_u, less, equal, up, dn);
-  const unsigned key_b = (less + equal >= k + 1 || up == 0xffffffffu) ? key_a : up;
+  const Key key_b = (less + equal >= k + 1 || up == kKeyMax) ? key_a : up;
   if (threadIdx.x == 0) {
-    const double a = fkey_inv(key_a), b = fkey_inv(key_b), frac = h - floor(h);
+    const double a = dkey_inv(key_a), b = dkey_inv(key_b), frac = h - floor(h);
     f75[s] = (a + frac * (b - a)) / lib[s];
   }
 }
@@ -173,26 +178,27 @@ struct TmmArgs {
 };
 
 __global__ void __launch_bounds__(kSelThreads) tmm_kernel(const TmmArgs A) {
-  __shared__ unsigned hist[256], bc[2], sh_u[2];
+  __shared__ unsigned hist[256], bc[2];
+  __shared__ Key sh_u[2];
   __shared__ int sh_i[2];
   __shared__ double red[2][kSelThreads / 32];
   __shared__ float sh_maxabs;
   const int s = blockIdx.x;
   const double nO = A.lib[s], nR = A.lib[A.ref];
-  const float inv_nO = (float)(1.0 / nO), inv_nR = (float)(1.0 / nR);
-  auto values = [&](int g, float& logR, float& absE, double& v) {
+  // same expressions, in the same order, as the float64 oracle: exact ties stay exact ties
+  auto values = [&](int g, double& logR, double& absE, double& v) {
     if (A.rowmask && !A.rowmask[g]) return false;
     const int o = A.counts[(size_t)g * A.S + s], r = A.counts[(size_t)g * A.S + A.ref];
     if (o <= 0 || r <= 0) return false;                      // non-finite M or A
-    const float lo = log2f((float)o * inv_nO), lr = log2f((float)r * inv_nR);
-    logR = lo - lr;
-    absE = 0.5f * (lo + lr);
-    if (!(absE > (float)A.a_cutoff)) return false;
+    const double po = (double)o / nO, pr = (double)r / nR;
+    logR = log2(po / pr);
+    absE = (log2(po) + log2(pr)) * 0.5;
+    if (!(absE > A.a_cutoff)) return false;
     v = (nO - o) / nO / o + (nR - r) / nR / r;
     return true;
   };
-  auto genL = [&](int g, unsigned& key) { float l, a; double v; if (!values(g, l, a, v)) return false; key = fkey(l); return true; };
-  auto genA = [&](int g, unsigned& key) { float l, a; double v; if (!values(g, l, a, v)) return false; key = fkey(a); return true; };
+  auto genL = [&](int g, Key& key) { double l, a, v; if (!values(g, l, a, v)) return false; key = dkey(l); return true; };
+  auto genA = [&](int g, Key& key) { double l, a, v; if (!values(g, l, a, v)) return false; key = dkey(a); return true; };
 
   // n = number of finite genes; max |logR|
   if (threadIdx.x == 0) { sh_i[0] = 0; sh_maxabs = 0.f; }
@@ -200,8 +206,8 @@ __global__ void __launch_bounds__(kSelThreads) tmm_kernel(const TmmArgs A) {
   int cnt = 0;
   float mx = 0.f;
   for (int g = threadIdx.x; g < A.G; g += blockDim.x) {
-    float l, a; double v;
-    if (values(g, l, a, v)) { ++cnt; mx = fmaxf(mx, fabsf(l)); }
+    double l, a, v;
+    if (values(g, l, a, v)) { ++cnt; mx = fmaxf(mx, (float)fabs(l)); }
   }
   cnt = warp_sum(cnt);
   mx = warp_max(mx);
@@ -216,20 +222,17 @@ __global__ void __launch_bounds__(kSelThreads) tmm_kernel(const TmmArgs A) {
   }
   const double loL = floor(n * A.logratio_trim) + 1, hiL = n + 1 - loL;
   const double loS = floor(n * A.sum_trim) + 1, hiS = n + 1 - loS;
-  unsigned kLlo, kLhi, kAlo, kAhi;
+  Key kLlo, kLhi, kAlo, kAhi;
   trim_thresholds(A.G, n, loL, hiL, genL, hist, bc, sh_i, sh_u, kLlo, kLhi);
   trim_thresholds(A.G, n, loS, hiS, genA, hist, bc, sh_i, sh_u, kAlo, kAhi);
 
   double num = 0.0, den = 0.0;
   for (int g = threadIdx.x; g < A.G; g += blockDim.x) {
-    float l, a; double v;
+    double l, a, v;
     if (!values(g, l, a, v)) continue;
-    const unsigned kl = fkey(l), ka = fkey(a);
+    const Key kl = dkey(l), ka = dkey(a);
     if (kl >= kLlo && kl <= kLhi && ka >= kAlo && ka <= kAhi) {
-      // the weighted mean uses the double-precision M value so the factor itself is not float-limited
-      const int o = A.counts[(size_t)g * A.S + s], r = A.counts[(size_t)g * A.S + A.ref];
-      const double lr = log2((o / nO) / (r / nR));
-      num += lr / v;
+      num += l / v;
       den += 1.0 / v;
     }
   }
