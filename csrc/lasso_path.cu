@@ -589,3 +589,112 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// Allocation-free variant of cml_lognet_path.
+//
+// Who needs this: code that is not allowed to create device memory at the point where it wants a fit -
+// a plugin running inside a host application that owns the GPU heap and hands out no allocator, a
+// service whose memory budget is fixed at start-up, a latency-critical loop in which a cudaMalloc (which
+// may synchronise the whole device) is unacceptable, or a process that has already spent its memory on
+// the cohort.  Such callers can still provide inputs and outputs (they own those), but not the solver's
+// per-warp work slab.  Here that slab is a fixed array inside the library image: it exists on every GPU
+// that loads libcml_b200.so from load until exit, costs kLognetStaticBytes there, and nothing is ever
+// allocated or freed by this entry point (no cudaMalloc / cudaFree / allocating library call).
+//
+// Consequences the caller must know:
+//   * Capacity.  One resident warp needs 3*p floats.  The number of replicates fitted concurrently is
+//     floor(kLognetStaticBytes / (12*p)) (at most the usual resident-warp count); further replicates of the
+//     batch are taken in turn by the same warps, so any B works but throughput drops as p grows.
+//     p > kLognetStaticBytes/12 (699,050 genes) cannot run at all and is rejected with CML_E2BIG.
+//   * Sharing.  Every call on a device uses the SAME array.  Two calls that may execute at the same time
+//     on one GPU (different streams, different host threads) would overwrite each other's coefficients:
+//     serialise them.  Calls on different GPUs are independent (each device has its own copy).
+//   * Stale contents.  The array keeps whatever the previous call left.  That is harmless and nothing is
+//     cleared: the solver writes every slab word (coefficient, curvature, gradient of each gene) during
+//     its per-replicate set-up pass before it reads any of them.
+//   * First call.  In host code the array's name is only a handle, not a device address, so the first
+//     call on each device (with that device current) asks the runtime for the real address
+//     (cudaGetSymbolAddress) and caches it.  Make that first call outside any stream capture.
+#include <mutex>
+
+namespace cml {
+namespace {
+
+constexpr size_t kLognetStaticBytes = 8u << 20;                         // 8 MiB per GPU
+constexpr size_t kLognetStaticFloats = kLognetStaticBytes / sizeof(float);
+static __device__ __align__(256) float g_lognet_static_scratch[kLognetStaticFloats];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+float* g_static_addr[kMaxDevices] = {nullptr};
+
+// Device address of the slab on the CURRENT device (resolved once per device, under a lock).
+int lognet_static_scratch(float** out) {
+  int dev = -1;
+  CML_CUDA(cudaGetDevice(&dev));
+  CML_REQUIRE(dev >= 0 && dev < kMaxDevices, CML_EINVAL, "cml_lognet_path_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_addr[dev] == nullptr) {
+    float* ptr = nullptr;
+    CML_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_lognet_static_scratch));
+    CML_REQUIRE(ptr != nullptr, CML_EINVAL, "cml_lognet_path_static: runtime returned a null address for the scratch array");
+    g_static_addr[dev] = ptr;
+  }
+  *out = g_static_addr[dev];
+  return 0;
+}
+
+}  // namespace
+}  // namespace cml
+
+extern "C" {
+
+size_t cml_lognet_static_scratch_bytes(void) { return cml::kLognetStaticBytes; }
+
+int cml_lognet_path_static(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
+                           long long y_stride, const float* w, const unsigned char* ju, long long ju_stride,
+                           const float* vp, const float* lam, float alpha, float thresh, int intercept, int kopt,
+                           int maxit, int* m_out, float* ca_out, int* kin_out, float* a0_out, float* dev_out,
+                           float* eta_out, float* freq_out, float* nulldev_out, int* npasses_out, int* lmu_out,
+                           int* jerr_out, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(B > 0 && n > 0 && p > 0 && nlam > 0 && nx > 0, CML_EINVAL, "cml_lognet_path_static: empty problem");
+  const size_t per_warp = 3 * static_cast<size_t>(p);
+  CML_REQUIRE(per_warp <= kLognetStaticFloats, CML_E2BIG,
+              "cml_lognet_path_static: p=%d genes need %zu bytes of work space per replicate but the built-in array holds "
+              "%zu bytes (max p = %zu); use cml_lognet_path with caller-provided scratch",
+              p, per_warp * sizeof(float), kLognetStaticBytes, kLognetStaticFloats / 3);
+  CML_REQUIRE(n_pad == cml_lognet_n_pad(n) || (n_pad % 32 == 0 && n_pad >= n && cml_lognet_n_pad(n_pad) == n_pad),
+              CML_EINVAL, "cml_lognet_path_static: n_pad=%d is not a supported padded size for n=%d (max 1024)", n_pad, n);
+  const size_t smem = smem_bytes(p, nx, n_pad);
+  CML_REQUIRE(smem <= 48 * 1024, CML_E2BIG,
+              "cml_lognet_path_static: p=%d nx=%d n_pad=%d needs %zu B shared memory per warp (max 48 KB)", p, nx, n_pad, smem);
+  float* slab = nullptr;
+  const int rc = lognet_static_scratch(&slab);
+  if (rc) return rc;
+  const size_t fit = kLognetStaticFloats / per_warp;                    // warps whose slabs fit side by side
+  int grid = cml_lognet_grid(B, n_pad);
+  if (static_cast<size_t>(grid) > fit) grid = static_cast<int>(fit);
+  LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, ju, ju_stride, vp, lam, alpha, thresh, intercept,
+                 kopt, maxit, slab, m_out, ca_out, kin_out, a0_out, dev_out, eta_out,
+                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (n_pad / 32) {
+    case 1: return launch<1>(P, grid, smem, st);
+    case 2: return launch<2>(P, grid, smem, st);
+    case 3: return launch<3>(P, grid, smem, st);
+    case 4: return launch<4>(P, grid, smem, st);
+    case 5: return launch<5>(P, grid, smem, st);
+    case 6: return launch<6>(P, grid, smem, st);
+    case 8: return launch<8>(P, grid, smem, st);
+    case 12: return launch<12>(P, grid, smem, st);
+    case 16: return launch<16>(P, grid, smem, st);
+    case 24: return launch<24>(P, grid, smem, st);
+    case 32: return launch<32>(P, grid, smem, st);
+  }
+  set_error("cml_lognet_path_static: unsupported n_pad %d", n_pad);
+  return CML_EINVAL;
+}
+
+}  // extern "C"

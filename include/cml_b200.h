@@ -50,6 +50,29 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
                     float* a0_out, float* dev_out, float* eta_out, float* freq_out, float* nulldev_out,
                     int* npasses_out, int* lmu_out, int* jerr_out, void* stream);
 
+/* ---- allocation-free variant of cml_lognet_path -----------------------------------------------------
+ * No counterpart in the reference (it has no device code and no memory management of its own).
+ * For callers that may not create device memory when they need a fit: a plugin inside an application
+ * that owns the GPU heap, a service with a memory budget frozen at start-up, a latency-critical loop
+ * where cudaMalloc's device-wide synchronisation is not acceptable.  Same arguments and results as
+ * cml_lognet_path minus (scratch, scratch_bytes): the per-warp work space is a fixed array of
+ * cml_lognet_static_scratch_bytes() (8 MiB) inside the library image, present on every GPU that loads the
+ * library until the process exits.  Nothing is allocated or freed by the call.
+ *   - limit: 12*p bytes per concurrently fitted replicate must fit, so p <= 699,050 genes; larger p returns
+ *     CML_E2BIG (7) with a message.  Concurrency is min(resident warps, 8 MiB / (12*p)); any B is accepted.
+ *   - the array is shared by all calls on a device and keeps the previous call's contents; the solver
+ *     overwrites every word before reading it, so nothing is cleared - but two calls that can run at the
+ *     same time on one GPU race on it: serialise them (one stream, or events).
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress, with that
+ *     device current) and caches it; make that first call outside any stream capture.                  */
+size_t cml_lognet_static_scratch_bytes(void);
+int cml_lognet_path_static(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
+                           long long y_stride, const float* w, const unsigned char* ju, long long ju_stride,
+                           const float* vp, const float* lam, float alpha, float thresh, int intercept, int kopt,
+                           int maxit, int* m_out, float* ca_out, int* kin_out, float* a0_out, float* dev_out,
+                           float* eta_out, float* freq_out, float* nulldev_out, int* npasses_out, int* lmu_out,
+                           int* jerr_out, void* stream);
+
 /* ---- K13: replicate batching --------------------------------------------------------------------
  * Weight rows for bootstrap (mode 0), k-of-n subsample (mode 1) and repeated k-fold (mode 2, k = folds)
  * replicates, generated on the device with a counter-based RNG.  Replaces the sequential refit loops
