@@ -1,0 +1,482 @@
+"""Random forests and gradient-boosted trees on the batched histogram tree engine (csrc/trees.cu).
+
+* :class:`RandomForest`    - Breiman RF as used at cml_targetaml_seanalysis.Rmd:1037-1050 (n-of-n bootstrap,
+  ``mtry = floor(sqrt(p))``, ``nodesize = 1``, Gini splits, OOB error, MeanDecreaseGini, proximity) and the
+  depth-limited sklearn variant of scripts/model_comp.py:9.
+* :class:`GradientBoosting` - second-order (xgboost: model_comp.py:7, cml_targetaml_seanalysis.Rmd:1164-1186)
+  and first-order stochastic (sklearn ``GradientBoostingClassifier``: model_comp.py:8) boosting with logistic
+  loss and gain / cover / frequency importance.
+
+Every tree of a batch grows in the same launches (one per level).  With n <= 256 samples features are
+rank-binned, so the split search equals the exact greedy search of the CPU libraries.  CPU tensors run a
+NumPy restatement of the same level-wise algorithm (``_grow_numpy``), which is also the test oracle.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from .. import _native
+
+_I, _F, _P, _ULL = ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_ulonglong
+_native.register_signature("cml_rank_bins", [_P, _I, _I, _I, _P, _I, _P, _P, _P])
+_native.register_signature("cml_apply_bins", [_P, _I, _I, _I, _P, _P, _P, _I, _P])
+_native.register_signature("cml_forest_level", [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P,
+                                                _P, _P, _P, _P, _P, _P, _I, _I, _F, _F, _F, _F, _F, _F, _ULL, _P, _P, _P,
+                                                _P, _P])
+_native.register_signature("cml_forest_predict", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P])
+_native.register_signature("cml_forest_proximity", [_P, _I, _I, _P, _P])
+
+GINI, NEWTON = 0, 1
+
+
+# ------------------------------------------------------------------------------------------------ binning
+@dataclass
+class Binner:
+    """Per-feature bins.  ``edges[f, b]`` is the value bin ``b`` stands for (distinct values when n <= 256,
+    quantile representatives otherwise); new data are binned at the midpoints between neighbours."""
+    edges: torch.Tensor      # [p, 256] fp32
+    n_edges: torch.Tensor    # [p] int32
+    max_bin: int
+
+    @staticmethod
+    def fit(x: torch.Tensor, max_bin: int = 256):
+        """x: samples x genes.  Returns (binner, bins[p, n_pad] uint8)."""
+        n, p = x.shape
+        n_pad = (n + 3) // 4 * 4
+        xt = x.t().contiguous().float()
+        if n <= 256 and x.is_cuda:
+            bins = torch.empty(p, n_pad, dtype=torch.uint8, device=x.device)
+            edges = torch.full((p, 256), float("inf"), dtype=torch.float32, device=x.device)
+            n_edges = torch.empty(p, dtype=torch.int32, device=x.device)
+            rc = _native.cuda().cml_rank_bins(_native.ptr(xt), p, n, n, _native.ptr(bins), n_pad, _native.ptr(edges),
+                                              _native.ptr(n_edges), _native.stream_ptr())
+            _native.check(rc, "cml_rank_bins")
+            return Binner(edges, n_edges, int(n_edges.max().item())), bins
+        xs = xt.double()
+        if n <= 256:
+            reps = [torch.unique(xs[f]) for f in range(p)]
+        else:
+            qs = torch.linspace(0, 1, max_bin, dtype=torch.float64, device=x.device)
+            sub = xs if n <= 100000 else xs[:, torch.randperm(n, device=x.device)[:100000]]
+            qv = torch.quantile(sub, qs, dim=1).t()
+            reps = [torch.unique(qv[f]) for f in range(p)]
+        edges = torch.full((p, 256), float("inf"), dtype=torch.float32, device=x.device)
+        n_edges = torch.zeros(p, dtype=torch.int32, device=x.device)
+        for f, r in enumerate(reps):
+            edges[f, : r.numel()] = r.float()
+            n_edges[f] = r.numel()
+        b = Binner(edges, n_edges, max(2, int(n_edges.max().item())))
+        return b, b.transform(x)
+
+    def transform(self, x: torch.Tensor) -> torch.Tensor:
+        m, p = x.shape
+        m_pad = (m + 3) // 4 * 4
+        xt = x.t().contiguous().float()
+        if x.is_cuda:
+            bins = torch.empty(p, m_pad, dtype=torch.uint8, device=x.device)
+            rc = _native.cuda().cml_apply_bins(_native.ptr(xt), p, m, m, _native.ptr(self.edges), _native.ptr(self.n_edges),
+                                               _native.ptr(bins), m_pad, _native.stream_ptr())
+            _native.check(rc, "cml_apply_bins")
+            return bins
+        bins = torch.zeros(p, m_pad, dtype=torch.uint8)
+        e, ne, xn, out = self.edges.numpy(), self.n_edges.numpy(), xt.numpy(), bins.numpy()
+        for f in range(p):
+            mids = 0.5 * (e[f, : ne[f] - 1] + e[f, 1: ne[f]])
+            out[f, :m] = np.searchsorted(mids, xn[f], side="right")
+        return bins
+
+
+# ------------------------------------------------------------------------------------------------ tree batch
+@dataclass
+class TreeBatch:
+    feat: torch.Tensor       # [T, max_nodes] int32, -1 = leaf
+    thr: torch.Tensor        # [T, max_nodes] int32 (go left iff bin <= thr)
+    left: torch.Tensor       # [T, max_nodes] int32 (right child = left + 1)
+    value: torch.Tensor      # [T, max_nodes] fp32
+    gain: torch.Tensor
+    cover: torch.Tensor
+    node_count: torch.Tensor # [T] int32
+
+
+def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: Optional[torch.Tensor] = None,
+         criterion: int = GINI, mtry: int = 0, max_depth: int = 64, max_nodes: Optional[int] = None, max_bin: int = 256,
+         lam: float = 0.0, gamma: float = 0.0, min_child_weight: float = 0.0, min_samples_leaf: float = 1.0,
+         min_samples_split: float = 2.0, eta: float = 1.0, seed: int = 0, feature_mask: Optional[torch.Tensor] = None,
+         importance: Optional[Dict[str, torch.Tensor]] = None, in_tree: Optional[torch.Tensor] = None) -> TreeBatch:
+    """Grow ``T = s0.shape[0]`` trees.  ``in_tree`` ([T, n] bool) restricts each tree to a sample subset
+    (bootstrap members / row subsample); samples outside never enter the root."""
+    T = s0.shape[0]
+    p, n_pad = bins.shape
+    dev = bins.device
+    if max_nodes is None:
+        max_nodes = min(2 * n + 1, 2 ** (min(max_depth, 20) + 1) - 1)
+    if not bins.is_cuda:
+        return _grow_numpy(bins, n, s0, s1, s2, criterion, mtry, max_depth, max_nodes, max_bin, lam, gamma, min_child_weight,
+                           min_samples_leaf, min_samples_split, eta, seed, feature_mask, importance, in_tree)
+    i32 = dict(dtype=torch.int32, device=dev)
+    f32 = dict(dtype=torch.float32, device=dev)
+    if in_tree is None:
+        in_tree = torch.ones(T, n, dtype=torch.bool, device=dev)
+    order = torch.argsort((~in_tree).to(torch.uint8), dim=1, stable=True).to(torch.int32).contiguous()
+    counts = in_tree.sum(1).to(torch.int32)
+    order2 = order.clone()
+    feat = torch.full((T, max_nodes), -1, **i32)
+    thr = torch.zeros(T, max_nodes, **i32)
+    left = torch.full((T, max_nodes), -1, **i32)
+    value = torch.zeros(T, max_nodes, **f32)
+    gain = torch.zeros(T, max_nodes, **f32)
+    cover = torch.zeros(T, max_nodes, **f32)
+    node_count = torch.ones(T, **i32)
+    frontier = torch.zeros(T, 5, **i32)
+    frontier[:, 0] = torch.arange(T, **i32)
+    frontier[:, 3] = counts
+    nf = T
+    next_count = torch.zeros(1, **i32)
+    lb = _native.cuda()
+    P = _native.ptr
+    s0 = s0.float().contiguous()
+    s1 = s1.float().contiguous()
+    s2c = s2.float().contiguous() if s2 is not None else None
+    fm = feature_mask.to(device=dev, dtype=torch.uint8).contiguous() if feature_mask is not None else None
+    imp = importance or {}
+    depth = 0
+    while nf > 0 and depth <= max_depth:
+        nxt = torch.empty(2 * nf, 5, **i32)
+        next_count.zero_()
+        rc = lb.cml_forest_level(P(bins), p, n, n_pad, max_bin, P(s0), P(s1), P(s2c), T, max_nodes, max_depth, P(order),
+                                 P(order2), P(frontier), nf, P(nxt), P(next_count), P(node_count), P(feat), P(thr), P(left),
+                                 P(value), P(gain), P(cover), criterion, int(mtry), float(lam), float(gamma),
+                                 float(min_child_weight), float(min_samples_leaf), float(min_samples_split), float(eta),
+                                 seed & (2**64 - 1), P(fm), P(imp.get("gain")), P(imp.get("cover")), P(imp.get("freq")),
+                                 _native.stream_ptr())
+        _native.check(rc, "cml_forest_level")
+        nf = int(next_count.item())
+        frontier = nxt[:nf].contiguous()
+        order, order2 = order2, order
+        depth += 1
+    return TreeBatch(feat, thr, left, value, gain, cover, node_count)
+
+
+def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):
+    """(leaf[T, m] int32, value[T, m] fp32) for samples binned as ``bins[p, m_pad]``."""
+    T, max_nodes = trees.feat.shape
+    if not bins.is_cuda:
+        return _predict_numpy(trees, bins, m)
+    leaf = torch.empty(T, m, dtype=torch.int32, device=bins.device)
+    val = torch.empty(T, m, dtype=torch.float32, device=bins.device)
+    P = _native.ptr
+    rc = _native.cuda().cml_forest_predict(P(bins), m, bins.shape[1], T, max_nodes, P(trees.feat), P(trees.thr), P(trees.left),
+                                           P(trees.value), P(leaf), P(val), _native.stream_ptr())
+    _native.check(rc, "cml_forest_predict")
+    return leaf, val
+
+
+# ------------------------------------------------------------------------------------------------ NumPy restatement
+def _score(crit, a, b, lam):
+    if crit == GINI:
+        return np.where(b > 0, (a * a + (b - a) * (b - a)) / np.where(b > 0, b, 1), 0.0)
+    return a * a / (b + lam)
+
+
+_M64 = (1 << 64) - 1
+
+
+def _mix(z):
+    z = (z + 0x9E3779B97F4A7C15) & _M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def _node_candidates(seed, tree, node, p, mtry, fmask):
+    """Same counter-based sampling as the kernel (splitmix64), so CPU and GPU trees see the same candidates."""
+    base = _mix((seed & _M64) ^ ((0x9E3779B97F4A7C15 * (tree + 1)) & _M64) ^ ((0xC2B2AE3D27D4EB4F * (node + 1)) & _M64))
+    got, seen, ctr = [], set(), 0
+    while len(got) < mtry and ctr < 64 * p:
+        f = ((_mix((base + ctr) & _M64) >> 32) * p) >> 32
+        ctr += 1
+        if f in seen or (fmask is not None and not fmask[f]):
+            continue
+        seen.add(f)
+        got.append(f)
+    return got
+
+
+def _grow_numpy(bins, n, s0, s1, s2, crit, mtry, max_depth, max_nodes, max_bin, lam, gamma, mcw, msl, mss, eta, seed, fmask,
+                importance, in_tree):
+    B = bins.numpy()
+    S0, S1 = s0.double().numpy(), s1.double().numpy()
+    S2 = s2.double().numpy() if s2 is not None else None
+    T, p = S0.shape[0], B.shape[0]
+    fm = fmask.numpy().astype(bool) if fmask is not None else None
+    feat = np.full((T, max_nodes), -1, np.int32)
+    thr = np.zeros((T, max_nodes), np.int32)
+    left = np.full((T, max_nodes), -1, np.int32)
+    value = np.zeros((T, max_nodes), np.float32)
+    gain = np.zeros((T, max_nodes), np.float32)
+    cover = np.zeros((T, max_nodes), np.float32)
+    ncount = np.ones(T, np.int32)
+    all_feats = mtry <= 0 or mtry >= p
+    for t in range(T):
+        members = np.arange(n) if in_tree is None else np.flatnonzero(in_tree[t].numpy())
+        frontier = [(0, members, 0)]
+        while frontier:
+            nxt = []
+            for node, idx, depth in frontier:
+                a, b = S0[t, idx].sum(), S1[t, idx].sum()
+                if crit == GINI:
+                    v = a / b if b > 0 else 0.0
+                elif S2 is not None:
+                    c = S2[t, idx].sum()
+                    v = eta * (a / c if c > 1e-30 else 0.0)
+                else:
+                    v = -eta * a / (b + lam)
+                value[t, node], cover[t, node] = v, b
+                pure = crit == GINI and (a <= 0 or a >= b)
+                if not (depth < max_depth and idx.size >= mss and idx.size >= 2 and not pure and b >= 2 * mcw):
+                    continue
+                cands = [f for f in range(p) if fm is None or fm[f]] if all_feats else _node_candidates(seed, t, node, p, mtry, fm)
+                parent = float(_score(crit, np.float64(a), np.float64(b), lam))
+                best = (-np.inf, -1, -1)
+                for f in cands:
+                    bb = B[f, idx]
+                    h0 = np.bincount(bb, weights=S0[t, idx], minlength=max_bin)
+                    h1 = np.bincount(bb, weights=S1[t, idx], minlength=max_bin)
+                    c0, c1 = np.cumsum(h0), np.cumsum(h1)
+                    r0, r1 = a - c0, b - c1
+                    ok = (h1 > 0) & (r1 > 0) & (c1 >= mcw) & (r1 >= mcw) & (c1 >= msl) & (r1 >= msl)
+                    ok[max_bin - 1:] = False
+                    if not ok.any():
+                        continue
+                    g = np.where(ok, _score(crit, c0, c1, lam) + _score(crit, r0, r1, lam) - parent, -np.inf)
+                    bi = int(np.argmax(g))
+                    if g[bi] > best[0] or (g[bi] == best[0] and (f < best[1] or best[1] < 0)):
+                        best = (float(g[bi]), f, bi)
+                bg, bf, bbin = best
+                real = bg - gamma if crit == NEWTON else bg
+                if bf < 0 or not real > 1e-7 * max(1.0, abs(parent)):
+                    continue
+                child = int(ncount[t])
+                if child + 1 >= max_nodes:
+                    continue
+                ncount[t] += 2
+                goes_left = B[bf, idx] <= bbin
+                feat[t, node], thr[t, node], left[t, node], gain[t, node] = bf, bbin, child, real
+                if importance is not None:
+                    importance["gain"][bf] += real
+                    importance["cover"][bf] += b
+                    importance["freq"][bf] += 1
+                nxt.append((child, idx[goes_left], depth + 1))
+                nxt.append((child + 1, idx[~goes_left], depth + 1))
+            frontier = nxt
+    t_ = torch.from_numpy
+    return TreeBatch(t_(feat), t_(thr), t_(left), t_(value), t_(gain), t_(cover), t_(ncount))
+
+
+def _predict_numpy(trees: TreeBatch, bins, m):
+    B = bins.numpy()
+    feat, thr, left, value = (x.numpy() for x in (trees.feat, trees.thr, trees.left, trees.value))
+    T = feat.shape[0]
+    leaf = np.zeros((T, m), np.int32)
+    cols = np.arange(m)
+    for t in range(T):
+        node = np.zeros(m, np.int64)
+        while True:
+            f = feat[t, node]
+            ia = np.flatnonzero(f >= 0)
+            if ia.size == 0:
+                break
+            go_right = B[f[ia], cols[ia]] > thr[t, node[ia]]
+            node[ia] = left[t, node[ia]] + go_right
+        leaf[t] = node
+    val = np.take_along_axis(value, leaf.astype(np.int64), axis=1)
+    return torch.from_numpy(leaf), torch.from_numpy(val.astype(np.float32))
+
+
+# ------------------------------------------------------------------------------------------------ random forest
+@dataclass
+class RandomForest:
+    """Binary-classification random forest (Breiman)."""
+    n_trees: int = 500
+    mtry: Optional[int] = None            # default floor(sqrt(p)) like randomForest
+    max_depth: int = 64
+    min_samples_leaf: int = 1             # randomForest nodesize
+    bootstrap: bool = True
+    seed: int = 20                        # the reference's set.seed(20), cml_targetaml_seanalysis.Rmd:1026
+    proximity: bool = False
+    tree_batch: int = 2048
+
+    binner: Binner = field(default=None, repr=False)
+    trees: list = field(default_factory=list, repr=False)
+    importance_: torch.Tensor = field(default=None, repr=False)      # MeanDecreaseGini
+    oob_error_: float = None
+    oob_votes_: torch.Tensor = field(default=None, repr=False)
+    proximity_: torch.Tensor = field(default=None, repr=False)
+    confusion_oob_: torch.Tensor = field(default=None, repr=False)
+
+    def fit(self, x: torch.Tensor, y: torch.Tensor) -> "RandomForest":
+        from ..ops.metrics import confusion_matrix
+        from ..ops.replicate import replicate_weights
+        n, p = x.shape
+        dev = x.device
+        self.binner, bins = Binner.fit(x)
+        mtry = self.mtry if self.mtry is not None else max(1, int(np.floor(np.sqrt(p))))
+        yf = y.float().to(dev)
+        imp = {k: torch.zeros(p, dtype=torch.float32, device=dev) for k in ("gain", "cover", "freq")}
+        votes1 = torch.zeros(n, device=dev)
+        nvote = torch.zeros(n, device=dev)
+        prox = torch.zeros(n, n, device=dev) if self.proximity else None
+        self.trees = []
+        done = 0
+        while done < self.n_trees:
+            T = min(self.tree_batch, self.n_trees - done)
+            if self.bootstrap:
+                w = replicate_weights(T, n, mode="bootstrap", seed=self.seed, device=dev, rep0=done)[:, :n].contiguous()
+            else:
+                w = torch.ones(T, n, device=dev)
+            tb = grow(bins, n, w * yf[None, :], w, criterion=GINI, mtry=mtry, max_depth=self.max_depth,
+                      max_bin=self.binner.max_bin, min_samples_leaf=float(self.min_samples_leaf), seed=self.seed + done,
+                      importance=imp, in_tree=w > 0)
+            self.trees.append(tb)
+            leaf, val = predict_leaves(tb, bins, n)
+            vote = (val > 0.5).float()
+            oob = (w == 0).float()
+            votes1 += (vote * oob).sum(0)
+            nvote += oob.sum(0)
+            if prox is not None:
+                if dev.type == "cuda":
+                    rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), T, n, _native.ptr(prox),
+                                                             _native.stream_ptr())
+                    _native.check(rc, "cml_forest_proximity")
+                else:
+                    prox += (leaf[:, :, None] == leaf[:, None, :]).float().sum(0)
+            done += T
+        self.importance_ = imp["gain"] / self.n_trees
+        self.importance_cover_ = imp["cover"]
+        self.importance_freq_ = imp["freq"]
+        frac = votes1 / nvote.clamp_min(1)
+        self.oob_votes_ = frac
+        pred = (frac > 0.5).float()
+        has = nvote > 0
+        self.oob_error_ = float((pred[has] != yf[has]).float().mean())
+        self.confusion_oob_ = confusion_matrix(pred[has], yf[has])
+        if prox is not None:
+            self.proximity_ = prox / self.n_trees
+        return self
+
+    def _accumulate(self, x, fn):
+        bins = self.binner.transform(x)
+        m = x.shape[0]
+        acc = torch.zeros(m, device=x.device)
+        for tb in self.trees:
+            _, val = predict_leaves(tb, bins, m)
+            acc += fn(val).sum(0)
+        return acc / self.n_trees
+
+    def predict_proba(self, x: torch.Tensor) -> torch.Tensor:
+        """Fraction of trees voting class 1 (randomForest ``type="prob"``)."""
+        return self._accumulate(x, lambda v: (v > 0.5).float())
+
+    def predict_proba_mean(self, x: torch.Tensor) -> torch.Tensor:
+        """Mean of per-tree leaf class fractions (sklearn ``predict_proba``)."""
+        return self._accumulate(x, lambda v: v)
+
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        return (self.predict_proba(x) > 0.5).long()
+
+
+# ------------------------------------------------------------------------------------------------ gradient boosting
+@dataclass
+class GradientBoosting:
+    """Logistic-loss tree boosting.  ``mode='xgboost'``: second order with L2 ``reg_lambda`` (XGBClassifier as
+    used in model_comp.py:7).  ``mode='sklearn'``: first-order residual fitting with friedman-MSE splits, Newton
+    leaf values, row ``subsample`` and per-node ``max_features`` (GradientBoostingClassifier, model_comp.py:8)."""
+    n_estimators: int = 100
+    learning_rate: float = 0.3
+    max_depth: int = 6
+    reg_lambda: float = 1.0
+    gamma: float = 0.0
+    min_child_weight: float = 1.0
+    subsample: float = 1.0
+    max_features: Optional[object] = None     # None | 'log2' | 'sqrt' | int
+    min_samples_leaf: int = 1
+    mode: str = "xgboost"
+    seed: int = 8
+    base_score: float = 0.5
+
+    binner: Binner = field(default=None, repr=False)
+    trees: list = field(default_factory=list, repr=False)
+    train_error_: list = field(default_factory=list, repr=False)
+    importance_: Dict[str, torch.Tensor] = field(default=None, repr=False)
+    init_: float = 0.0
+
+    def _mtry(self, p):
+        mf = self.max_features
+        if mf is None:
+            return 0
+        if mf == "log2":
+            return max(1, int(np.log2(p)))
+        if mf == "sqrt":
+            return max(1, int(np.sqrt(p)))
+        return int(mf)
+
+    def fit(self, x: torch.Tensor, y: torch.Tensor) -> "GradientBoosting":
+        from ..ops.replicate import replicate_weights
+        n, p = x.shape
+        dev = x.device
+        self.binner, bins = Binner.fit(x)
+        yf = y.float().to(dev)
+        imp = {k: torch.zeros(p, dtype=torch.float32, device=dev) for k in ("gain", "cover", "freq")}
+        if self.mode == "xgboost":
+            self.init_ = float(np.log(self.base_score / (1 - self.base_score)))
+        else:
+            pr = float(yf.mean())
+            self.init_ = float(np.log(pr / (1 - pr)))
+        margin = torch.full((n,), self.init_, device=dev)
+        self.trees, self.train_error_ = [], []
+        k_sub = max(1, int(round(self.subsample * n)))
+        for r in range(self.n_estimators):
+            pr = torch.sigmoid(margin)
+            in_tree = None
+            if self.subsample < 1.0:
+                in_tree = replicate_weights(1, n, mode="subsample", k=k_sub, seed=self.seed, device=dev, rep0=r)[:, :n] > 0
+            if self.mode == "xgboost":
+                g, h = (pr - yf)[None, :], (pr * (1 - pr))[None, :]
+                tb = grow(bins, n, g, h, criterion=NEWTON, mtry=self._mtry(p), max_depth=self.max_depth,
+                          max_bin=self.binner.max_bin, lam=self.reg_lambda, gamma=self.gamma,
+                          min_child_weight=self.min_child_weight, min_samples_leaf=0.0, eta=self.learning_rate,
+                          seed=self.seed + r, importance=imp, in_tree=in_tree)
+            else:
+                res = (yf - pr)[None, :]
+                tb = grow(bins, n, res, torch.ones_like(res), s2=(pr * (1 - pr))[None, :], criterion=NEWTON,
+                          mtry=self._mtry(p), max_depth=self.max_depth, max_bin=self.binner.max_bin, lam=0.0,
+                          min_samples_leaf=float(self.min_samples_leaf), eta=self.learning_rate, seed=self.seed + r,
+                          importance=imp, in_tree=in_tree)
+            self.trees.append(tb)
+            _, val = predict_leaves(tb, bins, n)
+            margin = margin + val[0]
+            self.train_error_.append(float(((margin > 0).float() != yf).float().mean()))
+        tot = {k: float(v.sum()) for k, v in imp.items()}
+        self.importance_ = {"gain": imp["gain"] / max(tot["gain"], 1e-30), "cover": imp["cover"] / max(tot["cover"], 1e-30),
+                            "frequency": imp["freq"] / max(tot["freq"], 1e-30)}
+        return self
+
+    def decision_function(self, x: torch.Tensor, n_trees: Optional[int] = None) -> torch.Tensor:
+        bins = self.binner.transform(x)
+        m = x.shape[0]
+        margin = torch.full((m,), self.init_, device=x.device)
+        for tb in self.trees[: n_trees or len(self.trees)]:
+            _, val = predict_leaves(tb, bins, m)
+            margin = margin + val.sum(0)
+        return margin
+
+    def predict_proba(self, x: torch.Tensor, n_trees: Optional[int] = None) -> torch.Tensor:
+        return torch.sigmoid(self.decision_function(x, n_trees))
+
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        return (self.decision_function(x) > 0).long()

@@ -98,6 +98,54 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
 int cml_to_bf16_rownorm(const float* x, long long ldx, void* y_bf16, long long ldy, float* norm, int rows, int cols,
                         float shift, const float* col_shift, const float* col_scale, void* stream);
 
+/* ---- K1-K3: count normalisation ------------------------------------------------------------------------
+ * Replaces edgeR DGEList -> cpm filter -> calcNormFactors(TMM) -> cpm(log=TRUE, prior.count=1)
+ * (JSmith_code/Normalization_and_Batch_Effect_Investigation.Rmd:49-63; Differential_Expression_and_Lasso.Rmd:217-227).
+ * counts: int32 [G][S] gene-major.                                                                       */
+int cml_lib_sizes(const int* counts, int G, int S, unsigned long long* lib_out, void* stream);
+int cml_cpm_pass_count(const int* counts, int G, int S, const double* lib, double min_cpm, int* npass, void* stream);
+int cml_nonzero_rows(const int* counts, int G, int S, unsigned char* mask, void* stream);
+int cml_quantile75(const int* counts, int G, int S, const unsigned char* rowmask, int n_rows, const double* lib,
+                   double* f75, void* stream);
+int cml_tmm_factors(const int* counts, int G, int S, const unsigned char* rowmask, const double* lib, int ref,
+                    double logratio_trim, double sum_trim, double a_cutoff, double* factor, void* stream);
+int cml_logcpm(const int* counts, int G, int S, const int* rows, int n_rows, const double* lib_eff, double prior,
+               double mean_lib, float* out, float* out_t, long long ld_t, void* stream);
+
+/* ---- K4-K5: limma-voom ------------------------------------------------------------------------------------
+ * Replaces voom -> lmFit -> contrasts.fit -> eBayes (JSmith_code/Limma_Voom_DE_Function.R:36-41). k <= 8.   */
+int cml_voom_ols(const int* counts, int G, int S, int k, const double* lib_eff, const double* design, const double* hat,
+                 double* coef_ols, double* sigma_ols, double* amean, float* E, void* stream);
+int cml_lowess_points(const double* x, const double* y, const double* rw, int n, int ns, const int* pts, int m,
+                      double* fit, void* stream);
+int cml_voom_wls(const int* counts, int G, int S, int k, const double* lib_eff, const double* design,
+                 const double* coef_ols, const double* trend_x, const double* trend_y, int m, const double* contrast,
+                 double* coef, double* stdev_unscaled, double* sigma, double* coef_c, double* su_c, float* weights,
+                 void* stream);
+int cml_ebayes(const double* coef, const double* su, const double* sigma, const double* df_res, double df_res_scalar,
+               int G, double s20, double df0, double df_total_cap, double var_prior, double proportion, double* t_out,
+               double* p_out, double* lods_out, double* s2post_out, double* dft_out, void* stream);
+
+/* ---- K8/K9: batched histogram trees ---------------------------------------------------------------------
+ * Replaces randomForest (cml_targetaml_seanalysis.Rmd:1037-1050), xgboost (:1164-1186; scripts/model_comp.py:7) and
+ * sklearn GradientBoosting/RandomForest (scripts/model_comp.py:8-9).  bins: uint8 [p][n_pad] feature-major.
+ * cml_forest_level grows every open node of a batch of T trees by one level; frontier records are 5 ints
+ * (tree, node, start, count, depth); *next_count must be zero on entry.  criterion 0 = gini, 1 = newton.   */
+int cml_rank_bins(const float* xt, int p, int n, int ld, unsigned char* bins, int n_pad, float* edges, int* n_edges,
+                  void* stream);
+int cml_apply_bins(const float* xt, int p, int m, int ld, const float* edges, const int* n_edges, unsigned char* bins,
+                   int m_pad, void* stream);
+int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max_bin, const float* s0, const float* s1,
+                     const float* s2, int T, int max_nodes, int max_depth, int* order_in, int* order_out,
+                     const int* frontier, int n_frontier, int* next_frontier, int* next_count, int* node_count,
+                     int* feat, int* thr, int* left, float* value, float* gain, float* cover, int criterion, int mtry,
+                     float lambda, float gamma, float min_child_weight, float min_samples_leaf, float min_samples_split,
+                     float eta, unsigned long long seed, const unsigned char* feature_mask, float* imp_gain,
+                     float* imp_cover, float* imp_freq, void* stream);
+int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int max_nodes, const int* feat, const int* thr,
+                       const int* left, const float* value, int* leaf_out, float* value_out, void* stream);
+int cml_forest_proximity(const int* leaf, int T, int n, float* prox, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
