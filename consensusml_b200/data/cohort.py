@@ -89,7 +89,7 @@ class Cohort:
         return self.select_samples(flag == "train"), self.select_samples(flag == "test")
 
     def labels(self, column: str = "deg.risk") -> torch.Tensor:
-        y = pd.to_numeric(self.col_data[column]).to_numpy()
+        y = np.array(pd.to_numeric(self.col_data[column]).to_numpy(), copy=True)
         return torch.as_tensor(y, dtype=torch.float32, device=self.assay.device)
 
     def design(self, dtype=torch.float32) -> torch.Tensor:

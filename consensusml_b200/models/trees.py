@@ -132,7 +132,7 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     gain = torch.zeros(T, max_nodes, **f32)
     cover = torch.zeros(T, max_nodes, **f32)
     node_count = torch.ones(T, **i32)
-    frontier = torch.zeros(T, 5, **i32)
+    frontier = torch.zeros(T, 7, **i32)
     frontier[:, 0] = torch.arange(T, **i32)
     frontier[:, 3] = counts
     nf = T
@@ -146,7 +146,7 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     imp = importance or {}
     depth = 0
     while nf > 0 and depth <= max_depth:
-        nxt = torch.empty(2 * nf, 5, **i32)
+        nxt = torch.empty(2 * nf, 7, **i32)
         next_count.zero_()
         rc = lb.cml_forest_level(P(bins), p, n, n_pad, max_bin, P(s0), P(s1), P(s2c), T, max_nodes, max_depth, P(order),
                                  P(order2), P(frontier), nf, P(nxt), P(next_count), P(node_count), P(feat), P(thr), P(left),
@@ -193,9 +193,10 @@ def _mix(z):
     return z ^ (z >> 31)
 
 
-def _node_candidates(seed, tree, node, p, mtry, fmask):
-    """Same counter-based sampling as the kernel (splitmix64), so CPU and GPU trees see the same candidates."""
-    base = _mix((seed & _M64) ^ ((0x9E3779B97F4A7C15 * (tree + 1)) & _M64) ^ ((0xC2B2AE3D27D4EB4F * (node + 1)) & _M64))
+def _node_candidates(seed, tree, key, p, mtry, fmask):
+    """Same counter-based sampling as the kernel (splitmix64 keyed by the node's path from the root), so CPU
+    and GPU trees see the same candidates whatever order node ids were handed out in."""
+    base = _mix((seed & _M64) ^ ((0x9E3779B97F4A7C15 * (tree + 1)) & _M64) ^ key)
     got, seen, ctr = [], set(), 0
     while len(got) < mtry and ctr < 64 * p:
         f = ((_mix((base + ctr) & _M64) >> 32) * p) >> 32
@@ -224,10 +225,10 @@ def _grow_numpy(bins, n, s0, s1, s2, crit, mtry, max_depth, max_nodes, max_bin, 
     all_feats = mtry <= 0 or mtry >= p
     for t in range(T):
         members = np.arange(n) if in_tree is None else np.flatnonzero(in_tree[t].numpy())
-        frontier = [(0, members, 0)]
+        frontier = [(0, members, 0, 0)]
         while frontier:
             nxt = []
-            for node, idx, depth in frontier:
+            for node, idx, depth, key in frontier:
                 a, b = S0[t, idx].sum(), S1[t, idx].sum()
                 if crit == GINI:
                     v = a / b if b > 0 else 0.0
@@ -240,7 +241,7 @@ def _grow_numpy(bins, n, s0, s1, s2, crit, mtry, max_depth, max_nodes, max_bin, 
                 pure = crit == GINI and (a <= 0 or a >= b)
                 if not (depth < max_depth and idx.size >= mss and idx.size >= 2 and not pure and b >= 2 * mcw):
                     continue
-                cands = [f for f in range(p) if fm is None or fm[f]] if all_feats else _node_candidates(seed, t, node, p, mtry, fm)
+                cands = [f for f in range(p) if fm is None or fm[f]] if all_feats else _node_candidates(seed, t, key, p, mtry, fm)
                 parent = float(_score(crit, np.float64(a), np.float64(b), lam))
                 best = (-np.inf, -1, -1)
                 for f in cands:
@@ -271,8 +272,8 @@ def _grow_numpy(bins, n, s0, s1, s2, crit, mtry, max_depth, max_nodes, max_bin, 
                     importance["gain"][bf] += real
                     importance["cover"][bf] += b
                     importance["freq"][bf] += 1
-                nxt.append((child, idx[goes_left], depth + 1))
-                nxt.append((child + 1, idx[~goes_left], depth + 1))
+                nxt.append((child, idx[goes_left], depth + 1, _mix(key ^ 0xA24BAED4963EE407)))
+                nxt.append((child + 1, idx[~goes_left], depth + 1, _mix(key ^ 0x9FB21C651E98DF25)))
             frontier = nxt
     t_ = torch.from_numpy
     return TreeBatch(t_(feat), t_(thr), t_(left), t_(value), t_(gain), t_(cover), t_(ncount))

@@ -28,6 +28,7 @@ enum Criterion : int { CRIT_GINI = 0, CRIT_NEWTON = 1 };
 
 struct Frontier {          // one entry per open node
   int tree, node, start, count, depth;
+  unsigned key_lo, key_hi;   // path key: identifies the node by its route from the root, independent of numbering
 };
 
 struct ForestArgs {
@@ -119,8 +120,9 @@ __global__ void __launch_bounds__(kWarps * 32) forest_level_kernel(const ForestA
   int ncand = all_features ? A.p : min(A.mtry, kMaxMtry);
   if (!all_features) {
     if (warp == 0) {
+      // node ids are handed out by atomics (order varies run to run); the path key does not
       const unsigned long long base = mix64(A.seed ^ (0x9E3779B97F4A7C15ull * (unsigned long long)(F.tree + 1)) ^
-                                            (0xC2B2AE3D27D4EB4Full * (unsigned long long)(F.node + 1)));
+                                            (((unsigned long long)F.key_hi << 32) | F.key_lo));
       int got = 0;
       unsigned long long ctr = 0;
       while (got < ncand && ctr < 64ull * (unsigned long long)A.p) {
@@ -255,8 +257,11 @@ __global__ void __launch_bounds__(kWarps * 32) forest_level_kernel(const ForestA
       atomicAdd(&A.imp_freq[bf], 1.f);
     }
     const int slot = atomicAdd(A.next_count, 2);
-    A.next_frontier[slot] = Frontier{F.tree, child, F.start, nleft, F.depth + 1};
-    A.next_frontier[slot + 1] = Frontier{F.tree, child + 1, F.start + nleft, F.count - nleft, F.depth + 1};
+    const unsigned long long key = ((unsigned long long)F.key_hi << 32) | F.key_lo;
+    const unsigned long long kl = mix64(key ^ 0xA24BAED4963EE407ull), kr = mix64(key ^ 0x9FB21C651E98DF25ull);
+    A.next_frontier[slot] = Frontier{F.tree, child, F.start, nleft, F.depth + 1, (unsigned)kl, (unsigned)(kl >> 32)};
+    A.next_frontier[slot + 1] = Frontier{F.tree, child + 1, F.start + nleft, F.count - nleft, F.depth + 1, (unsigned)kr,
+                                         (unsigned)(kr >> 32)};
   }
 }
 

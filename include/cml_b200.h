@@ -129,8 +129,8 @@ int cml_ebayes(const double* coef, const double* su, const double* sigma, const 
 /* ---- K8/K9: batched histogram trees ---------------------------------------------------------------------
  * Replaces randomForest (cml_targetaml_seanalysis.Rmd:1037-1050), xgboost (:1164-1186; scripts/model_comp.py:7) and
  * sklearn GradientBoosting/RandomForest (scripts/model_comp.py:8-9).  bins: uint8 [p][n_pad] feature-major.
- * cml_forest_level grows every open node of a batch of T trees by one level; frontier records are 5 ints
- * (tree, node, start, count, depth); *next_count must be zero on entry.  criterion 0 = gini, 1 = newton.   */
+ * cml_forest_level grows every open node of a batch of T trees by one level; frontier records are 7 ints
+ * (tree, node, start, count, depth, key_lo, key_hi; key = 0 for roots); *next_count must be zero on entry.  criterion 0 = gini, 1 = newton.   */
 int cml_rank_bins(const float* xt, int p, int n, int ld, unsigned char* bins, int n_pad, float* edges, int* n_edges,
                   void* stream);
 int cml_apply_bins(const float* xt, int p, int m, int ld, const float* edges, const int* n_edges, unsigned char* bins,

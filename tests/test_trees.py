@@ -113,12 +113,19 @@ def test_gpu_trees_match_numpy_restatement(aml):
     kw["in_tree"] = (w > 0).cuda()
     gpu = TR.grow(bins.cuda(), 93, (w * ytr[None, :]).cuda(), w.cuda(), **kw)
     assert torch.equal(gpu.node_count.cpu(), cpu.node_count)
-    assert torch.equal(gpu.feat.cpu(), cpu.feat)
-    assert torch.equal(gpu.thr.cpu(), cpu.thr)
-    assert torch.allclose(gpu.value.cpu(), cpu.value, atol=1e-6)
+    # node ids are handed out by atomics on the GPU, so compare numbering-independent views of the trees
+    def splits(tb, t):
+        nc = int(tb.node_count[t])
+        f, th, cv = tb.feat[t, :nc].cpu(), tb.thr[t, :nc].cpu(), tb.cover[t, :nc].cpu()
+        return sorted((int(a), int(b), round(float(c), 3)) for a, b, c in zip(f, th, cv) if a >= 0)
+    for t in range(6):
+        assert splits(gpu, t) == splits(cpu, t), t
     lc, vc = TR.predict_leaves(cpu, bins, 93)
     lg, vg = TR.predict_leaves(gpu, bins.cuda(), 93)
-    assert torch.equal(lg.cpu(), lc)
+    assert torch.allclose(vg.cpu(), vc, atol=1e-6)
+    for t in range(6):                       # same partition of the samples into leaves
+        a, b = lc[t], lg[t].cpu()
+        assert torch.equal(a[:, None] == a[None, :], b[:, None] == b[None, :])
 
 
 @pytest.mark.gpu
