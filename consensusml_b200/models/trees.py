@@ -29,7 +29,7 @@ _native.register_signature("cml_forest_level", [_P, _I, _I, _I, _I, _P, _P, _P, 
                                                 _P, _P, _P, _P, _P, _P, _I, _I, _F, _F, _F, _F, _F, _F, _ULL, _P, _P, _P,
                                                 _P, _P])
 _native.register_signature("cml_forest_predict", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P])
-_native.register_signature("cml_forest_proximity", [_P, _I, _I, _P, _P])
+_native.register_signature("cml_forest_proximity", [_P, _P, _I, _I, _P, _P, _P])
 
 GINI, NEWTON = 0, 1
 
@@ -310,6 +310,7 @@ class RandomForest:
     bootstrap: bool = True
     seed: int = 20                        # the reference's set.seed(20), cml_targetaml_seanalysis.Rmd:1026
     proximity: bool = False
+    oob_prox: bool = True                 # randomForest's default: proximity from out-of-bag pairs only
     tree_batch: int = 2048
 
     binner: Binner = field(default=None, repr=False)
@@ -332,6 +333,7 @@ class RandomForest:
         votes1 = torch.zeros(n, device=dev)
         nvote = torch.zeros(n, device=dev)
         prox = torch.zeros(n, n, device=dev) if self.proximity else None
+        pairs = torch.zeros(n, n, device=dev) if self.proximity else None
         self.trees = []
         done = 0
         while done < self.n_trees:
@@ -350,12 +352,16 @@ class RandomForest:
             votes1 += (vote * oob).sum(0)
             nvote += oob.sum(0)
             if prox is not None:
+                use_oob = self.oob_prox and self.bootstrap
+                ob = (w == 0).to(torch.uint8).contiguous() if use_oob else None
                 if dev.type == "cuda":
-                    rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), T, n, _native.ptr(prox),
-                                                             _native.stream_ptr())
+                    rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), _native.ptr(ob), T, n,
+                                                             _native.ptr(prox), _native.ptr(pairs), _native.stream_ptr())
                     _native.check(rc, "cml_forest_proximity")
                 else:
-                    prox += (leaf[:, :, None] == leaf[:, None, :]).float().sum(0)
+                    both = (ob[:, :, None] & ob[:, None, :]).bool() if use_oob else torch.ones(T, n, n, dtype=torch.bool)
+                    prox += ((leaf[:, :, None] == leaf[:, None, :]) & both).float().sum(0)
+                    pairs += both.float().sum(0)
             done += T
         self.importance_ = imp["gain"] / self.n_trees
         self.importance_cover_ = imp["cover"]
@@ -367,7 +373,8 @@ class RandomForest:
         self.oob_error_ = float((pred[has] != yf[has]).float().mean())
         self.confusion_oob_ = confusion_matrix(pred[has], yf[has])
         if prox is not None:
-            self.proximity_ = prox / self.n_trees
+            self.proximity_ = prox / pairs.clamp_min(1)
+            self.proximity_.fill_diagonal_(1.0)
         return self
 
     def _accumulate(self, x, fn):

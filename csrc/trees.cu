@@ -295,12 +295,20 @@ __global__ void forest_predict_kernel(const unsigned char* __restrict__ bins, in
 }
 
 // prox[i][j] += #trees in which samples i and j share a terminal node (randomForest proximity, un-normalised)
-__global__ void forest_proximity_kernel(const int* __restrict__ leaf, int T, int n, float* __restrict__ prox) {
+// With `oob` ([T][n], 1 = sample out of bag in that tree) only trees in which BOTH samples are out of bag count
+// (randomForest's default oob.prox) and pairs[i][j] receives the number of such trees.
+__global__ void forest_proximity_kernel(const int* __restrict__ leaf, const unsigned char* __restrict__ oob, int T, int n,
+                                        float* __restrict__ prox, float* __restrict__ pairs) {
   const int i = blockIdx.x;
   for (int j = threadIdx.x; j < n; j += blockDim.x) {
-    int c = 0;
-    for (int t = 0; t < T; ++t) c += leaf[(size_t)t * n + i] == leaf[(size_t)t * n + j];
+    int c = 0, q = 0;
+    for (int t = 0; t < T; ++t) {
+      const bool both = !oob || (oob[(size_t)t * n + i] && oob[(size_t)t * n + j]);
+      q += both;
+      c += both && leaf[(size_t)t * n + i] == leaf[(size_t)t * n + j];
+    }
     prox[(size_t)i * n + j] += (float)c;
+    if (pairs) pairs[(size_t)i * n + j] += (float)q;
   }
 }
 
@@ -416,9 +424,9 @@ int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int m
   return 0;
 }
 
-int cml_forest_proximity(const int* leaf, int T, int n, float* prox, void* stream) {
+int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n, float* prox, float* pairs, void* stream) {
   using namespace cml;
-  forest_proximity_kernel<<<n, 128, 0, static_cast<cudaStream_t>(stream)>>>(leaf, T, n, prox);
+  forest_proximity_kernel<<<n, 128, 0, static_cast<cudaStream_t>(stream)>>>(leaf, oob, T, n, prox, pairs);
   CML_LAUNCH_CHECK();
   return 0;
 }

@@ -144,7 +144,7 @@ int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max
                      float* imp_cover, float* imp_freq, void* stream);
 int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int max_nodes, const int* feat, const int* thr,
                        const int* left, const float* value, int* leaf_out, float* value_out, void* stream);
-int cml_forest_proximity(const int* leaf, int T, int n, float* prox, void* stream);
+int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n, float* prox, float* pairs, void* stream);
 
 #ifdef __cplusplus
 }
