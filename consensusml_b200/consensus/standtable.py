@@ -49,7 +49,7 @@ class StandTable:
         """R ``write.csv`` layout: quoted header with a leading empty name, quoted row names and strings."""
         with open(path, "w", newline="") as fh:
             fh.write(",".join([_q("")] + [_q(c) for c in self.df.columns]) + "\n")
-            str_cols = {c for c in self.df.columns if self.df[c].dtype == object}
+            str_cols = {c for c in self.df.columns if not pd.api.types.is_numeric_dtype(self.df[c])}
             for gid, row in zip(self.df.index, self.df.itertuples(index=False)):
                 cells = [_q(gid)]
                 for c, v in zip(self.df.columns, row):
