@@ -1,0 +1,178 @@
+"""Sample-sharded L1 logistic regression for cohorts too large for the warp-per-replicate solver.
+
+The reference's cohorts have n <= 474 samples; the north-star asks for 1M samples x 20k genes across 8 GPUs.
+At that size the design matrix is streamed, not cached: every rank holds a contiguous block of samples (bf16,
+row-major) and the genes are partitioned among the ranks for the update.  One proximal-gradient (FISTA)
+iteration is
+
+    r      = w (y - sigmoid(X v))                 xb_residual kernel        (local rows)
+    g_own  = sum_ranks X_r^T r_r  [own genes]     xtr_reduce_scatter kernel (FUSED: peer red.add + signals)
+    beta   = soft(v + s g/n, s lambda)            prox_allgather kernel     (FUSED: peer stores of the new slice)
+
+so the two collectives of the iteration (reduce-scatter of the gradient, all-gather of the coefficients) are
+issued from inside the kernels over NVLink.  ``backend="unfused"`` runs the same iteration with torch ops and
+``torch.distributed`` collectives (NCCL or gloo) - the comparator and the CPU path.
+
+glmnet parity note: this solver minimises the same objective ((1/n) sum w_i logloss_i + lambda |beta|_1, no
+intercept by default) but by FISTA instead of cyclic coordinate descent, so it agrees with the path solver to
+optimisation tolerance, not update for update."""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from ..parallel import fused as F
+from ..parallel import symm
+from ..parallel.dist import all_reduce_, equal_shard
+
+
+@dataclass
+class LargeFit:
+    beta: torch.Tensor
+    iterations: int
+    objective: float
+    step: float
+    history: list
+
+
+def lipschitz_estimate(x: torch.Tensor, n_total: int, iters: int = 12) -> float:
+    """Largest eigenvalue of X^T X / (4 n) by power iteration (set-up only; partial products all-reduced)."""
+    p = x.shape[1]
+    g = torch.Generator(device="cpu").manual_seed(0)
+    v = torch.randn(p, generator=g).to(x.device)
+    v /= v.norm()
+    lam = 1.0
+    xf = x if x.dtype == torch.float32 else None
+    for _ in range(iters):
+        u = (x.float() @ v) if xf is None else xf @ v
+        w = (x.float().t() @ u) if xf is None else xf.t() @ u
+        all_reduce_(w)
+        lam = float(w.norm())
+        v = w / (lam + 1e-30)
+    return lam / (4.0 * n_total)
+
+
+def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Optional[int] = None, max_iter: int = 200,
+        tol: float = 1e-5, backend: str = "auto", weights: Optional[torch.Tensor] = None, beta0: Optional[torch.Tensor] = None,
+        step: Optional[float] = None, check_every: int = 10) -> LargeFit:
+    """L1 logistic regression on this rank's rows (``x_local`` [n_r, p]); every rank returns the full ``beta``."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    n_r, p = x_local.shape
+    dev = x_local.device
+    if n_total is None:
+        t = torch.tensor([n_r], dtype=torch.float64, device=dev)
+        all_reduce_(t)
+        n_total = int(t.item())
+    if backend == "auto":
+        backend = "fused" if x_local.is_cuda else "unfused"
+    if step is None:
+        step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
+    if backend == "unfused":
+        return _fit_unfused(x_local, y_local, lam, n_total, max_iter, tol, weights, beta0, step, check_every)
+
+    lb = _native.cuda()
+    P = _native.ptr
+    st = _native.stream_ptr
+    xb = x_local if x_local.dtype == torch.bfloat16 else F.to_bf16_padded(x_local)
+    ldx = xb.shape[1]
+    rs = F.XtrReduceScatter(p, 1, dev)
+    rank = rs.rank
+    beta = symm.alloc((ldx,), torch.float32, dev)
+    v = symm.alloc((ldx,), torch.float32, dev)
+    if beta0 is not None:
+        beta.local[:p] = beta0.float()
+        v.local[:p] = beta0.float()
+    y = y_local.float().contiguous()
+    w = weights.float().contiguous() if weights is not None else None
+    R = torch.empty(n_r, dtype=torch.float32, device=dev)
+    loss = torch.zeros(1, dtype=torch.float64, device=dev)
+    done = torch.zeros(4, dtype=torch.int32, device=dev)
+    dmax = torch.zeros(1, dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+    beta.barrier()
+    bptr, vptr, sptr = F._ptr_array(beta.peer_ptrs), F._ptr_array(v.peer_ptrs), F._ptr_array(rs.grad.signal_ptrs)
+    my_pad = ctypes.c_void_p(rs.grad.signal_ptrs[rank])
+    tk = 1.0
+    history = []
+    it = 0
+    obj = float("nan")
+    for it in range(1, max_iter + 1):
+        if it > 1:      # the coefficient slices of every owner have landed in this rank's copy
+            _native.check(lb.cml_wait_signals(my_pad, F.SIG_BETA, world, it - 1, st()), "cml_wait_signals")
+        check = (it % check_every == 0) or it == max_iter
+        if check:
+            loss.zero_()
+            dmax.zero_()
+        _native.check(lb.cml_xb_residual(P(xb), ldx, n_r, p, P(v.local), 0.0, P(y), P(w), P(R), None, P(loss), st()),
+                      "cml_xb_residual")
+        rs.launch(xb, R)
+        rs.wait()
+        tk1 = (1.0 + np.sqrt(1.0 + 4.0 * tk * tk)) / 2.0
+        mom = (tk - 1.0) / tk1
+        tk = tk1
+        _native.check(lb.cml_prox_allgather(P(rs.grad.local), rs.genes_owned, rs.gene0, None, step, lam, 1.0 / n_total, mom,
+                                            bptr, vptr, sptr, rank, world, P(beta.local), P(done), it, F.SIG_BETA, P(dmax),
+                                            st()), "cml_prox_allgather")
+        if check:
+            # convergence test on the largest coefficient change of this iteration (max over ranks); the loss printed
+            # is that of the extrapolated point v, enough to watch progress
+            stats = torch.stack([dmax[0].double(), loss[0]])
+            d = stats[:1].clone()
+            s = stats[1:].clone()
+            all_reduce_(d, dist.ReduceOp.MAX)
+            all_reduce_(s)
+            _native.check(lb.cml_wait_signals(my_pad, F.SIG_BETA, world, it, st()), "cml_wait_signals")
+            obj = float(s.item()) / n_total + lam * float(beta.local[:p].abs().sum())
+            history.append((it, obj, float(d.item())))
+            if float(d.item()) < tol:
+                break
+    _native.check(lb.cml_wait_signals(my_pad, F.SIG_BETA, world, it, st()), "cml_wait_signals")
+    torch.cuda.synchronize()
+    beta.barrier()
+    out = beta.local[:p].clone()
+    torch.cuda.synchronize()
+    beta.barrier()
+    return LargeFit(out, it, obj, step, history)
+
+
+def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_every) -> LargeFit:
+    p = x.shape[1]
+    dev = x.device
+    xf = x.float()
+    beta = torch.zeros(p, dtype=torch.float32, device=dev) if beta0 is None else beta0.float().clone()
+    v = beta.clone()
+    w = weights.float() if weights is not None else torch.ones_like(y, dtype=torch.float32)
+    yf = y.float()
+    tk = 1.0
+    history = []
+    obj = float("nan")
+    it = 0
+    for it in range(1, max_iter + 1):
+        eta = xf @ v
+        r = w * (yf - torch.sigmoid(eta))
+        g = xf.t() @ r
+        all_reduce_(g)
+        z = v + step * g / n_total
+        thr = step * lam
+        bnew = torch.sign(z) * (z.abs() - thr).clamp_min(0)
+        tk1 = (1.0 + np.sqrt(1.0 + 4.0 * tk * tk)) / 2.0
+        mom = (tk - 1.0) / tk1
+        tk = tk1
+        d = float((bnew - beta).abs().max())
+        v = bnew + mom * (bnew - beta)
+        beta = bnew
+        if it % check_every == 0 or it == max_iter:
+            sp = torch.where(eta > 0, eta + torch.log1p(torch.exp(-eta)), torch.log1p(torch.exp(eta)))
+            s = (w * (sp - yf * eta)).double().sum().reshape(1)
+            all_reduce_(s)
+            obj = float(s.item()) / n_total + lam * float(beta.abs().sum())
+            history.append((it, obj, d))
+            if d < tol:
+                break
+    return LargeFit(beta, it, obj, step, history)

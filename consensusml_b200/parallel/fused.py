@@ -1,0 +1,223 @@
+"""Python faces of the fused compute + collective kernels (csrc/fused.cu, csrc/gemm_tcgen05.cu).
+
+Three paths, each with an un-fused comparator built from torch ops + ``torch.distributed`` collectives that the
+tests hold the kernels to:
+
+1. ``hist_allreduce``        - per-level (g, h) histograms, reduced across ranks by NVLS ``multimem.red``
+2. ``xtr_reduce_scatter``    - lasso gradient ``X^T r`` reduce-scattered by gene with peer ``red.add``
+3. ``gram_allgather``        - kernel-matrix rows against every rank's samples; TMA reads the peers' tiles
+
+Nothing comparable exists in the reference (single-process CPU)."""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+from ..ops import gemm as G
+from . import symm
+from .dist import equal_shard
+
+_I, _LL, _F, _P, _U, _SZ = ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_void_p, ctypes.c_uint, ctypes.c_size_t
+_native.register_signature("cml_xtr_rs_scratch_bytes", [_I, _I], _SZ)
+_native.register_signature("cml_xtr_reduce_scatter", [_P, _LL, _I, _I, _P, _I, _P, _P, _P, _I, _I, _I, _LL, _U, _P])
+_native.register_signature("cml_wait_signals", [_P, _I, _I, _U, _P])
+_native.register_signature("cml_prox_allgather", [_P, _I, _I, _P, _F, _F, _F, _F, _P, _P, _P, _I, _I, _P, _P, _U, _I, _P, _P])
+_native.register_signature("cml_xb_residual", [_P, _LL, _I, _I, _P, _F, _P, _P, _P, _P, _P, _P])
+_native.register_signature("cml_hist_scratch_bytes", [_I, _I], _SZ)
+_native.register_signature("cml_hist_ft", [_I, _I], _I)
+_native.register_signature("cml_hist_allreduce", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _U, _I, _P])
+_native.register_signature("cml_split_score_gain", [_P, _I, _I, _I, _F, _F, _F, _P, _P])
+
+SIG_GRAD, SIG_BETA, SIG_HIST = 0, 8, 16      # signal-pad word ranges (one word per rank each)
+
+
+def _ptr_array(ptrs: List[int]):
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)
+
+
+def to_bf16_padded(x: torch.Tensor) -> torch.Tensor:
+    """fp32 [n, p] -> bf16 [n, pad8(p)] (zero padded), through the conversion kernel."""
+    return G.to_bf16_rows(x.float().contiguous())[0]
+
+
+# ------------------------------------------------------------------------------------------------ path 2
+class XtrReduceScatter:
+    """``g_owned = sum_ranks (X_r^T R_r)[owned genes]`` with the reduction done by peer atomics inside the kernel."""
+
+    def __init__(self, p: int, nb: int, device):
+        self.p, self.nb = p, nb
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.genes_per_rank = equal_shard(p, self.world)
+        self.grad = symm.alloc((self.genes_per_rank * nb,), torch.float32, device)       # owner-side accumulator
+        lib = _native.cuda()
+        self.scratch = torch.zeros(lib.cml_xtr_rs_scratch_bytes(p, nb), dtype=torch.uint8, device=device)
+        self.epoch = 0
+
+    @property
+    def gene0(self) -> int:
+        return self.rank * self.genes_per_rank
+
+    @property
+    def genes_owned(self) -> int:
+        return max(0, min(self.p, self.gene0 + self.genes_per_rank) - self.gene0)
+
+    def launch(self, x_bf16: torch.Tensor, R: torch.Tensor) -> int:
+        """Start the fused kernel for this rank's rows; returns the epoch to wait for."""
+        self.epoch += 1
+        n, ldx = x_bf16.shape
+        rc = _native.cuda().cml_xtr_reduce_scatter(
+            _native.ptr(x_bf16), ldx, n, self.p, _native.ptr(R), self.nb, _native.ptr(self.scratch),
+            _ptr_array(self.grad.peer_ptrs), _ptr_array(self.grad.signal_ptrs), self.rank, self.world, self.genes_per_rank, 0,
+            self.epoch, _native.stream_ptr())
+        _native.check(rc, "cml_xtr_reduce_scatter")
+        return self.epoch
+
+    def wait(self, epoch: Optional[int] = None) -> None:
+        rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(self.grad.signal_ptrs[self.rank]), SIG_GRAD, self.world,
+                                             self.epoch if epoch is None else epoch, _native.stream_ptr())
+        _native.check(rc, "cml_wait_signals")
+
+    def result(self) -> torch.Tensor:
+        """Owned slice [genes_owned, nb] (valid after ``wait``); the caller clears it before the epoch after next."""
+        return self.grad.local[: self.genes_owned * self.nb].view(self.genes_owned, self.nb)
+
+
+def xtr_reduce_scatter_unfused(x: torch.Tensor, R: torch.Tensor, p: int) -> torch.Tensor:
+    """Comparator: library matmul + ``reduce_scatter_tensor`` (NCCL / gloo)."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    gpr = equal_shard(p, world)
+    full = torch.zeros(gpr * world, R.shape[1], dtype=torch.float32, device=x.device)
+    full[:p] = x.float().t() @ R.float()
+    if world == 1:
+        return full[:p]
+    out = torch.empty(gpr, R.shape[1], dtype=torch.float32, device=x.device)
+    if x.is_cuda:
+        dist.reduce_scatter_tensor(out, full)
+    else:
+        dist.all_reduce(full)
+        r = dist.get_rank()
+        out = full[r * gpr:(r + 1) * gpr]
+    r = dist.get_rank()
+    return out[: max(0, min(p, (r + 1) * gpr) - r * gpr)]
+
+
+# ------------------------------------------------------------------------------------------------ path 3
+def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Optional[float] = None, n_total: Optional[int] = None,
+                   shift: float = 0.0, cache: Optional[dict] = None) -> torch.Tensor:
+    """Rows of the kernel matrix for this rank's samples against ALL samples: ``K[local, :]`` of shape
+    [n_local, n_total].  Each rank publishes its bf16 block (+ squared norms) in symmetric memory; the GEMM's TMA
+    producer then loads B tiles straight from the peers' blocks over NVLink - the all-gather never exists as a copy."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    n_local, p = x_local.shape
+    dev = x_local.device
+    ld = (p + 7) // 8 * 8
+    rows = n_local if world == 1 else equal_shard(n_total, world)
+    xb = symm.alloc((rows, ld), torch.bfloat16, dev)
+    nrm = symm.alloc((rows,), torch.float32, dev)
+    G.to_bf16_rows(x_local.float().contiguous(), shift=shift, out=xb.local[:n_local], norm_out=nrm.local[:n_local])
+    torch.cuda.synchronize()
+    xb.barrier()
+    n_total = n_local if n_total is None else n_total
+    gamma = 1.0 / p if gamma is None else gamma
+    epi, alpha = (G.EPI_RBF, gamma) if kernel == "radial" else (G.EPI_SCALE, 1.0)
+    out = G.gemm_tn(xb.local[:n_local], None, n_total, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
+                    b_ptrs=xb.peer_ptrs, norm_b_ptrs=nrm.peer_ptrs, rows_per_src=rows, ldb=ld)
+    torch.cuda.synchronize()
+    xb.barrier()                     # nobody frees / rewrites its block while a peer may still be reading it
+    if cache is not None:
+        cache["xb"], cache["nrm"] = xb, nrm
+    return out
+
+
+def gram_allgather_unfused(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Optional[float] = None, shift: float = 0.0):
+    """Comparator: NCCL all-gather of the bf16-rounded blocks, then a plain fp32 matmul + epilogue in torch."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    xb, nrm = G.to_bf16_rows(x_local.float().contiguous(), shift=shift)
+    if world > 1:
+        parts = [torch.empty_like(xb) for _ in range(world)]
+        dist.all_gather(parts, xb)
+        allx = torch.cat(parts)
+    else:
+        allx = xb
+    a, b = xb.float(), allx.float()
+    dot = a @ b.t()
+    if kernel != "radial":
+        return dot
+    gamma = 1.0 / x_local.shape[1] if gamma is None else gamma
+    d2 = (a * a).sum(1)[:, None] + (b * b).sum(1)[None, :] - 2 * dot
+    return torch.exp(-gamma * d2.clamp_min(0))
+
+
+# ------------------------------------------------------------------------------------------------ path 1
+class HistAllReduce:
+    """Per-level gradient histograms ``hist[node, feature, bin, (g, h)]`` summed over ranks inside the build kernel."""
+
+    def __init__(self, p: int, nbins: int, max_nodes: int, device):
+        self.p, self.nbins, self.max_nodes = p, nbins, max_nodes
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        size = max_nodes * p * nbins * 2
+        self.hist = symm.alloc((size,), torch.float32, device)
+        self.local = torch.zeros(size, dtype=torch.float32, device=device)
+        self.counters = torch.zeros(p + 16, dtype=torch.int32, device=device)
+        self.epoch = 0
+
+    def build(self, bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, n_nodes: int, use_multicast: bool = True):
+        """Launch build + reduce; returns the reduced histogram view [n_nodes, p, nbins, 2] after waiting."""
+        self.epoch += 1
+        mc = self.hist.multicast_ptr if (use_multicast and self.world > 1) else 0
+        rc = _native.cuda().cml_hist_allreduce(
+            _native.ptr(bins), bins.shape[1], n, self.p, self.nbins, _native.ptr(node), _native.ptr(gh), n_nodes,
+            _native.ptr(self.local), _native.ptr(self.counters), ctypes.c_void_p(mc), _ptr_array(self.hist.peer_ptrs),
+            _ptr_array(self.hist.signal_ptrs), self.rank, self.world, self.epoch, SIG_HIST, _native.stream_ptr())
+        _native.check(rc, "cml_hist_allreduce")
+        rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(self.hist.signal_ptrs[self.rank]), SIG_HIST, self.world, self.epoch,
+                                             _native.stream_ptr())
+        _native.check(rc, "cml_wait_signals")
+        return self.hist.local[: n_nodes * self.p * self.nbins * 2].view(n_nodes, self.p, self.nbins, 2)
+
+    def clear(self, n_nodes: int) -> None:
+        """Zero the reduced histogram for the next level - after every rank has finished reading it."""
+        torch.cuda.synchronize()
+        self.hist.barrier()
+        self.hist.local[: n_nodes * self.p * self.nbins * 2].zero_()
+        torch.cuda.synchronize()
+        self.hist.barrier()
+
+
+def hist_unfused(bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, n_nodes: int, p: int, nbins: int) -> torch.Tensor:
+    """Comparator: histogram by ``index_add_`` + ``all_reduce``."""
+    dev = bins.device
+    hist = torch.zeros(n_nodes * p * nbins, 2, dtype=torch.float32, device=dev)
+    valid = node[:n] >= 0
+    idx_s = torch.nonzero(valid).flatten()
+    nd = node[:n][idx_s].long()
+    for f in range(p):
+        flat = (nd * p + f) * nbins + bins[f, :n][idx_s].long()
+        hist.index_add_(0, flat, gh[idx_s])
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(hist)
+    return hist.view(n_nodes, p, nbins, 2)
+
+
+def best_splits(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_child_weight: float = 1.0):
+    """Per open node: (gain, feature, bin) from the reduced histogram via ``cml_split_score_gain``.
+    Returns int64 tensors feature, bin (-1 where no valid split) and fp32 gain."""
+    n_nodes, p, nbins, _ = hist.shape
+    best = torch.zeros(n_nodes, dtype=torch.int64, device=hist.device)
+    rc = _native.cuda().cml_split_score_gain(_native.ptr(hist.contiguous()), n_nodes, p, nbins, lam, gamma, min_child_weight,
+                                             _native.ptr(best), _native.stream_ptr())
+    _native.check(rc, "cml_split_score_gain")
+    key = best
+    has = key != 0
+    gain = ((key >> 32) & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+    feat = 0xFFFFF - ((key >> 12) & 0xFFFFF)
+    b = 0xFFF - (key & 0xFFF)
+    return torch.where(has, gain, torch.zeros_like(gain)), torch.where(has, feat, -torch.ones_like(feat)), \
+        torch.where(has, b, -torch.ones_like(b))

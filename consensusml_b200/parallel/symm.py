@@ -1,0 +1,62 @@
+"""Symmetric (peer-mapped) device buffers over NVLink.
+
+Every rank allocates the same buffer, the ranks exchange handles once, and afterwards each rank holds the
+device address of every peer's copy.  The fused kernels take those addresses (``peer_ptrs``) plus the
+addresses of a small per-rank signal pad and issue plain / atomic stores to them from inside the kernel -
+that is the whole transport.  Built on ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric handles).
+With one rank the "peers" are the local buffer, so the same kernels run unchanged on a single GPU."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass
+class SymmBuffer:
+    local: torch.Tensor            # this rank's copy
+    peer_ptrs: List[int]           # device address of every rank's copy (index = rank)
+    signal_ptrs: List[int]         # device address of every rank's signal pad
+    multicast_ptr: int             # NVLS multicast address (0 if unavailable)
+    rank: int
+    world: int
+    handle: object = None
+
+    def barrier(self, channel: int = 0) -> None:
+        if self.handle is not None:
+            self.handle.barrier(channel=channel)
+        elif dist.is_initialized():
+            dist.barrier()
+
+    def peer_view(self, r: int) -> torch.Tensor:
+        """Tensor view of rank r's copy (for tests / un-fused fallbacks)."""
+        if self.handle is None:
+            return self.local
+        return self.handle.get_buffer(r, tuple(self.local.shape), self.local.dtype)
+
+
+_SIGNAL_PAD_WORDS = 4096
+
+
+def alloc(shape, dtype, device) -> SymmBuffer:
+    """Collective: every rank calls with the same shape / dtype."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    if world == 1 or torch.device(device).type != "cuda":
+        t = torch.zeros(shape, dtype=dtype, device=device)
+        pad = torch.zeros(_SIGNAL_PAD_WORDS, dtype=torch.int32, device=device)
+        buf = SymmBuffer(t, [t.data_ptr()] * world, [pad.data_ptr()] * world, 0, rank, world, None)
+        buf._pad = pad
+        return buf
+    import torch.distributed._symmetric_memory as sm
+    t = sm.empty(shape, dtype=dtype, device=device)
+    t.zero_()
+    h = sm.rendezvous(t, dist.group.WORLD)
+    mc = 0
+    try:
+        mc = int(h.multicast_ptr or 0)
+    except Exception:
+        mc = 0
+    return SymmBuffer(t, [int(p) for p in h.buffer_ptrs], [int(p) for p in h.signal_pad_ptrs], mc, rank, world, h)

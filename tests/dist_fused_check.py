@@ -1,0 +1,119 @@
+"""Multi-rank checks of the fused compute+collective paths against their un-fused comparators.
+Run under torchrun (NCCL, one rank per GPU) or with --cpu (gloo, un-fused logic only).  Prints 'ALL OK' on rank 0."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from consensusml_b200.parallel import dist as D
+from consensusml_b200.parallel.dist import shard_bounds
+
+
+def synth(n, p, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, p, generator=g)
+    beta = torch.zeros(p)
+    beta[:8] = torch.tensor([1.0, -1.0, 0.8, -0.8, 0.6, -0.6, 0.5, 0.5])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ beta)).float()
+    return x, y
+
+
+def main():
+    cpu = "--cpu" in sys.argv
+    from consensusml_b200.models import lasso_large as LL
+    n, p = (3000, 120) if cpu else (6000, 2500)
+    x, y = synth(n, p)
+    ref_single = None
+    if cpu:      # single-process answer first, while no process group exists (its all-reduces are then no-ops)
+        step0 = 1.0 / LL.lipschitz_estimate(x, n)
+        ref_single = LL._fit_unfused(x, y, 0.02, n, 150, 1e-5, None, None, step0, 10)
+    rank, world, dev = D.init("gloo" if cpu else None)
+    lo, hi = shard_bounds(n, world, rank)
+    xl, yl = x[lo:hi].to(dev), y[lo:hi].to(dev)
+    ok = True
+    if cpu:
+        fit = LL.fit(xl, yl, 0.02, n_total=n, max_iter=150, backend="unfused", step=step0)
+        if rank == 0:
+            err = float((fit.beta - ref_single.beta).abs().max())
+            print("gloo sharded vs single-process beta max diff", err, "nnz", int((fit.beta != 0).sum()))
+            ok &= err < 1e-4
+    else:
+        from consensusml_b200.parallel import fused as F
+        # ---- path 2: X^T R reduce-scatter
+        for nb in (1, 4):
+            g = torch.Generator().manual_seed(5 + nb)
+            R = torch.randn(n, nb, generator=g)[lo:hi].contiguous().to(dev)
+            xb = F.to_bf16_padded(xl)
+            rs = F.XtrReduceScatter(p, nb, dev)
+            for rep in range(2):                      # twice: the scratch cleans itself
+                rs.launch(xb, R)
+                rs.wait()
+                torch.cuda.synchronize()
+                got = rs.result().clone()
+                ref = F.xtr_reduce_scatter_unfused(xb[:, :p], R, p)
+                err = float((got - ref).abs().max() / ref.abs().max())
+                torch.cuda.synchronize(); rs.grad.barrier()
+                rs.grad.local.zero_()
+                torch.cuda.synchronize(); rs.grad.barrier()
+                print(f"[{rank}] xtr_rs nb={nb} rep={rep} rel err {err:.2e}", flush=True)
+                ok &= err < 1e-4
+        # ---- path 3: all-gather -> tcgen05 Gram
+        for kern in ("radial", "linear"):
+            got = F.gram_allgather(xl, kernel=kern, n_total=n)
+            # comparator needs equal block sizes
+            ref = F.gram_allgather_unfused(xl, kernel=kern)
+            if n % world == 0:
+                err = float((got - ref).abs().max() / ref.abs().max())
+                print(f"[{rank}] gram_allgather {kern} rel err {err:.2e}", flush=True)
+                ok &= err < 2e-3
+        # ---- path 1: histogram + all-reduce (NVLS multicast and peer-red variants)
+        nbins, pf, n_nodes = 32, 96, 4
+        g = torch.Generator().manual_seed(9)
+        bins_full = torch.randint(0, nbins, (pf, n), generator=g, dtype=torch.uint8)
+        node_full = torch.randint(-1, n_nodes, (n,), generator=g).to(torch.int16)
+        gh_full = torch.randn(n, 2, generator=g)
+        nl = hi - lo
+        n_pad = (nl + 3) // 4 * 4
+        bins = torch.zeros(pf, n_pad, dtype=torch.uint8)
+        bins[:, :nl] = bins_full[:, lo:hi]
+        bins, node, gh = bins.to(dev), node_full[lo:hi].contiguous().to(dev), gh_full[lo:hi].contiguous().to(dev)
+        H = F.HistAllReduce(pf, nbins, 8, dev)
+        ref = F.hist_unfused(bins, nl, node, gh, n_nodes, pf, nbins)
+        for mc in (True, False):
+            got = H.build(bins, nl, node, gh, n_nodes, use_multicast=mc).clone()
+            torch.cuda.synchronize()
+            err = float((got - ref).abs().max() / ref.abs().max())
+            print(f"[{rank}] hist_allreduce multicast={mc} rel err {err:.2e}", flush=True)
+            ok &= err < 1e-4
+            H.clear(n_nodes)
+        gain, feat, b = F.best_splits(ref)
+        hh = ref.double()
+        cg, ch = hh[..., 0].cumsum(-1), hh[..., 1].cumsum(-1)
+        tg, th = cg[..., -1:], ch[..., -1:]
+        gn = cg ** 2 / (ch + 1) + (tg - cg) ** 2 / (th - ch + 1) - tg ** 2 / (th + 1)
+        valid = (hh[..., 1] > 0) & (ch >= 1) & (th - ch >= 1)
+        valid[..., -1] = False
+        gn = torch.where(valid, gn, torch.full_like(gn, -1e30))
+        bestg = gn.flatten(1).max(1).values
+        ok &= bool(torch.allclose(gain.double(), bestg.clamp_min(0), rtol=1e-3, atol=1e-3))
+        # ---- the sharded lasso: fused vs un-fused, same step and iteration count
+        fu = LL.fit(xl, yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="fused")
+        un = LL.fit(xl.bfloat16().float(), yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="unfused", step=fu.step)
+        err = float((fu.beta - un.beta).abs().max())
+        print(f"[{rank}] lasso_large fused vs unfused beta max diff {err:.2e} nnz {int((fu.beta != 0).sum())} obj {fu.objective:.5f}/{un.objective:.5f}", flush=True)
+        ok &= err < 2e-3
+    t = torch.tensor([1.0 if ok else 0.0], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("ALL OK" if float(t.item()) == 1.0 else "FAILED", flush=True)
+    D.shutdown()
+    sys.exit(0 if float(t.item()) == 1.0 else 1)
+
+
+if __name__ == "__main__":
+    main()
