@@ -37,7 +37,7 @@ class SymmBuffer:
         return self.handle.get_buffer(r, tuple(self.local.shape), self.local.dtype)
 
 
-_SIGNAL_PAD_WORDS = 4096
+_SIGNAL_PAD_WORDS = 256
 
 
 def alloc(shape, dtype, device) -> SymmBuffer:
@@ -59,4 +59,13 @@ def alloc(shape, dtype, device) -> SymmBuffer:
         mc = int(h.multicast_ptr or 0)
     except Exception:
         mc = 0
-    return SymmBuffer(t, [int(p) for p in h.buffer_ptrs], [int(p) for p in h.signal_pad_ptrs], mc, rank, world, h)
+    # Our kernels keep their completion words in a symmetric buffer of their own: torch's signal pad belongs to
+    # torch (its barrier() lives there), and sharing it deadlocks.
+    sig = sm.empty((_SIGNAL_PAD_WORDS,), dtype=torch.int32, device=device)
+    sig.zero_()
+    hs = sm.rendezvous(sig, dist.group.WORLD)
+    torch.cuda.synchronize()
+    h.barrier(channel=0)
+    buf = SymmBuffer(t, [int(p) for p in h.buffer_ptrs], [int(p) for p in hs.buffer_ptrs], mc, rank, world, h)
+    buf._pad, buf._pad_handle = sig, hs
+    return buf

@@ -24,6 +24,8 @@ def synth(n, p, seed=0):
 
 def main():
     cpu = "--cpu" in sys.argv
+    import faulthandler
+    faulthandler.dump_traceback_later(90, exit=True)      # a hung collective must not hold the GPU box
     from consensusml_b200.models import lasso_large as LL
     n, p = (3000, 120) if cpu else (6000, 2500)
     x, y = synth(n, p)
