@@ -1,0 +1,163 @@
+#!/usr/bin/env python
+"""Roofline report for the three fused compute+collective paths (and the plain tcgen05 GEMM) on a synthetic cohort
+sharded across the ranks: per-GPU shard fixed (weak scaling), device-timed with CUDA events, max over ranks,
+L2 flushed between repetitions.  Prints one JSON line per measurement on rank 0.
+
+    python bench/fused_paths.py                       # 1 GPU
+    torchrun --nproc-per-node N bench/fused_paths.py  # N GPUs
+
+Roofline denominators come from MEASURED_PEAKS.json (HBM copy bandwidth, cuBLAS bf16 throughput) and the
+measured NVLink peer bandwidth of the profiling recipe (770 GB/s per direction)."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+
+from consensusml_b200 import _native
+from consensusml_b200.parallel import dist as D
+from consensusml_b200.parallel import fused as F
+
+NVLINK_GBS = 770.0
+
+
+def peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return d["hbm_gbs"], d["bf16_tflops"], "measured"
+    except Exception:
+        return 6650.0, 1590.0, "fallback"
+
+
+def timed(fn, reps, flush):
+    ms = []
+    for _ in range(reps):
+        flush()
+        D.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    ms.sort()
+    return D.max_over_ranks(ms[len(ms) // 2])
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=125000, help="samples per GPU")
+    ap.add_argument("--genes", type=int, default=20000)
+    ap.add_argument("--gram-rows", type=int, default=8192, help="samples per GPU for the Gram path")
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--nodes", type=int, default=4)
+    ap.add_argument("--bins", type=int, default=256)
+    ap.add_argument("--skip", default="")
+    args = ap.parse_args()
+    rank, world, dev = D.init()
+    hbm, tf, how = peaks()
+    lib = _native.cuda()
+    fb = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush = lambda: lib.cml_l2_flush(_native.ptr(fb), fb.numel(), _native.stream_ptr())
+    n, p = args.rows, args.genes
+    out = []
+
+    def emit(**kw):
+        kw.update(n_gpus=world, peaks=how)
+        if rank == 0:
+            print(json.dumps(kw), flush=True)
+        out.append(kw)
+
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    # ------------------------------------------------------------------ path 2: X^T r + reduce-scatter
+    if "xtr" not in args.skip:
+        ld = (p + 7) // 8 * 8
+        xb = torch.empty(n, ld, dtype=torch.bfloat16, device=dev).normal_()
+        for nb in (1, 4):
+            R = torch.randn(n, nb, device=dev)
+            rs = F.XtrReduceScatter(p, nb, dev)
+
+            def run():
+                rs.launch(xb, R)
+                rs.wait()
+            run(); torch.cuda.synchronize(); rs.grad.barrier(); rs.grad.local.zero_(); torch.cuda.synchronize(); rs.grad.barrier()
+            ms = timed(run, args.reps, flush)
+            bytes_hbm = n * ld * 2 + n * nb * 4
+            link_bytes = p * nb * 4 * (world - 1) / world
+            t_roof = max(bytes_hbm / (hbm * 1e9), link_bytes / (NVLINK_GBS * 1e9), 2.0 * n * p * nb / (tf * 1e12))
+            emit(path="xtr_reduce_scatter", nb=nb, rows_per_gpu=n, genes=p, ms=ms, hbm_gbs=bytes_hbm / ms / 1e6,
+                 frac_of_hbm_roofline=t_roof / (ms / 1e3), nvlink_bytes=link_bytes)
+            if world > 1:
+                def run_un():
+                    full = xb[:, :p].float().t() @ R if False else torch.matmul(xb[:, :p].t().float() if False else xb.t()[:p].float(), R)
+                    o = torch.empty(rs.genes_per_rank, nb, device=dev)
+                    pad = torch.zeros(rs.genes_per_rank * world, nb, device=dev)
+                    pad[:p] = full
+                    dist.reduce_scatter_tensor(o, pad)
+                # the un-fused comparator materialises an fp32 copy of X; time only on small shards
+                if n * p <= 2e8:
+                    emit(path="xtr_unfused_torch_nccl", nb=nb, ms=timed(run_un, args.reps, flush))
+            del rs, R
+        del xb
+        torch.cuda.empty_cache()
+    # ------------------------------------------------------------------ path 1: histogram + all-reduce
+    if "hist" not in args.skip:
+        n_pad = (n + 3) // 4 * 4
+        bins = torch.randint(0, args.bins, (p, n_pad), dtype=torch.uint8, device=dev)
+        node = torch.randint(0, args.nodes, (n,), device=dev).to(torch.int16)
+        gh = torch.randn(n, 2, device=dev)
+        H = F.HistAllReduce(p, args.bins, args.nodes, dev)
+        for mc in ([True, False] if world > 1 else [False]):
+            def run():
+                H.build(bins, n, node, gh, args.nodes, use_multicast=mc)
+            run(); H.clear(args.nodes)
+            ms_list = []
+            for _ in range(args.reps):
+                flush(); D.barrier()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); run(); b.record(); torch.cuda.synchronize()
+                ms_list.append(a.elapsed_time(b)); H.clear(args.nodes)
+            ms_list.sort()
+            ms = D.max_over_ranks(ms_list[len(ms_list) // 2])
+            bytes_hbm = p * n_pad + n * 10
+            link = args.nodes * p * args.bins * 8 * (world - 1) / world
+            t_roof = max(bytes_hbm / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
+            emit(path="hist_allreduce", multicast=mc, rows_per_gpu=n, genes=p, bins=args.bins, nodes=args.nodes, ms=ms,
+                 frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, smem_atomics=2.0 * n * p, atomics_per_s=2.0 * n * p / ms * 1e3)
+        del bins, H
+        torch.cuda.empty_cache()
+    # ------------------------------------------------------------------ path 3: all-gather -> tcgen05 Gram (RBF)
+    if "gram" not in args.skip:
+        m = args.gram_rows
+        x = torch.randn(m, p, device=dev)
+        cache = {}
+
+        def run():
+            F.gram_allgather(x, kernel="radial", n_total=m * world, cache=cache)
+        run()
+        # time only the GEMM (conversion + publication are set-up): re-issue it on the published blocks
+        from consensusml_b200.ops import gemm as G
+        xbuf, nrm = cache["xb"], cache["nrm"]
+        ld = xbuf.local.shape[1]
+        outbuf = torch.empty(m, (m * world + 3) // 4 * 4, device=dev)
+
+        def gemm_only():
+            G.gemm_tn(xbuf.local, None, m * world, epilogue=G.EPI_RBF, alpha=1.0 / p, norm_a=nrm.local, b_ptrs=xbuf.peer_ptrs,
+                      norm_b_ptrs=nrm.peer_ptrs, rows_per_src=m, ldb=ld, out=outbuf)
+        gemm_only()
+        ms = timed(gemm_only, args.reps, flush)
+        flops = 2.0 * m * m * world * ld
+        link = (world - 1) * m * ld * 2
+        t_roof = max(flops / (tf * 1e12), link / (NVLINK_GBS * 1e9))
+        emit(path="gram_allgather_tcgen05_rbf", rows_per_gpu=m, genes=p, ms=ms, tflops=flops / ms / 1e9,
+             frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
+    D.barrier()
+    D.shutdown()
+
+
+if __name__ == "__main__":
+    main()

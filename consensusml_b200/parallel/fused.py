@@ -30,7 +30,7 @@ _native.register_signature("cml_prox_allgather", [_P, _I, _I, _P, _F, _F, _F, _F
 _native.register_signature("cml_xb_residual", [_P, _LL, _I, _I, _P, _F, _P, _P, _P, _P, _P, _P])
 _native.register_signature("cml_hist_scratch_bytes", [_I, _I], _SZ)
 _native.register_signature("cml_hist_ft", [_I, _I], _I)
-_native.register_signature("cml_hist_allreduce", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _U, _I, _P])
+_native.register_signature("cml_hist_allreduce", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _U, _I, _F, _F, _P])
 _native.register_signature("cml_split_score_gain", [_P, _I, _I, _I, _F, _F, _F, _P, _P])
 
 SIG_GRAD, SIG_BETA, SIG_HIST = 0, 8, 16      # signal-pad word ranges (one word per rank each)
@@ -168,14 +168,21 @@ class HistAllReduce:
         self.counters = torch.zeros(p + 16, dtype=torch.int32, device=device)
         self.epoch = 0
 
-    def build(self, bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, n_nodes: int, use_multicast: bool = True):
-        """Launch build + reduce; returns the reduced histogram view [n_nodes, p, nbins, 2] after waiting."""
+    def build(self, bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, n_nodes: int, use_multicast: bool = True,
+              g_bound: Optional[float] = None, h_bound: Optional[float] = None):
+        """Launch build + reduce; returns the reduced histogram view [n_nodes, p, nbins, 2] after waiting.
+        ``g_bound`` / ``h_bound`` bound |g| and |h| (1 and 0.25 for logistic loss); they fix the fixed-point scale of the
+        shared-memory accumulation and are measured from ``gh`` when omitted."""
+        if g_bound is None or h_bound is None:
+            mx = gh.abs().amax(0)
+            g_bound, h_bound = float(mx[0]) + 1e-30, float(mx[1]) + 1e-30
         self.epoch += 1
         mc = self.hist.multicast_ptr if (use_multicast and self.world > 1) else 0
         rc = _native.cuda().cml_hist_allreduce(
             _native.ptr(bins), bins.shape[1], n, self.p, self.nbins, _native.ptr(node), _native.ptr(gh), n_nodes,
             _native.ptr(self.local), _native.ptr(self.counters), ctypes.c_void_p(mc), _ptr_array(self.hist.peer_ptrs),
-            _ptr_array(self.hist.signal_ptrs), self.rank, self.world, self.epoch, SIG_HIST, _native.stream_ptr())
+            _ptr_array(self.hist.signal_ptrs), self.rank, self.world, self.epoch, SIG_HIST, float(g_bound), float(h_bound),
+            _native.stream_ptr())
         _native.check(rc, "cml_hist_allreduce")
         rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(self.hist.signal_ptrs[self.rank]), SIG_HIST, self.world, self.epoch,
                                              _native.stream_ptr())

@@ -247,36 +247,45 @@ constexpr int kHistThreads = 256;
 __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
     const unsigned char* __restrict__ bins, long long n_pad, int n, int p, int nbins, const short* __restrict__ node,
     const float2* __restrict__ gh, int n_nodes, int FT, float* __restrict__ local_hist, unsigned* __restrict__ tile_count,
-    unsigned* __restrict__ done_count, float* mc_hist, Peers P, unsigned epoch, int rows_per_chunk, int sig_base) {
-  extern __shared__ float sh[];                 // [n_nodes][FT][nbins][2]
+    unsigned* __restrict__ done_count, float* mc_hist, Peers P, unsigned epoch, int rows_per_chunk, int sig_base, float scale_g,
+    float scale_h) {
+  // Shared-memory accumulation is int32 fixed point: fp32 shared atomics compile to a CAS loop (ATOMS.CAST.SPIN) while
+  // integer adds are native ATOMS.ADD, and integer sums are order independent (bit-reproducible histograms).
+  extern __shared__ int sh[];                   // [n_nodes][FT][nbins][2]
   __shared__ unsigned sh_last;
   const int tile = blockIdx.x, chunk = blockIdx.y;
   const int f0 = tile * FT, f1 = min(p, f0 + FT);
   const int per_node = FT * nbins * 2;
   const int sh_total = n_nodes * per_node;
-  for (int t = threadIdx.x; t < sh_total; t += blockDim.x) sh[t] = 0.f;
+  for (int t = threadIdx.x; t < sh_total; t += blockDim.x) sh[t] = 0;
   __syncthreads();
   const int i0 = chunk * rows_per_chunk, i1 = min(n, i0 + rows_per_chunk);
   for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
     const int nd = node[i];
     if (nd < 0) continue;
-    const float2 g = gh[i];
+    const float2 gf = gh[i];
+    const int qg = __float2int_rn(gf.x * scale_g), qh = __float2int_rn(gf.y * scale_h);
     for (int f = f0; f < f1; ++f) {
       const int b = bins[(size_t)f * n_pad + i];
-      float* cell = sh + nd * per_node + ((f - f0) * nbins + b) * 2;
-      atomicAdd(cell, g.x);
-      atomicAdd(cell + 1, g.y);
+      // shared layout [node][feature][plane g|h][bin]: consecutive bins sit in consecutive banks, so the 32 lanes of an
+      // atomic spread over all 32 banks (an interleaved (g,h) pair would confine each instruction to 16 of them)
+      int* cell = sh + nd * per_node + (f - f0) * nbins * 2 + b;
+      atomicAdd(cell, qg);
+      atomicAdd(cell + nbins, qh);
     }
   }
   __syncthreads();
   // fold into the rank-local histogram: layout [node][p][nbins][2]
+  const float inv_g = 1.f / scale_g, inv_h = 1.f / scale_h;
   for (int t = threadIdx.x; t < sh_total; t += blockDim.x) {
-    const float v = sh[t];
-    if (v == 0.f) continue;
+    const int q = sh[t];
+    if (q == 0) continue;
     const int nd = t / per_node, rem = t % per_node;
     const int f = f0 + rem / (nbins * 2);
     if (f >= f1) continue;
-    atomicAdd(&local_hist[((size_t)nd * p + f) * nbins * 2 + rem % (nbins * 2)], v);
+    const int within = rem % (nbins * 2), plane = within / nbins, b = within % nbins;
+    const float v = (float)q * (plane ? inv_h : inv_g);
+    atomicAdd(&local_hist[(((size_t)nd * p + f) * nbins + b) * 2 + plane], v);
   }
   __threadfence();
   __syncthreads();
@@ -450,7 +459,8 @@ size_t cml_hist_scratch_bytes(int p, int ft) { return (size_t)(cml::ceil_div(p, 
 // every rank's symmetric copy (peer_bufs[r]); those copies must be zero at entry.
 int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
                        int n_nodes, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
-                       const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, void* stream) {
+                       const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, float g_bound, float h_bound,
+                       void* stream) {
   using namespace cml;
   CML_REQUIRE(n > 0 && p > 0 && nbins >= 2 && nbins <= 256 && n_nodes >= 1, CML_EINVAL, "cml_hist_allreduce: bad shape");
   CML_REQUIRE((nbins * 2) % 4 == 0, CML_EINVAL, "cml_hist_allreduce: nbins must be even");
@@ -467,9 +477,12 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
   chunks = ceil_div(n, rows_per_chunk);
   Peers P = make_peers(peer_bufs, peer_sigs, rank, world);
   dim3 grid(tiles, chunks);
+  CML_REQUIRE(g_bound > 0.f && h_bound > 0.f, CML_EINVAL, "cml_hist_allreduce: |g| and |h| bounds must be positive");
+  // the largest per-CTA sum is rows_per_chunk * bound: scale so that it stays below 2^30
+  const float scale_g = 1073741824.f / ((float)rows_per_chunk * g_bound), scale_h = 1073741824.f / ((float)rows_per_chunk * h_bound);
   hist_allreduce_kernel<<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
       bins, n_pad, n, p, nbins, node, static_cast<const float2*>(gh), n_nodes, FT, local_hist, tile_count, done, mc_hist, P, epoch,
-      rows_per_chunk, sig_base);
+      rows_per_chunk, sig_base, scale_g, scale_h);
   CML_LAUNCH_CHECK();
   return 0;
 }

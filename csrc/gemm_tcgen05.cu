@@ -307,7 +307,9 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
               (long long)n_src * rows_per_src, N);
   GemmParams P;
   memset(&P, 0, sizeof(P));
-  const int BN = 128;
+  // N = 256 per MMA halves the shared-memory bytes read per FLOP (the 128x128 atom reads A+B at exactly the 128 B/clk
+  // shared-memory rate); use it whenever a source is wide enough to fill such tiles
+  const int BN = (rows_per_src < N ? rows_per_src : N) >= 768 ? 256 : 128;
   int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
   if (rc) return rc;
   for (int s = 0; s < n_src; ++s) {
@@ -328,6 +330,7 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
   P.alpha = alpha;
   P.tiles_m = ceil_div(M, BM);
   P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
+  if (BN == 256) return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
   return launch_gemm<128, 6>(P, static_cast<cudaStream_t>(stream));
 }
 
