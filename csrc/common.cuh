@@ -43,6 +43,14 @@ __device__ __forceinline__ float warp_sum(float v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
   return v;
 }
+// four independent butterfly reductions, interleaved so that their shuffle latencies overlap
+__device__ __forceinline__ void warp_sum4(float (&v)[4]) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) v[q] += __shfl_xor_sync(FULL, v[q], o);
+  }
+}
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);

@@ -87,29 +87,49 @@ struct Warp {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) x[j] = __ldg(xk + 32 * j);
   }
+  // Streaming variant for the KKT pass over all p genes: bypass L1 so that the pass does not evict the screened
+  // columns the coordinate sweeps keep coming back to.
+  __device__ __forceinline__ void load_col_stream(int k, float (&x)[NPL]) const {
+    const float* xk = P.xt + (size_t)k * P.n_pad + lane;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j)
+      asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(x[j]) : "l"(xk + 32 * j));
+  }
   __device__ __forceinline__ float vpk(int k) const { return P.vp ? __ldg(P.vp + k) : 1.f; }
   __device__ __forceinline__ bool bit(const unsigned* s, int k) const { return (s[k >> 5] >> (k & 31)) & 1u; }
 
+  // Everything a coordinate step needs from memory, fetched a few coordinates ahead of its use: the column (L2/L1),
+  // the coefficient, curvature and penalty factor (global scratch).  The step itself then has no load on its
+  // critical path - only the dot product, the butterfly reduction and the scalar soft-threshold.
+  struct Pre {
+    float x[NPL];
+    float bk, xvk, pk;
+    int k;
+  };
+  __device__ __forceinline__ void fetch(int k, Pre& e) const {
+    e.k = k;
+    load_col(k, e.x);
+    e.bk = b[k];
+    e.xvk = xv[k];
+    e.pk = vpk(k);
+  }
+
   // One coordinate step; returns true when the coefficient moved.
-  __device__ __forceinline__ bool cd(int k, const float (&x)[NPL], float al1, float al2, float& dlx) {
-    // scalar state first: these global loads then overlap the dot product and its butterfly reduction
-    const float bk = b[k], xvk = xv[k], pk = vpk(k);
+  __device__ __forceinline__ bool cd(const Pre& e, float al1, float al2, float& dlx) {
     float g = 0.f;
 #pragma unroll
-    for (int j = 0; j < NPL; ++j) g = fmaf(r[j], x[j], g);
+    for (int j = 0; j < NPL; ++j) g = fmaf(r[j], e.x[j], g);
     g = warp_sum(g);
-    const float u = g + xvk * bk;
-    const float au = fabsf(u) - pk * al1;
-    const float nb = au > 0.f ? copysignf(au, u) / (xvk + pk * al2) : 0.f;
-    const float d = nb - bk;
+    const float u = g + e.xvk * e.bk;
+    const float au = fabsf(u) - e.pk * al1;
+    const float nb = au > 0.f ? copysignf(au, u) / (e.xvk + e.pk * al2) : 0.f;
+    const float d = nb - e.bk;
     if (d == 0.f) return false;
-    __syncwarp();
-    if (lane == 0) b[k] = nb;
-    dlx = fmaxf(dlx, xvk * d * d);
+    if (lane == 0) b[e.k] = nb;
+    dlx = fmaxf(dlx, e.xvk * d * d);
 #pragma unroll
-    for (int j = 0; j < NPL; ++j) r[j] = fmaf(-d * v[j], x[j], r[j]);
+    for (int j = 0; j < NPL; ++j) r[j] = fmaf(-d * v[j], e.x[j], r[j]);
     ++version;
-    __syncwarp();
     return true;
   }
 
@@ -130,10 +150,10 @@ struct Warp {
   }
 
   // Sweep over the whole screened set in feature order; new non-zeros join the active list.
-  // Returns false on active-list overflow.
+  // Returns false on active-list overflow.  A coordinate is visited once per sweep, so values prefetched two
+  // coordinates ahead cannot be stale.
   __device__ bool sweep_screened(float al1, float al2, float& dlx) {
     const int pw = (P.p + 31) >> 5;
-    // walk the set bits in feature order with the NEXT column already in flight
     int wd = 0;
     unsigned bits = 0u;
     auto next_feature = [&]() -> int {
@@ -145,42 +165,44 @@ struct Warp {
       bits &= bits - 1;
       return k;
     };
-    int k = next_feature();
-    if (k < 0) return true;
-    float xc[NPL], xn[NPL];
-    load_col(k, xc);
-    while (k >= 0) {
-      const int kn = next_feature();
-      if (kn >= 0) load_col(kn, xn);
-      const bool was_in = bit(inm, k);
-      if (cd(k, xc, al1, al2, dlx) && !was_in) {
+    Pre e0, e1, e2;
+    int k0 = next_feature();
+    if (k0 < 0) return true;
+    fetch(k0, e0);
+    int k1 = next_feature();
+    if (k1 >= 0) fetch(k1, e1);
+    __syncwarp();
+    while (k0 >= 0) {
+      const int k2 = k1 >= 0 ? next_feature() : -1;
+      if (k2 >= 0) fetch(k2, e2);
+      const bool was_in = bit(inm, k0);
+      if (cd(e0, al1, al2, dlx) && !was_in) {
         if (nin >= P.nx) return false;
         __syncwarp();   // every lane has read the membership word before lane 0 rewrites it
         if (lane == 0) {
-          inm[k >> 5] |= 1u << (k & 31);
-          m[nin] = k;
+          inm[k0 >> 5] |= 1u << (k0 & 31);
+          m[nin] = k0;
         }
         ++nin;
-        __syncwarp();
       }
-#pragma unroll
-      for (int j = 0; j < NPL; ++j) xc[j] = xn[j];
-      k = kn;
+      e0 = e1; e1 = e2;
+      k0 = k1; k1 = k2;
     }
+    __syncwarp();
     return true;
   }
 
   __device__ void sweep_active(float al1, float al2, float& dlx) {
     if (nin == 0) return;
-    float xc[NPL], xn[NPL];
-    load_col(m[0], xc);
+    Pre e0, e1, e2;
+    fetch(m[0], e0);
+    if (nin > 1) fetch(m[1], e1);
     for (int l = 0; l < nin; ++l) {
-      const int k = m[l];
-      if (l + 1 < nin) load_col(m[l + 1], xn);   // prefetch the next column under this reduction
-      cd(k, xc, al1, al2, dlx);
-#pragma unroll
-      for (int j = 0; j < NPL; ++j) xc[j] = xn[j];
+      if (l + 2 < nin) fetch(m[l + 2], e2);
+      cd(e0, al1, al2, dlx);
+      e0 = e1; e1 = e2;
     }
+    __syncwarp();          // lane 0's coefficient stores are ordered before whatever reads them next
   }
 
   // Recompute q, v, r at the current coefficients. Returns sum(v).
@@ -219,7 +241,7 @@ struct Warp {
 };
 
 template <int NPL>
-__global__ void __launch_bounds__(32, (NPL <= 4 ? 32 : (NPL <= 8 ? 24 : 12)))
+__global__ void __launch_bounds__(32, (NPL <= 4 ? 28 : (NPL <= 8 ? 20 : 12)))
 lognet_path_kernel(const LognetParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x;
@@ -367,15 +389,30 @@ lognet_path_kernel(const LognetParams P) {
             for (int wd = 0; wd < pw; ++wd) {
               unsigned bits = W.ixx[wd];
               while (bits) {
-                const int k = (wd << 5) + __ffs(bits) - 1;
-                bits &= bits - 1;
-                float x[NPL];
-                W.load_col(k, x);
-                float s = 0.f;
+                int kk[4];
+                int c = 0;
 #pragma unroll
-                for (int j = 0; j < NPL; ++j) s = fmaf(W.v[j] * x[j], x[j], s);
-                s = warp_sum(s);
-                if (lane == 0) W.xv[k] = s;
+                for (int q = 0; q < 4; ++q) {
+                  kk[q] = bits ? (wd << 5) + __ffs(bits) - 1 : -1;
+                  if (bits) { bits &= bits - 1; ++c; }
+                }
+                float sacc[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  sacc[q] = 0.f;
+                  if (q < c) {
+                    float x[NPL];
+                    W.load_col(kk[q], x);        // these columns are swept next: keep them in L1
+#pragma unroll
+                    for (int j = 0; j < NPL; ++j) sacc[q] = fmaf(W.v[j] * x[j], x[j], sacc[q]);
+                  }
+                }
+                warp_sum4(sacc);
+                if (lane == 0) {
+#pragma unroll
+                  for (int q = 0; q < 4; ++q)
+                    if (q < c) W.xv[kk[q]] = sacc[q];
+                }
               }
             }
             __syncwarp();
@@ -422,17 +459,35 @@ lognet_path_kernel(const LognetParams P) {
               unsigned todo = use & ~skip;
               unsigned newbits = 0u;
               while (todo) {
-                const int kk = __ffs(todo) - 1;
-                todo &= todo - 1;
-                const int k = k0 + kk;
-                float x[NPL];
-                W.load_col(k, x);
-                float g = 0.f;
+                // four independent gradients at a time: their column loads and butterfly reductions overlap
+                int kk[4];
+                int c = 0;
 #pragma unroll
-                for (int j = 0; j < NPL; ++j) g = fmaf(W.r[j], x[j], g);
-                g = fabsf(warp_sum(g));
-                if (lane == 0) W.ga[k] = g;
-                if (g > al1 * W.vpk(k)) newbits |= 1u << kk;
+                for (int q = 0; q < 4; ++q) {
+                  kk[q] = todo ? __ffs(todo) - 1 : -1;
+                  if (todo) { todo &= todo - 1; ++c; }
+                }
+                float g[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  g[q] = 0.f;
+                  if (q < c) {
+                    float x[NPL];
+                    W.load_col_stream(k0 + kk[q], x);
+#pragma unroll
+                    for (int j = 0; j < NPL; ++j) g[q] = fmaf(W.r[j], x[j], g[q]);
+                  }
+                }
+                warp_sum4(g);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  if (q < c) {
+                    const int k = k0 + kk[q];
+                    const float ag = fabsf(g[q]);
+                    if (lane == 0) W.ga[k] = ag;
+                    if (ag > al1 * W.vpk(k)) newbits |= 1u << kk[q];
+                  }
+                }
               }
               if (newbits) {
                 added = true;
@@ -529,7 +584,7 @@ size_t smem_bytes(int p, int nx, int n_pad) {
 
 int resident_warps(int n_pad) {
   const int npl = n_pad / 32;
-  const int per_sm = npl <= 4 ? 32 : (npl <= 8 ? 24 : 12);
+  const int per_sm = npl <= 4 ? 28 : (npl <= 8 ? 20 : 12);
   return per_sm * sm_count();
 }
 
