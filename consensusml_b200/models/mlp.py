@@ -1,0 +1,133 @@
+"""Small dense networks trained over a hyper-parameter grid in one batch (K17).
+
+The reference advertises "Neural Networks with keras" (README.md:25) but ships no such code; BASELINE.json asks for a
+"small Keras-style MLP" trained across its hyper-parameter grid.  All G configurations (hidden width, learning rate,
+weight decay, seed) are trained together: their first layers are concatenated along the output axis, so the forward
+p -> sum(h) product and the matching weight-gradient are two tcgen05 GEMMs per step on CUDA
+(``ops.gemm.gemm_tn``, bf16 operands / fp32 accumulate, fp32 master weights); the per-configuration tails are
+block-diagonal and tiny.  Sample-sharded training all-reduces the concatenated gradient once per step.
+CPU tensors run the same maths in fp32 torch."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from itertools import product
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from ..ops import gemm as G
+from ..parallel.dist import all_reduce_
+
+
+@dataclass
+class MLPGridResult:
+    configs: List[Dict]
+    train_loss: torch.Tensor       # [G]
+    val_loss: Optional[torch.Tensor]
+    val_auc: Optional[torch.Tensor]
+    w1: torch.Tensor               # [H_total, p]
+    b1: torch.Tensor
+    w2: torch.Tensor               # [H_total]
+    b2: torch.Tensor               # [G]
+    offsets: List[int]
+    mean: torch.Tensor
+    scale: torch.Tensor
+
+    def predict_proba(self, x: torch.Tensor, config: int) -> torch.Tensor:
+        xs = ((x.float() - self.mean) / self.scale)
+        lo, hi = self.offsets[config], self.offsets[config + 1]
+        h = torch.relu(xs @ self.w1[lo:hi].t() + self.b1[lo:hi])
+        return torch.sigmoid(h @ self.w2[lo:hi] + self.b2[config])
+
+    def input_importance(self, config: int) -> torch.Tensor:
+        """|w2|-weighted column norms of the first layer: a per-gene importance for the consensus table."""
+        lo, hi = self.offsets[config], self.offsets[config + 1]
+        return (self.w1[lo:hi].abs() * self.w2[lo:hi].abs()[:, None]).sum(0)
+
+
+def make_grid(hidden=(16, 32, 64), lr=(1e-3, 3e-3), weight_decay=(0.0, 1e-3), seeds=(0,)) -> List[Dict]:
+    return [dict(hidden=h, lr=l, weight_decay=w, seed=s) for h, l, w, s in product(hidden, lr, weight_decay, seeds)]
+
+
+def _matmul_nt(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """a [M, K] @ b[N, K]^T.  On CUDA with GEMM-sized shapes this is the tcgen05 kernel."""
+    if a.is_cuda and a.shape[0] >= 32 and b.shape[0] >= 64 and a.shape[1] >= 64:
+        ab, _ = G.to_bf16_rows(a.contiguous())
+        bb, _ = G.to_bf16_rows(b.contiguous())
+        return G.gemm_tn(ab, [bb], b.shape[0])
+    return a @ b.t()
+
+
+def train_grid(x: torch.Tensor, y: torch.Tensor, configs: Sequence[Dict], epochs: int = 200, x_val: Optional[torch.Tensor] = None,
+               y_val: Optional[torch.Tensor] = None, n_total: Optional[int] = None) -> MLPGridResult:
+    """Full-batch Adam on binary cross-entropy for every configuration at once (one hidden ReLU layer)."""
+    from ..ops.metrics import auc
+    dev = x.device
+    n, p = x.shape
+    n_total = n if n_total is None else n_total
+    xf = x.float()
+    mean = xf.mean(0)
+    sd = xf.std(0, unbiased=True)
+    scale = torch.where(sd > 0, sd, torch.ones_like(sd))
+    xs = ((xf - mean) / scale).contiguous()
+    yf = y.float()
+    Gn = len(configs)
+    hs = [int(c["hidden"]) for c in configs]
+    offsets = [0] + list(np.cumsum(hs))
+    H = offsets[-1]
+    w1 = torch.empty(H, p, device=dev)
+    w2 = torch.empty(H, device=dev)
+    for gi, c in enumerate(configs):
+        gen = torch.Generator(device="cpu").manual_seed(int(c.get("seed", 0)) * 1009 + gi)
+        lo, hi = offsets[gi], offsets[gi + 1]
+        w1[lo:hi] = (torch.randn(hi - lo, p, generator=gen) * np.sqrt(2.0 / p)).to(dev)
+        w2[lo:hi] = (torch.randn(hi - lo, generator=gen) * np.sqrt(1.0 / (hi - lo))).to(dev)
+    b1 = torch.zeros(H, device=dev)
+    b2 = torch.zeros(Gn, device=dev)
+    seg = torch.repeat_interleave(torch.arange(Gn, device=dev), torch.tensor(hs, device=dev))     # hidden unit -> config
+    lr_u = torch.tensor([c["lr"] for c in configs], device=dev)[seg]
+    wd_u = torch.tensor([c.get("weight_decay", 0.0) for c in configs], device=dev)[seg]
+    lr_g = torch.tensor([c["lr"] for c in configs], device=dev)
+    params = [w1, b1, w2, b2]
+    m = [torch.zeros_like(t) for t in params]
+    v = [torch.zeros_like(t) for t in params]
+    lrs = [lr_u[:, None], lr_u, lr_u, lr_g]
+    wds = [wd_u[:, None], None, wd_u, None]
+    b1a, b2a, eps = 0.9, 0.999, 1e-8
+    xst = xs.t().contiguous()
+    loss_g = torch.zeros(Gn, device=dev)
+    for t in range(1, epochs + 1):
+        pre = _matmul_nt(xs, w1) + b1                                  # [n, H]   GEMM 1
+        h = torch.relu(pre)
+        logit = torch.zeros(n, Gn, device=dev).index_add_(1, seg, h * w2[None, :]) + b2[None, :]
+        prob = torch.sigmoid(logit)
+        dlogit = (prob - yf[:, None]) / n_total                        # [n, G]
+        loss_g = -(yf[:, None] * torch.log(prob.clamp_min(1e-12)) + (1 - yf[:, None]) * torch.log((1 - prob).clamp_min(1e-12))).sum(0)
+        dh = dlogit[:, seg] * w2[None, :] * (pre > 0)                  # [n, H]
+        gw2 = (dlogit[:, seg] * h).sum(0)
+        gb2 = dlogit.sum(0)
+        gw1 = _matmul_nt(dh.t().contiguous(), xst)                     # [H, p]   GEMM 2
+        gb1 = dh.sum(0)
+        grads = [gw1, gb1, gw2, gb2]
+        for gr in grads:
+            all_reduce_(gr)                                            # sample-sharded: one reduction per tensor
+        for i, (pt, gr) in enumerate(zip(params, grads)):
+            if wds[i] is not None:
+                gr = gr + wds[i] * pt
+            m[i].mul_(b1a).add_(gr, alpha=1 - b1a)
+            v[i].mul_(b2a).addcmul_(gr, gr, value=1 - b2a)
+            mh = m[i] / (1 - b1a ** t)
+            vh = v[i] / (1 - b2a ** t)
+            pt.sub_(lrs[i] * mh / (vh.sqrt() + eps))
+    all_reduce_(loss_g)
+    res = MLPGridResult(list(configs), loss_g / n_total, None, None, w1, b1, w2, b2, [int(o) for o in offsets], mean, scale)
+    if x_val is not None:
+        yv = y_val.float()
+        vl, va = [], []
+        for gi in range(Gn):
+            pr = res.predict_proba(x_val, gi).clamp(1e-12, 1 - 1e-12)
+            vl.append(float(-(yv * torch.log(pr) + (1 - yv) * torch.log(1 - pr)).mean()))
+            va.append(auc(pr, yv))
+        res.val_loss, res.val_auc = torch.tensor(vl), torch.tensor(va)
+    return res
