@@ -1,0 +1,83 @@
+"""Command line: ``python -m consensusml_b200.cli <command> [--config file] [section.key=value ...]``.
+
+The reference has no CLI - its entry points are "open the notebook and run the chunks" (SURVEY.md 1).  Commands:
+
+  run         the full ensemble + consensus pipeline (default cohort: bundled TARGET-AML)
+  lasso       the reference's headline model only (runLasso + gene CSV)
+  de          limma-voom DE on a counts CSV: writes the DEG table in the reference's format
+  normalize   TMM log2-CPM of a counts CSV
+  build       compile the native libraries
+  config      print the resolved configuration
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="consensusml_b200", description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("command", choices=["run", "lasso", "de", "normalize", "build", "config"])
+    ap.add_argument("--config", default=None)
+    ap.add_argument("--counts", default=None, help="genes x samples counts CSV")
+    ap.add_argument("--groups", default=None, help="CSV with columns sample,group (1 = non-reference level)")
+    ap.add_argument("overrides", nargs="*", help="section.key=value")
+    args = ap.parse_args(argv)
+    from ..runtime import config as C
+    cfg = C.load(args.config, args.overrides)
+    if args.command == "config":
+        print(json.dumps(cfg.to_dict(), indent=1))
+        return 0
+    if args.command == "build":
+        from .. import _build
+        _build.build_all()
+        print(_build.ptxas_report())
+        return 0
+    import numpy as np
+    import pandas as pd
+    import torch
+    from .. import pipeline
+    dev = pipeline.resolve_device(cfg)
+    os.makedirs(cfg.io.out_dir, exist_ok=True)
+    if args.command == "run":
+        summary = pipeline.run(cfg)
+        print(json.dumps(summary, indent=1, default=str))
+        return 0
+    if args.command == "lasso":
+        from .. import consensus, datasets
+        from ..models import lasso
+        res = lasso.run_lasso(datasets.load_target_aml(), seed=cfg.lasso.seed, alpha=cfg.lasso.alpha, nfolds=cfg.lasso.nfolds, device=dev)
+        path = os.path.join(cfg.io.out_dir, "Logistic_Lasso_RiskGroup_Associated_Genes.csv")
+        consensus.write_lasso_gene_csv(res.nonzero_coef, path)
+        print(json.dumps({"lambda_min": res.cv.lambda_min, "test_error": res.test_error, "auc": res.test_auc,
+                          "confusion": res.confusion.tolist(), "genes": len(res.nonzero_coef), "csv": path}))
+        return 0
+    if args.counts is None:
+        ap.error(f"'{args.command}' needs --counts")
+    from ..io import counts as IC
+    counts, genes, samples = IC.read_counts_csv(args.counts)
+    counts = counts.to(dev)
+    if args.command == "normalize":
+        from ..stats import normalize as N
+        norm = N.tmm_normalize(counts, cfg.normalize.min_cpm, cfg.normalize.min_samples, prior_count=cfg.normalize.prior_count)
+        kept = [g for g, k in zip(genes, norm.keep.cpu().tolist()) if k]
+        IC.write_matrix_csv(os.path.join(cfg.io.out_dir, "TMMCPM_log2_Norm_Counts.csv"), norm.logcpm, kept, samples)
+        print(json.dumps({"genes_kept": len(kept), "norm_factor_range": [float(norm.norm_factors.min()), float(norm.norm_factors.max())]}))
+        return 0
+    if args.command == "de":
+        if args.groups is None:
+            ap.error("'de' needs --groups")
+        from ..stats import de as DE
+        g = pd.read_csv(args.groups).set_index("sample").loc[samples, "group"].to_numpy()
+        res = DE.voom_de(counts, g, min_frac=cfg.de.min_frac, p_value=cfg.de.p_value, lfc=cfg.de.lfc, span=cfg.de.span)
+        path = os.path.join(cfg.io.out_dir, "DEGs.csv")
+        DE.write_deg_table(res.table(genes), path)
+        print(json.dumps({"genes_tested": int(res.keep.sum()), "degs": int(len(res.deg_order)), "csv": path}))
+        return 0
+    return 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,141 @@
+"""Sample filters, label recoding, train/test splits and class re-balancing.
+
+Reference: tissue-code filter and label recoding (JSmith_code/Differential_Expression_and_Lasso.Rmd:119-146;
+seobjects/make_seobj_targetaml.R:56-83; scripts/model_comp.py:58-60; cml_targetaml_seanalysis.Rmd:435-451), the
+seed-2019 two-thirds split (Differential_Expression_and_Lasso.Rmd:159-186), the fixed id lists
+(JSmith_code/TARGET_AML_{Training,Testing}_Samples.csv), the 70/30 split of VikasP/AML.R:159-165 and the ROSE
+over-sampling stub (Differential_Expression_and_Lasso.Rmd:536-543)."""
+from __future__ import annotations
+
+from typing import Iterable, Optional, Sequence, Tuple
+
+import numpy as np
+import pandas as pd
+
+from ..data import Cohort
+
+NON_DIAGNOSTIC = ("04A", "40A", "02A", "06A", "11A")          # excluded at DEL:122
+PRIMARY = ("03A", "09A")                                        # kept at MSE:56-59
+
+
+def diagnostic_id(barcode: str) -> str:
+    return barcode.replace("-", ".").split(".")[3] if barcode.count(".") + barcode.count("-") >= 3 else ""
+
+
+def filter_diagnostic(clinical: pd.DataFrame, column: str = "Diagnostic ID", drop: Iterable[str] = NON_DIAGNOSTIC,
+                      keep: Optional[Iterable[str]] = None) -> pd.DataFrame:
+    ids = clinical[column].astype(str)
+    if keep is not None:
+        return clinical[ids.isin(list(keep))]
+    pat = "|".join(drop)
+    return clinical[~ids.str.contains(pat, regex=True)]
+
+
+def recode_risk(clinical: pd.DataFrame, column: str = "Risk group") -> pd.DataFrame:
+    """``RiskGroup.Class``: High/Standard -> "Yes", Low -> "No", Unknown -> "Unknown" (DEL:128-131), plus the numeric
+    ``deg.risk`` (0 = Low, 1 = Standard/High; SEA:435-451) and ``Low Risk`` of model_comp.py:60."""
+    out = clinical.copy()
+    rg = out[column].astype(str)
+    out["RiskGroup.Class"] = np.where(rg.str.contains("High|Standard"), "Yes", np.where(rg.str.contains("Low"), "No", "Unknown"))
+    out["deg.risk"] = np.where(out["RiskGroup.Class"] == "Yes", 1, np.where(out["RiskGroup.Class"] == "No", 0, -1))
+    out["Low Risk"] = (rg == "Low").astype(int)
+    return out
+
+
+def age_class(clinical: pd.DataFrame, column: str = "Age at Diagnosis in Days") -> pd.Series:
+    age = pd.to_numeric(clinical[column], errors="coerce")
+    return pd.Series(np.where(age > age.median(), "Yes", "No"), index=clinical.index)
+
+
+def mll_update(clinical: pd.DataFrame, column: str = "Primary Cytogenetic Code") -> pd.Series:
+    c = clinical[column].astype(str)
+    return pd.Series(np.where(c == "MLL", "MLL", np.where(c == "Unknown", "Unknown", "No")), index=clinical.index)
+
+
+def drop_unknown(cohort: Cohort, column: str = "deg.risk") -> Cohort:
+    v = cohort.col_data[column]
+    bad = v.astype(str).isin(["Unknown", "-1", "nan", "None"])
+    return cohort.select_samples(~bad.to_numpy())
+
+
+def dedupe_samples(ids: Sequence[str], key=lambda s: s[:16]) -> np.ndarray:
+    """Keep the first sample of every patient (the reference dedupes by patient code, VikasP/AML.R:31-64)."""
+    seen, keep = set(), []
+    for i, s in enumerate(ids):
+        k = key(s)
+        if k not in seen:
+            seen.add(k)
+            keep.append(i)
+    return np.asarray(keep)
+
+
+def split_random(ids: Sequence[str], train_frac: float = 2.0 / 3.0, seed: int = 2019) -> Tuple[list, list]:
+    """``sample(ids, size = n * frac)``-style split (R's RNG stream is not reproducible here; the reference's own id
+    lists are what ``split_fixed`` uses)."""
+    rng = np.random.default_rng(seed)
+    ids = list(ids)
+    k = int(len(ids) * train_frac)
+    tr = set(rng.choice(len(ids), k, replace=False).tolist())
+    return [s for i, s in enumerate(ids) if i in tr], [s for i, s in enumerate(ids) if i not in tr]
+
+
+def split_stratified(labels: Sequence, train_frac: float = 0.7, seed: int = 2128) -> np.ndarray:
+    """Boolean train mask with the class proportions preserved (the 70/30 split of VikasP/AML.R:159-165)."""
+    rng = np.random.default_rng(seed)
+    lab = np.asarray(labels)
+    mask = np.zeros(lab.size, bool)
+    for v in np.unique(lab):
+        idx = np.flatnonzero(lab == v)
+        k = int(round(train_frac * idx.size))
+        mask[rng.choice(idx, k, replace=False)] = True
+    return mask
+
+
+def split_fixed(cohort: Cohort, train_ids: Iterable[str], test_ids: Iterable[str], usi=lambda s: ".".join(s.replace("-", ".").split(".")[:3]),
+                column: str = "exptset.seahack") -> Cohort:
+    """Attach the reference's committed train/test id lists as a split column."""
+    tr = {i.replace("-", ".") for i in train_ids}
+    te = {i.replace("-", ".") for i in test_ids}
+    flag = []
+    for s in cohort.sample_ids:
+        u = usi(s)
+        flag.append("train" if u in tr else ("test" if u in te else "unassigned"))
+    out = Cohort(cohort.assay, cohort.gene_ids, cohort.sample_ids, cohort.row_data, cohort.col_data.copy(), dict(cohort.metadata),
+                 cohort.assay_name)
+    if len(out.col_data) == 0:
+        out.col_data = pd.DataFrame(index=range(len(flag)))
+    out.col_data[column] = flag
+    return out
+
+
+def holdout_then_split(n: int, holdout_frac: float = 0.2, test_size: float = 0.33, seed: int = 8):
+    """model_comp.py:102-107: 20 % holdout, then a 67/33 split of the rest.  Returns index arrays (train, test, holdout)."""
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(n)
+    h = int(round(holdout_frac * n))
+    hold, rest = perm[:h], perm[h:]
+    t = int(np.ceil(test_size * rest.size))
+    return rest[t:], rest[:t], hold
+
+
+def resample_balanced(labels: Sequence, n_out: Optional[int] = None, p: float = 0.5, method: str = "both", seed: int = 1) -> np.ndarray:
+    """ROSE ``ovun.sample(method = "both" | "over" | "under", p, N, seed)``: indices of a re-balanced sample in which
+    the minority class makes up a fraction ``p``."""
+    rng = np.random.default_rng(seed)
+    lab = np.asarray(labels)
+    vals, counts = np.unique(lab, return_counts=True)
+    if vals.size != 2:
+        raise ValueError("binary labels expected")
+    minority, majority = vals[np.argmin(counts)], vals[np.argmax(counts)]
+    i_min, i_maj = np.flatnonzero(lab == minority), np.flatnonzero(lab == majority)
+    if method == "both":
+        n_out = lab.size if n_out is None else n_out
+        n_min = rng.binomial(n_out, p)
+        return np.concatenate([rng.choice(i_min, n_min, replace=True), rng.choice(i_maj, n_out - n_min, replace=True)])
+    if method == "over":
+        n_min = int(round(i_maj.size * p / (1 - p)))
+        return np.concatenate([i_maj, rng.choice(i_min, n_min, replace=True)])
+    if method == "under":
+        n_maj = int(round(i_min.size * (1 - p) / p))
+        return np.concatenate([i_min, rng.choice(i_maj, min(n_maj, i_maj.size), replace=False)])
+    raise ValueError(method)

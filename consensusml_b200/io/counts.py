@@ -1,0 +1,76 @@
+"""Count-matrix ingestion: per-sample file concatenation and reference-format CSV readers.
+
+``concat_counts`` replaces ``catExpnData(filenames, regex, cols, header, removeFirstLine, sep)``
+(JSmith_code/Cat_Expn_Data.r:7-49; used at GDC_Data_Download.Rmd:306-349 to build the 60,488 x 474 matrix): a C++
+mmap parser (csrc/host/count_files.cpp) fills the genes x samples int32 matrix with one thread per file.
+``read_counts_csv`` reads the concatenated CSV layout the reference then writes (genes as rows, first column = id)."""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import pandas as pd
+import torch
+
+from .. import _native
+
+
+def concat_counts(filenames: Sequence[str], regex: Optional[str] = None, id_col: int = 0, value_col: int = 1, header: bool = False,
+                  remove_first_line: bool = False, sep: str = "\t", drop_summary_rows: bool = True,
+                  threads: Optional[int] = None) -> Tuple[torch.Tensor, List[str], List[str]]:
+    """Returns (counts int32 [genes, samples], gene ids, sample ids).  ``regex`` with one capture group extracts the
+    sample id from the file name (the reference's ``gsub(regex, "\\\\1", filenames)``).  HTSeq's ``__no_feature`` style
+    summary rows are dropped (VikasP/AML.R:151 removes rows starting with ``__``)."""
+    lib = _native.host()
+    lib.cml_host_counts_scan.restype = ctypes.c_long
+    lib.cml_host_counts_scan.argtypes = [ctypes.c_char_p, ctypes.c_char, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    lib.cml_host_counts_id.argtypes = [ctypes.c_long, ctypes.c_char_p, ctypes.c_int]
+    lib.cml_host_counts_concat.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.c_int, ctypes.c_char, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_int, ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_int]
+    files = [os.fspath(f) for f in filenames]
+    if not files:
+        raise ValueError("no files")
+    skip = int(bool(header)) + int(bool(remove_first_line))
+    n_genes = lib.cml_host_counts_scan(files[0].encode(), sep.encode(), skip, id_col, value_col)
+    if n_genes <= 0:
+        raise ValueError(f"{files[0]}: could not parse (code {n_genes})")
+    buf = ctypes.create_string_buffer(256)
+    genes = []
+    for i in range(n_genes):
+        lib.cml_host_counts_id(i, buf, 256)
+        genes.append(buf.value.decode())
+    out = np.zeros((n_genes, len(files)), dtype=np.int32)
+    status = np.zeros(len(files), dtype=np.int64)
+    arr = (ctypes.c_char_p * len(files))(*[f.encode() for f in files])
+    bad = lib.cml_host_counts_concat(arr, len(files), sep.encode(), skip, id_col, value_col, out.ctypes.data, n_genes,
+                                     status.ctypes.data, threads or min(16, os.cpu_count() or 1))
+    if bad:
+        which = [(files[i], int(status[i])) for i in np.flatnonzero(status)]
+        raise ValueError(f"{bad} count file(s) do not match the gene list of {files[0]}: {which[:5]}")
+    if regex is not None:
+        samples = [re.sub(regex, r"\1", os.path.basename(f)) for f in files]
+    else:
+        samples = [os.path.basename(f) for f in files]
+    if drop_summary_rows:
+        keep = np.array([not g.startswith("__") for g in genes])
+        out, genes = out[keep], [g for g, k in zip(genes, keep) if k]
+    return torch.from_numpy(np.ascontiguousarray(out)), genes, samples
+
+
+def read_counts_csv(path: str, id_column: int = 0) -> Tuple[torch.Tensor, List[str], List[str]]:
+    """Genes x samples CSV (first column gene id, header = sample barcodes), e.g. the reference's
+    ``TARGET_NBL_AML_RT_WT_HTSeq_Counts.csv`` (read at Differential_Expression_and_Lasso.Rmd:91)."""
+    df = pd.read_csv(path, index_col=id_column)
+    return torch.from_numpy(df.to_numpy(dtype=np.int32)), [str(i) for i in df.index], [str(c) for c in df.columns]
+
+
+def write_matrix_csv(path: str, matrix: torch.Tensor, row_ids: Sequence[str], col_ids: Sequence[str]) -> None:
+    pd.DataFrame(matrix.cpu().numpy(), index=list(row_ids), columns=list(col_ids)).to_csv(path)
+
+
+def read_manifest(path: str) -> pd.DataFrame:
+    """GDC manifest / id map (Manifest_Data/GCD_TARGET_Data_Manifest_AML_NBL_WT_RT.csv; GDC_Data_Download.Rmd:219-229)."""
+    return pd.read_csv(path)

@@ -1,0 +1,62 @@
+"""Headless dumps of the arrays behind the reference's figures (no graphics stack on this box: pictures are left
+out, their data are written as CSV / NPZ).
+
+Reference plots: volcano (JSmith_code/Differential_Expression_and_Lasso.Rmd:33-85), DEG heatmaps with clustering
+(cml_targetaml_seanalysis.Rmd:509-623), lasso performance curves (:806-881), Spearman correlation heatmaps and
+densities (:883-1017), RF / XGB importance bars and SVM weight bars (:697-713, 1098-1143, 1267-1293)."""
+from __future__ import annotations
+
+import os
+from typing import Dict, Optional, Sequence
+
+import numpy as np
+import pandas as pd
+import torch
+
+from ..stats import correlation as C
+
+
+def volcano_data(logfc: np.ndarray, p_value: np.ndarray, adj_p: np.ndarray, gene_ids: Sequence[str], lfc: float = 1.0,
+                 fdr: float = 0.05) -> pd.DataFrame:
+    """x = log2 fold change, y = -log10 p, class in {up, down, ns} (the three colours of ``volcano_plot``)."""
+    cls = np.where((adj_p < fdr) & (logfc > lfc), "up", np.where((adj_p < fdr) & (logfc < -lfc), "down", "ns"))
+    return pd.DataFrame({"gene": list(gene_ids), "logFC": logfc, "neg_log10_p": -np.log10(np.maximum(p_value, 1e-300)),
+                         "adj.P.Val": adj_p, "class": cls})
+
+
+def top_quantile(values: np.ndarray, gene_ids: Sequence[str], q: float = 0.99, absolute: bool = True) -> pd.DataFrame:
+    """Genes above the ``q`` quantile of (absolute) importance / weight - the bars of SEA:697-713 and :1098-1116."""
+    v = np.abs(values) if absolute else values
+    thr = np.quantile(v, q)
+    idx = np.flatnonzero(v > thr)
+    idx = idx[np.argsort(-v[idx])]
+    return pd.DataFrame({"gene": [gene_ids[i] for i in idx], "value": values[idx]})
+
+
+def lasso_rep_curves(results) -> pd.DataFrame:
+    """Per exclusion replicate: TPR, TNR, FDR, FOR, test error, number of genes (SEA:811-880)."""
+    rows = []
+    for i, r in enumerate(results, 1):
+        rep = r.report.as_dict() if r.report is not None else {}
+        rows.append({"rep": i, "n_genes": len(r.nonzero_coef), "test_error": r.test_error, "auc": r.test_auc,
+                     **{k: rep.get(k) for k in ("tpr", "tnr", "fdr", "for")}})
+    return pd.DataFrame(rows)
+
+
+def correlation_heatmap(assay: torch.Tensor, gene_idx_rows: Sequence[int], gene_idx_cols: Sequence[int],
+                        samples: Optional[Sequence[int]] = None):
+    """Spearman block between two gene sets (rep1 vs rep2 / rep3 genes, SEA:889-969) with clustered ordering."""
+    a = assay[torch.as_tensor(list(gene_idx_rows))].float()
+    b = assay[torch.as_tensor(list(gene_idx_cols))].float()
+    cor = C.correlation(a, b, samples=samples, exact=True)
+    ro, co = C.heatmap_order(cor) if min(cor.shape) > 2 else (np.arange(cor.shape[0]), np.arange(cor.shape[1]))
+    grid, dens = C.kde(cor.flatten())
+    return {"cor": cor.cpu().numpy(), "row_order": ro, "col_order": co, "density_x": grid.cpu().numpy(), "density_y": dens.cpu().numpy()}
+
+
+def write_all(out_dir: str, tables: Dict[str, pd.DataFrame], arrays: Optional[Dict[str, Dict[str, np.ndarray]]] = None) -> None:
+    os.makedirs(out_dir, exist_ok=True)
+    for name, df in tables.items():
+        df.to_csv(os.path.join(out_dir, f"{name}.csv"), index=False)
+    for name, arrs in (arrays or {}).items():
+        np.savez_compressed(os.path.join(out_dir, f"{name}.npz"), **arrs)

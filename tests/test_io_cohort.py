@@ -1,0 +1,75 @@
+import os
+
+import numpy as np
+import pandas as pd
+import pytest
+import torch
+
+from consensusml_b200 import cohort as CO
+from consensusml_b200.io import counts as IC
+
+REF = "/root/reference"
+
+
+def test_concat_counts_native_parser(tmp_path):
+    rng = np.random.default_rng(0)
+    genes = [f"ENSG{i:011d}.{i % 7 + 1}" for i in range(500)] + ["__no_feature", "__ambiguous"]
+    mat = rng.poisson(30, (len(genes), 7))
+    files = []
+    for s in range(7):
+        p = tmp_path / f"{s:02d}_TARGET-20-PAAAA{s}-09A-01R.htseq.counts"
+        with open(p, "w") as fh:
+            for g, v in zip(genes, mat[:, s]):
+                fh.write(f"{g}\t{v}\n")
+        files.append(str(p))
+    counts, gids, sids = IC.concat_counts(files, regex=r"^\d+_(TARGET-[0-9A-Z-]+)\.htseq\.counts$")
+    assert counts.shape == (500, 7) and counts.dtype == torch.int32
+    assert gids == genes[:500] and sids[3] == "TARGET-20-PAAAA3-09A-01R"
+    assert np.array_equal(counts.numpy(), mat[:500])
+    # a file whose gene order differs is rejected with its name
+    bad = tmp_path / "bad.counts"
+    bad.write_text("".join(f"{g}\t1\n" for g in reversed(genes)))
+    with pytest.raises(ValueError, match="bad.counts"):
+        IC.concat_counts(files + [str(bad)])
+    out = tmp_path / "m.csv"
+    IC.write_matrix_csv(str(out), counts, gids, sids)
+    c2, g2, s2 = IC.read_counts_csv(str(out))
+    assert torch.equal(c2, counts) and g2 == gids and s2 == sids
+
+
+def test_label_recoding_and_filters():
+    df = pd.DataFrame({"Diagnostic ID": ["09A", "03A", "04A", "40A", "01A"], "Risk group": ["Low", "High", "Standard", "Unknown", "Low"],
+                       "Age at Diagnosis in Days": [100, 200, 300, 400, 500], "Primary Cytogenetic Code": ["MLL", "Normal", "Unknown", "MLL", "inv(16)"]})
+    kept = CO.filter_diagnostic(df)
+    assert list(kept["Diagnostic ID"]) == ["09A", "03A", "01A"]
+    assert list(CO.filter_diagnostic(df, keep=CO.PRIMARY)["Diagnostic ID"]) == ["09A", "03A"]
+    r = CO.recode_risk(df)
+    assert list(r["RiskGroup.Class"]) == ["No", "Yes", "Yes", "Unknown", "No"]
+    assert list(r["deg.risk"]) == [0, 1, 1, -1, 0] and list(r["Low Risk"]) == [1, 0, 0, 0, 1]
+    assert list(CO.age_class(df)) == ["No", "No", "No", "Yes", "Yes"]
+    assert list(CO.mll_update(df)) == ["MLL", "No", "Unknown", "MLL", "No"]
+    assert CO.dedupe_samples(["TARGET-20-PABLDZ-09A-01R", "TARGET-20-PABLDZ-03A-01R", "TARGET-20-PADYIR-09A-01R"]).tolist() == [0, 2]
+
+
+def test_splits_and_resampling():
+    ids = [f"s{i}" for i in range(145)]
+    tr, te = CO.split_random(ids, 2 / 3, seed=2019)
+    assert len(tr) == 96 and len(te) == 49 and not set(tr) & set(te)       # the reference's 96 / 49
+    y = np.array([0] * 60 + [1] * 40)
+    m = CO.split_stratified(y, 0.7)
+    assert m.sum() == 70 and y[m].sum() == 28
+    a, b, c = CO.holdout_then_split(137)
+    assert len(c) == 27 and len(a) + len(b) + len(c) == 137 and len(b) == 37   # 27 / 73 / 37 as in the walkthrough
+    idx = CO.resample_balanced(np.array([0] * 90 + [1] * 10), n_out=1000, p=0.5)
+    frac = (np.array([0] * 90 + [1] * 10)[idx] == 1).mean()
+    assert idx.size == 1000 and 0.44 < frac < 0.56
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not mounted")
+def test_fixed_split_reproduces_reference_flags(aml):
+    tr = pd.read_csv(f"{REF}/JSmith_code/TARGET_AML_Training_Samples.csv")["x"].tolist()
+    te = pd.read_csv(f"{REF}/JSmith_code/TARGET_AML_Testing_Samples.csv")["x"].tolist()
+    assert len(tr) == 96 and len(te) == 49
+    out = CO.split_fixed(aml, tr, te, column="split2")
+    assert (out.col_data["split2"].to_numpy() == aml.col_data["exptset.seahack"].to_numpy()).all()   # 93 / 44 after Unknown drop
+    assert (out.col_data["split2"] == "train").sum() == 93

@@ -1,0 +1,82 @@
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from consensusml_b200 import pipeline
+from consensusml_b200.runtime import config as C
+from consensusml_b200.runtime.log import NumericalFailure, RunLog, check_finite, describe_jerr
+from consensusml_b200.runtime.store import ArtifactStore
+
+
+def test_config_defaults_overrides_and_hash(tmp_path):
+    cfg = C.load(None, ["lasso.exclusion_reps=2", "rf.n_trees=[50]", "svm.enabled=false", "io.out_dir=" + str(tmp_path)])
+    assert cfg.lasso.exclusion_reps == 2 and cfg.rf.n_trees == [50] and cfg.svm.enabled is False
+    assert cfg.split.seed == 2019 and cfg.rf.seed == 20 and cfg.svm.seed == 50          # the reference's seeds
+    h = cfg.hash()
+    cfg.lasso.alpha = 0.5
+    assert cfg.hash() != h and cfg.hash(["rf"]) == C.load(None, ["rf.n_trees=[50]"]).hash(["rf"])
+    with pytest.raises(KeyError):
+        C.load(None, ["lasso.nope=1"])
+    p = tmp_path / "c.yaml"
+    p.write_text("lasso:\n  alpha: 0.25\nconsensus:\n  method: borda\n")
+    c2 = C.load(str(p))
+    assert c2.lasso.alpha == 0.25 and c2.consensus.method == "borda"
+
+
+def test_store_resume_and_log(tmp_path):
+    log = RunLog(str(tmp_path / "run.jsonl"))
+    store = ArtifactStore(str(tmp_path), resume=True)
+    calls = []
+    fn = lambda: (calls.append(1), {"x": torch.arange(3)})[1]
+    a = store.run("stage1", "h1", fn, log)
+    b = store.run("stage1", "h1", fn, log)
+    assert len(calls) == 1 and torch.equal(a["x"], b["x"])
+    store.run("stage1", "h2", fn, log)                 # configuration changed -> recomputed
+    assert len(calls) == 2
+    with log.stage("demo", bytes_moved=1e6):
+        pass
+    recs = [json.loads(l) for l in open(tmp_path / "run.jsonl")]
+    assert any(r["event"] == "stage_skipped" for r in recs) and any(r.get("stage") == "demo" and "gb_per_s" in r for r in recs)
+    with pytest.raises(NumericalFailure):
+        check_finite("w", torch.tensor([1.0, float("nan")]))
+    assert "lambda index 7" in describe_jerr(-7) and "capacity" in describe_jerr(-10012)
+
+
+@pytest.mark.slow
+def test_pipeline_small_cpu(tmp_path):
+    cfg = C.load(None, ["io.out_dir=" + str(tmp_path), "device=cpu", "lasso.exclusion_reps=1", "rf.n_trees=[60]", "rf.proximity=false",
+                        'gbm.reps=[{"max_depth": 2, "nrounds": 2}]', 'svm.kernels=["linear"]', "svm.weightfilt=[null]"])
+    s = pipeline.run(cfg)
+    assert s["lasso"]["confusion"] == [[21, 2], [1, 20]] and abs(s["lasso"]["auc"] - 0.9835) < 1e-3
+    assert s["xgb1"]["n_genes"] == 6 and s["rf_60"]["oob_error"] < 0.2 and s["svm1"]["auc"] > 0.9
+    for f in ("standouttable.csv", "consensus_rank.csv", "membership_table.csv", "Logistic_Lasso_RiskGroup_Associated_Genes.csv",
+              "run.jsonl", "report/volcano.csv", "report/lasso_rep_curves.csv"):
+        assert os.path.exists(tmp_path / f), f
+    # second run resumes the lasso stage from its checkpoint
+    pipeline.run(cfg)
+    recs = [json.loads(l) for l in open(tmp_path / "run.jsonl")]
+    assert any(r["event"] == "stage_skipped" and r["stage"] == "models/lasso" for r in recs)
+
+
+def test_counts_to_cohort_cpu():
+    from consensusml_b200.io.synthetic import nb_counts
+    c, g = nb_counts(4000, 48, seed=2, n_de=250)
+    train = np.arange(48) % 3 != 0
+    co = pipeline.cohort_from_counts(torch.from_numpy(c), [f"ENSG{i:011d}.1" for i in range(4000)], [f"s{i}" for i in range(48)], g, train,
+                                     C.Config())
+    assert 20 < co.n_genes < 600 and co.n_samples == 48
+    assert (co.row_data["p.adj.bh"] < 0.05).all() and (co.row_data["logFC"].abs() > 1).all()
+    tr, te = co.split()
+    assert tr.n_samples == 32 and te.n_samples == 16
+
+
+def test_cli_config_and_lasso(tmp_path, capsys):
+    from consensusml_b200.cli.main import main
+    assert main(["config", "lasso.alpha=0.5"]) == 0
+    assert json.loads(capsys.readouterr().out)["lasso"]["alpha"] == 0.5
+    assert main(["lasso", "device=cpu", "io.out_dir=" + str(tmp_path)]) == 0
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert out["genes"] == 13 and out["confusion"] == [[21, 2], [1, 20]]
