@@ -108,6 +108,21 @@ def main():
         err = float((fu.beta - un.beta).abs().max())
         print(f"[{rank}] lasso_large fused vs unfused beta max diff {err:.2e} nnz {int((fu.beta != 0).sum())} obj {fu.objective:.5f}/{un.objective:.5f}", flush=True)
         ok &= err < 2e-3
+        # ---- sharded GBM on the fused histogram path: identical trees on every rank, sensible accuracy
+        from consensusml_b200.models.gbm_large import GBMLarge
+        from consensusml_b200.ops.metrics import auc
+        gx, gy = synth(4000, 64, seed=3)
+        glo, ghi = shard_bounds(4000, world, rank)
+        gb = GBMLarge(n_estimators=8, max_depth=3, nbins=64).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
+        a = auc(gb.predict_proba(gx.to(dev)), gy.to(dev))
+        sig = torch.stack([t.feat.float().sum() + t.thr.float().sum() for t in gb.trees]).sum().reshape(1)
+        lo_s, hi_s = sig.clone(), sig.clone()
+        if world > 1:
+            dist.all_reduce(lo_s, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi_s, op=dist.ReduceOp.MAX)
+        same = bool(lo_s.item() == hi_s.item())
+        print(f"[{rank}] gbm_large auc {a:.4f} trees identical across ranks: {same} top genes {torch.argsort(-gb.importance_gain_)[:4].tolist()}", flush=True)
+        ok &= a > 0.85 and same
     t = torch.tensor([1.0 if ok else 0.0], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
