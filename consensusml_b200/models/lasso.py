@@ -122,6 +122,32 @@ def cv_from_eta(eta_folds: torch.Tensor, y: torch.Tensor, foldid: np.ndarray, la
     return CVResult(lam, cvm, cvsd, nzero, float(lmin), float(l1se), imin, i1, measure, foldid)
 
 
+class _side_stream:
+    """Run the enclosed launches on their own CUDA stream so that independent path batches overlap on the GPU
+    (a single fit occupies one warp, so the train fit, the CV batch and the refit would otherwise queue up behind
+    each other for ~0.13 s each).  No-op for CPU tensors."""
+
+    def __init__(self, enabled: bool):
+        self.enabled = enabled and torch.cuda.is_available()
+        self.stream = torch.cuda.Stream() if self.enabled else None
+        self.ctx = None
+
+    def __enter__(self):
+        if self.enabled:
+            self.stream.wait_stream(torch.cuda.current_stream())
+            self.ctx = torch.cuda.stream(self.stream)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *a):
+        if self.enabled:
+            self.ctx.__exit__(*a)
+
+    def join(self):
+        if self.enabled:
+            torch.cuda.current_stream().wait_stream(self.stream)
+
+
 def fit_cv(x: torch.Tensor, y: torch.Tensor, lam: Optional[np.ndarray] = None, *, nfolds: Optional[int] = None,
            foldid: Optional[np.ndarray] = None, alpha: float = 1.0, intercept: bool = False,
            measure: str = "class", seed: int = 2019, feature_mask: Optional[torch.Tensor] = None,
@@ -145,11 +171,16 @@ def fit_cv(x: torch.Tensor, y: torch.Tensor, lam: Optional[np.ndarray] = None, *
         # two launches: solver variant is a launch-level switch
         w0 = torch.as_tensor(base_w[None, :], device=dev)
         packed = K.pack_design(x) if x.is_cuda else None
-        full = K.lognet_path(x, y, w0, lam, alpha=alpha, intercept=intercept, modified_newton=False,
-                             feature_mask=feature_mask, packed=packed, nx=nx)
         wcv = torch.as_tensor(np.concatenate([base_w[None, :], wf], 0), device=dev)
-        folds = K.lognet_path(x, y, wcv, lam, alpha=alpha, intercept=intercept, modified_newton=True,
-                              feature_mask=feature_mask, packed=packed, nx=nx)
+        s_full, s_cv = _side_stream(x.is_cuda), _side_stream(x.is_cuda)
+        with s_full:
+            full = K.lognet_path(x, y, w0, lam, alpha=alpha, intercept=intercept, modified_newton=False,
+                                 feature_mask=feature_mask, packed=packed, nx=nx)
+        with s_cv:
+            folds = K.lognet_path(x, y, wcv, lam, alpha=alpha, intercept=intercept, modified_newton=True,
+                                  feature_mask=feature_mask, packed=packed, nx=nx)
+        s_full.join()
+        s_cv.join()
         nzero = folds.df()[0].cpu().numpy()
         eta_f = folds.eta[1:]
     else:
@@ -179,15 +210,19 @@ def run_lasso(cohort: Cohort, seed: int = 2019, lam: Optional[np.ndarray] = None
     xtr, ytr = x_all[tr_idx], y_all[tr_idx]
     xte, yte = x_all[te_idx], y_all[te_idx]
 
+    # the full-data refit does not depend on the CV result: start it first, on its own stream
+    ones = torch.ones(1, x_all.shape[0], dtype=torch.float64, device=x_all.device)
+    s_final = _side_stream(x_all.is_cuda)
+    with s_final:
+        final = K.lognet_path(x_all, y_all, ones, lam, alpha=alpha, intercept=False, modified_newton=False)
     full, folds, cv = fit_cv(xtr, ytr, lam, nfolds=nfolds, alpha=alpha, seed=seed)
+    s_final.join()
     beta_tr = full.dense(0)
     eta_te = xte.to(beta_tr.dtype) @ beta_tr[cv.index_min] + full.a0[0, cv.index_min]
     pred = (eta_te > 0).long()
     rep = M.binary_report(pred, yte)
     prob = torch.sigmoid(eta_te)
 
-    ones = torch.ones(1, x_all.shape[0], dtype=torch.float64, device=x_all.device)
-    final = K.lognet_path(x_all, y_all, ones, lam, alpha=alpha, intercept=False, modified_newton=False)
     beta_f = final.dense(0)
     coef = beta_f[cv.index_min].double().cpu().numpy()
     nz = np.flatnonzero(coef != 0)
