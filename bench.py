@@ -91,7 +91,8 @@ def main():
     # a distinct cohort per step, staged in pinned host memory (the e2e arm copies it every step)
     pool = []
     for s in range(total):
-        x, y = synth_cohort(1000 * rank + s)
+        x, y = synth_cohort(s)          # every rank bootstraps the SAME cohort (its replicates differ by seed): that is how
+                                        # a stability-selection job is spread over GPUs, and it keeps the ranks' work balanced
         pool.append((torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()))
     flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
     lib = _native.cuda()

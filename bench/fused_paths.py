@@ -146,8 +146,13 @@ def main():
         outbuf = torch.empty(m, (m * world + 3) // 4 * 4, device=dev)
 
         def gemm_only():
-            G.gemm_tn(xbuf.local, None, m * world, epilogue=G.EPI_RBF, alpha=1.0 / p, norm_a=nrm.local, b_ptrs=xbuf.peer_ptrs,
-                      norm_b_ptrs=nrm.peer_ptrs, rows_per_src=m, ldb=ld, out=outbuf)
+            if world > 1:
+                stg = cache["stage"]
+                G.gemm_tn_staged(xbuf.local, xbuf.peer_ptrs, m * world, m, ld, stg["stage"], stg["norm"], stg["flags"], stg.next_epoch(),
+                                 rank, epilogue=G.EPI_RBF, alpha=1.0 / p, norm_a=nrm.local, peer_norm_ptrs=nrm.peer_ptrs, out=outbuf)
+            else:
+                G.gemm_tn(xbuf.local, None, m * world, epilogue=G.EPI_RBF, alpha=1.0 / p, norm_a=nrm.local, b_ptrs=xbuf.peer_ptrs,
+                          norm_b_ptrs=nrm.peer_ptrs, rows_per_src=m, ldb=ld, out=outbuf)
         gemm_only()
         ms = timed(gemm_only, args.reps, flush)
         flops = 2.0 * m * m * world * ld

@@ -75,6 +75,32 @@ def gemm_tn(a_bf16: torch.Tensor, b_sources: Sequence[torch.Tensor], n_total: in
     return c[:, :n_total]
 
 
+_native.register_signature("cml_gemm_tn_bf16_staged", [_I, _I, _I, _P, _LL, _P, _I, _I, _LL, _P, _LL, _I, _F, _P, _P, _P, _P, _P,
+                                                         ctypes.c_uint, _I, _I, _P])
+_native.register_signature("cml_gemm_staged_flags", [_I, _I], _I)
+
+
+def gemm_tn_staged(a_bf16: torch.Tensor, peer_ptrs: Sequence[int], n_total: int, rows_per_src: int, ldb: int, stage: torch.Tensor,
+                   stage_norm: Optional[torch.Tensor], flags: torch.Tensor, epoch: int, rank: int, *, epilogue: int = EPI_SCALE,
+                   alpha: float = 1.0, norm_a: Optional[torch.Tensor] = None, peer_norm_ptrs: Optional[Sequence[int]] = None,
+                   out: Optional[torch.Tensor] = None, n_copiers: int = 12) -> torch.Tensor:
+    """Fused all-gather -> GEMM: ``peer_ptrs[s]`` is the device address of source block ``s`` (peer memory); copier CTAs
+    of the same kernel stage the blocks into ``stage`` while the GEMM CTAs consume the tiles that have arrived."""
+    M, K = a_bf16.shape
+    n_src = len(peer_ptrs)
+    ldc = (n_total + 3) // 4 * 4
+    c = out if out is not None else torch.empty(M, ldc, dtype=torch.float32, device=a_bf16.device)
+    arr_b = (ctypes.c_void_p * n_src)(*peer_ptrs)
+    arr_n = (ctypes.c_void_p * n_src)(*peer_norm_ptrs) if peer_norm_ptrs is not None else None
+    rc = _native.cuda().cml_gemm_tn_bf16_staged(M, n_total, K, _native.ptr(a_bf16), K, arr_b, n_src, rows_per_src, ldb,
+                                                _native.ptr(c), c.stride(0), epilogue, float(alpha),
+                                                _native.ptr(norm_a) if norm_a is not None else None, arr_n,
+                                                _native.ptr(stage), _native.ptr(stage_norm) if stage_norm is not None else None,
+                                                _native.ptr(flags), epoch & 0xFFFFFFFF, rank, n_copiers, _native.stream_ptr())
+    _native.check(rc, "cml_gemm_tn_bf16_staged")
+    return c[:, :n_total]
+
+
 def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optional[float] = None) -> torch.Tensor:
     """K(i, j) = exp(-gamma |x_i - z_j|^2); gamma defaults to 1/p as in e1071."""
     gamma = 1.0 / x.shape[1] if gamma is None else gamma

@@ -109,30 +109,64 @@ def xtr_reduce_scatter_unfused(x: torch.Tensor, R: torch.Tensor, p: int) -> torc
 
 # ------------------------------------------------------------------------------------------------ path 3
 def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Optional[float] = None, n_total: Optional[int] = None,
-                   shift: float = 0.0, cache: Optional[dict] = None) -> torch.Tensor:
+                   shift: float = 0.0, cache: Optional[dict] = None, staged: Optional[bool] = None) -> torch.Tensor:
     """Rows of the kernel matrix for this rank's samples against ALL samples: ``K[local, :]`` of shape
-    [n_local, n_total].  Each rank publishes its bf16 block (+ squared norms) in symmetric memory; the GEMM's TMA
-    producer then loads B tiles straight from the peers' blocks over NVLink - the all-gather never exists as a copy."""
+    [n_local, n_total].  Each rank publishes its bf16 block (+ squared norms) in symmetric memory.  With several ranks
+    the GEMM kernel itself performs the all-gather: a dozen of its CTAs stream the peers' blocks over NVLink into a local
+    staging buffer (bulk async copies) and flag each tile as it lands, while the remaining CTAs run tcgen05 tiles on
+    whatever has arrived - own block first, then the peers in ring order.  (Reading peer tiles directly from the TMA
+    producer also works and is kept for one rank / ``staged=False``, but peer reads bypass the local L2, so every B tile
+    then crosses NVLink once per M-tile.)"""
     world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
     n_local, p = x_local.shape
     dev = x_local.device
     ld = (p + 7) // 8 * 8
+    n_total = n_local if n_total is None else n_total
     rows = n_local if world == 1 else equal_shard(n_total, world)
     xb = symm.alloc((rows, ld), torch.bfloat16, dev)
     nrm = symm.alloc((rows,), torch.float32, dev)
     G.to_bf16_rows(x_local.float().contiguous(), shift=shift, out=xb.local[:n_local], norm_out=nrm.local[:n_local])
     torch.cuda.synchronize()
     xb.barrier()
-    n_total = n_local if n_total is None else n_total
     gamma = 1.0 / p if gamma is None else gamma
     epi, alpha = (G.EPI_RBF, gamma) if kernel == "radial" else (G.EPI_SCALE, 1.0)
-    out = G.gemm_tn(xb.local[:n_local], None, n_total, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
-                    b_ptrs=xb.peer_ptrs, norm_b_ptrs=nrm.peer_ptrs, rows_per_src=rows, ldb=ld)
+    use_stage = (world > 1) if staged is None else staged
+    if use_stage:
+        st = gram_stage_buffers(world, rows, ld, dev)
+        out = G.gemm_tn_staged(xb.local[:n_local], xb.peer_ptrs, n_total, rows, ld, st["stage"], st["norm"], st["flags"],
+                               st.next_epoch(), rank, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
+                               peer_norm_ptrs=nrm.peer_ptrs)
+        if cache is not None:
+            cache["stage"] = st
+    else:
+        out = G.gemm_tn(xb.local[:n_local], None, n_total, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
+                        b_ptrs=xb.peer_ptrs, norm_b_ptrs=nrm.peer_ptrs, rows_per_src=rows, ldb=ld)
     torch.cuda.synchronize()
     xb.barrier()                     # nobody frees / rewrites its block while a peer may still be reading it
     if cache is not None:
         cache["xb"], cache["nrm"] = xb, nrm
     return out
+
+
+class _StageBuffers(dict):
+    def next_epoch(self) -> int:
+        self["epoch"] = self.get("epoch", 0) + 1
+        return self["epoch"]
+
+
+_STAGE_CACHE: dict = {}
+
+
+def gram_stage_buffers(world: int, rows: int, ld: int, device) -> "_StageBuffers":
+    """Local staging buffer, norm buffer and tile flags for the staged all-gather GEMM (cached per shape)."""
+    key = (world, rows, ld, str(device))
+    if key not in _STAGE_CACHE:
+        nflags = _native.cuda().cml_gemm_staged_flags(world, rows)
+        _STAGE_CACHE[key] = _StageBuffers(stage=torch.empty(world * rows, ld, dtype=torch.bfloat16, device=device),
+                                          norm=torch.empty(world * rows, dtype=torch.float32, device=device),
+                                          flags=torch.zeros(nflags, dtype=torch.int32, device=device))
+    return _STAGE_CACHE[key]
 
 
 def gram_allgather_unfused(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Optional[float] = None, shift: float = 0.0):

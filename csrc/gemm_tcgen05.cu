@@ -84,6 +84,18 @@ struct GemmParams {
   int epilogue;
   float alpha;                    // SCALE: multiplier;  RBF: gamma
   int tiles_m, tiles_n_per_src;
+  // ---- staged all-gather (n_copiers > 0): the first n_copiers CTAs pull every source block (peer memory) into the
+  // local staging buffer with bulk async copies and publish one flag per (source, n-tile); the GEMM CTAs wait for the
+  // flag of the tile they are about to load.  Peer reads bypass the local L2, so without staging a B tile would
+  // cross NVLink once per M-tile that uses it.
+  const void* peer_src[kMaxSrc];
+  const float* peer_norm[kMaxSrc];
+  void* stage;                    // bf16 [n_src * rows_per_src][ldb]
+  float* stage_norm;              // [n_src * rows_per_src]
+  unsigned* flags;                // [n_src * tiles_n_per_src], ready when == epoch
+  unsigned epoch;
+  int n_copiers, rank;
+  long long ldb;
 };
 
 template <int BN, int STAGES>
@@ -95,11 +107,93 @@ struct SmemLayout {
   static constexpr int kTotal = STAGES * kStageBytes + kBarrierBytes + 1024;   // +1024: manual alignment slack
 };
 
+__device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+               "l"(gsrc), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store_s2g(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Copier CTA: streams source blocks (ring order starting at this rank's own block) into the staging buffer through a
+// ring of shared-memory slots: bulk load peer -> smem (mbarrier), bulk store smem -> local global (bulk group).
+template <int BN>
+__device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
+  using namespace sm100;
+  constexpr int kSlots = 6;
+  constexpr uint32_t kChunk = 32 * 1024;
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 127u) & ~127u;
+  const uint32_t bar0 = base + kSlots * kChunk;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kSlots; ++s) mbar_init(bar0 + 8u * s, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int items = P.n_src * P.tiles_n_per_src;
+  const size_t row_bytes = (size_t)P.ldb * 2;
+  uint32_t issued = 0, drained = 0;      // chunk counters across items (slot = counter % kSlots, parity from counter / kSlots)
+  for (int it = blockIdx.x; it < items; it += P.n_copiers) {
+    const int si = it / P.tiles_n_per_src, n_loc = it % P.tiles_n_per_src;
+    const int src = (P.rank + si) % P.n_src;
+    const int rows_here = min(P.rows_per_src, P.N - src * P.rows_per_src);
+    const int r0 = n_loc * BN, r1 = min(rows_here, r0 + BN);
+    if (r1 > r0) {
+      const uint8_t* gsrc = static_cast<const uint8_t*>(P.peer_src[src]) + (size_t)r0 * row_bytes;
+      uint8_t* gdst = static_cast<uint8_t*>(P.stage) + ((size_t)src * P.rows_per_src + r0) * row_bytes;
+      const size_t total = (size_t)(r1 - r0) * row_bytes;               // multiple of 16 (ldb % 8 == 0)
+      const int nchunks = (int)((total + kChunk - 1) / kChunk);
+      if (threadIdx.x == 0) {
+        for (int c = 0; c < nchunks + (kSlots - 1); ++c) {
+          if (c < nchunks) {
+            const uint32_t slot = issued % kSlots;
+            if (issued >= kSlots) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // slot's previous store has left smem
+            const uint32_t bytes = (uint32_t)min((size_t)kChunk, total - (size_t)c * kChunk);
+            mbar_arrive_expect_tx(bar0 + 8u * slot, bytes);
+            bulk_load_g2s(base + slot * kChunk, gsrc + (size_t)c * kChunk, bytes, bar0 + 8u * slot);
+            ++issued;
+          }
+          const int d = c - (kSlots - 1);
+          if (d >= 0) {
+            const uint32_t slot = drained % kSlots;
+            mbar_wait(bar0 + 8u * slot, (drained / kSlots) & 1u);
+            const uint32_t bytes = (uint32_t)min((size_t)kChunk, total - (size_t)d * kChunk);
+            bulk_store_s2g(gdst + (size_t)d * kChunk, base + slot * kChunk, bytes);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            ++drained;
+          }
+        }
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // stores complete (written, not just read)
+        asm volatile("fence.proxy.async;" ::: "memory");
+      } else if (P.peer_norm[src] && P.stage_norm) {
+        for (int r = r0 + (int)threadIdx.x - 1; r < r1; r += (int)blockDim.x - 1)
+          P.stage_norm[(size_t)src * P.rows_per_src + r] = P.peer_norm[src][r];
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.flags + (size_t)src * P.tiles_n_per_src + n_loc), "r"(P.epoch) : "memory");
+  }
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_constant__ GemmParams P) {
   using L = SmemLayout<BN, STAGES>;
   using namespace sm100;
   extern __shared__ uint8_t smem_raw[];
+  if ((int)blockIdx.x < P.n_copiers) {
+    copier_role<BN>(P, smem_raw);
+    return;
+  }
+  const int tile0 = (int)blockIdx.x - P.n_copiers, tile_stride = (int)gridDim.x - P.n_copiers;
+  const bool staged = P.n_copiers > 0;
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;              // SWIZZLE_128B tiles need 1024-byte alignment
   uint8_t* gen_base = smem_raw + (base - raw);
@@ -118,7 +212,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&P.map_a);
-    for (int s = 0; s < P.n_src; ++s) prefetch_tensormap(&P.map_b[s]);
+    for (int s = 0; s < (staged ? 1 : P.n_src); ++s) prefetch_tensormap(&P.map_b[s]);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
     fence_barrier_init();
@@ -137,15 +231,24 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
-        const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
+        if (staged) {
+          const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
+          while (ld_acquire_gpu(flag) != P.epoch) {
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");          // staged bytes were written through the async proxy
+        }
+        const int brow = staged ? src * P.rows_per_src + n_loc * BN : n_loc * BN;
+        const CUtensorMap* mapb = staged ? &P.map_b[0] : &P.map_b[src];
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
           mbar_arrive_expect_tx(full_bar(stage), L::kStageBytes);
           tma_load_2d(sa, &P.map_a, full_bar(stage), kb * BK, m_blk * BM);
-          tma_load_2d(sb, &P.map_b[src], full_bar(stage), kb * BK, n_loc * BN);
+          tma_load_2d(sb, mapb, full_bar(stage), kb * BK, brow);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -158,7 +261,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);          // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -184,9 +287,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
     const int quarter = warp & 3;                            // TMEM lane quarter this warp may read
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
-      const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      const int src = staged ? (P.rank + si) % P.n_src : si;
       const int row = m_blk * BM + quarter * 32 + lane;
       const int col_src0 = n_loc * BN;                       // column offset inside the source
       const int rows_here = min(P.rows_per_src, P.N - src * P.rows_per_src);
@@ -194,7 +298,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
       tc_fence_after();
       float na = 0.f;
       if (P.epilogue != EPI_SCALE && row < P.M) na = __ldg(P.norm_a + row);
-      const float* nb = P.norm_b[src];
+      const float* nb = staged ? P.stage_norm + (size_t)src * P.rows_per_src : P.norm_b[src];
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         float v[32];
@@ -244,7 +348,8 @@ int launch_gemm(const GemmParams& P, cudaStream_t st) {
   auto kern = gemm_tn_kernel<BN, STAGES>;
   CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
-  const int grid = tiles < sm_count() ? tiles : sm_count();
+  int grid = tiles < sm_count() ? tiles : sm_count();
+  if (P.n_copiers > 0) grid = sm_count();          // copier CTAs + GEMM CTAs must all be co-resident (flags are spun on)
   kern<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;
@@ -333,5 +438,44 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
   if (BN == 256) return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
   return launch_gemm<128, 6>(P, static_cast<cudaStream_t>(stream));
 }
+
+// Fused all-gather -> GEMM with staging (see GemmParams): B source s lives at peer_ptrs[s] (peer or local device
+// memory, bf16 [rows_per_src][ldb]); `stage` is a local bf16 [n_src * rows_per_src][ldb] buffer, `flags` a zeroed-once
+// unsigned [n_src * ceil(rows_per_src / BN)] array and `epoch` a value that differs from every earlier call's
+// (flags are compared for equality, so they never need clearing).  `rank` selects the ring order of the sources.
+int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, const void* const* peer_ptrs, int n_src,
+                            int rows_per_src, long long ldb, float* c, long long ldc, int epilogue, float alpha,
+                            const float* norm_a, const float* const* peer_norm_ptrs, void* stage, float* stage_norm,
+                            unsigned* flags, unsigned epoch, int rank, int n_copiers, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(M > 0 && N > 0 && K > 0, CML_EINVAL, "cml_gemm_tn_bf16_staged: empty problem");
+  CML_REQUIRE(n_src >= 1 && n_src <= kMaxSrc && rank >= 0 && rank < n_src, CML_EINVAL, "cml_gemm_tn_bf16_staged: bad n_src/rank");
+  CML_REQUIRE(epilogue >= 0 && epilogue <= 2, CML_EINVAL, "cml_gemm_tn_bf16_staged: unknown epilogue %d", epilogue);
+  CML_REQUIRE(epilogue == EPI_SCALE || (norm_a && peer_norm_ptrs && stage_norm), CML_EINVAL, "cml_gemm_tn_bf16_staged: distance epilogues need row norms");
+  CML_REQUIRE(stage && flags && ldb % 8 == 0 && ldb >= K, CML_EINVAL, "cml_gemm_tn_bf16_staged: staging buffer / pitch invalid");
+  CML_REQUIRE(n_copiers >= 1 && n_copiers < sm_count() / 2, CML_EINVAL, "cml_gemm_tn_bf16_staged: n_copiers=%d out of range", n_copiers);
+  GemmParams P;
+  memset(&P, 0, sizeof(P));
+  const int BN = 256;
+  int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
+  if (rc) return rc;
+  rc = make_tmap_bf16_k64(&P.map_b[0], stage, (long long)n_src * rows_per_src, K, ldb, BN);
+  if (rc) return rc;
+  for (int s = 0; s < n_src; ++s) {
+    P.peer_src[s] = peer_ptrs[s];
+    P.peer_norm[s] = peer_norm_ptrs ? peer_norm_ptrs[s] : nullptr;
+  }
+  P.norm_a = norm_a; P.c = c; P.ldc = ldc;
+  P.M = M; P.N = N; P.K = K;
+  P.n_src = n_src; P.rows_per_src = rows_per_src;
+  P.epilogue = epilogue; P.alpha = alpha;
+  P.tiles_m = ceil_div(M, BM);
+  P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
+  P.stage = stage; P.stage_norm = stage_norm; P.flags = flags; P.epoch = epoch;
+  P.n_copiers = n_copiers; P.rank = rank; P.ldb = ldb;
+  return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
+}
+
+int cml_gemm_staged_flags(int n_src, int rows_per_src) { return n_src * cml::ceil_div(rows_per_src, 256); }
 
 }  // extern "C"

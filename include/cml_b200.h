@@ -93,6 +93,15 @@ int cml_replicate_weights(float* w, int B, int n, int n_pad, unsigned long long 
 int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const void* const* b_ptrs, int n_src,
                      int rows_per_src, long long ldb, float* c, long long ldc, int epilogue, float alpha,
                      const float* norm_a, const float* const* norm_b_ptrs, void* stream);
+/* Fused all-gather -> GEMM: the B blocks live in peer (NVLink-mapped) memory; n_copiers CTAs of the same kernel pull
+ * them into `stage` with bulk async copies and publish per-tile flags while the other CTAs run tcgen05 tiles on
+ * whatever has arrived (own block first, then the peers in ring order).  flags: cml_gemm_staged_flags() unsigned words,
+ * zeroed once; epoch must differ from every earlier call.  No counterpart in the reference (single process).          */
+int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, const void* const* peer_ptrs, int n_src,
+                            int rows_per_src, long long ldb, float* c, long long ldc, int epilogue, float alpha,
+                            const float* norm_a, const float* const* peer_norm_ptrs, void* stage, float* stage_norm,
+                            unsigned* flags, unsigned epoch, int rank, int n_copiers, void* stream);
+int cml_gemm_staged_flags(int n_src, int rows_per_src);
 /* fp32 [rows][ldx] -> bf16 [rows][ldy] (zero padded) with optional (x - shift - col_shift[j]) * col_scale[j],
  * plus squared row norms of the rounded values.                                                       */
 int cml_to_bf16_rownorm(const float* x, long long ldx, void* y_bf16, long long ldy, float* norm, int rows, int cols,

@@ -65,7 +65,10 @@ def main():
                 ok &= err < 1e-4
         # ---- path 3: all-gather -> tcgen05 Gram
         for kern in ("radial", "linear"):
-            got = F.gram_allgather(xl, kernel=kern, n_total=n)
+            got = F.gram_allgather(xl, kernel=kern, n_total=n)                 # staged in-kernel all-gather when world > 1
+            got_staged1 = F.gram_allgather(xl, kernel=kern, n_total=n, staged=True)      # force the staged path (also on 1 rank)
+            got_direct = F.gram_allgather(xl, kernel=kern, n_total=n, staged=False)      # TMA reads peer tiles directly
+            ok &= bool(torch.equal(got, got_staged1)) and bool(torch.allclose(got, got_direct, rtol=1e-5, atol=1e-6))
             # comparator needs equal block sizes
             ref = F.gram_allgather_unfused(xl, kernel=kern)
             if n % world == 0:
