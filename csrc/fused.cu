@@ -260,18 +260,31 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
   for (int t = threadIdx.x; t < sh_total; t += blockDim.x) sh[t] = 0;
   __syncthreads();
   const int i0 = chunk * rows_per_chunk, i1 = min(n, i0 + rows_per_chunk);
-  for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-    const int nd = node[i];
-    if (nd < 0) continue;
-    const float2 gf = gh[i];
-    const int qg = __float2int_rn(gf.x * scale_g), qh = __float2int_rn(gf.y * scale_h);
+  // Four consecutive samples per thread: one 32-bit load brings their bins for a feature (n_pad is a multiple of 4 and
+  // chunks start on multiples of 256), so the per-feature cost is one load + index arithmetic for eight atomics.
+  for (int i = i0 + 4 * (int)threadIdx.x; i < i1; i += 4 * (int)blockDim.x) {
+    int nd[4], qg[4], qh[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const bool ok = i + q < i1;
+      nd[q] = ok ? (int)node[i + q] : -1;
+      const float2 gf = ok ? gh[i + q] : make_float2(0.f, 0.f);
+      qg[q] = __float2int_rn(gf.x * scale_g);
+      qh[q] = __float2int_rn(gf.y * scale_h);
+    }
+    if ((nd[0] & nd[1] & nd[2] & nd[3]) < 0 && nd[0] < 0 && nd[1] < 0 && nd[2] < 0 && nd[3] < 0) continue;
     for (int f = f0; f < f1; ++f) {
-      const int b = bins[(size_t)f * n_pad + i];
-      // shared layout [node][feature][plane g|h][bin]: consecutive bins sit in consecutive banks, so the 32 lanes of an
+      const unsigned packed = *reinterpret_cast<const unsigned*>(bins + (size_t)f * n_pad + i);
+      // shared layout [node][feature][plane g|h][bin]: consecutive bins sit in consecutive banks, so the lanes of an
       // atomic spread over all 32 banks (an interleaved (g,h) pair would confine each instruction to 16 of them)
-      int* cell = sh + nd * per_node + (f - f0) * nbins * 2 + b;
-      atomicAdd(cell, qg);
-      atomicAdd(cell + nbins, qh);
+      int* frow = sh + (f - f0) * nbins * 2;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (nd[q] < 0) continue;
+        int* cell = frow + nd[q] * per_node + ((packed >> (8 * q)) & 255u);
+        atomicAdd(cell, qg[q]);
+        atomicAdd(cell + nbins, qh[q]);
+      }
     }
   }
   __syncthreads();
@@ -465,7 +478,7 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
   CML_REQUIRE(n > 0 && p > 0 && nbins >= 2 && nbins <= 256 && n_nodes >= 1, CML_EINVAL, "cml_hist_allreduce: bad shape");
   CML_REQUIRE((nbins * 2) % 4 == 0, CML_EINVAL, "cml_hist_allreduce: nbins must be even");
   int FT = 8;
-  while (FT > 1 && (size_t)n_nodes * FT * nbins * 2 * sizeof(float) > 96 * 1024) FT >>= 1;
+  while (FT > 1 && (size_t)n_nodes * FT * nbins * 2 * sizeof(float) > 36 * 1024) FT >>= 1;
   const size_t smem = (size_t)n_nodes * FT * nbins * 2 * sizeof(float);
   CML_REQUIRE(smem <= 200 * 1024, CML_E2BIG, "cml_hist_allreduce: %d open nodes x %d bins do not fit shared memory", n_nodes, nbins);
   CML_CUDA(cudaFuncSetAttribute(hist_allreduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -489,7 +502,7 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
 
 int cml_hist_ft(int n_nodes, int nbins) {
   int FT = 8;
-  while (FT > 1 && (size_t)n_nodes * FT * nbins * 2 * sizeof(float) > 96 * 1024) FT >>= 1;
+  while (FT > 1 && (size_t)n_nodes * FT * nbins * 2 * sizeof(float) > 36 * 1024) FT >>= 1;
   return FT;
 }
 
