@@ -139,3 +139,32 @@ def resample_balanced(labels: Sequence, n_out: Optional[int] = None, p: float = 
         n_maj = int(round(i_min.size * (1 - p) / p))
         return np.concatenate([i_min, rng.choice(i_maj, min(n_maj, i_maj.size), replace=False)])
     raise ValueError(method)
+
+
+def qc_summary(clinical: pd.DataFrame) -> dict:
+    """Clinical summaries of JSmith_code/aml-target_qc-scripts_SeanMaden.R:17-87: counts by gender, age statistics and
+    the above/below-median age classifier, blast percentages, event-free survival with its <= median classifier."""
+    out = {"n": len(clinical)}
+    if "Gender" in clinical:
+        out["gender"] = clinical["Gender"].value_counts(dropna=False).to_dict()
+    for col, key in (("Age at Diagnosis in Days", "age_days"), ("Bone marrow leukemic blast percentage (%)", "bm_blast_pct"),
+                     ("Peripheral blasts (%)", "pb_blast_pct"), ("Event Free Survival Time in Days", "efs_days"),
+                     ("Overall Survival Time in Days", "os_days")):
+        if col in clinical:
+            v = pd.to_numeric(clinical[col], errors="coerce").dropna()
+            if len(v):
+                out[key] = {"n": int(len(v)), "mean": float(v.mean()), "median": float(v.median()), "min": float(v.min()),
+                            "max": float(v.max()), "above_median": int((v > v.median()).sum())}
+    if "Risk group" in clinical:
+        out["risk_group"] = clinical["Risk group"].value_counts(dropna=False).to_dict()
+    return out
+
+
+def balance_test(labels_a: Sequence, labels_b: Sequence) -> dict:
+    """Chi-square independence test of two categorical columns, e.g. gender vs binarised risk
+    (cml_targetaml_seanalysis.Rmd:462,470: p = 0.8044 for gender, 0.6591 for age class)."""
+    import torch
+    from ..ops.metrics import chisq_test
+    tab = pd.crosstab(pd.Series(list(labels_a)), pd.Series(list(labels_b)))
+    stat, dof, p = chisq_test(torch.as_tensor(tab.to_numpy()))
+    return {"table": tab, "statistic": stat, "dof": dof, "p_value": p}

@@ -136,3 +136,21 @@ class Cohort:
         rows = {n: list(unwrap(v)) for n, v in zip(em.names, em.value)}
         return Cohort(torch.from_numpy(m), gene_ids, sample_ids, pd.DataFrame(rows), pd.DataFrame(cols),
                       {"source": "SummarizedExperiment"})
+
+
+class MultiCohort(dict):
+    """Named assays over the same samples - the role of the reference's MultiAssayExperiment
+    (seobjects/make_seobj_targetaml.R:234-252: gene counts, TMM log-CPM and the DEG subset keyed by experiment name).
+    A plain mapping ``name -> Cohort`` that checks sample alignment and subsets all members together."""
+
+    def add(self, name: str, cohort: Cohort) -> "MultiCohort":
+        if self and list(next(iter(self.values())).sample_ids) != list(cohort.sample_ids):
+            raise ValueError(f"assay '{name}' has different samples than the existing assays")
+        self[name] = cohort
+        return self
+
+    def select_samples(self, mask_or_idx) -> "MultiCohort":
+        out = MultiCohort()
+        for k, v in self.items():
+            out[k] = v.select_samples(mask_or_idx)
+        return out
