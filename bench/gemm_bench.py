@@ -33,9 +33,15 @@ for (M, N, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (16384, 16384, 2048), 
     b = torch.randn(N, K, device="cuda").bfloat16()
     c = torch.empty(M, (N + 3) // 4 * 4, device="cuda")
     na = torch.ones(M, device="cuda"); nb = torch.ones(N, device="cuda")
+    G.set_variant(1)
+    one_cta = timed(lambda: G.gemm_tn(a, [b], N, out=c))
+    G.set_variant(2)
+    pair = timed(lambda: G.gemm_tn(a, [b], N, out=c))
+    G.set_variant(0)
     ours = timed(lambda: G.gemm_tn(a, [b], N, out=c))
     rbf = timed(lambda: G.gemm_tn(a, [b], N, epilogue=G.EPI_RBF, alpha=1e-4, norm_a=na, norm_b=[nb], out=c))
     cublas = timed(lambda: torch.matmul(a, b.t()))
     fl = 2.0 * M * N * K
     print(json.dumps({"M": M, "N": N, "K": K, "ours_ms": ours, "ours_tflops": fl / ours / 1e9, "ours_rbf_tflops": fl / rbf / 1e9,
+                      "one_cta_tflops": fl / one_cta / 1e9, "cta_pair_tflops": fl / pair / 1e9,
                       "cublas_bf16_out_ms": cublas, "cublas_tflops": fl / cublas / 1e9}), flush=True)

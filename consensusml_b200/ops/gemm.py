@@ -18,7 +18,14 @@ _I, _LL, _F, _P = ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_void
 _native.register_signature("cml_to_bf16_rownorm", [_P, _LL, _P, _LL, _P, _I, _I, _F, _P, _P, _P])
 _native.register_signature("cml_gemm_tn_bf16", [_I, _I, _I, _P, _LL, _P, _I, _I, _LL, _P, _LL, _I, _F, _P, _P, _P])
 
+_native.register_signature("cml_gemm_set_variant", [_I])
+
 EPI_SCALE, EPI_RBF, EPI_SQDIST = 0, 1, 2
+
+
+def set_variant(variant: int) -> None:
+    """0 = choose by shape, 1 = single-CTA tcgen05 kernel, 2 = CTA-pair (``cta_group::2``) kernel."""
+    _native.check(_native.cuda().cml_gemm_set_variant(int(variant)), "cml_gemm_set_variant")
 
 
 def _pad8(k: int) -> int:

@@ -10,14 +10,15 @@
 //   * k-means / hclust distance blocks.
 // The reference delegates all of these to CPU libraries; nothing in it is a GEMM kernel.
 //
-// Structure (one CTA per SM, persistent over output tiles, 192 threads):
+// Structure (one CTA per SM, persistent over output tiles, 320 threads):
 //   warp 0     : TMA producer - cp.async.bulk.tensor 2-D boxes (64 bf16 x 128 rows, 128B swizzle) of A and B
 //                into a STAGES-deep shared-memory ring, completion on `full` mbarriers;
 //   warp 1     : allocates TMEM, then a single thread issues tcgen05.mma (M=128, N=BN, K=16, cta_group::1)
 //                straight from the swizzled tiles via shared-memory descriptors; tcgen05.commit releases
 //                ring slots (`empty`) and publishes finished accumulators (`tmem_full`);
-//   warps 2..5 : epilogue - tcgen05.ld the fp32 accumulator (32 lanes x 32 columns per warp per load), apply
-//                the fused epilogue (scale | RBF exponent with row/column squared norms), store to global.
+//   warps 2..9 : epilogue - tcgen05.ld the fp32 accumulator (32 lanes x 32 columns per warp per load), apply
+//                the fused epilogue (scale | RBF exponent with row/column squared norms), stage the chunk in
+//                swizzled shared memory and write it with one TMA tensor store.
 //                Two accumulator stages in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
 // The B operand may be spread over several "sources" (one tensor map + norm vector each).  With one source
 // it is a plain GEMM; with the sources being the symmetric-memory buffers of the NVLink peers it is the fused
@@ -64,17 +65,37 @@ int make_tmap_bf16_k64(CUtensorMap* out, const void* base, long long rows, long 
   return 0;
 }
 
+// fp32 row-major C [rows][cols] with pitch ld as 32 x 32 boxes, 128B swizzle (the epilogue's staging layout).
+int make_tmap_f32_box32(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld) {
+  EncodeTiledFn enc = get_encode_tiled();
+  CML_REQUIRE(enc != nullptr, CML_ENOTSUP, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CML_REQUIRE(r == CUDA_SUCCESS, 2000 + static_cast<int>(r), "cuTensorMapEncodeTiled (C) failed with CUresult %d", static_cast<int>(r));
+  return 0;
+}
+
 namespace {
 
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int kMaxSrc = 8;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;                            // two per TMEM lane quarter: each takes half of the columns
+constexpr int kThreads = 64 + 32 * kEpiWarps;
+constexpr int kEpiChunkBytes = 32 * 32 * 4;              // one 32-row x 32-column fp32 chunk
+constexpr int kEpiStageBytes = kEpiWarps * kEpiChunkBytes; // one staging chunk per epilogue warp
 
 enum Epilogue : int { EPI_SCALE = 0, EPI_RBF = 1, EPI_SQDIST = 2 };
 
 struct GemmParams {
   CUtensorMap map_a;
   CUtensorMap map_b[kMaxSrc];
+  CUtensorMap map_c;              // fp32 C as 32 x 32 boxes (128B swizzle) for the TMA-store epilogue
+  int c_tma;                      // 0: C pitch/alignment unsuitable for TMA -> register stores
   const float* norm_b[kMaxSrc];   // squared row norms of every B source (RBF / distance epilogues)
   const float* norm_a;
   float* c;
@@ -103,8 +124,10 @@ struct SmemLayout {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kRingBytes = STAGES * kStageBytes;
   static constexpr int kBarrierBytes = (2 * STAGES + 4) * 8 + 16;
-  static constexpr int kTotal = STAGES * kStageBytes + kBarrierBytes + 1024;   // +1024: manual alignment slack
+  static constexpr int kTotal = kRingBytes + kEpiStageBytes + kBarrierBytes + 1024;   // +1024: manual alignment slack
+  static_assert(kTotal <= 227 * 1024, "shared memory budget");
 };
 
 __device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
@@ -183,6 +206,112 @@ __device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
   }
 }
 
+// Epilogue of one accumulator: this warp owns TMEM lanes [quarter*32, +32) = 32 output rows, BN columns.
+// Per 32-column chunk: tcgen05.ld -> fused math in registers -> st.shared.v4 into a 128B-swizzled 32 x 32 staging
+// tile (conflict-free: the 8 lanes of a quarter-warp hit 8 different 16-byte columns) -> ONE TMA tensor store that
+// writes 32 full 128-byte lines and clips rows >= M.  (Register stores wrote 16 bytes into 32 different lines per
+// instruction; with K <= 1024 that made the epilogue longer than the MMAs of the tile.)  Chunks that straddle the end
+// of a source, or a C that TMA cannot address, fall back to register stores.
+// 2^x on the SFU without the denormal pre/post scaling of exp2f (results below 2^-126 flush to zero)
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_tile_impl(const GemmParams& P, uint32_t tmem_acc, int row_warp0, int lane, int src,
+                                                   int col_src0, const float* nb, uint32_t stage_u32, uint8_t* stage_gen,
+                                                   int chunk_begin) {
+  using namespace sm100;
+  const int row = row_warp0 + lane;
+  const int rows_here = min(P.rows_per_src, P.N - src * P.rows_per_src);
+  float na = 0.f;
+  if (EPI != EPI_SCALE && row < P.M) na = __ldg(P.norm_a + row);
+  const float g = -P.alpha * 1.4426950408889634f;
+  const bool nb_vec = EPI != EPI_SCALE && (reinterpret_cast<uintptr_t>(nb) & 15) == 0;
+  constexpr int kChunks = BN / 32 / 2;                   // this warp's half of the tile's columns
+  uint32_t rr[2][32];                                    // chunk c+1 is in flight from TMEM while chunk c is processed
+  tmem_acc += chunk_begin * 32;
+  tmem_ld_32x32_issue(tmem_acc, rr[0]);
+#pragma unroll
+  for (int c = 0; c < kChunks; ++c) {
+    const int c0 = (chunk_begin + c) * 32;
+    const int cs = col_src0 + c0;                        // first column of this chunk within the source
+    const bool live = row_warp0 < P.M && cs < rows_here; // warp-uniform
+    const int nvalid = min(32, rows_here - cs);
+    float nbv[32];                                       // column norms of this chunk (same for every lane: L1 broadcast)
+    if (EPI != EPI_SCALE && live) {
+      if (nb_vec && nvalid == 32) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(nb + cs) + q);
+          nbv[4 * q] = t.x; nbv[4 * q + 1] = t.y; nbv[4 * q + 2] = t.z; nbv[4 * q + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) nbv[j] = (j < nvalid) ? __ldg(nb + cs + j) : 0.f;
+      }
+    }
+    tmem_ld_wait(rr[c & 1]);
+    if (c + 1 < kChunks) tmem_ld_32x32_issue(tmem_acc + (c + 1) * 32, rr[(c + 1) & 1]);
+    if (!live) continue;
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rr[c & 1][j]);
+    if (EPI == EPI_SCALE) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= P.alpha;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float d2 = fmaxf(na + nbv[j] - 2.f * v[j], 0.f);
+        v[j] = (EPI == EPI_RBF) ? ex2_ftz(g * d2) : d2;
+      }
+    }
+    const int ccol = src * P.rows_per_src + cs;
+    if (P.c_tma && nvalid == 32) {
+      constexpr uint32_t buf = 0;
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous store has left the buffer
+      __syncwarp();
+      float4* dst = reinterpret_cast<float4*>(stage_gen + buf + lane * 128);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) dst[q ^ (lane & 7)] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                         reinterpret_cast<uint64_t>(&P.map_c)),
+                     "r"(stage_u32 + buf), "r"(ccol), "r"(row_warp0)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    } else if (row < P.M) {
+      float* out = P.c + (size_t)row * P.ldc + ccol;
+      if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < nvalid) out[j] = v[j];
+      }
+    }
+  }
+}
+
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& P, uint32_t tmem_acc, int row_warp0, int lane, int src,
+                                              int col_src0, const float* nb, uint32_t stage_u32, uint8_t* stage_gen,
+                                              int chunk_begin) {
+  if (P.epilogue == EPI_SCALE)
+    epilogue_tile_impl<BN, EPI_SCALE>(P, tmem_acc, row_warp0, lane, src, col_src0, nb, stage_u32, stage_gen, chunk_begin);
+  else if (P.epilogue == EPI_RBF)
+    epilogue_tile_impl<BN, EPI_RBF>(P, tmem_acc, row_warp0, lane, src, col_src0, nb, stage_u32, stage_gen, chunk_begin);
+  else
+    epilogue_tile_impl<BN, EPI_SQDIST>(P, tmem_acc, row_warp0, lane, src, col_src0, nb, stage_u32, stage_gen, chunk_begin);
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_constant__ GemmParams P) {
   using L = SmemLayout<BN, STAGES>;
@@ -197,12 +326,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;              // SWIZZLE_128B tiles need 1024-byte alignment
   uint8_t* gen_base = smem_raw + (base - raw);
-  const uint32_t bar0 = base + STAGES * L::kStageBytes;
+  const uint32_t bar0 = base + L::kRingBytes + kEpiStageBytes;
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
   auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
   auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + 2 + s); };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen_base + STAGES * L::kStageBytes + (2 * STAGES + 4) * 8);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen_base + L::kRingBytes + kEpiStageBytes + (2 * STAGES + 4) * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_kb = (P.K + BK - 1) / BK;
@@ -214,7 +343,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
     prefetch_tensormap(&P.map_a);
     for (int s = 0; s < (staged ? 1 : P.n_src); ++s) prefetch_tensormap(&P.map_b[s]);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), kEpiWarps); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -285,54 +414,26 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
   } else {
     // ===================== epilogue warps (TMEM -> registers -> global) =====================
     const int quarter = warp & 3;                            // TMEM lane quarter this warp may read
+    const int ew = warp - 2, chunk_begin = (ew >> 2) * (BN / 64);   // warps 2..5: left half of the columns, 6..9: right half
+    const uint32_t epi_u32 = base + L::kRingBytes + ew * kEpiChunkBytes;
+    uint8_t* epi_gen = gen_base + L::kRingBytes + ew * kEpiChunkBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
       const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
       const int src = staged ? (P.rank + si) % P.n_src : si;
-      const int row = m_blk * BM + quarter * 32 + lane;
-      const int col_src0 = n_loc * BN;                       // column offset inside the source
-      const int rows_here = min(P.rows_per_src, P.N - src * P.rows_per_src);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      float na = 0.f;
-      if (P.epilogue != EPI_SCALE && row < P.M) na = __ldg(P.norm_a + row);
       const float* nb = staged ? P.stage_norm + (size_t)src * P.rows_per_src : P.norm_b[src];
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        float v[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN + c0, v);
-        const int cs = col_src0 + c0;                        // first column of this chunk within the source
-        if (row < P.M && cs < rows_here) {
-          float* out = P.c + (size_t)row * P.ldc + (size_t)src * P.rows_per_src + cs;
-          const int nvalid = min(32, rows_here - cs);
-          if (P.epilogue == EPI_SCALE) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= P.alpha;
-          } else {
-            const float g = (P.epilogue == EPI_RBF) ? -P.alpha * 1.4426950408889634f : 0.f;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float nbj = (j < nvalid) ? __ldg(nb + cs + j) : 0.f;
-              const float d2 = fmaxf(na + nbj - 2.f * v[j], 0.f);
-              v[j] = (P.epilogue == EPI_RBF) ? exp2f(g * d2) : d2;
-            }
-          }
-          if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(out) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-            for (int j = 0; j < nvalid; ++j) out[j] = v[j];
-          }
-        }
-      }
+      epilogue_tile<BN>(P, tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN, m_blk * BM + quarter * 32, lane, src,
+                        n_loc * BN, nb, epi_u32, epi_gen, chunk_begin);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(acc));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // C tiles are written before the CTA exits
   }
   tc_fence_before();
   __syncthreads();
@@ -354,6 +455,167 @@ int launch_gemm(const GemmParams& P, cudaStream_t st) {
   CML_LAUNCH_CHECK();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): the two CTAs of a 2-cluster (one TPC) own ONE 256 x 256 output tile.  CTA r of
+// the pair stages rows [r*128, r*128+128) of the A tile and rows [r*128, ...) of the B tile (its half of N); the
+// leader's single MMA thread issues tcgen05.mma.cta_group::2 with M = 256, N = 256 and the tensor cores of both SMs
+// read the other SM's B half over the pair link.  Per 256x256x64 step the pair pulls 64 KB from L2 (the single-CTA
+// kernel: 96 KB) and each SM reads 8 KB of shared memory per MMA instead of 12 KB.
+//   barriers: full[s]  - leader only; both CTAs' TMA loads complete_tx on it (cp.async.bulk.tensor ... cta_group::2)
+//             empty[s] - one per CTA; the leader's tcgen05.commit multicasts the arrival to both
+//             tfull[a] - one per CTA (multicast commit): accumulator stage a is complete in BOTH CTAs' TMEM
+//             tempty[a]- leader only, 16 arrivals: the eight epilogue warps of each CTA (remote mbarrier.arrive)
+template <int STAGES>
+struct PairLayout {
+  static constexpr int kABytes = 128 * BK * 2;
+  static constexpr int kBBytes = 128 * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kRingBytes = STAGES * kStageBytes;
+  static constexpr int kBarrierBytes = (2 * STAGES + 4) * 8 + 16;
+  static constexpr int kTotal = kRingBytes + kEpiStageBytes + kBarrierBytes + 1024;
+  static_assert(kTotal <= 227 * 1024, "shared memory budget");
+};
+
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn_pair_kernel(const __grid_constant__ GemmParams P) {
+  using L = PairLayout<STAGES>;
+  using namespace sm100;
+  constexpr int BN = 256, BM2 = 256;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int tile0 = (int)(blockIdx.x >> 1), tile_stride = (int)(gridDim.x >> 1);
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen_base = smem_raw + (base - raw);
+  const uint32_t bar0 = base + L::kRingBytes + kEpiStageBytes;
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + 2 + s); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gen_base + L::kRingBytes + kEpiStageBytes + (2 * STAGES + 4) * 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = (P.K + BK - 1) / BK;
+  const int tiles_n = P.tiles_n_per_src * P.n_src;
+  const int num_tiles = P.tiles_m * tiles_n;
+  constexpr uint32_t kTmemCols = 2 * BN;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&P.map_a);
+    if (P.c_tma) prefetch_tensormap(&P.map_c);
+    for (int s = 0; s < P.n_src; ++s) prefetch_tensormap(&P.map_b[s]);
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * kEpiWarps); }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();                                        // barriers + TMEM of BOTH CTAs are ready
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (one thread in each CTA) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
+        const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+        const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        const int arow = m_blk * BM2 + (int)cta * 128;
+        const int brow = n_loc * BN + (int)cta * 128;
+        const CUtensorMap* mapb = &P.map_b[src];
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
+          const uint32_t fb = mapa_cluster(full_bar(stage), 0);
+          if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * L::kStageBytes);
+          tma_load_2d_pair(sa, &P.map_a, fb, kb * BK, arow);
+          tma_load_2d_pair(sb, mapb, fb, kb * BK, brow);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+      // tail: every commit aimed at this CTA's empty barriers has landed before the CTA may exit
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread of the leader CTA) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(BM2, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
+          const uint64_t adesc = umma_desc_k_sw128(sa), bdesc = umma_desc_k_sw128(sb);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) umma_bf16_pair(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+          umma_commit_pair(empty_bar(stage), 3);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit_pair(tfull_bar(acc), 3);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps: this CTA's 128 rows x 256 columns =====================
+    const int quarter = warp & 3;
+    const int ew = warp - 2, chunk_begin = (ew >> 2) * (BN / 64);   // warps 2..5: left half of the columns, 6..9: right half
+    const uint32_t epi_u32 = base + L::kRingBytes + ew * kEpiChunkBytes;
+    uint8_t* epi_gen = gen_base + L::kRingBytes + ew * kEpiChunkBytes;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
+      const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+      const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      epilogue_tile<BN>(P, tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN,
+                        m_blk * BM2 + (int)cta * 128 + quarter * 32, lane, src, n_loc * BN, P.norm_b[src], epi_u32, epi_gen, chunk_begin);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_cluster(tempty_bar(acc), 0));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();                                        // neither CTA leaves while the other may still touch it
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, kTmemCols);
+  }
+}
+
+template <int STAGES>
+int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
+  using L = PairLayout<STAGES>;
+  auto kern = gemm_tn_pair_kernel<STAGES>;
+  CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+  const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
+  const int pairs = sm_count() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kern<<<grid, kThreads, L::kTotal, st>>>(P);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+int g_gemm_variant = 0;   // 0 = choose by shape, 1 = single-CTA kernel, 2 = CTA-pair kernel
 
 // fp32 row-major -> bf16 row-major with zero-padded pitch, fused with the squared row norm of the
 // ROUNDED values (so that the RBF epilogue's |a|^2 + |b|^2 - 2ab is exactly consistent with the MMA inputs).
@@ -414,29 +676,48 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
   memset(&P, 0, sizeof(P));
   // N = 256 per MMA halves the shared-memory bytes read per FLOP (the 128x128 atom reads A+B at exactly the 128 B/clk
   // shared-memory rate); use it whenever a source is wide enough to fill such tiles
-  const int BN = (rows_per_src < N ? rows_per_src : N) >= 768 ? 256 : 128;
+  const int src_rows = rows_per_src < N ? rows_per_src : N;
+  const int BN = src_rows >= 768 ? 256 : 128;
+  // CTA pairs (256 x 256 tiles) once there are enough such tiles to occupy every pair of SMs
+  const bool pair = g_gemm_variant == 2 ||
+                    (g_gemm_variant == 0 && BN == 256 && (long long)ceil_div(M, 256) * ceil_div(src_rows, 256) * n_src >= sm_count() / 2);
   int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
   if (rc) return rc;
   for (int s = 0; s < n_src; ++s) {
     const long long rows_s = (long long)N - (long long)s * rows_per_src < rows_per_src ? (long long)N - (long long)s * rows_per_src
                                                                                       : rows_per_src;
     CML_REQUIRE(rows_s > 0, CML_EINVAL, "cml_gemm_tn_bf16: source %d is empty", s);
-    rc = make_tmap_bf16_k64(&P.map_b[s], b_ptrs[s], rows_s, K, ldb, BN);
+    rc = make_tmap_bf16_k64(&P.map_b[s], b_ptrs[s], rows_s, K, ldb, pair ? 128 : BN);
     if (rc) return rc;
     P.norm_b[s] = norm_b_ptrs ? norm_b_ptrs[s] : nullptr;
   }
   P.norm_a = norm_a;
   P.c = c;
   P.ldc = ldc;
+  P.c_tma = (reinterpret_cast<uintptr_t>(c) & 15) == 0 && ldc % 4 == 0 && ldc >= N;
+  if (P.c_tma && (rc = make_tmap_f32_box32(&P.map_c, c, M, N, ldc)) != 0) return rc;
   P.M = M; P.N = N; P.K = K;
   P.n_src = n_src;
   P.rows_per_src = rows_per_src;
   P.epilogue = epilogue;
   P.alpha = alpha;
+  if (pair) {
+    P.tiles_m = ceil_div(M, 256);
+    P.tiles_n_per_src = ceil_div(src_rows, 256);
+    return launch_gemm_pair<6>(P, static_cast<cudaStream_t>(stream));
+  }
   P.tiles_m = ceil_div(M, BM);
-  P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
+  P.tiles_n_per_src = ceil_div(src_rows, BN);
   if (BN == 256) return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
   return launch_gemm<128, 6>(P, static_cast<cudaStream_t>(stream));
+}
+
+// 0 = choose by shape (default), 1 = always the single-CTA kernel, 2 = always the CTA-pair kernel.  For benchmarks/tests.
+int cml_gemm_set_variant(int variant) {
+  using namespace cml;
+  CML_REQUIRE(variant >= 0 && variant <= 2, CML_EINVAL, "cml_gemm_set_variant: %d not in 0..2", variant);
+  g_gemm_variant = variant;
+  return 0;
 }
 
 // Fused all-gather -> GEMM with staging (see GemmParams): B source s lives at peer_ptrs[s] (peer or local device
@@ -466,6 +747,8 @@ int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, c
     P.peer_norm[s] = peer_norm_ptrs ? peer_norm_ptrs[s] : nullptr;
   }
   P.norm_a = norm_a; P.c = c; P.ldc = ldc;
+  P.c_tma = (reinterpret_cast<uintptr_t>(c) & 15) == 0 && ldc % 4 == 0 && ldc >= N;
+  if (P.c_tma && (rc = make_tmap_f32_box32(&P.map_c, c, M, N, ldc)) != 0) return rc;
   P.M = M; P.N = N; P.K = K;
   P.n_src = n_src; P.rows_per_src = rows_per_src;
   P.epilogue = epilogue; P.alpha = alpha;

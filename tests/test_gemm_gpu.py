@@ -59,3 +59,47 @@ def test_multi_source_b_matches_single():
     # ragged last source
     split2 = G.gemm_tn(ab, parts, 600, epilogue=G.EPI_RBF, alpha=0.01, norm_a=na, norm_b=norms)
     assert torch.equal(whole[:, :600], split2)
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 64), (512, 1024, 512), (300, 1000, 200), (1000, 1984, 137), (2304, 2560, 1000),
+                                    (4096, 4096, 2048)])
+def test_cta_pair_kernel_matches_reference(m, n, k):
+    """cta_group::2 kernel (two SMs per 256 x 256 tile), forced for every shape including ragged edges."""
+    a, b = _ref_inputs(m, n, k, 5)
+    ab, na = G.to_bf16_rows(a)
+    bb, nb = G.to_bf16_rows(b)
+    ref = ab[:, :k].float() @ bb[:, :k].float().t()
+    G.set_variant(2)
+    try:
+        c = G.gemm_tn(ab, [bb], n, alpha=0.5)
+        d2 = G.gemm_tn(ab, [bb], n, epilogue=G.EPI_SQDIST, norm_a=na, norm_b=[nb])
+        torch.cuda.synchronize()
+    finally:
+        G.set_variant(0)
+    scale = max(1.0, ref.abs().max().item())
+    assert (c - 0.5 * ref).abs().max().item() < 1e-3 * scale
+    d2ref = (na[:, None] + nb[None, :] - 2 * ref).clamp_min(0)
+    assert (d2 - d2ref).abs().max().item() < 2e-3 * scale
+    G.set_variant(1)
+    try:
+        c1 = G.gemm_tn(ab, [bb], n, alpha=0.5)
+        torch.cuda.synchronize()
+    finally:
+        G.set_variant(0)
+    assert (c - c1).abs().max().item() < 1e-3 * scale
+
+
+def test_cta_pair_multi_source():
+    a, b = _ref_inputs(512, 4 * 384, 256, 6)
+    ab, na = G.to_bf16_rows(a)
+    bb, nb = G.to_bf16_rows(b)
+    parts = [bb[i * 384:(i + 1) * 384].contiguous() for i in range(4)]
+    norms = [nb[i * 384:(i + 1) * 384].contiguous() for i in range(4)]
+    ref = torch.exp(-0.01 * (na[:, None] + nb[None, :] - 2 * (ab.float() @ bb.float().t())).clamp_min(0))
+    G.set_variant(2)
+    try:
+        split = G.gemm_tn(ab, parts, 1500, epilogue=G.EPI_RBF, alpha=0.01, norm_a=na, norm_b=norms)
+        torch.cuda.synchronize()
+    finally:
+        G.set_variant(0)
+    assert (split - ref[:, :1500]).abs().max().item() < 1e-4
