@@ -212,6 +212,24 @@ __device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
 // writes 32 full 128-byte lines and clips rows >= M.  (Register stores wrote 16 bytes into 32 different lines per
 // instruction; with K <= 1024 that made the epilogue longer than the MMAs of the tile.)  Chunks that straddle the end
 // of a source, or a C that TMA cannot address, fall back to register stores.
+// Tile order: groups of kGroupM m-tiles sweep all n-tiles before the next group starts, so the ~#SM tiles in flight
+// touch a kGroupM x (#SM / kGroupM) block of the output and its A/B panels stay L2-resident (plain column order would
+// stream all of A once per 2-3 n-tiles).
+constexpr int kGroupM = 8;
+__device__ __forceinline__ void tile_to_mn(int tile, int tiles_m, int tiles_n, bool grouped, int& m_blk, int& n_blk) {
+  if (!grouped) {
+    m_blk = tile % tiles_m;
+    n_blk = tile / tiles_m;
+    return;
+  }
+  const int per_group = kGroupM * tiles_n;
+  const int group = tile / per_group, in_group = tile - group * per_group;
+  const int m0 = group * kGroupM;
+  const int gm = min(kGroupM, tiles_m - m0);
+  m_blk = m0 + in_group % gm;
+  n_blk = in_group / gm;
+}
+
 // 2^x on the SFU without the denormal pre/post scaling of exp2f (results below 2^-126 flush to zero)
 __device__ __forceinline__ float ex2_ftz(float x) {
   float y;
@@ -361,7 +379,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
-        const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+        int m_blk, n_blk;
+        tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
         const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
         const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
         if (staged) {
@@ -420,7 +439,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
-      const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+      int m_blk, n_blk;
+      tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
       const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
       const int src = staged ? (P.rank + si) % P.n_src : si;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -525,7 +545,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
-        const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+        int m_blk, n_blk;
+        tile_to_mn(tile, P.tiles_m, tiles_n, true, m_blk, n_blk);
         const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
         const int arow = m_blk * BM2 + (int)cta * 128;
         const int brow = n_loc * BN + (int)cta * 128;
@@ -581,7 +602,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
-      const int m_blk = tile % P.tiles_m, n_blk = tile / P.tiles_m;
+      int m_blk, n_blk;
+      tile_to_mn(tile, P.tiles_m, tiles_n, true, m_blk, n_blk);
       const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
