@@ -503,9 +503,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
   using namespace sm100;
   constexpr int BN = 256, BM2 = 256;
   extern __shared__ uint8_t smem_raw[];
+  if ((int)blockIdx.x < P.n_copiers) {                       // n_copiers is even: whole clusters take the copier role
+    copier_role<BN>(P, smem_raw);
+    return;
+  }
+  const bool staged = P.n_copiers > 0;
   const uint32_t cta = cluster_ctarank();
   const bool leader = cta == 0;
-  const int tile0 = (int)(blockIdx.x >> 1), tile_stride = (int)(gridDim.x >> 1);
+  const int tile0 = ((int)blockIdx.x - P.n_copiers) >> 1, tile_stride = ((int)gridDim.x - P.n_copiers) >> 1;
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* gen_base = smem_raw + (base - raw);
@@ -525,7 +530,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&P.map_a);
     if (P.c_tma) prefetch_tensormap(&P.map_c);
-    for (int s = 0; s < P.n_src; ++s) prefetch_tensormap(&P.map_b[s]);
+    for (int s = 0; s < (staged ? 1 : P.n_src); ++s) prefetch_tensormap(&P.map_b[s]);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * kEpiWarps); }
     fence_barrier_init();
@@ -546,11 +551,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         int m_blk, n_blk;
-        tile_to_mn(tile, P.tiles_m, tiles_n, true, m_blk, n_blk);
-        const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+        const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+        const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
+        if (staged) {
+          const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
+          while (ld_acquire_gpu(flag) != P.epoch) {
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         const int arow = m_blk * BM2 + (int)cta * 128;
-        const int brow = n_loc * BN + (int)cta * 128;
-        const CUtensorMap* mapb = &P.map_b[src];
+        const int brow = (staged ? src * P.rows_per_src : 0) + n_loc * BN + (int)cta * 128;
+        const CUtensorMap* mapb = staged ? &P.map_b[0] : &P.map_b[src];
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = base + stage * L::kStageBytes, sb = sa + L::kABytes;
@@ -603,12 +615,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       int m_blk, n_blk;
-      tile_to_mn(tile, P.tiles_m, tiles_n, true, m_blk, n_blk);
-      const int src = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+      const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
+      const int src = staged ? (P.rank + si) % P.n_src : si;
+      const float* nb = staged ? P.stage_norm + (size_t)src * P.rows_per_src : P.norm_b[src];
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       epilogue_tile<BN>(P, tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN,
-                        m_blk * BM2 + (int)cta * 128 + quarter * 32, lane, src, n_loc * BN, P.norm_b[src], epi_u32, epi_gen, chunk_begin);
+                        m_blk * BM2 + (int)cta * 128 + quarter * 32, lane, src, n_loc * BN, nb, epi_u32, epi_gen, chunk_begin);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_cluster(tempty_bar(acc), 0));
@@ -631,7 +645,8 @@ int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
   CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
   const int pairs = sm_count() / 2;
-  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  int grid = 2 * (tiles < pairs ? tiles : pairs);
+  if (P.n_copiers > 0) grid = 2 * pairs;             // copier clusters + GEMM clusters must all be co-resident (flags are spun on)
   kern<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;
@@ -760,9 +775,11 @@ int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, c
   GemmParams P;
   memset(&P, 0, sizeof(P));
   const int BN = 256;
+  const bool pair = g_gemm_variant != 1;             // CTA pairs unless the single-CTA kernel is forced
+  if (pair) n_copiers = (n_copiers + 1) & ~1;
   int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
   if (rc) return rc;
-  rc = make_tmap_bf16_k64(&P.map_b[0], stage, (long long)n_src * rows_per_src, K, ldb, BN);
+  rc = make_tmap_bf16_k64(&P.map_b[0], stage, (long long)n_src * rows_per_src, K, ldb, pair ? 128 : BN);
   if (rc) return rc;
   for (int s = 0; s < n_src; ++s) {
     P.peer_src[s] = peer_ptrs[s];
@@ -774,10 +791,11 @@ int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, c
   P.M = M; P.N = N; P.K = K;
   P.n_src = n_src; P.rows_per_src = rows_per_src;
   P.epilogue = epilogue; P.alpha = alpha;
-  P.tiles_m = ceil_div(M, BM);
+  P.tiles_m = ceil_div(M, pair ? 256 : BM);
   P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
   P.stage = stage; P.stage_norm = stage_norm; P.flags = flags; P.epoch = epoch;
   P.n_copiers = n_copiers; P.rank = rank; P.ldb = ldb;
+  if (pair) return launch_gemm_pair<6>(P, static_cast<cudaStream_t>(stream));
   return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
 }
 
