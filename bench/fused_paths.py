@@ -160,6 +160,20 @@ def main():
         t_roof = max(flops / (tf * 1e12), link / (NVLINK_GBS * 1e9))
         emit(path="gram_allgather_tcgen05_rbf", rows_per_gpu=m, genes=p, ms=ms, tflops=flops / ms / 1e9,
              frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
+    if "transpose" not in args.skip:
+        # ---- path 4: sample-shard -> gene-shard transpose, 32768 samples per GPU x 20k genes fp32 (2.6 GB per GPU)
+        from consensusml_b200.parallel import transpose as TR
+        m, p = 32768, args.genes
+        x = torch.randn(m, p, device=dev)
+        plan = TR.ShardTranspose(m * world, p, dev)
+        plan(x)
+        ms = timed(lambda: plan(x), args.reps, flush)
+        ms_nccl = timed(lambda: TR.shard_transpose_unfused(x, m * world), args.reps, flush)
+        byts = 2.0 * m * p * 4                                  # read once + write once per GPU
+        link = m * p * 4 * (world - 1) / world
+        t_roof = max(byts / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
+        emit(path="shard_transpose", rows_per_gpu=m, genes=p, ms=ms, nccl_all_to_all_plus_transpose_ms=ms_nccl,
+             gbs=byts / ms / 1e6, frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
     D.barrier()
     D.shutdown()
 

@@ -197,6 +197,50 @@ __global__ void prox_allgather_kernel(float* __restrict__ grad_owned, int genes_
   }
 }
 
+// ============================================================================================ path 4
+// Shard transpose (the all-to-all between the two layouts of the pipeline): every rank holds a row block of a matrix
+// (samples x genes for the model kernels) and needs a column block of it, transposed (genes x samples for the per-gene
+// statistics) - or the other way round.  One kernel: 64 x 32 word tiles are transposed through padded shared memory and
+// the transposed rows (64 words = 256 bytes) are stored straight into the owner's symmetric buffer over NVLink; the
+// last CTA releases this rank's signal word on every destination.  No send/receive staging, no separate transpose.
+//   X      32-bit words [rows_local][ldx]                     (this rank's rows [row0, row0 + rows_local) of the matrix)
+//   out_d  32-bit words [cols owned by d][ldy], owner d has columns [col_start[d], col_start[d+1])
+//   out_d[c - col_start[d]][row0 + r] = X[r][c]
+struct ColStarts {
+  int v[kMaxRanks + 1];
+};
+
+__global__ void __launch_bounds__(256) shard_transpose_kernel(const unsigned* __restrict__ X, long long ldx, int rows_local, int cols,
+                                                              ColStarts cs, long long ldy, int row0, Peers P,
+                                                              unsigned* __restrict__ done_count, unsigned epoch, int sig_base) {
+  __shared__ unsigned tile[64][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 64;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int r = r0 + warp + 8 * k, c = c0 + lane;
+    tile[warp + 8 * k][lane] = (r < rows_local && c < cols) ? __ldg(X + (size_t)r * ldx + c) : 0u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int cl = warp + 8 * k, c = c0 + cl;
+    if (c >= cols) continue;
+    int d = 0;
+    while (d + 1 < P.world && c >= cs.v[d + 1]) ++d;
+    unsigned* dst = reinterpret_cast<unsigned*>(P.buf[d]) + (size_t)(c - cs.v[d]) * ldy + row0 + r0;
+    if (r0 + lane < rows_local) dst[lane] = tile[lane][cl];
+    if (r0 + 32 + lane < rows_local) dst[32 + lane] = tile[32 + lane][cl];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0 && atomicAdd(done_count, 1u) == gridDim.x * gridDim.y - 1) {
+    *done_count = 0u;
+    __threadfence_system();
+    for (int r = 0; r < P.world; ++r) st_release_sys(P.sig[r] + sig_base + P.rank, epoch);
+  }
+}
+
 // eta_i = b0 + sum_j X[i][j] v[j];  r_i = w_i (y_i - sigmoid(eta_i));  loss += w_i * logloss.   Warp per row.
 __global__ void __launch_bounds__(256) xb_residual_kernel(const __nv_bfloat16* __restrict__ X, long long ldx, int n, int p,
                                                           const float* __restrict__ v, float b0, const float* __restrict__ y,
@@ -448,6 +492,27 @@ int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const floa
   prox_allgather_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad_owned, genes_owned, gene0, pf, step, lambda, inv_n,
                                                                               momentum, Pb, Pv, beta_local, done_count, epoch,
                                                                               sig_base, delta_max);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// Path 4: rows [row0, row0 + rows_local) of a 32-bit-word matrix [.][cols] -> column blocks on their owners, transposed.
+// col_start: world + 1 ints.  out_bufs[d]: owner d's [col_start[d+1] - col_start[d]][ldy] buffer (symmetric memory).
+// done_count: one zero-initialised unsigned.  Completion: signal word sig_base + rank on every destination == epoch.
+int cml_shard_transpose(const void* x, long long ldx, int rows_local, int cols, const int* col_start, const void* const* out_bufs,
+                        long long ldy, int row0, const void* const* peer_sigs, int rank, int world, unsigned* done_count,
+                        unsigned epoch, int sig_base, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, CML_EINVAL, "cml_shard_transpose: bad rank/world");
+  CML_REQUIRE(cols > 0 && rows_local >= 0 && ldx >= cols && row0 >= 0 && row0 + rows_local <= ldy, CML_EINVAL,
+              "cml_shard_transpose: rows [%d, %d) do not fit pitch %lld", row0, row0 + rows_local, ldy);
+  ColStarts cs;
+  for (int r = 0; r <= kMaxRanks; ++r) cs.v[r] = r <= world ? col_start[r] : cols;
+  CML_REQUIRE(cs.v[0] == 0 && cs.v[world] == cols, CML_EINVAL, "cml_shard_transpose: col_start must run from 0 to cols");
+  Peers P = make_peers(out_bufs, peer_sigs, rank, world);
+  dim3 grid(ceil_div(cols, 32), max(1, ceil_div(rows_local, 64)));
+  shard_transpose_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const unsigned*>(x), ldx, rows_local, cols, cs,
+                                                                              ldy, row0, P, done_count, epoch, sig_base);
   CML_LAUNCH_CHECK();
   return 0;
 }

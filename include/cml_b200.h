@@ -158,6 +158,47 @@ int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int m
                        const int* left, const float* value, int* leaf_out, float* value_out, void* stream);
 int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n, float* prox, float* pairs, void* stream);
 
+/* ---- K7: SVM (SMO dual solver, decision values) - e1071::svm at cml_targetaml_seanalysis.Rmd:151-154,166-169 ---- */
+int cml_svm_smo(int B, int n, const float* K, long long k_stride, long long ldk, const float* y, long long y_stride,
+    const float* cbound, long long c_stride, float eps, int max_iter, float* alpha, float* rho, int* iters,
+    float* obj, void* stream);
+int cml_svm_decision(const float* K, long long k_stride, long long ldk, int m, int n, const float* coef, const float* rho,
+    int B, float* dec, void* stream);
+
+/* ---- K11/K15/plots: row standardisation for correlation, Gaussian KDE, k-means assignment ---- */
+int cml_standardize_rows(const float* x, long long ldx, int rows, int n, int ranked, void* z_bf16, long long ldz, float* z_f32,
+    const int* cols, void* stream);
+int cml_kde(const float* x, int n, float bw, float lo, float hi, int n_grid, float* out, void* stream);
+int cml_kmeans_assign(const float* d2, long long ld, int n, int k, int* assign, float* mind, void* stream);
+
+/* ---- Fused compute + collective kernels over NVLink peer memory (absent from the reference) ---- */
+size_t cml_xtr_rs_scratch_bytes(int p, int nb);
+int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
+    const void* const* peer_bufs, const void* const* peer_sigs, int rank, int world,
+    int genes_per_rank, long long slot_base, unsigned epoch, void* stream);
+int cml_wait_signals(const void* pad, int base, int world, unsigned epoch, void* stream);
+int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const float* pf, float step, float lambda, float inv_n,
+    float momentum, const void* const* beta_bufs, const void* const* v_bufs, const void* const* peer_sigs,
+    int rank, int world, const float* beta_local, unsigned* done_count, unsigned epoch, int sig_base,
+    float* delta_max, void* stream);
+/* Path 4, shard transpose (all-to-all between the sample-sharded and the gene-sharded layout): rows
+ * [row0, row0 + rows_local) of a matrix of 32-bit words -> column blocks on their owner ranks, transposed, written by peer
+ * stores from inside the transpose kernel.  col_start: world + 1 ints; out_bufs[d]: owner d's [cols of d][ldy] symmetric
+ * buffer; completion = signal word (sig_base + rank) == epoch on every destination (cml_wait_signals). */
+int cml_shard_transpose(const void* x, long long ldx, int rows_local, int cols, const int* col_start, const void* const* out_bufs,
+    long long ldy, int row0, const void* const* peer_sigs, int rank, int world, unsigned* done_count,
+    unsigned epoch, int sig_base, void* stream);
+int cml_xb_residual(const void* x_bf16, long long ldx, int n, int p, const float* v, float b0, const float* y, const float* w,
+    float* R, float* eta_out, double* loss_sum, void* stream);
+size_t cml_hist_scratch_bytes(int p, int ft);
+int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
+    int n_nodes, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
+    const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, float g_bound, float h_bound,
+    void* stream);
+int cml_hist_ft(int n_nodes, int nbins);
+int cml_split_score_gain(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
+    unsigned long long* best, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

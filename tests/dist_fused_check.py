@@ -37,6 +37,23 @@ def main():
     lo, hi = shard_bounds(n, world, rank)
     xl, yl = x[lo:hi].to(dev), y[lo:hi].to(dev)
     ok = True
+    # ---- path 4: sample-shard -> gene-shard transpose (all_to_all comparator everywhere, fused kernel on CUDA)
+    from consensusml_b200.parallel import transpose as TR
+    c0, c1 = shard_bounds(p, world, rank)
+    want = x[:, c0:c1].t().contiguous()
+    got_u = TR.shard_transpose_unfused(xl, n)
+    ok &= bool(torch.equal(got_u.cpu(), want))
+    if not cpu:
+        plan = TR.ShardTranspose(n, p, dev)
+        for rep in range(3):                                  # alternating output buffers, increasing epochs
+            got_f = plan(xl * (rep + 1))
+            torch.cuda.synchronize()
+            ok &= bool(torch.equal(got_f.cpu(), want * (rep + 1)))
+        back = TR.ShardTranspose(p, n, dev)                   # and back: gene-sharded -> sample-sharded
+        again = back(got_u.contiguous())
+        torch.cuda.synchronize()
+        ok &= bool(torch.equal(again.cpu(), x[lo:hi]))
+        print(f"[{rank}] shard_transpose fused == all_to_all: {ok}", flush=True)
     if cpu:
         fit = LL.fit(xl, yl, 0.02, n_total=n, max_iter=150, backend="unfused", step=step0)
         if rank == 0:
