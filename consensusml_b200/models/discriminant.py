@@ -224,6 +224,103 @@ def _voom_transform(counts: torch.Tensor, y: torch.Tensor, n_classes: int):
 METHODS = ("PLDA", "PLDA2", "NBLDA", "pam", "voomNSC", "voomDLDA")
 
 
+@dataclass
+class QDA:
+    """Quadratic discriminant analysis with the class covariances shrunk towards their diagonal (``shrink`` = 0 is
+    plain QDA; needed as soon as genes outnumber the samples of a class).  The reference only stubs this
+    (BuieRProj/KM_WHATEVER.Rmd:375-386 prepares the frame and stops)."""
+    shrink: float = 0.1
+    means_: torch.Tensor = field(default=None, repr=False)
+    chol_: list = field(default_factory=list, repr=False)
+    logdet_: torch.Tensor = field(default=None, repr=False)
+    logprior_: torch.Tensor = field(default=None, repr=False)
+
+    def fit(self, x: torch.Tensor, y: torch.Tensor, n_classes: int = 2) -> "QDA":
+        x = x.double()
+        self.means_, self.chol_, ld, lp = [], [], [], []
+        for c in range(n_classes):
+            xc = x[y.to(x.device) == c]
+            mu = xc.mean(0)
+            d = xc - mu
+            cov = d.t() @ d / max(xc.shape[0] - 1, 1)
+            diag = torch.diag(torch.diagonal(cov).clamp_min(1e-8))
+            cov = (1 - self.shrink) * cov + self.shrink * diag + 1e-8 * torch.eye(x.shape[1], dtype=x.dtype, device=x.device)
+            L = torch.linalg.cholesky(cov)
+            self.means_.append(mu)
+            self.chol_.append(L)
+            ld.append(2 * torch.log(torch.diagonal(L)).sum())
+            lp.append(np.log(max(xc.shape[0], 1) / x.shape[0]))
+        self.logdet_ = torch.stack(ld)
+        self.logprior_ = torch.tensor(lp, dtype=x.dtype, device=x.device)
+        return self
+
+    def decision_function(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.double()
+        sc = []
+        for mu, L, ld, lp in zip(self.means_, self.chol_, self.logdet_, self.logprior_):
+            z = torch.linalg.solve_triangular(L, (x - mu).t(), upper=False)
+            sc.append(-0.5 * (z * z).sum(0) - 0.5 * ld + lp)
+        return torch.stack(sc, 1)
+
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        return self.decision_function(x).argmax(1)
+
+    def selected_genes(self) -> torch.Tensor:
+        return torch.arange(self.means_[0].numel())
+
+
+def _svm_radial(cost, seed):
+    from .svm import SVC
+    return SVC(kernel="radial", cost=float(cost))
+
+
+def _logitboost(n_iter, seed):
+    # caTools::LogitBoost = Newton boosting of decision stumps on the logistic loss
+    from .trees import GradientBoosting
+    return GradientBoosting(n_estimators=int(n_iter), max_depth=1, learning_rate=0.5, reg_lambda=0.0, min_child_weight=1e-3,
+                            mode="xgboost", seed=seed)
+
+
+def _blackboost(depth, seed):
+    # mboost::blackboost = first-order boosting of shallow regression trees, nu = 0.1
+    from .trees import GradientBoosting
+    return GradientBoosting(n_estimators=100, max_depth=int(depth), learning_rate=0.1, mode="sklearn", seed=seed)
+
+
+def _deepboost(depth, seed):
+    # deepboost: boosted trees with a complexity penalty that grows with depth -> split penalty gamma, L2 leaf penalty
+    from .trees import GradientBoosting
+    return GradientBoosting(n_estimators=50, max_depth=int(depth), learning_rate=0.3, reg_lambda=1.0, gamma=0.05 * int(depth),
+                            mode="xgboost", seed=seed)
+
+
+_TRANSFORMED = {"svmRadial": _svm_radial, "LogitBoost": _logitboost, "blackboost": _blackboost, "deepboost": _deepboost,
+                "qda": lambda shrink, seed: QDA(shrink=float(shrink))}
+
+
+class _TransformedModel:
+    """A learner trained on VST / rlog values; ``predict`` takes raw counts (genes x samples) like the count models."""
+
+    def __init__(self, model, pre, size_factors_train):
+        self.model, self.pre = model, pre
+        self.geo_ref_ = None
+
+    def _transform(self, counts):
+        sf = deseq_size_factors(counts)
+        return (deseq_vst(counts, sf) if self.pre == "deseq-vst" else deseq_rlog(counts, sf)).float().t().contiguous()
+
+    def predict(self, counts: torch.Tensor) -> torch.Tensor:
+        return self.model.predict(self._transform(counts))
+
+    def selected_genes(self) -> torch.Tensor:
+        m = self.model
+        if hasattr(m, "importance_") and m.importance_ is not None:
+            return torch.nonzero(m.importance_["gain"] > 0).flatten().cpu()
+        if hasattr(m, "selected_genes"):
+            return m.selected_genes()
+        return torch.arange(m.x_.shape[1])
+
+
 def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "PLDA", tune: Optional[Sequence[float]] = None,
              folds: int = 5, repeats: int = 10, seed: int = 2128, pre: str = "deseq-vst", n_classes: int = 2):
     """MLSeq-style ``classify``: tune the method's shrinkage parameter by repeated k-fold CV (5 x 10 in the reference,
@@ -233,7 +330,12 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
     y_train = y_train.to(counts_train.device)
     if tune is None:
         tune = {"PLDA": np.linspace(0, 15, 10), "PLDA2": np.linspace(0, 15, 10), "NBLDA": [0.0],
-                "pam": np.linspace(0, 4, 10), "voomNSC": np.linspace(0, 4, 10), "voomDLDA": [0.0]}[method]
+                "pam": np.linspace(0, 4, 10), "voomNSC": np.linspace(0, 4, 10), "voomDLDA": [0.0],
+                "svmRadial": [2.0 ** k for k in range(-2, 8)],          # caret: C = 2^((1:tuneLength) - 3)
+                "LogitBoost": [11, 21, 31],                             # caret: nIter
+                "blackboost": [1, 2, 3],                                # caret: maxdepth (mstop fixed below)
+                "deepboost": [1, 2, 3],                                 # caret: tree_depth
+                "qda": [0.0, 0.1, 0.5]}[method]                         # shrinkage towards the diagonal
     masks = replicate_weights(folds * repeats, n, mode="kfold", k=folds, seed=seed, device="cpu")[:, :n] > 0     # True = train
 
     def make(param):
@@ -243,11 +345,20 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
             return PoissonLDA(rho=float(param), power=True)
         if method == "NBLDA":
             return NBLDA()
+        if method in _TRANSFORMED:
+            return _TRANSFORMED[method](param, seed)
         return NearestShrunkenCentroids(threshold=float(param))
+
+    transformed = None
+    if method in _TRANSFORMED:                                    # caret-trained learners on the VST / rlog matrix
+        sf = deseq_size_factors(counts_train)
+        transformed = (deseq_vst(counts_train, sf) if pre == "deseq-vst" else deseq_rlog(counts_train, sf)).float()
 
     def fit_predict(param, tr, te):
         ctr, cte, ytr = counts_train[:, tr], counts_train[:, te], y_train[tr]
         mdl = make(param)
+        if method in _TRANSFORMED:
+            return mdl.fit(transformed[:, tr].t().contiguous(), ytr).predict(transformed[:, te].t().contiguous())
         if method in ("PLDA", "PLDA2", "NBLDA"):
             return mdl.fit(ctr, ytr, n_classes).predict(cte)
         if method == "pam":
@@ -272,7 +383,9 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
         table[float(param)] = float(np.mean(acc)) if acc else float("nan")
     best = max(table, key=lambda k: (table[k], k))
     mdl = make(best)
-    if method in ("PLDA", "PLDA2", "NBLDA"):
+    if method in _TRANSFORMED:
+        mdl = _TransformedModel(mdl.fit(transformed.t().contiguous(), y_train), pre, sf)
+    elif method in ("PLDA", "PLDA2", "NBLDA"):
         mdl.fit(counts_train, y_train, n_classes)
     elif method == "pam":
         sf = deseq_size_factors(counts_train)

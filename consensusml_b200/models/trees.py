@@ -180,7 +180,8 @@ def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):
 def _score(crit, a, b, lam):
     if crit == GINI:
         return np.where(b > 0, (a * a + (b - a) * (b - a)) / np.where(b > 0, b, 1), 0.0)
-    return a * a / (b + lam)
+    den = b + lam
+    return np.where(den > 0, a * a / np.where(den > 0, den, 1), 0.0)
 
 
 _M64 = (1 << 64) - 1

@@ -151,3 +151,17 @@ def test_kmeans_and_discriminant_on_gpu(counts100):
     x[:200] += 2
     a, b = kmeans.kmeans(x, 2, nstart=5), kmeans.kmeans(x.cuda(), 2, nstart=5)
     assert abs(a.tot_withinss - b.tot_withinss) / a.tot_withinss < 1e-3
+
+
+@pytest.mark.parametrize("method,tune", [("svmRadial", [0.25, 4.0]), ("LogitBoost", [11]), ("blackboost", [1]), ("deepboost", [2]),
+                                          ("qda", [0.5])])
+def test_mlseq_caret_learners_on_transformed_counts(counts100, method, tune):
+    """svmRadial / LogitBoost / blackboost / deepboost trials of VikasP/AML.R:174-198,318-364 (+ the QDA stub of
+    BuieRProj/KM_WHATEVER.Rmd:375-386): learners trained on the VST matrix, predicting from raw counts."""
+    c, y = counts100
+    tr = torch.arange(96) % 10 < 7
+    model, table = D.classify(c[:, tr], y[tr], method, tune=tune, folds=2, repeats=1, pre="deseq-vst")
+    assert all(0.5 <= v <= 1.0 for v in table.values()), table
+    pred = model.predict(c[:, ~tr])
+    assert float((pred == y[~tr]).float().mean()) >= 0.75
+    assert 1 <= len(D.selected_genes(model, [f"g{i}" for i in range(100)])) <= 100
