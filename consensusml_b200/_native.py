@@ -52,7 +52,8 @@ def cuda() -> ctypes.CDLL:
                     raise NativeError(
                         f"libcml_b200.so is missing and could not be built ({exc}); "
                         "run `python -m consensusml_b200._build`") from exc
-            lib = ctypes.CDLL(str(_build.CUDA_LIB))
+            # CML_B200_LIB: load an alternative build of the kernel library (tuning experiments)
+            lib = ctypes.CDLL(os.environ.get("CML_B200_LIB") or str(_build.CUDA_LIB))
             lib.cml_last_error.restype = ctypes.c_char_p
             _declare(lib)
             _cuda = lib

@@ -51,6 +51,23 @@ __device__ __forceinline__ void warp_sum4(float (&v)[4]) {
     for (int q = 0; q < 4; ++q) v[q] += __shfl_xor_sync(FULL, v[q], o);
   }
 }
+// Sixteen sums at once: on return lane L holds the warp-wide sum of a[L & 15].  Each stage folds pairs of values
+// across one lane bit (the lane keeps the member its bit selects and receives the partner's copy of it), so the 16
+// reductions cost 15 + 1 shuffles instead of 80; the results come out lane-parallel, ready for a coalesced store.
+__device__ __forceinline__ float warp_sum16_transposed(float (&a)[16], int lane) {
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const int o = 1 << s;
+    const bool hi = (lane & o) != 0;
+#pragma unroll
+    for (int i = 0; i < (8 >> s); ++i) {
+      const float keep = hi ? a[2 * i + 1] : a[2 * i];
+      const float send = hi ? a[2 * i] : a[2 * i + 1];
+      a[i] = keep + __shfl_xor_sync(FULL, send, o);
+    }
+  }
+  return a[0] + __shfl_xor_sync(FULL, a[0], 16);
+}
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);

@@ -31,6 +31,7 @@ struct PathArgs {
   int intercept, kopt, maxit, nx;
 };
 
+static thread_local long long g_cnt[8];   // visit counters of the calling thread (cml_host_lognet_counters)
 inline double dotw(const double* a, const double* b, int n) {
   double s = 0.0;
   for (int i = 0; i < n; ++i) s += a[i] * b[i];
@@ -150,6 +151,7 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
         if (A.kopt == 0) {
           for (int j = 0; j < p; ++j) {
             if (!ixx[j]) continue;
+            ++g_cnt[3];
             const double* xj = A.xt + (size_t)j * n;
             double s = 0.0;
             for (int i = 0; i < n; ++i) s += v[i] * xj[i] * xj[i];
@@ -157,10 +159,11 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
           }
         }
         while (true) {  // full sweep over the screened set, then iterate on the active set
-          ++nlp;
+          ++nlp; ++g_cnt[7];
           double dlx = 0.0;
           for (int k = 0; k < p; ++k) {
             if (!ixx[k]) continue;
+            ++g_cnt[0];
             if (cd_update(k, al1, al2, dlx) && mm[k] == 0) {
               ++nin;
               if (nin > A.nx) { overflow = true; break; }
@@ -175,6 +178,7 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
           while (true) {
             ++nlp;
             dlx = 0.0;
+            g_cnt[1] += nin; ++g_cnt[6];
             for (int l = 0; l < nin; ++l) cd_update(m[l], al1, al2, dlx);
             intercept_update(dlx);
             if (dlx < shr) break;
@@ -182,6 +186,7 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
           }
         }
         if (overflow) break;
+        g_cnt[4] += nin; ++g_cnt[5];
         // refresh the quadratic approximation at the new coefficients
         for (int i = 0; i < n; ++i) {
           double fi = b[0];
@@ -203,6 +208,7 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
           bool added = false;
           for (int k = 0; k < p; ++k) {
             if (ixx[k] || !ju[k]) continue;
+            ++g_cnt[2];
             ga[k] = std::fabs(dotw(r.data(), A.xt + (size_t)k * n, n));
             if (ga[k] > al1 * vpn[k]) { ixx[k] = 1; added = true; }
           }
@@ -241,6 +247,7 @@ finish:
 }  // namespace
 
 extern "C" {
+void cml_host_lognet_counters(long long* out) { for (int i = 0; i < 8; ++i) { out[i] = g_cnt[i]; g_cnt[i] = 0; } }
 
 // Batched entry: B replicates share xt/y/lambda; replicate b uses w[b*n..], ju[b*p..] (ju may be null).
 // Outputs per replicate: beta (B x nlam x p), a0 (B x nlam), dev_ratio (B x nlam), df (B x nlam),

@@ -55,25 +55,39 @@ struct LognetParams {
   int* npasses_out;           // [B]
   int* lmu_out;               // [B]
   int* jerr_out;              // [B]
+  long long* prof_out;        // [B][8] phase cycle counts (profile build of the kernel only)
+  unsigned* next_rep;         // work counter (zero at launch): replicates beyond the first wave are handed out dynamically
 };
+
+// floats of global scratch per resident warp: {b, xv} pairs + |gradient|, kept even so the pairs stay 8-byte aligned
+__host__ __device__ inline size_t scratch_stride(int p) { return 3 * (size_t)p + (p & 1); }
 
 template <int NPL>
 struct Warp {
   // ---- per-lane register state ----
   float r[NPL], v[NPL];
-  // ---- shared-memory views ----
-  unsigned* ixx;   // screened set
-  unsigned* inm;   // active set membership
-  unsigned* jub;   // usable features
-  int* m;          // active list (order of entry)
-  float* bs;       // coefficients at the start of the IRLS iteration, by active position
-  float* wq;       // normalised weights
-  float* ys;       // response
-  float* qs;       // fitted probabilities
-  // ---- global scratch ----
-  float* b;        // coefficients by feature
-  float* xv;       // curvature by feature
-  float* ga;       // |gradient| by feature at the last KKT evaluation
+  // ---- shared-memory views: [pend 16][wq n_pad][ys n_pad][qs n_pad][m nx][bs nx][ixx pw][inm pw][jub pw] ----
+  // The fixed-size arrays come first: with n_pad = 32 * NPL known at compile time their addresses are constants, and
+  // the rest are one multiply-add away from values in the constant bank - none of these views occupies a register.
+  static constexpr int kFixedBytes = 16 * 4 + 3 * 32 * NPL * 4;
+  __device__ __forceinline__ unsigned char* sbase() const {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    return smem_raw;
+  }
+  __device__ __forceinline__ int* pend() const { return reinterpret_cast<int*>(sbase()); }                  // waiting group
+  __device__ __forceinline__ float* wq() const { return reinterpret_cast<float*>(sbase() + 64); }           // normalised weights
+  __device__ __forceinline__ float* ys() const { return wq() + 32 * NPL; }                                  // response
+  __device__ __forceinline__ float* qs() const { return wq() + 64 * NPL; }                                  // fitted probabilities
+  __device__ __forceinline__ int* m() const { return reinterpret_cast<int*>(sbase() + kFixedBytes); }       // active list (entry order)
+  __device__ __forceinline__ float* bs() const { return reinterpret_cast<float*>(m() + P.nx); }             // coefficients at IRLS start
+  __device__ __forceinline__ unsigned* ixx() const { return reinterpret_cast<unsigned*>(m() + 2 * P.nx); }  // screened set
+  __device__ __forceinline__ unsigned* inm() const { return ixx() + ((P.p + 31) >> 5); }                    // active membership
+  __device__ __forceinline__ unsigned* jub() const { return ixx() + 2 * ((P.p + 31) >> 5); }                // usable features
+  // ---- global scratch of this warp: {b, xv} pairs by feature, then |gradient| at the last KKT evaluation ----
+  float* gb;
+  __device__ __forceinline__ float& b(int k) const { return gb[2 * k]; }
+  __device__ __forceinline__ float& xv(int k) const { return gb[2 * k + 1]; }
+  __device__ __forceinline__ float& ga(int k) const { return gb[2 * P.p + k]; }
   const LognetParams& P;
   const int lane;
   int nin = 0, nlp = 0;
@@ -109,8 +123,9 @@ struct Warp {
   __device__ __forceinline__ void fetch(int k, Pre& e) const {
     e.k = k;
     load_col(k, e.x);
-    e.bk = b[k];
-    e.xvk = xv[k];
+    const float2 bx = *reinterpret_cast<const float2*>(gb + 2 * k);
+    e.bk = bx.x;
+    e.xvk = bx.y;
     e.pk = vpk(k);
   }
 
@@ -122,10 +137,10 @@ struct Warp {
     g = warp_sum(g);
     const float u = g + e.xvk * e.bk;
     const float au = fabsf(u) - e.pk * al1;
-    const float nb = au > 0.f ? copysignf(au, u) / (e.xvk + e.pk * al2) : 0.f;
+    const float nb = au > 0.f ? __fdividef(copysignf(au, u), e.xvk + e.pk * al2) : 0.f;   // 2-ulp divide: the iteration is self-correcting
     const float d = nb - e.bk;
     if (d == 0.f) return false;
-    if (lane == 0) b[e.k] = nb;
+    if (lane == 0) b(e.k) = nb;
     dlx = fmaxf(dlx, e.xvk * d * d);
 #pragma unroll
     for (int j = 0; j < NPL; ++j) r[j] = fmaf(-d * v[j], e.x[j], r[j]);
@@ -149,9 +164,16 @@ struct Warp {
     }
   }
 
-  // Sweep over the whole screened set in feature order; new non-zeros join the active list.
-  // Returns false on active-list overflow.  A coordinate is visited once per sweep, so values prefetched two
-  // coordinates ahead cannot be stale.
+  // Sweep over the whole screened set in feature order; new non-zeros join the active list.  Returns false on
+  // active-list overflow.
+  //
+  // Most screened features are not in the active list: their coefficient is zero and, nearly always, stays zero - and a
+  // coordinate that does not move leaves the residual untouched, so consecutive such coordinates do not depend on each
+  // other.  They are therefore collected (up to 16) and evaluated TOGETHER against the current residual: independent
+  // column loads, one transposed reduction, lane q tests feature q.  Features already in the active list are the likely
+  // movers and take the sequential step; the pending group is flushed before each of them, so every evaluation sees
+  // exactly the residual the one-at-a-time sweep would have shown it.  If a pending feature does move (a new entry),
+  // the ones before it are final, it takes the sequential step, and the ones after it are evaluated again.
   __device__ bool sweep_screened(float al1, float al2, float& dlx) {
     const int pw = (P.p + 31) >> 5;
     int wd = 0;
@@ -159,48 +181,98 @@ struct Warp {
     auto next_feature = [&]() -> int {
       while (bits == 0u) {
         if (wd >= pw) return -1;
-        bits = ixx[wd++];
+        bits = ixx()[wd++];
       }
       const int k = ((wd - 1) << 5) + __ffs(bits) - 1;
       bits &= bits - 1;
       return k;
     };
-    Pre e0, e1, e2;
-    int k0 = next_feature();
-    if (k0 < 0) return true;
-    fetch(k0, e0);
-    int k1 = next_feature();
-    if (k1 >= 0) fetch(k1, e1);
-    __syncwarp();
-    while (k0 >= 0) {
-      const int k2 = k1 >= 0 ? next_feature() : -1;
-      if (k2 >= 0) fetch(k2, e2);
-      const bool was_in = bit(inm, k0);
-      if (cd(e0, al1, al2, dlx) && !was_in) {
+    auto step = [&](int k) -> bool {
+      Pre e;
+      fetch(k, e);
+      const bool was_in = bit(inm(), k);
+      if (cd(e, al1, al2, dlx) && !was_in) {
         if (nin >= P.nx) return false;
         __syncwarp();   // every lane has read the membership word before lane 0 rewrites it
         if (lane == 0) {
-          inm[k0 >> 5] |= 1u << (k0 & 31);
-          m[nin] = k0;
+          inm()[k >> 5] |= 1u << (k & 31);
+          m()[nin] = k;
         }
         ++nin;
+        __syncwarp();
       }
-      e0 = e1; e1 = e2;
-      k0 = k1; k1 = k2;
+      return true;
+    };
+    int np = 0;
+    auto flush = [&]() -> bool {
+      __syncwarp();                                  // pend()[] written by lane 0
+      int first = 0;
+      while (first < np) {
+        // unconditional loads (slots outside [first, np) re-read a valid column and are masked out below): without
+        // branches between them the 16 x NPL loads go out back to back and their L2 latencies overlap
+        float acc[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          float x[NPL];
+          load_col(pend()[max(first, min(q, np - 1))], x);
+          acc[q] = 0.f;
+#pragma unroll
+          for (int j = 0; j < NPL; ++j) acc[q] = fmaf(r[j], x[j], acc[q]);
+        }
+        const float g = warp_sum16_transposed(acc, lane);
+        const int q = lane & 15;
+        const bool valid = q >= first && q < np;
+        const float pk = valid ? vpk(pend()[q]) : 1.f;
+        const unsigned movers = __ballot_sync(FULL, valid && fabsf(g) - pk * al1 > 0.f) & 0xffffu;
+        if (movers == 0u) break;
+        const int q1 = __ffs(movers) - 1;
+        if (!step(pend()[q1])) return false;
+        first = q1 + 1;
+      }
+      np = 0;
+      __syncwarp();                                  // pend()[] is read before lane 0 refills it
+      return true;
+    };
+    for (int k = next_feature(); k >= 0; k = next_feature()) {
+      if (bit(inm(), k)) {
+        if (np > 0 && !flush()) return false;
+        if (!step(k)) return false;
+      } else {
+        if (lane == 0) pend()[np] = k;
+        if (++np == 16 && !flush()) return false;
+      }
     }
+    if (np > 0 && !flush()) return false;
     __syncwarp();
     return true;
   }
 
   __device__ void sweep_active(float al1, float al2, float& dlx) {
     if (nin == 0) return;
-    Pre e0, e1, e2;
-    fetch(m[0], e0);
-    if (nin > 1) fetch(m[1], e1);
-    for (int l = 0; l < nin; ++l) {
-      if (l + 2 < nin) fetch(m[l + 2], e2);
-      cd(e0, al1, al2, dlx);
-      e0 = e1; e1 = e2;
+    // L1 prefetch hints well ahead of the register prefetch: one instruction covers 8 upcoming columns (lane = column
+    // l0 + lane/4, 128-byte line lane%4), so the loads issued two coordinates ahead hit L1 instead of waiting on L2.
+    auto hint = [&](int l0) {
+      const int idx = l0 + (lane >> 2), j = lane & 3;
+      if (idx < nin && j < NPL) {
+        const float* a = P.xt + (size_t)m()[idx] * P.n_pad + 32 * j;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+      }
+    };
+    hint(0);
+    hint(8);
+    Pre ea, eb, ec;
+    fetch(m()[0], ea);
+    if (nin > 1) fetch(m()[1], eb);
+    for (int l = 0; l < nin; l += 3) {     // slots rotate a -> b -> c: no register copies between coordinates
+      if ((l & 7) < 3) hint((l & ~7) + 16);        // once per 8 coordinates (l advances by 3): columns 16..23 ahead
+      if (l + 2 < nin) fetch(m()[l + 2], ec);
+      cd(ea, al1, al2, dlx);
+      if (l + 1 >= nin) break;
+      if (l + 3 < nin) fetch(m()[l + 3], ea);
+      cd(eb, al1, al2, dlx);
+      if (l + 2 >= nin) break;
+      if (l + 4 < nin) fetch(m()[l + 4], eb);
+      cd(ec, al1, al2, dlx);
     }
     __syncwarp();          // lane 0's coefficient stores are ordered before whatever reads them next
   }
@@ -211,8 +283,8 @@ struct Warp {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) eta[j] = b0;
     for (int l = 0; l < nin; ++l) {
-      const int k = m[l];
-      const float bk = b[k];
+      const int k = m()[l];
+      const float bk = b(k);
       float x[NPL];
       load_col(k, x);
 #pragma unroll
@@ -224,8 +296,8 @@ struct Warp {
       const int i = lane + 32 * j;
       const float f = eta[j];
       const float q = f < fmin_ ? 0.f : (f > fmax_ ? 1.f : 1.f / (1.f + expf(-f)));
-      qs[i] = q;
-      const float wi = wq[i];
+      qs()[i] = q;
+      const float wi = wq()[i];
       v[j] = wi * q * (1.f - q);
       s += v[j];
     }
@@ -235,39 +307,42 @@ struct Warp {
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
       const int i = lane + 32 * j;
-      r[j] = wq[i] * (ys[i] - qs[i]);
+      r[j] = wq()[i] * (ys()[i] - qs()[i]);
     }
   }
 };
 
-template <int NPL>
-__global__ void __launch_bounds__(32, (NPL <= 4 ? 28 : (NPL <= 8 ? 20 : 12)))
+// PROF = true builds the same kernel with clock64() phase timers (cml_lognet_path_profile); the production
+// instantiation carries none of it.
+#define PROF_MARK(i)                          \
+  if constexpr (PROF) {                       \
+    const long long t_now_ = clock64();       \
+    t_ph[i] += t_now_ - t_last;               \
+    t_last = t_now_;                          \
+  }
+
+#ifndef CML_LASSO_WARPS_SMALL
+#define CML_LASSO_WARPS_SMALL 20
+#endif
+template <int NPL, bool PROF = false>
+__global__ void __launch_bounds__(32, (NPL <= 4 ? CML_LASSO_WARPS_SMALL : (NPL <= 8 ? 20 : 12)))
 lognet_path_kernel(const LognetParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x;
   const int pw = (P.p + 31) >> 5;
   Warp<NPL> W(P, lane);
-  {
-    unsigned char* s = smem_raw;
-    W.ixx = reinterpret_cast<unsigned*>(s); s += sizeof(unsigned) * pw;
-    W.inm = reinterpret_cast<unsigned*>(s); s += sizeof(unsigned) * pw;
-    W.jub = reinterpret_cast<unsigned*>(s); s += sizeof(unsigned) * pw;
-    W.m = reinterpret_cast<int*>(s);        s += sizeof(int) * P.nx;
-    W.bs = reinterpret_cast<float*>(s);     s += sizeof(float) * P.nx;
-    W.wq = reinterpret_cast<float*>(s);     s += sizeof(float) * P.n_pad;
-    W.ys = reinterpret_cast<float*>(s);     s += sizeof(float) * P.n_pad;
-    W.qs = reinterpret_cast<float*>(s);
-  }
-  W.b = P.scratch + (size_t)blockIdx.x * 3 * P.p;
-  W.xv = W.b + P.p;
-  W.ga = W.xv + P.p;
+  W.gb = P.scratch + (size_t)blockIdx.x * scratch_stride(P.p);
 
   const float pmin = 1e-9f;
   const float fmax_ = logf(1.f / pmin - 1.f), fmin_ = -fmax_;
   const float vmin = (1.f + pmin) * pmin * (1.f - pmin);
   const float bta = P.alpha, omb = 1.f - bta;
 
-  for (int rep = blockIdx.x; rep < P.B; rep += gridDim.x) {
+  // The first gridDim.x replicates are taken by block index; every warp that finishes one draws the next from a global
+  // counter, so fits that need more passes do not leave the other warps of the last wave idle.
+  for (int rep = blockIdx.x; rep < P.B;) {
+    [[maybe_unused]] long long t_ph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    [[maybe_unused]] long long t_last = PROF ? clock64() : 0;
     // ------------------------------------------------------------------ set-up
     const float* wsrc = P.w + (size_t)rep * P.n_pad;
     const float* ysrc = P.y + (size_t)rep * P.y_stride;
@@ -284,8 +359,8 @@ lognet_path_kernel(const LognetParams P) {
       const int i = lane + 32 * j;
       const float wi = sw > 0.f ? wsrc[i] / sw : 0.f;
       const float yi = ysrc[i];
-      W.wq[i] = wi;
-      W.ys[i] = yi;
+      W.wq()[i] = wi;
+      W.ys()[i] = yi;
       q0 = fmaf(wi, yi, q0);
       if (wi > 0.f && i < first_i) first_i = i;
     }
@@ -295,7 +370,7 @@ lognet_path_kernel(const LognetParams P) {
     if (!(sw > 0.f)) jerr = 10000;
     else if (q0 <= pmin) jerr = 8001;
     else if (q0 >= 1.f - pmin) jerr = 9001;
-    for (int wd = lane; wd < pw; wd += 32) { W.ixx[wd] = 0u; W.inm[wd] = 0u; W.jub[wd] = 0u; }
+    for (int wd = lane; wd < pw; wd += 32) { W.ixx()[wd] = 0u; W.inm()[wd] = 0u; W.jub()[wd] = 0u; }
     __syncwarp();
 
     float dev0 = 0.f, dev1 = 0.f, shr = 0.f;
@@ -310,10 +385,10 @@ lognet_path_kernel(const LognetParams P) {
 #pragma unroll
       for (int j = 0; j < NPL; ++j) {
         const int i = lane + 32 * j;
-        const float wi = W.wq[i], yi = W.ys[i];
+        const float wi = W.wq()[i], yi = W.ys()[i];
         W.v[j] = vi * wi;
         W.r[j] = wi * (yi - q0);
-        W.qs[i] = q0;
+        W.qs()[i] = q0;
         if (yi > 0.f) dacc += wi * yi * logf(yi);
         if (yi < 1.f) dacc += wi * (1.f - yi) * logf(1.f - yi);
       }
@@ -339,7 +414,7 @@ lognet_path_kernel(const LognetParams P) {
           float g = 0.f, s2 = 0.f;
 #pragma unroll
           for (int j = 0; j < NPL; ++j) {
-            const float wi = W.wq[lane + 32 * j];
+            const float wi = W.wq()[lane + 32 * j];
             differs |= (wi > 0.f) && (x[j] != xf);
             g = fmaf(W.r[j], x[j], g);
             s2 = fmaf(wi * x[j], x[j], s2);
@@ -349,18 +424,19 @@ lognet_path_kernel(const LognetParams P) {
           if (P.kopt > 0) s2 = warp_sum(s2);
           if (usable) usable_bits |= 1u << kk;
           if (lane == 0) {
-            W.b[k] = 0.f;
-            W.ga[k] = usable ? fabsf(g) : 0.f;
-            W.xv[k] = (P.kopt > 0 && usable) ? 0.25f * s2 : 0.f;
+            W.b(k) = 0.f;
+            W.ga(k) = usable ? fabsf(g) : 0.f;
+            W.xv(k) = (P.kopt > 0 && usable) ? 0.25f * s2 : 0.f;
           }
         }
-        if (lane == 0) W.jub[k0 >> 5] = usable_bits;
+        if (lane == 0) W.jub()[k0 >> 5] = usable_bits;
       }
       __syncwarp();
     } else if (lane == 0) {
       P.nulldev_out[rep] = 0.f;
     }
 
+    PROF_MARK(0);
     // ------------------------------------------------------------------ lambda path
     float al = 0.f;
     bool stop = jerr != 0;
@@ -372,57 +448,58 @@ lognet_path_kernel(const LognetParams P) {
       for (int wd = 0; wd < pw; ++wd) {
         const int k = (wd << 5) + lane;
         bool add = false;
-        if (k < P.p) add = !W.bit(W.ixx, k) && W.bit(W.jub, k) && W.ga[k] > tlam * W.vpk(k);
+        if (k < P.p) add = !W.bit(W.ixx(), k) && W.bit(W.jub(), k) && W.ga(k) > tlam * W.vpk(k);
         const unsigned bits = __ballot_sync(FULL, add);
-        if (bits && lane == 0) W.ixx[wd] |= bits;
+        if (bits && lane == 0) W.ixx()[wd] |= bits;
       }
       __syncwarp();
 
+      PROF_MARK(1);
       bool overflow = false, done = false;
       while (!done) {                      // re-entered when the KKT check admits new features
         while (true) {                     // IRLS iterations
           if (W.nlp > P.maxit) { jerr = -(ilm + 1); stop = true; done = true; break; }
           const float b0s = W.b0;
-          for (int l = lane; l < W.nin; l += 32) W.bs[l] = W.b[W.m[l]];
+          for (int l = lane; l < W.nin; l += 32) W.bs()[l] = W.b(W.m()[l]);
           __syncwarp();
           if (P.kopt == 0) {
-            for (int wd = 0; wd < pw; ++wd) {
-              unsigned bits = W.ixx[wd];
-              while (bits) {
-                int kk[4];
-                int c = 0;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  kk[q] = bits ? (wd << 5) + __ffs(bits) - 1 : -1;
-                  if (bits) { bits &= bits - 1; ++c; }
-                }
-                float sacc[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  sacc[q] = 0.f;
-                  if (q < c) {
-                    float x[NPL];
-                    W.load_col(kk[q], x);        // these columns are swept next: keep them in L1
-#pragma unroll
-                    for (int j = 0; j < NPL; ++j) sacc[q] = fmaf(W.v[j] * x[j], x[j], sacc[q]);
-                  }
-                }
-                warp_sum4(sacc);
-                if (lane == 0) {
-#pragma unroll
-                  for (int q = 0; q < 4; ++q)
-                    if (q < c) W.xv[kk[q]] = sacc[q];
-                }
+            // curvature of every screened feature at the new weights, sixteen at a time (see warp_sum16_transposed)
+            int wd = 0, np = 0;
+            unsigned bits = 0u;
+            bool more = true;
+            while (more) {
+              while (np < 16) {
+                while (bits == 0u && wd < pw) bits = W.ixx()[wd++];
+                if (bits == 0u) { more = false; break; }
+                if (lane == 0) W.pend()[np] = ((wd - 1) << 5) + __ffs(bits) - 1;
+                bits &= bits - 1;
+                ++np;
               }
+              if (np == 0) break;
+              __syncwarp();
+              float acc[16];
+#pragma unroll
+              for (int q = 0; q < 16; ++q) {       // unconditional loads (clamped slot): see sweep_screened
+                float x[NPL];
+                W.load_col(W.pend()[min(q, np - 1)], x);
+                acc[q] = 0.f;
+#pragma unroll
+                for (int j = 0; j < NPL; ++j) acc[q] = fmaf(W.v[j] * x[j], x[j], acc[q]);
+              }
+              const float sx = warp_sum16_transposed(acc, lane);
+              if (lane < np) W.xv(W.pend()[lane]) = sx;
+              __syncwarp();
+              np = 0;
             }
-            __syncwarp();
           }
+          PROF_MARK(2);
           bool fail = false;
           while (true) {                   // full sweep, then active-set sweeps to convergence
             ++W.nlp;
             float dlx = 0.f;
             if (!W.sweep_screened(al1, al2, dlx)) { overflow = true; break; }
             W.intercept_step(dlx);
+            PROF_MARK(3);
             if (dlx < shr) break;
             if (W.nlp > P.maxit) { fail = true; break; }
             while (true) {
@@ -433,6 +510,7 @@ lognet_path_kernel(const LognetParams P) {
               if (dlx < shr) break;
               if (W.nlp > P.maxit) { fail = true; break; }
             }
+            PROF_MARK(4);
             if (fail) break;
           }
           if (fail) { jerr = -(ilm + 1); stop = true; done = true; break; }
@@ -444,54 +522,50 @@ lognet_path_kernel(const LognetParams P) {
           if (!ix) {
             bool mine = false;
             for (int l = lane; l < W.nin; l += 32) {
-              const int k = W.m[l];
-              const float d = W.b[k] - W.bs[l];
-              mine |= W.xv[k] * d * d > shr;
+              const int k = W.m()[l];
+              const float d = W.b(k) - W.bs()[l];
+              mine |= W.xv(k) * d * d > shr;
             }
             ix = __any_sync(FULL, mine);
           }
           if (ix) continue;
+          PROF_MARK(5);
           // KKT check over the features that are not screened in
           bool added = false;
           if (W.version != W.ga_version) {
             for (int k0 = 0; k0 < P.p; k0 += 32) {
-              const unsigned skip = W.ixx[k0 >> 5], use = W.jub[k0 >> 5];
+              const unsigned skip = W.ixx()[k0 >> 5], use = W.jub()[k0 >> 5];
               unsigned todo = use & ~skip;
               unsigned newbits = 0u;
-              while (todo) {
-                // four independent gradients at a time: their column loads and butterfly reductions overlap
-                int kk[4];
-                int c = 0;
+              if (todo == 0u) continue;
+              // sixteen gradients per round: independent column loads, one transposed reduction (16 shuffles for all of
+              // them), then lane q owns feature q - coalesced store of |g| and one ballot for the threshold test
+#pragma unroll 1
+              for (int h = 0; h < 2; ++h) {
+                const unsigned th = (todo >> (16 * h)) & 0xffffu;
+                if (th == 0u) continue;
+                const int kb = k0 + 16 * h;
+                float acc[16];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  kk[q] = todo ? __ffs(todo) - 1 : -1;
-                  if (todo) { todo &= todo - 1; ++c; }
-                }
-                float g[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  g[q] = 0.f;
-                  if (q < c) {
+                for (int q = 0; q < 16; ++q) {
+                  acc[q] = 0.f;
+                  if ((th >> q) & 1u) {
                     float x[NPL];
-                    W.load_col_stream(k0 + kk[q], x);
+                    W.load_col_stream(kb + q, x);
 #pragma unroll
-                    for (int j = 0; j < NPL; ++j) g[q] = fmaf(W.r[j], x[j], g[q]);
+                    for (int j = 0; j < NPL; ++j) acc[q] = fmaf(W.r[j], x[j], acc[q]);
                   }
                 }
-                warp_sum4(g);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  if (q < c) {
-                    const int k = k0 + kk[q];
-                    const float ag = fabsf(g[q]);
-                    if (lane == 0) W.ga[k] = ag;
-                    if (ag > al1 * W.vpk(k)) newbits |= 1u << kk[q];
-                  }
-                }
+                const float ag = fabsf(warp_sum16_transposed(acc, lane));
+                const int q = lane & 15, k = kb + q;
+                const bool valid = ((th >> q) & 1u) != 0u;
+                if (valid && lane < 16) W.ga(k) = ag;
+                const bool add = valid && ag > al1 * (valid ? W.vpk(k) : 1.f);
+                newbits |= (__ballot_sync(FULL, add) & 0xffffu) << (16 * h);
               }
               if (newbits) {
                 added = true;
-                if (lane == 0) W.ixx[k0 >> 5] |= newbits;
+                if (lane == 0) W.ixx()[k0 >> 5] |= newbits;
               }
             }
             W.ga_version = W.version;
@@ -500,15 +574,16 @@ lognet_path_kernel(const LognetParams P) {
             for (int wd = 0; wd < pw; ++wd) {
               const int k = (wd << 5) + lane;
               bool add = false;
-              if (k < P.p) add = !W.bit(W.ixx, k) && W.bit(W.jub, k) && W.ga[k] > al1 * W.vpk(k);
+              if (k < P.p) add = !W.bit(W.ixx(), k) && W.bit(W.jub(), k) && W.ga(k) > al1 * W.vpk(k);
               const unsigned bits = __ballot_sync(FULL, add);
               if (bits) {
                 added = true;
-                if (lane == 0) W.ixx[wd] |= bits;
+                if (lane == 0) W.ixx()[wd] |= bits;
               }
             }
           }
           __syncwarp();
+          PROF_MARK(6);
           if (!added) done = true;
           break;
         }
@@ -519,8 +594,8 @@ lognet_path_kernel(const LognetParams P) {
       // ---- record this lambda
       const size_t row = (size_t)rep * P.nlam + ilm;
       for (int l = lane; l < W.nin; l += 32) {
-        const int k = W.m[l];
-        const float bk = W.b[k];
+        const int k = W.m()[l];
+        const float bk = W.b(k);
         if (P.ca_out) P.ca_out[row * P.nx + l] = bk;
         // stability selection: how many replicates of this batch picked gene k at this lambda
         if (P.freq_out && bk != 0.f) atomicAdd(P.freq_out + (size_t)ilm * P.p + k, 1.f);
@@ -529,9 +604,9 @@ lognet_path_kernel(const LognetParams P) {
 #pragma unroll
       for (int j = 0; j < NPL; ++j) {
         const int i = lane + 32 * j;
-        const float pp = fminf(fmaxf(pmin, W.qs[i]), 1.f - pmin);
-        const float yi = W.ys[i];
-        dacc -= W.wq[i] * (yi * logf(pp) + (1.f - yi) * logf(1.f - pp));
+        const float pp = fminf(fmaxf(pmin, W.qs()[i]), 1.f - pmin);
+        const float yi = W.ys()[i];
+        dacc -= W.wq()[i] * (yi * logf(pp) + (1.f - yi) * logf(1.f - pp));
       }
       dacc = warp_sum(dacc);
       if (lane == 0) {
@@ -545,8 +620,8 @@ lognet_path_kernel(const LognetParams P) {
 #pragma unroll
         for (int j = 0; j < NPL; ++j) eta[j] = W.b0;
         for (int l = 0; l < W.nin; ++l) {
-          const int k = W.m[l];
-          const float bk = W.b[k];
+          const int k = W.m()[l];
+          const float bk = W.b(k);
           float x[NPL];
           W.load_col(k, x);
 #pragma unroll
@@ -555,16 +630,24 @@ lognet_path_kernel(const LognetParams P) {
 #pragma unroll
         for (int j = 0; j < NPL; ++j) P.eta_out[row * P.n_pad + lane + 32 * j] = eta[j];
       }
+      PROF_MARK(7);
       lmu = ilm + 1;
       if (W.xmz <= vmin) break;
     }
     if (P.m_out)
-      for (int l = lane; l < W.nin; l += 32) P.m_out[(size_t)rep * P.nx + l] = W.m[l];
+      for (int l = lane; l < W.nin; l += 32) P.m_out[(size_t)rep * P.nx + l] = W.m()[l];
+    if constexpr (PROF) {
+      if (lane == 0)
+        for (int i = 0; i < 8; ++i) P.prof_out[(size_t)rep * 8 + i] = t_ph[i];
+    }
     if (lane == 0) {
       P.npasses_out[rep] = W.nlp;
       P.lmu_out[rep] = lmu;
       P.jerr_out[rep] = jerr;
     }
+    int nxt = 0;
+    if (lane == 0) nxt = (int)(atomicAdd(P.next_rep, 1u) + gridDim.x);
+    rep = __shfl_sync(FULL, nxt, 0);
     __syncwarp();
   }
 }
@@ -579,12 +662,12 @@ int launch(const LognetParams& P, int grid, size_t smem, cudaStream_t st) {
 
 size_t smem_bytes(int p, int nx, int n_pad) {
   const size_t pw = (p + 31) / 32;
-  return 3 * pw * sizeof(unsigned) + (size_t)nx * (sizeof(int) + sizeof(float)) + 3 * (size_t)n_pad * sizeof(float);
+  return 3 * pw * sizeof(unsigned) + (size_t)nx * (sizeof(int) + sizeof(float)) + 16 * sizeof(int) + 3 * (size_t)n_pad * sizeof(float);
 }
 
 int resident_warps(int n_pad) {
   const int npl = n_pad / 32;
-  const int per_sm = npl <= 4 ? 28 : (npl <= 8 ? 20 : 12);
+  const int per_sm = npl <= 4 ? CML_LASSO_WARPS_SMALL : (npl <= 8 ? 20 : 12);
   return per_sm * sm_count();
 }
 
@@ -603,7 +686,7 @@ int cml_lognet_n_pad(int n) {
 int cml_lognet_grid(int B, int n_pad) { return B < cml::resident_warps(n_pad) ? B : cml::resident_warps(n_pad); }
 
 size_t cml_lognet_scratch_bytes(int B, int n_pad, int p) {
-  return (size_t)cml_lognet_grid(B, n_pad) * 3 * (size_t)p * sizeof(float);
+  return (size_t)cml_lognet_grid(B, n_pad) * cml::scratch_stride(p) * sizeof(float) + 256;   // + the work counter
 }
 
 int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
@@ -622,10 +705,12 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
   const size_t smem = smem_bytes(p, nx, n_pad);
   CML_REQUIRE(smem <= 48 * 1024, CML_E2BIG, "cml_lognet_path: p=%d nx=%d n_pad=%d needs %zu B shared memory per warp (max 48 KB)",
               p, nx, n_pad, smem);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned* counter = reinterpret_cast<unsigned*>(static_cast<float*>(scratch) + (size_t)grid * scratch_stride(p));
+  CML_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), st));
   LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, ju, ju_stride, vp, lam, alpha, thresh, intercept,
                  kopt, maxit, static_cast<float*>(scratch), m_out, ca_out, kin_out, a0_out, dev_out, eta_out,
-                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out};
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out, nullptr, counter};
   switch (n_pad / 32) {
     case 1: return launch<1>(P, grid, smem, st);
     case 2: return launch<2>(P, grid, smem, st);
@@ -641,6 +726,39 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
   }
   set_error("cml_lognet_path: unsupported n_pad %d", n_pad);
   return CML_EINVAL;
+}
+
+// Tracing build of the same kernel (n_pad <= 128): prof_out [B][8] receives the clock64() cycles replicate b spent in
+// 0 set-up pass, 1 strong-rule screening, 2 curvature (xv) refresh, 3 sweeps over the screened set, 4 active-set sweeps,
+// 5 IRLS refresh + convergence test, 6 KKT pass, 7 recording the lambda.  grid_limit > 0 caps the number of warps
+// (e.g. one per SM) to see latency without co-resident fits.
+int cml_lognet_path_profile(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
+                            long long y_stride, const float* w, const float* lam, float alpha, float thresh, int intercept,
+                            int kopt, int maxit, void* scratch, size_t scratch_bytes, int* kin_out, float* a0_out,
+                            float* dev_out, float* nulldev_out, int* npasses_out, int* lmu_out, int* jerr_out,
+                            long long* prof_out, int grid_limit, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(B > 0 && n > 0 && p > 0 && nlam > 0 && nx > 0 && prof_out, CML_EINVAL, "cml_lognet_path_profile: empty problem");
+  CML_REQUIRE(n_pad % 32 == 0 && n_pad >= n && n_pad <= 128, CML_EINVAL, "cml_lognet_path_profile: n_pad=%d (supported: 32..128)", n_pad);
+  int grid = cml_lognet_grid(B, n_pad);
+  if (grid_limit > 0 && grid_limit < grid) grid = grid_limit;
+  CML_REQUIRE(scratch_bytes >= (size_t)grid * scratch_stride(p) * sizeof(float) + 256, CML_EINVAL, "cml_lognet_path_profile: scratch too small");
+  const size_t smem = smem_bytes(p, nx, n_pad);
+  CML_REQUIRE(smem <= 48 * 1024, CML_E2BIG, "cml_lognet_path_profile: %zu B shared memory per warp (max 48 KB)", smem);
+  LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, nullptr, 0, nullptr, lam, alpha, thresh, intercept,
+                 kopt, maxit, static_cast<float*>(scratch), nullptr, nullptr, kin_out, a0_out, dev_out, nullptr,
+                 nullptr, nulldev_out, npasses_out, lmu_out, jerr_out, prof_out, nullptr};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  P.next_rep = reinterpret_cast<unsigned*>(static_cast<float*>(scratch) + (size_t)grid * scratch_stride(p));
+  CML_CUDA(cudaMemsetAsync(P.next_rep, 0, sizeof(unsigned), st));
+  switch (n_pad / 32) {
+    case 1: lognet_path_kernel<1, true><<<grid, 32, smem, st>>>(P); break;
+    case 2: lognet_path_kernel<2, true><<<grid, 32, smem, st>>>(P); break;
+    case 3: lognet_path_kernel<3, true><<<grid, 32, smem, st>>>(P); break;
+    default: lognet_path_kernel<4, true><<<grid, 32, smem, st>>>(P); break;
+  }
+  CML_LAUNCH_CHECK();
+  return 0;
 }
 
 }  // extern "C"
@@ -659,9 +777,9 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
 //
 // Consequences the caller must know:
 //   * Capacity.  One resident warp needs 3*p floats.  The number of replicates fitted concurrently is
-//     floor(kLognetStaticBytes / (12*p)) (at most the usual resident-warp count); further replicates of the
+//     floor((kLognetStaticBytes - 256) / (12*p)) (at most the usual resident-warp count); further replicates of the
 //     batch are taken in turn by the same warps, so any B works but throughput drops as p grows.
-//     p > kLognetStaticBytes/12 (699,050 genes) cannot run at all and is rejected with CML_E2BIG.
+//     p > (kLognetStaticBytes - 256)/12 (699,029 genes) cannot run at all and is rejected with CML_E2BIG.
 //   * Sharing.  Every call on a device uses the SAME array.  Two calls that may execute at the same time
 //     on one GPU (different streams, different host threads) would overwrite each other's coefficients:
 //     serialise them.  Calls on different GPUs are independent (each device has its own copy).
@@ -678,6 +796,7 @@ namespace {
 
 constexpr size_t kLognetStaticBytes = 8u << 20;                         // 8 MiB per GPU
 constexpr size_t kLognetStaticFloats = kLognetStaticBytes / sizeof(float);
+constexpr size_t kLognetStaticUsable = kLognetStaticFloats - 64;       // the last 256 bytes hold the kernel's work counter
 static __device__ __align__(256) float g_lognet_static_scratch[kLognetStaticFloats];
 
 constexpr int kMaxDevices = 64;
@@ -715,11 +834,11 @@ int cml_lognet_path_static(int B, int n, int n_pad, int p, int nlam, int nx, con
                            int* jerr_out, void* stream) {
   using namespace cml;
   CML_REQUIRE(B > 0 && n > 0 && p > 0 && nlam > 0 && nx > 0, CML_EINVAL, "cml_lognet_path_static: empty problem");
-  const size_t per_warp = 3 * static_cast<size_t>(p);
-  CML_REQUIRE(per_warp <= kLognetStaticFloats, CML_E2BIG,
+  const size_t per_warp = scratch_stride(p);
+  CML_REQUIRE(per_warp <= kLognetStaticUsable, CML_E2BIG,
               "cml_lognet_path_static: p=%d genes need %zu bytes of work space per replicate but the built-in array holds "
               "%zu bytes (max p = %zu); use cml_lognet_path with caller-provided scratch",
-              p, per_warp * sizeof(float), kLognetStaticBytes, kLognetStaticFloats / 3);
+              p, per_warp * sizeof(float), kLognetStaticBytes, kLognetStaticUsable / 3);
   CML_REQUIRE(n_pad == cml_lognet_n_pad(n) || (n_pad % 32 == 0 && n_pad >= n && cml_lognet_n_pad(n_pad) == n_pad),
               CML_EINVAL, "cml_lognet_path_static: n_pad=%d is not a supported padded size for n=%d (max 1024)", n_pad, n);
   const size_t smem = smem_bytes(p, nx, n_pad);
@@ -728,13 +847,15 @@ int cml_lognet_path_static(int B, int n, int n_pad, int p, int nlam, int nx, con
   float* slab = nullptr;
   const int rc = lognet_static_scratch(&slab);
   if (rc) return rc;
-  const size_t fit = kLognetStaticFloats / per_warp;                    // warps whose slabs fit side by side
+  const size_t fit = kLognetStaticUsable / per_warp;                    // warps whose slabs fit side by side
   int grid = cml_lognet_grid(B, n_pad);
   if (static_cast<size_t>(grid) > fit) grid = static_cast<int>(fit);
   LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, ju, ju_stride, vp, lam, alpha, thresh, intercept,
                  kopt, maxit, slab, m_out, ca_out, kin_out, a0_out, dev_out, eta_out,
-                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out};
+                 freq_out, nulldev_out, npasses_out, lmu_out, jerr_out, nullptr,
+                 reinterpret_cast<unsigned*>(slab + kLognetStaticUsable)};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CML_CUDA(cudaMemsetAsync(P.next_rep, 0, sizeof(unsigned), st));     // a memset node, not an allocation
   switch (n_pad / 32) {
     case 1: return launch<1>(P, grid, smem, st);
     case 2: return launch<2>(P, grid, smem, st);

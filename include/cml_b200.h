@@ -58,7 +58,7 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
  * cml_lognet_path minus (scratch, scratch_bytes): the per-warp work space is a fixed array of
  * cml_lognet_static_scratch_bytes() (8 MiB) inside the library image, present on every GPU that loads the
  * library until the process exits.  Nothing is allocated or freed by the call.
- *   - limit: 12*p bytes per concurrently fitted replicate must fit, so p <= 699,050 genes; larger p returns
+ *   - limit: 12*p bytes per concurrently fitted replicate must fit, so p <= 699,029 genes; larger p returns
  *     CML_E2BIG (7) with a message.  Concurrency is min(resident warps, 8 MiB / (12*p)); any B is accepted.
  *   - the array is shared by all calls on a device and keeps the previous call's contents; the solver
  *     overwrites every word before reading it, so nothing is cleared - but two calls that can run at the
