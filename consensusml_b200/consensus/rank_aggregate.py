@@ -52,7 +52,7 @@ def aggregate(importances: Dict[str, Sequence[float]], gene_ids: Sequence[str], 
               top: Optional[int] = None) -> pd.DataFrame:
     """Consensus table: one row per gene, per-model ranks, mean rank, Borda, RRA rho; sorted by ``method``."""
     names = list(importances)
-    imp = torch.stack([torch.as_tensor(np.asarray(importances[n], dtype=np.float64)) for n in names], 1)
+    imp = torch.stack([torch.as_tensor(np.array(importances[n], dtype=np.float64)) for n in names], 1)
     ranks = rank_matrix(imp)
     df = pd.DataFrame({f"rank_{n}": ranks[:, j].numpy() for j, n in enumerate(names)}, index=list(gene_ids))
     df["mean_rank"] = mean_rank(ranks).numpy()

@@ -48,5 +48,6 @@ def annotate(gene_ids: Iterable[str]) -> pd.DataFrame:
     if missing.any():
         fill = out[missing.values].merge(ens2, on="Gene_ID", how="left")
         for c in ["Gene.name", "Chromosome.scaffold.name", "Gene.start..bp.", "Gene.end..bp.", "Karyotype.band"]:
-            merged.loc[missing.values, c] = fill[c].values
+            merged[c] = merged[c].astype(object)             # mixed str / number / missing: keep pandas from coercing
+            merged.loc[missing.values, c] = fill[c].astype(object).values
     return merged

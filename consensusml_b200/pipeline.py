@@ -59,7 +59,7 @@ def cohort_from_counts(counts: torch.Tensor, gene_ids, sample_ids, group: np.nda
     return Cohort(assay.double(), ids, list(sample_ids), rd, cd, {"n_deg": len(ids), "df_prior": de.df_prior})
 
 
-def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = None) -> Dict:
+def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = None, return_details: bool = False) -> Dict:
     """Run the ensemble + consensus on ``cohort`` (default: the bundled TARGET-AML DEG cohort).  Returns a summary dict
     and writes ``standouttable.csv``, the lasso gene CSV, ``consensus_rank.csv`` and the report dumps."""
     dev = resolve_device(cfg)
@@ -74,6 +74,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
     genes = cohort.gene_ids
     st = CS.StandTable(cohort)
     importances: Dict[str, np.ndarray] = {}
+    scores: Dict[str, np.ndarray] = {}            # test-set class-1 probabilities per model (for one-vs-rest voting)
     summary: Dict[str, Dict] = {}
     data_key = f"{cohort.n_genes}x{cohort.n_samples}"
 
@@ -117,9 +118,11 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
                 tag = f"{nt // 1000}k" if nt % 1000 == 0 else str(nt)
                 st.add(f"rfnb_{tag}_MeanDecNodeImp", rf.importance_.cpu().numpy())
                 pred = rf.predict(xte)
+                proba = rf.predict_proba(xte)
                 summary[f"rf_{tag}"] = {"oob_error": rf.oob_error_, "test_error": float((pred != yte.long()).float().mean()),
-                                        "auc": M.auc(rf.predict_proba(xte), yte)}
+                                        "auc": M.auc(proba, yte)}
                 importances["rf"] = rf.importance_.cpu().numpy()
+                scores["rf"] = proba.float().cpu().numpy()
 
     if cfg.gbm.enabled:
         with log.stage("gbm"):
@@ -131,6 +134,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
                 summary[f"xgb{i}"] = {"train_error": gb.train_error_[-1], "test_error": float(((pr > 0.5).float() != yte).float().mean()),
                                       "auc": M.auc(pr, yte), "n_genes": int((gb.importance_["gain"] > 0).sum())}
                 importances["xgb"] = gb.importance_["gain"].cpu().numpy()
+                scores["xgb"] = pr.float().cpu().numpy()
 
     if cfg.mlp.enabled:
         with log.stage("mlp"):
@@ -156,4 +160,80 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
             R.write_all(os.path.join(out, "report"), {"volcano": R.volcano_data(rd["logFC"].to_numpy(float), rd["p.unadj"].to_numpy(float),
                                                                                   rd["p.adj.bh"].to_numpy(float), genes)})
     log.event("run_end", summary=summary)
+    if return_details:
+        return {"summary": summary, "importances": importances, "scores": scores, "rank": rank}
+    return summary
+
+
+def multiclass_cohort_from_counts(counts: torch.Tensor, gene_ids, sample_ids, label: np.ndarray, train_mask: np.ndarray, cfg: Config,
+                                  max_genes_per_class: int = 500, log: Optional[RunLog] = None) -> Cohort:
+    """Raw counts + integer class labels -> TMM log2-CPM restricted to the union of the one-vs-rest limma-voom DEGs
+    (training samples only; at most ``max_genes_per_class`` per class, by P value)."""
+    log = log or RunLog()
+    dev = counts.device
+    with log.stage("normalize", bytes_moved=float(counts.numel() * 4 * 3)):
+        norm = N.tmm_normalize(counts, cfg.normalize.min_cpm, cfg.normalize.min_samples, prior_count=cfg.normalize.prior_count)
+    kept_full = np.flatnonzero(norm.keep.cpu().numpy())
+    pos = {g: i for i, g in enumerate(kept_full)}
+    tr = torch.as_tensor(np.flatnonzero(train_mask), device=dev)
+    ctr = counts[:, tr].contiguous()
+    chosen: Dict[int, int] = {}
+    with log.stage("voom_de_one_vs_rest"):
+        for c in np.unique(label):
+            de = DE.voom_de(ctr, (label[train_mask] == c).astype(np.int8), min_frac=cfg.de.min_frac, p_value=cfg.de.p_value,
+                            lfc=cfg.de.lfc, span=cfg.de.span)
+            for g in de.gene_index[de.deg_order][:max_genes_per_class]:
+                if g in pos:
+                    chosen.setdefault(int(g), int(c))
+    rows = [pos[g] for g in sorted(chosen)]
+    ids = [gene_ids[g] for g in sorted(chosen)]
+    assay = norm.logcpm[torch.as_tensor(rows, device=dev)]
+    rd = pd.DataFrame({"ensembl_gene_id": [i.split(".")[0] for i in ids], "first_class": [chosen[g] for g in sorted(chosen)]})
+    cd = pd.DataFrame({"class": label.astype(int), "deg.risk": 0, "exptset.seahack": np.where(train_mask, "train", "test")})
+    return Cohort(assay.double(), ids, list(sample_ids), rd, cd, {"n_deg": len(ids)})
+
+
+def run_multiclass(cfg: Config, cohort: Cohort, class_column: str = "class", class_names: Optional[Dict[int, str]] = None,
+                   log: Optional[RunLog] = None) -> Dict:
+    """Pan-cancer style multiclass run (BASELINE.json config 3): the binary ensemble is fitted one-vs-rest for every
+    class, each class gets its own standard table / consensus ranking under ``out_dir/<class>/``, the per-class rankings
+    are aggregated into one pan-class consensus list, and samples are assigned to the class whose one-vs-rest models
+    give the highest mean probability.  (The reference's notebooks only ever fit the two-group AML risk model; its
+    pan-cancer matrix is used for normalisation checks - Normalization_and_Batch_Effect_Investigation.Rmd:49-66.)"""
+    import copy
+    out = cfg.io.out_dir
+    log = log or RunLog(os.path.join(out, "run.jsonl"))
+    labels = cohort.col_data[class_column].to_numpy()
+    classes = sorted(np.unique(labels).tolist())
+    test_mask = (cohort.col_data["exptset.seahack"] == "test").to_numpy()
+    per_class, ranks, votes = {}, {}, []
+    for c in classes:
+        name = (class_names or {}).get(c, str(c))
+        sub = copy.copy(cohort)
+        sub.col_data = cohort.col_data.copy()
+        sub.col_data["deg.risk"] = (labels == c).astype(int)
+        cfg_c = copy.deepcopy(cfg)
+        cfg_c.io.out_dir = os.path.join(out, f"class_{name}")
+        with log.stage(f"one_vs_rest[{name}]"):
+            det = run(cfg_c, sub, log=RunLog(os.path.join(cfg_c.io.out_dir, "run.jsonl")), return_details=True)
+        per_class[name] = det["summary"]
+        if det["rank"] is not None:
+            ranks[name] = det["rank"]
+        if det["scores"]:
+            votes.append(np.mean(np.stack(list(det["scores"].values())), 0))
+    summary: Dict = {"classes": [(class_names or {}).get(c, str(c)) for c in classes], "per_class": per_class}
+    if votes:
+        pred = np.asarray(classes)[np.argmax(np.stack(votes, 1), 1)]
+        truth = labels[test_mask]
+        summary["accuracy"] = float((pred == truth).mean())
+        summary["confusion"] = [[int(((truth == a) & (pred == b)).sum()) for b in classes] for a in classes]
+    if ranks:
+        # a gene's pan-class score is its best (smallest) consensus rank over the classes; ties broken by the mean rank
+        cols = {n: r["mean_rank"] if "mean_rank" in r else r.iloc[:, 0] for n, r in ranks.items()}
+        tab = pd.DataFrame({n: v.rank(method="average") for n, v in cols.items()})
+        tab["best_rank"], tab["mean_rank"] = tab.min(axis=1), tab.mean(axis=1)
+        tab = tab.sort_values(["best_rank", "mean_rank"])
+        tab.to_csv(os.path.join(out, "consensus_rank_multiclass.csv"))
+        summary["top"] = tab.index[: cfg.consensus.top].tolist()
+    log.event("multiclass_end", accuracy=summary.get("accuracy"), n_classes=len(classes))
     return summary

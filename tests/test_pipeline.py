@@ -80,3 +80,20 @@ def test_cli_config_and_lasso(tmp_path, capsys):
     assert main(["lasso", "device=cpu", "io.out_dir=" + str(tmp_path)]) == 0
     out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
     assert out["genes"] == 13 and out["confusion"] == [[21, 2], [1, 20]]
+
+
+def test_multiclass_one_vs_rest_cpu(tmp_path):
+    """Pan-cancer style run (BASELINE.json config 3) on a small synthetic 3-class count matrix."""
+    from consensusml_b200.io.synthetic import nb_counts_multiclass
+    c, lab = nb_counts_multiclass(3000, (30, 28, 26), n_de_per_class=150, seed=4)
+    train = np.arange(lab.size) % 3 != 0
+    cfg = C.load(None, ["io.out_dir=" + str(tmp_path), "device=cpu", "lasso.exclusion_reps=1", "lasso.nfolds=4", "rf.n_trees=[40]",
+                        "rf.proximity=false", 'gbm.reps=[{"max_depth": 2, "nrounds": 3}]', "svm.enabled=false", "mlp.enabled=false"])
+    co = pipeline.multiclass_cohort_from_counts(torch.from_numpy(c), [f"ENSG{i:011d}.1" for i in range(3000)],
+                                                [f"s{i}" for i in range(lab.size)], lab, train, cfg, max_genes_per_class=60)
+    assert 30 <= co.n_genes <= 180
+    s = pipeline.run_multiclass(cfg, co, class_names={0: "AML", 1: "NBL", 2: "WT"})
+    assert s["classes"] == ["AML", "NBL", "WT"] and s["accuracy"] >= 0.85
+    assert np.asarray(s["confusion"]).sum() == int((~train).sum())
+    assert len(s["top"]) > 0 and os.path.exists(tmp_path / "consensus_rank_multiclass.csv")
+    assert os.path.exists(tmp_path / "class_AML" / "standouttable.csv")
