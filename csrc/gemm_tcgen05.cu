@@ -288,7 +288,7 @@ __device__ __forceinline__ void epilogue_tile_impl(const GemmParams& P, uint32_t
       }
     }
     const int ccol = src * P.rows_per_src + cs;
-    if (P.c_tma && nvalid == 32) {
+    if (P.c_tma && nvalid == 32 && (ccol & 3) == 0) {       // TMA stores need a 16-byte aligned start in global memory
       constexpr uint32_t buf = 0;
       if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous store has left the buffer
       __syncwarp();

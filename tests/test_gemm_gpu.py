@@ -103,3 +103,33 @@ def test_cta_pair_multi_source():
     finally:
         G.set_variant(0)
     assert (split - ref[:, :1500]).abs().max().item() < 1e-4
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("n_src,rows,k,rank", [(8, 750, 2500, 3), (4, 1024, 512, 0), (2, 300, 200, 1)])
+def test_staged_allgather_gemm_with_local_sources(n_src, rows, k, rank, variant):
+    """The fused all-gather -> GEMM with every 'peer' block living on this GPU: copier CTAs stage the blocks, GEMM CTAs
+    (single-CTA kernel or CTA pairs) consume tiles as their flags arrive.  Same kernel path as the multi-GPU run."""
+    g = torch.Generator().manual_seed(7)
+    a = torch.randn(rows, k, generator=g).cuda()
+    blocks = [torch.randn(rows, k, generator=g).cuda() for _ in range(n_src)]
+    blocks[rank] = a
+    ab, na = G.to_bf16_rows(a)
+    bb = [G.to_bf16_rows(b) for b in blocks]
+    ld = ab.shape[1]
+    n_total = n_src * rows
+    stage = torch.empty(n_total, ld, dtype=torch.bfloat16, device="cuda")
+    snorm = torch.empty(n_total, device="cuda")
+    from consensusml_b200 import _native
+    flags = torch.zeros(_native.cuda().cml_gemm_staged_flags(n_src, rows), dtype=torch.int32, device="cuda")
+    ref = torch.cat([ab.float() @ b.float().t() for b, _ in bb], 1)
+    d2 = (na[:, None] + torch.cat([nb for _, nb in bb])[None, :] - 2 * ref).clamp_min(0)
+    G.set_variant(variant)
+    try:
+        for epoch in (1, 2):
+            got = G.gemm_tn_staged(ab, [b.data_ptr() for b, _ in bb], n_total, rows, ld, stage, snorm, flags, epoch, rank,
+                                   epilogue=G.EPI_SQDIST, norm_a=na, peer_norm_ptrs=[nb.data_ptr() for _, nb in bb])
+            torch.cuda.synchronize()
+            assert (got - d2).abs().max().item() < 2e-3 * max(1.0, d2.abs().max().item())
+    finally:
+        G.set_variant(0)
