@@ -73,3 +73,18 @@ def test_fixed_split_reproduces_reference_flags(aml):
     out = CO.split_fixed(aml, tr, te, column="split2")
     assert (out.col_data["split2"].to_numpy() == aml.col_data["exptset.seahack"].to_numpy()).all()   # 93 / 44 after Unknown drop
     assert (out.col_data["split2"] == "train").sum() == 93
+
+
+def test_read_manifest_and_merge(tmp_path):
+    """GDC id-map CSV -> frame usable by api.clean.manifest_clinical_merge (GDC_Data_Download.Rmd:219-229, scripts/clean.py:1-18)."""
+    import pandas as pd
+    from consensusml_b200.api import clean
+    from consensusml_b200.io.counts import read_manifest
+    p = tmp_path / "manifest.csv"
+    pd.DataFrame({"file_id": ["f1", "f2", "f3"], "project.project_id": ["TARGET-AML", "TARGET-AML", "TARGET-NBL"],
+                  "entity_submitter_id": ["TARGET-20-PABCDE-09A-01R", "TARGET-20-PAXYZW-03A-01R", "TARGET-30-PAQQQQ-01A-01R"]}).to_csv(p, index=False)
+    man = read_manifest(str(p))
+    assert list(man.columns) == ["file_id", "project.project_id", "entity_submitter_id"] and len(man) == 3
+    clin = pd.DataFrame({"TARGET USI": ["TARGET-20-PABCDE", "TARGET-20-PAXYZW"], "Risk group": ["Low", "High"]})
+    merged = clean.manifest_clinical_merge(man, clin, "TARGET-AML")
+    assert len(merged) == 2 and set(merged["Risk group"]) == {"Low", "High"}
