@@ -50,6 +50,17 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
                     float* a0_out, float* dev_out, float* eta_out, float* freq_out, float* nulldev_out,
                     int* npasses_out, int* lmu_out, int* jerr_out, void* stream);
 
+/* Tracing build of the path kernel (n_pad <= 128, no feature mask / penalty factors / coefficient output): prof_out
+ * [B][8] receives the clock64() cycles replicate b spent in 0 set-up pass, 1 strong-rule screening, 2 curvature refresh,
+ * 3 sweeps over the screened set, 4 active-set sweeps, 5 IRLS refresh + convergence test, 6 KKT pass, 7 recording.
+ * grid_limit > 0 caps the number of resident warps (e.g. one per SM).  scratch as for cml_lognet_path.  The reference has
+ * no profiling hooks. */
+int cml_lognet_path_profile(int B, int n, int n_pad, int p, int nlam, int nx, const float* xt, const float* y,
+                            long long y_stride, const float* w, const float* lam, float alpha, float thresh, int intercept,
+                            int kopt, int maxit, void* scratch, size_t scratch_bytes, int* kin_out, float* a0_out,
+                            float* dev_out, float* nulldev_out, int* npasses_out, int* lmu_out, int* jerr_out,
+                            long long* prof_out, int grid_limit, void* stream);
+
 /* ---- allocation-free variant of cml_lognet_path -----------------------------------------------------
  * No counterpart in the reference (it has no device code and no memory management of its own).
  * For callers that may not create device memory when they need a fit: a plugin inside an application
@@ -198,6 +209,23 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
 int cml_hist_ft(int n_nodes, int nbins);
 int cml_split_score_gain(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
     unsigned long long* best, void* stream);
+
+/* ---- libcml_host.so (csrc/host): float64 CPU restatements and parsers ------------------------------------------ */
+/* glmnet lognet path, B replicates sharing xt [p][n] / y / lambda; outputs per replicate (see csrc/host/lognet_cpu.cpp). */
+int cml_host_lognet_path(int B, int n, int p, int nlam, const double* xt, const double* y, const double* w,
+                         const signed char* ju, const double* vp, const double* lam, double alpha, double thresh,
+                         int intercept, int kopt, int maxit, int nx, double* beta, double* a0, double* dev_ratio,
+                         int* df, double* nulldev, int* npasses, int* lmu, int* jerr);
+/* Visit counters of the calling thread since the last call: screened-sweep steps, active-sweep steps, KKT gradient
+ * evaluations, curvature evaluations, columns read by IRLS refreshes, IRLS iterations, active sweeps, screened sweeps. */
+void cml_host_lognet_counters(long long* out8);
+/* Per-sample count files -> gene x sample matrix (Cat_Expn_Data.r:7-49): scan the first file for the gene ids, read them
+ * back one by one, then parse all files in parallel (mmap) into out[genes][n_files]; status[f] = 0 or the negative line
+ * number of the first problem in file f. */
+long cml_host_counts_scan(const char* path, char sep, int skip_lines, int id_col, int val_col);
+int cml_host_counts_id(long i, char* buf, int cap);
+int cml_host_counts_concat(const char* const* paths, int n_files, char sep, int skip_lines, int id_col, int val_col,
+                           int* out, long n_genes, long* status, int n_threads);
 
 #ifdef __cplusplus
 }
