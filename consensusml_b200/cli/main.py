@@ -2,7 +2,10 @@
 
 The reference has no CLI - its entry points are "open the notebook and run the chunks" (SURVEY.md 1).  Commands:
 
-  run         the full ensemble + consensus pipeline (default cohort: bundled TARGET-AML)
+  run         the full ensemble + consensus pipeline (default cohort: bundled TARGET-AML; with --counts/--groups: normalise,
+              DE-prefilter and model your own two-group cohort, the Differential_Expression_and_Lasso.Rmd flow)
+  multiclass  one-vs-rest ensemble + pan-class consensus on a counts CSV with a multi-level group column
+  concat      per-sample HTSeq count files -> one genes x samples counts CSV (Cat_Expn_Data.r)
   lasso       the reference's headline model only (runLasso + gene CSV)
   de          limma-voom DE on a counts CSV: writes the DEG table in the reference's format
   normalize   TMM log2-CPM of a counts CSV
@@ -19,12 +22,14 @@ import sys
 
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="consensusml_b200", description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
-    ap.add_argument("command", choices=["run", "lasso", "de", "normalize", "build", "config"])
+    ap.add_argument("command", choices=["run", "multiclass", "concat", "lasso", "de", "normalize", "build", "config"])
     ap.add_argument("--config", default=None)
     ap.add_argument("--counts", default=None, help="genes x samples counts CSV")
     ap.add_argument("--groups", default=None, help="CSV with columns sample,group (1 = non-reference level)")
+    ap.add_argument("--files", default=None, help="concat: glob pattern of the per-sample count files (sample id = file name up to the first dot)")
+    ap.add_argument("--train-frac", type=float, default=2.0 / 3.0, help="run/multiclass on counts: stratified training fraction")
     ap.add_argument("overrides", nargs="*", help="section.key=value")
-    args = ap.parse_args(argv)
+    args = ap.parse_intermixed_args(argv)
     from ..runtime import config as C
     cfg = C.load(args.config, args.overrides)
     if args.command == "config":
@@ -41,8 +46,41 @@ def main(argv=None) -> int:
     from .. import pipeline
     dev = pipeline.resolve_device(cfg)
     os.makedirs(cfg.io.out_dir, exist_ok=True)
-    if args.command == "run":
+    if args.command == "concat":
+        from ..io import counts as IC
+        if not args.files:
+            ap.error("'concat' needs --files")
+        import glob
+        files = sorted(glob.glob(args.files))
+        if not files:
+            ap.error(f"no file matches {args.files!r}")
+        mat, genes, ids = IC.concat_counts(files, regex=r"^([^.]*).*$")
+        path = os.path.join(cfg.io.out_dir, "HTSeq_Counts.csv")
+        IC.write_matrix_csv(path, torch.as_tensor(mat), genes, ids)
+        print(json.dumps({"genes": len(genes), "samples": len(ids), "csv": path}))
+        return 0
+    if args.command == "run" and args.counts is None:
         summary = pipeline.run(cfg)
+        print(json.dumps(summary, indent=1, default=str))
+        return 0
+    if args.command in ("run", "multiclass"):
+        from ..cohort import ops as CO
+        from ..io import counts as IC
+        if args.groups is None:
+            ap.error(f"'{args.command}' on counts needs --groups")
+        counts, genes, samples = IC.read_counts_csv(args.counts)
+        grp = pd.read_csv(args.groups).set_index("sample").loc[samples, "group"]
+        levels = sorted(grp.unique().tolist())
+        lab = grp.map({v: i for i, v in enumerate(levels)}).to_numpy()
+        train = CO.split_stratified(lab, args.train_frac, seed=cfg.split.seed)
+        if args.command == "run":
+            if len(levels) != 2:
+                ap.error("'run' needs a two-level group column; use 'multiclass'")
+            co = pipeline.cohort_from_counts(counts.to(dev), genes, samples, lab, train, cfg)
+            summary = pipeline.run(cfg, co)
+        else:
+            co = pipeline.multiclass_cohort_from_counts(counts.to(dev), genes, samples, lab, train, cfg)
+            summary = pipeline.run_multiclass(cfg, co, class_names={i: str(v) for i, v in enumerate(levels)})
         print(json.dumps(summary, indent=1, default=str))
         return 0
     if args.command == "lasso":

@@ -97,3 +97,30 @@ def test_multiclass_one_vs_rest_cpu(tmp_path):
     assert np.asarray(s["confusion"]).sum() == int((~train).sum())
     assert len(s["top"]) > 0 and os.path.exists(tmp_path / "consensus_rank_multiclass.csv")
     assert os.path.exists(tmp_path / "class_AML" / "standouttable.csv")
+
+
+def test_cli_concat_then_run_on_counts(tmp_path, capsys):
+    """Per-sample HTSeq files -> counts CSV -> normalise + DE prefilter + ensemble, all through the CLI."""
+    import pandas as pd
+    from consensusml_b200.cli.main import main
+    from consensusml_b200.io.synthetic import nb_counts
+    c, g = nb_counts(2500, 42, seed=5, n_de=200)
+    files = []
+    for j in range(42):
+        f = tmp_path / f"S{j:03d}.htseq.counts"
+        with open(f, "w") as fh:
+            for i in range(2500):
+                fh.write(f"ENSG{i:011d}.1\t{c[i, j]}\n")
+            fh.write("__no_feature\t123\n")
+        files.append(str(f))
+    out = tmp_path / "out"
+    assert main(["concat", "--files", str(tmp_path / "*.htseq.counts"), "io.out_dir=" + str(out)]) == 0
+    info = json.loads(capsys.readouterr().out)
+    assert info["genes"] == 2500 and info["samples"] == 42
+    pd.DataFrame({"sample": [f"S{j:03d}" for j in range(42)], "group": np.where(g == 1, "High", "Low")}).to_csv(tmp_path / "groups.csv", index=False)
+    rc = main(["run", "--counts", info["csv"], "--groups", str(tmp_path / "groups.csv"), "io.out_dir=" + str(out), "device=cpu",
+               "lasso.exclusion_reps=1", "lasso.nfolds=4", "rf.n_trees=[30]", "rf.proximity=false", 'gbm.reps=[{"max_depth": 2, "nrounds": 2}]',
+               "svm.enabled=false", "mlp.enabled=false"])
+    assert rc == 0
+    summary = json.loads(capsys.readouterr().out)
+    assert summary["lasso"]["auc"] > 0.8 and os.path.exists(out / "standouttable.csv") and os.path.exists(out / "consensus_rank.csv")
