@@ -13,9 +13,15 @@ import torch
 import torch.distributed as dist
 
 
-def init(backend: Optional[str] = None) -> tuple[int, int, torch.device]:
+def init(backend: Optional[str] = None, timeout_s: Optional[float] = None) -> tuple[int, int, torch.device]:
     """Initialise from the torchrun environment (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_*).
-    Returns (rank, world_size, device).  A single-process call needs no environment."""
+    Returns (rank, world_size, device).  A single-process call needs no environment.
+
+    ``timeout_s`` (default: ``CML_DIST_TIMEOUT_S`` or 600) is the collective watchdog: a rank that never arrives makes
+    the others raise instead of hanging the node (the fused kernels add their own guard - tests run them under a
+    ``faulthandler`` deadline because a spinning kernel cannot be interrupted by NCCL's watchdog)."""
+    import datetime
+    timeout = datetime.timedelta(seconds=float(timeout_s if timeout_s is not None else os.environ.get("CML_DIST_TIMEOUT_S", 600)))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -27,9 +33,9 @@ def init(backend: Optional[str] = None) -> tuple[int, int, torch.device]:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
         if use_cuda:
-            dist.init_process_group(backend or "nccl", device_id=device)
+            dist.init_process_group(backend or "nccl", device_id=device, timeout=timeout)
         else:
-            dist.init_process_group(backend or "gloo")
+            dist.init_process_group(backend or "gloo", timeout=timeout)
     return rank, world, device
 
 
