@@ -262,3 +262,75 @@ def best_splits(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_ch
     b = 0xFFF - (key & 0xFFF)
     return torch.where(has, gain, torch.zeros_like(gain)), torch.where(has, feat, -torch.ones_like(feat)), \
         torch.where(has, b, -torch.ones_like(b))
+
+
+# ------------------------------------------------------------------------------------------------ path 2b
+# Replicate-batched gradient as a tcgen05 GEMM fused with its reduce-scatter (csrc/gemm_rs.cu).  EXPERIMENTAL: the kernel
+# compiles for sm_100a and has a GPU test, but it has not run on hardware yet - nothing in the package calls it by default.
+SIG_GEMM_RS = 32
+_native.register_signature("cml_xtr_gemm_reduce_scatter",
+                           [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p,
+                                                 ctypes.c_longlong, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                                 ctypes.c_uint, ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_void_p])
+
+
+def split_bf16(r: torch.Tensor) -> torch.Tensor:
+    """[B, K] fp32 -> [2B, K] bf16: rows [0, B) the bf16 rounding of r, rows [B, 2B) the rounding of the remainder, so
+    that hi + lo carries 16 mantissa bits into a bf16 tensor-core product."""
+    hi = r.bfloat16()
+    lo = (r - hi.float()).bfloat16()
+    return torch.cat([hi, lo], 0).contiguous()
+
+
+class XtrGemmReduceScatter:
+    """``G_owned[genes_owned, B] = sum_ranks (Xt_r . Rt_r^T)[owned genes]`` - GEMM and reduce-scatter in one kernel.
+
+    ``xt`` is the gene-major bf16 copy of this rank's rows ([p, ld], ld % 8 == 0), ``rt`` the replicate-major bf16
+    residuals ([B, ld] or the [2B, ld] hi/lo split).  Results alternate between two symmetric buffers; the one returned by
+    ``result()`` stays valid until the next ``launch``."""
+
+    def __init__(self, p: int, B: int, device, use_tma_reduce: bool = False):
+        assert B % 32 == 0, "B must be a multiple of 32"
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.p, self.B, self.use_tma = p, B, use_tma_reduce
+        self.genes_per_rank = ((p + self.world - 1) // self.world + 31) // 32 * 32
+        self.gene0 = min(p, self.rank * self.genes_per_rank)
+        self.genes_owned = max(0, min(p, self.gene0 + self.genes_per_rank) - self.gene0)
+        self.bufs = [symm.alloc((self.genes_per_rank, B), torch.float32, device) for _ in range(2)]
+        self.done = torch.zeros(4, dtype=torch.int32, device=device)
+        self.epoch = 0
+
+    def launch(self, xt: torch.Tensor, rt: torch.Tensor, alpha: float = 1.0) -> None:
+        assert xt.dtype == torch.bfloat16 and rt.dtype == torch.bfloat16 and xt.shape[1] == rt.shape[1] and xt.shape[1] % 8 == 0
+        assert xt.shape[0] == self.p and rt.shape[0] in (self.B, 2 * self.B)
+        self.epoch += 1
+        buf, nxt = self.bufs[self.epoch & 1], self.bufs[(self.epoch + 1) & 1]
+        nxt.local.zero_()            # the buffer of the NEXT epoch: peers cannot add to it before they see this epoch's signal
+        rc = _native.cuda().cml_xtr_gemm_reduce_scatter(
+            self.p, rt.shape[0], self.B, xt.shape[1], _native.ptr(xt), xt.stride(0), _native.ptr(rt), rt.stride(0),
+            _ptr_array(buf.peer_ptrs), self.B, self.genes_per_rank, _ptr_array(buf.signal_ptrs), self.rank, self.world,
+            _native.ptr(self.done), self.epoch, SIG_GEMM_RS, float(alpha), int(self.use_tma), _native.stream_ptr())
+        _native.check(rc, "cml_xtr_gemm_reduce_scatter")
+
+    def wait(self) -> None:
+        buf = self.bufs[self.epoch & 1]
+        rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(buf.signal_ptrs[self.rank]), SIG_GEMM_RS, self.world, self.epoch,
+                                             _native.stream_ptr())
+        _native.check(rc, "cml_wait_signals")
+
+    def result(self) -> torch.Tensor:
+        return self.bufs[self.epoch & 1].local[: self.genes_owned]
+
+
+def xtr_gemm_rs_unfused(xt: torch.Tensor, rt: torch.Tensor, p: int, B: int, genes_per_rank: int) -> torch.Tensor:
+    """Comparator / CPU path: fp32 matmul of the same bf16 operands, all-reduce, slice of the owned genes."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    g = xt.float() @ rt.float().t()
+    if rt.shape[0] == 2 * B:
+        g = g[:, :B] + g[:, B:]
+    if world > 1:
+        dist.all_reduce(g)
+    g0 = min(p, rank * genes_per_rank)
+    return g[g0: min(p, g0 + genes_per_rank)]

@@ -218,5 +218,7 @@ using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
 EncodeTiledFn get_encode_tiled();
 // Row-major bf16 matrix [rows][cols] with `ld` elements between rows; box = 64 columns x box_rows rows, 128B swizzle.
 int make_tmap_bf16_k64(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows);
+// Row-major fp32 matrix [rows][cols] with pitch ld (floats) as 32 x 32 boxes, 128B swizzle (epilogue staging layout).
+int make_tmap_f32_box32(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld);
 
 }  // namespace cml

@@ -199,6 +199,15 @@ int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const floa
 int cml_shard_transpose(const void* x, long long ldx, int rows_local, int cols, const int* col_start, const void* const* out_bufs,
     long long ldy, int row0, const void* const* peer_sigs, int rank, int world, unsigned* done_count,
     unsigned epoch, int sig_base, void* stream);
+/* Path 2b (EXPERIMENTAL - compiled, not yet run on hardware): replicate-batched gradient G = alpha * Xt . Rt^T as a CTA-pair
+ * tcgen05 GEMM whose epilogue reduces each tile into the owning rank's buffer over NVLink (register red.add.v4.f32, or a
+ * TMA tensor reduce with use_tma_reduce = 1); split-K over the samples comes for free because the landing is an atomic add.
+ * xt bf16 [p][ldxt] gene-major, rt bf16 [N][ldrt] with N = B or 2B (hi/lo split, column n lands in n % B); out_bufs[d]:
+ * owner d's fp32 [genes_per_rank][ldo] buffer, zero before the epoch; completion = signal word (sig_base + rank) == epoch. */
+int cml_xtr_gemm_reduce_scatter(int p, int N, int B, int K, const void* xt_bf16, long long ldxt, const void* rt_bf16, long long ldrt,
+                                const void* const* out_bufs, long long ldo, int genes_per_rank, const void* const* peer_sigs,
+                                int rank, int world, unsigned* done_count, unsigned epoch, int sig_base, float alpha,
+                                int use_tma_reduce, void* stream);
 int cml_xb_residual(const void* x_bf16, long long ldx, int n, int p, const float* v, float b0, const float* y, const float* w,
     float* R, float* eta_out, double* loss_sum, void* stream);
 size_t cml_hist_scratch_bytes(int p, int ft);
