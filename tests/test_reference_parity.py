@@ -1,0 +1,113 @@
+"""Side-by-side runs against the reference's OWN Python helpers, loaded unmodified from ``/root/reference/scripts`` when that
+tree is present (it exists on the development box only; elsewhere these tests skip).  ``dummies.py`` lacks its pandas
+import (scripts/README.md calls it unused), so ``pd`` is injected into its module namespace - nothing else is touched."""
+import importlib.util
+import os
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from consensusml_b200.api import clean, dummies
+
+REF = "/root/reference/scripts"
+pytestmark = pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not available")
+
+
+def _load(name):
+    spec = importlib.util.spec_from_file_location(f"ref_{name}", os.path.join(REF, f"{name}.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _tables(seed=0, n=12, genes=7):
+    rng = np.random.default_rng(seed)
+    usi = [f"TARGET-20-PA{''.join(rng.choice(list('ABCDEFGH'), 4))}" for _ in range(n)]
+    bar = [f"{u}-{rng.choice(['09A', '03A', '01A'])}-01R" for u in usi]
+    manifest = pd.DataFrame({"file_id": [f"f{i}" for i in range(n + 3)],
+                             "project.project_id": ["TARGET-AML"] * n + ["TARGET-NBL"] * 3,
+                             "entity_submitter_id": bar + [f"TARGET-30-PAZZZ{i}-01A-01R" for i in range(3)]})
+    clinical = pd.DataFrame({"TARGET USI": usi[:-2] + ["TARGET-20-PANONE"], "Risk group": rng.choice(["Low", "High", "Standard"], n - 1),
+                             "Age": rng.integers(1, 20, n - 1)})
+    assay = pd.DataFrame(rng.normal(size=(genes, n)), columns=[b.replace("-", ".") for b in bar])
+    assay.insert(0, "gene", [f"ENSG{i:05d}" for i in range(genes)])
+    return manifest, clinical, assay
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_clean_functions_equal_the_reference(seed):
+    ref = _load("clean")
+    manifest, clinical, assay = _tables(seed)
+    with pd.option_context("mode.chained_assignment", None):
+        a = ref.manifest_clinical_merge(manifest.copy(), clinical.copy(), "TARGET-AML")
+    b = clean.manifest_clinical_merge(manifest.copy(), clinical.copy(), "TARGET-AML")
+    pd.testing.assert_frame_equal(a.reset_index(drop=True), b.reset_index(drop=True), check_dtype=False)
+    ta = ref.assay_transpose(assay.copy())
+    tb = clean.assay_transpose(assay.copy())
+    pd.testing.assert_frame_equal(ta, tb, check_dtype=False, check_names=False)
+    assert ref.column_reorder(a) == clean.column_reorder(b)
+    ma = ref.assay_clinical_merge(ta.copy(), a.copy())
+    mb = clean.assay_clinical_merge(tb.copy(), b.copy())
+    pd.testing.assert_frame_equal(ma, mb, check_dtype=False, check_names=False)
+    assert list(mb.columns[:2]) == [mb.columns[0], "Diagnostic ID"] and set(mb["Diagnostic ID"]) <= {"09A", "03A", "01A"}
+
+
+def test_dummies_equal_the_reference():
+    ref = _load("dummies")
+    ref.pd = pd                                   # the reference file forgot `import pandas as pd`
+    train = pd.Series(["a", "b", "a", "c"])
+    test = pd.Series(["b", "zzz", "a"], index=[5, 6, 7])
+    a = ref.make_dummies(test, train.unique(), "city")
+    b = dummies.make_dummies(test, train.unique(), "city")
+    pd.testing.assert_frame_equal(a, b, check_dtype=False)
+    assert b.loc[6].sum() == 0                     # level unseen in training -> all zeros
+    df = pd.DataFrame({"city": ["x", "y", "x"], "phone": ["p", "p", "q"], "v": [1, 2, 3]})
+    pd.testing.assert_frame_equal(ref.make_dummies_dataframe(df.copy(), ["city", "phone"]),
+                                  dummies.make_dummies_dataframe(df.copy(), ["city", "phone"]), check_dtype=False)
+
+
+def test_model_comp_data_preparation_equals_the_reference():
+    """scripts/model_comp.py imports xgboost (not installed) at module top; a stub module lets the file load unmodified so
+    that its pure pandas / sklearn functions (data_prep_columns, model_prep, model_prep_loc) can be compared with ours."""
+    import sys
+    import types
+    from consensusml_b200.api import model_comp as ours
+    stub = types.ModuleType("xgboost")
+    stub.XGBClassifier = object
+    had = sys.modules.get("xgboost")
+    sys.modules["xgboost"] = stub
+    try:
+        ref = _load("model_comp")
+    finally:
+        if had is None:
+            sys.modules.pop("xgboost", None)
+        else:
+            sys.modules["xgboost"] = had
+    rng = np.random.default_rng(3)
+    n, genes = 90, 2600
+    clin = {f"c{i}": rng.integers(0, 5, n) for i in range(84)}
+    clin["c1"] = rng.choice(["09A", "03A", "01A", "11A"], n, p=[0.5, 0.3, 0.15, 0.05])
+    clin["c2"] = rng.choice(["Low", "Standard", "High", "Unknown"], n, p=[0.4, 0.3, 0.25, 0.05])
+    df = pd.DataFrame(clin).rename(columns={"c1": "Diagnostic ID", "c2": "Risk group"})
+    sd = rng.permutation(np.linspace(0.2, 6.0, genes))               # well separated variances: no ordering ties
+    g = pd.DataFrame(rng.normal(size=(n, genes)) * sd, columns=[f"ENSG{i:06d}" for i in range(genes)])
+    tail = pd.DataFrame({f"t{i}": rng.integers(0, 3, n) for i in range(4)})
+    df = pd.concat([df, g, tail], axis=1)
+    for var in ("Max", "Min"):
+        a_df, a_cols = ref.data_prep_columns(df.copy(), var)
+        b_df, b_cols = ours.data_prep_columns(df.copy(), var)
+        pd.testing.assert_frame_equal(a_df, b_df, check_dtype=False)
+        assert len(a_cols) == len(b_cols) and set(a_cols) == set(b_cols)
+        assert a_cols[:1000] == b_cols[:1000]                        # same order within the first class's top-1000
+    with pd.option_context("mode.chained_assignment", None):
+        ra = ref.model_prep(a_df, a_cols)
+    rb = ours.model_prep(b_df, a_cols)
+    for x, y in zip(ra[:4], rb[:4]):
+        assert np.array_equal(np.asarray(x), np.asarray(y))
+    pd.testing.assert_frame_equal(ra[4], rb[4], check_dtype=False)
+    names = [a_df.columns[i] for i in a_cols[:50]]
+    with pd.option_context("mode.chained_assignment", None):
+        la = ref.model_prep_loc(a_df, names)
+    lb = ours.model_prep_loc(b_df, names)
+    assert np.array_equal(np.asarray(la[0]), np.asarray(lb[0])) and np.array_equal(np.asarray(la[3]), np.asarray(lb[3]))
