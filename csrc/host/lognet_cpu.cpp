@@ -31,6 +31,7 @@ struct PathArgs {
   int intercept, kopt, maxit, nx;
 };
 
+static int g_active_cov = 0;   // 1: covariance updates inside the active-set sweeps (cml_host_lognet_set_active_mode)
 static thread_local long long g_cnt[8];   // visit counters of the calling thread (cml_host_lognet_counters)
 inline double dotw(const double* a, const double* b, int n) {
   double s = 0.0;
@@ -175,6 +176,71 @@ int lognet_path(const PathArgs& A, double* beta /*nlam x p*/, double* a0 /*nlam*
           intercept_update(dlx);
           if (dlx < shr) break;
           if (nlp > A.maxit) { jerr = -(ilm + 1); goto finish; }
+          if (g_active_cov && nin > 0) {
+            // Active-set sweeps with covariance updates: the gradients g_l = x_l . r of the active coordinates are kept
+            // current through C[l][j] = sum_i v_i x_il x_ij instead of being recomputed as dot products, so a coordinate
+            // step has no length-n reduction on its critical path (the form the GPU kernel wants: one broadcast, a few
+            // scalar operations, one fused multiply-add per lane).  Mathematically the same iteration as below; the
+            // residual is brought up to date once, when the sweeps have converged.
+            const int K = nin;
+            std::vector<double> gact(K), C((size_t)K * K), cv(K), db(K, 0.0);
+            for (int l = 0; l < K; ++l) {
+              const double* xl = A.xt + (size_t)m[l] * n;
+              gact[l] = dotw(r.data(), xl, n);
+              double s = 0.0;
+              for (int i = 0; i < n; ++i) s += v[i] * xl[i];
+              cv[l] = s;
+              for (int j = 0; j <= l; ++j) {
+                const double* xj = A.xt + (size_t)m[j] * n;
+                double c = 0.0;
+                for (int i = 0; i < n; ++i) c += v[i] * xl[i] * xj[i];
+                C[(size_t)l * K + j] = C[(size_t)j * K + l] = c;
+              }
+            }
+            double sr = 0.0, d0sum = 0.0;
+            for (int i = 0; i < n; ++i) sr += r[i];
+            bool fail = false;
+            while (true) {
+              ++nlp;
+              dlx = 0.0;
+              g_cnt[1] += nin; ++g_cnt[6];
+              for (int l = 0; l < K; ++l) {
+                const int k = m[l];
+                const double bk = b[k + 1];
+                const double u = gact[l] + xv[k] * bk;
+                const double au = std::fabs(u) - vpn[k] * al1;
+                const double nb = au > 0.0 ? std::copysign(au, u) / (xv[k] + vpn[k] * al2) : 0.0;
+                const double d = nb - bk;
+                if (d == 0.0) continue;
+                b[k + 1] = nb;
+                dlx = std::max(dlx, xv[k] * d * d);
+                const double* Cl = &C[(size_t)l * K];
+                for (int j = 0; j < K; ++j) gact[j] -= d * Cl[j];
+                sr -= d * cv[l];
+                db[l] += d;
+              }
+              if (A.intercept) {
+                const double d = sr / xmz;
+                if (d != 0.0) {
+                  b[0] += d;
+                  dlx = std::max(dlx, xmz * d * d);
+                  for (int j = 0; j < K; ++j) gact[j] -= d * cv[j];
+                  sr -= d * xmz;
+                  d0sum += d;
+                }
+              }
+              if (dlx < shr) break;
+              if (nlp > A.maxit) { fail = true; break; }
+            }
+            for (int l = 0; l < K; ++l) {
+              if (db[l] == 0.0) continue;
+              const double* xl = A.xt + (size_t)m[l] * n;
+              for (int i = 0; i < n; ++i) r[i] -= db[l] * v[i] * xl[i];
+            }
+            if (d0sum != 0.0)
+              for (int i = 0; i < n; ++i) r[i] -= d0sum * v[i];
+            if (fail) { jerr = -(ilm + 1); goto finish; }
+          } else
           while (true) {
             ++nlp;
             dlx = 0.0;
@@ -247,6 +313,9 @@ finish:
 }  // namespace
 
 extern "C" {
+// 0 (default): every coordinate step recomputes its gradient as a dot product, statement for statement glmnet.
+// 1: covariance updates inside the active-set sweeps (same iteration, different rounding).  Process-wide.
+void cml_host_lognet_set_active_mode(int mode) { g_active_cov = mode != 0; }
 void cml_host_lognet_counters(long long* out) { for (int i = 0; i < 8; ++i) { out[i] = g_cnt[i]; g_cnt[i] = 0; } }
 
 // Batched entry: B replicates share xt/y/lambda; replicate b uses w[b*n..], ju[b*p..] (ju may be null).

@@ -105,3 +105,26 @@ def test_stability_selection_cpu_small():
     f = out["max_freq"]
     assert f[0] > 0.9 and f[1] > 0.9
     assert f[2:].mean() < 0.5
+
+
+def test_covariance_active_sweeps_are_the_same_iteration(aml):
+    """Host solver with covariance updates inside the active-set sweeps (no length-n reduction per coordinate step - the
+    formulation evaluated for the GPU kernel): same pass counts and coefficients as the statement-for-statement glmnet loop."""
+    import torch
+    from consensusml_b200 import _native
+    from consensusml_b200.ops import lasso as K
+    from consensusml_b200.ops.replicate import replicate_weights
+    tr, _ = aml.split()
+    x, y = tr.design(torch.float64), tr.labels().double()
+    w = torch.cat([torch.ones(1, 93, dtype=torch.float64), replicate_weights(3, 93, seed=1).double()[:, :93]])
+    lam = K.default_lambda_grid()
+    host = _native.host()
+    try:
+        host.cml_host_lognet_set_active_mode(1)
+        cov = K.lognet_path(x, y, w, lam, want_eta=False)
+    finally:
+        host.cml_host_lognet_set_active_mode(0)
+    ref = K.lognet_path(x, y, w, lam, want_eta=False)
+    assert cov.npasses.tolist() == ref.npasses.tolist()
+    for b in range(4):
+        assert (cov.dense(b) - ref.dense(b)).abs().max() < 1e-12
