@@ -15,6 +15,7 @@
 
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "cml_b200.h"
 #include "common.cuh"
@@ -151,9 +152,13 @@ __global__ void __launch_bounds__(kXtrThreads) xtr_reduce_scatter_kernel(
 }
 
 // Spin until signal words [base, base+world) of the local pad have all reached `epoch`.
-__global__ void wait_signals_kernel(const unsigned* pad, int base, int world, unsigned epoch) {
+// A peer that never signals (crashed rank, protocol mistake) would leave this kernel spinning for good and the device
+// unusable; after `timeout_cycles` (0 = wait for ever) the kernel traps instead, which surfaces as a CUDA error on the host.
+__global__ void wait_signals_kernel(const unsigned* pad, int base, int world, unsigned epoch, long long timeout_cycles) {
   if (threadIdx.x < world) {
+    const long long t0 = clock64();
     while ((int)(ld_acquire_sys(pad + base + threadIdx.x) - epoch) < 0) {
+      if (timeout_cycles > 0 && clock64() - t0 > timeout_cycles) __trap();
     }
   }
 }
@@ -477,7 +482,14 @@ int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, cons
 
 int cml_wait_signals(const void* pad, int base, int world, unsigned epoch, void* stream) {
   using namespace cml;
-  wait_signals_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const unsigned*>(pad), base, world, epoch);
+  // CML_WAIT_TIMEOUT_S: seconds before a wait gives up (default 30, 0 = never); converted at ~2 GHz
+  static const long long timeout_cycles = [] {
+    const char* e = getenv("CML_WAIT_TIMEOUT_S");
+    const double sec = e ? atof(e) : 30.0;
+    return sec > 0 ? static_cast<long long>(sec * 2.0e9) : 0LL;
+  }();
+  wait_signals_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const unsigned*>(pad), base, world, epoch,
+                                                                       timeout_cycles);
   CML_LAUNCH_CHECK();
   return 0;
 }
