@@ -24,7 +24,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 N_TRAIN, P_GENES, N_LAMBDA = 93, 1984, 100
-REPS_PER_GPU = int(os.environ.get("CML_BENCH_REPS", 8192))
+# 8880 = 3 x (148 SMs x 20 resident path-fit warps): three full waves of the path kernel on a B200 (8192, used for the
+# numbers in profiles/ up to this change, left the third wave 77 % full)
+REPS_PER_GPU = int(os.environ.get("CML_BENCH_REPS", 8880))
 METRIC = "lasso_path_fits_per_sec"
 
 
