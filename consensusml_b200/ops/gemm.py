@@ -23,6 +23,14 @@ _native.register_signature("cml_gemm_set_variant", [_I])
 EPI_SCALE, EPI_RBF, EPI_SQDIST = 0, 1, 2
 
 
+_native.register_signature("cml_gemm_set_staged_grouping", [_I])
+
+
+def set_staged_grouping(on: bool) -> None:
+    """Grouped tile order inside each source block of the staged all-gather GEMM (opt-in until measured on hardware)."""
+    _native.check(_native.cuda().cml_gemm_set_staged_grouping(int(bool(on))), "cml_gemm_set_staged_grouping")
+
+
 def set_variant(variant: int) -> None:
     """0 = choose by shape, 1 = single-CTA tcgen05 kernel, 2 = CTA-pair (``cta_group::2``) kernel."""
     _native.check(_native.cuda().cml_gemm_set_variant(int(variant)), "cml_gemm_set_variant")

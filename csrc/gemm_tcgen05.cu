@@ -116,6 +116,7 @@ struct GemmParams {
   unsigned* flags;                // [n_src * tiles_n_per_src], ready when == epoch
   unsigned epoch;
   int n_copiers, rank;
+  int staged_grouped;             // staged mode: grouped tile order inside each source block (0 = m-fastest, the measured default)
   long long ldb;
 };
 
@@ -228,6 +229,23 @@ __device__ __forceinline__ void tile_to_mn(int tile, int tiles_m, int tiles_n, b
   const int gm = min(kGroupM, tiles_m - m0);
   m_blk = m0 + in_group % gm;
   n_blk = in_group / gm;
+}
+
+// Staged all-gather: the source blocks are visited strictly in ring order (their data arrives in that order).  Inside a
+// block the tiles are m-fastest by default; with P.staged_grouped they follow the grouped order of the plain GEMM, which
+// keeps the A panels L2-resident at 8 GPUs (written after GPU access closed: opt-in until measured).
+__device__ __forceinline__ void tile_to_mn_src(const GemmParams& P, int tile, int tiles_n, bool staged, int& m_blk, int& n_blk) {
+  if (!staged) {
+    tile_to_mn(tile, P.tiles_m, tiles_n, true, m_blk, n_blk);
+  } else if (!P.staged_grouped) {
+    tile_to_mn(tile, P.tiles_m, tiles_n, false, m_blk, n_blk);
+  } else {
+    const int per_src = P.tiles_m * P.tiles_n_per_src;
+    const int si = tile / per_src;
+    int n_loc;
+    tile_to_mn(tile - si * per_src, P.tiles_m, P.tiles_n_per_src, true, m_blk, n_loc);
+    n_blk = si * P.tiles_n_per_src + n_loc;
+  }
 }
 
 // 2^x on the SFU without the denormal pre/post scaling of exp2f (results below 2^-126 flush to zero)
@@ -380,7 +398,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         int m_blk, n_blk;
-        tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+        tile_to_mn_src(P, tile, tiles_n, staged, m_blk, n_blk);
         const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
         const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
         if (staged) {
@@ -440,7 +458,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       int m_blk, n_blk;
-      tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+      tile_to_mn_src(P, tile, tiles_n, staged, m_blk, n_blk);
       const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
       const int src = staged ? (P.rank + si) % P.n_src : si;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -551,7 +569,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
       uint32_t phase = 0;
       for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
         int m_blk, n_blk;
-        tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+        tile_to_mn_src(P, tile, tiles_n, staged, m_blk, n_blk);
         const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
         const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
         if (staged) {
@@ -615,7 +633,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_stride) {
       int m_blk, n_blk;
-      tile_to_mn(tile, P.tiles_m, tiles_n, !staged, m_blk, n_blk);
+      tile_to_mn_src(P, tile, tiles_n, staged, m_blk, n_blk);
       const int si = n_blk / P.tiles_n_per_src, n_loc = n_blk % P.tiles_n_per_src;
       const int src = staged ? (P.rank + si) % P.n_src : si;
       const float* nb = staged ? P.stage_norm + (size_t)src * P.rows_per_src : P.norm_b[src];
@@ -653,6 +671,7 @@ int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
 }
 
 int g_gemm_variant = 0;   // 0 = choose by shape, 1 = single-CTA kernel, 2 = CTA-pair kernel
+int g_staged_grouped = 0; // staged all-gather GEMM: grouped tile order inside a source block
 
 // fp32 row-major -> bf16 row-major with zero-padded pitch, fused with the squared row norm of the
 // ROUNDED values (so that the RBF epilogue's |a|^2 + |b|^2 - 2ab is exactly consistent with the MMA inputs).
@@ -795,8 +814,15 @@ int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, c
   P.tiles_n_per_src = ceil_div(rows_per_src < N ? rows_per_src : N, BN);
   P.stage = stage; P.stage_norm = stage_norm; P.flags = flags; P.epoch = epoch;
   P.n_copiers = n_copiers; P.rank = rank; P.ldb = ldb;
+  P.staged_grouped = g_staged_grouped;
   if (pair) return launch_gemm_pair<6>(P, static_cast<cudaStream_t>(stream));
   return launch_gemm<256, 4>(P, static_cast<cudaStream_t>(stream));
+}
+
+// 1: grouped tile order inside each source block of the staged all-gather GEMM (default 0; not yet measured on hardware).
+int cml_gemm_set_staged_grouping(int on) {
+  cml::g_staged_grouped = on ? 1 : 0;
+  return 0;
 }
 
 int cml_gemm_staged_flags(int n_src, int rows_per_src) { return n_src * cml::ceil_div(rows_per_src, 256); }

@@ -116,6 +116,8 @@ int cml_gemm_staged_flags(int n_src, int rows_per_src);
 /* Kernel choice of cml_gemm_tn_bf16: 0 = by shape (CTA pairs / cta_group::2 with 256 x 256 tiles once there are enough
  * tiles for every SM pair), 1 = single-CTA kernel, 2 = CTA-pair kernel.  Process-wide; meant for benchmarks and tests. */
 int cml_gemm_set_variant(int variant);
+/* 1: grouped tile order inside each source block of the staged all-gather GEMM (default 0 = m-fastest; opt-in until measured). */
+int cml_gemm_set_staged_grouping(int on);
 /* fp32 [rows][ldx] -> bf16 [rows][ldy] (zero padded) with optional (x - shift - col_shift[j]) * col_scale[j],
  * plus squared row norms of the rounded values.                                                       */
 int cml_to_bf16_rownorm(const float* x, long long ldx, void* y_bf16, long long ldy, float* norm, int rows, int cols,

@@ -133,3 +133,15 @@ def test_staged_allgather_gemm_with_local_sources(n_src, rows, k, rank, variant)
             assert (got - d2).abs().max().item() < 2e-3 * max(1.0, d2.abs().max().item())
     finally:
         G.set_variant(0)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("CML_EXPERIMENTAL") != "1", reason="opt-in until measured on hardware: set CML_EXPERIMENTAL=1")
+@pytest.mark.parametrize("variant", [0, 1])
+def test_staged_allgather_gemm_grouped_tile_order(variant):
+    """Same check as above with the grouped tile order inside each source block switched on."""
+    G.set_staged_grouping(True)
+    try:
+        test_staged_allgather_gemm_with_local_sources(8, 750, 2500, 3, variant)
+        test_staged_allgather_gemm_with_local_sources(4, 1024, 512, 0, variant)
+    finally:
+        G.set_staged_grouping(False)

@@ -5,7 +5,7 @@
 mkdir -p gpurun_out/session
 O=gpurun_out/session
 echo "== full GPU suite";           timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -3 | tee $O/pytest_gpu.txt
-echo "== experimental GEMM-RS";     CML_EXPERIMENTAL=1 CML_WAIT_TIMEOUT_S=10 timeout 180 python -m pytest tests/test_gemm_rs_gpu.py -x -q 2>&1 | tail -5 | tee $O/pytest_gemm_rs.txt
+echo "== experimental GEMM-RS";     CML_EXPERIMENTAL=1 CML_WAIT_TIMEOUT_S=10 timeout 240 python -m pytest tests/test_gemm_rs_gpu.py tests/test_gemm_gpu.py -q -k "gemm_rs or grouped or single_rank or emulated" 2>&1 | tail -5 | tee $O/pytest_gemm_rs.txt
 echo "== bench.py";                 timeout 300 python bench.py --steps 4 --warmup 3 2>/dev/null | tail -1 | tee $O/bench.json | cut -c1-300
 echo "== pipeline bench";           timeout 400 python bench/pipeline_bench.py 2>/dev/null | tail -1 | tee $O/pipeline.json | cut -c1-600
 echo "== stability bench";          timeout 300 python bench/stability_bench.py 2>&1 | tail -1 | tee $O/stability.json | cut -c1-600
