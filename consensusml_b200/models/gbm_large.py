@@ -63,6 +63,10 @@ class GBMLarge:
     min_child_weight: float = 1.0
     nbins: int = 256
     use_multicast: bool = True
+    backend: str = "auto"                 # "fused" (CUDA kernels, in-kernel all-reduce) | "unfused" (torch + all_reduce; CPU path)
+    sibling_subtraction: bool = False     # build only the smaller child of every split, derive its sibling from the parent
+                                          # (halves the samples histogrammed per level; exact with the kernel's fixed-point sums).
+                                          # Opt-in until it has been run on the GPU path.
     trees: List[LevelTree] = field(default_factory=list, repr=False)
     cuts: torch.Tensor = field(default=None, repr=False)
     importance_gain_: torch.Tensor = field(default=None, repr=False)
@@ -77,12 +81,14 @@ class GBMLarge:
         p = bins.shape[0]
         n = y_local.numel()
         D = self.max_depth
-        H = F.HistAllReduce(p, self.nbins, 2 ** (D - 1) if D > 0 else 1, dev)
+        backend = self.backend if self.backend != "auto" else ("fused" if bins.is_cuda else "unfused")
+        H = F.HistAllReduce(p, self.nbins, 2 ** (D - 1) if D > 0 else 1, dev) if backend == "fused" else None
         y = y_local.float()
         margin = torch.zeros(n, device=dev)
         ar = torch.arange(n, device=dev)
         self.trees = []
         self.importance_gain_ = torch.zeros(p, device=dev)
+        self.samples_histogrammed_ = 0            # local samples that went through a histogram build (work measure)
         for _ in range(self.n_estimators):
             pr = torch.sigmoid(margin)
             gh = torch.stack([pr - y, pr * (1 - pr)], 1).contiguous()
@@ -91,25 +97,54 @@ class GBMLarge:
             thr_all = torch.zeros(2 ** D - 1, dtype=torch.int64, device=dev)
             value_all = torch.zeros(2 ** (D + 1) - 1, device=dev)
             alive = torch.ones(n, dtype=torch.bool, device=dev)
+            prev_hist = None
             for level in range(D + 1):
                 n_nodes = 2 ** level
                 base = n_nodes - 1
-                # node totals (tiny): local index_add + all-reduce
-                tot = torch.zeros(n_nodes, 2, device=dev)
+                # node totals (tiny): local index_add + all-reduce; the third column counts samples (sibling choice)
+                tot = torch.zeros(n_nodes, 3, device=dev)
                 idx = node[alive].long()
-                tot.index_add_(0, idx, gh[alive])
+                tot.index_add_(0, idx, torch.cat([gh[alive], torch.ones(int(alive.sum()), 1, device=dev)], 1))
                 all_reduce_(tot)
                 value_all[base:base + n_nodes] = -self.learning_rate * tot[:, 0] / (tot[:, 1] + self.reg_lambda)
                 if level == D:
                     break
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                hist = H.build(bins, n, torch.where(alive, node, torch.full_like(node, -1)), gh, n_nodes,
-                               use_multicast=self.use_multicast, g_bound=1.0, h_bound=0.25)
-                gain, feat, thr = F.best_splits(hist, self.reg_lambda, self.gamma, self.min_child_weight)
-                e1.record()
-                H.clear(n_nodes)
-                self.level_ms_.append((level, e0.elapsed_time(e1)))
+                e0 = e1 = None
+                if bins.is_cuda:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                build_node = torch.where(alive, node, torch.full_like(node, -1))
+                derive = None
+                if self.sibling_subtraction and prev_hist is not None:
+                    # the smaller child of every pair is histogrammed, the larger one is parent - smaller
+                    cnt = tot[:, 2].view(-1, 2)
+                    small_is_right = cnt[:, 1] < cnt[:, 0]
+                    small = torch.stack([~small_is_right, small_is_right], 1).flatten()          # [n_nodes] bool
+                    build_node = torch.where(alive & small[node.long()], node, torch.full_like(node, -1))
+                    derive = ~small
+                self.samples_histogrammed_ += int((build_node >= 0).sum())
+                if backend == "fused":
+                    hist = H.build(bins, n, build_node, gh, n_nodes, use_multicast=self.use_multicast, g_bound=1.0, h_bound=0.25)
+                else:
+                    hist = F.hist_unfused(bins, n, build_node, gh, n_nodes, p, self.nbins)
+                if derive is not None:
+                    hist = hist.clone() if backend == "fused" else hist
+                    parent = prev_hist.repeat_interleave(2, dim=0)                               # parent of node j is j // 2
+                    sibling = hist.view(-1, 2, p, self.nbins, 2).flip(1).reshape(n_nodes, p, self.nbins, 2)
+                    hist = torch.where(derive.view(-1, 1, 1, 1), parent - sibling, hist)
+                    hist = torch.where((tot[:, 2] == 0).view(-1, 1, 1, 1), torch.zeros_like(hist), hist)   # children of unsplit nodes
+                if self.sibling_subtraction:
+                    prev_hist = hist.clone()
+                if backend == "fused":
+                    gain, feat, thr = F.best_splits(hist, self.reg_lambda, self.gamma, self.min_child_weight)
+                else:
+                    gain, feat, thr = F.best_splits_torch(hist, self.reg_lambda, self.gamma, self.min_child_weight)
+                if e1 is not None:
+                    e1.record()
+                    e1.synchronize()
+                    self.level_ms_.append((level, e0.elapsed_time(e1)))
+                if backend == "fused":
+                    H.clear(n_nodes)
                 split = feat >= 0
                 feat_all[base:base + n_nodes] = torch.where(split, feat, torch.full_like(feat, -1))
                 thr_all[base:base + n_nodes] = thr

@@ -264,6 +264,25 @@ def best_splits(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_ch
         torch.where(has, b, -torch.ones_like(b))
 
 
+def best_splits_torch(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_child_weight: float = 1.0):
+    """Same contract as ``best_splits`` in plain torch (CPU path and oracle): xgboost's second-order gain
+    ``G_L^2/(H_L+lam) + G_R^2/(H_R+lam) - G^2/(H+lam) - gamma`` over every cut after an occupied bin (ties: lowest feature, bin)."""
+    hh = hist.double()
+    cg, ch = hh[..., 0].cumsum(-1), hh[..., 1].cumsum(-1)
+    tg, th = cg[..., -1:], ch[..., -1:]
+    gain = cg ** 2 / (ch + lam) + (tg - cg) ** 2 / (th - ch + lam) - tg ** 2 / (th + lam) - gamma     # as the kernel: not halved
+    valid = (hh[..., 1] > 0) & (ch >= min_child_weight) & (th - ch >= min_child_weight) & (th - ch > 0)
+    valid[..., -1] = False
+    gain = torch.where(valid, gain, torch.full_like(gain, -1.0))
+    n_nodes, p, nbins = gain.shape
+    flat = gain.reshape(n_nodes, -1)
+    best, arg = flat.max(1)
+    has = best > 0
+    feat, b = arg // nbins, arg % nbins
+    neg = -torch.ones_like(feat)
+    return torch.where(has, best, torch.zeros_like(best)).float(), torch.where(has, feat, neg), torch.where(has, b, neg)
+
+
 # ------------------------------------------------------------------------------------------------ path 2b
 # Replicate-batched gradient as a tcgen05 GEMM fused with its reduce-scatter (csrc/gemm_rs.cu).  EXPERIMENTAL: the kernel
 # compiles for sm_100a and has a GPU test, but it has not run on hardware yet - nothing in the package calls it by default.

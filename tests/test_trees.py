@@ -158,3 +158,25 @@ def test_gpu_xgboost_mode_matches_cpu_and_reference(aml):
     assert int((gb.importance_["gain"] > 0).sum()) == 6
     gb2 = TR.GradientBoosting(n_estimators=60, learning_rate=0.1, max_depth=3, mode="xgboost").fit(xtr, ytr)
     assert M.auc(gb2.predict_proba(xte), yte) > 0.93
+
+
+def test_gbm_large_sibling_subtraction_builds_the_same_trees_cpu():
+    """Level-wise large-cohort GBM on the torch backend: histogramming only the smaller child of every split and deriving
+    its sibling from the parent gives the same trees with less than half of the samples histogrammed."""
+    import torch
+    from consensusml_b200.models.gbm_large import GBMLarge, quantile_bin
+    from consensusml_b200.ops.metrics import auc
+    g = torch.Generator().manual_seed(3)
+    n, p = 2500, 30
+    x = torch.randn(n, p, generator=g)
+    beta = torch.zeros(p)
+    beta[:6] = torch.tensor([1.2, -1.0, 0.8, -0.8, 0.6, 0.5])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ beta + 0.8 * x[:, 6] * x[:, 7])).float()
+    bins, cuts = quantile_bin(x, 32)
+    full = GBMLarge(n_estimators=5, max_depth=4, nbins=32).fit(None, y, bins=bins, cuts=cuts)
+    sub = GBMLarge(n_estimators=5, max_depth=4, nbins=32, sibling_subtraction=True).fit(None, y, bins=bins, cuts=cuts)
+    for a, b in zip(full.trees, sub.trees):
+        assert torch.equal(a.feat, b.feat) and torch.equal(a.thr, b.thr)
+        assert (a.value - b.value).abs().max() < 1e-5
+    assert sub.samples_histogrammed_ < 0.55 * full.samples_histogrammed_
+    assert auc(sub.predict_proba(x), y) > 0.8
