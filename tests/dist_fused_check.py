@@ -55,6 +55,24 @@ def main():
         ok &= bool(torch.equal(again.cpu(), x[lo:hi]))
         print(f"[{rank}] shard_transpose fused == all_to_all: {ok}", flush=True)
     if cpu:
+        # sample-sharded GBM on the torch backend: every rank grows the same trees, with and without sibling subtraction
+        from consensusml_b200.models.gbm_large import GBMLarge, apply_cuts
+        gx, gy = synth(2000, 24, seed=3)
+        glo, ghi = shard_bounds(2000, world, rank)
+        cuts = torch.quantile(gx, torch.linspace(0, 1, 33)[1:-1], dim=0).t().contiguous()      # same cut points on every rank
+        gbins = apply_cuts(gx[glo:ghi], cuts)
+        sigs = []
+        for sub in (False, True):
+            gb = GBMLarge(n_estimators=4, max_depth=3, nbins=32, sibling_subtraction=sub).fit(None, gy[glo:ghi], bins=gbins, cuts=cuts)
+            sigs.append(torch.stack([t.feat.float().sum() * 131 + t.thr.float().sum() for t in gb.trees]))
+        both = torch.stack(sigs)
+        lo_s, hi_s = both.clone(), both.clone()
+        if world > 1:
+            dist.all_reduce(lo_s, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi_s, op=dist.ReduceOp.MAX)
+        ok &= bool(torch.equal(lo_s, hi_s)) and bool(torch.equal(both[0], both[1]))
+        if rank == 0:
+            print("gloo sharded GBM: trees identical across ranks and with sibling subtraction:", ok)
         fit = LL.fit(xl, yl, 0.02, n_total=n, max_iter=150, backend="unfused", step=step0)
         if rank == 0:
             err = float((fit.beta - ref_single.beta).abs().max())
