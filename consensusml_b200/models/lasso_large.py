@@ -176,3 +176,37 @@ def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_
             if d < tol:
                 break
     return LargeFit(beta, it, obj, step, history)
+
+
+def lambda_max(x_local: torch.Tensor, y_local: torch.Tensor, n_total: int, weights: Optional[torch.Tensor] = None) -> float:
+    """Smallest lambda with an all-zero solution (no intercept): ``max_j |x_j^T w (y - 1/2)| / n`` (one all-reduce)."""
+    w = weights.float() if weights is not None else torch.ones_like(y_local, dtype=torch.float32)
+    g = x_local.float().t() @ (w * (y_local.float() - 0.5))
+    all_reduce_(g)
+    return float(g.abs().max()) / n_total
+
+
+def fit_path(x_local: torch.Tensor, y_local: torch.Tensor, lams=None, *, n_lambda: int = 20, lambda_min_ratio: float = 0.05,
+             n_total: Optional[int] = None, max_iter: int = 300, tol: float = 1e-5, backend: str = "auto",
+             weights: Optional[torch.Tensor] = None):
+    """Warm-started path of the sharded solver over a descending lambda grid (default: geometric from ``lambda_max`` down to
+    ``lambda_min_ratio * lambda_max``, glmnet's construction).  The Lipschitz step is estimated once.  Returns
+    ``(lams, [LargeFit per lambda])``; every rank holds every coefficient vector."""
+    if n_total is None:
+        t = torch.tensor([x_local.shape[0]], dtype=torch.float64, device=x_local.device)
+        all_reduce_(t)
+        n_total = int(t.item())
+    if lams is None:
+        lmax = lambda_max(x_local, y_local, n_total, weights)
+        lams = np.geomspace(lmax, lmax * lambda_min_ratio, n_lambda)
+    lams = np.asarray(lams, dtype=np.float64)
+    if np.any(np.diff(lams) > 0):
+        raise ValueError("lambda grid must be descending")
+    step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
+    fits, beta = [], None
+    for lam in lams:
+        f = fit(x_local, y_local, float(lam), n_total=n_total, max_iter=max_iter, tol=tol, backend=backend, weights=weights,
+                beta0=beta, step=step)
+        beta = f.beta
+        fits.append(f)
+    return lams, fits

@@ -165,3 +165,23 @@ def test_mlseq_caret_learners_on_transformed_counts(counts100, method, tune):
     pred = model.predict(c[:, ~tr])
     assert float((pred == y[~tr]).float().mean()) >= 0.75
     assert 1 <= len(D.selected_genes(model, [f"g{i}" for i in range(100)])) <= 100
+
+
+def test_sharded_solver_path_agrees_with_coordinate_descent():
+    """FISTA path of the large-cohort solver (torch backend) against the glmnet-semantics path solver on the same grid:
+    lambda_max gives the empty model, every later solution matches to optimisation tolerance."""
+    from consensusml_b200.models import lasso_large as LL
+    from consensusml_b200.ops import lasso as K
+    g = torch.Generator().manual_seed(0)
+    n, p = 400, 60
+    x = torch.randn(n, p, generator=g)
+    beta = torch.zeros(p)
+    beta[:5] = torch.tensor([1.5, -1.2, 1.0, -0.8, 0.6])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ beta)).float()
+    lams, fits = LL.fit_path(x, y, n_lambda=6, max_iter=3000, tol=1e-7)
+    assert int((fits[0].beta != 0).sum()) == 0 and int((fits[-1].beta != 0).sum()) > 5
+    ref = K.lognet_path(x.double(), y.double(), torch.ones(1, n, dtype=torch.float64), lams, thresh=1e-12)
+    for i in range(len(lams)):
+        assert (fits[i].beta.double() - ref.dense(0)[i]).abs().max() < 5e-6
+    with pytest.raises(ValueError):
+        LL.fit_path(x, y, lams=[0.01, 0.1])
