@@ -64,7 +64,7 @@ def data_prep_columns(df: pd.DataFrame, var: str, gene_slice: Tuple[int, Optiona
     take: List[int] = []
     for cls in (1, 0):
         sub = df2.loc[df2["Low Risk"] == cls, gene_cols].to_numpy(dtype=np.float32)
-        idx = variance_topk(torch.from_numpy(sub), k, largest=reverse).tolist()
+        idx = variance_topk(torch.from_numpy(np.array(sub)), k, largest=reverse).tolist()
         for i in idx:
             pos = i + lo
             if pos not in take:

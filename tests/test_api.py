@@ -89,3 +89,31 @@ def test_model_comp_runs_on_real_cohort_cpu(aml, capsys):
     out = capsys.readouterr().out
     assert "Ensemble Log Loss" in out and "XGBoost Log Loss" in out
     assert xgb.extras["log_loss"]["ensemble"] < 0.6
+
+
+def test_walkthrough_on_a_synthetic_frame_cpu(tmp_path):
+    """The notebook's end-to-end flow (variance-selected / random / all genes, L1 logistic, set intersections, holdout)."""
+    import pandas as pd
+    from consensusml_b200.api import walkthrough as W
+    rng = np.random.default_rng(7)
+    n, genes = 140, 300
+    clin = {f"c{i}": rng.integers(0, 4, n) for i in range(84)}
+    df = pd.DataFrame(clin).rename(columns={"c1": "Diagnostic ID", "c2": "Risk group"})
+    df["Diagnostic ID"] = rng.choice(["09A", "03A", "01A"], n)
+    risk = rng.choice(["Low", "Standard", "High"], n, p=[0.45, 0.3, 0.25])
+    df["Risk group"] = risk
+    x = rng.normal(size=(n, genes))
+    x[:, :12] += (risk == "Low")[:, None] * 1.6                      # twelve informative genes
+    g = pd.DataFrame(x, columns=[f"ENSG{i:05d}" for i in range(genes)])
+    tail = pd.DataFrame({f"t{i}": rng.integers(0, 3, n) for i in range(3)})   # + the added "Low Risk" = the 4 trailing columns
+    frame = pd.concat([df, g, tail], axis=1)
+    cols = W.random_gene_columns(genes, 50, 84, np.random.default_rng(1))
+    assert 40 <= len(cols) <= 50 and min(cols) >= 84 and max(cols) < 84 + genes and len(set(cols)) == len(cols)
+    out = W.run_walkthrough(frame, k_var=40, k_random=60, n_random=2, device="cpu", tree_scale=0.03, out_csv=str(tmp_path / "lasso_genes.csv"))
+    assert set(out["experiments"]) == {"variance_selected", "random_1", "random_2", "all_genes", "l1_logistic"}
+    assert out["experiments"]["all_genes"]["n_genes"] == genes and out["experiments"]["all_genes"]["ensemble"] < 0.69
+    informative = {f"ENSG{i:05d}" for i in range(12)}
+    assert len(informative & set(out["lasso_genes"])) >= 6
+    assert set(out["intersections"]) == {"xgboost&random_forest", "xgboost&lasso", "random_forest&lasso", "xgboost&random_forest&lasso"}
+    assert out["membership"]["n_models"].max() <= 3 and out["holdout"]["l1_logistic"] < 0.69
+    assert (tmp_path / "lasso_genes.csv").exists()
