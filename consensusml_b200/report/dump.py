@@ -3,7 +3,8 @@ out, their data are written as CSV / NPZ).
 
 Reference plots: volcano (JSmith_code/Differential_Expression_and_Lasso.Rmd:33-85), DEG heatmaps with clustering
 (cml_targetaml_seanalysis.Rmd:509-623), lasso performance curves (:806-881), Spearman correlation heatmaps and
-densities (:883-1017), RF / XGB importance bars and SVM weight bars (:697-713, 1098-1143, 1267-1293)."""
+densities (:883-1017), RF / XGB importance bars and SVM weight bars (:697-713, 1098-1143, 1267-1293), per-sample log2-CPM
+boxplots by cohort (JSmith_code/Normalization_and_Batch_Effect_Investigation.Rmd:120-140)."""
 from __future__ import annotations
 
 import os
@@ -31,6 +32,31 @@ def top_quantile(values: np.ndarray, gene_ids: Sequence[str], q: float = 0.99, a
     idx = np.flatnonzero(v > thr)
     idx = idx[np.argsort(-v[idx])]
     return pd.DataFrame({"gene": [gene_ids[i] for i in idx], "value": values[idx]})
+
+
+def cohort_group(sample_id: str) -> str:
+    """Cohort from the TARGET project code inside a barcode (``TARGET.30.`` NBL, ``.20.`` AML, ``.50.`` WT, ``.52.`` RT, ...;
+    Normalization_and_Batch_Effect_Investigation.Rmd:120-126)."""
+    parts = sample_id.replace("-", ".").split(".")
+    code = parts[1] if len(parts) > 1 else ""
+    return {"30": "NBL", "20": "AML", "21": "AML", "50": "WT", "51": "CCSK", "52": "RT", "40": "OS"}.get(code, "NA")
+
+
+def boxplot_stats(logcpm: torch.Tensor, sample_ids: Sequence[str]) -> pd.DataFrame:
+    """Per-sample box-and-whisker numbers of a genes x samples log2-CPM matrix (median, hinges, 1.5 IQR whiskers, outlier
+    count), ordered by median like the reference's ``reorder(USI, Log2.CPM, FUN = median)`` plot, with the cohort label."""
+    x = logcpm.double()
+    q = torch.quantile(x, torch.tensor([0.25, 0.5, 0.75], dtype=torch.float64, device=x.device), dim=0)
+    iqr = q[2] - q[0]
+    lo_f, hi_f = q[0] - 1.5 * iqr, q[2] + 1.5 * iqr
+    inside = (x >= lo_f) & (x <= hi_f)
+    big, small = torch.finfo(torch.float64).max, torch.finfo(torch.float64).min
+    whisk_lo = torch.where(inside, x, torch.full_like(x, big)).amin(0)
+    whisk_hi = torch.where(inside, x, torch.full_like(x, small)).amax(0)
+    df = pd.DataFrame({"sample": list(sample_ids), "group": [cohort_group(s) for s in sample_ids], "median": q[1].cpu().numpy(),
+                       "q1": q[0].cpu().numpy(), "q3": q[2].cpu().numpy(), "whisker_low": whisk_lo.cpu().numpy(),
+                       "whisker_high": whisk_hi.cpu().numpy(), "n_outliers": (~inside).sum(0).cpu().numpy()})
+    return df.sort_values("median", kind="stable").reset_index(drop=True)
 
 
 def lasso_rep_curves(results) -> pd.DataFrame:

@@ -40,3 +40,22 @@ def test_qc_summary_balance_and_multicohort(aml):
     assert sub["deg"].n_samples == 10 and sub["deg_copy"].n_samples == 10
     with pytest.raises(ValueError):
         mc.add("bad", aml.select_samples(np.arange(5)))
+
+
+def test_boxplot_stats_match_numpy_percentiles():
+    """Data behind the per-sample log2-CPM boxplots of the normalisation notebook."""
+    import numpy as np
+    import torch
+    from consensusml_b200.report.dump import boxplot_stats, cohort_group
+    rng = np.random.default_rng(0)
+    x = rng.normal(size=(500, 6)) + np.arange(6)[None, :] * 0.3
+    x[0, 2] = 40.0                                                  # one far outlier
+    ids = ["TARGET.20.PAAAAA.09A.01R", "TARGET.30.PABBBB.01A.01R", "TARGET.50.PACCCC.01A.01R", "TARGET-20-PADDDD-03A-01R",
+           "TARGET.52.PAEEEE.01A.01R", "X"]
+    df = boxplot_stats(torch.from_numpy(x), ids)
+    assert df["median"].is_monotonic_increasing
+    assert [cohort_group(i) for i in ids] == ["AML", "NBL", "WT", "AML", "RT", "NA"]
+    row = df[df["sample"] == ids[2]].iloc[0]
+    q1, med, q3 = np.percentile(x[:, 2], [25, 50, 75])
+    assert abs(row["median"] - med) < 1e-12 and abs(row["q1"] - q1) < 1e-12 and abs(row["q3"] - q3) < 1e-12
+    assert row["whisker_high"] < 40 and row["n_outliers"] >= 1
