@@ -160,6 +160,69 @@ def qc_summary(clinical: pd.DataFrame) -> dict:
     return out
 
 
+def r_summary(values) -> dict:
+    """R's ``summary()`` of a numeric vector: min, quartiles (type-7 quantiles), median, mean, max and the NA count."""
+    v = pd.to_numeric(pd.Series(values), errors="coerce")
+    na = int(v.isna().sum())
+    v = v.dropna().to_numpy(dtype=float)
+    if v.size == 0:
+        return {"n": 0, "na": na}
+    q1, med, q3 = np.quantile(v, [0.25, 0.5, 0.75])
+    return {"n": int(v.size), "min": float(v.min()), "q1": float(q1), "median": float(med), "mean": float(v.mean()),
+            "q3": float(q3), "max": float(v.max()), "na": na}
+
+
+def qc_report(clinical: pd.DataFrame) -> dict:
+    """Everything ``aml-target_qc-scripts_SeanMaden.R:17-71`` prints: gender and CNS-disease tables, ``summary()`` of age
+    (days and years), blast percentage and survival times, the young / old classifier (age below / not below the median),
+    its cross-table with gender and the survival summaries inside each age class."""
+    out = {"n": len(clinical)}
+    for col, key in (("Gender", "gender"), ("CNS disease", "cns_disease")):
+        if col in clinical:
+            out[key] = clinical[col].value_counts().sort_index().to_dict()
+    age = pd.to_numeric(clinical.get("Age at Diagnosis in Days"), errors="coerce") if "Age at Diagnosis in Days" in clinical else None
+    if age is not None:
+        out["age_days"] = r_summary(age)
+        out["age_years"] = r_summary(age / 365)
+        med = float(np.nanmedian(age))
+        cls = np.where(age < med, "young", "old")
+        out["median_age_days"] = med
+        out["age_class"] = pd.Series(cls).value_counts().to_dict()
+        if "Gender" in clinical:
+            out["age_class_by_gender"] = pd.crosstab(pd.Series(cls, name="class.age"), clinical["Gender"].reset_index(drop=True))
+        for col, key in (("Overall Survival Time in Days", "os_days"), ("Event Free Survival Time in Days", "efs_days")):
+            if col in clinical:
+                out[key] = r_summary(clinical[col])
+                for c in ("young", "old"):
+                    out[f"{key}_{c}"] = r_summary(clinical[col].to_numpy()[cls == c])
+    if "Bone marrow leukemic blast percentage (%)" in clinical:
+        out["bm_blast_pct"] = r_summary(clinical["Bone marrow leukemic blast percentage (%)"])
+    return out
+
+
+def barcode_table(sample_ids: Sequence[str]) -> dict:
+    """Split TARGET barcodes (``TARGET-20-PABCDE-09A-01R``, ``-`` or ``.`` separated) into their five fields and count the
+    tissue codes (09A, 03A, ...) and portion codes (01R, ...) - the barcode matrix of the QC script (lines 74-87)."""
+    rows = [str(s).replace("-", ".").split(".") for s in sample_ids]
+    rows = [r for r in rows if len(r) >= 5]
+    bcm = pd.DataFrame([r[:5] for r in rows], columns=["program", "project", "case", "tissue", "portion"])
+    return {"matrix": bcm, "tissue": bcm["tissue"].value_counts().sort_index().to_dict(),
+            "portion": bcm["portion"].value_counts().sort_index().to_dict()}
+
+
+def survival_density_groups(clinical: pd.DataFrame) -> pd.DataFrame:
+    """Long table (group, survival.time) of the four curves of the "Survival Time by Age Classifier" plot (lines 96-113):
+    overall and event-free survival for the young and the old class.  Densities come from ``stats.correlation.kde``."""
+    age = pd.to_numeric(clinical["Age at Diagnosis in Days"], errors="coerce")
+    cls = np.where(age < float(np.nanmedian(age)), "young", "old")
+    parts = []
+    for c in ("young", "old"):
+        for col, tag in (("Overall Survival Time in Days", "overallsurv"), ("Event Free Survival Time in Days", "efsurv")):
+            v = pd.to_numeric(clinical[col], errors="coerce").to_numpy()[cls == c]
+            parts.append(pd.DataFrame({"group": f"{c}.{tag}", "survival.time": v[~np.isnan(v)]}))
+    return pd.concat(parts, ignore_index=True)
+
+
 def balance_test(labels_a: Sequence, labels_b: Sequence) -> dict:
     """Chi-square independence test of two categorical columns, e.g. gender vs binarised risk
     (cml_targetaml_seanalysis.Rmd:462,470: p = 0.8044 for gender, 0.6591 for age class)."""

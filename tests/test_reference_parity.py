@@ -111,3 +111,26 @@ def test_model_comp_data_preparation_equals_the_reference():
         la = ref.model_prep_loc(a_df, names)
     lb = ours.model_prep_loc(b_df, names)
     assert np.array_equal(np.asarray(la[0]), np.asarray(lb[0])) and np.array_equal(np.asarray(la[3]), np.asarray(lb[3]))
+
+
+def test_qc_report_reproduces_the_numbers_committed_in_the_qc_script():
+    """aml-target_qc-scripts_SeanMaden.R records its outputs as comments (lines 17-71); ``Clinical_Data/AML_dataframe.csv`` is
+    in the reference tree, so they can be checked directly."""
+    from consensusml_b200.cohort import ops as CO
+    cd = pd.read_csv("/root/reference/Clinical_Data/AML_dataframe.csv", index_col=0)
+    q = CO.qc_report(cd)
+    assert q["gender"] == {"Female": 96, "Male": 91} and q["cns_disease"] == {"No": 175, "Yes": 12}
+    a = q["age_days"]
+    assert (a["min"], round(a["q1"]), a["median"], round(a["mean"]), round(a["q3"]), a["max"]) == (137, 966, 3273, 3205, 5251, 8231)
+    assert abs(q["age_years"]["median"] - 8.9671) < 1e-4 and abs(q["age_years"]["max"] - 22.5507) < 1e-4
+    b = q["bm_blast_pct"]
+    assert (b["min"], b["q1"], b["median"], round(b["mean"], 2), b["q3"], b["max"], b["na"]) == (14.0, 58.25, 73.6, 70.92, 89.0, 100.0, 5)
+    tab = q["age_class_by_gender"]
+    assert tab.loc["old"].to_dict() == {"Female": 46, "Male": 48} and tab.loc["young"].to_dict() == {"Female": 50, "Male": 43}
+    assert (q["os_days"]["min"], q["os_days"]["q1"], q["os_days"]["median"], q["os_days"]["max"]) == (112.0, 501.5, 1229.0, 4022.0)
+    assert (q["efs_days"]["median"], q["efs_days"]["q3"]) == (392.0, 861.5)
+    assert q["os_days_young"]["median"] == 1464 and q["os_days_old"]["median"] == 924 and q["efs_days_old"]["q1"] == 262.5
+    bc = CO.barcode_table(cd["entity_submitter_id"])
+    assert set(bc["tissue"]) <= {"01A", "02A", "03A", "04A", "06A", "09A", "11A", "40A"} and sum(bc["tissue"].values()) == len(cd)
+    g = CO.survival_density_groups(cd)
+    assert set(g["group"]) == {"young.overallsurv", "young.efsurv", "old.overallsurv", "old.efsurv"}
