@@ -230,6 +230,10 @@ int cml_host_lognet_path(int B, int n, int p, int nlam, const double* xt, const 
 /* Visit counters of the calling thread since the last call: screened-sweep steps, active-sweep steps, KKT gradient
  * evaluations, curvature evaluations, columns read by IRLS refreshes, IRLS iterations, active sweeps, screened sweeps. */
 void cml_host_lognet_counters(long long* out8);
+/* 0 (default): glmnet's loop statement for statement; 1: covariance updates inside the active-set sweeps (same iteration). */
+void cml_host_lognet_set_active_mode(int mode);
+/* Host build of the eBayes kernel's Student-t tail (csrc/tdist.cuh): two-sided p of n statistics, df[i * df_stride]. */
+void cml_host_t_two_sided(const double* t, const double* df, int df_stride, int n, double* p_out);
 /* Per-sample count files -> gene x sample matrix (Cat_Expn_Data.r:7-49): scan the first file for the gene ids, read them
  * back one by one, then parse all files in parallel (mmap) into out[genes][n_files]; status[f] = 0 or the negative line
  * number of the first problem in file f. */

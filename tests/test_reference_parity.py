@@ -134,3 +134,40 @@ def test_qc_report_reproduces_the_numbers_committed_in_the_qc_script():
     assert set(bc["tissue"]) <= {"01A", "02A", "03A", "04A", "06A", "09A", "11A", "40A"} and sum(bc["tissue"].values()) == len(cd)
     g = CO.survival_density_groups(cd)
     assert set(g["group"]) == {"young.overallsurv", "young.efsurv", "old.overallsurv", "old.efsurv"}
+
+
+def test_gpu_student_t_tail_reproduces_the_reference_deg_table_pvalues():
+    """The reference's committed limma table (1998 DEGs: t, P.Value, adj.P.Val) is consistent with one total df (residual 94 +
+    prior 1.885) and 17,445 tested genes.  The eBayes kernel's Student-t tail - the same source compiled for the host
+    (csrc/tdist.cuh) - must return its P.Value column."""
+    import ctypes
+    from scipy import optimize, stats
+    from consensusml_b200 import _native
+    from consensusml_b200.oracle.limma import bh_adjust
+    d = pd.read_csv("/root/reference/JSmith_code/Results/TARGET_AML_High.Std.Risk_vs_LowRisk_DEGs.csv", index_col=0)
+    t, p = d["t"].to_numpy(), d["P.Value"].to_numpy()
+    df = optimize.brentq(lambda v: np.log(2 * stats.t.sf(abs(t[0]), v)) - np.log(p[0]), 5, 5000)
+    assert 95.8 < df < 96.0                                        # 96 training samples - 2 groups + df.prior
+    out = np.empty_like(t)
+    dfv = np.array([df])
+    lib = _native.host()
+    lib.cml_host_t_two_sided.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    lib.cml_host_t_two_sided.restype = None
+    lib.cml_host_t_two_sided(t.ctypes.data, dfv.ctypes.data, 0, t.size, out.ctypes.data)
+    assert np.max(np.abs(out / p - 1)) < 1e-9                      # p-values from 5e-15 to 5e-3
+    # BH: adj.P.Val = P.Value * n / rank (then a running minimum), with rank counted among ALL tested genes; the table drops
+    # genes with |logFC| <= 1, so rank >= row number.  n = 17,445 makes the implied ranks integers, increasing down the table.
+    n_tested = int(round(d["adj.P.Val"].iloc[0] / p[0]))
+    assert n_tested == 17445
+    rank = n_tested * p / d["adj.P.Val"].to_numpy()
+    near_int = np.abs(rank - np.round(rank)) < 1e-6
+    assert near_int.mean() > 0.5                                   # the other rows take their value from a later gene (running min)
+    r = np.round(rank[near_int])
+    assert (np.diff(r) > 0).all() and (r >= np.flatnonzero(near_int) + 1).all()
+    # and our BH on a vector with those ranks filled in reproduces the column where it is rank-determined
+    full = np.ones(n_tested)
+    full[(r - 1).astype(int)] = p[near_int]
+    order_fill = np.setdiff1d(np.arange(int(r.max())), (r - 1).astype(int))
+    full[order_fill] = np.interp(order_fill, (r - 1), p[near_int])          # any monotone filler between known ranks
+    ours = bh_adjust(full)[(r - 1).astype(int)]
+    assert np.max(np.abs(ours / d["adj.P.Val"].to_numpy()[near_int] - 1)) < 1e-6
