@@ -124,3 +124,25 @@ def test_cli_concat_then_run_on_counts(tmp_path, capsys):
     assert rc == 0
     summary = json.loads(capsys.readouterr().out)
     assert summary["lasso"]["auc"] > 0.8 and os.path.exists(out / "standouttable.csv") and os.path.exists(out / "consensus_rank.csv")
+
+
+def test_cli_normalize_and_de_on_counts_csv(tmp_path, capsys):
+    """`normalize` writes the TMM log2-CPM matrix, `de` the limma-voom table in the reference's column layout."""
+    import pandas as pd
+    from consensusml_b200.cli.main import main
+    from consensusml_b200.io.counts import write_matrix_csv
+    from consensusml_b200.io.synthetic import nb_counts
+    c, g = nb_counts(1500, 24, seed=9, n_de=120)
+    genes, samples = [f"ENSG{i:011d}.2" for i in range(1500)], [f"S{j:02d}" for j in range(24)]
+    write_matrix_csv(str(tmp_path / "counts.csv"), torch.from_numpy(c), genes, samples)
+    pd.DataFrame({"sample": samples, "group": g}).to_csv(tmp_path / "groups.csv", index=False)
+    assert main(["normalize", "--counts", str(tmp_path / "counts.csv"), "io.out_dir=" + str(tmp_path), "device=cpu"]) == 0
+    info = json.loads(capsys.readouterr().out)
+    norm = pd.read_csv(tmp_path / "TMMCPM_log2_Norm_Counts.csv", index_col=0)
+    assert norm.shape == (info["genes_kept"], 24) and 0.5 < info["norm_factor_range"][0] <= 1 <= info["norm_factor_range"][1] < 2
+    assert main(["de", "--counts", str(tmp_path / "counts.csv"), "--groups", str(tmp_path / "groups.csv"), "io.out_dir=" + str(tmp_path),
+                 "device=cpu"]) == 0
+    info = json.loads(capsys.readouterr().out)
+    deg = pd.read_csv(info["csv"], index_col=0)
+    assert list(deg.columns) == ["logFC", "AveExpr", "t", "P.Value", "adj.P.Val", "B"] and len(deg) == info["degs"] > 10
+    assert (deg["adj.P.Val"] < 0.05).all() and (deg["logFC"].abs() > 1).all() and deg["P.Value"].is_monotonic_increasing
