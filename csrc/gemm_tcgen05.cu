@@ -10,20 +10,27 @@
 //   * k-means / hclust distance blocks.
 // The reference delegates all of these to CPU libraries; nothing in it is a GEMM kernel.
 //
-// Structure (one CTA per SM, persistent over output tiles, 320 threads):
+// Two kernels share one structure (one CTA per SM, persistent over output tiles, 320 threads):
+//   gemm_tn_pair_kernel  - CTA pairs (cta_group::2): the two SMs of a TPC own one 256 x 256 tile; used whenever there are
+//                          enough such tiles for every pair (see the comment above the kernel);
+//   gemm_tn_kernel<BN>   - single CTA, 128 x BN tiles (BN = 128 | 256) for small or ragged problems.
 //   warp 0     : TMA producer - cp.async.bulk.tensor 2-D boxes (64 bf16 x 128 rows, 128B swizzle) of A and B
 //                into a STAGES-deep shared-memory ring, completion on `full` mbarriers;
-//   warp 1     : allocates TMEM, then a single thread issues tcgen05.mma (M=128, N=BN, K=16, cta_group::1)
-//                straight from the swizzled tiles via shared-memory descriptors; tcgen05.commit releases
+//   warp 1     : allocates TMEM, then a single thread issues tcgen05.mma (K=16 per instruction, four per 64-wide
+//                k-block) straight from the swizzled tiles via shared-memory descriptors; tcgen05.commit releases
 //                ring slots (`empty`) and publishes finished accumulators (`tmem_full`);
-//   warps 2..9 : epilogue - tcgen05.ld the fp32 accumulator (32 lanes x 32 columns per warp per load), apply
-//                the fused epilogue (scale | RBF exponent with row/column squared norms), stage the chunk in
-//                swizzled shared memory and write it with one TMA tensor store.
-//                Two accumulator stages in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
-// The B operand may be spread over several "sources" (one tensor map + norm vector each).  With one source
-// it is a plain GEMM; with the sources being the symmetric-memory buffers of the NVLink peers it is the fused
-// all-gather -> GEMM: the TMA engine pulls peer tiles over NVLink directly into shared memory, so no
-// gathered copy of X is ever materialised (see consensusml_b200/parallel/fused.py).
+//   warps 2..9 : epilogue - two warps per TMEM lane quarter, each takes half of the columns: tcgen05.ld of chunk
+//                c+1 in flight while chunk c (32 lanes x 32 fp32 columns) gets the fused epilogue (scale | RBF
+//                exponent | squared distance with row / column norms), is staged in 128B-swizzled shared memory
+//                and written with ONE TMA tensor store.  Two accumulator stages in TMEM let the epilogue of
+//                tile t overlap the MMAs of tile t+1.
+// Tiles are visited in groups of 8 m-tiles (tile_to_mn) so that the operand panels stay L2-resident.
+// The B operand may be spread over several "sources" (one tensor map + norm vector each).  With one source it is a
+// plain GEMM.  With the sources being the symmetric-memory buffers of the NVLink peers it is the fused all-gather ->
+// GEMM, in two forms: direct (the TMA producer reads peer tiles; correct but every tile crosses NVLink once per
+// m-tile because peer reads are not cached in the local L2) and STAGED (the default for world > 1): the first
+// n_copiers CTAs of the same launch bulk-copy the peers' blocks into a local staging buffer and publish per-tile
+// flags, the GEMM CTAs consume tiles as their flags arrive (consensusml_b200/parallel/fused.py).
 #include <cuda_bf16.h>
 
 #include <cmath>
