@@ -7,7 +7,9 @@
 // sequential cyclic coordinate descent, so the parallel axis on a B200 is the *replicate*
 // (fold x bootstrap x exclusion set), not the coordinate.
 //
-// Design: ONE WARP = ONE PATH FIT.  A CTA is a single warp, 16-32 of them are resident per SM, and each
+// Design: ONE WARP = ONE PATH FIT.  A CTA is a single warp, 20 of them are resident per SM (96 registers: the sweeps
+// keep three prefetch slots and must not spill - a spilled prefetch is a blocking load), further replicates are drawn from a
+// global counter as warps finish, and each
 // runs the whole 100-lambda path of one replicate without any block-level barrier.  The sample axis is
 // spread over the 32 lanes (NPL samples per lane held in registers: residual r and IRLS weight v), a
 // coordinate's gradient is a lane-local FMA chain plus one butterfly reduction, and the scalar
@@ -22,6 +24,9 @@
 // statement by statement (that file is validated against the reference's stored glmnet objects), with one
 // exact shortcut: a KKT pass is skipped when no coefficient has changed since the gradients were last
 // computed (true for every lambda above lambda_max), because it would recompute identical numbers.
+// Two evaluation-order changes that leave the iteration itself untouched: screened features outside the active list are
+// evaluated sixteen at a time against the current residual (they cannot change it unless they enter - see sweep_screened),
+// and the KKT / curvature passes reduce sixteen dot products with one transposed butterfly (warp_sum16_transposed).
 #include <cfloat>
 #include <cmath>
 
