@@ -57,6 +57,7 @@ def main():
     ap.add_argument("--nodes", type=int, default=4)
     ap.add_argument("--bins", type=int, default=256)
     ap.add_argument("--skip", default="")
+    ap.add_argument("--experimental", action="store_true", help="also time the kernels / modes that are still opt-in")
     args = ap.parse_args()
     rank, world, dev = D.init()
     hbm, tf, how = peaks()
@@ -160,6 +161,39 @@ def main():
         t_roof = max(flops / (tf * 1e12), link / (NVLINK_GBS * 1e9))
         emit(path="gram_allgather_tcgen05_rbf", rows_per_gpu=m, genes=p, ms=ms, tflops=flops / ms / 1e9,
              frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
+    if args.experimental:
+        # ---- opt-in: tcgen05 GEMM fused with the reduce-scatter (replicate-batched gradient), B = 256 residual columns
+        n, p, B = args.rows, args.genes, 256
+        ld = (n + 7) // 8 * 8
+        xt = torch.randn(p, ld, device=dev, dtype=torch.bfloat16)
+        rt = torch.randn(B, ld, device=dev, dtype=torch.bfloat16)
+        for use_tma in (False, True):
+            op = F.XtrGemmReduceScatter(p, B, dev, use_tma_reduce=use_tma)
+
+            def run():
+                op.launch(xt, rt)
+                op.wait()
+            run()
+            ms = timed(run, args.reps, flush)
+            flops = 2.0 * p * B * ld
+            byts = (p + B) * ld * 2.0
+            link = 4.0 * p * B * (world - 1) / world
+            t_roof = max(flops / (tf * 1e12), byts / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
+            emit(path="xtr_gemm_reduce_scatter", tma_reduce=use_tma, rows_per_gpu=n, genes=p, B=B, ms=ms, tflops=flops / ms / 1e9,
+                 hbm_gbs=byts / ms / 1e6, frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
+            del op
+        del xt, rt
+        if world > 1 and "gram" not in args.skip:
+            from consensusml_b200.ops import gemm as G
+            m = args.gram_rows
+            xg = torch.randn(m, p, device=dev)
+            cache = {}
+            for grouped in (False, True):
+                G.set_staged_grouping(grouped)
+                F.gram_allgather(xg, kernel="radial", n_total=m * world, cache=cache)
+                ms = timed(lambda: F.gram_allgather(xg, kernel="radial", n_total=m * world, cache=cache), args.reps, flush)
+                emit(path="gram_allgather_whole_call", staged_grouped=grouped, rows_per_gpu=m, genes=p, ms=ms)
+            G.set_staged_grouping(False)
     if "transpose" not in args.skip:
         # ---- path 4: sample-shard -> gene-shard transpose, 32768 samples per GPU x 20k genes fp32 (2.6 GB per GPU)
         from consensusml_b200.parallel import transpose as TR

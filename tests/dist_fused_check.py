@@ -161,6 +161,46 @@ def main():
         same = bool(lo_s.item() == hi_s.item())
         print(f"[{rank}] gbm_large auc {a:.4f} trees identical across ranks: {same} top genes {torch.argsort(-gb.importance_gain_)[:4].tolist()}", flush=True)
         ok &= a > 0.85 and same
+    if not cpu and os.environ.get("CML_EXPERIMENTAL") == "1":
+        # ---- opt-in: kernels / modes written while the GPUs were closed (not part of the default verdict until proven)
+        from consensusml_b200.ops import gemm as G
+        from consensusml_b200.models.gbm_large import GBMLarge
+        xok = True
+        B = 64
+        g = torch.Generator().manual_seed(21)
+        Rfull = torch.randn(n, B, generator=g)
+        ld = (hi - lo + 7) // 8 * 8
+        xt = torch.zeros(p, ld, dtype=torch.bfloat16, device=dev)
+        xt[:, : hi - lo] = xl.t().bfloat16()
+        rt32 = torch.zeros(B, ld, device=dev)
+        rt32[:, : hi - lo] = Rfull[lo:hi].t().to(dev)
+        for use_tma in (False, True):
+            op = F.XtrGemmReduceScatter(p, B, dev, use_tma_reduce=use_tma)
+            for rt in (rt32.bfloat16(), F.split_bf16(rt32)):
+                op.launch(xt, rt)
+                op.wait()
+                torch.cuda.synchronize()
+                got = op.result().clone()
+                ref = F.xtr_gemm_rs_unfused(xt, rt, p, B, op.genes_per_rank)
+                err = float((got - ref).abs().max() / ref.abs().max())
+                print(f"[{rank}] EXPERIMENTAL gemm_rs tma={use_tma} rows={rt.shape[0]} rel err {err:.2e}", flush=True)
+                xok &= err < 2e-3
+                torch.cuda.synchronize(); op.bufs[0].barrier()
+        G.set_staged_grouping(True)
+        got_g = F.gram_allgather(xl, kernel="radial", n_total=n)
+        G.set_staged_grouping(False)
+        got_p = F.gram_allgather(xl, kernel="radial", n_total=n)
+        xok &= bool(torch.equal(got_g, got_p))
+        print(f"[{rank}] EXPERIMENTAL staged grouped order equals plain order: {bool(torch.equal(got_g, got_p))}", flush=True)
+        gx, gy = synth(4000, 64, seed=3)
+        glo, ghi = shard_bounds(4000, world, rank)
+        a = GBMLarge(n_estimators=4, max_depth=3, nbins=64).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
+        b = GBMLarge(n_estimators=4, max_depth=3, nbins=64, sibling_subtraction=True).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
+        same = all(torch.equal(s_.feat, t_.feat) and torch.equal(s_.thr, t_.thr) for s_, t_ in zip(a.trees, b.trees))
+        print(f"[{rank}] EXPERIMENTAL sibling subtraction on the fused histogram path: same trees {same}, samples histogrammed "
+              f"{a.samples_histogrammed_} -> {b.samples_histogrammed_}", flush=True)
+        xok &= same
+        print(f"[{rank}] EXPERIMENTAL verdict: {'OK' if xok else 'FAILED'}", flush=True)
     t = torch.tensor([1.0 if ok else 0.0], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
