@@ -21,7 +21,8 @@ from consensusml_b200.runtime import config as C
 
 
 def main():
-    dev = torch.device("cuda")
+    cpu = "--cpu" in sys.argv                      # dry run of the script logic without a GPU (use with --small)
+    dev = torch.device("cpu" if cpu else "cuda")
     small = "--small" in sys.argv
     genes, sizes = (6000, (40, 40, 30, 30)) if small else (60488, (145, 160, 70, 99))
     t0 = time.perf_counter()
@@ -33,16 +34,17 @@ def main():
         idx = rng.permutation(np.flatnonzero(label == c))
         train[idx[: len(idx) // 3]] = False
     out_dir = tempfile.mkdtemp(prefix="pancancer_")
-    cfg = C.load(None, ["io.out_dir=" + out_dir, "device=cuda", "lasso.exclusion_reps=3", "lasso.nfolds=5", "rf.n_trees=[2000]",
+    cfg = C.load(None, ["io.out_dir=" + out_dir, ("device=cpu" if cpu else "device=cuda"), "lasso.exclusion_reps=3", "lasso.nfolds=5", "rf.n_trees=[2000]",
                         'gbm.reps=[{"max_depth": 3, "nrounds": 50}]', "mlp.enabled=false"])
     c_dev = torch.from_numpy(counts).to(dev)
     ids = [f"ENSG{i:011d}.1" for i in range(genes)]
-    torch.cuda.synchronize(); t0 = time.perf_counter()
+    sync = (lambda: None) if cpu else torch.cuda.synchronize
+    sync(); t0 = time.perf_counter()
     co = pipeline.multiclass_cohort_from_counts(c_dev, ids, [f"s{i}" for i in range(label.size)], label, train, cfg)
-    torch.cuda.synchronize(); prep_s = time.perf_counter() - t0
+    sync(); prep_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     s = pipeline.run_multiclass(cfg, co, class_names={0: "AML", 1: "NBL", 2: "WT", 3: "RT"})
-    torch.cuda.synchronize(); fit_s = time.perf_counter() - t0
+    sync(); fit_s = time.perf_counter() - t0
     print(json.dumps({"config": "pan-cancer multiclass (synthetic counts of the reference's shape)", "genes": genes, "samples": int(label.size),
                       "classes": s["classes"], "prefilter_genes": co.n_genes, "normalise_plus_4x_voom_s": round(prep_s, 3),
                       "one_vs_rest_ensemble_plus_consensus_s": round(fit_s, 3), "total_s": round(prep_s + fit_s, 3),

@@ -21,22 +21,25 @@ from consensusml_b200.ops.replicate import replicate_weights
 
 
 def main():
-    dev = torch.device("cuda")
+    cpu = "--cpu" in sys.argv                      # dry run of the script logic without a GPU (use with --small)
+    n_boot = 8 if "--small" in sys.argv else 1000
+    dev = torch.device("cpu" if cpu else "cuda")
+    sync = (lambda: None) if cpu else torch.cuda.synchronize
     co = datasets.load_target_aml()
     tr, _ = co.split()
-    x, y = tr.design(torch.float32).to(dev), tr.labels().to(dev).float()
+    x, y = tr.design(torch.float64 if cpu else torch.float32).to(dev), tr.labels().to(dev).to(torch.float64 if cpu else torch.float32)
     lam = K.default_lambda_grid()
     alphas = (0.25, 0.5, 0.75, 1.0)
-    L.stability_selection(x, y, lam, n_boot=64, alphas=(1.0,))                      # warm-up
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    out = L.stability_selection(x, y, lam, n_boot=1000, alphas=alphas, seed=1)
-    torch.cuda.synchronize(); stab_s = time.perf_counter() - t0
+    L.stability_selection(x, y, lam, n_boot=min(64, n_boot), alphas=(1.0,))         # warm-up
+    sync(); t0 = time.perf_counter()
+    out = L.stability_selection(x, y, lam, n_boot=n_boot, alphas=alphas, seed=1)
+    sync(); stab_s = time.perf_counter() - t0
     top = torch.argsort(-out["max_freq"])[:10].cpu().tolist()
     costs, gammas = [0.25, 1.0, 4.0, 16.0], [0.25 / x.shape[1], 1.0 / x.shape[1], 4.0 / x.shape[1]]
-    S.grid_search(x, y, costs[:1], gammas[:1])
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    gs = S.grid_search(x, y, costs, gammas, nfolds=5)
-    torch.cuda.synchronize(); svm_s = time.perf_counter() - t0
+    S.grid_search(x.float(), y.float(), costs[:1], gammas[:1])
+    sync(); t0 = time.perf_counter()
+    gs = S.grid_search(x.float(), y.float(), costs, gammas, nfolds=5)
+    sync(); svm_s = time.perf_counter() - t0
     # CPU arm: 8 bootstrap path fits per alpha on one core
     xc, yc = x.double().cpu(), y.double().cpu()
     cpu_rate = {}
@@ -45,9 +48,9 @@ def main():
         t0 = time.perf_counter()
         K.lognet_path(xc, yc, w, lam, alpha=a, want_eta=False)
         cpu_rate[a] = 8 / (time.perf_counter() - t0)
-    cpu_est = sum(1000 / r for r in cpu_rate.values())
+    cpu_est = sum(n_boot / r for r in cpu_rate.values())
     print(json.dumps({"config": "stability selection: 1000 bootstraps x alpha grid + RBF-SVM grid (TARGET-AML 93 x 1984)",
-                      "path_fits": 4000, "gpu_stability_s": round(stab_s, 3), "gpu_path_fits_per_s": round(4000 / stab_s, 1),
+                      "path_fits": 4 * n_boot, "gpu_stability_s": round(stab_s, 3), "gpu_path_fits_per_s": round(4 * n_boot / stab_s, 1),
                       "gpu_svm_grid_s": round(svm_s, 3), "svm_grid_points": len(costs) * len(gammas) * 5,
                       "svm_best": [gs["best_cost"], gs["best_gamma"]], "cpu_one_core_path_fits_per_s": {str(k): round(v, 2) for k, v in cpu_rate.items()},
                       "cpu_one_core_stability_s_extrapolated": round(cpu_est, 1), "speedup_vs_one_core": round(cpu_est / stab_s, 1),
