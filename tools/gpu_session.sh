@@ -10,6 +10,7 @@ echo "== bench.py";                 timeout 300 python bench.py --steps 4 --warm
 echo "== pipeline bench";           timeout 400 python bench/pipeline_bench.py 2>/dev/null | tail -1 | tee $O/pipeline.json | cut -c1-600
 echo "== stability bench";          timeout 300 python bench/stability_bench.py 2>&1 | tail -1 | tee $O/stability.json | cut -c1-600
 echo "== pan-cancer bench";         timeout 600 python bench/pancancer_bench.py 2>&1 | tail -1 | tee $O/pancancer.json | cut -c1-600
+echo "== stage bench";              timeout 300 python bench/stage_bench.py 2>&1 | grep "^{" | tee $O/stage_bench.jsonl | cut -c1-250
 echo "== gemm bench";               timeout 200 python bench/gemm_bench.py 2>/dev/null | tee $O/gemm_bench.jsonl | cut -c1-250
 echo "== lasso phases";             timeout 200 python tools/prof_lasso_phases.py 2>&1 | tail -3 | tee $O/lasso_phases.jsonl | cut -c1-300
 echo "== ncu: CTA-pair GEMM (after the plain run above exited 0)"
