@@ -14,5 +14,5 @@ echo "== stage bench";              timeout 300 python bench/stage_bench.py 2>&1
 echo "== gemm bench";               timeout 200 python bench/gemm_bench.py 2>/dev/null | tee $O/gemm_bench.jsonl | cut -c1-250
 echo "== lasso phases";             timeout 200 python tools/prof_lasso_phases.py 2>&1 | tail -3 | tee $O/lasso_phases.jsonl | cut -c1-300
 echo "== ncu: CTA-pair GEMM (after the plain run above exited 0)"
-timeout 400 ncu --set full --clock-control none --import-source on -k regex:gemm_tn_pair_kernel --launch-skip 2 --launch-count 1 \
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:gemm_tn_pair_kernel --launch-skip 1 --launch-count 1 \
   -o $O/prof_gemm_pair -f python tools/prof_kernels.py gemm 2>&1 | tail -2
