@@ -60,8 +60,9 @@ def lipschitz_estimate(x: torch.Tensor, n_total: int, iters: int = 12) -> float:
 
 def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Optional[int] = None, max_iter: int = 200,
         tol: float = 1e-5, backend: str = "auto", weights: Optional[torch.Tensor] = None, beta0: Optional[torch.Tensor] = None,
-        step: Optional[float] = None, check_every: int = 10) -> LargeFit:
-    """L1 logistic regression on this rank's rows (``x_local`` [n_r, p]); every rank returns the full ``beta``."""
+        step: Optional[float] = None, check_every: int = 10, alpha: float = 1.0) -> LargeFit:
+    """L1 (``alpha = 1``) or elastic-net logistic regression, glmnet's penalty ``lam (alpha |b|_1 + (1 - alpha)/2 |b|^2)``, on this
+    rank's rows (``x_local`` [n_r, p]); every rank returns the full ``beta``."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     n_r, p = x_local.shape
     dev = x_local.device
@@ -74,7 +75,7 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
     if step is None:
         step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
     if backend == "unfused":
-        return _fit_unfused(x_local, y_local, lam, n_total, max_iter, tol, weights, beta0, step, check_every)
+        return _fit_unfused(x_local, y_local, lam, n_total, max_iter, tol, weights, beta0, step, check_every, alpha)
 
     lb = _native.cuda()
     P = _native.ptr
@@ -116,9 +117,14 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
         tk1 = (1.0 + np.sqrt(1.0 + 4.0 * tk * tk)) / 2.0
         mom = (tk - 1.0) / tk1
         tk = tk1
-        _native.check(lb.cml_prox_allgather(P(rs.grad.local), rs.genes_owned, rs.gene0, None, step, lam, 1.0 / n_total, mom,
-                                            bptr, vptr, sptr, rank, world, P(beta.local), P(done), it, F.SIG_BETA, P(dmax),
-                                            st()), "cml_prox_allgather")
+        if alpha >= 1.0:
+            _native.check(lb.cml_prox_allgather(P(rs.grad.local), rs.genes_owned, rs.gene0, None, step, lam, 1.0 / n_total, mom,
+                                                bptr, vptr, sptr, rank, world, P(beta.local), P(done), it, F.SIG_BETA, P(dmax),
+                                                st()), "cml_prox_allgather")
+        else:
+            _native.check(lb.cml_prox_allgather_enet(P(rs.grad.local), rs.genes_owned, rs.gene0, None, step, lam * alpha,
+                                                     lam * (1.0 - alpha), 1.0 / n_total, mom, bptr, vptr, sptr, rank, world,
+                                                     P(beta.local), P(done), it, F.SIG_BETA, P(dmax), st()), "cml_prox_allgather_enet")
         if check:
             # convergence test on the largest coefficient change of this iteration (max over ranks); the loss printed
             # is that of the extrapolated point v, enough to watch progress
@@ -128,7 +134,8 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
             all_reduce_(d, dist.ReduceOp.MAX)
             all_reduce_(s)
             _native.check(lb.cml_wait_signals(my_pad, F.SIG_BETA, world, it, st()), "cml_wait_signals")
-            obj = float(s.item()) / n_total + lam * float(beta.local[:p].abs().sum())
+            bl = beta.local[:p]
+            obj = float(s.item()) / n_total + lam * (alpha * float(bl.abs().sum()) + 0.5 * (1.0 - alpha) * float((bl * bl).sum()))
             history.append((it, obj, float(d.item())))
             if float(d.item()) < tol:
                 break
@@ -141,7 +148,7 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
     return LargeFit(out, it, obj, step, history)
 
 
-def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_every) -> LargeFit:
+def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_every, alpha: float = 1.0) -> LargeFit:
     p = x.shape[1]
     dev = x.device
     xf = x.float()
@@ -159,8 +166,8 @@ def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_
         g = xf.t() @ r
         all_reduce_(g)
         z = v + step * g / n_total
-        thr = step * lam
-        bnew = torch.sign(z) * (z.abs() - thr).clamp_min(0)
+        thr = step * lam * alpha
+        bnew = torch.sign(z) * (z.abs() - thr).clamp_min(0) / (1.0 + step * lam * (1.0 - alpha))
         tk1 = (1.0 + np.sqrt(1.0 + 4.0 * tk * tk)) / 2.0
         mom = (tk - 1.0) / tk1
         tk = tk1
@@ -171,7 +178,7 @@ def _fit_unfused(x, y, lam, n_total, max_iter, tol, weights, beta0, step, check_
             sp = torch.where(eta > 0, eta + torch.log1p(torch.exp(-eta)), torch.log1p(torch.exp(eta)))
             s = (w * (sp - yf * eta)).double().sum().reshape(1)
             all_reduce_(s)
-            obj = float(s.item()) / n_total + lam * float(beta.abs().sum())
+            obj = float(s.item()) / n_total + lam * (alpha * float(beta.abs().sum()) + 0.5 * (1.0 - alpha) * float((beta * beta).sum()))
             history.append((it, obj, d))
             if d < tol:
                 break
@@ -188,7 +195,7 @@ def lambda_max(x_local: torch.Tensor, y_local: torch.Tensor, n_total: int, weigh
 
 def fit_path(x_local: torch.Tensor, y_local: torch.Tensor, lams=None, *, n_lambda: int = 20, lambda_min_ratio: float = 0.05,
              n_total: Optional[int] = None, max_iter: int = 300, tol: float = 1e-5, backend: str = "auto",
-             weights: Optional[torch.Tensor] = None):
+             weights: Optional[torch.Tensor] = None, alpha: float = 1.0):
     """Warm-started path of the sharded solver over a descending lambda grid (default: geometric from ``lambda_max`` down to
     ``lambda_min_ratio * lambda_max``, glmnet's construction).  The Lipschitz step is estimated once.  Returns
     ``(lams, [LargeFit per lambda])``; every rank holds every coefficient vector."""
@@ -197,7 +204,7 @@ def fit_path(x_local: torch.Tensor, y_local: torch.Tensor, lams=None, *, n_lambd
         all_reduce_(t)
         n_total = int(t.item())
     if lams is None:
-        lmax = lambda_max(x_local, y_local, n_total, weights)
+        lmax = lambda_max(x_local, y_local, n_total, weights) / max(alpha, 1e-3)
         lams = np.geomspace(lmax, lmax * lambda_min_ratio, n_lambda)
     lams = np.asarray(lams, dtype=np.float64)
     if np.any(np.diff(lams) > 0):
@@ -206,7 +213,7 @@ def fit_path(x_local: torch.Tensor, y_local: torch.Tensor, lams=None, *, n_lambd
     fits, beta = [], None
     for lam in lams:
         f = fit(x_local, y_local, float(lam), n_total=n_total, max_iter=max_iter, tol=tol, backend=backend, weights=weights,
-                beta0=beta, step=step)
+                beta0=beta, step=step, alpha=alpha)
         beta = f.beta
         fits.append(f)
     return lams, fits

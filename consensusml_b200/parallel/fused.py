@@ -27,6 +27,7 @@ _native.register_signature("cml_xtr_rs_scratch_bytes", [_I, _I], _SZ)
 _native.register_signature("cml_xtr_reduce_scatter", [_P, _LL, _I, _I, _P, _I, _P, _P, _P, _I, _I, _I, _LL, _U, _P])
 _native.register_signature("cml_wait_signals", [_P, _I, _I, _U, _P])
 _native.register_signature("cml_prox_allgather", [_P, _I, _I, _P, _F, _F, _F, _F, _P, _P, _P, _I, _I, _P, _P, _U, _I, _P, _P])
+_native.register_signature("cml_prox_allgather_enet", [_P, _I, _I, _P, _F, _F, _F, _F, _F, _P, _P, _P, _I, _I, _P, _P, _U, _I, _P, _P])
 _native.register_signature("cml_xb_residual", [_P, _LL, _I, _I, _P, _F, _P, _P, _P, _P, _P, _P])
 _native.register_signature("cml_hist_scratch_bytes", [_I, _I], _SZ)
 _native.register_signature("cml_hist_ft", [_I, _I], _I)

@@ -167,13 +167,13 @@ __global__ void wait_signals_kernel(const unsigned* pad, int base, int world, un
 // FISTA / proximal-gradient step on the genes this rank owns, fused with the all-gather of the result:
 //   g        = grad_buf[j] (sum over ranks of X^T r, landed by the kernel above)   -> then cleared for epoch+2
 //   z_j      = v_j + step * g / n_total                  (v = extrapolated point)
-//   beta_new = soft(z_j, step * lambda * pf_j)
+//   beta_new = soft(z_j, step * lambda * pf_j) * shrink      (shrink = 1 / (1 + step * lambda_ridge) for the elastic net, 1 for the lasso)
 //   v_new    = beta_new + momentum * (beta_new - beta_old)
 // beta_new and v_new are written into EVERY rank's coefficient buffers with peer stores, then signalled.
 __global__ void prox_allgather_kernel(float* __restrict__ grad_owned, int genes_owned, int gene0, const float* __restrict__ pf,
                                       float step, float lambda, float inv_n, float momentum, Peers Pbeta, Peers Pv,
                                       const float* __restrict__ beta_local, unsigned* __restrict__ done_count, unsigned epoch,
-                                      int sig_base, float* __restrict__ delta_max) {
+                                      int sig_base, float* __restrict__ delta_max, float shrink) {
   float dmax = 0.f;
   for (int jl = blockIdx.x * blockDim.x + threadIdx.x; jl < genes_owned; jl += gridDim.x * blockDim.x) {
     const int j = gene0 + jl;
@@ -183,7 +183,7 @@ __global__ void prox_allgather_kernel(float* __restrict__ grad_owned, int genes_
     const float vold = Pv.buf[Pv.rank][j];
     const float z = vold + step * g * inv_n;
     const float thr = step * lambda * (pf ? pf[j] : 1.f);
-    const float bnew = z > thr ? z - thr : (z < -thr ? z + thr : 0.f);
+    const float bnew = (z > thr ? z - thr : (z < -thr ? z + thr : 0.f)) * shrink;      // * 1.0f is exact: the lasso path is unchanged
     const float vnew = bnew + momentum * (bnew - bold);
     dmax = fmaxf(dmax, fabsf(bnew - bold));
     for (int r = 0; r < Pbeta.world; ++r) {
@@ -503,7 +503,24 @@ int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const floa
   const int blocks = max(1, min(ceil_div(genes_owned, 256), sm_count()));
   prox_allgather_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad_owned, genes_owned, gene0, pf, step, lambda, inv_n,
                                                                               momentum, Pb, Pv, beta_local, done_count, epoch,
-                                                                              sig_base, delta_max);
+                                                                              sig_base, delta_max, 1.0f);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// Elastic-net form of the step above: lambda_l1 = lambda * alpha is the soft threshold, the ridge part lambda * (1 - alpha)
+// enters as shrink = 1 / (1 + step * lambda_ridge).  Separate entry so that the lasso call keeps its signature.
+int cml_prox_allgather_enet(float* grad_owned, int genes_owned, int gene0, const float* pf, float step, float lambda_l1,
+                            float lambda_ridge, float inv_n, float momentum, const void* const* beta_bufs, const void* const* v_bufs,
+                            const void* const* peer_sigs, int rank, int world, const float* beta_local, unsigned* done_count,
+                            unsigned epoch, int sig_base, float* delta_max, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(lambda_ridge >= 0.f && step > 0.f, CML_EINVAL, "cml_prox_allgather_enet: step must be positive and lambda_ridge non-negative");
+  Peers Pb = make_peers(beta_bufs, peer_sigs, rank, world), Pv = make_peers(v_bufs, peer_sigs, rank, world);
+  const int blocks = max(1, min(ceil_div(genes_owned, 256), sm_count()));
+  prox_allgather_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad_owned, genes_owned, gene0, pf, step, lambda_l1, inv_n,
+                                                                              momentum, Pb, Pv, beta_local, done_count, epoch,
+                                                                              sig_base, delta_max, 1.0f / (1.0f + step * lambda_ridge));
   CML_LAUNCH_CHECK();
   return 0;
 }

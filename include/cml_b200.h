@@ -194,6 +194,11 @@ int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const floa
     float momentum, const void* const* beta_bufs, const void* const* v_bufs, const void* const* peer_sigs,
     int rank, int world, const float* beta_local, unsigned* done_count, unsigned epoch, int sig_base,
     float* delta_max, void* stream);
+/* Elastic-net form of cml_prox_allgather: soft threshold step * lambda_l1, then * 1 / (1 + step * lambda_ridge). */
+int cml_prox_allgather_enet(float* grad_owned, int genes_owned, int gene0, const float* pf, float step, float lambda_l1,
+                            float lambda_ridge, float inv_n, float momentum, const void* const* beta_bufs, const void* const* v_bufs,
+                            const void* const* peer_sigs, int rank, int world, const float* beta_local, unsigned* done_count,
+                            unsigned epoch, int sig_base, float* delta_max, void* stream);
 /* Path 4, shard transpose (all-to-all between the sample-sharded and the gene-sharded layout): rows
  * [row0, row0 + rows_local) of a matrix of 32-bit words -> column blocks on their owner ranks, transposed, written by peer
  * stores from inside the transpose kernel.  col_start: world + 1 ints; out_bufs[d]: owner d's [cols of d][ldy] symmetric

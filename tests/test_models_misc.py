@@ -185,3 +185,9 @@ def test_sharded_solver_path_agrees_with_coordinate_descent():
         assert (fits[i].beta.double() - ref.dense(0)[i]).abs().max() < 5e-6
     with pytest.raises(ValueError):
         LL.fit_path(x, y, lams=[0.01, 0.1])
+    # elastic net (glmnet's penalty, alpha = 0.5) against the same coordinate-descent solver
+    lams, fits = LL.fit_path(x, y, n_lambda=5, max_iter=4000, tol=1e-7, alpha=0.5)
+    ref = K.lognet_path(x.double(), y.double(), torch.ones(1, n, dtype=torch.float64), lams, alpha=0.5, thresh=1e-12)
+    assert int((fits[0].beta != 0).sum()) == 0
+    for i in range(len(lams)):
+        assert (fits[i].beta.double() - ref.dense(0)[i]).abs().max() < 5e-6
