@@ -200,6 +200,11 @@ def main():
         print(f"[{rank}] EXPERIMENTAL sibling subtraction on the fused histogram path: same trees {same}, samples histogrammed "
               f"{a.samples_histogrammed_} -> {b.samples_histogrammed_}", flush=True)
         xok &= same
+        fu = LL.fit(xl, yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="fused", alpha=0.5)
+        un = LL.fit(xl.bfloat16().float(), yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="unfused", step=fu.step, alpha=0.5)
+        err = float((fu.beta - un.beta).abs().max())
+        print(f"[{rank}] EXPERIMENTAL elastic-net (alpha 0.5) fused vs unfused beta max diff {err:.2e}", flush=True)
+        xok &= err < 2e-3
         print(f"[{rank}] EXPERIMENTAL verdict: {'OK' if xok else 'FAILED'}", flush=True)
     t = torch.tensor([1.0 if ok else 0.0], device=dev)
     if world > 1:
