@@ -239,6 +239,13 @@ void cml_host_lognet_counters(long long* out8);
 void cml_host_lognet_set_active_mode(int mode);
 /* Host build of the eBayes kernel's Student-t tail (csrc/tdist.cuh): two-sided p of n statistics, df[i * df_stride]. */
 void cml_host_t_two_sided(const double* t, const double* df, int df_stride, int n, double* p_out);
+/* Genes x samples integer CSV -> int32 matrix, parsed by a thread pool over an mmap (pandas: 5.8 s, this: 0.2 s at
+ * 60,488 x 474).  open() indexes the lines and the header; header(j) returns sample id j; read() fills out[rows][cols] and
+ * ids[rows][id_cap] (NUL-terminated) and returns 0 or -(line number) of the first row that is not plain integers. */
+int cml_host_csv_open(const char* path, char sep, long* rows, long* cols);
+int cml_host_csv_header(long j, char* buf, int cap);
+long cml_host_csv_read(char sep, int* out, char* ids, int id_cap, int n_threads);
+void cml_host_csv_close(void);
 /* Per-sample count files -> gene x sample matrix (Cat_Expn_Data.r:7-49): scan the first file for the gene ids, read them
  * back one by one, then parse all files in parallel (mmap) into out[genes][n_files]; status[f] = 0 or the negative line
  * number of the first problem in file f. */

@@ -88,3 +88,37 @@ def test_read_manifest_and_merge(tmp_path):
     clin = pd.DataFrame({"TARGET USI": ["TARGET-20-PABCDE", "TARGET-20-PAXYZW"], "Risk group": ["Low", "High"]})
     merged = clean.manifest_clinical_merge(man, clin, "TARGET-AML")
     assert len(merged) == 2 and set(merged["Risk group"]) == {"Low", "High"}
+
+
+def test_native_csv_matrix_reader_matches_pandas(tmp_path):
+    """csrc/host/csv_matrix.cpp: quoted ids and values, CRLF, "12.0", negative numbers, blank lines; non-integer files fall back."""
+    import numpy as np
+    import pandas as pd
+    import torch
+    from consensusml_b200.io import counts as IC
+    rng = np.random.default_rng(0)
+    m = rng.integers(0, 500000, size=(257, 13)).astype(np.int32)
+    m[3, 4] = -7
+    genes = [f"ENSG{i:011d}.{i % 17}" for i in range(257)]
+    samples = [f"TARGET.20.PA{i:04d}.09A.01R" for i in range(13)]
+    p1 = tmp_path / "plain.csv"
+    IC.write_matrix_csv(str(p1), torch.from_numpy(m), genes, samples)
+    a = IC._read_counts_csv_native(str(p1), threads=3)
+    b = IC.read_counts_csv(str(p1), native=False)
+    assert a is not None and torch.equal(a[0], b[0]) and a[1] == b[1] == genes and a[2] == b[2] == samples
+    p2 = tmp_path / "quoted_crlf.csv"
+    with open(p2, "w", newline="") as fh:                       # R's write.csv style, Windows line ends, a blank line
+        fh.write(",".join(['""'] + [f'"{s}"' for s in samples]) + "\r\n")
+        for i in range(257):
+            fh.write(",".join([f'"{genes[i]}"'] + [f"{v}.0" if j % 2 else f'"{v}"' for j, v in enumerate(m[i])]) + "\r\n")
+            if i == 100:
+                fh.write("\r\n")
+    c = IC.read_counts_csv(str(p2))
+    assert torch.equal(c[0], torch.from_numpy(m)) and c[1] == genes and c[2] == samples
+    p3 = tmp_path / "floats.csv"
+    pd.DataFrame(m[:5] + 0.5, index=genes[:5], columns=samples).to_csv(p3)
+    assert IC._read_counts_csv_native(str(p3)) is None          # not an integer matrix: the general reader takes over
+    p4 = tmp_path / "ragged.csv"
+    p4.write_text("id,a,b\nx,1,2\ny,3\n")
+    assert IC._read_counts_csv_native(str(p4)) is None
+    assert IC._read_counts_csv_native(str(tmp_path / "missing.csv")) is None
