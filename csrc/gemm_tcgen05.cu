@@ -741,9 +741,11 @@ int cml_gemm_tn_bf16(int M, int N, int K, const void* a, long long lda, const vo
   // shared-memory rate); use it whenever a source is wide enough to fill such tiles
   const int src_rows = rows_per_src < N ? rows_per_src : N;
   const int BN = src_rows >= 768 ? 256 : 128;
-  // CTA pairs (256 x 256 tiles) once there are enough such tiles to occupy every pair of SMs
+  // CTA pairs (256 x 256 tiles) once there are enough such tiles to occupy every pair of SMs.  A multi-source B is how peer
+  // buffers enter (direct all-gather): those stay on the single-CTA kernel, whose producer issues plain per-CTA TMA loads.
   const bool pair = g_gemm_variant == 2 ||
-                    (g_gemm_variant == 0 && BN == 256 && (long long)ceil_div(M, 256) * ceil_div(src_rows, 256) * n_src >= sm_count() / 2);
+                    (g_gemm_variant == 0 && n_src == 1 && BN == 256 &&
+                     (long long)ceil_div(M, 256) * ceil_div(src_rows, 256) >= sm_count() / 2);
   int rc = make_tmap_bf16_k64(&P.map_a, a, M, K, lda, BM);
   if (rc) return rc;
   for (int s = 0; s < n_src; ++s) {
