@@ -105,8 +105,33 @@ def read_counts_csv(path: str, id_column: int = 0, native: bool = True) -> Tuple
     return torch.from_numpy(df.to_numpy(dtype=np.int32)), [str(i) for i in df.index], [str(c) for c in df.columns]
 
 
-def write_matrix_csv(path: str, matrix: torch.Tensor, row_ids: Sequence[str], col_ids: Sequence[str]) -> None:
-    pd.DataFrame(matrix.cpu().numpy(), index=list(row_ids), columns=list(col_ids)).to_csv(path)
+def write_matrix_csv(path: str, matrix: torch.Tensor, row_ids: Sequence[str], col_ids: Sequence[str], native: bool = True,
+                     threads: Optional[int] = None) -> None:
+    """Matrix with row and column ids -> CSV (empty first header cell, like ``write.csv`` / ``DataFrame.to_csv``).  int32 /
+    int64-that-fit and floating matrices go through the parallel native writer (csrc/host/csv_matrix.cpp: doubles in their
+    shortest round-trip form, so the file reads back to exactly the same values); ids containing the separator, quotes or
+    line breaks, and other dtypes, fall back to pandas."""
+    m = matrix.detach().cpu()
+    plain = all(not any(ch in s for ch in ',"\n\r') for s in list(row_ids) + list(col_ids))
+    if native and plain and m.dim() == 2 and m.shape[0] == len(row_ids) and m.shape[1] == len(col_ids) and m.numel() > 0:
+        lib = _native.host()
+        arr = None
+        if m.dtype in (torch.float64, torch.float32, torch.bfloat16, torch.float16):
+            arr, fn = np.ascontiguousarray(m.to(torch.float64).numpy()), lib.cml_host_csv_write_f64
+        elif m.dtype in (torch.int32, torch.int16, torch.uint8, torch.int8) or (m.dtype == torch.int64 and int(m.abs().max()) < 2 ** 31):
+            arr, fn = np.ascontiguousarray(m.to(torch.int32).numpy()), lib.cml_host_csv_write_i32
+        if arr is not None:
+            fn.restype = ctypes.c_long
+            fn.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_long, ctypes.POINTER(ctypes.c_char_p),
+                           ctypes.POINTER(ctypes.c_char_p), ctypes.c_char, ctypes.c_int]
+            rid = (ctypes.c_char_p * len(row_ids))(*[str(s).encode() for s in row_ids])
+            cid = (ctypes.c_char_p * len(col_ids))(*[str(s).encode() for s in col_ids])
+            rc = fn(os.fspath(path).encode(), arr.ctypes.data, arr.shape[0], arr.shape[1], rid, cid, b",",
+                    threads or min(16, os.cpu_count() or 1))
+            if rc != 0:
+                raise OSError(f"could not write {path} (code {rc})")
+            return
+    pd.DataFrame(m.numpy() if m.dtype != torch.bfloat16 else m.float().numpy(), index=list(row_ids), columns=list(col_ids)).to_csv(path)
 
 
 def read_manifest(path: str) -> pd.DataFrame:

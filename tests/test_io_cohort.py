@@ -122,3 +122,27 @@ def test_native_csv_matrix_reader_matches_pandas(tmp_path):
     p4.write_text("id,a,b\nx,1,2\ny,3\n")
     assert IC._read_counts_csv_native(str(p4)) is None
     assert IC._read_counts_csv_native(str(tmp_path / "missing.csv")) is None
+
+
+def test_native_csv_matrix_writer_round_trips(tmp_path):
+    """Parallel writer: doubles in shortest round-trip form (exact when read back), integers, fallback for awkward ids."""
+    import numpy as np
+    import pandas as pd
+    import torch
+    from consensusml_b200.io import counts as IC
+    rng = np.random.default_rng(1)
+    x = rng.normal(size=(1300, 9)) * np.array([1e-12, 1e-3, 1, 1, 1e3, 1e8, 1e18, 1, 1])
+    x[0, 0], x[1, 1], x[2, 2], x[3, 3] = np.nan, 1e-300, 5.0, -0.0
+    rows, cols = [f"ENSG{i:05d}.3" for i in range(1300)], [f"S{j}" for j in range(9)]
+    IC.write_matrix_csv(str(tmp_path / "f.csv"), torch.from_numpy(x), rows, cols, threads=3)
+    d = pd.read_csv(tmp_path / "f.csv", index_col=0, float_precision="round_trip")
+    assert list(d.index) == rows and list(d.columns) == cols and np.array_equal(d.to_numpy(), x, equal_nan=True)
+    m = rng.integers(-5, 10 ** 9, size=(700, 4))
+    IC.write_matrix_csv(str(tmp_path / "i.csv"), torch.from_numpy(m), rows[:700], cols[:4])
+    back = IC.read_counts_csv(str(tmp_path / "i.csv"))
+    assert torch.equal(back[0], torch.from_numpy(m).int()) and back[1] == rows[:700] and back[2] == cols[:4]
+    IC.write_matrix_csv(str(tmp_path / "q.csv"), torch.from_numpy(x[:3]), ['a,b', 'c "d"', "e"], cols)     # pandas fallback quotes them
+    q = pd.read_csv(tmp_path / "q.csv", index_col=0)
+    assert list(q.index) == ['a,b', 'c "d"', "e"]
+    with pytest.raises(OSError):
+        IC.write_matrix_csv(str(tmp_path / "no_such_dir" / "x.csv"), torch.from_numpy(x[:3]), rows[:3], cols)
