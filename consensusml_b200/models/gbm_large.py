@@ -139,6 +139,7 @@ class GBMLarge:
                     gain, feat, thr = F.best_splits(hist, self.reg_lambda, self.gamma, self.min_child_weight)
                 else:
                     gain, feat, thr = F.best_splits_torch(hist, self.reg_lambda, self.gamma, self.min_child_weight)
+                gain, feat, thr = F.agree_splits(gain, feat, thr)       # one decision for all ranks (see its docstring)
                 if e1 is not None:
                     e1.record()
                     e1.synchronize()

@@ -265,6 +265,29 @@ def best_splits(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_ch
         torch.where(has, b, -torch.ones_like(b))
 
 
+def agree_splits(gain: torch.Tensor, feat: torch.Tensor, thr: torch.Tensor):
+    """Make the split decision single-sourced across ranks.
+
+    Every rank scores its own copy of the reduced histogram.  The copies are sums of floats that arrive in a different
+    order on every rank, so they may differ in the last ulp and a near-tie in gain could otherwise pick a different
+    (feature, bin) on different ranks - which would route samples inconsistently without any error.  The decision is
+    therefore packed into one ordered 64-bit key per node (gain bits | inverted feature | inverted bin, the same key
+    ``cml_split_score_gain`` builds) and MAX-all-reduced: n_nodes words per level."""
+    if not (dist.is_initialized() and dist.get_world_size() > 1):
+        return gain, feat, thr
+    has = feat >= 0
+    gbits = gain.float().contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF      # gains are > 0: bit order = value order
+    key = (gbits << 32) | ((0xFFFFF - feat.clamp_min(0)) << 12) | (0xFFF - thr.clamp_min(0))
+    key = torch.where(has, key, torch.zeros_like(key))
+    dist.all_reduce(key, op=dist.ReduceOp.MAX)
+    has = key != 0
+    g = ((key >> 32) & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+    f = 0xFFFFF - ((key >> 12) & 0xFFFFF)
+    b = 0xFFF - (key & 0xFFF)
+    neg = -torch.ones_like(f)
+    return torch.where(has, g, torch.zeros_like(g)), torch.where(has, f, neg), torch.where(has, b, neg)
+
+
 def best_splits_torch(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, min_child_weight: float = 1.0):
     """Same contract as ``best_splits`` in plain torch (CPU path and oracle): xgboost's second-order gain
     ``G_L^2/(H_L+lam) + G_R^2/(H_R+lam) - G^2/(H+lam) - gamma`` over every cut after an occupied bin (ties: lowest feature, bin)."""

@@ -82,7 +82,11 @@ bool parse_row(const char* p, const char* eol, char sep, long cols, int32_t* out
     if (b < t && *b == '-') { neg = true; ++b; }
     long v = 0;
     bool any = false;
-    for (; b < t && *b >= '0' && *b <= '9'; ++b) { v = v * 10 + (*b - '0'); any = true; }
+    for (; b < t && *b >= '0' && *b <= '9'; ++b) {
+      v = v * 10 + (*b - '0');
+      any = true;
+      if (v > 2147483647L) return false;            // bail out before `v` itself can overflow on a 20-digit field
+    }
     if (b < t && *b == '.') {                       // "12.0": digits after the point must all be zero
       ++b;
       for (; b < t && *b == '0'; ++b) {}

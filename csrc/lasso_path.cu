@@ -202,6 +202,11 @@ struct Warp {
         if (lane == 0) {
           inm()[k >> 5] |= 1u << (k & 31);
           m()[nin] = k;
+          // its coefficient at the start of this IRLS iteration was zero: the convergence test after the sweeps compares
+          // b(k) with bs()[l] for every l < nin, new entries included (lognet_cpu.cpp keeps bs by feature, zero-initialised).
+          // Without this store the test read whatever the slot held before - stale shared memory on a warp's first
+          // replicate - and could run (or skip) an IRLS iteration depending on the launch.
+          bs()[nin] = 0.f;
         }
         ++nin;
         __syncwarp();

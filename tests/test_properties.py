@@ -74,7 +74,7 @@ def test_auc_is_rank_based_and_antisymmetric(score, seed):
 
 
 @FAST
-@given(hnp.arrays(np.float64, st.tuples(st.integers(5, 40), st.integers(2, 5)), elements=st.floats(-3, 3, allow_nan=False)),
+@given(hnp.arrays(np.float64, st.tuples(st.integers(5, 40), st.integers(2, 5)), elements=st.floats(-3, 3, allow_nan=False, allow_subnormal=False)),   # a subnormal times 0.5 underflows into a tie
        st.integers(0, 2 ** 31 - 1))
 def test_rank_aggregation_is_permutation_equivariant_and_scale_free(imp, seed):
     t = torch.from_numpy(imp)
