@@ -30,6 +30,12 @@ OBJDIR = ROOT / "build" / "obj"
 
 CUDA_LIB = LIBDIR / "libcml_b200.so"
 HOST_LIB = LIBDIR / "libcml_host.so"
+EMU_LIB = LIBDIR / "libcml_emu.so"
+EMUDIR = ROOT / "build" / "emu"
+
+# kernels that only need warp / block primitives run under the host execution model (csrc/emu/cuda_emu.h);
+# the tcgen05 / TMA GEMMs (gemm_tcgen05.cu, gemm_rs.cu) do not
+EMU_EXCLUDE = {"gemm_tcgen05.cu", "gemm_rs.cu"}
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -59,7 +65,7 @@ def _digest(paths: List[Path], extra: str) -> str:
 
 def _headers() -> List[Path]:
     return sorted(list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + list(INCLUDE.glob("*.h"))
-                  + list((CSRC / "host").glob("*.h")))
+                  + list((CSRC / "host").glob("*.h")) + list((CSRC / "emu").glob("*.h")))
 
 
 def _run(cmd: List[str], log: Path) -> None:
@@ -121,6 +127,108 @@ def build_host(force: bool = False) -> Path:
     if force or not HOST_LIB.exists() or HOST_LIB.stat().st_mtime < newest:
         _run([gxx, "-shared", "-o", str(HOST_LIB)] + [str(o) for o in objs] + ["-lpthread"], OBJDIR / "link_host.log")
     return HOST_LIB
+
+
+def _match_paren(text: str, i: int) -> int:
+    """Index just past the parenthesis that closes the one at ``text[i]``."""
+    depth = 0
+    for j in range(i, len(text)):
+        c = text[j]
+        if c == "(":
+            depth += 1
+        elif c == ")":
+            depth -= 1
+            if depth == 0:
+                return j + 1
+    raise ValueError("unbalanced parentheses in a kernel launch")
+
+
+def _split_top(text: str) -> List[str]:
+    parts, depth, cur = [], 0, []
+    for c in text:
+        if c in "([{":
+            depth += 1
+        elif c in ")]}":
+            depth -= 1
+        if c == "," and depth == 0:
+            parts.append("".join(cur).strip())
+            cur = []
+        else:
+            cur.append(c)
+    parts.append("".join(cur).strip())
+    return parts
+
+
+def emu_translate(src: str) -> str:
+    """Rewrite the two CUDA constructs g++ cannot parse: ``kernel<<<grid, block, smem, stream>>>(args);`` becomes a call
+    of ``cml_emu::launch`` with the kernel invocation as its body, and ``extern __shared__ T name[];`` becomes a pointer
+    to the emulated dynamic shared memory.  Everything else is handled by macros and inline functions in cuda_emu.h."""
+    import re
+    out = []
+    pos = 0
+    while True:
+        i = src.find("<<<", pos)
+        if i < 0:
+            out.append(src[pos:])
+            break
+        # kernel name (with optional template arguments) ends at i
+        j = i
+        if src[j - 1] == ">":
+            depth = 0
+            while True:
+                j -= 1
+                if src[j] == ">":
+                    depth += 1
+                elif src[j] == "<":
+                    depth -= 1
+                    if depth == 0:
+                        break
+        while j > 0 and (src[j - 1].isalnum() or src[j - 1] in "_:"):
+            j -= 1
+        name = src[j:i]
+        k = src.index(">>>", i)
+        cfg = _split_top(src[i + 3:k])
+        while len(cfg) < 3:
+            cfg.append("0")
+        a0 = src.index("(", k)
+        a1 = _match_paren(src, a0)
+        args = src[a0:a1]
+        out.append(src[pos:j])
+        out.append(f"::cml_emu::launch(dim3({cfg[0]}), dim3({cfg[1]}), (size_t)({cfg[2]}), [&]() {{ {name}{args}; }})")
+        pos = a1
+    text = "".join(out)
+    text = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w:]+(?:\s+[\w:]+)*?)\s+(\w+)\[\];",
+                  r"\1* \2 = reinterpret_cast<\1*>(::cml_emu::dyn_smem());", text)
+    return text
+
+
+def build_emu(force: bool = False) -> Path:
+    """Build ``libcml_emu.so``: the kernel sources compiled by g++ against the host execution model."""
+    EMUDIR.mkdir(parents=True, exist_ok=True)
+    gen = []
+    for src in sorted(CSRC.glob("*.cu")):
+        if src.name in EMU_EXCLUDE:
+            continue
+        dst = EMUDIR / f"{src.stem}.emu.cpp"
+        text = f'#line 1 "{src}"\n' + emu_translate(src.read_text())
+        if not dst.exists() or dst.read_text() != text:
+            dst.write_text(text)
+        gen.append(dst)
+    gen.append(CSRC / "emu" / "cuda_emu.cpp")
+    gxx = shutil.which("g++") or "g++"
+    flags = ["-O1", "-g", "-std=c++17", "-fPIC", "-DCML_EMU=1", "-fno-fast-math", "-ffp-contract=off", "-Wno-unknown-pragmas",
+             "-Wno-attributes", "-I", str(INCLUDE), "-I", str(CSRC), "-I", str(CSRC / "emu"), "-include", str(CSRC / "emu" / "cuda_emu.h")]
+    if os.environ.get("CML_EMU_SANITIZE"):
+        flags += ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"]
+    objs = _compile_objects(gen, [gxx], flags, "emu", force)
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    newest = max(o.stat().st_mtime for o in objs)
+    if force or not EMU_LIB.exists() or EMU_LIB.stat().st_mtime < newest:
+        link = [gxx, "-shared", "-o", str(EMU_LIB)] + [str(o) for o in objs] + ["-lpthread"]
+        if os.environ.get("CML_EMU_SANITIZE"):
+            link += ["-fsanitize=address,undefined"]
+        _run(link, OBJDIR / "link_emu.log")
+    return EMU_LIB
 
 
 def build_all(force: bool = False, cuda: bool = True) -> None:

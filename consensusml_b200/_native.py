@@ -19,6 +19,8 @@ from . import _build
 _lock = threading.Lock()
 _cuda: Optional[ctypes.CDLL] = None
 _host: Optional[ctypes.CDLL] = None
+_emu: Optional[ctypes.CDLL] = None
+_emu_depth = 1 if os.environ.get("CML_EMU") == "1" else 0
 
 
 class NativeError(RuntimeError):
@@ -40,9 +42,65 @@ def cuda_available() -> bool:
     return torch.cuda.is_available()
 
 
+def emulating() -> bool:
+    """True while kernels are served by the host execution model (``libcml_emu.so``, csrc/emu/cuda_emu.h)."""
+    return _emu_depth > 0
+
+
+def on_device(t) -> bool:
+    """Should this tensor be handled by the kernel library?  CUDA tensors always; CPU tensors only inside
+    ``emulation()`` (then the same kernel source runs on the host, thread by thread)."""
+    return bool(t.is_cuda) or _emu_depth > 0
+
+
+class emulation:
+    """Context manager: route the op wrappers to the emulated kernel library for CPU tensors.
+
+    ``seed`` (or ``CML_EMU_SEED``) != 0 shuffles the order in which emulated threads run between synchronisation
+    points and changes the garbage dynamic shared memory starts with; results that depend on it expose a race or an
+    uninitialised read.  ``sms`` sets the multiprocessor count the launchers see (grid sizing)."""
+
+    def __init__(self, seed: Optional[int] = None, sms: Optional[int] = None):
+        self.env = {"CML_EMU_SEED": seed, "CML_EMU_SMS": sms}
+        self.saved = {}
+
+    def __enter__(self):
+        global _emu_depth
+        for k, v in self.env.items():
+            if v is not None:
+                self.saved[k] = os.environ.get(k)
+                os.environ[k] = str(v)
+        _emu_depth += 1
+        return self
+
+    def __exit__(self, *a):
+        global _emu_depth
+        _emu_depth -= 1
+        for k, old in self.saved.items():
+            if old is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = old
+
+
+def emu() -> ctypes.CDLL:
+    global _emu
+    with _lock:
+        if _emu is None:
+            path = _build.build_emu()
+            lib = ctypes.CDLL(str(path))
+            lib.cml_last_error.restype = ctypes.c_char_p
+            _declare(lib)
+            _emu = lib
+        return _emu
+
+
 def cuda() -> ctypes.CDLL:
-    """Load the sm_100a kernel library (building it first if absent and nvcc exists)."""
+    """Load the sm_100a kernel library (building it first if absent and nvcc exists).  Inside ``emulation()`` this is
+    the emulated library instead: same entry points (minus the tcgen05 GEMMs), host pointers, no streams."""
     global _cuda
+    if _emu_depth > 0:
+        return emu()
     with _lock:
         if _cuda is None:
             if not _build.CUDA_LIB.exists():
@@ -89,8 +147,9 @@ def _declare(lib) -> None:
 def register_signature(name: str, args, res=ctypes.c_int) -> None:
     """Used by op modules to declare the C signature of the entry points they bind."""
     _SIGNATURES[name] = (list(args), res)
-    if _cuda is not None:
-        _declare(_cuda)
+    for lib in (_cuda, _emu):
+        if lib is not None:
+            _declare(lib)
 
 
 def check(code: int, what: str) -> None:
@@ -110,6 +169,8 @@ def ptr(t) -> ctypes.c_void_p:
 
 def stream_ptr() -> ctypes.c_void_p:
     import torch
+    if _emu_depth > 0:
+        return ctypes.c_void_p(0)
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

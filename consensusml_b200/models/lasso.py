@@ -16,6 +16,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 import torch
 
+from .. import _native
 from ..data import Cohort
 from ..ops import lasso as K
 from ..ops import metrics as M
@@ -170,7 +171,7 @@ def fit_cv(x: torch.Tensor, y: torch.Tensor, lam: Optional[np.ndarray] = None, *
     if cv_modified_newton:
         # two launches: solver variant is a launch-level switch
         w0 = torch.as_tensor(base_w[None, :], device=dev)
-        packed = K.pack_design(x) if x.is_cuda else None
+        packed = K.pack_design(x) if _native.on_device(x) else None
         wcv = torch.as_tensor(np.concatenate([base_w[None, :], wf], 0), device=dev)
         s_full, s_cv = _side_stream(x.is_cuda), _side_stream(x.is_cuda)
         with s_full:
@@ -205,7 +206,7 @@ def run_lasso(cohort: Cohort, seed: int = 2019, lam: Optional[np.ndarray] = None
     y_all = cohort.labels(label_col).to(torch.float64)
     if device is not None:
         x_all, y_all = x_all.to(device), y_all.to(device)
-    if x_all.is_cuda:
+    if _native.on_device(x_all):
         x_all, y_all = x_all.float(), y_all.float()
     xtr, ytr = x_all[tr_idx], y_all[tr_idx]
     xte, yte = x_all[te_idx], y_all[te_idx]
@@ -260,7 +261,7 @@ def stability_selection(x: torch.Tensor, y: torch.Tensor, lam: np.ndarray, *, n_
     from ..ops.replicate import replicate_weights
     n, p = x.shape
     dev = x.device
-    if x.is_cuda:
+    if _native.on_device(x):
         packed = K.pack_design(x)
         n_pad = packed[1]
     else:
@@ -275,7 +276,7 @@ def stability_selection(x: torch.Tensor, y: torch.Tensor, lam: np.ndarray, *, n_
             nb = min(batch, n_boot - done)
             w = replicate_weights(nb, n, mode=mode, k=k, seed=seed + 7919 * ai, device=dev, n_pad=n_pad, rep0=done)
             K.lognet_path(x, y, w[:, :n], lam, alpha=alpha, want_eta=False, packed=packed, nx=nx, freq_out=freq[ai],
-                          padded_weights=w if x.is_cuda else None, want_coef=False)
+                          padded_weights=w if _native.on_device(x) else None, want_coef=False)
             done += nb
         freq[ai] /= n_boot
     return {"freq": freq, "max_freq": freq.amax(dim=(0, 1)), "alphas": torch.tensor(list(alphas)), "lam": torch.as_tensor(lam)}
@@ -293,7 +294,7 @@ def l1_logistic(x: torch.Tensor, y: torch.Tensor, C: float = 1.0, intercept: boo
     selection rule ``coef_ > 0`` (lines 1488-1489, 3914), which silently drops negative coefficients."""
     n = x.shape[0]
     lam_target = 1.0 / (C * n)
-    xd = x.double() if not x.is_cuda else x.float()
+    xd = x.double() if not _native.on_device(x) else x.float()
     yd = y.to(xd.dtype)
     r0 = yd - yd.mean() if intercept else yd - 0.5
     lam_max = float((xd.t() @ r0).abs().max() / n)

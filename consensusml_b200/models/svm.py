@@ -112,7 +112,7 @@ def solve_dual(K: torch.Tensor, y_pm: torch.Tensor, cbound: torch.Tensor, eps: f
     """Solve B dual problems.  K: [n, n] (shared) or [B, n, n]; y_pm: [n] or [B, n] in {-1, +1};
     cbound: [B, n] per-sample cost (0 removes the sample).  Returns (alpha [B, n], rho [B], iters [B])."""
     B, n = cbound.shape
-    if not K.is_cuda:
+    if not _native.on_device(K):
         Kn = K.double().numpy()
         yn = y_pm.double().numpy()
         out = [smo_numpy(Kn if Kn.ndim == 2 else Kn[b], yn if yn.ndim == 1 else yn[b], cbound[b].double().numpy(), eps, max_iter)

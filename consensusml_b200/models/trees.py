@@ -49,7 +49,7 @@ class Binner:
         n, p = x.shape
         n_pad = (n + 3) // 4 * 4
         xt = x.t().contiguous().float()
-        if n <= 256 and x.is_cuda:
+        if n <= 256 and _native.on_device(x):
             bins = torch.empty(p, n_pad, dtype=torch.uint8, device=x.device)
             edges = torch.full((p, 256), float("inf"), dtype=torch.float32, device=x.device)
             n_edges = torch.empty(p, dtype=torch.int32, device=x.device)
@@ -77,7 +77,7 @@ class Binner:
         m, p = x.shape
         m_pad = (m + 3) // 4 * 4
         xt = x.t().contiguous().float()
-        if x.is_cuda:
+        if _native.on_device(x):
             bins = torch.empty(p, m_pad, dtype=torch.uint8, device=x.device)
             rc = _native.cuda().cml_apply_bins(_native.ptr(xt), p, m, m, _native.ptr(self.edges), _native.ptr(self.n_edges),
                                                _native.ptr(bins), m_pad, _native.stream_ptr())
@@ -115,7 +115,7 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     dev = bins.device
     if max_nodes is None:
         max_nodes = min(2 * n + 1, 2 ** (min(max_depth, 20) + 1) - 1)
-    if not bins.is_cuda:
+    if not _native.on_device(bins):
         return _grow_numpy(bins, n, s0, s1, s2, criterion, mtry, max_depth, max_nodes, max_bin, lam, gamma, min_child_weight,
                            min_samples_leaf, min_samples_split, eta, seed, feature_mask, importance, in_tree)
     i32 = dict(dtype=torch.int32, device=dev)
@@ -165,7 +165,7 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
 def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):
     """(leaf[T, m] int32, value[T, m] fp32) for samples binned as ``bins[p, m_pad]``."""
     T, max_nodes = trees.feat.shape
-    if not bins.is_cuda:
+    if not _native.on_device(bins):
         return _predict_numpy(trees, bins, m)
     leaf = torch.empty(T, m, dtype=torch.int32, device=bins.device)
     val = torch.empty(T, m, dtype=torch.float32, device=bins.device)
@@ -355,7 +355,7 @@ class RandomForest:
             if prox is not None:
                 use_oob = self.oob_prox and self.bootstrap
                 ob = (w == 0).to(torch.uint8).contiguous() if use_oob else None
-                if dev.type == "cuda":
+                if _native.on_device(leaf):
                     rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), _native.ptr(ob), T, n,
                                                              _native.ptr(prox), _native.ptr(pairs), _native.stream_ptr())
                     _native.check(rc, "cml_forest_proximity")

@@ -110,7 +110,7 @@ def lognet_path(x: torch.Tensor, y: torch.Tensor, weights: torch.Tensor, lam, *,
         penalty_factor = pf * p / pf.sum()
     if freq_out is not None and (tuple(freq_out.shape) != (L, p) or freq_out.dtype != torch.float32):
         raise ValueError("freq_out must be a float32 [L, p] tensor")
-    if x.is_cuda:
+    if _native.on_device(x):
         return _path_cuda(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
                           feature_mask, penalty_factor, want_eta, packed, freq_out, padded_weights, want_coef)
     out = _path_host(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,

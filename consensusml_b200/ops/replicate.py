@@ -23,7 +23,7 @@ def replicate_weights(B: int, n: int, *, mode: str = "bootstrap", k: int = 0, se
     repeat ``b // k``.  ``rep0`` offsets the replicate counter so successive batches continue one stream."""
     n_pad = n if n_pad is None else n_pad
     dev = torch.device(device)
-    if dev.type == "cuda":
+    if dev.type == "cuda" or _native.emulating():
         w = torch.empty(B, n_pad, dtype=torch.float32, device=dev)
         rc = _native.cuda().cml_replicate_weights(_native.ptr(w), B, n, n_pad, ctypes.c_ulonglong(seed & (2**64 - 1)),
                                                   MODES[mode], int(k), int(rep0), _native.stream_ptr())

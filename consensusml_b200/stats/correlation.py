@@ -44,7 +44,7 @@ def correlation(x: torch.Tensor, y: Optional[torch.Tensor] = None, method: str =
     subset of sample columns (the reference repeats the heatmap on five sample subsets, SEA:889-969)."""
     ranked = method == "spearman"
     cols = torch.as_tensor(list(samples)) if samples is not None else None
-    if not x.is_cuda:
+    if not _native.on_device(x):
         def z(a):
             a = a.double()
             if cols is not None:
@@ -107,7 +107,7 @@ def kde(x: torch.Tensor, n_grid: int = 512, bw: Optional[float] = None, cut: flo
     bw = bw_nrd0(xf) if bw is None else bw
     lo, hi = float(xf.min()) - cut * bw, float(xf.max()) + cut * bw
     grid = torch.linspace(lo, hi, n_grid, device=x.device)
-    if not x.is_cuda:
+    if not _native.on_device(x):
         u = (grid[:, None].double() - xf[None, :].double()) / bw
         return grid, (torch.exp(-0.5 * u * u).sum(1) / (xf.numel() * bw * np.sqrt(2 * np.pi))).float()
     out = torch.empty(n_grid, dtype=torch.float32, device=x.device)

@@ -110,7 +110,7 @@ def voom_de(counts: torch.Tensor, group, *, min_frac: float = 0.05, p_value: flo
     """Two-group limma-voom DE on raw counts (genes x samples).  ``group`` = 1 for the non-reference level.
     A custom ``design`` ([S, k<=8]) and ``contrast`` ([k]) may replace the two-group default."""
     group = np.asarray(group)
-    if not counts.is_cuda:
+    if not _native.on_device(counts):
         c = counts.numpy().astype(np.float64)
         r = O.voom_de(c, group, min_frac) if design is None else _oracle_general(c, design, contrast, min_frac)
         eb = r["ebayes"]

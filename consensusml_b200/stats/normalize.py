@@ -35,7 +35,7 @@ def _as_counts(counts: torch.Tensor) -> torch.Tensor:
 def lib_sizes(counts: torch.Tensor) -> torch.Tensor:
     """Column sums (``DGEList`` library sizes), float64 [S]."""
     counts = _as_counts(counts)
-    if not counts.is_cuda:
+    if not _native.on_device(counts):
         return counts.to(torch.float64).sum(0)
     G, S = counts.shape
     out = torch.empty(S, dtype=torch.int64, device=counts.device)
@@ -48,7 +48,7 @@ def cpm_pass_counts(counts: torch.Tensor, lib: torch.Tensor, min_cpm: float = 1.
     """Per gene, the number of samples whose CPM is at least ``min_cpm`` (int32 [G]).  When the cohort is
     sample-sharded these per-gene counts are what gets all-reduced across ranks."""
     counts = _as_counts(counts)
-    if not counts.is_cuda:
+    if not _native.on_device(counts):
         return torch.from_numpy((O.cpm(counts.numpy().astype(np.float64), lib.numpy()) >= min_cpm).sum(1).astype(np.int32))
     G, S = counts.shape
     out = torch.empty(G, dtype=torch.int32, device=counts.device)
@@ -72,7 +72,7 @@ def tmm_factors(counts: torch.Tensor, lib: Optional[torch.Tensor] = None, *, log
     """edgeR ``calcNormFactors(method="TMM")`` on a (filtered) count matrix; float64 [S] with geometric mean 1."""
     counts = _as_counts(counts)
     lib = lib_sizes(counts) if lib is None else lib.double()
-    if not counts.is_cuda:
+    if not _native.on_device(counts):
         return torch.from_numpy(O.tmm_factors(counts.numpy().astype(np.float64), lib.numpy(), ref_column))
     lib = lib.contiguous()
     G, S = counts.shape
@@ -101,7 +101,7 @@ def log_cpm(counts: torch.Tensor, lib: torch.Tensor, norm_factors: Optional[torc
     ``sample_major=True`` writes the transposed samples x genes model matrix directly."""
     counts = _as_counts(counts)
     eff = lib.double() * (1.0 if norm_factors is None else norm_factors.double())
-    if not counts.is_cuda:
+    if not _native.on_device(counts):
         c = counts.numpy().astype(np.float64)
         if rows is not None:
             c = c[rows.numpy()]

@@ -110,6 +110,19 @@ __device__ __forceinline__ float block_sum(float v, float* scratch) {
 __host__ __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ __forceinline__ long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 
+// ---- cache-hint and system-scope PTX shared by several kernels -------------------------------------------------------
+// Under the host execution model (CML_EMU, csrc/emu/cuda_emu.h) these are plain accesses: one OS thread runs every
+// emulated thread, so there is nothing to order; a multicast (multimem) address does not exist there and traps.
+#ifdef CML_EMU
+inline int4 ld_stream(const int4* p) { return *p; }
+inline float ld_stream_f32(const float* p) { return *p; }
+inline void prefetch_l1(const void*) {}
+inline void red_add_v4_sys(float* addr, float4 v) { addr[0] += v.x; addr[1] += v.y; addr[2] += v.z; addr[3] += v.w; }
+inline void red_add_sys(float* addr, float v) { *addr += v; }
+inline void multimem_red_add_v4(float*, float4) { ::cml_emu::trap("multimem.red is not available under the host execution model"); }
+inline void st_release_sys(unsigned* addr, unsigned v) { *addr = v; }
+inline unsigned ld_acquire_sys(const unsigned* addr) { return *addr; }
+#else
 // 128-bit streaming loads that do not pollute L1 (single-use data).
 __device__ __forceinline__ int4 ld_stream(const int4* p) {
   int4 r;
@@ -117,5 +130,33 @@ __device__ __forceinline__ int4 ld_stream(const int4* p) {
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
+__device__ __forceinline__ float ld_stream_f32(const float* p) {
+  float r;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// reductions into (possibly peer) global memory and the release / acquire pair of the completion signals
+__device__ __forceinline__ void red_add_v4_sys(float* addr, float4 v) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_sys(float* addr, float v) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_v4(float* mc_addr, float4 v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_release_sys(unsigned* addr, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* addr) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+#endif
 
 }  // namespace cml

@@ -31,27 +31,6 @@ struct Peers {
   int rank, world;
 };
 
-__device__ __forceinline__ void red_add_v4_sys(float* addr, float4 v) {
-  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-}
-__device__ __forceinline__ void red_add_sys(float* addr, float v) {
-  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
-}
-__device__ __forceinline__ void multimem_red_add_v4(float* mc_addr, float4 v) {
-  asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
-               "f"(v.z), "f"(v.w)
-               : "memory");
-}
-__device__ __forceinline__ void st_release_sys(unsigned* addr, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* addr) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-  return v;
-}
-
 // ============================================================================================ path 2
 // g[j][b] = sum_i X[i][j] R[i][b] over this rank's rows, reduce-scattered by gene: gene j is owned by rank
 // j / genes_per_rank and lands in that rank's buffer at [(j % genes_per_rank)][b].

@@ -53,13 +53,6 @@ struct RsParams {
   float alpha;
 };
 
-__device__ __forceinline__ void red_add_v4_sys(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-__device__ __forceinline__ void st_release_sys(unsigned* addr, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-
 // (k-slice, m, n) of a work item: k-slices outermost, grouped (m, n) order inside a slice (panels stay L2-resident)
 __device__ __forceinline__ void decode(const RsParams& P, int item, int& ks, int& m_blk, int& n_blk) {
   const int per_slice = P.tiles_m * P.tiles_n;
@@ -210,7 +203,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) xtr_gem
         } else if (row_warp0 + lane < P.p) {
           float* dst = P.out[owner] + (size_t)(lrow0 + lane) * P.ldo + ocol0;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) red_add_v4_sys(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          for (int j = 0; j < 32; j += 4) red_add_v4_sys(dst + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
         }
       }
       tc_fence_before();

@@ -112,7 +112,7 @@ struct Warp {
     const float* xk = P.xt + (size_t)k * P.n_pad + lane;
 #pragma unroll
     for (int j = 0; j < NPL; ++j)
-      asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(x[j]) : "l"(xk + 32 * j));
+      x[j] = ld_stream_f32(xk + 32 * j);
   }
   __device__ __forceinline__ float vpk(int k) const { return P.vp ? __ldg(P.vp + k) : 1.f; }
   __device__ __forceinline__ bool bit(const unsigned* s, int k) const { return (s[k >> 5] >> (k & 31)) & 1u; }
@@ -265,7 +265,7 @@ struct Warp {
       const int idx = l0 + (lane >> 2), j = lane & 3;
       if (idx < nin && j < NPL) {
         const float* a = P.xt + (size_t)m()[idx] * P.n_pad + 32 * j;
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+        prefetch_l1(a);
       }
     };
     hint(0);

@@ -24,7 +24,10 @@ _I, _LL, _SZ, _F, _P = ctypes.c_int, ctypes.c_longlong, ctypes.c_size_t, ctypes.
 
 def _lib():
     from consensusml_b200 import _build
-    lib = ctypes.CDLL(str(_build.CUDA_LIB))
+    return _declare(ctypes.CDLL(str(_build.CUDA_LIB)))
+
+
+def _declare(lib):
     lib.cml_last_error.restype = ctypes.c_char_p
     head = [_I] * 6 + [_P, _P, _LL, _P, _P, _LL, _P, _P, _F, _F, _I, _I, _I]
     lib.cml_lognet_path.argtypes = head + [_P, _SZ] + [_P] * 11 + [_P]
@@ -52,8 +55,7 @@ def _problem(seed, B, n, p, L):
     return x, y, w, lam
 
 
-def _outputs(B, L, nx, n_pad, p):
-    dev = "cuda"
+def _outputs(B, L, nx, n_pad, p, dev="cuda"):
     i32, f32 = dict(dtype=torch.int32, device=dev), dict(dtype=torch.float32, device=dev)
     return dict(m=torch.zeros(B, nx, **i32), ca=torch.zeros(B, L, nx, **f32), kin=torch.zeros(B, L, **i32),
                 a0=torch.zeros(B, L, **f32), dev=torch.zeros(B, L, **f32), eta=torch.zeros(B, L, n_pad, **f32),
@@ -61,31 +63,34 @@ def _outputs(B, L, nx, n_pad, p):
                 lmu=torch.zeros(B, **i32), jerr=torch.zeros(B, **i32))
 
 
-def _run(lib, static, x, y, w, lam, nx=128):
+def _run(lib, static, x, y, w, lam, nx=128, device="cuda"):
+    """``device="cpu"`` is used by tests/test_emu_kernels.py, which drives the same two entry points of the emulated
+    library (host pointers, no stream)."""
     B, n = w.shape
     p = x.shape[1]
     L = lam.numel()
     n_pad = lib.cml_lognet_n_pad(n)
-    xt = torch.zeros(p, n_pad, device="cuda")
-    xt[:, :n] = x.t().cuda()
-    yp = torch.zeros(n_pad, device="cuda")
-    yp[:n] = y.cuda()
-    wp = torch.zeros(B, n_pad, device="cuda")
-    wp[:, :n] = w.cuda()
-    lam_d = lam.cuda()
-    o = _outputs(B, L, nx, n_pad, p)
+    xt = torch.zeros(p, n_pad, device=device)
+    xt[:, :n] = x.t().to(device)
+    yp = torch.zeros(n_pad, device=device)
+    yp[:n] = y.to(device)
+    wp = torch.zeros(B, n_pad, device=device)
+    wp[:, :n] = w.to(device)
+    lam_d = lam.to(device)
+    o = _outputs(B, L, nx, n_pad, p, device)
     ptr = lambda t: ctypes.c_void_p(t.data_ptr())
-    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream if device == "cuda" else 0)
     head = [B, n, n_pad, p, L, nx, ptr(xt), ptr(yp), 0, ptr(wp), None, 0, None, ptr(lam_d), 1.0, 1e-7, 0, 0, 100000]
     outs = [ptr(o[k]) for k in ("m", "ca", "kin", "a0", "dev", "eta", "freq", "nulldev", "npasses", "lmu", "jerr")]
     if static:
         rc = lib.cml_lognet_path_static(*head, *outs, stream)
     else:
         nbytes = lib.cml_lognet_scratch_bytes(B, n_pad, p)
-        scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")      # the ordinary path: caller-provided scratch
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=device)      # the ordinary path: caller-provided scratch
         rc = lib.cml_lognet_path(*head, ptr(scratch), nbytes, *outs, stream)
     assert rc == 0, lib.cml_last_error().decode()
-    torch.cuda.synchronize()
+    if device == "cuda":
+        torch.cuda.synchronize()
     return o
 
 
@@ -111,16 +116,14 @@ def test_static_scratch_entry_matches_regular_entry_twice():
         ref = _run(lib, False, x, y, w, lam)
         got = _run(lib, True, x, y, w, lam)
         assert int(ref["jerr"].abs().max()) == 0 and int(got["jerr"].abs().max()) == 0
-        # same tolerances as tests/test_lasso_gpu.py; pass counts and selection counts may move by a hair because a
-        # replicate whose convergence test sits on the threshold can take one sweep more or less
-        assert (ref["kin"] - got["kin"]).abs().max() <= 1
-        assert ((ref["npasses"] - got["npasses"]).abs().float() <= 0.05 * ref["npasses"].float() + 2).all()
-        assert (ref["a0"] - got["a0"]).abs().max() < 5e-3
-        assert (ref["dev"] - got["dev"]).abs().max() < 2e-3
-        assert (ref["eta"] - got["eta"]).abs().max() < 2e-2
-        assert (ref["freq"] - got["freq"]).abs().max() <= 2
+        # Both entry points run the same kernel on the same inputs; only the address of the work slab and the number
+        # of warps sharing the batch differ, and neither enters the arithmetic of a fit: the results are identical.
+        # (Round 1 needed tolerances here because the kernel read one shared-memory word before writing it; see
+        # tests/test_emu_kernels.py::test_lasso_path_kernel_does_not_depend_on_stale_shared_memory_or_thread_order.)
+        for k in ("kin", "npasses", "lmu", "a0", "dev", "eta", "freq", "nulldev"):
+            assert torch.equal(ref[k], got[k]), k
         for b in (0, B // 2, B - 1):
-            assert (_dense(ref, b, p) - _dense(got, b, p)).abs().max() < 5e-3
+            assert torch.equal(_dense(ref, b, p), _dense(got, b, p))
         assert float(got["freq"].sum()) > 0
 
 
