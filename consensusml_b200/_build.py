@@ -233,6 +233,7 @@ def build_emu(force: bool = False) -> Path:
 
 def build_all(force: bool = False, cuda: bool = True) -> None:
     build_host(force)
+    build_emu(force)
     if cuda:
         build_cuda(force)
 

@@ -100,6 +100,22 @@ class Cohort:
         return Cohort(self.assay.to(device), self.gene_ids, self.sample_ids, self.row_data, self.col_data,
                       dict(self.metadata), self.assay_name)
 
+    def fingerprint(self, label_col: str = "deg.risk", split_col: str = "exptset.seahack") -> str:
+        """Content hash of what a model fit depends on: gene and sample ids, the label and split columns and the assay
+        values.  Checkpoints are keyed by it, so two cohorts of the same shape never share a cached result."""
+        import hashlib
+        h = hashlib.sha256()
+        h.update("\x1f".join(self.gene_ids).encode())
+        h.update(b"\x1e")
+        h.update("\x1f".join(self.sample_ids).encode())
+        for col in (label_col, split_col):
+            h.update(b"\x1e")
+            if col in self.col_data:
+                h.update("\x1f".join(map(str, self.col_data[col].tolist())).encode())
+        a = self.assay.detach().to("cpu", torch.float64).contiguous()
+        h.update(a.numpy().tobytes())
+        return h.hexdigest()[:24]
+
     # ---- persistence --------------------------------------------------------------------
     def save(self, path: str) -> None:
         torch.save({"assay": self.assay.cpu(), "gene_ids": self.gene_ids, "sample_ids": self.sample_ids,

@@ -60,8 +60,10 @@ def _matmul_nt(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
 
 
 def train_grid(x: torch.Tensor, y: torch.Tensor, configs: Sequence[Dict], epochs: int = 200, x_val: Optional[torch.Tensor] = None,
-               y_val: Optional[torch.Tensor] = None, n_total: Optional[int] = None) -> MLPGridResult:
-    """Full-batch Adam on binary cross-entropy for every configuration at once (one hidden ReLU layer)."""
+               y_val: Optional[torch.Tensor] = None, n_total: Optional[int] = None, sharded: bool = False) -> MLPGridResult:
+    """Full-batch Adam on binary cross-entropy for every configuration at once (one hidden ReLU layer).
+    ``sharded=True``: ``x`` holds this rank's samples of an ``n_total``-sample cohort and the gradients are all-reduced
+    (a collective - every rank must call); the default trains on ``x`` alone, whatever process group exists."""
     from ..ops.metrics import auc
     dev = x.device
     n, p = x.shape
@@ -110,7 +112,7 @@ def train_grid(x: torch.Tensor, y: torch.Tensor, configs: Sequence[Dict], epochs
         gw1 = _matmul_nt(dh.t().contiguous(), xst)                     # [H, p]   GEMM 2
         gb1 = dh.sum(0)
         grads = [gw1, gb1, gw2, gb2]
-        for gr in grads:
+        for gr in (grads if sharded else ()):
             all_reduce_(gr)                                            # sample-sharded: one reduction per tensor
         for i, (pt, gr) in enumerate(zip(params, grads)):
             if wds[i] is not None:
@@ -120,7 +122,8 @@ def train_grid(x: torch.Tensor, y: torch.Tensor, configs: Sequence[Dict], epochs
             mh = m[i] / (1 - b1a ** t)
             vh = v[i] / (1 - b2a ** t)
             pt.sub_(lrs[i] * mh / (vh.sqrt() + eps))
-    all_reduce_(loss_g)
+    if sharded:
+        all_reduce_(loss_g)
     res = MLPGridResult(list(configs), loss_g / n_total, None, None, w1, b1, w2, b2, [int(o) for o in offsets], mean, scale)
     if x_val is not None:
         yv = y_val.float()

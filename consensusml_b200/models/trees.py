@@ -323,59 +323,93 @@ class RandomForest:
     confusion_oob_: torch.Tensor = field(default=None, repr=False)
 
     def fit(self, x: torch.Tensor, y: torch.Tensor) -> "RandomForest":
-        from ..ops.metrics import confusion_matrix
-        from ..ops.replicate import replicate_weights
-        n, p = x.shape
-        dev = x.device
-        self.binner, bins = Binner.fit(x)
-        mtry = self.mtry if self.mtry is not None else max(1, int(np.floor(np.sqrt(p))))
-        yf = y.float().to(dev)
-        imp = {k: torch.zeros(p, dtype=torch.float32, device=dev) for k in ("gain", "cover", "freq")}
-        votes1 = torch.zeros(n, device=dev)
-        nvote = torch.zeros(n, device=dev)
-        prox = torch.zeros(n, n, device=dev) if self.proximity else None
-        pairs = torch.zeros(n, n, device=dev) if self.proximity else None
-        self.trees = []
-        done = 0
+        self.begin(x, y)
+        parts, done = [], 0
         while done < self.n_trees:
             T = min(self.tree_batch, self.n_trees - done)
-            if self.bootstrap:
-                w = replicate_weights(T, n, mode="bootstrap", seed=self.seed, device=dev, rep0=done)[:, :n].contiguous()
-            else:
-                w = torch.ones(T, n, device=dev)
-            tb = grow(bins, n, w * yf[None, :], w, criterion=GINI, mtry=mtry, max_depth=self.max_depth,
-                      max_bin=self.binner.max_bin, min_samples_leaf=float(self.min_samples_leaf), seed=self.seed + done,
-                      importance=imp, in_tree=w > 0)
-            self.trees.append(tb)
-            leaf, val = predict_leaves(tb, bins, n)
-            vote = (val > 0.5).float()
-            oob = (w == 0).float()
-            votes1 += (vote * oob).sum(0)
-            nvote += oob.sum(0)
-            if prox is not None:
-                use_oob = self.oob_prox and self.bootstrap
-                ob = (w == 0).to(torch.uint8).contiguous() if use_oob else None
-                if _native.on_device(leaf):
-                    rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), _native.ptr(ob), T, n,
-                                                             _native.ptr(prox), _native.ptr(pairs), _native.stream_ptr())
-                    _native.check(rc, "cml_forest_proximity")
-                else:
-                    both = (ob[:, :, None] & ob[:, None, :]).bool() if use_oob else torch.ones(T, n, n, dtype=torch.bool)
-                    prox += ((leaf[:, :, None] == leaf[:, None, :]) & both).float().sum(0)
-                    pairs += both.float().sum(0)
+            parts.append(self.grow_chunk(done, T))
             done += T
-        self.importance_ = imp["gain"] / self.n_trees
-        self.importance_cover_ = imp["cover"]
-        self.importance_freq_ = imp["freq"]
-        frac = votes1 / nvote.clamp_min(1)
+        return self.finish(parts)
+
+    # The forest is a sum over trees of everything it reports (importance, out-of-bag votes, proximity counts), and a
+    # tree's randomness depends only on (seed, tree index).  ``begin / grow_chunk / finish`` expose that: chunks of
+    # trees can be grown in any order, on any rank (parallel/tasks.py), and merged - the result does not depend on how
+    # the chunks were distributed, only on where their boundaries are.
+    def begin(self, x: torch.Tensor, y: torch.Tensor) -> "RandomForest":
+        n, p = x.shape
+        self.binner, self._bins = Binner.fit(x)
+        self._mtry = self.mtry if self.mtry is not None else max(1, int(np.floor(np.sqrt(p))))
+        self._yf = y.float().to(x.device)
+        self._n, self._p = n, p
+        self.trees = []
+        return self
+
+    def grow_chunk(self, tree0: int, T: int, x_eval: Optional[torch.Tensor] = None, keep_trees: bool = True) -> Dict[str, torch.Tensor]:
+        """Grow trees [tree0, tree0 + T) and return their contribution to every forest statistic (device tensors):
+        importance sums, out-of-bag vote counts, proximity / pair counts and - with ``x_eval`` - the number of trees
+        voting class 1 for each evaluation sample."""
+        from ..ops.replicate import replicate_weights
+        n, p, dev, bins, yf = self._n, self._p, self._bins.device, self._bins, self._yf
+        imp = {k: torch.zeros(p, dtype=torch.float32, device=dev) for k in ("gain", "cover", "freq")}
+        if self.bootstrap:
+            w = replicate_weights(T, n, mode="bootstrap", seed=self.seed, device=dev, rep0=tree0)[:, :n].contiguous()
+        else:
+            w = torch.ones(T, n, device=dev)
+        tb = grow(bins, n, w * yf[None, :], w, criterion=GINI, mtry=self._mtry, max_depth=self.max_depth,
+                  max_bin=self.binner.max_bin, min_samples_leaf=float(self.min_samples_leaf), seed=self.seed + tree0,
+                  importance=imp, in_tree=w > 0)
+        if keep_trees:
+            self.trees.append(tb)
+        leaf, val = predict_leaves(tb, bins, n)
+        oob = (w == 0).float()
+        part = {"n_trees": torch.tensor(T), "gain": imp["gain"], "cover": imp["cover"], "freq": imp["freq"],
+                "votes1": ((val > 0.5).float() * oob).sum(0), "nvote": oob.sum(0), "nodes": tb.node_count.sum()}
+        if self.proximity:
+            prox = torch.zeros(n, n, device=dev)
+            pairs = torch.zeros(n, n, device=dev)
+            use_oob = self.oob_prox and self.bootstrap
+            ob = (w == 0).to(torch.uint8).contiguous() if use_oob else None
+            if _native.on_device(leaf):
+                rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), _native.ptr(ob), T, n,
+                                                         _native.ptr(prox), _native.ptr(pairs), _native.stream_ptr())
+                _native.check(rc, "cml_forest_proximity")
+            else:
+                both = (ob[:, :, None] & ob[:, None, :]).bool() if use_oob else torch.ones(T, n, n, dtype=torch.bool)
+                prox += ((leaf[:, :, None] == leaf[:, None, :]) & both).float().sum(0)
+                pairs += both.float().sum(0)
+            part["prox"], part["pairs"] = prox, pairs
+        if x_eval is not None:
+            _, ve = predict_leaves(tb, self.binner.transform(x_eval), x_eval.shape[0])
+            part["eval_votes1"] = (ve > 0.5).float().sum(0)
+        return part
+
+    def finish(self, parts) -> "RandomForest":
+        """Merge chunk contributions (in the order given; sums of non-negative counts, so the order does not matter
+        for anything but the last bit of the fp32 importance sums - pass them sorted by tree0 for bit-reproducibility)."""
+        from ..ops.metrics import confusion_matrix
+        dev = self._bins.device
+        tot = {}
+        for part in parts:
+            for k, v in part.items():
+                v = torch.as_tensor(v).to(dev)
+                tot[k] = v.clone() if k not in tot else tot[k] + v
+        nt = int(tot["n_trees"])
+        self.n_trees_grown_ = nt
+        self.importance_ = tot["gain"] / nt
+        self.importance_cover_ = tot["cover"]
+        self.importance_freq_ = tot["freq"]
+        self.mean_nodes_ = float(tot["nodes"]) / nt
+        frac = tot["votes1"] / tot["nvote"].clamp_min(1)
         self.oob_votes_ = frac
         pred = (frac > 0.5).float()
-        has = nvote > 0
+        has = tot["nvote"] > 0
+        yf = self._yf
         self.oob_error_ = float((pred[has] != yf[has]).float().mean())
         self.confusion_oob_ = confusion_matrix(pred[has], yf[has])
-        if prox is not None:
-            self.proximity_ = prox / pairs.clamp_min(1)
+        if "prox" in tot:
+            self.proximity_ = tot["prox"] / tot["pairs"].clamp_min(1)
             self.proximity_.fill_diagonal_(1.0)
+        self.eval_proba_ = tot["eval_votes1"] / nt if "eval_votes1" in tot else None
         return self
 
     def _accumulate(self, x, fn):

@@ -1,0 +1,94 @@
+"""Static task scheduler: spread the independent pieces of a pipeline run over the ranks.
+
+The reference runs its ensemble strictly one model after the other in one R session (cml_targetaml_seanalysis.Rmd:638-1298:
+SVM x4 at :648-667, 15 x LOOCV lasso at :728-773, RF 2k/5k/10k at :1037-1050, xgboost x5 at :1164-1186).  None of those
+stages depends on another - only the consensus table at the end needs all of them - so on N GPUs they are independent
+tasks: the sequential lasso exclusion chain stays on one rank, the 17,000 forest trees are cut into fixed 1000-tree
+chunks, every SVM / boosting / MLP configuration is a task of its own.
+
+Design rules
+  * The task list and its chunk boundaries never depend on the world size, and every task derives its random streams
+    from its own identity (tree index, replicate index), so the merged result is the same for 1, 2, 4 or 8 ranks.
+  * Assignment is longest-processing-time-first on declared costs, computed identically on every rank (no
+    communication, no work stealing: the run is a second long, a dynamic queue would cost more than it saves).
+  * Results are small (per-gene vectors, n x n proximity sums); one ``all_gather_object`` at the end gives every rank
+    every result.  Device time per task is recorded so the limiting task can be named.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass, field
+from typing import Any, Callable, Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+@dataclass
+class Task:
+    name: str
+    cost: float
+    fn: Callable[[], Any]
+    group: str = ""
+
+
+@dataclass
+class TaskReport:
+    assignment: Dict[str, int] = field(default_factory=dict)     # task -> rank
+    seconds: Dict[str, float] = field(default_factory=dict)      # task -> wall seconds on its rank
+    rank_seconds: List[float] = field(default_factory=list)      # per rank: sum of its tasks
+
+    def critical(self) -> Dict[str, Any]:
+        if not self.rank_seconds:
+            return {}
+        r = max(range(len(self.rank_seconds)), key=lambda i: self.rank_seconds[i])
+        mine = {k: v for k, v in self.seconds.items() if self.assignment.get(k) == r}
+        top = max(mine, key=mine.get) if mine else None
+        return {"rank": r, "seconds": self.rank_seconds[r], "largest_task": top, "largest_task_seconds": mine.get(top)}
+
+
+def assign(tasks: List[Task], world: int) -> Dict[str, int]:
+    """Longest-processing-time-first: heaviest task to the least loaded rank (ties: lowest rank, input order)."""
+    load = [0.0] * world
+    out: Dict[str, int] = {}
+    order = sorted(range(len(tasks)), key=lambda i: (-tasks[i].cost, i))
+    for i in order:
+        r = min(range(world), key=lambda k: (load[k], k))
+        out[tasks[i].name] = r
+        load[r] += tasks[i].cost
+    return out
+
+
+def run_tasks(tasks: List[Task], *, enabled: bool = True) -> tuple[Dict[str, Any], TaskReport]:
+    """Run every task on the rank it is assigned to and return ``{task name: result}`` complete on every rank.
+    Results must be picklable and live on the host (tasks copy what they return off the device)."""
+    names = [t.name for t in tasks]
+    if len(set(names)) != len(names):
+        raise ValueError("task names must be unique")
+    world = dist.get_world_size() if (enabled and dist.is_initialized()) else 1
+    rank = dist.get_rank() if world > 1 else 0
+    amap = assign(tasks, world)
+    local: Dict[str, Any] = {}
+    secs: Dict[str, float] = {}
+    for t in tasks:
+        if amap[t.name] != rank:
+            continue
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        local[t.name] = t.fn()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        secs[t.name] = time.perf_counter() - t0
+    if world > 1:
+        gathered: List[Optional[tuple]] = [None] * world
+        dist.all_gather_object(gathered, (local, secs))
+        results: Dict[str, Any] = {}
+        all_secs: Dict[str, float] = {}
+        for part, s in gathered:
+            results.update(part)
+            all_secs.update(s)
+    else:
+        results, all_secs = local, secs
+    rep = TaskReport(amap, all_secs, [sum(v for k, v in all_secs.items() if amap[k] == r) for r in range(world)])
+    return {n: results[n] for n in names}, rep

@@ -18,7 +18,7 @@ from .data import Cohort
 from .models import lasso as L
 from .models import mlp as MLP
 from .models import svm as S
-from .models import trees as T
+from .models import trees as T_
 from .ops import metrics as M
 from .report import dump as R
 from .runtime.config import Config
@@ -59,109 +59,226 @@ def cohort_from_counts(counts: torch.Tensor, gene_ids, sample_ids, group: np.nda
     return Cohort(assay.double(), ids, list(sample_ids), rd, cd, {"n_deg": len(ids), "df_prior": de.df_prior})
 
 
+def _host(t):
+    return t.detach().float().cpu().numpy() if isinstance(t, torch.Tensor) else np.asarray(t)
+
+
+def _rf_tag(nt: int) -> str:
+    return f"{nt // 1000}k" if nt % 1000 == 0 else str(nt)
+
+
+def build_tasks(cfg: Config, cohort: Cohort, dev: torch.device, store: Optional[ArtifactStore], key: str, log: RunLog):
+    """The independent pieces of one ensemble run (see parallel/tasks.py).  Every task returns host-side, picklable data.
+    The device copies of the design matrices are created lazily - a rank only uploads what its own tasks need."""
+    from .parallel.tasks import Task
+    cache: Dict[str, object] = {}
+
+    def data():
+        if "xy" not in cache:
+            tr, te = cohort.split()
+            cache["xy"] = (tr.design(torch.float32).to(dev, non_blocking=True), tr.labels().to(dev, non_blocking=True),
+                           te.design(torch.float32).to(dev, non_blocking=True), te.labels().to(dev, non_blocking=True))
+        return cache["xy"]
+
+    def checkpointed(name, fn):
+        if store is None:
+            return fn
+        return lambda: store.run(f"tasks/{name}", key, lambda: {"v": fn()}, log)["v"]
+
+    tasks = []
+
+    def add(name, cost, fn, group):
+        tasks.append(Task(name, cost, checkpointed(name, fn), group))
+
+    if cfg.lasso.enabled:
+        def lasso_task():
+            reps = L.exclusion_reps(cohort, nreps=cfg.lasso.exclusion_reps, seed=cfg.lasso.seed, alpha=cfg.lasso.alpha,
+                                    nfolds=cfg.lasso.nfolds, device=dev)
+            r1 = reps[0]
+            return {"nonzero": [r.nonzero_coef for r in reps], "curves": R.lasso_rep_curves(reps),
+                    "test_error": [r.test_error for r in reps], "jerr": [r.jerr for r in reps],
+                    "rep1": {"lambda_min": r1.cv.lambda_min, "lambda_1se": r1.cv.lambda_1se, "test_error": r1.test_error,
+                             "auc": r1.test_auc, "logloss": r1.test_logloss, "confusion": r1.confusion.tolist(),
+                             "train_npasses": r1.train_npasses, "final_npasses": r1.final_npasses}}
+        # the exclusion chain is sequential (each replicate removes the genes the previous ones selected): one task
+        add("lasso", 4.0 + 0.75 * cfg.lasso.exclusion_reps, lasso_task, "lasso")
+
+    if cfg.svm.enabled:
+        k = 0
+        for kern in cfg.svm.kernels:
+            for wf in cfg.svm.weightfilt:
+                k += 1
+
+                def svm_task(kern=kern, wf=wf, k=k):
+                    xtr, ytr, xte, yte = data()
+                    r = S.run_svm(xtr, ytr, xte, yte, kern, weightfilt=wf, seed=cfg.svm.seed)
+                    check_finite(f"svm{k}_weights", r.weightsvect)
+                    # the weights of the model that is actually evaluated (the reference stored the pre-filter vector twice)
+                    w = torch.zeros(cohort.n_genes, device=dev)
+                    w[r.columns] = r.model.weights()
+                    return {"weights": _host(w), "score": _host(torch.sigmoid(r.decision_test)),
+                            "summary": {"kernel": kern, "weightfilt": wf, "test_error": r.test_error, "auc": r.auc,
+                                        "precision": r.precision_test, "recall": r.recall_test, "iters": r.model.iters_}}
+                add(f"svm{k}", 1.0 if not wf else 1.5, svm_task, "svm")
+
+    if cfg.rf.enabled:
+        chunk = max(1, int(cfg.rf.chunk))
+        for nt in cfg.rf.n_trees:
+            tag = _rf_tag(nt)
+            for c0 in range(0, nt, chunk):
+                T = min(chunk, nt - c0)
+
+                def rf_task(nt=nt, c0=c0, T=T):
+                    xtr, ytr, xte, _ = data()
+                    pk = ("rf", nt)
+                    if pk not in cache:          # binning + labels once per forest and rank
+                        cache[pk] = T_.RandomForest(n_trees=nt, proximity=cfg.rf.proximity, seed=cfg.rf.seed).begin(xtr, ytr)
+                    part = cache[pk].grow_chunk(c0, T, x_eval=xte, keep_trees=False)
+                    return {kk: _host(v) for kk, v in part.items()}
+                add(f"rf_{tag}_t{c0}", 1.2 * T / 1000.0, rf_task, f"rf_{tag}")
+
+    if cfg.gbm.enabled:
+        for i, rep in enumerate(cfg.gbm.reps, 1):
+            def gbm_task(rep=rep):
+                xtr, ytr, xte, yte = data()
+                gb = T_.GradientBoosting(n_estimators=int(rep["nrounds"]), learning_rate=cfg.gbm.eta, max_depth=int(rep["max_depth"]),
+                                         mode="xgboost").fit(xtr, ytr)
+                pr = gb.predict_proba(xte)
+                gain = gb.importance_["gain"]
+                return {"gain": _host(gain), "score": _host(pr),
+                        "summary": {"train_error": gb.train_error_[-1], "test_error": float(((pr > 0.5).float() != yte).float().mean()),
+                                    "auc": M.auc(pr, yte), "n_genes": int((gain > 0).sum())}}
+            add(f"xgb{i}", 0.05 * float(rep["nrounds"]) * min(float(rep["max_depth"]), 8.0) / 4.0 + 0.2, gbm_task, "gbm")
+
+    if cfg.mlp.enabled:
+        def mlp_task():
+            xtr, ytr, xte, yte = data()
+            grid = MLP.make_grid(cfg.mlp.hidden, cfg.mlp.lr, cfg.mlp.weight_decay)
+            # the grid point is chosen on an inner split of the TRAINING samples; the held-out test set is only used to
+            # report that single choice (lasso / SVM / RF / GBM never see the test set either)
+            n = xtr.shape[0]
+            perm = torch.randperm(n, generator=torch.Generator().manual_seed(cfg.mlp.seed)).to(dev)
+            n_val = max(2, int(round(cfg.mlp.val_frac * n)))
+            iv, it = perm[:n_val], perm[n_val:]
+            sel = MLP.train_grid(xtr[it], ytr[it], grid, epochs=cfg.mlp.epochs, x_val=xtr[iv], y_val=ytr[iv])
+            best = int(torch.argmin(sel.val_loss))
+            res = MLP.train_grid(xtr, ytr, [grid[best]], epochs=cfg.mlp.epochs, x_val=xte, y_val=yte)
+            return {"importance": _host(res.input_importance(0)), "score": _host(res.predict_proba(xte, 0)),
+                    "summary": {"best": grid[best], "inner_val_loss": float(sel.val_loss[best]), "inner_val_auc": float(sel.val_auc[best]),
+                                "auc": float(res.val_auc[0]), "test_loss": float(res.val_loss[0])}}
+        add("mlp", 2.0, mlp_task, "mlp")
+    return tasks
+
+
 def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = None, return_details: bool = False) -> Dict:
     """Run the ensemble + consensus on ``cohort`` (default: the bundled TARGET-AML DEG cohort).  Returns a summary dict
-    and writes ``standouttable.csv``, the lasso gene CSV, ``consensus_rank.csv`` and the report dumps."""
+    and writes ``standouttable.csv``, the lasso gene CSV, ``consensus_rank.csv`` and the report dumps.
+
+    Under ``torchrun`` (``torch.distributed`` initialised, ``cfg.dist.enabled``) the independent stages are spread over
+    the ranks (parallel/tasks.py); every rank returns the same summary, rank 0 writes the files.  The result does not
+    depend on the number of ranks."""
+    import torch.distributed as dist
+    from .parallel.tasks import run_tasks
     dev = resolve_device(cfg)
     out = cfg.io.out_dir
-    log = log or RunLog(os.path.join(out, "run.jsonl"))
-    store = ArtifactStore(out, resume=cfg.resume)
+    multi = cfg.dist.enabled and dist.is_initialized() and dist.get_world_size() > 1
+    rank = dist.get_rank() if multi else 0
+    log = log or RunLog(os.path.join(out, "run.jsonl") if cfg.write_outputs else None, rank=rank)
+    store = ArtifactStore(out, resume=cfg.resume, rank=rank) if cfg.checkpoint else None
     cohort = cohort or datasets.load_target_aml()
-    log.event("run_start", device=str(dev), genes=cohort.n_genes, samples=cohort.n_samples, config_hash=cfg.hash())
-    tr, te = cohort.split()
-    xtr, ytr = tr.design(torch.float32).to(dev), tr.labels().to(dev)
-    xte, yte = te.design(torch.float32).to(dev), te.labels().to(dev)
+    fp = cohort.fingerprint()
+    log.event("run_start", device=str(dev), genes=cohort.n_genes, samples=cohort.n_samples, config_hash=cfg.hash(),
+              cohort_fingerprint=fp, world=dist.get_world_size() if multi else 1)
     genes = cohort.gene_ids
+    # a checkpoint is only reused for the same configuration AND the same data (ids, labels, split and assay content)
+    key = cfg.hash(["lasso", "svm", "rf", "gbm", "mlp", "split"]) + ":" + fp
+    tasks = build_tasks(cfg, cohort, dev, store, key, log)
+    results, report = run_tasks(tasks, enabled=cfg.dist.enabled)
+    for t in tasks:
+        log.event("task", task=t.name, group=t.group, rank=report.assignment[t.name], seconds=report.seconds.get(t.name))
+
     st = CS.StandTable(cohort)
     importances: Dict[str, np.ndarray] = {}
     scores: Dict[str, np.ndarray] = {}            # test-set class-1 probabilities per model (for one-vs-rest voting)
     summary: Dict[str, Dict] = {}
-    data_key = f"{cohort.n_genes}x{cohort.n_samples}"
+    tr_c, te_c = cohort.split()
+    yte_np = te_c.labels().cpu().numpy()
 
     if cfg.lasso.enabled:
-        def lasso_stage():
-            reps = L.exclusion_reps(cohort, nreps=cfg.lasso.exclusion_reps, seed=cfg.lasso.seed, alpha=cfg.lasso.alpha,
-                                    nfolds=cfg.lasso.nfolds, device=dev)
-            return {"reps": reps}
-        with log.stage("lasso"):
-            res = store.run("models/lasso", cfg.hash(["lasso", "split"]) + data_key, lasso_stage, log)["reps"]
-        for i, r in enumerate(res, 1):
-            st.add(f"lasso_coef_rep{i}", r.nonzero_coef)
+        lr = results["lasso"]
+        for i, nz in enumerate(lr["nonzero"], 1):
+            st.add(f"lasso_coef_rep{i}", nz)
         importances["lasso"] = st.df["lasso_coef_rep1"].to_numpy()
-        r1 = res[0]
-        CS.write_lasso_gene_csv(r1.nonzero_coef, os.path.join(out, "Logistic_Lasso_RiskGroup_Associated_Genes.csv"))
-        summary["lasso"] = {"lambda_min": r1.cv.lambda_min, "lambda_1se": r1.cv.lambda_1se, "test_error": r1.test_error,
-                            "auc": r1.test_auc, "confusion": r1.confusion.tolist(), "n_genes": [len(r.nonzero_coef) for r in res],
-                            "jerr": r1.jerr}
-        R.write_all(os.path.join(out, "report"), {"lasso_rep_curves": R.lasso_rep_curves(res)})
-
+        summary["lasso"] = {**lr["rep1"], "n_genes": [len(nz) for nz in lr["nonzero"]], "test_errors": lr["test_error"],
+                            "jerr": lr["jerr"][0], "genes_rep1": sorted(lr["nonzero"][0])}
     if cfg.svm.enabled:
-        with log.stage("svm"):
-            k = 0
-            for kern in cfg.svm.kernels:
-                for wf in cfg.svm.weightfilt:
-                    k += 1
-                    r = S.run_svm(xtr, ytr, xte, yte, kern, weightfilt=wf, seed=cfg.svm.seed)
-                    check_finite(f"svm{k}_weights", r.weightsvect)
-                    # the weights of the model that is actually evaluated (the reference stored the pre-filter vector twice)
-                    w = torch.zeros(len(genes), device=dev)
-                    w[r.columns] = r.model.weights()
-                    st.add(f"svm{k}_weights", w.cpu().numpy())
-                    summary[f"svm{k}"] = {"kernel": kern, "weightfilt": wf, "test_error": r.test_error, "auc": r.auc,
-                                          "precision": r.precision_test, "recall": r.recall_test}
-            importances["svm"] = st.df["svm1_weights"].to_numpy()
-
+        k = 0
+        for kern in cfg.svm.kernels:
+            for wf in cfg.svm.weightfilt:
+                k += 1
+                r = results[f"svm{k}"]
+                st.add(f"svm{k}_weights", r["weights"])
+                summary[f"svm{k}"] = r["summary"]
+                scores.setdefault("svm", r["score"])
+        importances["svm"] = st.df["svm1_weights"].to_numpy()
     if cfg.rf.enabled:
-        with log.stage("random_forest"):
-            for nt in cfg.rf.n_trees:
-                rf = T.RandomForest(n_trees=nt, proximity=cfg.rf.proximity, seed=cfg.rf.seed).fit(xtr, ytr)
-                tag = f"{nt // 1000}k" if nt % 1000 == 0 else str(nt)
-                st.add(f"rfnb_{tag}_MeanDecNodeImp", rf.importance_.cpu().numpy())
-                pred = rf.predict(xte)
-                proba = rf.predict_proba(xte)
-                summary[f"rf_{tag}"] = {"oob_error": rf.oob_error_, "test_error": float((pred != yte.long()).float().mean()),
-                                        "auc": M.auc(proba, yte)}
-                importances["rf"] = rf.importance_.cpu().numpy()
-                scores["rf"] = proba.float().cpu().numpy()
-
+        from .models.trees import RandomForest
+        ytr_t = tr_c.labels()
+        for nt in cfg.rf.n_trees:
+            tag = _rf_tag(nt)
+            parts = [results[t.name] for t in tasks if t.group == f"rf_{tag}"]         # task order = tree order
+            rf = RandomForest(n_trees=nt, proximity=cfg.rf.proximity, seed=cfg.rf.seed)
+            rf._bins, rf._yf = torch.zeros(1), ytr_t.float()                            # merge on the host
+            rf.finish(parts)
+            imp = rf.importance_.numpy()
+            st.add(f"rfnb_{tag}_MeanDecNodeImp", imp)
+            proba = rf.eval_proba_.numpy()
+            summary[f"rf_{tag}"] = {"oob_error": rf.oob_error_, "test_error": float(((proba > 0.5) != (yte_np > 0.5)).mean()),
+                                    "auc": M.auc(torch.from_numpy(proba), torch.from_numpy(yte_np)), "mean_nodes": rf.mean_nodes_}
+            importances["rf"] = imp
+            scores["rf"] = proba
+            if cfg.rf.proximity and cfg.write_outputs and rank == 0:
+                R.write_all(os.path.join(out, "report"), {}, {f"rf_{tag}_proximity": {"proximity": rf.proximity_.numpy()}})
     if cfg.gbm.enabled:
-        with log.stage("gbm"):
-            for i, rep in enumerate(cfg.gbm.reps, 1):
-                gb = T.GradientBoosting(n_estimators=int(rep["nrounds"]), learning_rate=cfg.gbm.eta, max_depth=int(rep["max_depth"]),
-                                        mode="xgboost").fit(xtr, ytr)
-                st.add(f"xg{i}_imp", gb.importance_["gain"].cpu().numpy())
-                pr = gb.predict_proba(xte)
-                summary[f"xgb{i}"] = {"train_error": gb.train_error_[-1], "test_error": float(((pr > 0.5).float() != yte).float().mean()),
-                                      "auc": M.auc(pr, yte), "n_genes": int((gb.importance_["gain"] > 0).sum())}
-                importances["xgb"] = gb.importance_["gain"].cpu().numpy()
-                scores["xgb"] = pr.float().cpu().numpy()
-
+        for i, _ in enumerate(cfg.gbm.reps, 1):
+            r = results[f"xgb{i}"]
+            st.add(f"xg{i}_imp", r["gain"])
+            summary[f"xgb{i}"] = r["summary"]
+            importances["xgb"] = r["gain"]
+            scores["xgb"] = r["score"]
     if cfg.mlp.enabled:
-        with log.stage("mlp"):
-            grid = MLP.make_grid(cfg.mlp.hidden, cfg.mlp.lr, cfg.mlp.weight_decay)
-            res = MLP.train_grid(xtr, ytr, grid, epochs=cfg.mlp.epochs, x_val=xte, y_val=yte)
-            best = int(res.val_auc.argmax())
-            st.add("mlp_importance", res.input_importance(best).cpu().numpy())
-            importances["mlp"] = res.input_importance(best).cpu().numpy()
-            summary["mlp"] = {"best": grid[best], "auc": float(res.val_auc[best]), "val_loss": float(res.val_loss[best])}
+        r = results["mlp"]
+        st.add("mlp_importance", r["importance"])
+        importances["mlp"] = r["importance"]
+        scores["mlp"] = r["score"]
+        summary["mlp"] = r["summary"]
 
-    with log.stage("consensus"):
-        st.write_csv(os.path.join(out, "standouttable.csv"))
-        rank = None
-        if len(importances) >= 2:
-            rank = CS.aggregate(importances, genes, method=cfg.consensus.method)
-            rank.to_csv(os.path.join(out, "consensus_rank.csv"))
-            sets = CS.selection_sets({k: pd.Series(v, index=genes) for k, v in importances.items()}, positive_only=False)
-            CS.membership_table(sets).to_csv(os.path.join(out, "membership_table.csv"))
-            summary["consensus"] = {"top": rank.index[: cfg.consensus.top].tolist(),
-                                    "intersections": {k: len(v) for k, v in CS.intersections(sets).items()}}
-        rd = cohort.row_data
-        if "logFC" in rd and "p.unadj" in rd:
-            R.write_all(os.path.join(out, "report"), {"volcano": R.volcano_data(rd["logFC"].to_numpy(float), rd["p.unadj"].to_numpy(float),
-                                                                                  rd["p.adj.bh"].to_numpy(float), genes)})
+    rank_tab = None
+    if len(importances) >= 2:
+        rank_tab = CS.aggregate(importances, genes, method=cfg.consensus.method)
+        sets = CS.selection_sets({k: pd.Series(v, index=genes) for k, v in importances.items()}, positive_only=False)
+        summary["consensus"] = {"top": rank_tab.index[: cfg.consensus.top].tolist(),
+                                "intersections": {k: len(v) for k, v in CS.intersections(sets).items()}}
+    summary["schedule"] = {"critical": report.critical(), "rank_seconds": report.rank_seconds,
+                           "group_seconds": {g: sum(report.seconds.get(t.name, 0.0) for t in tasks if t.group == g)
+                                             for g in sorted({t.group for t in tasks})}}
+    if cfg.write_outputs and rank == 0:
+        with log.stage("write_outputs"):
+            os.makedirs(out, exist_ok=True)
+            st.write_csv(os.path.join(out, "standouttable.csv"))
+            if cfg.lasso.enabled:
+                CS.write_lasso_gene_csv(results["lasso"]["nonzero"][0], os.path.join(out, "Logistic_Lasso_RiskGroup_Associated_Genes.csv"))
+                R.write_all(os.path.join(out, "report"), {"lasso_rep_curves": results["lasso"]["curves"]})
+            if rank_tab is not None:
+                rank_tab.to_csv(os.path.join(out, "consensus_rank.csv"))
+                CS.membership_table(sets).to_csv(os.path.join(out, "membership_table.csv"))
+            rd = cohort.row_data
+            if "logFC" in rd and "p.unadj" in rd:
+                R.write_all(os.path.join(out, "report"), {"volcano": R.volcano_data(rd["logFC"].to_numpy(float), rd["p.unadj"].to_numpy(float),
+                                                                                      rd["p.adj.bh"].to_numpy(float), genes)})
     log.event("run_end", summary=summary)
     if return_details:
-        return {"summary": summary, "importances": importances, "scores": scores, "rank": rank}
+        return {"summary": summary, "importances": importances, "scores": scores, "rank": rank_tab, "standtable": st.df}
     return summary
 
 

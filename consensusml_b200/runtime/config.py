@@ -50,7 +50,7 @@ class LassoConfig:
     enabled: bool = True
     alpha: float = 1.0
     nfolds: Optional[int] = None           # None = leave-one-out (SEA:100)
-    exclusion_reps: int = 3
+    exclusion_reps: int = 15              # SEA:728-773 ran 15 replicates
     seed: int = 2019
     stability_boot: int = 0
 
@@ -69,6 +69,7 @@ class RFConfig:
     n_trees: List[int] = field(default_factory=lambda: [2000, 5000, 10000])
     proximity: bool = True
     seed: int = 20
+    chunk: int = 1000                      # trees per scheduler task; fixed so that results do not depend on the world size
 
 
 @dataclass
@@ -87,6 +88,8 @@ class MLPConfig:
     lr: List[float] = field(default_factory=lambda: [1e-3, 3e-3])
     weight_decay: List[float] = field(default_factory=lambda: [0.0, 1e-3])
     epochs: int = 200
+    val_frac: float = 0.25                 # inner split of the training samples used to pick the grid point
+    seed: int = 0
 
 
 @dataclass
@@ -97,8 +100,9 @@ class ConsensusConfig:
 
 @dataclass
 class DistConfig:
-    backend: str = "auto"                  # nccl on GPUs, gloo on CPU
-    fused: bool = True
+    enabled: bool = True                   # under torchrun: spread the independent stages over the ranks (parallel/tasks.py)
+    backend: str = "auto"                  # nccl on GPUs, gloo on CPU (parallel.dist.init)
+    fused: bool = True                     # large sample-sharded cohorts: in-kernel collectives (models/lasso_large, gbm_large)
 
 
 @dataclass
@@ -116,6 +120,8 @@ class Config:
     dist: DistConfig = field(default_factory=DistConfig)
     device: str = "auto"
     resume: bool = True
+    checkpoint: bool = True                # write per-task artefacts (and reuse them when `resume`)
+    write_outputs: bool = True             # standouttable / gene CSV / report dumps (benchmarks of the compute switch this off)
 
     def to_dict(self) -> Dict[str, Any]:
         return asdict(self)

@@ -63,7 +63,7 @@ class ArtifactStore:
         """Run ``fn`` unless a matching checkpoint exists; ``fn`` returns a dict of picklable results."""
         if self.is_done(stage, config_hash):
             if log:
-                log.event("stage_skipped", stage=stage, reason="checkpoint matches configuration")
+                log.event("stage_skipped", stage=stage, reason="checkpoint matches configuration and data", key=config_hash)
             return self.load(stage, "result.pt")
         t0 = time.perf_counter()
         out = fn()

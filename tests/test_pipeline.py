@@ -58,7 +58,38 @@ def test_pipeline_small_cpu(tmp_path):
     # second run resumes the lasso stage from its checkpoint
     pipeline.run(cfg)
     recs = [json.loads(l) for l in open(tmp_path / "run.jsonl")]
-    assert any(r["event"] == "stage_skipped" and r["stage"] == "models/lasso" for r in recs)
+    assert any(r["event"] == "stage_skipped" and r["stage"] == "tasks/lasso" for r in recs)
+    # ... but not for a different cohort of the same shape (the key used to hold only the shape)
+    from consensusml_b200 import datasets
+    co = datasets.load_target_aml()
+    co.assay = co.assay.clone()
+    co.assay[0, 0] += 1.0
+    n_before = sum(r["event"] == "stage_skipped" for r in recs)
+    pipeline.run(cfg, co)
+    recs = [json.loads(l) for l in open(tmp_path / "run.jsonl")]
+    assert sum(r["event"] == "stage_skipped" for r in recs) == n_before
+
+
+def test_task_assignment_is_deterministic_and_balanced():
+    from consensusml_b200.parallel.tasks import Task, assign
+    tasks = [Task("lasso", 15.0, lambda: 0)] + [Task(f"rf{i}", 1.2, lambda: 0) for i in range(17)] + [Task(f"svm{i}", 1.0, lambda: 0) for i in range(4)]
+    for world in (1, 2, 4, 8):
+        a = assign(tasks, world)
+        assert a == assign(tasks, world) and set(a.values()) <= set(range(world))
+        load = [sum(t.cost for t in tasks if a[t.name] == r) for r in range(world)]
+        assert max(load) <= max(15.0, sum(t.cost for t in tasks) / world + 1.2)       # LPT bound: optimum + one small task
+
+
+def test_pipeline_two_ranks_gloo_matches_single_process(tmp_path):
+    """The ensemble spread over two processes (gloo) gives the same standouttable as one process."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = os.path.join(root, "tests", "dist_pipeline_check.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29547", script, str(tmp_path)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env={**os.environ, "CML_DIST_TIMEOUT_S": "120"})
+    assert r.returncode == 0 and "PIPELINE DIST OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
 
 
 def test_counts_to_cohort_cpu():
