@@ -1,17 +1,26 @@
 #!/usr/bin/env python
-"""Flagship benchmark: stability-selection logistic lasso (glmnet-semantics 100-lambda paths).
+"""Flagship benchmark: wall-clock of the TARGET-AML risk-group consensus pipeline through the public API.
 
-One step = one ``stability_selection`` call of the public API on a fresh cohort of the reference's
-modelling shape (93 training samples x 1984 DEG genes, the matrix behind the reference's headline
-lasso result; cml_targetaml_seanalysis.Rmd:94-101): REPS bootstrap replicates per GPU, each a full
-pathwise coordinate-descent fit over the reference's grid ``10^seq(10,-2,length=100)``, followed by
-the per-gene selection frequencies (all-reduced over ranks when N > 1).  The metric is complete
-path fits per second, summed over all GPUs (BASELINE.json: "fits/sec 1/2/4/8 GPU"); weak scaling -
-every GPU always fits REPS replicates per step.
+BASELINE.json: "consensus-pipeline wall-clock + held-out AUC/gene-overlap vs ref CPU; fits/sec 1/2/4/8 GPU".
 
-Contract: ``python bench.py --gpus N --steps K --warmup W`` prints ONE JSON line on rank 0.
-``--impl reference`` reports that the reference cannot be run (it has no build system and its
-modelling script imports xgboost, which is not installed).
+One step = one ``consensusml_b200.pipeline.run`` on the bundled real cohort (1984 DEG genes x 137 samples, the
+reference's own modelling matrix and 93/44 split) with the reference's configuration
+(cml_targetaml_seanalysis.Rmd:638-1298): 15 lasso exclusion replicates each with leave-one-out CV over the 100-lambda grid,
+SVM x4, random forest 2k / 5k / 10k trees with proximity, xgboost-mode boosting x5, consensus rank aggregation.
+On N GPUs the independent stages are spread over the ranks (parallel/tasks.py) - strong scaling, the total work is fixed.
+Inputs are the real data (no synthetic stand-in); the result is checked inside the same run: held-out AUC, the
+confusion matrix and the 13 lasso genes against the reference's stored R output, and the top-50 consensus genes against
+the CPU arm of this framework (datasets/target_aml/cpu_arm_summary.json, tools/make_cpu_arm_fixture.py).
+
+Secondary numbers in the same line: complete lasso path fits per second (stability selection, replicate-parallel over
+ranks), the reference's ``model_comp`` ensemble (scripts/model_comp.py:6-34) through ``api.model_comp`` for a like-for-like
+comparison with the reference arm, and - for N > 1 - the fused compute+collective paths on the synthetic sample-sharded
+cohort with their roofline fractions.
+
+Contract: ``python bench.py --gpus N --steps K --warmup W`` prints ONE JSON line on rank 0 (launched through
+``torch.distributed.run`` for N > 1).  ``--impl reference`` runs the reference's own ``model_comp.model_comp`` from the
+unmodified copy in baseline/_ref on the same cohort (the only stage of the reference that can execute without R; see
+DESIGN.md "Reference arm").
 """
 import argparse
 import json
@@ -23,57 +32,140 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-N_TRAIN, P_GENES, N_LAMBDA = 93, 1984, 100
-# 8880 = 3 x (148 SMs x 20 resident path-fit warps): three full waves of the path kernel on a B200 (8192, used for the
-# numbers in profiles/ up to this change, left the third wave 77 % full)
-REPS_PER_GPU = int(os.environ.get("CML_BENCH_REPS", 8880))
-METRIC = "lasso_path_fits_per_sec"
+METRIC = "consensus_pipeline_wall_s"
+REF_AUC = 0.9835                      # lasso rep 1 held-out AUC derived from the reference's stored glmnet object
+REF_CONFUSION = [[21, 2], [1, 20]]    # JSmith_code/Results/RiskGroup_Confusion_Matrix.csv
+CPU_ARM_WALL_S = 45.4
 
 
-def reference_arm():
+# ------------------------------------------------------------------------------------------------ reference arm
+def _ref_dir():
+    return os.path.join(ROOT, "baseline", "_ref")
+
+
+def install_reference():
+    """``pip install /root/reference`` cannot work (the reference has no setup.py / pyproject: it is notebooks plus three
+    loose modules that its own notebook imports from the working directory, model_walkthrough.ipynb raw line 146), so the
+    install is a verbatim copy of its ``scripts/`` directory.  Returns the path or None."""
+    dst = os.path.join(_ref_dir(), "scripts")
+    if os.path.isfile(os.path.join(dst, "model_comp.py")):
+        return dst
+    src = os.environ.get("CML_REFERENCE_DIR", "/root/reference")
+    if not os.path.isfile(os.path.join(src, "scripts", "model_comp.py")):
+        return None
+    import shutil
+    os.makedirs(dst, exist_ok=True)
+    for f in ("model_comp.py", "clean.py", "dummies.py", "README.md"):
+        shutil.copyfile(os.path.join(src, "scripts", f), os.path.join(dst, f))
+    return dst
+
+
+def reference_arm(args):
+    """The reference's Python ensemble stage, unmodified, on the same cohort and split, on the CPU (it has no GPU path).
+    Its ``from xgboost import XGBClassifier`` cannot be satisfied (no xgboost wheel offline); baseline/standins/xgboost
+    maps that one class onto scikit-learn's GradientBoostingClassifier and the substitution is declared in the line."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return 0                       # the reference is a single-process CPU program: the other ranks have nothing to run
+    path = install_reference()
+    if path is None:
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is absent and /root/reference is not mounted"}))
+        return 0
+    import contextlib
+    import io
+    import numpy as np
+    import pandas as pd
+    sys.path.insert(0, os.path.join(ROOT, "baseline", "standins"))
+    sys.path.insert(0, path)
+    try:
+        import model_comp as ref_mc                                   # the reference module itself
+    except Exception as exc:                                           # pragma: no cover
+        print(json.dumps({"impl": "reference", "unavailable": f"import of the reference's model_comp failed: {exc!r}"}))
+        return 0
+    from consensusml_b200 import datasets
+    co = datasets.load_target_aml()
+    tr, te = co.split()
+    import torch
+    Xtr = pd.DataFrame(tr.design(torch.float64).numpy(), columns=co.gene_ids)
+    Xte = pd.DataFrame(te.design(torch.float64).numpy(), columns=co.gene_ids)
+    ytr, yte = tr.labels().numpy().astype(int), te.labels().numpy().astype(int)
+    import xgboost as standin
+    # a CPU program needs one warm-up at most; every step also spends ~28 s inside the (excluded) stand-in, so cap the count
+    steps, warm = min(args.steps, 3), min(args.warmup, 1)
+    times, inside, ll = [], [], None
+    for i in range(warm + steps):
+        buf = io.StringIO()
+        standin.seconds_inside = 0.0
+        t0 = time.perf_counter()
+        with contextlib.redirect_stdout(buf), contextlib.redirect_stderr(io.StringIO()):
+            xgb_m, rf_m = ref_mc.model_comp(Xtr, Xte, ytr, yte)
+        dt = time.perf_counter() - t0
+        if i >= warm:
+            times.append(dt - standin.seconds_inside)                  # the stand-in's own time is not charged to the reference
+            inside.append(standin.seconds_inside)
+        ll = {ln.rsplit(" ", 1)[0]: float(ln.rsplit(" ", 1)[1]) for ln in buf.getvalue().splitlines() if "Log Loss" in ln}
+    from sklearn.metrics import roc_auc_score
+    auc_rf = float(roc_auc_score(yte, rf_m.predict_proba(Xte)[:, 1]))
+    val = float(np.mean(times))
     print(json.dumps({
-        "impl": "reference",
-        "unavailable": "reference is R notebooks + scripts/model_comp.py: no setup.py/pyproject (pip install fails), "
-                       "R/glmnet/xgboost are not installed and model_comp.py imports xgboost at module top",
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "s", "n_gpus": world, "steps": steps, "warmup": warm,
+        "ms_per_step": val * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "fp64",
+        "data": "real: bundled TARGET-AML DEG cohort (1984 genes x 137 samples, reference split 93/44)",
+        "config": {"model": "reference scripts/model_comp.py::model_comp (XGBClassifier 700 + GradientBoosting 280 + RandomForest 300, "
+                            "probability-averaged ensemble, log-loss)", "global_batch": 93, "seq_len": 1984, "parallelism": "single process CPU",
+                   "coverage": "Python ensemble stage only - the R stages of the consensus pipeline (glmnet LOOCV x15, e1071 SVM x4, "
+                               "randomForest 17k trees, xgboost x5) need R, which is not installed; ours runs all of them",
+                   "substitutions": {"xgboost.XGBClassifier": "sklearn.ensemble.GradientBoostingClassifier with the same learning_rate / "
+                                                             "max_depth / n_estimators / random_state (no xgboost wheel offline); its own fit / "
+                                                             "predict time is measured and EXCLUDED from value",
+                                     "standin_seconds_excluded_per_step": float(np.mean(inside))},
+                   "install": "verbatim copy of /root/reference/scripts (pip install fails: no setup.py / pyproject.toml)"},
+        "log_loss": ll, "rf_auc": auc_rf, "gpu_launches": 0,
+        "e2e": {"value": val, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
     return 0
 
 
-def synth_cohort(seed, n=N_TRAIN, p=P_GENES):
-    """A cohort shaped like the reference's training matrix: log2-CPM-like genes with a planted
-    100-gene weak class signal (55 / 38 class balance as in the reference's training split)."""
-    import numpy as np
-    rng = np.random.default_rng(seed)
-    y = np.zeros(n, np.float32)
-    y[: int(round(n * 55 / 93))] = 1
-    rng.shuffle(y)
-    mu = rng.normal(2.0, 2.5, p)
-    sd = rng.uniform(0.6, 2.2, p)
-    x = (mu + sd * rng.standard_normal((n, p))).astype(np.float32)
-    sig = rng.choice(p, 100, replace=False)      # weak, diffuse signal: ~1000 CD passes and df ~ 60 at the
-    x[:, sig] += (y[:, None] - 0.5) * rng.uniform(0.2, 0.7, 100).astype(np.float32) * sd[sig].astype(np.float32)  # grid end, like the real cohort
-    return x, y
+# ------------------------------------------------------------------------------------------------ our arm
+def _accuracy(summary, cpu_arm, genes13):
+    from consensusml_b200.consensus.rank_aggregate import top_k_overlap
+    lasso = summary["lasso"]
+    top = summary["consensus"]["top"]
+    out = {"lasso_auc": lasso["auc"], "lasso_auc_ref": REF_AUC, "lasso_auc_abs_err": abs(lasso["auc"] - REF_AUC),
+           "lasso_confusion": lasso["confusion"], "lasso_confusion_matches_reference": lasso["confusion"] == REF_CONFUSION,
+           "lasso_lambda_min": lasso["lambda_min"],
+           "lasso_genes_matching_reference_13": len(set(g.split(".")[0] for g in lasso["genes_rep1"]) & genes13),
+           "lasso_genes_selected": len(lasso["genes_rep1"]), "lasso_genes_per_rep": lasso["n_genes"],
+           "auc": {k: v["auc"] for k, v in summary.items() if isinstance(v, dict) and "auc" in v}}
+    if cpu_arm:
+        out["top50_overlap_vs_cpu_arm"] = top_k_overlap(top, cpu_arm["consensus_ranking"], 50)
+        out["lasso_genes_equal_cpu_arm"] = sorted(lasso["genes_rep1"]) == sorted(cpu_arm["lasso_genes_rep1"])
+    return out
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--reps", type=int, default=REPS_PER_GPU)
-    ap.add_argument("--cpu-baseline-fits", type=int, default=16)
+    ap.add_argument("--fits", type=int, default=8880, help="bootstrap path fits per GPU for the secondary fits/s number (0 = skip)")
+    ap.add_argument("--no-fused", action="store_true", help="skip the fused-path block (N > 1)")
+    ap.add_argument("overrides", nargs="*", help="section.key=value overrides of the pipeline configuration")
     args = ap.parse_args()
     if args.impl == "reference":
-        return reference_arm()
-    args.warmup = max(args.warmup, 3)
+        return reference_arm(args)
+    if args.warmup < 3:
+        sys.stderr.write(f"bench.py: --warmup {args.warmup} is below the 3 warm-up steps the timing rules ask for\n")
 
     import numpy as np
+    import pandas as pd
     import torch
     import torch.distributed as dist
-    from consensusml_b200 import _native
-    from consensusml_b200.models import lasso
-    from consensusml_b200.ops import lasso as K
+    from consensusml_b200 import _native, datasets, pipeline
+    from consensusml_b200.data import Cohort
+    from consensusml_b200.runtime import config as C
     from consensusml_b200.runtime.clocks import ClockSampler
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -85,110 +177,196 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    _native.cuda()
-    lam = K.default_lambda_grid()
-    reps = args.reps
-    total = args.warmup + args.steps
-
-    # a distinct cohort per step, staged in pinned host memory (the e2e arm copies it every step)
-    pool = []
-    for s in range(total):
-        x, y = synth_cohort(s)          # every rank bootstraps the SAME cohort (its replicates differ by seed): that is how
-                                        # a stability-selection job is spread over GPUs, and it keeps the ranks' work balanced
-        pool.append((torch.from_numpy(x).pin_memory(), torch.from_numpy(y).pin_memory()))
-    flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
     lib = _native.cuda()
+    out_dir = os.path.join(os.environ.get("TMPDIR", "/tmp"), f"cml_bench_{os.getpid()}")
+    base = ["device=cuda:%d" % local_rank, "resume=false", "checkpoint=false", "io.out_dir=" + out_dir] + list(args.overrides)
+    cfg_dev = C.load(None, base + ["write_outputs=false"])
+    cfg_e2e = C.load(None, base + ["write_outputs=true"])
+
+    host = datasets.load_target_aml()                       # float64 assay, host memory
+    pinned = host.assay.float().pin_memory()                # what the end-to-end arm uploads every step
+    flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     def flush():
         lib.cml_l2_flush(_native.ptr(flush_buf), flush_buf.numel(), _native.stream_ptr())
-
-    def step_device(xg, yg, s):
-        out = lasso.stability_selection(xg, yg, lam, n_boot=reps, seed=17 + s + 100003 * rank, batch=reps)
-        freq = out["freq"]
-        if world > 1:
-            dist.all_reduce(freq)
-            freq /= world
-        return freq.amax(dim=(0, 1))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------- arm A: device-timed (inputs already resident) ----------------
-    dev_pool = [(x.to(dev), y.to(dev)) for x, y in pool]
-    for s in range(args.warmup):
-        step_device(*dev_pool[s], s)
+    def cohort_on_device(assay_dev):
+        return Cohort(assay_dev, host.gene_ids, host.sample_ids, host.row_data, host.col_data, dict(host.metadata), host.assay_name)
+
+    launches = {"n": 0}
+
+    # ---------------- arm A: device-timed, cohort already resident ----------------
+    resident = cohort_on_device(pinned.to(dev))
+    for _ in range(args.warmup):
+        pipeline.run(cfg_dev, resident)
     barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    summary = None
+    _native.reset_calls()
     with ClockSampler(local_rank) as clk:
         barrier()
         for i in range(args.steps):
             flush()
+            barrier()
             ev[i][0].record()
-            res = step_device(*dev_pool[args.warmup + i], args.warmup + i)
+            summary = pipeline.run(cfg_dev, resident)
             ev[i][1].record()
-        barrier()
-    ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            barrier()
+    calls = dict(_native.calls)
+    ncalls = torch.tensor([sum(calls.values())], dtype=torch.int64, device=dev)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    ms_per_step = ms_total / args.steps
-    value = world * reps * args.steps / (ms_total / 1e3)
-    sel_genes = int((res > 0.6).sum().item())
+        dist.all_reduce(ncalls)                             # launches of all ranks
+    ms = [a.elapsed_time(b) for a, b in ev]
+    t = torch.tensor(ms, dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)            # per step: the slowest rank
+    ms_per_step = float(t.mean().item())
+    value = ms_per_step / 1e3
 
-    # ---------------- arm B: end to end through the public API ----------------
+    # ---------------- arm B: end to end (pinned host -> device every step, outputs written, result read back) ----------------
+    e2e = []
     h2d = d2h = 0
     barrier()
-    e2e_s = 0.0
     for i in range(args.steps):
         flush()
-        torch.cuda.synchronize()
-        xp, yp = pool[args.warmup + i]
+        barrier()
         t0 = time.perf_counter()
-        xg = xp.to(dev, non_blocking=True)
-        yg = yp.to(dev, non_blocking=True)
-        host_res = step_device(xg, yg, args.warmup + i).cpu()      # device -> host read of the step's result
-        e2e_s += time.perf_counter() - t0
-        h2d = xp.numel() * xp.element_size() + yp.numel() * yp.element_size()
-        d2h = host_res.numel() * host_res.element_size()
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        assay_dev = pinned.to(dev, non_blocking=True)                       # H2D of the step's input
+        det = pipeline.run(cfg_e2e, cohort_on_device(assay_dev), return_details=True)   # results come back as host arrays (D2H)
+        barrier()
+        e2e.append(time.perf_counter() - t0)
+        h2d = pinned.numel() * pinned.element_size()
+        d2h = int(sum(np.asarray(v).nbytes for v in det["importances"].values()) + sum(np.asarray(v).nbytes for v in det["scores"].values()))
+    te = torch.tensor(e2e, dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * reps * args.steps / float(t.item())
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = float(te.mean().item())
 
-    # ---------------- context: the float64 C++ restatement of glmnet on one CPU core ----------------
-    cpu_fits_per_s = None
-    if rank == 0 and args.cpu_baseline_fits > 0:
-        x, y = pool[0]
-        nb = args.cpu_baseline_fits
-        from consensusml_b200.ops.replicate import replicate_weights
-        w = replicate_weights(nb, N_TRAIN, seed=1).double()
-        t0 = time.perf_counter()
-        K.lognet_path(x.double(), y.double(), w, lam, want_eta=False)
-        cpu_fits_per_s = nb / (time.perf_counter() - t0)
+    # ---------------- secondary: lasso path fits per second (replicate-parallel stability selection) ----------------
+    fits = None
+    if args.fits > 0:
+        from consensusml_b200.models import lasso
+        from consensusml_b200.ops import lasso as K
+        tr, _ = resident.split()
+        xg, yg = tr.design(torch.float32), tr.labels()
+        lam = K.default_lambda_grid()
+
+        def sel_step(s):
+            out = lasso.stability_selection(xg, yg, lam, n_boot=args.fits, seed=17 + s + 100003 * rank, batch=args.fits)
+            f = out["freq"]
+            if world > 1:
+                dist.all_reduce(f)
+            return f
+        for s in range(2):
+            sel_step(s)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for s in range(3):
+            sel_step(2 + s)
+        b.record()
+        barrier()
+        tf = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+        fits = {"lasso_path_fits_per_s": world * args.fits * 3 / (float(tf.item()) / 1e3), "fits_per_gpu_per_step": args.fits,
+                "shape": "93 x 1984 x 100 lambda (real training matrix), fp32 kernel vs float64 glmnet: coefficients agree to 2e-3",
+                "scaling": "weak"}
+
+    # ---------------- secondary: the reference's model_comp() through our API (like for like with --impl reference) ----------------
+    mc = None
+    try:
+        from consensusml_b200.api import model_comp as MC
+        tr, te_ = host.split()
+        Xtr = pd.DataFrame(tr.design(torch.float64).numpy(), columns=host.gene_ids)
+        Xte = pd.DataFrame(te_.design(torch.float64).numpy(), columns=host.gene_ids)
+        ytr, yte = tr.labels().numpy().astype(int), te_.labels().numpy().astype(int)
+        import contextlib
+        import io
+        tm = []
+        for i in range(3):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            with contextlib.redirect_stdout(io.StringIO()):
+                MC.model_comp(Xtr, Xte, ytr, yte)
+            torch.cuda.synchronize()
+            tm.append(time.perf_counter() - t0)
+        mc = {"model_comp_wall_s": float(np.mean(tm[1:])), "note": "api.model_comp: same three models, hyper-parameters and printed "
+              "log-losses as scripts/model_comp.py:6-34, host DataFrames in, fitted on this rank's GPU"}
+    except Exception as exc:
+        mc = {"error": repr(exc)}
+
+    # ---------------- secondary (N > 1): fused compute + collective paths ----------------
+    fused = None
+    if world > 1 and not args.no_fused:
+        fused = _fused_block(rank, world, dev)
 
     if rank == 0:
+        cpu_arm = None
+        try:
+            cpu_arm = json.load(open(datasets.path("cpu_arm_summary.json")))
+        except OSError:
+            pass
+        genes13 = set(pd.read_csv(datasets.path("lasso13_gene_symbols_biomart.csv")).iloc[:, 0].astype(str))
+        acc = _accuracy(summary, cpu_arm, genes13)
+        sched = summary["schedule"]
         print(json.dumps({
-            "metric": METRIC, "value": value, "unit": "path_fits/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"model": "logistic lasso, glmnet-semantics pathwise CD, stability selection",
-                       "n_samples": N_TRAIN, "n_genes": P_GENES, "n_lambda": N_LAMBDA,
-                       "lambda_grid": "10^seq(10,-2,length=100)", "replicates_per_gpu_per_step": reps,
-                       "global_batch": reps * world, "parallelism": f"replicate-parallel x{world} + freq all-reduce",
-                       "l2": "flushed (256 MiB write) before every timed step; inputs < L2",
-                       "selected_genes_last_step": sel_genes},
+            "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": value / CPU_ARM_WALL_S,
+            "vs_baseline_note": "value / 45.4 s = wall-clock of the same pipeline stages on one CPU core with compiled CPU libraries "
+            "(BASELINE.md section 4 row 1, bench/pipeline_bench.py cpu_arm; the reference publishes no pipeline timing of its own); lower is better",
+            "dtype": "fp32 solvers (lasso, trees, SMO) + bf16 tensor-core Gram with fp32 accumulate; reference is float64 - "
+                     "accuracy gates in this line", "data": "real: bundled TARGET-AML DEG cohort (1984 genes x 137 samples, reference split 93/44)",
+            "config": {"model": "TARGET-AML risk-group consensus pipeline: lasso x15 exclusion reps (LOOCV, 100 lambda) + SVM x4 + "
+                                "RF 2k/5k/10k (proximity) + xgboost-mode GBM x5 + rank aggregation",
+                       "global_batch": 93, "seq_len": 1984, "parallelism": f"stage/task-parallel x{world} (parallel/tasks.py), one all_gather_object",
+                       "l2": "flushed (256 MiB write) before every timed step; inputs < L2", "overrides": list(args.overrides)},
             "clocks": clk.summary(),
-            "e2e": {"value": e2e_value, "unit": "path_fits/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": 2 * args.steps,
-            "gpu_launches_note": "per step: cml_replicate_weights + cml_lognet_path (ours); torch zeros/transpose/amax excluded",
-            "cpu_oracle_fits_per_s_1core": cpu_fits_per_s,
-        }))
+            "e2e": {"value": e2e_value, "unit": "s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "includes": "pinned-host -> device copy of the assay, all stages, D2H of importances / scores, CSV + report files written"},
+            "gpu_launches": int(ncalls.item()),
+            "gpu_launches_note": "calls of libcml_b200.so entry points inside the timed region, all ranks (each launches at least one "
+                                 "kernel of ours); counted in consensusml_b200._native.check; torch's own kernels excluded",
+            "gpu_launches_rank0_by_entry": calls,
+            "accuracy": acc, "schedule": sched, "step_ms": ms,
+            "secondary": {"fits": fits, "model_comp": mc, "fused_paths": fused},
+        }, default=float))
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def _fused_block(rank, world, dev):
+    """The three fused compute+collective kernels on a synthetic sample-sharded cohort (per-GPU shard of the 1M x 20k
+    north-star shape, weak scaling), device-timed, max over ranks, each with its roofline fraction.  Guarded by a
+    deadline: a failure here is reported in the line, it does not lose the headline numbers."""
+    import signal
+    import torch
+
+    class _Deadline(Exception):
+        pass
+
+    def _alarm(*_):
+        raise _Deadline()
+    old = signal.signal(signal.SIGALRM, _alarm)
+    signal.alarm(int(os.environ.get("CML_BENCH_FUSED_DEADLINE_S", "240")))
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "bench"))
+        import fused_paths as FP
+        return FP.measure(rank, world, dev, rows_per_gpu=int(os.environ.get("CML_BENCH_ROWS", "125000")), genes=20000, reps=4)
+    except _Deadline:
+        return {"error": "fused-path block exceeded its deadline"}
+    except Exception as exc:                      # noqa: BLE001 - report, keep the headline
+        return {"error": repr(exc)}
+    finally:
+        signal.alarm(0)
+        signal.signal(signal.SIGALRM, old)
 
 
 if __name__ == "__main__":

@@ -152,7 +152,17 @@ def register_signature(name: str, args, res=ctypes.c_int) -> None:
             _declare(lib)
 
 
+# Every op wrapper reports the return code of its entry point through check(); counting there gives the number of
+# kernel-launching calls of OUR library per entry point (bench.py reports it as gpu_launches).
+calls: dict = {}
+
+
+def reset_calls() -> None:
+    calls.clear()
+
+
 def check(code: int, what: str) -> None:
+    calls[what] = calls.get(what, 0) + 1
     if code != 0:
         msg = cuda().cml_last_error().decode(errors="replace")
         raise NativeError(f"{what} failed with code {code}: {msg}")
