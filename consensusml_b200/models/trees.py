@@ -30,8 +30,10 @@ _native.register_signature("cml_forest_level", [_P, _I, _I, _I, _I, _P, _P, _P, 
                                                 _P, _P])
 _native.register_signature("cml_forest_predict", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P])
 _native.register_signature("cml_forest_proximity", [_P, _P, _I, _I, _P, _P, _P])
+_native.register_signature("cml_quantile_edges", [_P, _I, _I, ctypes.c_longlong, _I, _P, _P, _P])
 
 GINI, NEWTON = 0, 1
+QUANTILE_SAMPLE = 16384       # values per gene that enter the quantile sort (csrc/select.cu kQMaxSample)
 
 
 # ------------------------------------------------------------------------------------------------ binning
@@ -57,14 +59,26 @@ class Binner:
                                               _native.ptr(n_edges), _native.stream_ptr())
             _native.check(rc, "cml_rank_bins")
             return Binner(edges, n_edges, int(n_edges.max().item())), bins
+        if n > 256 and _native.on_device(x):
+            # quantile representatives from a shared-memory sort per gene (csrc/select.cu), then the midpoint binning kernel
+            edges = torch.empty(p, 256, dtype=torch.float32, device=x.device)
+            n_edges = torch.empty(p, dtype=torch.int32, device=x.device)
+            rc = _native.cuda().cml_quantile_edges(_native.ptr(xt), p, n, n, int(max_bin), _native.ptr(edges), _native.ptr(n_edges),
+                                                   _native.stream_ptr())
+            _native.check(rc, "cml_quantile_edges")
+            b = Binner(edges, n_edges, max(2, int(n_edges.max().item())))
+            return b, b.transform(x)
         xs = xt.double()
         if n <= 256:
             reps = [torch.unique(xs[f]) for f in range(p)]
         else:
+            # same rule as the kernel: all values up to 16,384 samples, beyond that an evenly strided sample of 16,384;
+            # type-7 quantiles in float64, rounded to fp32, duplicates dropped
+            S = min(n, QUANTILE_SAMPLE)
+            sub = xs if S == n else xs[:, (torch.arange(S, dtype=torch.int64, device=x.device) * n) // S]
             qs = torch.linspace(0, 1, max_bin, dtype=torch.float64, device=x.device)
-            sub = xs if n <= 100000 else xs[:, torch.randperm(n, device=x.device)[:100000]]
-            qv = torch.quantile(sub, qs, dim=1).t()
-            reps = [torch.unique(qv[f]) for f in range(p)]
+            qv = torch.quantile(sub, qs, dim=1).t().float()
+            reps = [torch.unique_consecutive(qv[f]) for f in range(p)]
         edges = torch.full((p, 256), float("inf"), dtype=torch.float32, device=x.device)
         n_edges = torch.zeros(p, dtype=torch.int32, device=x.device)
         for f, r in enumerate(reps):

@@ -67,16 +67,33 @@ def correlation(x: torch.Tensor, y: Optional[torch.Tensor] = None, method: str =
     return G.gemm_tn(zb, [yb], yb.shape[0]).clamp_(-1.0, 1.0)
 
 
+HCLUST_METHODS = {"single": 0, "complete": 1, "average": 2, "weighted": 3, "ward": 4}
+
+
+def hclust(dist: torch.Tensor, method: str = "complete"):
+    """Agglomerative clustering of a precomputed distance matrix with the framework's own nearest-neighbour-chain
+    implementation (csrc/host/hclust.cpp).  Returns (Z, leaves): the linkage matrix in scipy's convention ((n-1) x 4:
+    ids, height, size; sorted by height) and the left-to-right leaf order.  scipy is only the test oracle."""
+    lib = _native.host()
+    d = dist.detach().double().cpu()
+    d = (0.5 * (d + d.t())).clamp_min(0)
+    d.fill_diagonal_(0.0)
+    dn = np.ascontiguousarray(d.numpy())
+    n = dn.shape[0]
+    Z = np.zeros((max(n - 1, 0), 4))
+    leaves = np.zeros(n, np.int32)
+    lib.cml_host_hclust.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    rc = lib.cml_host_hclust(_native.np_ptr(dn), n, HCLUST_METHODS[method], _native.np_ptr(Z), _native.np_ptr(leaves))
+    if rc != 0:
+        raise ValueError(f"hclust: bad arguments (n={n}, method={method})")
+    return Z, leaves
+
+
 def hclust_order(dist: torch.Tensor, method: str = "complete") -> np.ndarray:
     """Leaf order of an agglomerative clustering of a distance matrix (ComplexHeatmap's default: complete linkage on
-    Euclidean distances).  Nearest-neighbour-chain over the precomputed matrix; the distance matrix itself comes from
-    the tcgen05 squared-distance GEMM (``ops.gemm.sq_dists``)."""
-    from scipy.cluster.hierarchy import leaves_list, linkage
-    from scipy.spatial.distance import squareform
-    d = dist.detach().double().cpu().numpy()
-    d = 0.5 * (d + d.T)
-    np.fill_diagonal(d, 0.0)
-    return leaves_list(linkage(squareform(np.maximum(d, 0), checks=False), method=method))
+    Euclidean distances, cml_targetaml_seanalysis.Rmd:536-613).  The distance matrix comes from the tcgen05
+    squared-distance GEMM (``ops.gemm.sq_dists``); the merges from ``hclust`` above."""
+    return hclust(dist, method)[1].astype(np.int64)
 
 
 def heatmap_order(x: torch.Tensor):

@@ -281,3 +281,60 @@ def test_replicate_weight_kernel_properties():
     assert ((sub == 0) | (sub == 1)).all() and (sub.sum(1) == 20).all()
     for r in range(2):                                         # every sample is left out by exactly one fold of a repeat
         assert ((kf[5 * r: 5 * r + 5] == 0).sum(0) == 1).all()
+
+
+def test_column_moments_topk_and_quantile_binning_kernels():
+    from consensusml_b200.models import trees as TR
+    from consensusml_b200.ops import colvar as CV
+    g = torch.Generator().manual_seed(12)
+    x = torch.randn(300, 70, generator=g) * torch.linspace(0.2, 3.0, 70)[None, :] + 5.0
+    x[:, 9] = x[:, 4]                                     # equal variances: tie broken by index
+    x[:, 20] = 1.25                                       # constant column
+    mask = torch.rand(300, generator=g) < 0.6
+    with _native.emulation(seed=3):
+        cnt, mean, m2 = CV.column_moments(x, mask)
+        idx_hi = CV.variance_topk(x, 11, largest=True, row_mask=mask)
+        idx_lo = CV.variance_topk(x, 7, largest=False)
+        tk = CV.topk(torch.tensor([3.0, 1.0, 3.0, 2.0, 3.0, -1.0]), 2)
+    xs = x[mask].double()
+    assert cnt == int(mask.sum())
+    assert torch.allclose(mean, xs.mean(0), rtol=1e-12, atol=1e-12)
+    assert torch.allclose(m2, ((xs - xs.mean(0)) ** 2).sum(0), rtol=1e-10, atol=1e-10)
+    var = xs.var(0, unbiased=True)
+    assert idx_hi.tolist() == torch.argsort(var.float(), descending=True, stable=True)[:11].tolist()
+    assert idx_lo.tolist() == torch.argsort(x.double().var(0, unbiased=True).float(), descending=False, stable=True)[:7].tolist()
+    assert tk.tolist() == [0, 2]
+    # quantile binning (n > 256): the kernel path and the host restatement produce the same edges and bins
+    xq = torch.randn(700, 9, generator=g)
+    xq[:, 2] = torch.round(xq[:, 2] * 2) / 2              # heavy ties -> fewer than max_bin distinct quantiles
+    bc, binsc = TR.Binner.fit(xq, max_bin=64)
+    with _native.emulation(seed=1):
+        bd, binsd = TR.Binner.fit(xq, max_bin=64)
+    assert torch.equal(bd.n_edges, bc.n_edges)
+    for f in range(9):
+        k = int(bc.n_edges[f])
+        assert torch.equal(bd.edges[f, :k], bc.edges[f, :k]), f
+    assert torch.equal(binsd[:, :700], binsc[:, :700])
+
+
+def test_kmeans_sweep_kernel_reaches_the_same_minima_as_the_host_path():
+    from consensusml_b200.models import kmeans as KM
+    g = torch.Generator().manual_seed(4)
+    centres = torch.tensor([[0.0, 0.0, 0.0], [4.0, 0.0, 1.0], [0.0, 5.0, -1.0], [5.0, 5.0, 3.0]])
+    x = torch.cat([c + 0.4 * torch.randn(30, 3, generator=g) for c in centres])
+    with _native.emulation(seed=2):
+        dev = KM.kmeans_sweep(x, ks=(4, 3, 2), nstart=10, seed=1000)
+        again = KM.kmeans_sweep(x, ks=(4, 3, 2), nstart=10, seed=1000)
+    for k in (4, 3, 2):
+        host = KM.kmeans(x, k, nstart=8, seed=1000)
+        r = dev[k]
+        assert r.centers.shape == (k, 3) and r.labels.shape == (120,)
+        # k = 4 is the planted structure (one minimum); for k < 4 several local minima lie within a few per cent
+        assert abs(r.tot_withinss - host.tot_withinss) <= (1e-3 if k == 4 else 0.03) * host.tot_withinss, (k, r.tot_withinss, host.tot_withinss)
+        # internal consistency: centres are the means of their members, withinss adds up, labels are nearest centres
+        for j in range(k):
+            assert torch.allclose(r.centers[j], x[r.labels == j].mean(0), atol=1e-5)
+        assert abs(float(r.withinss.sum()) - r.tot_withinss) < 1e-3
+        assert torch.equal(torch.cdist(x, r.centers).argmin(1), r.labels)
+        assert torch.equal(r.labels, again[k].labels) and r.tot_withinss == again[k].tot_withinss      # reproducible
+    assert sorted(torch.bincount(dev[4].labels).tolist()) == [30, 30, 30, 30]

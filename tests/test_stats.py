@@ -53,3 +53,20 @@ def test_gpu_spearman_and_kde(aml):
     g1, d1 = C.kde(v)
     g2, d2 = C.kde(v.cpu())
     assert (d1.cpu() - d2).abs().max() < 1e-4
+
+
+@pytest.mark.parametrize("method", ["complete", "average", "single", "weighted", "ward"])
+def test_own_hclust_matches_scipy_linkage(method):
+    """stats.correlation.hclust is the framework's nearest-neighbour-chain implementation; scipy is only the oracle."""
+    from scipy.cluster.hierarchy import leaves_list, linkage
+    from scipy.spatial.distance import pdist, squareform
+    rng = np.random.default_rng(3)
+    for n in (2, 3, 17, 120):
+        x = rng.standard_normal((n, 6))
+        d = squareform(pdist(x))
+        Z, leaves = C.hclust(torch.from_numpy(d), method)
+        ref = linkage(pdist(x), method=method)
+        assert np.allclose(Z[:, 2], ref[:, 2], rtol=1e-10, atol=1e-12), method
+        assert np.array_equal(Z[:, [0, 1, 3]], ref[:, [0, 1, 3]]), method
+        assert np.array_equal(leaves, leaves_list(ref))
+    assert "scipy" not in C.hclust.__code__.co_names and "linkage" not in C.hclust_order.__code__.co_names
