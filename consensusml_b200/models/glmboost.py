@@ -3,14 +3,22 @@
 centred predictors), with that script's prefilter (between-cohort mean difference, :44-53) and its dichotomised
 evaluation (:78-108).
 
-Each boosting step needs the univariate least-squares fit of the residual on every column: ``X^T r`` (the same
-product as the lasso gradient - the fused reduce-scatter path when sample-sharded) followed by an arg-max."""
+Each boosting step needs the univariate least-squares fit of the residual on every column (``X^T r``) followed by an
+arg-max and a rank-one residual update.  On CUDA all ``mstop`` steps are enqueued by one call of ``cml_glmboost``
+(csrc/boost.cu: a warp-per-column scoring kernel and a one-CTA update kernel per step, stream-ordered, no host round
+trip); CPU tensors run the float64 torch restatement below, which is also the oracle."""
 from __future__ import annotations
 
+import ctypes
 from dataclasses import dataclass
 from typing import Dict, Sequence
 
 import torch
+
+from .. import _native
+
+_I, _D, _P = ctypes.c_int, ctypes.c_double, ctypes.c_void_p
+_native.register_signature("cml_glmboost", [_P, _I, _I, _I, _P, _P, _P, _I, _D, _P, _P, _P, _P])
 
 
 @dataclass
@@ -36,6 +44,23 @@ def glmboost(x: torch.Tensor, y: torch.Tensor, mstop: int = 100, nu: float = 0.1
     offset = yd.mean()
     r = yd - offset
     coef = torch.zeros(xd.shape[1], dtype=torch.float64, device=x.device)
+    if _native.on_device(x):
+        n, p = xd.shape
+        n_pad = (n + 31) // 32 * 32
+        xct = torch.zeros(p, n_pad, dtype=torch.float32, device=x.device)
+        xct[:, :n] = xc.t().float()
+        ssd = (xct.double() ** 2).sum(1).contiguous()          # sums of squares of the columns the kernel actually reads
+        rp = torch.zeros(n_pad, dtype=torch.float64, device=x.device)
+        rp[:n] = r
+        best = torch.zeros(mstop, dtype=torch.int64, device=x.device)
+        path_t = torch.empty(mstop, dtype=torch.int32, device=x.device)
+        risk_t = torch.empty(mstop, dtype=torch.float64, device=x.device)
+        P = _native.ptr
+        rc = _native.cuda().cml_glmboost(P(xct), p, n, n_pad, P(ssd), P(rp), P(coef), int(mstop), float(nu), P(best), P(path_t), P(risk_t),
+                                         _native.stream_ptr())
+        _native.check(rc, "cml_glmboost")
+        intercept = float(offset - (coef * mean).sum())
+        return GLMBoostFit(intercept, coef, path_t.tolist(), risk_t.tolist())
     path, risk = [], []
     for _ in range(mstop):
         g = xc.t() @ r                                         # X^T r

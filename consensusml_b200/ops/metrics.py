@@ -3,16 +3,51 @@
 Reference: confusion + test error cml_targetaml_seanalysis.Rmd:105-108; TPR/TNR/FDR/FOR :815-848;
 log-loss scripts/model_comp.py:24-27; ROC via ROCR :176-177; chi-square balance checks :462,470.
 The reference never prints an AUC; BASELINE.md derives 0.9835 from the stored model, so AUC is
-first-class here.  These are tiny reductions (n <= a few hundred in the reference, counts are
-all-reduced across ranks when sample-sharded), implemented with torch tensor ops on whatever
-device the inputs live on.
+first-class here.  ``batch_metrics`` evaluates many score vectors (every lambda of a path, every grid
+configuration, every replicate) in ONE launch of ``binary_metrics_kernel`` (csrc/metrics.cu: in-CTA sort,
+rank-sum AUC with tie handling, log-loss, confusion counts); ``auc`` / ``log_loss`` / ``confusion_matrix`` of a
+device tensor go through it too.  CPU tensors use the torch restatement below, which is also the oracle.
 """
 from __future__ import annotations
 
+import ctypes
 from dataclasses import dataclass
-from typing import Dict
+from typing import Dict, Optional
 
 import torch
+
+from .. import _native
+
+_native.register_signature("cml_binary_metrics", [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                                  ctypes.c_longlong, ctypes.c_float, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p])
+_KERNEL_MAX_N = 8192
+
+
+def batch_metrics(scores: torch.Tensor, truth: torch.Tensor, threshold: float = 0.0, is_prob: bool = False) -> Dict[str, torch.Tensor]:
+    """Metrics of B score vectors at once.  scores [B, n]; truth [n] or [B, n] in {0, 1}; class 1 iff score > threshold
+    (0 for decision values / link scale, 0.5 for probabilities).  Returns float64 tensors of length B:
+    auc, logloss (NaN unless ``is_prob``), tn, fn, fp, tp, error."""
+    if scores.dim() == 1:
+        scores = scores[None, :]
+    B, n = scores.shape
+    if _native.on_device(scores) and n <= _KERNEL_MAX_N:
+        sc = scores.float().contiguous()
+        tr = truth.to(device=sc.device, dtype=torch.float32).contiguous()
+        out = torch.empty(B, 8, dtype=torch.float64, device=sc.device)
+        rc = _native.cuda().cml_binary_metrics(_native.ptr(sc), sc.stride(0), B, n, _native.ptr(tr), n if tr.dim() == 2 else 0,
+                                               float(threshold), int(is_prob), _native.ptr(out), _native.stream_ptr())
+        _native.check(rc, "cml_binary_metrics")
+    else:
+        out = torch.empty(B, 8, dtype=torch.float64, device=scores.device)
+        for b in range(B):
+            t = truth if truth.dim() == 1 else truth[b]
+            cm = _confusion_torch((scores[b] > threshold), t)
+            out[b, 0] = _auc_torch(scores[b], t)
+            out[b, 1] = _log_loss_torch(t, scores[b]) if is_prob else float("nan")
+            out[b, 2:6] = cm.flatten().double()
+            out[b, 6], out[b, 7] = cm[:, 1].sum(), cm[:, 0].sum()
+    return {"auc": out[:, 0], "logloss": out[:, 1], "tn": out[:, 2], "fn": out[:, 3], "fp": out[:, 4], "tp": out[:, 5],
+            "error": (out[:, 3] + out[:, 4]) / n}
 
 
 @dataclass
@@ -33,6 +68,13 @@ class BinaryReport:
 
 def confusion_matrix(pred: torch.Tensor, truth: torch.Tensor) -> torch.Tensor:
     """2x2 table with rows = predicted class, columns = true class (R's ``table(pred, truth)``)."""
+    if _native.on_device(pred) and pred.numel() <= _KERNEL_MAX_N:
+        m = batch_metrics(pred.flatten().float(), truth.flatten(), threshold=0.5)
+        return torch.stack([m["tn"], m["fn"], m["fp"], m["tp"]], 1).reshape(2, 2).long()
+    return _confusion_torch(pred, truth)
+
+
+def _confusion_torch(pred: torch.Tensor, truth: torch.Tensor) -> torch.Tensor:
     pred = pred.long().flatten()
     truth = truth.long().flatten()
     idx = pred * 2 + truth
@@ -55,6 +97,12 @@ def log_loss(truth: torch.Tensor, prob: torch.Tensor, eps: float = 1e-15) -> flo
     """Binary cross-entropy of P(class 1), clipped like scikit-learn's ``log_loss``."""
     if prob.dim() == 2:
         prob = prob[:, 1]
+    if _native.on_device(prob) and prob.numel() <= _KERNEL_MAX_N and eps == 1e-15:
+        return float(batch_metrics(prob.flatten(), truth.flatten(), threshold=0.5, is_prob=True)["logloss"][0])
+    return _log_loss_torch(truth, prob, eps)
+
+
+def _log_loss_torch(truth: torch.Tensor, prob: torch.Tensor, eps: float = 1e-15) -> float:
     p = prob.double().clamp(eps, 1 - eps)
     t = truth.double()
     return float(-(t * p.log() + (1 - t) * (1 - p).log()).mean())
@@ -81,6 +129,12 @@ def roc_curve(score: torch.Tensor, truth: torch.Tensor):
 
 def auc(score: torch.Tensor, truth: torch.Tensor) -> float:
     """Area under the ROC curve by the rank-sum (Mann-Whitney) identity with average ranks for ties."""
+    if _native.on_device(score) and score.numel() <= _KERNEL_MAX_N:
+        return float(batch_metrics(score.flatten(), truth.flatten())["auc"][0])
+    return _auc_torch(score, truth)
+
+
+def _auc_torch(score: torch.Tensor, truth: torch.Tensor) -> float:
     s = score.double().flatten()
     t = truth.double().flatten()
     n1 = float(t.sum())

@@ -184,6 +184,49 @@ int cml_standardize_rows(const float* x, long long ldx, int rows, int n, int ran
 int cml_kde(const float* x, int n, float bw, float lo, float hi, int n_grid, float* out, void* stream);
 int cml_kmeans_assign(const float* d2, long long ld, int n, int k, int* assign, float* mind, void* stream);
 
+/* ---- K12 + binning for n > 256 (csrc/select.cu) ---------------------------------------------------------------------
+ * Per-gene variance and top-k: scripts/model_comp.py:62-79 (`ldf.var(axis=0)`, 1000 most / least variable genes),
+ * VikasP/AML.R:157-158.  cml_column_moments: x [n][ldx] fp32 sample-major, rowmask [n] or NULL -> out3p = count | mean | M2
+ * (float64, [3][p]); the triple merges across sample shards (Chan).  cml_topk_select: indices of the k best of p values
+ * (set semantics of a stable sort: ties to the lower index; caller orders the k).  cml_quantile_edges: per gene, max_bin
+ * type-7 quantiles of (a strided sample of up to 16,384 of) its n values, duplicates removed -> edges [p][256], n_edges [p];
+ * cml_apply_bins turns them into uint8 bins (pan-cancer matrix: 474 samples, Normalization_and_Batch_Effect_Investigation.Rmd:55-61). */
+size_t cml_column_moments_scratch_bytes(int n, int p);
+int cml_column_moments(const float* x, long long ldx, int n, int p, const unsigned char* rowmask, void* scratch, double* out3p,
+                       void* stream);
+int cml_topk_select(const float* v, int p, int k, int largest, int* out_idx, int* out_count, void* stream);
+int cml_quantile_edges(const float* xt, int p, int n, long long ld, int max_bin, float* edges, int* n_edges, void* stream);
+
+/* ---- K15: batched k-means (csrc/kmeans.cu) - kmeans(df, k, nstart = 25) for k = 20..2, BuieRProj/KM_WHATEVER.Rmd:151-161.
+ * One CTA per (restart, k): k-means++ seeding + Lloyd to convergence.  ks_dev [nk] ints on the device; outputs
+ * centers [nk][R][kmax][d], labels [nk][R][n], mind [nk][R][n], withinss [nk][R][kmax], tot [nk][R], iters [nk][R]. */
+int cml_kmeans_lloyd(const float* x, long long ldx, int n, int d, const int* ks_dev, int nk, int kmax, int restarts, int max_iter,
+                     unsigned long long seed, float* centers, int* labels, float* mind, float* withinss, float* tot, int* iters,
+                     void* stream);
+int cml_kmeans_update(const float* x, long long ldx, int n, int d, int k, const int* labels, float* centers, int* counts, void* stream);
+
+/* ---- K16: component-wise L2 boosting (csrc/boost.cu) - mlr regr.glmboost, Ryan/Feature_selection_GLMTrain_WT_TARGET.R:56-64.
+ * xct [p][n_pad] centred columns, ss [p] their sums of squares, r [n_pad] residual (updated), coef [p] (updated),
+ * best [mstop] scratch words, path [mstop], risk [mstop].  All mstop steps are enqueued by this one call. */
+int cml_glmboost(const float* xct, int p, int n, int n_pad, const double* ss, double* r, double* coef, int mstop, double nu,
+                 unsigned long long* best, int* path, double* risk, void* stream);
+
+/* ---- K17: grid-batched MLP epoch (csrc/mlp.cu) - the "Neural Networks with keras" the reference only advertises (README.md:25).
+ * cml_mlp_tail: pre [n][ldp] = X W1^T (no bias) -> dhT bf16 [H][ldn], hv [n][H], dl [n][G], loss [n][G], prob [n][G] or NULL.
+ * cml_mlp_adam: state = 12 pointers (w1 b1 w2 b2 | first moments | second moments); gsmall = NULL or precomputed gb1|gw2|gb2. */
+int cml_mlp_tail(const float* pre, long long ldp, int n, int H, int G, const int* seg, const float* b1, const float* w2, const float* b2,
+                 const float* y, float inv_n_total, void* dhT_bf16, long long ldn, float* hv, float* dl, float* loss, float* prob,
+                 void* stream);
+int cml_mlp_adam(float* const* state, const float* gw1, long long ldg, const float* hv, const float* dl, const float* gsmall,
+                 void* w1_bf16, long long ldw, const int* cfg_of, const float* lr, const float* wd, int n, int H, int G, int p,
+                 float beta1, float beta2, float eps, int step, void* stream);
+
+/* ---- K18: batched evaluation metrics (csrc/metrics.cu) - confusion / TPR / TNR (cml_targetaml_seanalysis.Rmd:105-108,815-848),
+ * log-loss (scripts/model_comp.py:24-27), ROC area (ROCR, :176-177).  scores [B][ld]; truth [n] (stride 0) or [B][n] floats;
+ * out [B][8] float64: auc, logloss, tn, fn, fp, tp, n_pos, n_neg.  n <= 8192 per vector. */
+int cml_binary_metrics(const float* scores, long long ld, int B, int n, const float* truth, long long truth_stride, float threshold,
+                       int is_prob, double* out, void* stream);
+
 /* ---- Fused compute + collective kernels over NVLink peer memory (absent from the reference) ---- */
 size_t cml_xtr_rs_scratch_bytes(int p, int nb);
 int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
@@ -237,6 +280,10 @@ int cml_host_lognet_path(int B, int n, int p, int nlam, const double* xt, const 
 void cml_host_lognet_counters(long long* out8);
 /* 0 (default): glmnet's loop statement for statement; 1: covariance updates inside the active-set sweeps (same iteration). */
 void cml_host_lognet_set_active_mode(int mode);
+/* Agglomerative clustering (nearest-neighbour chain, Lance-Williams) of an n x n distance matrix: hclust(dist(x)) behind
+ * ComplexHeatmap's clustered heatmaps (cml_targetaml_seanalysis.Rmd:536-613).  method 0 single, 1 complete, 2 average,
+ * 3 weighted, 4 ward.  Z: (n-1) x 4 in scipy's linkage convention; leaves: dendrogram leaf order. */
+int cml_host_hclust(const double* dist, int n, int method, double* Z, int* leaves);
 /* Host build of the eBayes kernel's Student-t tail (csrc/tdist.cuh): two-sided p of n statistics, df[i * df_stride]. */
 void cml_host_t_two_sided(const double* t, const double* df, int df_stride, int n, double* p_out);
 /* Genes x samples integer CSV -> int32 matrix, parsed by a thread pool over an mmap (pandas: 5.8 s, this: 0.2 s at

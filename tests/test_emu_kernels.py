@@ -338,3 +338,96 @@ def test_kmeans_sweep_kernel_reaches_the_same_minima_as_the_host_path():
         assert torch.equal(torch.cdist(x, r.centers).argmin(1), r.labels)
         assert torch.equal(r.labels, again[k].labels) and r.tot_withinss == again[k].tot_withinss      # reproducible
     assert sorted(torch.bincount(dev[4].labels).tolist()) == [30, 30, 30, 30]
+
+
+def test_batched_metrics_kernel_matches_the_torch_restatement():
+    from consensusml_b200.ops import metrics as M
+    g = torch.Generator().manual_seed(21)
+    B, n = 5, 137
+    truth = (torch.rand(n, generator=g) < 0.45).float()
+    scores = torch.randn(B, n, generator=g) + truth[None, :] * torch.linspace(0, 2, B)[:, None]
+    scores[1] = torch.round(scores[1] * 2) / 2            # many tied scores
+    scores[4] = 0.3                                       # all tied: AUC 0.5 exactly
+    probs = torch.sigmoid(scores)
+    with _native.emulation(seed=6):
+        m = M.batch_metrics(scores, truth)
+        mp = M.batch_metrics(probs, truth, threshold=0.5, is_prob=True)
+        one_auc = M.auc(scores[2], truth)
+        cm = M.confusion_matrix((scores[2] > 0).float(), truth)
+        ll = M.log_loss(truth, probs[3])
+    for b in range(B):
+        assert abs(float(m["auc"][b]) - M._auc_torch(scores[b], truth)) < 1e-12, b
+        assert abs(float(mp["logloss"][b]) - M._log_loss_torch(truth, probs[b])) < 1e-6
+        ref = M._confusion_torch(scores[b] > 0, truth).flatten().tolist()
+        assert [int(m[k][b]) for k in ("tn", "fn", "fp", "tp")] == ref
+    assert float(m["auc"][4]) == 0.5 and torch.isnan(m["logloss"]).all()
+    assert abs(one_auc - M._auc_torch(scores[2], truth)) < 1e-12
+    assert torch.equal(cm, M._confusion_torch(scores[2] > 0, truth))
+    assert abs(ll - M._log_loss_torch(truth, probs[3])) < 1e-6
+
+
+def test_glmboost_kernels_follow_the_float64_path():
+    from consensusml_b200.models import glmboost as GB
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(70, 90, generator=g)
+    x[:, 11] = 2.0                                         # constant column: never usable
+    y = 300 + 40 * x[:, 3] - 25 * x[:, 17] + 5 * torch.randn(70, generator=g)
+    ref = GB.glmboost(x, y, mstop=30, nu=0.1)
+    with _native.emulation(seed=3):
+        fit = GB.glmboost(x, y, mstop=30, nu=0.1)
+    assert fit.path == ref.path
+    assert torch.allclose(fit.coef, ref.coef, rtol=1e-5, atol=1e-6) and abs(fit.intercept - ref.intercept) < 1e-3
+    assert np.allclose(fit.risk, ref.risk, rtol=1e-5)
+
+
+def test_mlp_epoch_kernels_match_a_torch_restatement_with_the_same_bf16_roundings():
+    from consensusml_b200.models import mlp as MLP
+    g = torch.Generator().manual_seed(5)
+    n, p = 61, 37
+    x = torch.randn(n, p, generator=g)
+    y = ((x[:, 0] - x[:, 1] + 0.5 * x[:, 2]) > 0).float()
+    grid = [dict(hidden=5, lr=3e-3, weight_decay=0.0, seed=0), dict(hidden=9, lr=1e-2, weight_decay=1e-3, seed=1),
+            dict(hidden=3, lr=1e-3, weight_decay=1e-2, seed=2)]
+    # one epoch must agree to rounding; over more epochs Adam's m / sqrt(v) amplifies last-bit differences of tiny
+    # gradients (and a bf16 rounding tie can flip), so the 12-epoch comparison is looser
+    for epochs, tol in ((1, 2e-6), (12, 1e-3)):
+        _check_mlp(MLP, x, y, grid, n, epochs, tol)
+
+
+def _check_mlp(MLP, x, y, grid, n, epochs, tol):
+    with _native.emulation(seed=4):
+        res = MLP.train_grid(x, y, grid, epochs=epochs)
+    # restatement: the fp32 torch loop of train_grid with bf16 rounding of the three GEMM operands (X, W1, dH)
+    bf = lambda t: t.to(torch.bfloat16).float()
+    xf = x.float()
+    mean, sd = xf.mean(0), xf.std(0, unbiased=True)
+    xs = (xf - mean) / torch.where(sd > 0, sd, torch.ones_like(sd))
+    ref = MLP.train_grid(x, y, grid, epochs=0)                              # initial weights only
+    w1, b1, w2, b2 = ref.w1.clone(), ref.b1.clone(), ref.w2.clone(), ref.b2.clone()
+    hs = [c["hidden"] for c in grid]
+    seg = torch.repeat_interleave(torch.arange(3), torch.tensor(hs))
+    lr_u = torch.tensor([c["lr"] for c in grid])[seg]
+    wd_u = torch.tensor([c["weight_decay"] for c in grid])[seg]
+    lr_g = torch.tensor([c["lr"] for c in grid])
+    params = [w1, b1, w2, b2]
+    m = [torch.zeros_like(t) for t in params]
+    v = [torch.zeros_like(t) for t in params]
+    lrs, wds = [lr_u[:, None], lr_u, lr_u, lr_g], [wd_u[:, None], None, wd_u, None]
+    xb = bf(xs)
+    for t in range(1, epochs + 1):
+        pre = xb @ bf(w1).t() + b1
+        h = torch.relu(pre)
+        logit = torch.zeros(n, 3).index_add_(1, seg, h * w2[None, :]) + b2[None, :]
+        prob = torch.sigmoid(logit)
+        dlogit = (prob - y[:, None]) / n
+        dh = dlogit[:, seg] * w2[None, :] * (pre > 0)
+        grads = [bf(dh).t() @ xb, dh.sum(0), (dlogit[:, seg] * h).sum(0), dlogit.sum(0)]
+        for i, (pt, gr) in enumerate(zip(params, grads)):
+            if wds[i] is not None:
+                gr = gr + wds[i] * pt
+            m[i].mul_(0.9).add_(gr, alpha=0.1)
+            v[i].mul_(0.999).addcmul_(gr, gr, value=0.001)
+            pt.sub_(lrs[i] * (m[i] / (1 - 0.9 ** t)) / ((v[i] / (1 - 0.999 ** t)).sqrt() + 1e-8))
+    for a, b in ((res.w1, w1), (res.b1, b1), (res.w2, w2), (res.b2, b2)):
+        assert float((a - b).abs().max()) <= tol, (epochs, float((a - b).abs().max()))
+    assert torch.isfinite(res.train_loss).all() and (res.train_loss < 0.8).all()
