@@ -33,6 +33,12 @@ _native.register_signature("cml_hist_scratch_bytes", [_I, _I], _SZ)
 _native.register_signature("cml_hist_ft", [_I, _I], _I)
 _native.register_signature("cml_hist_allreduce", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _I, _U, _I, _F, _F, _P])
 _native.register_signature("cml_split_score_gain", [_P, _I, _I, _I, _F, _F, _F, _P, _P])
+_native.register_signature("cml_split_score_gain_at", [_P, _I, _I, _I, _F, _F, _F, _P, _I, _P])
+_native.register_signature("cml_hist_build", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _P, _I, _I, _I, _U, _I, _F, _F, _P])
+_native.register_signature("cml_gbm_grad", [_P, _P, _P, _I, _P])
+_native.register_signature("cml_gbm_totals", [_P, _P, _I, _I, _P, _P])
+_native.register_signature("cml_hist_derive", [_P, _P, _P, _P, _P, _LL, _I, _P])
+_native.register_signature("cml_gbm_route", [_P, _LL, _P, _P, _P, _P, _P, _I, _I, _P])
 
 SIG_GRAD, SIG_BETA, SIG_HIST = 0, 8, 16      # signal-pad word ranges (one word per rank each)
 
@@ -231,6 +237,84 @@ class HistAllReduce:
         self.hist.local[: n_nodes * self.p * self.nbins * 2].zero_()
         torch.cuda.synchronize()
         self.hist.barrier()
+
+
+class HistEngine:
+    """Per-level gradient histograms with the reduce-scatter-by-feature landing.
+
+    Rank r owns features [r * fpr, (r + 1) * fpr): every rank's build kernel adds its finished feature tiles into the
+    OWNER's buffer only (peer ``red.add.v4.f32`` from inside the kernel), so a rank receives 1 / world of the histogram,
+    scores only its own features, and the ranks agree on the split with one MAX all-reduce of n_nodes 64-bit keys.
+    Compared with the all-reduce landing (``HistAllReduce``) that is 1 / world of the bytes landed per rank and
+    1 / world of the split-scoring work.  Slots: a launch builds ``n_slots`` histograms selected by a node -> slot table,
+    which is how sibling subtraction (build the smaller child only) and node batching (more open nodes than shared
+    memory holds) are expressed.  The landing buffer is cleaned by ``derive`` as it reads, so there is no separate clear
+    and no barrier between levels."""
+
+    MAX_SLOTS_PER_LAUNCH = 64
+
+    def __init__(self, p: int, nbins: int, max_slots: int, max_nodes: int, device):
+        self.p, self.nbins, self.max_slots = p, nbins, max_slots
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.fpr = ((p + self.world - 1) // self.world + 7) // 8 * 8          # features per rank: a multiple of every tile width
+        self.feat0 = self.rank * self.fpr
+        self.cells = self.fpr * nbins * 2
+        self.landing = symm.alloc((max_slots * self.cells,), torch.float32, device)
+        per_launch = min(max_slots, self.MAX_SLOTS_PER_LAUNCH)
+        self.local = torch.zeros(per_launch * p * nbins * 2, dtype=torch.float32, device=device)
+        self.counters = torch.zeros(p + 16, dtype=torch.int32, device=device)
+        self.levels = [torch.zeros(max_nodes * self.cells, dtype=torch.float32, device=device) for _ in range(2)]
+        self.best = torch.zeros(max_nodes, dtype=torch.int64, device=device)
+        self.epoch = 0
+        self.device = device
+
+    def build(self, bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, slot_of: torch.Tensor, n_slots: int,
+              g_bound: float, h_bound: float) -> None:
+        """Histogram the samples of the nodes that have a slot and land every feature tile on its owner.  Slots beyond what
+        shared memory holds per launch are built in batches (each batch re-reads the bins of its own samples only)."""
+        lib = _native.cuda()
+        S = self.MAX_SLOTS_PER_LAUNCH
+        for s0 in range(0, n_slots, S):
+            ns = min(S, n_slots - s0)
+            so = slot_of if n_slots <= S else torch.where((slot_of >= s0) & (slot_of < s0 + ns), slot_of - s0, torch.full_like(slot_of, -1))
+            self.epoch += 1
+            off = s0 * self.cells * 4
+            rc = lib.cml_hist_build(_native.ptr(bins), bins.shape[1], n, self.p, self.nbins, _native.ptr(node), _native.ptr(gh), ns,
+                                    _native.ptr(so.contiguous()), _native.ptr(self.local), _native.ptr(self.counters), None,
+                                    _ptr_array([a + off for a in self.landing.peer_ptrs]), _ptr_array(self.landing.signal_ptrs), self.rank,
+                                    self.world, self.fpr, self.epoch, SIG_HIST, float(g_bound), float(h_bound), _native.stream_ptr())
+            _native.check(rc, "cml_hist_build")
+            rc = lib.cml_wait_signals(ctypes.c_void_p(self.landing.signal_ptrs[self.rank]), SIG_HIST, self.world, self.epoch,
+                                      _native.stream_ptr())
+            _native.check(rc, "cml_wait_signals")
+
+    def derive(self, level: int, n_nodes: int, slot_of: torch.Tensor, count: torch.Tensor) -> torch.Tensor:
+        """Full histograms of this level's nodes for the owned features, [n_nodes, fpr, nbins, 2]: built slots are copied,
+        derived nodes are parent - sibling (the parent level is the buffer ``derive`` filled one level up)."""
+        full, parent = self.levels[level & 1], self.levels[(level + 1) & 1]
+        rc = _native.cuda().cml_hist_derive(_native.ptr(self.landing.local), _native.ptr(parent) if n_nodes > 1 else None, _native.ptr(full),
+                                            _native.ptr(slot_of.contiguous()), _native.ptr(count.contiguous()), self.cells, n_nodes,
+                                            _native.stream_ptr())
+        _native.check(rc, "cml_hist_derive")
+        return full[: n_nodes * self.cells].view(n_nodes, self.fpr, self.nbins, 2)
+
+    def best_keys(self, full: torch.Tensor, n_nodes: int, lam: float, gamma: float, min_child_weight: float) -> torch.Tensor:
+        """Packed (gain | feature | bin) key of the best split of every node over the OWNED features (global feature ids)."""
+        rc = _native.cuda().cml_split_score_gain_at(_native.ptr(full), n_nodes, self.fpr, self.nbins, lam, gamma, min_child_weight,
+                                                    _native.ptr(self.best), self.feat0, _native.stream_ptr())
+        _native.check(rc, "cml_split_score_gain_at")
+        return self.best[:n_nodes]
+
+
+def decode_split_keys(key: torch.Tensor):
+    """(gain fp32, feature int64, bin int64) from the packed keys; -1 / 0 where a node has no valid split."""
+    has = key != 0
+    gain = ((key >> 32) & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+    feat = 0xFFFFF - ((key >> 12) & 0xFFFFF)
+    b = 0xFFF - (key & 0xFFF)
+    neg = -torch.ones_like(feat)
+    return torch.where(has, gain, torch.zeros_like(gain)), torch.where(has, feat, neg), torch.where(has, b, neg)
 
 
 def hist_unfused(bins: torch.Tensor, n: int, node: torch.Tensor, gh: torch.Tensor, n_nodes: int, p: int, nbins: int) -> torch.Tensor:

@@ -276,7 +276,11 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
     const unsigned char* __restrict__ bins, long long n_pad, int n, int p, int nbins, const short* __restrict__ node,
     const float2* __restrict__ gh, int n_nodes, int FT, float* __restrict__ local_hist, unsigned* __restrict__ tile_count,
     unsigned* __restrict__ done_count, float* mc_hist, Peers P, unsigned epoch, int rows_per_chunk, int sig_base, float scale_g,
-    float scale_h) {
+    float scale_h, const short* __restrict__ slot_of, int feats_per_rank) {
+  // slot_of (optional): level-local node id -> histogram slot, -1 = node not built this launch (its histogram is derived
+  // from parent - sibling, or belongs to another node batch); n_nodes then counts SLOTS.  feats_per_rank > 0 selects the
+  // reduce-scatter landing: feature f belongs to rank f / feats_per_rank and its finished tile is added into that rank's
+  // buffer only, laid out [slot][f - owner * feats_per_rank][bin][2]; 0 keeps the all-reduce landing (every rank, [slot][f]).
   // Shared-memory accumulation is int32 fixed point: fp32 shared atomics compile to a CAS loop (ATOMS.CAST.SPIN) while
   // integer adds are native ATOMS.ADD, and integer sums are order independent (bit-reproducible histograms).
   extern __shared__ int sh[];                   // [n_nodes][FT][nbins][2]
@@ -296,6 +300,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
     for (int q = 0; q < 4; ++q) {
       const bool ok = i + q < i1;
       nd[q] = ok ? (int)node[i + q] : -1;
+      if (slot_of && nd[q] >= 0) nd[q] = (int)slot_of[nd[q]];
       const float2 gf = ok ? gh[i + q] : make_float2(0.f, 0.f);
       qg[q] = __float2int_rn(gf.x * scale_g);
       qh[q] = __float2int_rn(gf.y * scale_h);
@@ -335,14 +340,17 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
   if (!sh_last) return;
   __threadfence();
   const int row_floats = (f1 - f0) * nbins * 2;               // contiguous run per node
+  const int owner = feats_per_rank > 0 ? min(f0 / feats_per_rank, P.world - 1) : 0;      // tiles never straddle owners (host pads)
   for (int nd = 0; nd < n_nodes; ++nd) {
     const size_t off = ((size_t)nd * p + f0) * nbins * 2;
     float* src = local_hist + off;
+    const size_t off_rs = ((size_t)nd * feats_per_rank + (f0 - owner * feats_per_rank)) * nbins * 2;
     for (int e = threadIdx.x * 4; e < row_floats; e += blockDim.x * 4) {
       const float4 v = __ldcg(reinterpret_cast<const float4*>(src + e));
       *reinterpret_cast<float4*>(src + e) = make_float4(0.f, 0.f, 0.f, 0.f);
       if (v.x == 0.f && v.y == 0.f && v.z == 0.f && v.w == 0.f) continue;
-      if (mc_hist) multimem_red_add_v4(mc_hist + off + e, v);
+      if (feats_per_rank > 0) red_add_v4_sys(P.buf[owner] + off_rs + e, v);
+      else if (mc_hist) multimem_red_add_v4(mc_hist + off + e, v);
       else
         for (int r = 0; r < P.world; ++r) red_add_v4_sys(P.buf[r] + off + e, v);
     }
@@ -362,7 +370,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_allreduce_kernel(
 // Best split per open node from the all-reduced histogram: prefix scan over bins, xgboost gain.
 // One warp per (node, feature); per-node arg-max through a packed 64-bit atomicMax (gain bits | feature | bin).
 __global__ void split_score_gain_kernel(const float* __restrict__ hist, int n_nodes, int p, int nbins, float lambda, float gamma,
-                                        float min_child_weight, unsigned long long* __restrict__ best, float* __restrict__ best_stats) {
+                                        float min_child_weight, unsigned long long* __restrict__ best, float* __restrict__ best_stats,
+                                        int feat0) {
   const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= (long long)n_nodes * p) return;
@@ -403,7 +412,7 @@ __global__ void split_score_gain_kernel(const float* __restrict__ hist, int n_no
   if (lane == 0 && bbin >= 0 && bgain > 0.f) {
     // order-preserving key: positive floats compare like their bit patterns; smaller feature wins ties
     const unsigned long long key = ((unsigned long long)__float_as_uint(bgain) << 32) |
-                                   ((unsigned long long)(0xFFFFFu - (unsigned)f) << 12) | (unsigned)(0xFFFu - (unsigned)bbin);
+                                   ((unsigned long long)(0xFFFFFu - (unsigned)(f + feat0)) << 12) | (unsigned)(0xFFFu - (unsigned)bbin);
     atomicMax(&best[nd], key);
   }
   (void)best_stats;
@@ -541,19 +550,30 @@ int cml_xb_residual(const void* x_bf16, long long ldx, int n, int p, const float
 
 size_t cml_hist_scratch_bytes(int p, int ft) { return (size_t)(cml::ceil_div(p, ft) + 4) * sizeof(unsigned) + 64; }
 
-// local_hist: rank-local [n_nodes][p][nbins][2] zero-initialised (self-cleaning).  The reduced histogram appears in
-// every rank's symmetric copy (peer_bufs[r]); those copies must be zero at entry.
-int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
-                       int n_nodes, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
-                       const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, float g_bound, float h_bound,
-                       void* stream) {
+// local_hist: rank-local [n_slots][p][nbins][2] zero-initialised (self-cleaning).
+// feats_per_rank == 0: all-reduce landing - the reduced histogram appears in every rank's symmetric copy (peer_bufs[r],
+// [n_slots][p][nbins][2], zero at entry).  feats_per_rank > 0: reduce-scatter landing - rank r receives only features
+// [r * feats_per_rank, (r + 1) * feats_per_rank) as [n_slots][feats_per_rank][nbins][2]; feats_per_rank must be a multiple of
+// cml_hist_ft(n_slots, nbins) so that no feature tile straddles two owners.  slot_of: see the kernel.
+int cml_hist_build(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
+                   int n_slots, const short* slot_of, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
+                   const void* const* peer_sigs, int rank, int world, int feats_per_rank, unsigned epoch, int sig_base, float g_bound,
+                   float h_bound, void* stream) {
   using namespace cml;
-  CML_REQUIRE(n > 0 && p > 0 && nbins >= 2 && nbins <= 256 && n_nodes >= 1, CML_EINVAL, "cml_hist_allreduce: bad shape");
-  CML_REQUIRE((nbins * 2) % 4 == 0, CML_EINVAL, "cml_hist_allreduce: nbins must be even");
+  CML_REQUIRE(n > 0 && p > 0 && nbins >= 2 && nbins <= 256 && n_slots >= 1, CML_EINVAL, "cml_hist_build: bad shape");
+  CML_REQUIRE((nbins * 2) % 4 == 0, CML_EINVAL, "cml_hist_build: nbins must be even");
+  CML_REQUIRE(n_pad % 4 == 0 && (reinterpret_cast<uintptr_t>(bins) & 3) == 0, CML_EINVAL,
+              "cml_hist_build: bins rows must be 4-byte aligned (n_pad = %lld a multiple of 4): four bins are read per 32-bit load", n_pad);
+  CML_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, CML_EINVAL, "cml_hist_build: bad rank/world");
   int FT = 8;
-  while (FT > 1 && (size_t)n_nodes * FT * nbins * 2 * sizeof(float) > 36 * 1024) FT >>= 1;
-  const size_t smem = (size_t)n_nodes * FT * nbins * 2 * sizeof(float);
-  CML_REQUIRE(smem <= 200 * 1024, CML_E2BIG, "cml_hist_allreduce: %d open nodes x %d bins do not fit shared memory", n_nodes, nbins);
+  while (FT > 1 && (size_t)n_slots * FT * nbins * 2 * sizeof(float) > 36 * 1024) FT >>= 1;
+  const size_t smem = (size_t)n_slots * FT * nbins * 2 * sizeof(float);
+  CML_REQUIRE(smem <= 200 * 1024, CML_E2BIG, "cml_hist_build: %d histogram slots x %d bins do not fit shared memory (batch the nodes)",
+              n_slots, nbins);
+  CML_REQUIRE(feats_per_rank == 0 || (feats_per_rank % FT == 0 && (long long)feats_per_rank * world >= p), CML_EINVAL,
+              "cml_hist_build: feats_per_rank=%d must be a multiple of the feature tile %d and cover p=%d over %d ranks", feats_per_rank,
+              FT, p, world);
+  CML_REQUIRE(!(feats_per_rank > 0 && mc_hist), CML_EINVAL, "cml_hist_build: the reduce-scatter landing uses peer addresses, not the multicast address");
   CML_CUDA(cudaFuncSetAttribute(hist_allreduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int tiles = ceil_div(p, FT);
   unsigned* tile_count = static_cast<unsigned*>(counters);
@@ -563,14 +583,23 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
   chunks = ceil_div(n, rows_per_chunk);
   Peers P = make_peers(peer_bufs, peer_sigs, rank, world);
   dim3 grid(tiles, chunks);
-  CML_REQUIRE(g_bound > 0.f && h_bound > 0.f, CML_EINVAL, "cml_hist_allreduce: |g| and |h| bounds must be positive");
+  CML_REQUIRE(g_bound > 0.f && h_bound > 0.f, CML_EINVAL, "cml_hist_build: |g| and |h| bounds must be positive");
   // the largest per-CTA sum is rows_per_chunk * bound: scale so that it stays below 2^30
   const float scale_g = 1073741824.f / ((float)rows_per_chunk * g_bound), scale_h = 1073741824.f / ((float)rows_per_chunk * h_bound);
   hist_allreduce_kernel<<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
-      bins, n_pad, n, p, nbins, node, static_cast<const float2*>(gh), n_nodes, FT, local_hist, tile_count, done, mc_hist, P, epoch,
-      rows_per_chunk, sig_base, scale_g, scale_h);
+      bins, n_pad, n, p, nbins, node, static_cast<const float2*>(gh), n_slots, FT, local_hist, tile_count, done, mc_hist, P, epoch,
+      rows_per_chunk, sig_base, scale_g, scale_h, slot_of, feats_per_rank);
   CML_LAUNCH_CHECK();
   return 0;
+}
+
+// The all-reduce form with one slot per node (the entry point of round 1, kept for its callers).
+int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
+                       int n_nodes, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
+                       const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, float g_bound, float h_bound,
+                       void* stream) {
+  return cml_hist_build(bins, n_pad, n, p, nbins, node, gh, n_nodes, nullptr, local_hist, counters, mc_hist, peer_bufs, peer_sigs, rank,
+                        world, 0, epoch, sig_base, g_bound, h_bound, stream);
 }
 
 int cml_hist_ft(int n_nodes, int nbins) {
@@ -581,11 +610,23 @@ int cml_hist_ft(int n_nodes, int nbins) {
 
 int cml_split_score_gain(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
                          unsigned long long* best, void* stream) {
+  return cml_split_score_gain_at(hist, n_nodes, p, nbins, lambda, gamma, min_child_weight, best, 0, stream);
+}
+
+// Same, for a rank that holds only features [feat0, feat0 + p) of the cohort (reduce-scatter landing): the keys carry the
+// global feature index, so a MAX over the ranks' keys is the global best split.
+int cml_split_score_gain_at(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
+                            unsigned long long* best, int feat0, void* stream) {
   using namespace cml;
+  CML_REQUIRE(p >= 0 && feat0 >= 0 && feat0 + p <= 0xFFFFF, CML_E2BIG, "cml_split_score_gain: feature index beyond the 20-bit key field");
+  if (p == 0) {
+    CML_CUDA(cudaMemsetAsync(best, 0, sizeof(unsigned long long) * n_nodes, static_cast<cudaStream_t>(stream)));
+    return 0;
+  }
   const long long warps = (long long)n_nodes * p;
   CML_CUDA(cudaMemsetAsync(best, 0, sizeof(unsigned long long) * n_nodes, static_cast<cudaStream_t>(stream)));
   split_score_gain_kernel<<<(unsigned)ceil_div(warps, 8LL), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      hist, n_nodes, p, nbins, lambda, gamma, min_child_weight, best, nullptr);
+      hist, n_nodes, p, nbins, lambda, gamma, min_child_weight, best, nullptr, feat0);
   CML_LAUNCH_CHECK();
   return 0;
 }

@@ -265,9 +265,28 @@ int cml_hist_allreduce(const unsigned char* bins, long long n_pad, int n, int p,
     int n_nodes, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
     const void* const* peer_sigs, int rank, int world, unsigned epoch, int sig_base, float g_bound, float h_bound,
     void* stream);
+/* General form: n_slots histogram slots with an optional node -> slot table (slot_of[node] = -1: not built by this launch -
+ * sibling subtraction / node batching), and with feats_per_rank > 0 the reduce-scatter landing (rank r receives only its
+ * features, [n_slots][feats_per_rank][nbins][2]); feats_per_rank = 0 is the all-reduce landing above. */
+int cml_hist_build(const unsigned char* bins, long long n_pad, int n, int p, int nbins, const short* node, const void* gh,
+                   int n_slots, const short* slot_of, float* local_hist, void* counters, float* mc_hist, const void* const* peer_bufs,
+                   const void* const* peer_sigs, int rank, int world, int feats_per_rank, unsigned epoch, int sig_base, float g_bound,
+                   float h_bound, void* stream);
 int cml_hist_ft(int n_nodes, int nbins);
 int cml_split_score_gain(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
     unsigned long long* best, void* stream);
+int cml_split_score_gain_at(const float* hist, int n_nodes, int p, int nbins, float lambda, float gamma, float min_child_weight,
+    unsigned long long* best, int feat0, void* stream);
+/* Device steps of a boosting level (csrc/gbm.cu): logistic gradients; per-node (sum g, sum h, count) totals [n_nodes][3];
+ * sibling derivation full[2j], full[2j+1] from the built slot and parent[j] (zeroes the landing cells it reads); routing of
+ * the samples to the next level (or out of the tree, adding the node value to the margin).  xgboost semantics,
+ * cml_targetaml_seanalysis.Rmd:1164-1186. */
+int cml_gbm_grad(const float* margin, const float* y, void* gh, int n, void* stream);
+int cml_gbm_totals(const short* node, const void* gh, int n, int n_nodes, float* tot, void* stream);
+int cml_hist_derive(float* slots, const float* parent, float* full, const short* slot_of, const float* count, long long cells,
+                    int n_nodes, void* stream);
+int cml_gbm_route(const unsigned char* bins, long long n_pad, short* node, const long long* feat, const long long* thr,
+                  const float* value, float* margin, int n, int last_level, void* stream);
 
 /* ---- libcml_host.so (csrc/host): float64 CPU restatements and parsers ------------------------------------------ */
 /* glmnet lognet path, B replicates sharing xt [p][n] / y / lambda; outputs per replicate (see csrc/host/lognet_cpu.cpp). */
