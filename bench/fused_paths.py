@@ -60,16 +60,34 @@ def main():
     ap.add_argument("--experimental", action="store_true", help="also time the kernels / modes that are still opt-in")
     args = ap.parse_args()
     rank, world, dev = D.init()
+    measure(rank, world, dev, rows_per_gpu=args.rows, genes=args.genes, gram_rows=args.gram_rows, reps=args.reps, nodes=args.nodes,
+            bins_=args.bins, skip=args.skip, experimental=args.experimental, echo=True)
+    D.barrier()
+    D.shutdown()
+
+
+def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, reps=5, nodes=4, bins_=256, skip="", experimental=False,
+            echo=False):
+    """Time every fused path on a per-GPU shard of the given shape.  Returns the list of records (one dict per measurement,
+    each with the SM clock / throttle record sampled WHILE it was being timed); with ``echo`` rank 0 also prints them."""
+    import types
+    from consensusml_b200.runtime.clocks import ClockSampler
+    args = types.SimpleNamespace(rows=rows_per_gpu, genes=genes, gram_rows=gram_rows, reps=reps, nodes=nodes, bins=bins_, skip=skip,
+                                 experimental=experimental)
     hbm, tf, how = peaks()
     lib = _native.cuda()
     fb = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     flush = lambda: lib.cml_l2_flush(_native.ptr(fb), fb.numel(), _native.stream_ptr())
     n, p = args.rows, args.genes
     out = []
+    sampler = ClockSampler(dev.index or 0)
+    sampler.__enter__()
 
     def emit(**kw):
-        kw.update(n_gpus=world, peaks=how)
-        if rank == 0:
+        kw.update(n_gpus=world, peaks=how, clocks=sampler.summary())
+        sampler.samples.clear()
+        sampler.reasons.clear()
+        if rank == 0 and echo:
             print(json.dumps(kw), flush=True)
         out.append(kw)
 
@@ -94,7 +112,7 @@ def main():
                  frac_of_hbm_roofline=t_roof / (ms / 1e3), nvlink_bytes=link_bytes)
             if world > 1:
                 def run_un():
-                    full = xb[:, :p].float().t() @ R if False else torch.matmul(xb[:, :p].t().float() if False else xb.t()[:p].float(), R)
+                    full = torch.matmul(xb.t()[:p].float(), R)
                     o = torch.empty(rs.genes_per_rank, nb, device=dev)
                     pad = torch.zeros(rs.genes_per_rank * world, nb, device=dev)
                     pad[:p] = full
@@ -129,7 +147,30 @@ def main():
             t_roof = max(bytes_hbm / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
             emit(path="hist_allreduce", multicast=mc, rows_per_gpu=n, genes=p, bins=args.bins, nodes=args.nodes, ms=ms,
                  frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, smem_atomics=2.0 * n * p, atomics_per_s=2.0 * n * p / ms * 1e3)
-        del bins, H
+        del H
+        torch.cuda.empty_cache()
+        # the reduce-scatter-by-feature landing with sibling subtraction: a level with 2 * nodes open nodes histograms only the
+        # `nodes` smaller children (half of the samples), lands 1 / world of the bytes per rank, then derives + scores on the owner
+        E = F.HistEngine(p, args.bins, args.nodes, 2 * args.nodes, dev)
+        node2 = torch.randint(0, 2 * args.nodes, (n,), device=dev).to(torch.int16)
+        pair = torch.arange(args.nodes, device=dev, dtype=torch.int16)
+        slot_of = torch.stack([pair, torch.full_like(pair, -1)], 1).flatten().contiguous()      # left children built, right derived
+        count = torch.ones(2 * args.nodes, device=dev)
+        E.levels[1].normal_()                                                                   # a parent level to subtract from
+
+        def level():
+            E.build(bins, n, node2, gh, slot_of, args.nodes, 4.0, 4.0)
+            full = E.derive(1, 2 * args.nodes, slot_of, count)
+            E.best_keys(full, 2 * args.nodes, 1.0, 0.0, 1.0)
+        level()
+        ms = timed(level, args.reps, flush)
+        bytes_hbm = p * n_pad + n * 10
+        link = args.nodes * p * args.bins * 8 * (world - 1) / world
+        t_roof = max(bytes_hbm / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
+        emit(path="hist_reduce_scatter_level", rows_per_gpu=n, genes=p, bins=args.bins, open_nodes=2 * args.nodes, built_slots=args.nodes, ms=ms,
+             frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, smem_atomics=1.0 * n * p, atomics_per_s=1.0 * n * p / ms * 1e3,
+             includes="build (half of the samples) + peer landing + wait + sibling derivation + split scoring of the owned features")
+        del bins, E
         torch.cuda.empty_cache()
     # ------------------------------------------------------------------ path 3: all-gather -> tcgen05 Gram (RBF)
     if "gram" not in args.skip:
@@ -208,8 +249,8 @@ def main():
         t_roof = max(byts / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
         emit(path="shard_transpose", rows_per_gpu=m, genes=p, ms=ms, nccl_all_to_all_plus_transpose_ms=ms_nccl,
              gbs=byts / ms / 1e6, frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
-    D.barrier()
-    D.shutdown()
+    sampler.__exit__(None, None, None)
+    return out
 
 
 if __name__ == "__main__":

@@ -130,6 +130,23 @@ def main():
             print(f"[{rank}] hist_allreduce multicast={mc} rel err {err:.2e}", flush=True)
             ok &= err < 1e-4
             H.clear(n_nodes)
+        # ---- path 1b: the reduce-scatter-by-feature landing with a node -> slot table (HistEngine): rank r receives only its
+        # features of the two built nodes; twice, with the landing buffer cleaned in between as `derive` would leave it
+        E = F.HistEngine(pf, nbins, 2, 4, dev)
+        slot_of = torch.tensor([-1, 0, 1, -1], dtype=torch.int16, device=dev)
+        gb_, hb_ = float(gh_full[:, 0].abs().max()) + 1e-6, float(gh_full[:, 1].abs().max()) + 1e-6
+        f0, f1 = E.feat0, min(pf, E.feat0 + E.fpr)
+        for rep in range(2):
+            E.build(bins, nl, node, gh, slot_of, 2, gb_, hb_)
+            torch.cuda.synchronize()
+            got = E.landing.local[: 2 * E.cells].view(2, E.fpr, nbins, 2).clone()
+            if f1 > f0:
+                err = float((got[:, : f1 - f0] - ref[1:3, f0:f1]).abs().max() / ref.abs().max())
+                print(f"[{rank}] hist reduce-scatter landing rep={rep} features [{f0}, {f1}) rel err {err:.2e}", flush=True)
+                ok &= err < 1e-4
+            torch.cuda.synchronize(); E.landing.barrier()
+            E.landing.local.zero_()
+            torch.cuda.synchronize(); E.landing.barrier()
         gain, feat, b = F.best_splits(ref)
         hh = ref.double()
         cg, ch = hh[..., 0].cumsum(-1), hh[..., 1].cumsum(-1)
@@ -151,7 +168,13 @@ def main():
         from consensusml_b200.ops.metrics import auc
         gx, gy = synth(4000, 64, seed=3)
         glo, ghi = shard_bounds(4000, world, rank)
-        gb = GBMLarge(n_estimators=8, max_depth=3, nbins=64).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
+        from consensusml_b200.models.gbm_large import quantile_bin
+        gbins, gcuts = quantile_bin(gx[glo:ghi].to(dev), 64)
+        gb = GBMLarge(n_estimators=8, max_depth=3, nbins=64).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
+        gu = GBMLarge(n_estimators=8, max_depth=3, nbins=64, backend="unfused", sibling_subtraction=True).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
+        same_trees = all(torch.equal(s_.feat, t_.feat) and torch.equal(s_.thr[s_.feat >= 0], t_.thr[t_.feat >= 0]) for s_, t_ in zip(gb.trees, gu.trees))
+        print(f"[{rank}] gbm_large kernel level loop (reduce-scatter landing, sibling subtraction) == torch + NCCL path: {same_trees}", flush=True)
+        ok &= same_trees
         a = auc(gb.predict_proba(gx.to(dev)), gy.to(dev))
         sig = torch.stack([t.feat.float().sum() + t.thr.float().sum() for t in gb.trees]).sum().reshape(1)
         lo_s, hi_s = sig.clone(), sig.clone()
@@ -194,11 +217,10 @@ def main():
         print(f"[{rank}] EXPERIMENTAL staged grouped order equals plain order: {bool(torch.equal(got_g, got_p))}", flush=True)
         gx, gy = synth(4000, 64, seed=3)
         glo, ghi = shard_bounds(4000, world, rank)
-        a = GBMLarge(n_estimators=4, max_depth=3, nbins=64).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
+        a = GBMLarge(n_estimators=4, max_depth=3, nbins=64, sibling_subtraction=False).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
         b = GBMLarge(n_estimators=4, max_depth=3, nbins=64, sibling_subtraction=True).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
         same = all(torch.equal(s_.feat, t_.feat) and torch.equal(s_.thr, t_.thr) for s_, t_ in zip(a.trees, b.trees))
-        print(f"[{rank}] EXPERIMENTAL sibling subtraction on the fused histogram path: same trees {same}, samples histogrammed "
-              f"{a.samples_histogrammed_} -> {b.samples_histogrammed_}", flush=True)
+        print(f"[{rank}] EXPERIMENTAL sibling subtraction on the fused histogram path: same trees {same}", flush=True)
         xok &= same
         fu = LL.fit(xl, yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="fused", alpha=0.5)
         un = LL.fit(xl.bfloat16().float(), yl, 0.02, n_total=n, max_iter=60, tol=0.0, backend="unfused", step=fu.step, alpha=0.5)
