@@ -26,15 +26,21 @@ from ..ops import metrics as M
 
 _I, _LL, _F, _P = ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_void_p
 _native.register_signature("cml_svm_smo", [_I, _I, _P, _LL, _LL, _P, _LL, _P, _LL, _F, _I, _P, _P, _P, _P, _P])
+_native.register_signature("cml_svm_smo_warm", [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_void_p,
+                                                ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_float, ctypes.c_int, ctypes.c_void_p,
+                                                ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                ctypes.c_void_p])
 _native.register_signature("cml_svm_decision", [_P, _LL, _LL, _I, _I, _P, _P, _I, _P, _P])
 
 
 # ------------------------------------------------------------------------------------------------ solver
-def smo_numpy(K: np.ndarray, y: np.ndarray, cbound: np.ndarray, eps: float = 1e-3, max_iter: int = 1000000):
-    """libsvm's Solver (WSS2) in float64.  Returns (alpha, rho, iterations)."""
+def smo_numpy(K: np.ndarray, y: np.ndarray, cbound: np.ndarray, eps: float = 1e-3, max_iter: int = 1000000,
+              alpha0: Optional[np.ndarray] = None, g0: Optional[np.ndarray] = None, return_gradient: bool = False):
+    """libsvm's Solver (WSS2) in float64.  Returns (alpha, rho, iterations) [+ gradient].  ``alpha0`` / ``g0`` warm-start it
+    (sub-problem of a working set: ``g0`` is the global gradient Q alpha - e restricted to these variables)."""
     n = K.shape[0]
-    G_ = -np.ones(n)
-    a = np.zeros(n)
+    G_ = -np.ones(n) if g0 is None else np.array(g0, dtype=np.float64)
+    a = np.zeros(n) if alpha0 is None else np.array(alpha0, dtype=np.float64)
     kd = np.diag(K).copy()
     it = 0
     for it in range(max_iter):
@@ -105,6 +111,8 @@ def smo_numpy(K: np.ndarray, y: np.ndarray, cbound: np.ndarray, eps: float = 1e-
         ub = yg[ub_set].min() if ub_set.any() else np.inf
         lb = yg[lb_set].max() if lb_set.any() else -np.inf
         rho = 0.5 * (ub + lb)
+    if return_gradient:
+        return a, float(rho), it, G_
     return a, float(rho), it
 
 

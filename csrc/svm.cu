@@ -29,6 +29,11 @@ struct SmoArgs {
   float* rho;        // [B]
   int* iters;        // [B]
   float* obj;        // [B] dual objective
+  // warm start (all optional): the decomposition solver for large cohorts (models/svm_large.py) calls this kernel on the
+  // q x q sub-problem of a working set, starting from the current alpha and the current global gradient restricted to it
+  const float* alpha_init;   // [B][n] or null (zeros)
+  const float* g_init;       // [B][n] or null (-1: the gradient at alpha = 0)
+  float* g_out;              // [B][n] or null
 };
 
 struct ArgBest { float v; int i; };
@@ -71,7 +76,9 @@ __global__ void __launch_bounds__(kSmoThreads) smo_kernel(const SmoArgs A) {
   const float* ys = A.y + (size_t)b * A.y_stride;
   const float* cs = A.cbound + (size_t)b * A.c_stride;
   for (int t = threadIdx.x; t < n; t += blockDim.x) {
-    G[t] = -1.f; al[t] = 0.f; yy[t] = ys[t]; cb[t] = cs[t]; kd[t] = K[(size_t)t * A.ldk + t];
+    G[t] = A.g_init ? A.g_init[(size_t)b * n + t] : -1.f;
+    al[t] = A.alpha_init ? A.alpha_init[(size_t)b * n + t] : 0.f;
+    yy[t] = ys[t]; cb[t] = cs[t]; kd[t] = K[(size_t)t * A.ldk + t];
   }
   __syncthreads();
   int it = 0;
@@ -170,7 +177,10 @@ __global__ void __launch_bounds__(kSmoThreads) smo_kernel(const SmoArgs A) {
     A.iters[b] = it;
     A.obj[b] = 0.5f * objv;
   }
-  for (int t = threadIdx.x; t < n; t += blockDim.x) A.alpha[(size_t)b * n + t] = al[t];
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    A.alpha[(size_t)b * n + t] = al[t];
+    if (A.g_out) A.g_out[(size_t)b * n + t] = G[t];
+  }
 }
 
 // dec[b][m] = sum_t coef[b][t] K[m][t] - rho[b]   (coef = alpha * y);  one warp per (b, m)
@@ -202,7 +212,23 @@ int cml_svm_smo(int B, int n, const float* K, long long k_stride, long long ldk,
   const size_t smem = 5 * (size_t)n * sizeof(float);
   CML_REQUIRE(smem <= 200 * 1024, CML_E2BIG, "cml_svm_smo: n=%d samples exceed the single-CTA solver's limit (%d)", n, 200 * 1024 / 20);
   CML_CUDA(cudaFuncSetAttribute(smo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  SmoArgs A{K, k_stride, ldk, y, y_stride, cbound, c_stride, n, max_iter, eps, alpha, rho, iters, obj};
+  SmoArgs A{K, k_stride, ldk, y, y_stride, cbound, c_stride, n, max_iter, eps, alpha, rho, iters, obj, nullptr, nullptr, nullptr};
+  smo_kernel<<<B, kSmoThreads, smem, static_cast<cudaStream_t>(stream)>>>(A);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// Warm-started form: alpha_init / g_init give the starting point and its gradient G = Q alpha - e (restricted to these n
+// variables, the others held fixed), g_out receives the gradient at the returned alpha.  Used on working-set sub-problems.
+int cml_svm_smo_warm(int B, int n, const float* K, long long k_stride, long long ldk, const float* y, long long y_stride,
+                     const float* cbound, long long c_stride, float eps, int max_iter, const float* alpha_init, const float* g_init,
+                     float* alpha, float* g_out, float* rho, int* iters, float* obj, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(B > 0 && n > 1, CML_EINVAL, "cml_svm_smo_warm: empty problem");
+  const size_t smem = 5 * (size_t)n * sizeof(float);
+  CML_REQUIRE(smem <= 200 * 1024, CML_E2BIG, "cml_svm_smo_warm: n=%d variables exceed the single-CTA solver's limit (%d)", n, 200 * 1024 / 20);
+  CML_CUDA(cudaFuncSetAttribute(smo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SmoArgs A{K, k_stride, ldk, y, y_stride, cbound, c_stride, n, max_iter, eps, alpha, rho, iters, obj, alpha_init, g_init, g_out};
   smo_kernel<<<B, kSmoThreads, smem, static_cast<cudaStream_t>(stream)>>>(A);
   CML_LAUNCH_CHECK();
   return 0;

@@ -175,6 +175,11 @@ int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n
 int cml_svm_smo(int B, int n, const float* K, long long k_stride, long long ldk, const float* y, long long y_stride,
     const float* cbound, long long c_stride, float eps, int max_iter, float* alpha, float* rho, int* iters,
     float* obj, void* stream);
+/* Warm-started sub-problem solve for the working-set decomposition of large cohorts (models/svm_large.py): starts from
+ * alpha_init with gradient g_init (= Q alpha - e restricted to these variables), returns alpha and the gradient g_out. */
+int cml_svm_smo_warm(int B, int n, const float* K, long long k_stride, long long ldk, const float* y, long long y_stride,
+    const float* cbound, long long c_stride, float eps, int max_iter, const float* alpha_init, const float* g_init,
+    float* alpha, float* g_out, float* rho, int* iters, float* obj, void* stream);
 int cml_svm_decision(const float* K, long long k_stride, long long ldk, int m, int n, const float* coef, const float* rho,
     int B, float* dec, void* stream);
 

@@ -33,6 +33,10 @@ def main():
     if cpu:      # single-process answer first, while no process group exists (its all-reduces are then no-ops)
         step0 = 1.0 / LL.lipschitz_estimate(x, n)
         ref_single = LL._fit_unfused(x, y, 0.02, n, 150, 1e-5, None, None, step0, 10)
+        from consensusml_b200.models.svm_large import LargeSVC
+        sx = x[:800, :16]
+        sx = (sx - sx.mean(0)) / sx.std(0, unbiased=True)
+        svm_single = LargeSVC(kernel="radial", q=64).fit(sx, y[:800])
     rank, world, dev = D.init("gloo" if cpu else None)
     lo, hi = shard_bounds(n, world, rank)
     xl, yl = x[lo:hi].to(dev), y[lo:hi].to(dev)
@@ -73,6 +77,15 @@ def main():
         ok &= bool(torch.equal(lo_s, hi_s)) and bool(torch.equal(both[0], both[1]))
         if rank == 0:
             print("gloo sharded GBM: trees identical across ranks and with sibling subtraction:", ok)
+        # sample-sharded working-set SVM: the same dual optimum as one process (each rank nominates from its own shard)
+        slo, shi = shard_bounds(800, world, rank)
+        sv = LargeSVC(kernel="radial", q=64).fit(sx[slo:shi], y[slo:shi])
+        dec = sv.decision_function(sx[:40])
+        ok_svm = abs(sv.objective_ - svm_single.objective_) < 2e-3 * abs(svm_single.objective_) and sv.gap_ < 1e-3 and \
+            float((dec - svm_single.decision_function(sx[:40])).abs().max()) < 5e-2
+        if rank == 0:
+            print("gloo sharded working-set SVM: objective", sv.objective_, "single process", svm_single.objective_, "ok", ok_svm)
+        ok &= ok_svm
         fit = LL.fit(xl, yl, 0.02, n_total=n, max_iter=150, backend="unfused", step=step0)
         if rank == 0:
             err = float((fit.beta - ref_single.beta).abs().max())
@@ -182,6 +195,20 @@ def main():
             dist.all_reduce(lo_s, op=dist.ReduceOp.MIN)
             dist.all_reduce(hi_s, op=dist.ReduceOp.MAX)
         same = bool(lo_s.item() == hi_s.item())
+        # ---- large-n SVM: working-set decomposition whose kernel columns come from the all-gather -> tcgen05 Gram kernel
+        from consensusml_b200.models import svm as SV
+        from consensusml_b200.models.svm_large import LargeSVC
+        sn = 4096 // world * world
+        sx = x[:sn, :512]
+        sx = ((sx - sx.mean(0)) / sx.std(0, unbiased=True)).contiguous()
+        slo, shi = shard_bounds(sn, world, rank)
+        big = LargeSVC(kernel="radial", q=256).fit(sx[slo:shi].to(dev), y[:sn][slo:shi].to(dev))
+        small = SV.SVC(kernel="radial", scale=False).fit(sx.to(dev), y[:sn].to(dev))          # full-matrix single-CTA SMO
+        ypm = (2 * y[:sn] - 1).to(dev)
+        o_small = float(0.5 * (small.coef_ @ (SV.G.rbf_kernel(sx.to(dev), None, 1.0 / 512).float() @ small.coef_)) - small.coef_.abs().sum())
+        rel = abs(big.objective_ - o_small) / abs(o_small)
+        print(f"[{rank}] svm_large objective {big.objective_:.5f} vs full-matrix SMO {o_small:.5f} (rel {rel:.2e}) outer iters {big.outer_iters_} gap {big.gap_:.2e}", flush=True)
+        ok &= rel < 5e-3 and big.gap_ < 1e-3
         print(f"[{rank}] gbm_large auc {a:.4f} trees identical across ranks: {same} top genes {torch.argsort(-gb.importance_gain_)[:4].tolist()}", flush=True)
         ok &= a > 0.85 and same
     if not cpu and os.environ.get("CML_EXPERIMENTAL") == "1":

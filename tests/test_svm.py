@@ -81,3 +81,45 @@ def test_gpu_grid_search_runs(aml):
     out = S.grid_search(xtr, ytr, costs=[0.1, 1.0, 10.0], gammas=[1e-4, 1.0 / 1984, 5e-3], nfolds=5)
     assert out["cv_error"].shape == (3, 3)
     assert float(out["cv_error"].min()) < 0.25
+
+
+def _svm_blobs(n=420, p=12, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    y = (torch.rand(n, generator=g) < 0.5).float()
+    x = torch.randn(n, p, generator=g) + (y[:, None] - 0.5) * torch.tensor([1.6, -1.2, 0.8] + [0.0] * (p - 3))
+    return x, y
+
+
+@pytest.mark.parametrize("kernel", ["radial", "linear"])
+def test_large_svm_decomposition_reaches_the_smo_optimum_cpu(kernel):
+    """Working-set decomposition (models/svm_large.py) against the full-matrix SMO on a problem both can solve."""
+    from consensusml_b200.models.svm_large import LargeSVC
+    x, y = _svm_blobs()
+    xs = (x - x.mean(0)) / x.std(0, unbiased=True)
+    ref = S.SVC(kernel=kernel, scale=False).fit(xs, y)
+    big = LargeSVC(kernel=kernel, q=64, tol=1e-3).fit(xs, y)
+    ypm = 2 * y - 1
+    K = ref._kernel(xs).double()
+    def obj(a):
+        ay = a.double() * ypm.double()
+        return float(0.5 * ay @ K @ ay - a.double().sum())
+    o_ref, o_big = obj((ref.coef_ * ypm).abs()), obj(big.alpha_)
+    assert abs(o_big - o_ref) < 1e-3 * max(1.0, abs(o_ref)), (o_big, o_ref)
+    assert abs(big.objective_ - o_big) < 1e-2 * max(1.0, abs(o_big))                  # the solver's own bookkeeping agrees
+    assert big.gap_ < 1e-3 and 0 < big.outer_iters_ < 400
+    d_ref, d_big = ref.decision_function(xs[:50]), big.decision_function(xs[:50])
+    assert (d_ref - d_big).abs().max() < 5e-2 and ((d_ref > 0) == (d_big > 0)).float().mean() > 0.97
+    assert big.cache_hit_rate_ > 0.3                                                    # working sets overlap: the LRU cache pays
+
+
+def test_large_svm_subproblem_kernel_under_emulation():
+    """Same decomposition with the warm-started SMO kernel (csrc/svm.cu) solving the sub-problems on the emulator."""
+    from consensusml_b200 import _native
+    from consensusml_b200.models.svm_large import LargeSVC
+    x, y = _svm_blobs(n=160, p=6, seed=3)
+    xs = (x - x.mean(0)) / x.std(0, unbiased=True)
+    ref = LargeSVC(kernel="radial", q=32, tol=1e-3).fit(xs, y)
+    with _native.emulation(seed=2):
+        emu = LargeSVC(kernel="radial", q=32, tol=1e-3).fit(xs, y)
+    assert abs(emu.objective_ - ref.objective_) < 2e-3 * max(1.0, abs(ref.objective_))
+    assert emu.gap_ < 1e-3 and abs(emu.rho_ - ref.rho_) < 2e-2
