@@ -243,6 +243,7 @@ class LargeSVC:
         if cache is not None and cache.hits + cache.misses:
             self.cache_hit_rate_ = cache.hits / (cache.hits + cache.misses)
         self._x, self._y = x_local, y
+        self._sharded = world > 1               # decision_function is a collective only for a model fitted over several ranks
         self._gamma = gamma
         return self
 
@@ -262,6 +263,6 @@ class LargeSVC:
             dec = Kt.to(coef.dtype) @ coef[sv]
         else:
             dec = torch.zeros(x_new.shape[0], device=x_new.device)
-        if dist.is_initialized() and dist.get_world_size() > 1:
+        if self._sharded:
             dist.all_reduce(dec)
         return dec - self.rho_
