@@ -151,6 +151,22 @@ __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// Wait until a copier CTA of this grid has flagged a staged tile.  The copiers and the GEMM CTAs are co-resident by
+// construction (grid = SM count), but an SM held by another stream's kernel, or a copier that faulted on a bad peer
+// pointer, would otherwise leave this loop spinning for ever and the device unusable: back off after a short spin and
+// trap after ~20 s (at ~2 GHz), which surfaces as a CUDA error on the host - the same policy as wait_signals_kernel.
+constexpr long long kFlagTimeoutCycles = 40000000000LL;
+__device__ __forceinline__ void wait_tile_flag(const unsigned* flag, unsigned epoch) {
+  unsigned spins = 0;
+  long long t0 = 0;
+  while (ld_acquire_gpu(flag) != epoch) {
+    if (++spins == 64u) t0 = clock64();
+    if (spins > 64u) {
+      __nanosleep(128);
+      if (clock64() - t0 > kFlagTimeoutCycles) __trap();
+    }
+  }
+}
 
 // Copier CTA: streams source blocks (ring order starting at this rank's own block) into the staging buffer through a
 // ring of shared-memory slots: bulk load peer -> smem (mbarrier), bulk store smem -> local global (bulk group).
@@ -410,8 +426,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
         const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
         if (staged) {
           const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
-          while (ld_acquire_gpu(flag) != P.epoch) {
-          }
+          wait_tile_flag(flag, P.epoch);
           asm volatile("fence.proxy.async;" ::: "memory");          // staged bytes were written through the async proxy
         }
         const int brow = staged ? src * P.rows_per_src + n_loc * BN : n_loc * BN;
@@ -581,8 +596,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
         const int src = staged ? (P.rank + si) % P.n_src : si;      // ring order: own block first, then the peers
         if (staged) {
           const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
-          while (ld_acquire_gpu(flag) != P.epoch) {
-          }
+          wait_tile_flag(flag, P.epoch);
           asm volatile("fence.proxy.async;" ::: "memory");
         }
         const int arow = m_blk * BM2 + (int)cta * 128;
@@ -800,6 +814,11 @@ int cml_gemm_tn_bf16_staged(int M, int N, int K, const void* a, long long lda, c
   CML_REQUIRE(epilogue == EPI_SCALE || (norm_a && peer_norm_ptrs && stage_norm), CML_EINVAL, "cml_gemm_tn_bf16_staged: distance epilogues need row norms");
   CML_REQUIRE(stage && flags && ldb % 8 == 0 && ldb >= K, CML_EINVAL, "cml_gemm_tn_bf16_staged: staging buffer / pitch invalid");
   CML_REQUIRE(n_copiers >= 1 && n_copiers < sm_count() / 2, CML_EINVAL, "cml_gemm_tn_bf16_staged: n_copiers=%d out of range", n_copiers);
+  CML_REQUIRE((long long)n_src * rows_per_src >= N, CML_EINVAL, "cml_gemm_tn_bf16_staged: %d sources x %d rows do not cover N=%d", n_src,
+              rows_per_src, N);
+  for (int s = 0; s < n_src; ++s)
+    CML_REQUIRE(peer_ptrs[s] && (reinterpret_cast<uintptr_t>(peer_ptrs[s]) & 15) == 0, CML_EINVAL,
+                "cml_gemm_tn_bf16_staged: source %d is null or not 16-byte aligned (bulk copies need that)", s);
   GemmParams P;
   memset(&P, 0, sizeof(P));
   const int BN = 256;
