@@ -65,7 +65,8 @@ def tmm_ref_column(counts: np.ndarray, lib_size: np.ndarray) -> int:
     return int(np.argmin(np.abs(f75 - f75.mean())))
 
 
-def tmm_factors(counts: np.ndarray, lib_size: Optional[np.ndarray] = None, ref_column: Optional[int] = None) -> np.ndarray:
+def tmm_factors(counts: np.ndarray, lib_size: Optional[np.ndarray] = None, ref_column: Optional[int] = None,
+                normalize: bool = True) -> np.ndarray:
     """edgeR ``calcNormFactors(method="TMM")``: trimmed mean of M-values against a reference sample,
     precision weighted, scaled to geometric mean 1."""
     counts = np.asarray(counts, dtype=np.float64)
@@ -73,14 +74,15 @@ def tmm_factors(counts: np.ndarray, lib_size: Optional[np.ndarray] = None, ref_c
     x = counts[(counts > 0).any(1)]
     ref = tmm_ref_column(x, lib) if ref_column is None else ref_column
     f = np.array([_tmm_one(x[:, i], x[:, ref], lib[i], lib[ref]) for i in range(x.shape[1])])
-    return f / np.exp(np.mean(np.log(f)))
+    return f / np.exp(np.mean(np.log(f))) if normalize else f
 
 
 def log_cpm(counts: np.ndarray, lib_size: np.ndarray, norm_factors: Optional[np.ndarray] = None,
-            prior_count: float = 1.0) -> np.ndarray:
-    """edgeR ``cpm(dge, log=TRUE, prior.count=p)`` - the prior is scaled by relative library size."""
+            prior_count: float = 1.0, mean_lib: Optional[float] = None) -> np.ndarray:
+    """edgeR ``cpm(dge, log=TRUE, prior.count=p)`` - the prior is scaled by relative library size (``mean_lib``: the
+    mean effective library size when ``counts`` holds only a shard of the samples)."""
     lib = lib_size * (1.0 if norm_factors is None else norm_factors)
-    pcs = lib / lib.mean() * prior_count
+    pcs = lib / (lib.mean() if mean_lib is None else mean_lib) * prior_count
     return np.log2((counts + pcs[None, :]) / (lib + 2 * pcs)[None, :] * 1e6)
 
 

@@ -118,36 +118,57 @@ def voom_de(counts: torch.Tensor, group, *, min_frac: float = 0.05, p_value: flo
         return DEResult(torch.from_numpy(r["keep"]), np.flatnonzero(r["keep"]), torch.from_numpy(r["lib_size"]),
                         torch.from_numpy(r["norm_factors"]), r["coef"], r["fit"].amean, eb.t, eb.p_value, adj, eb.lods,
                         eb.s2_prior, eb.df_prior, eb.var_prior, r["deg_index"], r["trend"])
-    dev = counts.device
     counts = counts.to(torch.int32).contiguous()
     G_all, S = counts.shape
     lib = N.lib_sizes(counts)
     keep = N.cpm_filter(counts, 1.0, min_frac * S, strict=True, lib=lib)
     rows = torch.nonzero(keep).flatten()
     sub = counts[rows].contiguous()
-    G = sub.shape[0]
     nf = N.tmm_factors(sub, lib)
     lib_eff = (lib * nf).contiguous()
     X = _design_two_group(group) if design is None else np.asarray(design, np.float64)
     cvec = np.array([1.0, -1.0]) if contrast is None else np.asarray(contrast, np.float64)
+    r = voom_core(sub, lib_eff, X, cvec, span=span, proportion=proportion, stdev_coef_lim=stdev_coef_lim, p_value=p_value, lfc=lfc)
+    c = lambda v: v.cpu().numpy()
+    return DEResult(keep, c(rows), lib, nf, c(r["coef_c"]), c(r["amean"]), c(r["t"]), c(r["p"]), c(r["adj"]), c(r["lods"]), r["s20"], r["df0"],
+                    r["var_prior"], c(r["idx"]), tuple(c(v) for v in r["trend"]))
+
+
+def voom_core(sub: torch.Tensor, lib_eff: torch.Tensor, X: np.ndarray, cvec: np.ndarray, *, span: float = 0.5, proportion: float = 0.01,
+              stdev_coef_lim=(0.1, 4.0), p_value: float = 0.05, lfc: float = 1.0, gather=None) -> dict:
+    """voom weights -> weighted least squares -> contrast -> eBayes -> BH on the kernel path, for the gene rows in ``sub``
+    ([G_local, S] int32 counts of ALL samples, already filtered).
+
+    ``gather`` makes it gene-sharded (stats/sharded.py): every rank passes its block of genes and a function that
+    concatenates a per-gene vector over the ranks in gene order.  The per-gene kernels (voom_ols, voom_wls, ebayes) then run
+    on the local block only; the few steps that need every gene - the LOWESS mean-variance trend, the eBayes hyper-parameters,
+    the top-|t| mixture fit and the BH adjustment - run on the gathered G-length vectors, identically on every rank.  The
+    returned vectors are full length."""
+    dev = sub.device
+    ag = gather if gather is not None else (lambda v: v)
+    Gl, S = sub.shape
     k = X.shape[1]
     hat = np.linalg.solve(X.T @ X, X.T)
     Xd = torch.as_tensor(X, device=dev).contiguous()
     Hd = torch.as_tensor(hat, device=dev).contiguous()
     cd = torch.as_tensor(cvec, device=dev).contiguous()
     f64 = dict(dtype=torch.float64, device=dev)
-    coef_ols = torch.empty(G, k, **f64)
-    sig_ols = torch.empty(G, **f64)
-    amean = torch.empty(G, **f64)
+    coef_ols = torch.empty(Gl, k, **f64)
+    sig_ols = torch.empty(Gl, **f64)
+    amean_l = torch.empty(Gl, **f64)
     lb = _native.cuda()
     P = _native.ptr
     st = _native.stream_ptr()
-    _native.check(lb.cml_voom_ols(P(sub), G, S, k, P(lib_eff), P(Xd), P(Hd), P(coef_ols), P(sig_ols), P(amean), None, st),
-                  "cml_voom_ols")
-    # mean-variance trend
+    lib_eff = lib_eff.contiguous()
+    if Gl:
+        _native.check(lb.cml_voom_ols(P(sub), Gl, S, k, P(lib_eff), P(Xd), P(Hd), P(coef_ols), P(sig_ols), P(amean_l), None, st),
+                      "cml_voom_ols")
+    # mean-variance trend (needs the points of every gene)
+    amean = ag(amean_l)
+    G = amean.numel()
     sx = amean + torch.log2(lib_eff + 1.0).mean() - np.log2(1e6)
-    sy = sig_ols.sqrt()
-    nz = sub.sum(1) > 0
+    sy = ag(sig_ols.sqrt())
+    nz = ag((sub.sum(1) > 0).to(torch.uint8)).bool()
     sxk, syk = sx[nz], sy[nz]
     order = torch.argsort(sxk, stable=True)
     lx, ly_in = sxk[order].contiguous(), syk[order].contiguous()
@@ -155,14 +176,16 @@ def voom_de(counts: torch.Tensor, group, *, min_frac: float = 0.05, p_value: flo
     ux, inv = torch.unique_consecutive(lx, return_inverse=True)
     uy = torch.zeros_like(ux).index_add_(0, inv, ly) / torch.zeros_like(ux).index_add_(0, inv, torch.ones_like(ly))
     ux, uy = ux.contiguous(), uy.contiguous()
-    coef = torch.empty(G, k, **f64)
-    su = torch.empty(G, k, **f64)
-    sigma = torch.empty(G, **f64)
-    coef_c = torch.empty(G, **f64)
-    su_c = torch.empty(G, **f64)
-    _native.check(lb.cml_voom_wls(P(sub), G, S, k, P(lib_eff), P(Xd), P(coef_ols), P(ux), P(uy), ux.numel(), P(cd),
-                                  P(coef), P(su), P(sigma), P(coef_c), P(su_c), None, st), "cml_voom_wls")
+    coef = torch.empty(Gl, k, **f64)
+    su = torch.empty(Gl, k, **f64)
+    sigma_l = torch.empty(Gl, **f64)
+    coef_c_l = torch.empty(Gl, **f64)
+    su_c_l = torch.empty(Gl, **f64)
+    if Gl:
+        _native.check(lb.cml_voom_wls(P(sub), Gl, S, k, P(lib_eff), P(Xd), P(coef_ols), P(ux), P(uy), ux.numel(), P(cd),
+                                      P(coef), P(su), P(sigma_l), P(coef_c_l), P(su_c_l), None, st), "cml_voom_wls")
     # ---- empirical Bayes hyper-parameters: reductions on device, scalar special functions on host
+    sigma, coef_c, su_c = ag(sigma_l), ag(coef_c_l), ag(su_c_l)
     df_res = float(S - k)
     s2 = sigma * sigma
     med = float(torch.median(s2))
@@ -186,13 +209,15 @@ def voom_de(counts: torch.Tensor, group, *, min_frac: float = 0.05, p_value: flo
     var_prior = _tmixture_top(top.values.cpu().numpy(), su_c[top.indices].cpu().numpy(), df_total, proportion, v0_lim, G)
     if not np.isfinite(var_prior):
         var_prior = 1.0 / s20
-    t = torch.empty(G, **f64)
-    p = torch.empty(G, **f64)
-    lods = torch.empty(G, **f64)
-    s2p = torch.empty(G, **f64)
-    dft = torch.empty(G, **f64)
-    _native.check(lb.cml_ebayes(P(coef_c), P(su_c), P(sigma), None, df_res, G, s20, df0, df_cap, var_prior, proportion,
-                                P(t), P(p), P(lods), P(s2p), P(dft), st), "cml_ebayes")
+    t_l = torch.empty(Gl, **f64)
+    p_l = torch.empty(Gl, **f64)
+    lods_l = torch.empty(Gl, **f64)
+    s2p = torch.empty(Gl, **f64)
+    dft = torch.empty(Gl, **f64)
+    if Gl:
+        _native.check(lb.cml_ebayes(P(coef_c_l), P(su_c_l), P(sigma_l), None, df_res, Gl, s20, df0, df_cap, var_prior, proportion,
+                                    P(t_l), P(p_l), P(lods_l), P(s2p), P(dft), st), "cml_ebayes")
+    t, p, lods = ag(t_l), ag(p_l), ag(lods_l)
     # ---- BH + topTable (device sort + cummin)
     ordp = torch.argsort(p, descending=True, stable=True)
     ranks = G - torch.arange(G, device=dev, dtype=torch.float64)
@@ -202,9 +227,8 @@ def voom_de(counts: torch.Tensor, group, *, min_frac: float = 0.05, p_value: flo
     sig = (adj < p_value) & (coef_c.abs() > lfc)
     idx = torch.nonzero(sig).flatten()
     idx = idx[torch.argsort(p[idx], stable=True)]
-    c = lambda v: v.cpu().numpy()
-    return DEResult(keep, c(rows), lib, nf, c(coef_c), c(amean), c(t), c(p), c(adj), c(lods), s20, df0, float(var_prior),
-                    c(idx), (c(sx), c(sy), c(ux), c(uy)))
+    return {"coef_c": coef_c, "amean": amean, "t": t, "p": p, "adj": adj, "lods": lods, "s20": s20, "df0": df0, "var_prior": float(var_prior),
+            "idx": idx, "trend": (sx, sy, ux, uy)}
 
 
 def _tmixture_top(t_top: np.ndarray, su_top: np.ndarray, df: float, proportion: float, v0_lim, ngenes: int) -> float:

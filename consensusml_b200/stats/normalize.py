@@ -67,13 +67,38 @@ def cpm_filter(counts: torch.Tensor, min_cpm: float = 1.0, min_samples: float = 
     return n_ok > min_samples if strict else n_ok >= min_samples
 
 
+def upper_quartile_factors(counts: torch.Tensor, lib: torch.Tensor, all_rows: bool = False) -> torch.Tensor:
+    """edgeR's ``f75`` per sample: the 75 % quantile of count / library size over the genes with a count anywhere (the
+    statistic TMM picks its reference sample with).  float64 [S].  ``all_rows``: take every row (a sample shard cannot tell
+    from its own columns whether a gene has counts elsewhere; rows that passed the CPM filter all do)."""
+    counts = _as_counts(counts)
+    lib = lib.double().contiguous()
+    G, S = counts.shape
+    if not _native.on_device(counts):
+        c = counts.numpy().astype(np.float64)
+        if not all_rows:
+            c = c[c.sum(1) > 0]
+        return torch.from_numpy(np.quantile(c / lib.numpy()[None, :], 0.75, axis=0))
+    lb = _native.cuda()
+    P = _native.ptr
+    mask = torch.empty(G, dtype=torch.uint8, device=counts.device)
+    if all_rows:
+        mask.fill_(1)
+    else:
+        _native.check(lb.cml_nonzero_rows(P(counts), G, S, P(mask), _native.stream_ptr()), "cml_nonzero_rows")
+    f75 = torch.empty(S, dtype=torch.float64, device=counts.device)
+    _native.check(lb.cml_quantile75(P(counts), G, S, P(mask), int(mask.sum().item()), P(lib), P(f75), _native.stream_ptr()), "cml_quantile75")
+    return f75
+
+
 def tmm_factors(counts: torch.Tensor, lib: Optional[torch.Tensor] = None, *, logratio_trim: float = 0.3,
-                sum_trim: float = 0.05, a_cutoff: float = -1e10, ref_column: Optional[int] = None) -> torch.Tensor:
-    """edgeR ``calcNormFactors(method="TMM")`` on a (filtered) count matrix; float64 [S] with geometric mean 1."""
+                sum_trim: float = 0.05, a_cutoff: float = -1e10, ref_column: Optional[int] = None, normalize: bool = True) -> torch.Tensor:
+    """edgeR ``calcNormFactors(method="TMM")`` on a (filtered) count matrix; float64 [S] with geometric mean 1
+    (``normalize=False`` returns the raw factors - the sample-sharded path normalises over all ranks' samples)."""
     counts = _as_counts(counts)
     lib = lib_sizes(counts) if lib is None else lib.double()
     if not _native.on_device(counts):
-        return torch.from_numpy(O.tmm_factors(counts.numpy().astype(np.float64), lib.numpy(), ref_column))
+        return torch.from_numpy(O.tmm_factors(counts.numpy().astype(np.float64), lib.numpy(), ref_column, normalize=normalize))
     lib = lib.contiguous()
     G, S = counts.shape
     lb = _native.cuda()
@@ -92,20 +117,22 @@ def tmm_factors(counts: torch.Tensor, lib: Optional[torch.Tensor] = None, *, log
     f = torch.empty(S, dtype=torch.float64, device=counts.device)
     _native.check(lb.cml_tmm_factors(P(counts), G, S, P(mask), P(lib), int(ref_column), logratio_trim, sum_trim,
                                      a_cutoff, P(f), _native.stream_ptr()), "cml_tmm_factors")
-    return f / torch.exp(torch.log(f).mean())
+    return f / torch.exp(torch.log(f).mean()) if normalize else f
 
 
 def log_cpm(counts: torch.Tensor, lib: torch.Tensor, norm_factors: Optional[torch.Tensor] = None,
-            prior_count: float = 1.0, rows: Optional[torch.Tensor] = None, sample_major: bool = False) -> torch.Tensor:
+            prior_count: float = 1.0, rows: Optional[torch.Tensor] = None, sample_major: bool = False,
+            mean_eff: Optional[float] = None) -> torch.Tensor:
     """``cpm(dge, log=TRUE, prior.count=p)`` -> fp32.  ``rows`` selects genes (int indices);
-    ``sample_major=True`` writes the transposed samples x genes model matrix directly."""
+    ``sample_major=True`` writes the transposed samples x genes model matrix directly.  ``mean_eff`` overrides the mean
+    effective library size that scales the prior count (a sample shard passes the mean over ALL samples)."""
     counts = _as_counts(counts)
     eff = lib.double() * (1.0 if norm_factors is None else norm_factors.double())
     if not _native.on_device(counts):
         c = counts.numpy().astype(np.float64)
         if rows is not None:
             c = c[rows.numpy()]
-        out = torch.from_numpy(O.log_cpm(c, eff.numpy(), None, prior_count).astype(np.float32))
+        out = torch.from_numpy(O.log_cpm(c, eff.numpy(), None, prior_count, mean_lib=mean_eff).astype(np.float32))
         return out.t().contiguous() if sample_major else out
     G, S = counts.shape
     n_rows = G if rows is None else int(rows.numel())
@@ -119,7 +146,8 @@ def log_cpm(counts: torch.Tensor, lib: torch.Tensor, norm_factors: Optional[torc
     else:
         out = torch.empty(n_rows, S, dtype=torch.float32, device=counts.device)
     rc = _native.cuda().cml_logcpm(_native.ptr(counts), G, S, _native.ptr(rows_t), n_rows, _native.ptr(eff),
-                                   float(prior_count), float(eff.mean()), _native.ptr(out), _native.ptr(out_t), ld_t,
+                                   float(prior_count), float(eff.mean()) if mean_eff is None else float(mean_eff), _native.ptr(out),
+                                   _native.ptr(out_t), ld_t,
                                    _native.stream_ptr())
     _native.check(rc, "cml_logcpm")
     return out_t if sample_major else out

@@ -109,3 +109,15 @@ def test_gpu_student_t_pvalues():
         got = outs[1].cpu().numpy()
         ok = ref > 1e-280
         assert np.abs(np.log(got[ok]) - np.log(ref[ok])).max() < 1e-6
+
+
+def test_sample_sharded_normalisation_and_gene_sharded_voom_two_ranks():
+    """stats/sharded.py under gloo with the kernels on the host execution model (tests/dist_stats_check.py)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29552", os.path.join(root, "tests", "dist_stats_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env={**os.environ, "CML_DIST_TIMEOUT_S": "120"})
+    assert r.returncode == 0 and "STATS DIST OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
