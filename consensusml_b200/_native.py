@@ -168,13 +168,24 @@ def check(code: int, what: str) -> None:
         raise NativeError(f"{what} failed with code {code}: {msg}")
 
 
+class _KeepAlivePtr(ctypes.c_void_p):
+    """A pointer argument that owns a reference to the tensor it points into.  ``ptr(expr)`` is often called on a temporary
+    (``ptr(x.float().contiguous())``); without the reference the temporary dies as soon as ``ptr`` returns, its memory goes
+    back to the allocator, and the NEXT temporary of the same argument list can be handed the same block - before the launch
+    that was supposed to read it is even enqueued.  Holding the tensor until the foreign call returns makes the free
+    stream-ordered after the launch, which is what the caching allocator needs."""
+    _keep = None
+
+
 def ptr(t) -> ctypes.c_void_p:
-    """Device/host pointer of a contiguous torch tensor (``None`` -> NULL)."""
+    """Device/host pointer of a contiguous torch tensor (``None`` -> NULL).  The returned object keeps ``t`` alive."""
     if t is None:
         return ctypes.c_void_p(0)
     if not t.is_contiguous():
         raise ValueError("native kernels need contiguous tensors")
-    return ctypes.c_void_p(t.data_ptr())
+    p = _KeepAlivePtr(t.data_ptr())
+    p._keep = t
+    return p
 
 
 def stream_ptr() -> ctypes.c_void_p:
@@ -189,4 +200,6 @@ def np_ptr(a) -> ctypes.c_void_p:
         return ctypes.c_void_p(0)
     if not a.flags["C_CONTIGUOUS"]:
         raise ValueError("native host routines need C-contiguous arrays")
-    return ctypes.c_void_p(a.ctypes.data)
+    p = _KeepAlivePtr(a.ctypes.data)
+    p._keep = a
+    return p

@@ -6,8 +6,9 @@ number = 5, repeats = 10))`` and ``selectedGenes`` (VikasP/AML.R:167-291), on ra
 genes with a +1 pseudo-count (:157-171).
 
 Everything is expressed as batched tensor reductions over genes x samples (the per-class sums are one matmul with
-the class-indicator matrix), so it runs unchanged on CPU or GPU tensors; gene-sharded multi-GPU runs only need the
-per-sample scores all-reduced.  Implemented from the published methods: DESeq median-of-ratios (Anders & Huber 2010),
+the class-indicator matrix); on the kernel path the two reductions that are not a GEMM - the median-of-ratios size
+factors and the Poisson-LDA scores - are ``size_factors_kernel`` / ``plda_scores_kernel`` (csrc/discriminant.cu).
+Gene-sharded multi-GPU runs only need the per-sample scores all-reduced.  Implemented from the published methods: DESeq median-of-ratios (Anders & Huber 2010),
 Poisson LDA (Witten 2011), NBLDA (Dong et al. 2016), nearest shrunken centroids (Tibshirani et al. 2002), voom-based
 NSC / DLDA (Zararsiz et al. 2017)."""
 from __future__ import annotations
@@ -15,14 +16,30 @@ from __future__ import annotations
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence
 
+import ctypes
+
 import numpy as np
 import torch
+
+from .. import _native
+
+_I, _P = ctypes.c_int, ctypes.c_void_p
+_native.register_signature("cml_deseq_size_factors", [_P, _I, _I, _P, _P, _P])
+_native.register_signature("cml_plda_scores", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P])
 
 
 # ------------------------------------------------------------------------------------------------ normalisation
 def deseq_size_factors(counts: torch.Tensor) -> torch.Tensor:
     """Median-of-ratios size factors; ``counts`` is genes x samples.  Genes with a zero in any sample are skipped."""
     c = counts.double()
+    if _native.on_device(c) and c.shape[0] <= 25600:
+        c = c.contiguous()
+        G, S = c.shape
+        scratch = torch.empty(G, dtype=torch.float64, device=c.device)
+        sf = torch.empty(S, dtype=torch.float64, device=c.device)
+        rc = _native.cuda().cml_deseq_size_factors(_native.ptr(c), G, S, _native.ptr(scratch), _native.ptr(sf), _native.stream_ptr())
+        _native.check(rc, "cml_deseq_size_factors")
+        return sf
     ok = (c > 0).all(1)
     logc = torch.log(c[ok])
     loggeo = logc.mean(1, keepdim=True)
@@ -117,6 +134,16 @@ class PoissonLDA:
     def scores(self, counts: torch.Tensor) -> torch.Tensor:
         x = self._tx(counts)
         s = x.sum(0) / self.g_.sum()
+        if _native.on_device(x):
+            G, n = x.shape
+            k = self.d_.shape[1]
+            out = torch.empty(1, n, k, dtype=torch.float64, device=x.device)
+            P = _native.ptr
+            rc = _native.cuda().cml_plda_scores(P(x.contiguous()), G, n, k, 1, P(torch.log(self.d_).contiguous()),
+                                                P((self.g_[:, None] * self.d_).contiguous()), P(s.contiguous()),
+                                                P(torch.log(self.prior_).reshape(1, k).contiguous()), P(out), _native.stream_ptr())
+            _native.check(rc, "cml_plda_scores")
+            return out[0]
         return x.t() @ torch.log(self.d_) - s[:, None] * (self.g_[:, None] * self.d_).sum(0)[None, :] + torch.log(self.prior_)[None, :]
 
     def predict(self, counts: torch.Tensor) -> torch.Tensor:

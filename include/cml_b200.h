@@ -226,6 +226,12 @@ int cml_mlp_adam(float* const* state, const float* gw1, long long ldg, const flo
                  void* w1_bf16, long long ldw, const int* cfg_of, const float* lr, const float* wd, int n, int H, int G, int p,
                  float beta1, float beta2, float eps, int step, void* stream);
 
+/* ---- K14: count-based discriminants (csrc/discriminant.cu) - MLSeq classify() zoo, VikasP/AML.R:167-264.
+ * DESeq median-of-ratios size factors of a genes x samples matrix; Poisson-LDA scores out [B][n][k] for B fitted models. */
+int cml_deseq_size_factors(const double* counts, int G, int S, double* loggeo_scratch, double* sf, void* stream);
+int cml_plda_scores(const double* x, int G, int n, int k, int B, const double* logd, const double* gd, const double* s,
+                    const double* logprior, double* out, void* stream);
+
 /* ---- K18: batched evaluation metrics (csrc/metrics.cu) - confusion / TPR / TNR (cml_targetaml_seanalysis.Rmd:105-108,815-848),
  * log-loss (scripts/model_comp.py:24-27), ROC area (ROCR, :176-177).  scores [B][ld]; truth [n] (stride 0) or [B][n] floats;
  * out [B][8] float64: auc, logloss, tn, fn, fp, tp, n_pos, n_neg.  n <= 8192 per vector. */

@@ -460,3 +460,21 @@ def test_large_gbm_kernel_level_loop_builds_the_same_trees_as_the_torch_path():
             assert (a.value - b.value).abs().max() < 2e-4
         assert torch.allclose(ref.importance_gain_, got.importance_gain_, rtol=2e-3, atol=1e-3)
     assert _auc_torch(got.predict_proba(x), y) > 0.8
+
+
+def test_size_factor_and_plda_score_kernels():
+    from consensusml_b200.models import discriminant as D
+    c, y = nb_counts(120, 31, seed=8, n_de=30)
+    c = torch.from_numpy(c) + 1
+    c[5, 3] = 0                                           # a gene with a zero is skipped by the median of ratios
+    yt = torch.from_numpy(y).long()
+    sf_ref = D.deseq_size_factors(c)
+    m_ref = D.PoissonLDA(rho=2.0).fit(c, yt)
+    m2_ref = D.PoissonLDA(power=True).fit(c, yt)
+    with _native.emulation(seed=3):
+        sf = D.deseq_size_factors(c)
+        sc = m_ref.scores(c)
+        sc2 = m2_ref.scores(c[:, :7].contiguous())
+    assert torch.allclose(sf, sf_ref, rtol=1e-12, atol=1e-12)
+    assert torch.allclose(sc, m_ref.scores(c), rtol=1e-10, atol=1e-8)
+    assert torch.allclose(sc2, m2_ref.scores(c[:, :7].contiguous()), rtol=1e-10, atol=1e-8)
