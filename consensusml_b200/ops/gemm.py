@@ -116,10 +116,15 @@ def gemm_tn_staged(a_bf16: torch.Tensor, peer_ptrs: Sequence[int], n_total: int,
     return c[:, :n_total]
 
 
+# Below one 64-wide K block the TMA -> tcgen05 pipeline has nothing to pipeline (and no such shape is part of the validated
+# set, tests/test_gemm_gpu.py): feature dimensions that small go through plain torch on the same device.
+MIN_K = 64
+
+
 def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optional[float] = None) -> torch.Tensor:
     """K(i, j) = exp(-gamma |x_i - z_j|^2); gamma defaults to 1/p as in e1071."""
     gamma = 1.0 / x.shape[1] if gamma is None else gamma
-    if not x.is_cuda:
+    if not x.is_cuda or x.shape[1] < MIN_K:
         zz = x if z is None else z
         d2 = torch.cdist(x.double(), zz.double()) ** 2
         return torch.exp(-gamma * d2).to(x.dtype)
@@ -133,7 +138,7 @@ def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optiona
 
 
 def linear_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, scale: float = 1.0) -> torch.Tensor:
-    if not x.is_cuda:
+    if not x.is_cuda or x.shape[1] < MIN_K:
         zz = x if z is None else z
         return (scale * (x.double() @ zz.double().t())).to(x.dtype)
     xa, _ = to_bf16_rows(x.float())
@@ -142,7 +147,7 @@ def linear_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, scale: floa
 
 
 def sq_dists(x: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
-    if not x.is_cuda:
+    if not x.is_cuda or x.shape[1] < MIN_K:
         return (torch.cdist(x.double(), z.double()) ** 2).to(x.dtype)
     xa, na = to_bf16_rows(x.float())
     xb, nb = to_bf16_rows(z.float())

@@ -283,198 +283,10 @@ def test_replicate_weight_kernel_properties():
         assert ((kf[5 * r: 5 * r + 5] == 0).sum(0) == 1).all()
 
 
-def test_column_moments_topk_and_quantile_binning_kernels():
-    from consensusml_b200.models import trees as TR
-    from consensusml_b200.ops import colvar as CV
-    g = torch.Generator().manual_seed(12)
-    x = torch.randn(300, 70, generator=g) * torch.linspace(0.2, 3.0, 70)[None, :] + 5.0
-    x[:, 9] = x[:, 4]                                     # equal variances: tie broken by index
-    x[:, 20] = 1.25                                       # constant column
-    mask = torch.rand(300, generator=g) < 0.6
-    with _native.emulation(seed=3):
-        cnt, mean, m2 = CV.column_moments(x, mask)
-        idx_hi = CV.variance_topk(x, 11, largest=True, row_mask=mask)
-        idx_lo = CV.variance_topk(x, 7, largest=False)
-        tk = CV.topk(torch.tensor([3.0, 1.0, 3.0, 2.0, 3.0, -1.0]), 2)
-    xs = x[mask].double()
-    assert cnt == int(mask.sum())
-    assert torch.allclose(mean, xs.mean(0), rtol=1e-12, atol=1e-12)
-    assert torch.allclose(m2, ((xs - xs.mean(0)) ** 2).sum(0), rtol=1e-10, atol=1e-10)
-    var = xs.var(0, unbiased=True)
-    assert idx_hi.tolist() == torch.argsort(var.float(), descending=True, stable=True)[:11].tolist()
-    assert idx_lo.tolist() == torch.argsort(x.double().var(0, unbiased=True).float(), descending=False, stable=True)[:7].tolist()
-    assert tk.tolist() == [0, 2]
-    # quantile binning (n > 256): the kernel path and the host restatement produce the same edges and bins
-    xq = torch.randn(700, 9, generator=g)
-    xq[:, 2] = torch.round(xq[:, 2] * 2) / 2              # heavy ties -> fewer than max_bin distinct quantiles
-    bc, binsc = TR.Binner.fit(xq, max_bin=64)
-    with _native.emulation(seed=1):
-        bd, binsd = TR.Binner.fit(xq, max_bin=64)
-    assert torch.equal(bd.n_edges, bc.n_edges)
-    for f in range(9):
-        k = int(bc.n_edges[f])
-        assert torch.equal(bd.edges[f, :k], bc.edges[f, :k]), f
-    assert torch.equal(binsd[:, :700], binsc[:, :700])
+# ---- kernels added in round 2: the backend-agnostic cases of tests/kernel_cases.py on the host execution model
+import kernel_cases as KC
 
 
-def test_kmeans_sweep_kernel_reaches_the_same_minima_as_the_host_path():
-    from consensusml_b200.models import kmeans as KM
-    g = torch.Generator().manual_seed(4)
-    centres = torch.tensor([[0.0, 0.0, 0.0], [4.0, 0.0, 1.0], [0.0, 5.0, -1.0], [5.0, 5.0, 3.0]])
-    x = torch.cat([c + 0.4 * torch.randn(30, 3, generator=g) for c in centres])
-    with _native.emulation(seed=2):
-        dev = KM.kmeans_sweep(x, ks=(4, 3, 2), nstart=10, seed=1000)
-        again = KM.kmeans_sweep(x, ks=(4, 3, 2), nstart=10, seed=1000)
-    for k in (4, 3, 2):
-        host = KM.kmeans(x, k, nstart=8, seed=1000)
-        r = dev[k]
-        assert r.centers.shape == (k, 3) and r.labels.shape == (120,)
-        # k = 4 is the planted structure (one minimum); for k < 4 several local minima lie within a few per cent
-        assert abs(r.tot_withinss - host.tot_withinss) <= (1e-3 if k == 4 else 0.03) * host.tot_withinss, (k, r.tot_withinss, host.tot_withinss)
-        # internal consistency: centres are the means of their members, withinss adds up, labels are nearest centres
-        for j in range(k):
-            assert torch.allclose(r.centers[j], x[r.labels == j].mean(0), atol=1e-5)
-        assert abs(float(r.withinss.sum()) - r.tot_withinss) < 1e-3
-        assert torch.equal(torch.cdist(x, r.centers).argmin(1), r.labels)
-        assert torch.equal(r.labels, again[k].labels) and r.tot_withinss == again[k].tot_withinss      # reproducible
-    assert sorted(torch.bincount(dev[4].labels).tolist()) == [30, 30, 30, 30]
-
-
-def test_batched_metrics_kernel_matches_the_torch_restatement():
-    from consensusml_b200.ops import metrics as M
-    g = torch.Generator().manual_seed(21)
-    B, n = 5, 137
-    truth = (torch.rand(n, generator=g) < 0.45).float()
-    scores = torch.randn(B, n, generator=g) + truth[None, :] * torch.linspace(0, 2, B)[:, None]
-    scores[1] = torch.round(scores[1] * 2) / 2            # many tied scores
-    scores[4] = 0.3                                       # all tied: AUC 0.5 exactly
-    probs = torch.sigmoid(scores)
-    with _native.emulation(seed=6):
-        m = M.batch_metrics(scores, truth)
-        mp = M.batch_metrics(probs, truth, threshold=0.5, is_prob=True)
-        one_auc = M.auc(scores[2], truth)
-        cm = M.confusion_matrix((scores[2] > 0).float(), truth)
-        ll = M.log_loss(truth, probs[3])
-    for b in range(B):
-        assert abs(float(m["auc"][b]) - M._auc_torch(scores[b], truth)) < 1e-12, b
-        assert abs(float(mp["logloss"][b]) - M._log_loss_torch(truth, probs[b])) < 1e-6
-        ref = M._confusion_torch(scores[b] > 0, truth).flatten().tolist()
-        assert [int(m[k][b]) for k in ("tn", "fn", "fp", "tp")] == ref
-    assert float(m["auc"][4]) == 0.5 and torch.isnan(m["logloss"]).all()
-    assert abs(one_auc - M._auc_torch(scores[2], truth)) < 1e-12
-    assert torch.equal(cm, M._confusion_torch(scores[2] > 0, truth))
-    assert abs(ll - M._log_loss_torch(truth, probs[3])) < 1e-6
-
-
-def test_glmboost_kernels_follow_the_float64_path():
-    from consensusml_b200.models import glmboost as GB
-    g = torch.Generator().manual_seed(4)
-    x = torch.randn(70, 90, generator=g)
-    x[:, 11] = 2.0                                         # constant column: never usable
-    y = 300 + 40 * x[:, 3] - 25 * x[:, 17] + 5 * torch.randn(70, generator=g)
-    ref = GB.glmboost(x, y, mstop=30, nu=0.1)
-    with _native.emulation(seed=3):
-        fit = GB.glmboost(x, y, mstop=30, nu=0.1)
-    assert fit.path == ref.path
-    assert torch.allclose(fit.coef, ref.coef, rtol=1e-5, atol=1e-6) and abs(fit.intercept - ref.intercept) < 1e-3
-    assert np.allclose(fit.risk, ref.risk, rtol=1e-5)
-
-
-def test_mlp_epoch_kernels_match_a_torch_restatement_with_the_same_bf16_roundings():
-    from consensusml_b200.models import mlp as MLP
-    g = torch.Generator().manual_seed(5)
-    n, p = 61, 37
-    x = torch.randn(n, p, generator=g)
-    y = ((x[:, 0] - x[:, 1] + 0.5 * x[:, 2]) > 0).float()
-    grid = [dict(hidden=5, lr=3e-3, weight_decay=0.0, seed=0), dict(hidden=9, lr=1e-2, weight_decay=1e-3, seed=1),
-            dict(hidden=3, lr=1e-3, weight_decay=1e-2, seed=2)]
-    # one epoch must agree to rounding; over more epochs Adam's m / sqrt(v) amplifies last-bit differences of tiny
-    # gradients (and a bf16 rounding tie can flip), so the 12-epoch comparison is looser
-    for epochs, tol in ((1, 2e-6), (12, 1e-3)):
-        _check_mlp(MLP, x, y, grid, n, epochs, tol)
-
-
-def _check_mlp(MLP, x, y, grid, n, epochs, tol):
-    with _native.emulation(seed=4):
-        res = MLP.train_grid(x, y, grid, epochs=epochs)
-    # restatement: the fp32 torch loop of train_grid with bf16 rounding of the three GEMM operands (X, W1, dH)
-    bf = lambda t: t.to(torch.bfloat16).float()
-    xf = x.float()
-    mean, sd = xf.mean(0), xf.std(0, unbiased=True)
-    xs = (xf - mean) / torch.where(sd > 0, sd, torch.ones_like(sd))
-    ref = MLP.train_grid(x, y, grid, epochs=0)                              # initial weights only
-    w1, b1, w2, b2 = ref.w1.clone(), ref.b1.clone(), ref.w2.clone(), ref.b2.clone()
-    hs = [c["hidden"] for c in grid]
-    seg = torch.repeat_interleave(torch.arange(3), torch.tensor(hs))
-    lr_u = torch.tensor([c["lr"] for c in grid])[seg]
-    wd_u = torch.tensor([c["weight_decay"] for c in grid])[seg]
-    lr_g = torch.tensor([c["lr"] for c in grid])
-    params = [w1, b1, w2, b2]
-    m = [torch.zeros_like(t) for t in params]
-    v = [torch.zeros_like(t) for t in params]
-    lrs, wds = [lr_u[:, None], lr_u, lr_u, lr_g], [wd_u[:, None], None, wd_u, None]
-    xb = bf(xs)
-    for t in range(1, epochs + 1):
-        pre = xb @ bf(w1).t() + b1
-        h = torch.relu(pre)
-        logit = torch.zeros(n, 3).index_add_(1, seg, h * w2[None, :]) + b2[None, :]
-        prob = torch.sigmoid(logit)
-        dlogit = (prob - y[:, None]) / n
-        dh = dlogit[:, seg] * w2[None, :] * (pre > 0)
-        grads = [bf(dh).t() @ xb, dh.sum(0), (dlogit[:, seg] * h).sum(0), dlogit.sum(0)]
-        for i, (pt, gr) in enumerate(zip(params, grads)):
-            if wds[i] is not None:
-                gr = gr + wds[i] * pt
-            m[i].mul_(0.9).add_(gr, alpha=0.1)
-            v[i].mul_(0.999).addcmul_(gr, gr, value=0.001)
-            pt.sub_(lrs[i] * (m[i] / (1 - 0.9 ** t)) / ((v[i] / (1 - 0.999 ** t)).sqrt() + 1e-8))
-    for a, b in ((res.w1, w1), (res.b1, b1), (res.w2, w2), (res.b2, b2)):
-        assert float((a - b).abs().max()) <= tol, (epochs, float((a - b).abs().max()))
-    assert torch.isfinite(res.train_loss).all() and (res.train_loss < 0.8).all()
-
-
-def _gbm_problem(n=900, p=21, seed=3):
-    g = torch.Generator().manual_seed(seed)
-    x = torch.randn(n, p, generator=g)
-    beta = torch.zeros(p)
-    beta[:6] = torch.tensor([1.2, -1.0, 0.8, -0.8, 0.6, 0.5])
-    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ beta + 0.8 * x[:, 6] * x[:, 7])).float()
-    return x, y
-
-
-def test_large_gbm_kernel_level_loop_builds_the_same_trees_as_the_torch_path():
-    """Histogram build (slot table, reduce-scatter landing with world = 1), sibling derivation, split scoring, totals and
-    routing kernels against the torch restatement of the same level-wise algorithm."""
-    from consensusml_b200.models.gbm_large import GBMLarge, quantile_bin
-    from consensusml_b200.ops.metrics import _auc_torch
-    x, y = _gbm_problem()
-    bins, cuts = quantile_bin(x, 32)
-    ref = GBMLarge(n_estimators=3, max_depth=3, nbins=32, backend="unfused", sibling_subtraction=True).fit(None, y, bins=bins, cuts=cuts)
-    for sib in (True, False):
-        with _native.emulation(seed=5, sms=2):
-            got = GBMLarge(n_estimators=3, max_depth=3, nbins=32, sibling_subtraction=sib).fit(None, y, bins=bins, cuts=cuts)
-        for a, b in zip(ref.trees, got.trees):
-            assert torch.equal(a.feat, b.feat), (sib, a.feat, b.feat)
-            split = a.feat >= 0
-            assert torch.equal(a.thr[split], b.thr[split])
-            assert (a.value - b.value).abs().max() < 2e-4
-        assert torch.allclose(ref.importance_gain_, got.importance_gain_, rtol=2e-3, atol=1e-3)
-    assert _auc_torch(got.predict_proba(x), y) > 0.8
-
-
-def test_size_factor_and_plda_score_kernels():
-    from consensusml_b200.models import discriminant as D
-    c, y = nb_counts(120, 31, seed=8, n_de=30)
-    c = torch.from_numpy(c) + 1
-    c[5, 3] = 0                                           # a gene with a zero is skipped by the median of ratios
-    yt = torch.from_numpy(y).long()
-    sf_ref = D.deseq_size_factors(c)
-    m_ref = D.PoissonLDA(rho=2.0).fit(c, yt)
-    m2_ref = D.PoissonLDA(power=True).fit(c, yt)
-    with _native.emulation(seed=3):
-        sf = D.deseq_size_factors(c)
-        sc = m_ref.scores(c)
-        sc2 = m2_ref.scores(c[:, :7].contiguous())
-    assert torch.allclose(sf, sf_ref, rtol=1e-12, atol=1e-12)
-    assert torch.allclose(sc, m_ref.scores(c), rtol=1e-10, atol=1e-8)
-    assert torch.allclose(sc2, m2_ref.scores(c[:, :7].contiguous()), rtol=1e-10, atol=1e-8)
+@pytest.mark.parametrize("case", [n for n in dir(KC) if n.startswith("case_")])
+def test_round2_kernel_on_the_host_execution_model(case):
+    getattr(KC, case)(KC.EmuBackend())

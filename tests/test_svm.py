@@ -110,16 +110,3 @@ def test_large_svm_decomposition_reaches_the_smo_optimum_cpu(kernel):
     d_ref, d_big = ref.decision_function(xs[:50]), big.decision_function(xs[:50])
     assert (d_ref - d_big).abs().max() < 5e-2 and ((d_ref > 0) == (d_big > 0)).float().mean() > 0.97
     assert big.cache_hit_rate_ > 0.3                                                    # working sets overlap: the LRU cache pays
-
-
-def test_large_svm_subproblem_kernel_under_emulation():
-    """Same decomposition with the warm-started SMO kernel (csrc/svm.cu) solving the sub-problems on the emulator."""
-    from consensusml_b200 import _native
-    from consensusml_b200.models.svm_large import LargeSVC
-    x, y = _svm_blobs(n=160, p=6, seed=3)
-    xs = (x - x.mean(0)) / x.std(0, unbiased=True)
-    ref = LargeSVC(kernel="radial", q=32, tol=1e-3).fit(xs, y)
-    with _native.emulation(seed=2):
-        emu = LargeSVC(kernel="radial", q=32, tol=1e-3).fit(xs, y)
-    assert abs(emu.objective_ - ref.objective_) < 2e-3 * max(1.0, abs(ref.objective_))
-    assert emu.gap_ < 1e-3 and abs(emu.rho_ - ref.rho_) < 2e-2
