@@ -22,7 +22,8 @@ def test_pipeline_reference_cohort_gpu(tmp_path):
     assert s["svm1"]["auc"] > 0.9 and s["mlp"]["auc"] > 0.85
     assert len(s["consensus"]["top"]) == 50
     recs = [json.loads(l) for l in open(tmp_path / "run.jsonl")]
-    assert {r.get("stage") for r in recs if r["event"] == "stage"} >= {"lasso", "svm", "random_forest", "gbm", "mlp", "consensus"}
+    assert {r.get("group") for r in recs if r["event"] == "task"} >= {"lasso", "svm", "rf_2k", "gbm", "mlp"}
+    assert any(r["event"] == "stage" and r.get("stage") == "write_outputs" for r in recs)
 
 
 def test_counts_to_cohort_gpu():

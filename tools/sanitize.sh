@@ -9,4 +9,4 @@ python -m consensusml_b200._build > /dev/null
 export CML_SANITIZE=1
 exec compute-sanitizer --tool "$TOOL" --error-exitcode 9 --print-limit 20 \
   python -m pytest tests/test_lasso_gpu.py tests/test_gemm_gpu.py tests/test_normalize.py tests/test_de.py tests/test_trees.py \
-                   tests/test_svm.py tests/test_stats.py tests/test_fused.py -x -q -m gpu
+                   tests/test_svm.py tests/test_stats.py tests/test_x_fused.py -x -q -m gpu
