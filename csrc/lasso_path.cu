@@ -29,6 +29,7 @@
 // and the KKT / curvature passes reduce sixteen dot products with one transposed butterfly (warp_sum16_transposed).
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "cml_b200.h"
 #include "common.cuh"
@@ -67,20 +68,29 @@ struct LognetParams {
 // floats of global scratch per resident warp: {b, xv} pairs + |gradient|, kept even so the pairs stay 8-byte aligned
 __host__ __device__ inline size_t scratch_stride(int p) { return 3 * (size_t)p + (p & 1); }
 
-template <int NPL>
+// Shared state of a CTA-per-fit team (latency mode, NW > 1 warps): command word of the pass protocol and the column cache.
+struct TeamShared {
+  int cmd, flag, rep, first_i;      // pass command, "something was added" flag, replicate index, first weighted-in sample
+  float fa, fb;                     // pass parameters (thresholds)
+  int n_slots, cap;                 // column-cache slots handed out / available
+};
+
+template <int NPL, int NW = 1>
 struct Warp {
   // ---- per-lane register state ----
   float r[NPL], v[NPL];
-  // ---- shared-memory views: [pend 16][wq n_pad][ys n_pad][qs n_pad][m nx][bs nx][ixx pw][inm pw][jub pw] ----
+  // ---- shared-memory views: [pend 16 x NW][wq n_pad][ys n_pad][qs n_pad][m nx][bs nx][ixx pw][inm pw][jub pw] ----
   // The fixed-size arrays come first: with n_pad = 32 * NPL known at compile time their addresses are constants, and
   // the rest are one multiply-add away from values in the constant bank - none of these views occupies a register.
-  static constexpr int kFixedBytes = 16 * 4 + 3 * 32 * NPL * 4;
+  // A team (NW > 1, lognet_path_cta_kernel) appends [TeamShared][rsh n_pad][vsh n_pad][cslot p][bx 2 x cap][cols cap x n_pad].
+  static constexpr bool kTeam = NW > 1;
+  static constexpr int kFixedBytes = 16 * 4 * NW + 3 * 32 * NPL * 4;
   __device__ __forceinline__ unsigned char* sbase() const {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     return smem_raw;
   }
-  __device__ __forceinline__ int* pend() const { return reinterpret_cast<int*>(sbase()); }                  // waiting group
-  __device__ __forceinline__ float* wq() const { return reinterpret_cast<float*>(sbase() + 64); }           // normalised weights
+  __device__ __forceinline__ int* pend() const { return reinterpret_cast<int*>(sbase()) + 16 * wid; }       // waiting group (per warp)
+  __device__ __forceinline__ float* wq() const { return reinterpret_cast<float*>(sbase() + 64 * NW); }      // normalised weights
   __device__ __forceinline__ float* ys() const { return wq() + 32 * NPL; }                                  // response
   __device__ __forceinline__ float* qs() const { return wq() + 64 * NPL; }                                  // fitted probabilities
   __device__ __forceinline__ int* m() const { return reinterpret_cast<int*>(sbase() + kFixedBytes); }       // active list (entry order)
@@ -88,20 +98,47 @@ struct Warp {
   __device__ __forceinline__ unsigned* ixx() const { return reinterpret_cast<unsigned*>(m() + 2 * P.nx); }  // screened set
   __device__ __forceinline__ unsigned* inm() const { return ixx() + ((P.p + 31) >> 5); }                    // active membership
   __device__ __forceinline__ unsigned* jub() const { return ixx() + 2 * ((P.p + 31) >> 5); }                // usable features
+  // ---- team extras (only touched when NW > 1) ----
+  __device__ __forceinline__ TeamShared* team() const { return reinterpret_cast<TeamShared*>(jub() + ((P.p + 31) >> 5)); }
+  __device__ __forceinline__ float* rsh() const { return reinterpret_cast<float*>(team() + 1); }            // residual handed to the helpers
+  __device__ __forceinline__ float* vsh() const { return rsh() + 32 * NPL; }                                // IRLS weights handed to the helpers
+  __device__ __forceinline__ short* cslot() const { return reinterpret_cast<short*>(vsh() + 32 * NPL); }    // feature -> cache slot, -1 = not cached
+  __device__ __forceinline__ float* bx() const {                                                            // {b, xv} of the cached features
+    return reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(cslot()) + ((2 * (size_t)P.p + 15) & ~(size_t)15));
+  }
+  __device__ __forceinline__ float* cols(int cap) const { return bx() + 2 * (size_t)cap; }                  // cached columns [cap][n_pad]
   // ---- global scratch of this warp: {b, xv} pairs by feature, then |gradient| at the last KKT evaluation ----
+  // (a team keeps the pair of every CACHED feature in shared memory instead: the coordinate steps then never wait on L2)
   float* gb;
-  __device__ __forceinline__ float& b(int k) const { return gb[2 * k]; }
-  __device__ __forceinline__ float& xv(int k) const { return gb[2 * k + 1]; }
+  __device__ __forceinline__ float& b(int k) const {
+    if constexpr (kTeam) { const int sl = cslot()[k]; if (sl >= 0) return bx()[2 * sl]; }
+    return gb[2 * k];
+  }
+  __device__ __forceinline__ float& xv(int k) const {
+    if constexpr (kTeam) { const int sl = cslot()[k]; if (sl >= 0) return bx()[2 * sl + 1]; }
+    return gb[2 * k + 1];
+  }
   __device__ __forceinline__ float& ga(int k) const { return gb[2 * P.p + k]; }
   const LognetParams& P;
   const int lane;
+  const int wid;
+  int cache_cap = 0;
   int nin = 0, nlp = 0;
   unsigned version = 0, ga_version = 0;
   float b0 = 0.f, xmz = 0.f;
 
-  __device__ Warp(const LognetParams& p_, int lane_) : P(p_), lane(lane_) {}
+  __device__ Warp(const LognetParams& p_, int lane_, int wid_ = 0) : P(p_), lane(lane_), wid(wid_) {}
 
   __device__ __forceinline__ void load_col(int k, float (&x)[NPL]) const {
+    if constexpr (kTeam) {
+      const int sl = cslot()[k];
+      if (sl >= 0) {                     // column resident in shared memory: same values, no global-memory latency
+        const float* c = cols(cache_cap) + (size_t)sl * (32 * NPL) + lane;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) x[j] = c[32 * j];
+        return;
+      }
+    }
     const float* xk = P.xt + (size_t)k * P.n_pad + lane;
 #pragma unroll
     for (int j = 0; j < NPL; ++j) x[j] = __ldg(xk + 32 * j);
@@ -128,9 +165,14 @@ struct Warp {
   __device__ __forceinline__ void fetch(int k, Pre& e) const {
     e.k = k;
     load_col(k, e.x);
-    const float2 bx = *reinterpret_cast<const float2*>(gb + 2 * k);
-    e.bk = bx.x;
-    e.xvk = bx.y;
+    if constexpr (kTeam) {
+      e.bk = b(k);
+      e.xvk = xv(k);
+    } else {
+      const float2 bx = *reinterpret_cast<const float2*>(gb + 2 * k);
+      e.bk = bx.x;
+      e.xvk = bx.y;
+    }
     e.pk = vpk(k);
   }
 
@@ -320,7 +362,172 @@ struct Warp {
       r[j] = wq()[i] * (ys()[i] - qs()[i]);
     }
   }
+
+  // =========================================================================================== team passes (NW > 1)
+  // The passes over all p features are split over the warps of the team by 32-feature words (word wd belongs to warp
+  // wd % NW).  Every feature is evaluated with exactly the arithmetic of the one-warp kernel - same per-lane FMA chains
+  // over the same residual / weights, same reduction tree - so a team fit is bit-identical to a warp fit.
+  __device__ __forceinline__ void publish_rv() {                   // solver warp: hand residual and IRLS weights to the helpers
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) { rsh()[lane + 32 * j] = r[j]; vsh()[lane + 32 * j] = v[j]; }
+  }
+  __device__ __forceinline__ void adopt_rv() {
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) { r[j] = rsh()[lane + 32 * j]; v[j] = vsh()[lane + 32 * j]; }
+  }
+  // Newly screened features get a cache slot: their column and their {b, xv} pair move to shared memory.
+  __device__ void cache_insert(unsigned bits, int wd) {
+    while (bits) {
+      const int k = (wd << 5) + __ffs(bits) - 1;
+      bits &= bits - 1;
+      int sl = 0;
+      if (lane == 0) sl = atomicAdd(&team()->n_slots, 1);
+      sl = __shfl_sync(FULL, sl, 0);
+      if (sl >= cache_cap) continue;                               // cache full: the feature keeps living in global memory
+      const float* xk = P.xt + (size_t)k * P.n_pad + lane;
+      float* c = cols(cache_cap) + (size_t)sl * (32 * NPL) + lane;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) c[32 * j] = __ldg(xk + 32 * j);
+      if (lane == 0) {
+        bx()[2 * sl] = gb[2 * k];
+        bx()[2 * sl + 1] = gb[2 * k + 1];
+        cslot()[k] = (short)sl;
+      }
+    }
+  }
+  // set-up: usable flag, initial |gradient|, modified-Newton curvature bound of this warp's features (r = initial residual)
+  __device__ void pass_setup(int rep, int first_i) {
+    const int pw = (P.p + 31) >> 5;
+    const unsigned char* jurow = P.ju ? P.ju + (size_t)rep * P.ju_stride : nullptr;
+    const int fl = first_i & 31, fj = first_i >> 5;
+    for (int wd = wid; wd < pw; wd += NW) {
+      const int k0 = wd << 5;
+      unsigned usable_bits = 0u;
+      const int kend = min(32, P.p - k0);
+      if (k0 + lane < P.p) cslot()[k0 + lane] = (short)-1;
+      for (int kk = 0; kk < kend; ++kk) {
+        const int k = k0 + kk;
+        float x[NPL];
+        const float* xk = P.xt + (size_t)k * P.n_pad + lane;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) x[j] = __ldg(xk + 32 * j);
+        float xf = 0.f;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) if (j == fj) xf = x[j];
+        xf = __shfl_sync(FULL, xf, fl);
+        bool differs = false;
+        float g = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+          const float wi = wq()[lane + 32 * j];
+          differs |= (wi > 0.f) && (x[j] != xf);
+          g = fmaf(r[j], x[j], g);
+          s2 = fmaf(wi * x[j], x[j], s2);
+        }
+        const bool usable = __any_sync(FULL, differs) && (jurow == nullptr || jurow[k] != 0);
+        g = warp_sum(g);
+        if (P.kopt > 0) s2 = warp_sum(s2);
+        if (usable) usable_bits |= 1u << kk;
+        if (lane == 0) {
+          gb[2 * k] = 0.f;
+          ga(k) = usable ? fabsf(g) : 0.f;
+          gb[2 * k + 1] = (P.kopt > 0 && usable) ? 0.25f * s2 : 0.f;
+        }
+      }
+      if (lane == 0) jub()[wd] = usable_bits;
+    }
+  }
+  // sequential strong rule (threshold tlam) / threshold-only KKT check (threshold al1): same test, different threshold
+  __device__ bool pass_threshold(float thr) {
+    const int pw = (P.p + 31) >> 5;
+    bool added = false;
+    for (int wd = wid; wd < pw; wd += NW) {
+      const int k = (wd << 5) + lane;
+      bool add = false;
+      if (k < P.p) add = !bit(ixx(), k) && bit(jub(), k) && ga(k) > thr * vpk(k);
+      const unsigned bits = __ballot_sync(FULL, add);
+      if (bits) {
+        added = true;
+        __syncwarp();
+        if (lane == 0) ixx()[wd] |= bits;
+        cache_insert(bits, wd);
+      }
+    }
+    return added;
+  }
+  // curvature of every screened feature at the current IRLS weights v
+  __device__ void pass_xv() {
+    const int pw = (P.p + 31) >> 5;
+    for (int wd = wid; wd < pw; wd += NW) {
+      const unsigned word = ixx()[wd];
+      if (word == 0u) continue;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const unsigned th = (word >> (16 * h)) & 0xffffu;
+        if (th == 0u) continue;
+        const int kb = (wd << 5) + 16 * h;
+        float acc[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          acc[q] = 0.f;
+          if ((th >> q) & 1u) {
+            float x[NPL];
+            load_col(kb + q, x);
+#pragma unroll
+            for (int j = 0; j < NPL; ++j) acc[q] = fmaf(v[j] * x[j], x[j], acc[q]);
+          }
+        }
+        const float sx = warp_sum16_transposed(acc, lane);
+        const int q = lane & 15;
+        if (lane < 16 && ((th >> q) & 1u)) xv(kb + q) = sx;
+      }
+    }
+  }
+  // KKT check over the features that are not screened in: gradients against the current residual r
+  __device__ bool pass_kkt(float al1) {
+    const int pw = (P.p + 31) >> 5;
+    bool added = false;
+    for (int wd = wid; wd < pw; wd += NW) {
+      const int k0 = wd << 5;
+      const unsigned skip = ixx()[wd], use = jub()[wd];
+      const unsigned todo = use & ~skip;
+      unsigned newbits = 0u;
+      if (todo == 0u) continue;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const unsigned th = (todo >> (16 * h)) & 0xffffu;
+        if (th == 0u) continue;
+        const int kb = k0 + 16 * h;
+        float acc[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          acc[q] = 0.f;
+          if ((th >> q) & 1u) {
+            float x[NPL];
+            load_col_stream(kb + q, x);
+#pragma unroll
+            for (int j = 0; j < NPL; ++j) acc[q] = fmaf(r[j], x[j], acc[q]);
+          }
+        }
+        const float ag = fabsf(warp_sum16_transposed(acc, lane));
+        const int q = lane & 15, k = kb + q;
+        const bool valid = ((th >> q) & 1u) != 0u;
+        if (valid && lane < 16) ga(k) = ag;
+        const bool add = valid && ag > al1 * (valid ? vpk(k) : 1.f);
+        newbits |= (__ballot_sync(FULL, add) & 0xffffu) << (16 * h);
+      }
+      if (newbits) {
+        added = true;
+        __syncwarp();
+        if (lane == 0) ixx()[wd] |= newbits;
+        cache_insert(newbits, wd);
+      }
+    }
+    return added;
+  }
 };
+
+enum TeamCmd : int { TEAM_SETUP = 1, TEAM_STRONG, TEAM_XV, TEAM_KKT, TEAM_KKT_THRESH, TEAM_EXIT };
 
 // PROF = true builds the same kernel with clock64() phase timers (cml_lognet_path_profile); the production
 // instantiation carries none of it.
@@ -662,6 +869,284 @@ lognet_path_kernel(const LognetParams P) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Latency mode: ONE CTA = ONE PATH FIT (used when the batch has no more fits than the GPU has SMs - the 94 fits of a
+// leave-one-out round, cml_targetaml_seanalysis.Rmd:98-101, are the case that matters: fifteen such rounds run one after
+// the other in the exclusion loop :728-773, so their LATENCY, not their throughput, is the pipeline's critical path).
+//
+// With one warp per SM the one-warp kernel spends its time waiting: every coordinate step reads a column and a {b, xv}
+// pair that live in L2 / global scratch.  Here the fit owns the SM:
+//   * warp 0 runs the same sequential algorithm (same code: sweep_screened / sweep_active / refresh), but every feature
+//     that has entered the screened set has its column and its {b, xv} pair in SHARED memory (up to ~200 KB: ~500 columns
+//     at n = 93), so a coordinate step waits on shared-memory latency only;
+//   * warps 1..7 are helpers: the passes over all p features (set-up, strong rule, curvature refresh, KKT check) are
+//     split over the eight warps by 32-feature words, and the helper that admits a feature to the screened set also copies
+//     it into the cache.  Hand-over is by block barriers around each pass (command word in shared memory).
+// The arithmetic of every number is the one-warp kernel's, so the two kernels return identical bits; which one runs is a
+// scheduling decision (cml_lognet_path picks this one for B <= #SMs).
+constexpr int kTeamWarps = 8;
+
+template <int NPL>
+__global__ void __launch_bounds__(32 * kTeamWarps, 1) lognet_path_cta_kernel(const LognetParams P, int cache_cap) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int pw = (P.p + 31) >> 5;
+  Warp<NPL, kTeamWarps> W(P, lane, wid);
+  W.cache_cap = cache_cap;
+  W.gb = P.scratch + (size_t)blockIdx.x * scratch_stride(P.p);
+  TeamShared* T = W.team();
+
+  if (wid != 0) {
+    // ---------------------------------------------------------------- helpers: wait for a pass, do this warp's share
+    while (true) {
+      __syncthreads();
+      const int cmd = T->cmd;
+      if (cmd == TEAM_EXIT) break;
+      bool added = false;
+      if (cmd == TEAM_SETUP) { W.adopt_rv(); W.pass_setup(T->rep, T->first_i); }
+      else if (cmd == TEAM_STRONG || cmd == TEAM_KKT_THRESH) added = W.pass_threshold(T->fa);
+      else if (cmd == TEAM_XV) { W.adopt_rv(); W.pass_xv(); }
+      else if (cmd == TEAM_KKT) { W.adopt_rv(); added = W.pass_kkt(T->fa); }
+      if (added && lane == 0) T->flag = 1;
+      __syncthreads();
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- warp 0: the solver
+  auto team_pass = [&](int cmd, float fa, bool needs_rv) -> bool {
+    if (lane == 0) { T->cmd = cmd; T->fa = fa; T->flag = 0; }
+    if (needs_rv) W.publish_rv();
+    __syncthreads();
+    bool added = false;
+    if (cmd == TEAM_SETUP) W.pass_setup(T->rep, T->first_i);
+    else if (cmd == TEAM_STRONG || cmd == TEAM_KKT_THRESH) added = W.pass_threshold(fa);
+    else if (cmd == TEAM_XV) W.pass_xv();
+    else if (cmd == TEAM_KKT) added = W.pass_kkt(fa);
+    if (added && lane == 0) T->flag = 1;
+    __syncthreads();
+    return T->flag != 0;
+  };
+
+  const float pmin = 1e-9f;
+  const float fmax_ = logf(1.f / pmin - 1.f), fmin_ = -fmax_;
+  const float vmin = (1.f + pmin) * pmin * (1.f - pmin);
+  const float bta = P.alpha, omb = 1.f - bta;
+
+  for (int rep = blockIdx.x; rep < P.B;) {
+    // ------------------------------------------------------------------ set-up (scalar part: warp 0 alone)
+    const float* wsrc = P.w + (size_t)rep * P.n_pad;
+    const float* ysrc = P.y + (size_t)rep * P.y_stride;
+    float sw = 0.f;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) sw += wsrc[lane + 32 * j];
+    sw = warp_sum(sw);
+    int jerr = 0, lmu = 0;
+    W.nin = 0; W.nlp = 0; W.version = 0; W.ga_version = 0; W.b0 = 0.f;
+    float q0 = 0.f;
+    int first_i = 1 << 30;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+      const int i = lane + 32 * j;
+      const float wi = sw > 0.f ? wsrc[i] / sw : 0.f;
+      const float yi = ysrc[i];
+      W.wq()[i] = wi;
+      W.ys()[i] = yi;
+      q0 = fmaf(wi, yi, q0);
+      if (wi > 0.f && i < first_i) first_i = i;
+    }
+    q0 = warp_sum(q0);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) first_i = min(first_i, __shfl_xor_sync(FULL, first_i, o));
+    if (!(sw > 0.f)) jerr = 10000;
+    else if (q0 <= pmin) jerr = 8001;
+    else if (q0 >= 1.f - pmin) jerr = 9001;
+    for (int wd = lane; wd < pw; wd += 32) { W.ixx()[wd] = 0u; W.inm()[wd] = 0u; W.jub()[wd] = 0u; }
+    if (lane == 0) { T->n_slots = 0; T->rep = rep; T->first_i = first_i; }
+    __syncwarp();
+
+    float dev0 = 0.f, dev1 = 0.f, shr = 0.f;
+    if (jerr == 0) {
+      if (!P.intercept) q0 = 0.5f;
+      const float bz = P.intercept ? logf(q0 / (1.f - q0)) : 0.f;
+      const float vi = q0 * (1.f - q0);
+      W.b0 = bz;
+      W.xmz = vi;
+      dev1 = -(bz * q0 + logf(1.f - q0));
+      float dacc = 0.f;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const int i = lane + 32 * j;
+        const float wi = W.wq()[i], yi = W.ys()[i];
+        W.v[j] = vi * wi;
+        W.r[j] = wi * (yi - q0);
+        W.qs()[i] = q0;
+        if (yi > 0.f) dacc += wi * yi * logf(yi);
+        if (yi < 1.f) dacc += wi * (1.f - yi) * logf(1.f - yi);
+      }
+      dev0 = dev1 + warp_sum(dacc);
+      shr = P.thresh * dev0;
+      if (lane == 0) P.nulldev_out[rep] = 2.f * dev0 * sw;
+      team_pass(TEAM_SETUP, 0.f, true);          // one pass over every feature, eight warps wide
+    } else if (lane == 0) {
+      P.nulldev_out[rep] = 0.f;
+    }
+
+    // ------------------------------------------------------------------ lambda path
+    float al = 0.f;
+    bool stop = jerr != 0;
+    for (int ilm = 0; ilm < P.nlam && !stop; ++ilm) {
+      const float al0 = al;
+      al = P.lam[ilm];
+      const float al2 = al * omb, al1 = al * bta, tlam = bta * (2.f * al - al0);
+      team_pass(TEAM_STRONG, tlam, false);       // sequential strong rule (+ cache fill of what it admits)
+
+      bool overflow = false, done = false;
+      while (!done) {                      // re-entered when the KKT check admits new features
+        while (true) {                     // IRLS iterations
+          if (W.nlp > P.maxit) { jerr = -(ilm + 1); stop = true; done = true; break; }
+          const float b0s = W.b0;
+          for (int l = lane; l < W.nin; l += 32) W.bs()[l] = W.b(W.m()[l]);
+          __syncwarp();
+          if (P.kopt == 0) team_pass(TEAM_XV, 0.f, true);
+          bool fail = false;
+          while (true) {                   // full sweep, then active-set sweeps to convergence
+            ++W.nlp;
+            float dlx = 0.f;
+            if (!W.sweep_screened(al1, al2, dlx)) { overflow = true; break; }
+            W.intercept_step(dlx);
+            if (dlx < shr) break;
+            if (W.nlp > P.maxit) { fail = true; break; }
+            while (true) {
+              ++W.nlp;
+              dlx = 0.f;
+              W.sweep_active(al1, al2, dlx);
+              W.intercept_step(dlx);
+              if (dlx < shr) break;
+              if (W.nlp > P.maxit) { fail = true; break; }
+            }
+            if (fail) break;
+          }
+          if (fail) { jerr = -(ilm + 1); stop = true; done = true; break; }
+          if (overflow) { done = true; break; }
+          W.refresh(fmin_, fmax_);
+          if (W.xmz <= vmin) { done = true; break; }
+          W.reset_residual();
+          bool ix = W.xmz * (W.b0 - b0s) * (W.b0 - b0s) > shr;
+          if (!ix) {
+            bool mine = false;
+            for (int l = lane; l < W.nin; l += 32) {
+              const int k = W.m()[l];
+              const float d = W.b(k) - W.bs()[l];
+              mine |= W.xv(k) * d * d > shr;
+            }
+            ix = __any_sync(FULL, mine);
+          }
+          if (ix) continue;
+          // KKT check over the features that are not screened in
+          bool added;
+          if (W.version != W.ga_version) {
+            added = team_pass(TEAM_KKT, al1, true);
+            W.ga_version = W.version;
+          } else {
+            added = team_pass(TEAM_KKT_THRESH, al1, false);     // gradients still exact: only the threshold moved
+          }
+          if (!added) done = true;
+          break;
+        }
+      }
+      if (stop) break;
+      if (overflow) { jerr = -10000 - (ilm + 1); break; }
+
+      // ---- record this lambda
+      const size_t row = (size_t)rep * P.nlam + ilm;
+      for (int l = lane; l < W.nin; l += 32) {
+        const int k = W.m()[l];
+        const float bk = W.b(k);
+        if (P.ca_out) P.ca_out[row * P.nx + l] = bk;
+        if (P.freq_out && bk != 0.f) atomicAdd(P.freq_out + (size_t)ilm * P.p + k, 1.f);
+      }
+      float dacc = 0.f;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const int i = lane + 32 * j;
+        const float pp = fminf(fmaxf(pmin, W.qs()[i]), 1.f - pmin);
+        const float yi = W.ys()[i];
+        dacc -= W.wq()[i] * (yi * logf(pp) + (1.f - yi) * logf(1.f - pp));
+      }
+      dacc = warp_sum(dacc);
+      if (lane == 0) {
+        P.kin_out[row] = W.nin;
+        P.a0_out[row] = W.b0;
+        P.dev_out[row] = (dev1 - dacc) / dev0;
+      }
+      if (P.eta_out) {
+        float eta[NPL];
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) eta[j] = W.b0;
+        for (int l = 0; l < W.nin; ++l) {
+          const int k = W.m()[l];
+          const float bk = W.b(k);
+          float x[NPL];
+          W.load_col(k, x);
+#pragma unroll
+          for (int j = 0; j < NPL; ++j) eta[j] = fmaf(bk, x[j], eta[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) P.eta_out[row * P.n_pad + lane + 32 * j] = eta[j];
+      }
+      lmu = ilm + 1;
+      if (W.xmz <= vmin) break;
+    }
+    if (P.m_out)
+      for (int l = lane; l < W.nin; l += 32) P.m_out[(size_t)rep * P.nx + l] = W.m()[l];
+    if (lane == 0) {
+      P.npasses_out[rep] = W.nlp;
+      P.lmu_out[rep] = lmu;
+      P.jerr_out[rep] = jerr;
+    }
+    int nxt = 0;
+    if (lane == 0) nxt = (int)(atomicAdd(P.next_rep, 1u) + gridDim.x);
+    rep = __shfl_sync(FULL, nxt, 0);
+    __syncwarp();
+  }
+  if (lane == 0) T->cmd = TEAM_EXIT;
+  __syncthreads();
+}
+
+size_t team_base_bytes(int p, int nx, int n_pad) {
+  const size_t pw = (p + 31) / 32;
+  size_t b = 16 * 4 * kTeamWarps + 3 * (size_t)n_pad * 4 + (size_t)nx * 8 + 3 * pw * 4;        // the one-warp layout with NW pend areas
+  b += sizeof(TeamShared) + 2 * (size_t)n_pad * 4;                                             // team word + rsh + vsh
+  b += (2 * (size_t)p + 15) & ~(size_t)15;                                                     // cslot
+  return b;
+}
+
+template <int NPL>
+int launch_team(const LognetParams& P, int grid, cudaStream_t st) {
+  const size_t base = team_base_bytes(P.p, P.nx, P.n_pad);
+  const size_t budget = 200 * 1024;
+  const size_t per_slot = (size_t)P.n_pad * 4 + 8;
+  int cap = base + 16 < budget ? (int)((budget - base - 16) / per_slot) : 0;
+  if (cap > 32767) cap = 32767;
+  const size_t smem = base + (size_t)cap * per_slot + 16;
+  CML_CUDA(cudaFuncSetAttribute(lognet_path_cta_kernel<NPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lognet_path_cta_kernel<NPL><<<grid, 32 * kTeamWarps, smem, st>>>(P, cap);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+// Latency mode applies when every fit of the batch can have an SM of its own and the layout fits (p <= 32767 features
+// index the int16 slot table; the base arrays must leave room for at least 64 cached columns).  CML_LASSO_TEAM=0 disables
+// it, =1 forces it whenever the layout fits (tests).
+bool use_team_kernel(int B, int p, int nx, int n_pad) {
+  const char* e = getenv("CML_LASSO_TEAM");
+  const int mode = e ? atoi(e) : -1;
+  if (mode == 0) return false;
+  if (p > 32767 || n_pad > 256) return false;
+  if (team_base_bytes(p, nx, n_pad) + 64 * ((size_t)n_pad * 4 + 8) > 200 * 1024) return false;
+  return mode == 1 || B <= sm_count();
+}
+
 template <int NPL>
 int launch(const LognetParams& P, int grid, size_t smem, cudaStream_t st) {
   CML_CUDA(cudaFuncSetAttribute(lognet_path_kernel<NPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -721,6 +1206,18 @@ int cml_lognet_path(int B, int n, int n_pad, int p, int nlam, int nx, const floa
   LognetParams P{B, n, n_pad, p, nlam, nx, xt, y, y_stride, w, ju, ju_stride, vp, lam, alpha, thresh, intercept,
                  kopt, maxit, static_cast<float*>(scratch), m_out, ca_out, kin_out, a0_out, dev_out, eta_out,
                  freq_out, nulldev_out, npasses_out, lmu_out, jerr_out, nullptr, counter};
+  if (use_team_kernel(B, p, nx, n_pad)) {          // latency mode: one CTA per fit (same results, see lognet_path_cta_kernel)
+    const int tgrid = B < sm_count() ? B : sm_count();
+    switch (n_pad / 32) {
+      case 1: return launch_team<1>(P, tgrid, st);
+      case 2: return launch_team<2>(P, tgrid, st);
+      case 3: return launch_team<3>(P, tgrid, st);
+      case 4: return launch_team<4>(P, tgrid, st);
+      case 5: return launch_team<5>(P, tgrid, st);
+      case 6: return launch_team<6>(P, tgrid, st);
+      case 8: return launch_team<8>(P, tgrid, st);
+    }
+  }
   switch (n_pad / 32) {
     case 1: return launch<1>(P, grid, smem, st);
     case 2: return launch<2>(P, grid, smem, st);

@@ -259,3 +259,80 @@ def case_large_svm_subproblems_on_the_warm_started_smo_kernel(be):
     # (on a GPU the kernel columns come from the bf16 tensor-core Gram kernel: a slightly different kernel matrix)
     assert abs(got.objective_ - ref.objective_) < be.tol(2e-3, 2e-2) * max(1.0, abs(ref.objective_))
     assert got.gap_ < 1e-3 and abs(got.rho_ - ref.rho_) < be.tol(2e-2, 5e-2)
+
+
+def case_lasso_cta_per_fit_kernel_is_bit_identical_to_the_warp_kernel(be):
+    """Latency mode (one CTA per fit: shared-memory column cache, eight warps on the p-wide passes) against the validated
+    one-warp kernel: same arithmetic, so every output must be equal bit for bit, in all three solver variants."""
+    import os
+    from consensusml_b200.ops import lasso as K
+    g = torch.Generator().manual_seed(3)
+    n, p, B = 75, 200, 3
+    x = torch.randn(n, p, generator=g)
+    beta = torch.zeros(p)
+    beta[:6] = torch.tensor([1.0, -1.0, 0.8, -0.8, 0.5, 0.5])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ beta)).float()
+    w = torch.ones(B, n)
+    for b in range(1, B):
+        w[b, torch.randperm(n, generator=g)[:7]] = 0
+    mask = torch.ones(B, p, dtype=torch.bool)
+    mask[1, :4] = False
+    lam = np.geomspace(0.3, 0.02, 14)
+    old = os.environ.get("CML_LASSO_TEAM")
+    try:
+        for kw in (dict(), dict(alpha=0.5, intercept=True), dict(modified_newton=True)):
+            res = {}
+            for mode in ("0", "1"):
+                os.environ["CML_LASSO_TEAM"] = mode
+                with be.ctx(seed=int(mode) * 3 + 1):
+                    freq = be.dev(torch.zeros(len(lam), p))
+                    o = K.lognet_path(be.dev(x), be.dev(y), be.dev(w), lam, feature_mask=be.dev(mask), freq_out=freq, **kw)
+                    res[mode] = (o, _h(freq))
+            a, fa = res["0"]
+            b_, fb = res["1"]
+            assert int(_h(a.jerr).abs().max()) == 0
+            for name in ("npasses", "kin", "eta", "a0", "dev_ratio", "nulldev", "lmu"):
+                assert torch.equal(_h(getattr(a, name)), _h(getattr(b_, name))), (kw, name)
+            assert torch.equal(fa, fb)
+            for i in range(B):
+                assert torch.equal(_h(a.dense(i)), _h(b_.dense(i))), (kw, i)
+    finally:
+        if old is None:
+            os.environ.pop("CML_LASSO_TEAM", None)
+        else:
+            os.environ["CML_LASSO_TEAM"] = old
+
+
+def case_lasso_cta_per_fit_kernel_error_paths_match_the_warp_kernel(be):
+    """Active-list overflow, a replicate without weight, a one-class replicate and the iteration cap: the paths on which the
+    solver warp leaves its loops early while the helper warps are parked at a barrier."""
+    import os
+    from consensusml_b200.ops import lasso as K
+    g = torch.Generator().manual_seed(5)
+    n, p, B = 40, 90, 4
+    x = torch.randn(n, p, generator=g)
+    y = (x[:, 0] - x[:, 1] + 0.5 * torch.randn(n, generator=g) > 0).float()
+    w = torch.ones(B, n)
+    w[1] = 0
+    yy = torch.stack([y, y, torch.ones_like(y), y])
+    lam = np.geomspace(0.3, 0.02, 14)
+    old = os.environ.get("CML_LASSO_TEAM")
+    res = {}
+    try:
+        for mode in ("0", "1"):
+            os.environ["CML_LASSO_TEAM"] = mode
+            with be.ctx(seed=2):
+                res[mode] = (K.lognet_path(be.dev(x), be.dev(y), be.dev(w), lam, nx=6),
+                             K.lognet_path(be.dev(x), be.dev(yy), be.dev(w), lam, maxit=40))
+    finally:
+        if old is None:
+            os.environ.pop("CML_LASSO_TEAM", None)
+        else:
+            os.environ["CML_LASSO_TEAM"] = old
+    for i in (0, 1):
+        a, b_ = res["0"][i], res["1"][i]
+        for name in ("jerr", "lmu", "npasses", "kin"):
+            assert torch.equal(_h(getattr(a, name)), _h(getattr(b_, name))), (i, name)
+    j0, j1 = _h(res["1"][0].jerr).tolist(), _h(res["1"][1].jerr).tolist()
+    assert j0[1] == 10000 and all(v < -10000 for v in (j0[0], j0[2], j0[3]))          # no weight; active-list overflow
+    assert j1[1] == 10000 and j1[2] == 9001 and j1[0] < 0 and j1[3] < 0                # one class; iteration cap
