@@ -30,6 +30,7 @@ _native.register_signature("cml_forest_level", [_P, _I, _I, _I, _I, _P, _P, _P, 
                                                 _P, _P])
 _native.register_signature("cml_forest_predict", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P])
 _native.register_signature("cml_forest_proximity", [_P, _P, _I, _I, _P, _P, _P])
+_native.register_signature("cml_forest_onehot", [_P, _P, _I, _I, _I, _P, ctypes.c_longlong, _P, ctypes.c_longlong, _P])
 _native.register_signature("cml_quantile_edges", [_P, _I, _I, ctypes.c_longlong, _I, _P, _P, _P])
 
 GINI, NEWTON = 0, 1
@@ -188,6 +189,41 @@ def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):
                                            P(trees.value), P(leaf), P(val), _native.stream_ptr())
     _native.check(rc, "cml_forest_predict")
     return leaf, val
+
+
+PROXIMITY_GEMM_MIN_N = 256      # below this the O(n^2 T) comparison kernel is one cheap launch; above it the GEMM form wins
+
+
+def proximity_gemm(leaf: torch.Tensor, oob: Optional[torch.Tensor], max_nodes: int, max_cols: int = 1 << 16):
+    """(proximity counts, pair counts) [n, n] of a batch of trees as one-hot GEMMs: ``forest_onehot_kernel`` writes the
+    sample x (tree, leaf) membership matrix in bf16 and the tcgen05 GEMM multiplies it with its transpose (randomForest's
+    ``proximity = TRUE``, cml_targetaml_seanalysis.Rmd:1037-1050, at cohort sizes where n^2 T comparisons are too many).
+    Trees are processed in groups of at most ``max_cols`` one-hot columns."""
+    from ..ops import gemm as G
+    T, n = leaf.shape
+    dev = leaf.device
+    per = max(1, max_cols // max_nodes)
+    prox = torch.zeros(n, n, device=dev)
+    pairs = torch.zeros(n, n, device=dev)
+    for t0 in range(0, T, per):
+        t1 = min(T, t0 + per)
+        tt = t1 - t0
+        ldz = (tt * max_nodes + 7) // 8 * 8
+        ldo = (tt + 7) // 8 * 8
+        z = torch.zeros(n, ldz, dtype=torch.bfloat16, device=dev)
+        o = torch.zeros(n, ldo, dtype=torch.bfloat16, device=dev)
+        lf = leaf[t0:t1].contiguous()
+        ob = oob[t0:t1].contiguous() if oob is not None else None
+        rc = _native.cuda().cml_forest_onehot(_native.ptr(lf), _native.ptr(ob), tt, n, max_nodes, _native.ptr(z), ldz, _native.ptr(o), ldo,
+                                              _native.stream_ptr())
+        _native.check(rc, "cml_forest_onehot")
+        if z.is_cuda:
+            prox += G.gemm_tn(z, [z], n)
+            pairs += G.gemm_tn(o, [o], n) if ldo >= G.MIN_K else o.float() @ o.float().t()
+        else:                                   # host execution model: the same one-hot matrices, fp32 products
+            prox += z.float() @ z.float().t()
+            pairs += o.float() @ o.float().t()
+    return prox, pairs
 
 
 # ------------------------------------------------------------------------------------------------ NumPy restatement
@@ -383,7 +419,11 @@ class RandomForest:
             pairs = torch.zeros(n, n, device=dev)
             use_oob = self.oob_prox and self.bootstrap
             ob = (w == 0).to(torch.uint8).contiguous() if use_oob else None
-            if _native.on_device(leaf):
+            if _native.on_device(leaf) and n >= PROXIMITY_GEMM_MIN_N:
+                dp, dq = proximity_gemm(leaf.contiguous(), ob, tb.feat.shape[1])
+                prox += dp
+                pairs += dq
+            elif _native.on_device(leaf):
                 rc = _native.cuda().cml_forest_proximity(_native.ptr(leaf.contiguous()), _native.ptr(ob), T, n,
                                                          _native.ptr(prox), _native.ptr(pairs), _native.stream_ptr())
                 _native.check(rc, "cml_forest_proximity")

@@ -18,6 +18,8 @@
 #include <cfloat>
 #include <cmath>
 
+#include <cuda_bf16.h>
+
 #include "cml_b200.h"
 #include "common.cuh"
 
@@ -312,6 +314,21 @@ __global__ void forest_proximity_kernel(const int* __restrict__ leaf, const unsi
   }
 }
 
+// Proximity as a GEMM (large n): Z[i][t * max_nodes + leaf_t(i)] = 1 when sample i is counted for tree t (out-of-bag, or
+// always without an oob table); then proximity counts = Z Z^T and pair counts = O O^T with O[i][t] the same indicator - two
+// tcgen05 GEMMs (ops/gemm.py) instead of the O(n^2 T) comparison loop above.  0 / 1 are exact in bf16 and the products are
+// accumulated in fp32, so the counts are exact up to 2^24 trees.  z [n][ldz] and o [n][ldo] must be zero at entry.
+__global__ void forest_onehot_kernel(const int* __restrict__ leaf, const unsigned char* __restrict__ oob, int T, int n, int max_nodes,
+                                     __nv_bfloat16* __restrict__ z, long long ldz, __nv_bfloat16* __restrict__ o, long long ldo) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= (long long)T * n) return;
+  const int t = (int)(e / n), i = (int)(e % n);
+  if (oob && !oob[e]) return;
+  const __nv_bfloat16 one = __float2bfloat16_rn(1.f);
+  z[(size_t)i * ldz + (size_t)t * max_nodes + leaf[e]] = one;
+  if (o) o[(size_t)i * ldo + t] = one;
+}
+
 // Dense-rank binning for n <= 256: bin = number of DISTINCT smaller values (ties share a bin).
 // edges[f][b] = the value bin b stands for, n_edges[f] = number of occupied bins.
 __global__ void rank_bins_kernel(const float* __restrict__ xt, int p, int n, int ld, unsigned char* __restrict__ bins,
@@ -420,6 +437,17 @@ int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int m
   if (total <= 0) return 0;
   forest_predict_kernel<<<(unsigned)ceil_div(total, 256LL), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       bins, m, m_pad, T, max_nodes, feat, thr, left, value, leaf_out, value_out);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+int cml_forest_onehot(const int* leaf, const unsigned char* oob, int T, int n, int max_nodes, void* z_bf16, long long ldz, void* o_bf16,
+                      long long ldo, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(T > 0 && n > 0 && max_nodes > 0 && ldz >= (long long)T * max_nodes && (!o_bf16 || ldo >= T), CML_EINVAL,
+              "cml_forest_onehot: bad shape");
+  forest_onehot_kernel<<<(unsigned)ceil_div((long long)T * n, 256LL), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      leaf, oob, T, n, max_nodes, static_cast<__nv_bfloat16*>(z_bf16), ldz, static_cast<__nv_bfloat16*>(o_bf16), ldo);
   CML_LAUNCH_CHECK();
   return 0;
 }

@@ -170,6 +170,10 @@ int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max
 int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int max_nodes, const int* feat, const int* thr,
                        const int* left, const float* value, int* leaf_out, float* value_out, void* stream);
 int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n, float* prox, float* pairs, void* stream);
+/* Proximity as two GEMMs for large n: one-hot leaf membership z [n][ldz] (column t * max_nodes + leaf) and the counted-sample
+ * indicator o [n][ldo], both bf16 and zero at entry; proximity counts = z z^T, pair counts = o o^T (tcgen05 GEMM). */
+int cml_forest_onehot(const int* leaf, const unsigned char* oob, int T, int n, int max_nodes, void* z_bf16, long long ldz, void* o_bf16,
+                      long long ldo, void* stream);
 
 /* ---- K7: SVM (SMO dual solver, decision values) - e1071::svm at cml_targetaml_seanalysis.Rmd:151-154,166-169 ---- */
 int cml_svm_smo(int B, int n, const float* K, long long k_stride, long long ldk, const float* y, long long y_stride,

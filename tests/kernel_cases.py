@@ -336,3 +336,19 @@ def case_lasso_cta_per_fit_kernel_error_paths_match_the_warp_kernel(be):
     j0, j1 = _h(res["1"][0].jerr).tolist(), _h(res["1"][1].jerr).tolist()
     assert j0[1] == 10000 and all(v < -10000 for v in (j0[0], j0[2], j0[3]))          # no weight; active-list overflow
     assert j1[1] == 10000 and j1[2] == 9001 and j1[0] < 0 and j1[3] < 0                # one class; iteration cap
+
+
+def case_forest_proximity_as_one_hot_gemm(be):
+    """randomForest-style proximity through the one-hot membership kernel + GEMM against the definition."""
+    from consensusml_b200.models import trees as TR
+    g = torch.Generator().manual_seed(1)
+    T, n, max_nodes = 37, 70, 9
+    leaf = torch.randint(0, max_nodes, (T, n), generator=g, dtype=torch.int32)
+    ob = (torch.rand(T, n, generator=g) < 0.4).to(torch.uint8)
+    both = (ob[:, :, None] & ob[:, None, :]).bool()
+    want_p = ((leaf[:, :, None] == leaf[:, None, :]) & both).float().sum(0)
+    with be.ctx(seed=4):
+        p1, q1 = TR.proximity_gemm(be.dev(leaf), be.dev(ob), max_nodes, max_cols=100)        # several tree groups
+        p2, q2 = TR.proximity_gemm(be.dev(leaf), None, max_nodes)
+    assert torch.equal(_h(p1), want_p) and torch.equal(_h(q1), both.float().sum(0))
+    assert torch.equal(_h(p2), (leaf[:, :, None] == leaf[:, None, :]).float().sum(0)) and float(_h(q2).min()) == T
