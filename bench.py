@@ -152,6 +152,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--fits", type=int, default=8880, help="bootstrap path fits per GPU for the secondary fits/s number (0 = skip)")
     ap.add_argument("--no-fused", action="store_true", help="skip the fused-path block (N > 1)")
+    ap.add_argument("--device", default="cuda", choices=["cuda", "cpu"],
+                    help="cpu = dry run of this script's own logic on the CPU oracles (tests/test_api.py); its line is marked invalid")
     ap.add_argument("overrides", nargs="*", help="section.key=value overrides of the pipeline configuration")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -171,41 +173,62 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
+    on_gpu = args.device == "cuda"
+    if on_gpu and not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
+    if on_gpu:
+        torch.cuda.set_device(local_rank)
+        dev = torch.device("cuda", local_rank)
+    else:
+        dev = torch.device("cpu")
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    lib = _native.cuda()
-    out_dir = os.path.join(os.environ.get("TMPDIR", "/tmp"), f"cml_bench_{os.getpid()}")
-    base = ["device=cuda:%d" % local_rank, "resume=false", "checkpoint=false", "io.out_dir=" + out_dir] + list(args.overrides)
+        dist.init_process_group("nccl", device_id=dev) if on_gpu else dist.init_process_group("gloo")
+    lib = _native.cuda() if on_gpu else None
+    # one output directory for all ranks of this job (they share the launcher as parent)
+    out_dir = os.path.join(os.environ.get("TMPDIR", "/tmp"), f"cml_bench_{os.getppid() if world > 1 else os.getpid()}")
+    base = ["device=" + ("cuda:%d" % local_rank if on_gpu else "cpu"), "resume=false", "checkpoint=false", "io.out_dir=" + out_dir] + list(args.overrides)
     cfg_dev = C.load(None, base + ["write_outputs=false"])
     cfg_e2e = C.load(None, base + ["write_outputs=true"])
 
     host = datasets.load_target_aml()                       # float64 assay, host memory
-    pinned = host.assay.float().pin_memory()                # what the end-to-end arm uploads every step
-    flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    pinned = host.assay.float().pin_memory() if on_gpu else host.assay.float()      # what the end-to-end arm uploads every step
+    flush_buf = torch.empty(256 * 1024 * 1024 if on_gpu else 1, dtype=torch.uint8, device=dev)
 
     def flush():
-        lib.cml_l2_flush(_native.ptr(flush_buf), flush_buf.numel(), _native.stream_ptr())
+        if on_gpu:
+            lib.cml_l2_flush(_native.ptr(flush_buf), flush_buf.numel(), _native.stream_ptr())
 
     def barrier():
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        if on_gpu:
+            torch.cuda.synchronize()
+
+    class Stamp:
+        """A point in time on the launching stream: CUDA event on the GPU, host clock in the CPU dry run."""
+        def __init__(self):
+            self.ev = torch.cuda.Event(enable_timing=True) if on_gpu else None
+            self.t = 0.0
+
+        def record(self):
+            if on_gpu:
+                self.ev.record()
+            else:
+                self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return self.ev.elapsed_time(other.ev) if on_gpu else (other.t - self.t) * 1e3
 
     def cohort_on_device(assay_dev):
         return Cohort(assay_dev, host.gene_ids, host.sample_ids, host.row_data, host.col_data, dict(host.metadata), host.assay_name)
 
-    launches = {"n": 0}
 
     # ---------------- arm A: device-timed, cohort already resident ----------------
     resident = cohort_on_device(pinned.to(dev))
     for _ in range(args.warmup):
         pipeline.run(cfg_dev, resident)
     barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev = [(Stamp(), Stamp()) for _ in range(args.steps)]
     summary = None
     _native.reset_calls()
     with ClockSampler(local_rank) as clk:
@@ -265,7 +288,7 @@ def main():
         for s in range(2):
             sel_step(s)
         barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a, b = Stamp(), Stamp()
         a.record()
         for s in range(3):
             sel_step(2 + s)
@@ -289,13 +312,15 @@ def main():
         import contextlib
         import io
         tm = []
-        for i in range(3):
-            torch.cuda.synchronize()
+        for i in range(3 if on_gpu else 0):
+            barrier()
             t0 = time.perf_counter()
             with contextlib.redirect_stdout(io.StringIO()):
                 MC.model_comp(Xtr, Xte, ytr, yte)
-            torch.cuda.synchronize()
+            barrier()
             tm.append(time.perf_counter() - t0)
+        if not tm:
+            raise RuntimeError("skipped in the CPU dry run")
         mc = {"model_comp_wall_s": float(np.mean(tm[1:])), "note": "api.model_comp: same three models, hyper-parameters and printed "
               "log-losses as scripts/model_comp.py:6-34, host DataFrames in, fitted on this rank's GPU"}
     except Exception as exc:
@@ -316,6 +341,7 @@ def main():
         acc = _accuracy(summary, cpu_arm, genes13)
         sched = summary["schedule"]
         print(json.dumps({
+            **({} if on_gpu else {"invalid": "CPU dry run of bench.py (--device cpu): not a measurement"}),
             "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": value / CPU_ARM_WALL_S,

@@ -21,7 +21,7 @@ class RunLog:
     def __init__(self, path: Optional[str] = None, rank: int = 0, echo: bool = False):
         self.path, self.rank, self.echo = path, rank, echo
         self.records = []
-        if path and rank == 0:
+        if path:          # every rank writes its own file (<path>.rank<r> for r > 0), possibly before rank 0 has created the directory
             os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
 
     def event(self, kind: str, **fields) -> Dict[str, Any]:
