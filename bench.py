@@ -130,6 +130,8 @@ def reference_arm(args):
 # ------------------------------------------------------------------------------------------------ our arm
 def _accuracy(summary, cpu_arm, genes13):
     from consensusml_b200.consensus.rank_aggregate import top_k_overlap
+    if "lasso" not in summary or "consensus" not in summary:
+        return {"error": "lasso / consensus stage missing", "failed_tasks": summary.get("failed_tasks")}
     lasso = summary["lasso"]
     top = summary["consensus"]["top"]
     out = {"lasso_auc": lasso["auc"], "lasso_auc_ref": REF_AUC, "lasso_auc_abs_err": abs(lasso["auc"] - REF_AUC),
@@ -186,7 +188,10 @@ def main():
     lib = _native.cuda() if on_gpu else None
     # one output directory for all ranks of this job (they share the launcher as parent)
     out_dir = os.path.join(os.environ.get("TMPDIR", "/tmp"), f"cml_bench_{os.getppid() if world > 1 else os.getpid()}")
-    base = ["device=" + ("cuda:%d" % local_rank if on_gpu else "cpu"), "resume=false", "checkpoint=false", "io.out_dir=" + out_dir] + list(args.overrides)
+    # fail_fast=false: a stage that raises is reported in the line (summary["failed_tasks"] -> "failed_tasks"), it does not
+    # take the measurement of the other stages with it
+    base = ["device=" + ("cuda:%d" % local_rank if on_gpu else "cpu"), "resume=false", "checkpoint=false", "fail_fast=false",
+            "io.out_dir=" + out_dir] + list(args.overrides)
     cfg_dev = C.load(None, base + ["write_outputs=false"])
     cfg_e2e = C.load(None, base + ["write_outputs=true"])
 
@@ -360,7 +365,7 @@ def main():
             "gpu_launches_note": "calls of libcml_b200.so entry points inside the timed region, all ranks (each launches at least one "
                                  "kernel of ours); counted in consensusml_b200._native.check; torch's own kernels excluded",
             "gpu_launches_rank0_by_entry": calls,
-            "accuracy": acc, "schedule": sched, "step_ms": ms,
+            "accuracy": acc, "schedule": sched, "step_ms": ms, "failed_tasks": summary.get("failed_tasks"),
             "secondary": {"fits": fits, "model_comp": mc, "fused_paths": fused},
         }, default=float))
     if world > 1:

@@ -59,9 +59,21 @@ def assign(tasks: List[Task], world: int) -> Dict[str, int]:
     return out
 
 
-def run_tasks(tasks: List[Task], *, enabled: bool = True) -> tuple[Dict[str, Any], TaskReport]:
+class TaskError:
+    """Result of a task that raised (``fail_fast=False``): the ensemble goes on without that stage and reports it."""
+
+    def __init__(self, name: str, exc: BaseException):
+        self.name, self.error = name, f"{type(exc).__name__}: {exc}"
+
+    def __repr__(self):
+        return f"TaskError({self.name!r}, {self.error!r})"
+
+
+def run_tasks(tasks: List[Task], *, enabled: bool = True, fail_fast: bool = True) -> tuple[Dict[str, Any], TaskReport]:
     """Run every task on the rank it is assigned to and return ``{task name: result}`` complete on every rank.
-    Results must be picklable and live on the host (tasks copy what they return off the device)."""
+    Results must be picklable and live on the host (tasks copy what they return off the device).
+    ``fail_fast=False`` turns an exception inside a task into a ``TaskError`` result instead of aborting the run (every rank
+    still reaches the gather, so a failed stage cannot leave the other ranks waiting)."""
     names = [t.name for t in tasks]
     if len(set(names)) != len(names):
         raise ValueError("task names must be unique")
@@ -76,9 +88,14 @@ def run_tasks(tasks: List[Task], *, enabled: bool = True) -> tuple[Dict[str, Any
         if torch.cuda.is_available():
             torch.cuda.synchronize()
         t0 = time.perf_counter()
-        local[t.name] = t.fn()
-        if torch.cuda.is_available():
-            torch.cuda.synchronize()
+        try:
+            local[t.name] = t.fn()
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+        except Exception as exc:                       # noqa: BLE001 - reported, not swallowed
+            if fail_fast:
+                raise
+            local[t.name] = TaskError(t.name, exc)
         secs[t.name] = time.perf_counter() - t0
     if world > 1:
         gathered: List[Optional[tuple]] = [None] * world

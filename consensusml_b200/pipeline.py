@@ -193,9 +193,13 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
     # a checkpoint is only reused for the same configuration AND the same data (ids, labels, split and assay content)
     key = cfg.hash(["lasso", "svm", "rf", "gbm", "mlp", "split"]) + ":" + fp
     tasks = build_tasks(cfg, cohort, dev, store, key, log)
-    results, report = run_tasks(tasks, enabled=cfg.dist.enabled)
+    results, report = run_tasks(tasks, enabled=cfg.dist.enabled, fail_fast=cfg.fail_fast)
+    from .parallel.tasks import TaskError
+    failed = {n: r.error for n, r in results.items() if isinstance(r, TaskError)}
     for t in tasks:
-        log.event("task", task=t.name, group=t.group, rank=report.assignment[t.name], seconds=report.seconds.get(t.name))
+        log.event("task", task=t.name, group=t.group, rank=report.assignment[t.name], seconds=report.seconds.get(t.name),
+                  **({"error": failed[t.name]} if t.name in failed else {}))
+    ok = lambda name: name not in failed                      # stages that failed are left out of the table and reported
 
     st = CS.StandTable(cohort)
     importances: Dict[str, np.ndarray] = {}
@@ -204,7 +208,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
     tr_c, te_c = cohort.split()
     yte_np = te_c.labels().cpu().numpy()
 
-    if cfg.lasso.enabled:
+    if cfg.lasso.enabled and ok("lasso"):
         lr = results["lasso"]
         for i, nz in enumerate(lr["nonzero"], 1):
             st.add(f"lasso_coef_rep{i}", nz)
@@ -216,16 +220,20 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
         for kern in cfg.svm.kernels:
             for wf in cfg.svm.weightfilt:
                 k += 1
+                if not ok(f"svm{k}"):
+                    continue
                 r = results[f"svm{k}"]
                 st.add(f"svm{k}_weights", r["weights"])
                 summary[f"svm{k}"] = r["summary"]
                 scores.setdefault("svm", r["score"])
-        importances["svm"] = st.df["svm1_weights"].to_numpy()
+                importances.setdefault("svm", r["weights"])
     if cfg.rf.enabled:
         from .models.trees import RandomForest
         ytr_t = tr_c.labels()
         for nt in cfg.rf.n_trees:
             tag = _rf_tag(nt)
+            if not all(ok(t.name) for t in tasks if t.group == f"rf_{tag}"):
+                continue
             parts = [results[t.name] for t in tasks if t.group == f"rf_{tag}"]         # task order = tree order
             rf = RandomForest(n_trees=nt, proximity=cfg.rf.proximity, seed=cfg.rf.seed)
             rf._bins, rf._yf = torch.zeros(1), ytr_t.float()                            # merge on the host
@@ -241,12 +249,14 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
                 R.write_all(os.path.join(out, "report"), {}, {f"rf_{tag}_proximity": {"proximity": rf.proximity_.numpy()}})
     if cfg.gbm.enabled:
         for i, _ in enumerate(cfg.gbm.reps, 1):
+            if not ok(f"xgb{i}"):
+                continue
             r = results[f"xgb{i}"]
             st.add(f"xg{i}_imp", r["gain"])
             summary[f"xgb{i}"] = r["summary"]
             importances["xgb"] = r["gain"]
             scores["xgb"] = r["score"]
-    if cfg.mlp.enabled:
+    if cfg.mlp.enabled and ok("mlp"):
         r = results["mlp"]
         st.add("mlp_importance", r["importance"])
         importances["mlp"] = r["importance"]
@@ -259,6 +269,8 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
         sets = CS.selection_sets({k: pd.Series(v, index=genes) for k, v in importances.items()}, positive_only=False)
         summary["consensus"] = {"top": rank_tab.index[: cfg.consensus.top].tolist(),
                                 "intersections": {k: len(v) for k, v in CS.intersections(sets).items()}}
+    if failed:
+        summary["failed_tasks"] = failed
     summary["schedule"] = {"critical": report.critical(), "rank_seconds": report.rank_seconds,
                            "group_seconds": {g: sum(report.seconds.get(t.name, 0.0) for t in tasks if t.group == g)
                                              for g in sorted({t.group for t in tasks})}}
@@ -266,7 +278,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
         with log.stage("write_outputs"):
             os.makedirs(out, exist_ok=True)
             st.write_csv(os.path.join(out, "standouttable.csv"))
-            if cfg.lasso.enabled:
+            if cfg.lasso.enabled and ok("lasso"):
                 CS.write_lasso_gene_csv(results["lasso"]["nonzero"][0], os.path.join(out, "Logistic_Lasso_RiskGroup_Associated_Genes.csv"))
                 R.write_all(os.path.join(out, "report"), {"lasso_rep_curves": results["lasso"]["curves"]})
             if rank_tab is not None:

@@ -120,6 +120,7 @@ class Config:
     dist: DistConfig = field(default_factory=DistConfig)
     device: str = "auto"
     resume: bool = True
+    fail_fast: bool = True                 # False: a stage that raises is reported in summary["failed_tasks"], the others go on
     checkpoint: bool = True                # write per-task artefacts (and reuse them when `resume`)
     write_outputs: bool = True             # standouttable / gene CSV / report dumps (benchmarks of the compute switch this off)
 

@@ -177,3 +177,17 @@ def test_cli_normalize_and_de_on_counts_csv(tmp_path, capsys):
     deg = pd.read_csv(info["csv"], index_col=0)
     assert list(deg.columns) == ["logFC", "AveExpr", "t", "P.Value", "adj.P.Val", "B"] and len(deg) == info["degs"] > 10
     assert (deg["adj.P.Val"] < 0.05).all() and (deg["logFC"].abs() > 1).all() and deg["P.Value"].is_monotonic_increasing
+
+
+def test_failed_stage_is_reported_not_fatal_when_fail_fast_is_off(tmp_path, monkeypatch):
+    from consensusml_b200.models import svm as S
+    def boom(*a, **k):
+        raise RuntimeError("injected fault")
+    monkeypatch.setattr(S, "run_svm", boom)
+    ov = ["io.out_dir=" + str(tmp_path), "device=cpu", "lasso.exclusion_reps=1", "rf.n_trees=[30]", "rf.proximity=false",
+          'gbm.reps=[{"max_depth": 2, "nrounds": 2}]', 'svm.kernels=["linear"]', "svm.weightfilt=[null]", "checkpoint=false"]
+    s = pipeline.run(C.load(None, ov + ["fail_fast=false"]))
+    assert "injected fault" in s["failed_tasks"]["svm1"] and "svm1" not in s and s["lasso"]["confusion"] == [[21, 2], [1, 20]]
+    assert len(s["consensus"]["top"]) == 50
+    with pytest.raises(RuntimeError, match="injected fault"):
+        pipeline.run(C.load(None, ov))
