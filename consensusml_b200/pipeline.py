@@ -59,6 +59,58 @@ def cohort_from_counts(counts: torch.Tensor, gene_ids, sample_ids, group: np.nda
     return Cohort(assay.double(), ids, list(sample_ids), rd, cd, {"n_deg": len(ids), "df_prior": de.df_prior})
 
 
+def cohort_from_counts_sharded(counts_local: torch.Tensor, gene_ids, sample_ids, group: np.ndarray, train_mask: np.ndarray, cfg: Config,
+                               log: Optional[RunLog] = None) -> Cohort:
+    """``cohort_from_counts`` for a SAMPLE-SHARDED count matrix under torchrun: ``counts_local`` holds all genes of this rank's
+    block of samples (``parallel.dist.shard_bounds`` over ``len(sample_ids)``); ``gene_ids`` / ``sample_ids`` / ``group`` /
+    ``train_mask`` are global.  Normalisation runs sample-sharded and the voom prefilter gene-sharded (stats/sharded.py:
+    pass-count all-reduce, reference-column broadcast, shard transpose, five G-length all-gathers); the returned cohort -
+    TMM log2-CPM of the DEGs for ALL samples - is the same on every rank, ready for ``run``."""
+    import torch.distributed as dist
+    from .parallel.dist import shard_bounds
+    from .stats import sharded as SH
+    log = log or RunLog()
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    S = len(sample_ids)
+    lo, hi = shard_bounds(S, world, rank)
+    assert counts_local.shape[1] == hi - lo, "counts_local must hold this rank's sample block"
+    with log.stage("normalize_sharded", bytes_moved=float(counts_local.numel() * 4 * 3)):
+        nrm = SH.tmm_normalize_sharded(counts_local, cfg.normalize.min_cpm, cfg.normalize.min_samples, prior_count=cfg.normalize.prior_count)
+    with log.stage("voom_de_sharded"):
+        # the prefilter is fitted on the TRAINING samples only (DEL:254): every rank passes its training columns
+        tr_local = torch.as_tensor(np.flatnonzero(train_mask[lo:hi]), device=counts_local.device)
+        tr_counts = counts_local[:, tr_local].contiguous()
+        if world > 1:
+            # training samples are not evenly spread over the sample blocks: re-shard them evenly (all-gather of the training
+            # columns is G x n_train ints - small next to the cohort - then every rank keeps its own even block)
+            parts = [None] * world
+            dist.all_gather_object(parts, tr_counts.cpu())
+            full = torch.cat(parts, 1)
+            a, b = shard_bounds(full.shape[1], world, rank)
+            tr_counts = full[:, a:b].contiguous().to(counts_local.device)
+        de = SH.voom_de_sharded(tr_counts, group[train_mask], min_frac=cfg.de.min_frac, p_value=cfg.de.p_value, lfc=cfg.de.lfc,
+                                span=cfg.de.span)
+    deg_full = de.gene_index[de.deg_order]
+    kept_full = np.flatnonzero(nrm["keep"].cpu().numpy())
+    pos = {g: i for i, g in enumerate(kept_full)}
+    rows = [pos[g] for g in deg_full if g in pos]
+    local = nrm["logcpm"][torch.as_tensor(rows, device=counts_local.device)]               # [n_deg, S_local]
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, local.cpu())
+        assay = torch.cat(parts, 1).to(counts_local.device)
+    else:
+        assay = local
+    ids = [gene_ids[kept_full[r]] for r in rows]
+    tab = de.table(gene_ids)
+    rd = pd.DataFrame({"hgnc_id": "", "hgnc_symbol": "", "ensembl_gene_id": [i.split(".")[0] for i in ids],
+                       "logFC": tab.loc[ids, "logFC"].values, "AveExpr": tab.loc[ids, "AveExpr"].values, "t": tab.loc[ids, "t"].values,
+                       "p.unadj": tab.loc[ids, "P.Value"].values, "p.adj.bh": tab.loc[ids, "adj.P.Val"].values, "b": tab.loc[ids, "B"].values})
+    cd = pd.DataFrame({"deg.risk": group.astype(int), "exptset.seahack": np.where(train_mask, "train", "test")})
+    return Cohort(assay.double(), ids, list(sample_ids), rd, cd, {"n_deg": len(ids), "df_prior": de.df_prior, "sharded_over": world})
+
+
 def _host(t):
     return t.detach().float().cpu().numpy() if isinstance(t, torch.Tensor) else np.asarray(t)
 
