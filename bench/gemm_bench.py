@@ -9,6 +9,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 
+from consensusml_b200.runtime import clocks as CLK
+
+CLK.start_global()          # SM clocks / throttle reasons are sampled while every measurement below runs
+
 from consensusml_b200 import _native
 from consensusml_b200.ops import gemm as G
 
@@ -42,6 +46,6 @@ for (M, N, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (16384, 16384, 2048), 
     rbf = timed(lambda: G.gemm_tn(a, [b], N, epilogue=G.EPI_RBF, alpha=1e-4, norm_a=na, norm_b=[nb], out=c))
     cublas = timed(lambda: torch.matmul(a, b.t()))
     fl = 2.0 * M * N * K
-    print(json.dumps({"M": M, "N": N, "K": K, "ours_ms": ours, "ours_tflops": fl / ours / 1e9, "ours_rbf_tflops": fl / rbf / 1e9,
+    print(json.dumps({"clocks": CLK.snapshot(), "M": M, "N": N, "K": K, "ours_ms": ours, "ours_tflops": fl / ours / 1e9, "ours_rbf_tflops": fl / rbf / 1e9,
                       "one_cta_tflops": fl / one_cta / 1e9, "cta_pair_tflops": fl / pair / 1e9,
                       "cublas_bf16_out_ms": cublas, "cublas_tflops": fl / cublas / 1e9}), flush=True)

@@ -15,6 +15,10 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 
+from consensusml_b200.runtime import clocks as CLK
+
+CLK.start_global()          # SM clocks / throttle reasons are sampled while every measurement below runs
+
 from consensusml_b200 import pipeline
 from consensusml_b200.io.synthetic import nb_counts_multiclass
 from consensusml_b200.runtime import config as C
@@ -45,7 +49,7 @@ def main():
     t0 = time.perf_counter()
     s = pipeline.run_multiclass(cfg, co, class_names={0: "AML", 1: "NBL", 2: "WT", 3: "RT"})
     sync(); fit_s = time.perf_counter() - t0
-    print(json.dumps({"config": "pan-cancer multiclass (synthetic counts of the reference's shape)", "genes": genes, "samples": int(label.size),
+    print(json.dumps({"clocks": CLK.snapshot(), "config": "pan-cancer multiclass (synthetic counts of the reference's shape)", "genes": genes, "samples": int(label.size),
                       "classes": s["classes"], "prefilter_genes": co.n_genes, "normalise_plus_4x_voom_s": round(prep_s, 3),
                       "one_vs_rest_ensemble_plus_consensus_s": round(fit_s, 3), "total_s": round(prep_s + fit_s, 3),
                       "heldout_accuracy": s.get("accuracy"), "confusion": s.get("confusion"), "top10": s.get("top", [])[:10],

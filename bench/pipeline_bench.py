@@ -15,6 +15,10 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 
+from consensusml_b200.runtime import clocks as CLK
+
+CLK.start_global()          # SM clocks / throttle reasons are sampled while every measurement below runs
+
 from consensusml_b200 import datasets
 from consensusml_b200.models import lasso as L
 from consensusml_b200.models import svm as S
@@ -91,5 +95,5 @@ if __name__ == "__main__":
     gpu_arm(co, dev)                                   # warm-up: library load, kernel images, allocator
     g = gpu_arm(co, dev)
     c = cpu_arm(co, lasso_reps=int(os.environ.get("CML_CPU_LASSO_REPS", 3)))
-    print(json.dumps({"bench": "target_aml_ensemble", "gpu": g, "cpu": c, "speedup_total": c["total_s"] / g["total_s"],
+    print(json.dumps({"clocks": CLK.snapshot(), "bench": "target_aml_ensemble", "gpu": g, "cpu": c, "speedup_total": c["total_s"] / g["total_s"],
                       "speedup": {k: c[k] / g[k] for k in c if k.endswith("_s") and k in g}}))

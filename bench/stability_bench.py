@@ -13,6 +13,10 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 
+from consensusml_b200.runtime import clocks as CLK
+
+CLK.start_global()          # SM clocks / throttle reasons are sampled while every measurement below runs
+
 from consensusml_b200 import datasets
 from consensusml_b200.models import lasso as L
 from consensusml_b200.models import svm as S
@@ -49,7 +53,7 @@ def main():
         K.lognet_path(xc, yc, w, lam, alpha=a, want_eta=False)
         cpu_rate[a] = 8 / (time.perf_counter() - t0)
     cpu_est = sum(n_boot / r for r in cpu_rate.values())
-    print(json.dumps({"config": "stability selection: 1000 bootstraps x alpha grid + RBF-SVM grid (TARGET-AML 93 x 1984)",
+    print(json.dumps({"clocks": CLK.snapshot(), "config": "stability selection: 1000 bootstraps x alpha grid + RBF-SVM grid (TARGET-AML 93 x 1984)",
                       "path_fits": 4 * n_boot, "gpu_stability_s": round(stab_s, 3), "gpu_path_fits_per_s": round(4 * n_boot / stab_s, 1),
                       "gpu_svm_grid_s": round(svm_s, 3), "svm_grid_points": len(costs) * len(gammas) * 5,
                       "svm_best": [gs["best_cost"], gs["best_gamma"]], "cpu_one_core_path_fits_per_s": {str(k): round(v, 2) for k, v in cpu_rate.items()},

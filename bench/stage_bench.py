@@ -14,6 +14,10 @@ sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 
+from consensusml_b200.runtime import clocks as CLK
+
+CLK.start_global()          # SM clocks / throttle reasons are sampled while every measurement below runs
+
 
 def main():
     cpu, small = "--cpu" in sys.argv, "--small" in sys.argv
@@ -41,6 +45,7 @@ def main():
         if min_bytes:
             rec["min_bytes"] = int(min_bytes)
             rec["frac_of_hbm_roofline"] = round(min_bytes / (hbm * 1e9) / (ms / 1e3), 4)
+        rec["clocks"] = CLK.snapshot()
         print(json.dumps(rec), flush=True)
 
     from consensusml_b200 import datasets

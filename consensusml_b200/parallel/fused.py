@@ -131,8 +131,15 @@ def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Opti
     ld = (p + 7) // 8 * 8
     n_total = n_local if n_total is None else n_total
     rows = n_local if world == 1 else equal_shard(n_total, world)
-    xb = symm.alloc((rows, ld), torch.bfloat16, dev)
-    nrm = symm.alloc((rows,), torch.float32, dev)
+    # the symmetric block + norm buffers are allocated (and rendezvoused) once per shape and reused: a rendezvous per call
+    # would cost more than the GEMM at small sizes.  Safe to reuse because every call ends with a barrier (below).
+    key = (world, rows, ld, str(dev))
+    if key not in _GRAM_BUFFERS:
+        _GRAM_BUFFERS[key] = (symm.alloc((rows, ld), torch.bfloat16, dev), symm.alloc((rows,), torch.float32, dev))
+    xb, nrm = _GRAM_BUFFERS[key]
+    if n_local < rows:
+        xb.local[n_local:].zero_()
+        nrm.local[n_local:].zero_()
     G.to_bf16_rows(x_local.float().contiguous(), shift=shift, out=xb.local[:n_local], norm_out=nrm.local[:n_local])
     torch.cuda.synchronize()
     xb.barrier()
@@ -163,6 +170,7 @@ class _StageBuffers(dict):
 
 
 _STAGE_CACHE: dict = {}
+_GRAM_BUFFERS: dict = {}
 
 
 def gram_stage_buffers(world: int, rows: int, ld: int, device) -> "_StageBuffers":

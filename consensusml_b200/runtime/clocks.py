@@ -64,3 +64,26 @@ class ClockSampler:
         if self.error:
             out["error"] = self.error
         return out
+
+
+_GLOBAL: "ClockSampler | None" = None
+
+
+def start_global(device_index: int = 0) -> "ClockSampler":
+    """Start one sampler for the lifetime of a benchmark script; ``snapshot()`` then returns the record of the interval
+    since the previous snapshot (so every printed measurement carries the clocks seen while IT ran)."""
+    global _GLOBAL
+    if _GLOBAL is None:
+        _GLOBAL = ClockSampler(device_index)
+        _GLOBAL.__enter__()
+    return _GLOBAL
+
+
+def snapshot() -> Dict:
+    if _GLOBAL is None:
+        return {}
+    out = _GLOBAL.summary()
+    _GLOBAL.samples.clear()
+    _GLOBAL.reasons.clear()
+    _GLOBAL.power.clear()
+    return out
