@@ -60,9 +60,10 @@ def lipschitz_estimate(x: torch.Tensor, n_total: int, iters: int = 12) -> float:
 
 def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Optional[int] = None, max_iter: int = 200,
         tol: float = 1e-5, backend: str = "auto", weights: Optional[torch.Tensor] = None, beta0: Optional[torch.Tensor] = None,
-        step: Optional[float] = None, check_every: int = 10, alpha: float = 1.0) -> LargeFit:
+        step: Optional[float] = None, check_every: int = 10, alpha: float = 1.0, deterministic: bool = False) -> LargeFit:
     """L1 (``alpha = 1``) or elastic-net logistic regression, glmnet's penalty ``lam (alpha |b|_1 + (1 - alpha)/2 |b|^2)``, on this
-    rank's rows (``x_local`` [n_r, p]); every rank returns the full ``beta``."""
+    rank's rows (``x_local`` [n_r, p]); every rank returns the full ``beta``.  ``deterministic=True`` runs the gradient
+    reduce-scatter in its fixed-order form (no float atomics: bit-identical fits from run to run)."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     n_r, p = x_local.shape
     dev = x_local.device
@@ -82,7 +83,7 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
     st = _native.stream_ptr
     xb = x_local if x_local.dtype == torch.bfloat16 else F.to_bf16_padded(x_local)
     ldx = xb.shape[1]
-    rs = F.XtrReduceScatter(p, 1, dev)
+    rs = F.XtrReduceScatter(p, 1, dev, deterministic=deterministic, n_rows=n_r)
     rank = rs.rank
     beta = symm.alloc((ldx,), torch.float32, dev)
     v = symm.alloc((ldx,), torch.float32, dev)

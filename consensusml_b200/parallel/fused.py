@@ -26,6 +26,9 @@ _I, _LL, _F, _P, _U, _SZ = ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctyp
 _native.register_signature("cml_xtr_rs_scratch_bytes", [_I, _I], _SZ)
 _native.register_signature("cml_xtr_reduce_scatter", [_P, _LL, _I, _I, _P, _I, _P, _P, _P, _I, _I, _I, _LL, _U, _P])
 _native.register_signature("cml_wait_signals", [_P, _I, _I, _U, _P])
+_native.register_signature("cml_xtr_rs_det_scratch_bytes", [_I, _I, _I], _SZ)
+_native.register_signature("cml_xtr_reduce_scatter_det", [_P, _LL, _I, _I, _P, _I, _P, _P, _P, _I, _I, _I, _U, _P])
+_native.register_signature("cml_xtr_det_reduce", [_P, _P, _I, _I, _I, _P])
 _native.register_signature("cml_prox_allgather", [_P, _I, _I, _P, _F, _F, _F, _F, _P, _P, _P, _I, _I, _P, _P, _U, _I, _P, _P])
 _native.register_signature("cml_prox_allgather_enet", [_P, _I, _I, _P, _F, _F, _F, _F, _F, _P, _P, _P, _I, _I, _P, _P, _U, _I, _P, _P])
 _native.register_signature("cml_xb_residual", [_P, _LL, _I, _I, _P, _F, _P, _P, _P, _P, _P, _P])
@@ -54,16 +57,28 @@ def to_bf16_padded(x: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------------------ path 2
 class XtrReduceScatter:
-    """``g_owned = sum_ranks (X_r^T R_r)[owned genes]`` with the reduction done by peer atomics inside the kernel."""
+    """``g_owned = sum_ranks (X_r^T R_r)[owned genes]`` with the reduction done by peer atomics inside the kernel.
 
-    def __init__(self, p: int, nb: int, device):
-        self.p, self.nb = p, nb
+    ``deterministic=True`` selects the fixed-order form: row chunks are added in chunk order and every source rank stores
+    its tile into its own slot at the owner, which adds the slots in rank order (``cml_xtr_det_reduce``) - no float atomics,
+    bit-identical from run to run, at the price of a world-times larger landing buffer and one small extra kernel."""
+
+    def __init__(self, p: int, nb: int, device, deterministic: bool = False, n_rows: Optional[int] = None):
+        self.p, self.nb, self.deterministic = p, nb, deterministic
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.genes_per_rank = equal_shard(p, self.world)
-        self.grad = symm.alloc((self.genes_per_rank * nb,), torch.float32, device)       # owner-side accumulator
         lib = _native.cuda()
-        self.scratch = torch.zeros(lib.cml_xtr_rs_scratch_bytes(p, nb), dtype=torch.uint8, device=device)
+        if deterministic:
+            if n_rows is None:
+                raise ValueError("the deterministic reduce-scatter sizes its chunk slices from the local row count: pass n_rows")
+            self.n_rows = n_rows
+            self.slots = symm.alloc((self.world * self.genes_per_rank * nb,), torch.float32, device)      # [world][genes_per_rank][nb]
+            self.grad = symm.alloc((self.genes_per_rank * nb,), torch.float32, device)
+            self.scratch = torch.zeros(lib.cml_xtr_rs_det_scratch_bytes(n_rows, p, nb), dtype=torch.uint8, device=device)
+        else:
+            self.grad = symm.alloc((self.genes_per_rank * nb,), torch.float32, device)       # owner-side accumulator
+            self.scratch = torch.zeros(lib.cml_xtr_rs_scratch_bytes(p, nb), dtype=torch.uint8, device=device)
         self.epoch = 0
 
     @property
@@ -78,6 +93,13 @@ class XtrReduceScatter:
         """Start the fused kernel for this rank's rows; returns the epoch to wait for."""
         self.epoch += 1
         n, ldx = x_bf16.shape
+        if self.deterministic:
+            assert n == self.n_rows, "deterministic mode was sized for a different local row count"
+            rc = _native.cuda().cml_xtr_reduce_scatter_det(
+                _native.ptr(x_bf16), ldx, n, self.p, _native.ptr(R), self.nb, _native.ptr(self.scratch), _ptr_array(self.slots.peer_ptrs),
+                _ptr_array(self.slots.signal_ptrs), self.rank, self.world, self.genes_per_rank, self.epoch, _native.stream_ptr())
+            _native.check(rc, "cml_xtr_reduce_scatter_det")
+            return self.epoch
         rc = _native.cuda().cml_xtr_reduce_scatter(
             _native.ptr(x_bf16), ldx, n, self.p, _native.ptr(R), self.nb, _native.ptr(self.scratch),
             _ptr_array(self.grad.peer_ptrs), _ptr_array(self.grad.signal_ptrs), self.rank, self.world, self.genes_per_rank, 0,
@@ -86,9 +108,14 @@ class XtrReduceScatter:
         return self.epoch
 
     def wait(self, epoch: Optional[int] = None) -> None:
-        rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(self.grad.signal_ptrs[self.rank]), SIG_GRAD, self.world,
+        buf = self.slots if self.deterministic else self.grad
+        rc = _native.cuda().cml_wait_signals(ctypes.c_void_p(buf.signal_ptrs[self.rank]), SIG_GRAD, self.world,
                                              self.epoch if epoch is None else epoch, _native.stream_ptr())
         _native.check(rc, "cml_wait_signals")
+        if self.deterministic:            # add the per-source slots in rank order
+            rc = _native.cuda().cml_xtr_det_reduce(_native.ptr(self.slots.local), _native.ptr(self.grad.local), self.genes_per_rank, self.nb,
+                                                   self.world, _native.stream_ptr())
+            _native.check(rc, "cml_xtr_det_reduce")
 
     def result(self) -> torch.Tensor:
         """Owned slice [genes_owned, nb] (valid after ``wait``); the caller clears it before the epoch after next."""

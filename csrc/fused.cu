@@ -45,7 +45,11 @@ template <int NB>
 __global__ void __launch_bounds__(kXtrThreads) xtr_reduce_scatter_kernel(
     const __nv_bfloat16* __restrict__ X, long long ldx, int n, int p, const float* __restrict__ R, float* __restrict__ partial,
     unsigned* __restrict__ tile_count, unsigned* __restrict__ done_count, Peers P, int genes_per_rank, int slot_base,
-    unsigned epoch, int rows_per_chunk) {
+    unsigned epoch, int rows_per_chunk, int deterministic) {
+  // deterministic != 0: no floating-point atomics anywhere.  Every row chunk writes its partial into its own slice of
+  // `partial` ([chunks][p_pad][NB]), the last CTA of a gene tile adds the slices in chunk order, and the tile is STORED into
+  // the owner's per-source slot ([world][genes_per_rank][NB] at the owner) instead of being added to a shared accumulator;
+  // the owner sums the slots in rank order (xtr_det_reduce_kernel).  Same bytes over NVLink, world x the landing buffer.
   __shared__ float rs[256 * NB];
   __shared__ unsigned sh_last;
   const int tile = blockIdx.x, chunk = blockIdx.y;
@@ -80,13 +84,17 @@ __global__ void __launch_bounds__(kXtrThreads) xtr_reduce_scatter_kernel(
       }
     }
   }
-  // ---- phase 1: fold this chunk's partial into the rank-local tile (L2 atomics)
+  // ---- phase 1: fold this chunk's partial into the rank-local tile (L2 atomics), or park it in the chunk's own slice
+  const size_t p_pad = (size_t)gridDim.x * kTileGenes;
   if (active) {
 #pragma unroll
     for (int g = 0; g < kGenesPerThread; ++g)
       if (j0 + g < p)
 #pragma unroll
-        for (int b = 0; b < NB; ++b) atomicAdd(&partial[(size_t)(j0 + g) * NB + b], acc[g][b]);
+        for (int b = 0; b < NB; ++b) {
+          if (deterministic) partial[((size_t)chunk * p_pad + (j0 + g)) * NB + b] = acc[g][b];
+          else atomicAdd(&partial[(size_t)(j0 + g) * NB + b], acc[g][b]);
+        }
   }
   __threadfence();
   __syncthreads();
@@ -98,6 +106,16 @@ __global__ void __launch_bounds__(kXtrThreads) xtr_reduce_scatter_kernel(
   const int jt0 = tile * kTileGenes, jt1 = min(p, jt0 + kTileGenes);
   const int total = (jt1 - jt0) * NB;                       // floats in this tile, contiguous in `partial`
   float* src = partial + (size_t)jt0 * NB;
+  if (deterministic) {
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+      float sum = 0.f;
+      for (int c = 0; c < (int)gridDim.y; ++c) sum += __ldcg(src + (size_t)c * p_pad * NB + e);      // chunk order: reproducible
+      const int j = jt0 + e / NB;
+      const int owner = min(j / genes_per_rank, P.world - 1);
+      // slot of THIS source rank at the owner: [rank][gene - owner * genes_per_rank][b]
+      P.buf[owner][(size_t)slot_base + ((size_t)P.rank * genes_per_rank + (j - owner * genes_per_rank)) * NB + (e % NB)] = sum;
+    }
+  } else
   for (int e = threadIdx.x * 4; e < total; e += blockDim.x * 4) {
     const int j = jt0 + e / NB;                              // gene of the first element of this quad
     const int owner = min(j / genes_per_rank, P.world - 1);
@@ -140,6 +158,15 @@ __global__ void wait_signals_kernel(const unsigned* pad, int base, int world, un
       if (timeout_cycles > 0 && clock64() - t0 > timeout_cycles) __trap();
     }
   }
+}
+
+// Deterministic mode, owner side: grad[j][b] = sum over source ranks (in rank order) of slots[r][j][b].
+__global__ void xtr_det_reduce_kernel(const float* __restrict__ slots, float* __restrict__ grad, int genes_per_rank, int nb, int world) {
+  const size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x, total = (size_t)genes_per_rank * nb;
+  if (e >= total) return;
+  float s = 0.f;
+  for (int r = 0; r < world; ++r) s += __ldcg(slots + (size_t)r * total + e);
+  grad[e] = s;
 }
 
 // ---------------------------------------------------------------------------------------- owner-side update
@@ -441,6 +468,58 @@ size_t cml_xtr_rs_scratch_bytes(int p, int nb) {
   return (size_t)tiles * cml::kTileGenes * nb * sizeof(float) + (size_t)(tiles + 4) * sizeof(unsigned) + 64;
 }
 
+namespace {
+void xtr_chunking(int n, int tiles, int& chunks, int& rows_per_chunk) {
+  chunks = cml::ceil_div(cml::sm_count() * 8, tiles);            // enough row chunks for ~8 CTAs per SM
+  rows_per_chunk = cml::ceil_div(cml::ceil_div(n, chunks), 256) * 256;
+  chunks = cml::ceil_div(n, rows_per_chunk);
+}
+}  // namespace
+
+// Deterministic form: scratch holds one partial slice per row chunk (it need not be zero: every word is written before it
+// is read) followed by the tile counters (zero before the first call, left zero by every call).
+size_t cml_xtr_rs_det_scratch_bytes(int n, int p, int nb) {
+  const int tiles = cml::ceil_div(p, cml::kTileGenes);
+  int chunks, rpc;
+  xtr_chunking(n, tiles, chunks, rpc);
+  return (size_t)chunks * tiles * cml::kTileGenes * nb * sizeof(float) + (size_t)(tiles + 4) * sizeof(unsigned) + 64;
+}
+
+// peer_slots[r]: owner r's landing buffer [world][genes_per_rank][nb] (every word of source `rank`'s slice is overwritten).
+// After cml_wait_signals on the owner, cml_xtr_det_reduce sums its slots in rank order into grad_owned [genes_per_rank][nb].
+int cml_xtr_reduce_scatter_det(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
+                               const void* const* peer_slots, const void* const* peer_sigs, int rank, int world, int genes_per_rank,
+                               unsigned epoch, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(n > 0 && p > 0 && ldx % 8 == 0 && ldx >= p, CML_EINVAL, "cml_xtr_reduce_scatter_det: bad shape n=%d p=%d ldx=%lld", n, p, ldx);
+  CML_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, CML_EINVAL, "cml_xtr_reduce_scatter_det: bad rank/world");
+  CML_REQUIRE(nb == 1 || nb == 4 || nb == 8, CML_EINVAL, "cml_xtr_reduce_scatter_det: nb must be 1, 4 or 8 (got %d)", nb);
+  const int tiles = ceil_div(p, kTileGenes);
+  int chunks, rows_per_chunk;
+  xtr_chunking(n, tiles, chunks, rows_per_chunk);
+  float* partial = static_cast<float*>(scratch);
+  unsigned* tile_count = reinterpret_cast<unsigned*>(partial + (size_t)chunks * tiles * kTileGenes * nb);
+  unsigned* done = tile_count + tiles;
+  Peers P = make_peers(peer_slots, peer_sigs, rank, world);
+  dim3 grid(tiles, chunks);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* X = static_cast<const __nv_bfloat16*>(x_bf16);
+  if (nb == 1) xtr_reduce_scatter_kernel<1><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, 0, epoch, rows_per_chunk, 1);
+  else if (nb == 4) xtr_reduce_scatter_kernel<4><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, 0, epoch, rows_per_chunk, 1);
+  else xtr_reduce_scatter_kernel<8><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, 0, epoch, rows_per_chunk, 1);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
+int cml_xtr_det_reduce(const float* slots, float* grad_owned, int genes_per_rank, int nb, int world, void* stream) {
+  using namespace cml;
+  const size_t total = (size_t)genes_per_rank * nb;
+  if (total == 0) return 0;
+  xtr_det_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(slots, grad_owned, genes_per_rank, nb, world);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
+
 // scratch must be zero before the FIRST call and is left zero by every call.
 int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
                            const void* const* peer_bufs, const void* const* peer_sigs, int rank, int world,
@@ -461,9 +540,9 @@ int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, cons
   dim3 grid(tiles, chunks);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* X = static_cast<const __nv_bfloat16*>(x_bf16);
-  if (nb == 1) xtr_reduce_scatter_kernel<1><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk);
-  else if (nb == 4) xtr_reduce_scatter_kernel<4><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk);
-  else xtr_reduce_scatter_kernel<8><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk);
+  if (nb == 1) xtr_reduce_scatter_kernel<1><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk, 0);
+  else if (nb == 4) xtr_reduce_scatter_kernel<4><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk, 0);
+  else xtr_reduce_scatter_kernel<8><<<grid, kXtrThreads, 0, st>>>(X, ldx, n, p, R, partial, tile_count, done, P, genes_per_rank, (int)slot_base, epoch, rows_per_chunk, 0);
   CML_LAUNCH_CHECK();
   return 0;
 }

@@ -247,6 +247,15 @@ size_t cml_xtr_rs_scratch_bytes(int p, int nb);
 int cml_xtr_reduce_scatter(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
     const void* const* peer_bufs, const void* const* peer_sigs, int rank, int world,
     int genes_per_rank, long long slot_base, unsigned epoch, void* stream);
+/* Deterministic form of the reduce-scatter (a fixed reduction order per flag): no floating-point atomics - row
+ * chunks are added in chunk order, and every source rank STORES its tile into its own slot of the owner's landing buffer
+ * peer_slots[owner] = [world][genes_per_rank][nb]; after cml_wait_signals the owner calls cml_xtr_det_reduce, which adds the
+ * slots in rank order.  Bit-identical results from run to run and for any thread / CTA schedule. */
+size_t cml_xtr_rs_det_scratch_bytes(int n, int p, int nb);
+int cml_xtr_reduce_scatter_det(const void* x_bf16, long long ldx, int n, int p, const float* R, int nb, void* scratch,
+                               const void* const* peer_slots, const void* const* peer_sigs, int rank, int world, int genes_per_rank,
+                               unsigned epoch, void* stream);
+int cml_xtr_det_reduce(const float* slots, float* grad_owned, int genes_per_rank, int nb, int world, void* stream);
 int cml_wait_signals(const void* pad, int base, int world, unsigned epoch, void* stream);
 int cml_prox_allgather(float* grad_owned, int genes_owned, int gene0, const float* pf, float step, float lambda, float inv_n,
     float momentum, const void* const* beta_bufs, const void* const* v_bufs, const void* const* peer_sigs,

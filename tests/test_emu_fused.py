@@ -170,3 +170,41 @@ def test_xb_residual_and_split_scoring_kernels():
     assert abs(float(loss) - float(ll)) < 1e-4
     g2, f2, t2 = F.best_splits_torch(hist, 1.0, 0.0, 0.1)
     assert torch.equal(feat, f2) and torch.equal(thr, t2) and torch.allclose(gain, g2, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_deterministic_reduce_scatter_is_bit_reproducible_and_exact(world):
+    """The fixed-order form of X^T R reduce-scatter: chunk slices added in chunk order, per-source slots added in rank order."""
+    g = torch.Generator().manual_seed(30 + world)
+    n_loc, p, nb = 700, 1100, 4
+    gpr = (p + world - 1) // world
+    ld = (p + 7) // 8 * 8
+    Xb = []
+    for r in range(world):
+        t = torch.zeros(n_loc, ld, dtype=torch.bfloat16)
+        t[:, :p] = torch.randn(n_loc, p, generator=g).to(torch.bfloat16)
+        Xb.append(t)
+    R = [torch.randn(n_loc, nb, generator=g).contiguous() for _ in range(world)]
+    expect = sum(Xb[r][:, :p].float().t().double() @ R[r].double() for r in range(world))
+    runs = []
+    for seed in (1, 9):
+        with _native.emulation(seed=seed, sms=2):
+            lib = _native.cuda()
+            slots = [torch.full((world * gpr * nb,), float("nan")) for _ in range(world)]        # stale contents must not matter
+            sig = [torch.zeros(64, dtype=torch.int32) for _ in range(world)]
+            for r in range(world):
+                scratch = torch.zeros(lib.cml_xtr_rs_det_scratch_bytes(n_loc, p, nb), dtype=torch.uint8)
+                rc = lib.cml_xtr_reduce_scatter_det(P(Xb[r]), ld, n_loc, p, P(R[r]), nb, P(scratch), _ptrs(slots), _ptrs(sig), r, world, gpr, 1, None)
+                assert rc == 0, lib.cml_last_error()
+            grads = []
+            for r in range(world):
+                assert lib.cml_wait_signals(P(sig[r]), F.SIG_GRAD, world, 1, None) == 0
+                gr = torch.empty(gpr * nb)
+                lo, hi = r * gpr, min(p, (r + 1) * gpr)
+                # genes beyond p in the last owner's slice were never written: reduce only what exists
+                assert lib.cml_xtr_det_reduce(P(slots[r]), P(gr), gpr, nb, world, None) == 0
+                grads.append(gr[: (hi - lo) * nb].view(hi - lo, nb).clone())
+                assert torch.allclose(grads[-1].double(), expect[lo:hi], rtol=1e-4, atol=1e-3)
+        runs.append(grads)
+    for a, b in zip(*runs):
+        assert torch.equal(a, b)                     # same bits whatever the thread order
