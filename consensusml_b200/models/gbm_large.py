@@ -226,6 +226,17 @@ class GBMLarge:
 
     def decision_function(self, bins: torch.Tensor, n: int) -> torch.Tensor:
         dev = bins.device
+        if _native.on_device(bins) and self.trees:
+            # one kernel: every sample walks all trees (csrc/gbm.cu gbm_predict_kernel)
+            feat = torch.stack([t.feat for t in self.trees]).contiguous()
+            thr = torch.stack([t.thr for t in self.trees]).contiguous()
+            val = torch.stack([t.value for t in self.trees]).float().contiguous()
+            out = torch.empty(n, device=dev)
+            P = _native.ptr
+            rc = _native.cuda().cml_gbm_predict(P(bins), bins.shape[1], n, len(self.trees), self.max_depth, P(feat), P(thr), P(val), P(out),
+                                                _native.stream_ptr())
+            _native.check(rc, "cml_gbm_predict")
+            return out
         ar = torch.arange(n, device=dev)
         D = self.max_depth
         margin = torch.zeros(n, device=dev)

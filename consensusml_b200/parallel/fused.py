@@ -39,6 +39,7 @@ _native.register_signature("cml_split_score_gain", [_P, _I, _I, _I, _F, _F, _F, 
 _native.register_signature("cml_split_score_gain_at", [_P, _I, _I, _I, _F, _F, _F, _P, _I, _P])
 _native.register_signature("cml_hist_build", [_P, _LL, _I, _I, _I, _P, _P, _I, _P, _P, _P, _P, _P, _P, _I, _I, _I, _U, _I, _F, _F, _P])
 _native.register_signature("cml_gbm_grad", [_P, _P, _P, _I, _P])
+_native.register_signature("cml_gbm_predict", [_P, _LL, _I, _I, _I, _P, _P, _P, _P, _P])
 _native.register_signature("cml_gbm_totals", [_P, _P, _I, _I, _P, _P])
 _native.register_signature("cml_hist_derive", [_P, _P, _P, _P, _P, _LL, _I, _P])
 _native.register_signature("cml_gbm_route", [_P, _LL, _P, _P, _P, _P, _P, _I, _I, _P])

@@ -107,10 +107,44 @@ __global__ void gbm_route_kernel(const unsigned char* __restrict__ bins, long lo
   node[i] = (short)(2 * j + (b > (int)thr[j] ? 1 : 0));
 }
 
+// Margin of every sample under T level-stored trees (complete binary trees of depth D): one thread walks one sample through
+// all trees.  feat / thr [T][2^D - 1] (feat < 0: the walk stops at that node), value [T][2^(D+1) - 1].
+__global__ void gbm_predict_kernel(const unsigned char* __restrict__ bins, long long n_pad, int n, int T, int D,
+                                   const long long* __restrict__ feat, const long long* __restrict__ thr, const float* __restrict__ value,
+                                   float* __restrict__ margin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int n_int = (1 << D) - 1, n_all = (1 << (D + 1)) - 1;
+  float m = 0.f;
+  for (int t = 0; t < T; ++t) {
+    const long long* ft = feat + (size_t)t * n_int;
+    const long long* tt = thr + (size_t)t * n_int;
+    int node = 0, level = 0;
+    for (; level < D; ++level) {
+      const int idx = (1 << level) - 1 + node;
+      const long long f = ft[idx];
+      if (f < 0) break;
+      node = 2 * node + ((int)bins[(size_t)f * n_pad + i] > (int)tt[idx] ? 1 : 0);
+    }
+    m += value[(size_t)t * n_all + (1 << level) - 1 + node];
+  }
+  margin[i] = m;
+}
+
 }  // namespace
 }  // namespace cml
 
 extern "C" {
+
+int cml_gbm_predict(const unsigned char* bins, long long n_pad, int n, int T, int D, const long long* feat, const long long* thr,
+                    const float* value, float* margin, void* stream) {
+  using namespace cml;
+  CML_REQUIRE(n >= 0 && T >= 0 && D >= 0 && D <= 20, CML_EINVAL, "cml_gbm_predict: bad shape");
+  if (n == 0) return 0;
+  gbm_predict_kernel<<<ceil_div(n, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(bins, n_pad, n, T, D, feat, thr, value, margin);
+  CML_LAUNCH_CHECK();
+  return 0;
+}
 
 int cml_gbm_grad(const float* margin, const float* y, void* gh, int n, void* stream) {
   using namespace cml;

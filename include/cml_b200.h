@@ -306,6 +306,9 @@ int cml_split_score_gain_at(const float* hist, int n_nodes, int p, int nbins, fl
  * the samples to the next level (or out of the tree, adding the node value to the margin).  xgboost semantics,
  * cml_targetaml_seanalysis.Rmd:1164-1186. */
 int cml_gbm_grad(const float* margin, const float* y, void* gh, int n, void* stream);
+/* margin[i] = sum over T level-stored trees (depth D; feat / thr [T][2^D - 1], value [T][2^(D+1) - 1]) of the value where sample i stops */
+int cml_gbm_predict(const unsigned char* bins, long long n_pad, int n, int T, int D, const long long* feat, const long long* thr,
+                    const float* value, float* margin, void* stream);
 int cml_gbm_totals(const short* node, const void* gh, int n, int n_nodes, float* tot, void* stream);
 int cml_hist_derive(float* slots, const float* parent, float* full, const short* slot_of, const float* count, long long cells,
                     int n_nodes, void* stream);

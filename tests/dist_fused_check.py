@@ -236,6 +236,22 @@ def main():
                 print(f"[{rank}] EXPERIMENTAL gemm_rs tma={use_tma} rows={rt.shape[0]} rel err {err:.2e}", flush=True)
                 xok &= err < 2e-3
                 torch.cuda.synchronize(); op.bufs[0].barrier()
+        # deterministic reduce-scatter: two launches give the same bits, and agree with the atomic form
+        g = torch.Generator().manual_seed(77)
+        Rd = torch.randn(n, 4, generator=g)[lo:hi].contiguous().to(dev)
+        xbd = F.to_bf16_padded(xl)
+        rsd = F.XtrReduceScatter(p, 4, dev, deterministic=True, n_rows=hi - lo)
+        outs = []
+        for rep in range(2):
+            rsd.launch(xbd, Rd)
+            rsd.wait()
+            torch.cuda.synchronize()
+            outs.append(rsd.result().clone())
+            torch.cuda.synchronize(); rsd.grad.barrier()
+        refd = F.xtr_reduce_scatter_unfused(xbd[:, :p], Rd, p)
+        errd = float((outs[0] - refd).abs().max() / refd.abs().max())
+        print(f"[{rank}] EXPERIMENTAL deterministic xtr_rs: bit-equal across launches {bool(torch.equal(outs[0], outs[1]))}, rel err {errd:.2e}", flush=True)
+        xok &= bool(torch.equal(outs[0], outs[1])) and errd < 1e-4
         G.set_staged_grouping(True)
         got_g = F.gram_allgather(xl, kernel="radial", n_total=n)
         G.set_staged_grouping(False)

@@ -222,7 +222,13 @@ def case_large_gbm_kernel_level_loop_builds_the_same_trees_as_the_torch_path(be)
             assert torch.equal(a.thr[split], _h(b.thr)[split])
             assert (a.value - _h(b.value)).abs().max() < 2e-4
         assert torch.allclose(ref.importance_gain_, _h(got.importance_gain_), rtol=2e-3, atol=1e-3)
-    assert _auc_torch(_h(got.predict_proba(be.dev(x))), y) > 0.8
+    with be.ctx(seed=1):
+        pr_kernel = _h(got.predict_proba(be.dev(x)))                     # gbm_predict_kernel
+    got_host = GBMLarge(max_depth=3, nbins=32)
+    got_host.trees = [type(t)(_h(t.feat), _h(t.thr), _h(t.value)) for t in got.trees]
+    got_host.cuts = _h(got.cuts)
+    assert torch.allclose(pr_kernel, got_host.predict_proba(x), atol=1e-6)      # ... equals the torch walk over the same trees
+    assert _auc_torch(pr_kernel, y) > 0.8
 
 
 def case_size_factor_and_plda_score_kernels(be):
