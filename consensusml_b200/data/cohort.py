@@ -104,6 +104,9 @@ class Cohort:
         """Content hash of what a model fit depends on: gene and sample ids, the label and split columns and the assay
         values.  Checkpoints are keyed by it, so two cohorts of the same shape never share a cached result."""
         import hashlib
+        cached = getattr(self, "_fingerprint", None)
+        if cached is not None and cached[0] == (label_col, split_col, self.assay.data_ptr(), self.assay._version):
+            return cached[1]                      # same object, assay not written since: skip the device read-back and the hash
         h = hashlib.sha256()
         h.update("\x1f".join(self.gene_ids).encode())
         h.update(b"\x1e")
@@ -114,7 +117,9 @@ class Cohort:
                 h.update("\x1f".join(map(str, self.col_data[col].tolist())).encode())
         a = self.assay.detach().to("cpu", torch.float64).contiguous()
         h.update(a.numpy().tobytes())
-        return h.hexdigest()[:24]
+        fp = h.hexdigest()[:24]
+        self._fingerprint = ((label_col, split_col, self.assay.data_ptr(), self.assay._version), fp)
+        return fp
 
     # ---- persistence --------------------------------------------------------------------
     def save(self, path: str) -> None:
