@@ -44,8 +44,17 @@ def main(argv=None) -> int:
     import pandas as pd
     import torch
     from .. import pipeline
+    # under torchrun: one process per GPU; the pipeline spreads its stages over the ranks and rank 0 reports
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = 0
+    if world > 1 and args.command in ("run", "multiclass"):
+        from ..parallel import dist as PD
+        rank, world, ddev = PD.init()
+        if cfg.device == "auto":
+            cfg.device = str(ddev)
     dev = pipeline.resolve_device(cfg)
     os.makedirs(cfg.io.out_dir, exist_ok=True)
+    say = print if rank == 0 else (lambda *a, **k: None)
     if args.command == "concat":
         from ..io import counts as IC
         if not args.files:
@@ -61,7 +70,7 @@ def main(argv=None) -> int:
         return 0
     if args.command == "run" and args.counts is None:
         summary = pipeline.run(cfg)
-        print(json.dumps(summary, indent=1, default=str))
+        say(json.dumps(summary, indent=1, default=str))
         return 0
     if args.command in ("run", "multiclass"):
         from ..cohort import ops as CO
@@ -76,12 +85,19 @@ def main(argv=None) -> int:
         if args.command == "run":
             if len(levels) != 2:
                 ap.error("'run' needs a two-level group column; use 'multiclass'")
-            co = pipeline.cohort_from_counts(counts.to(dev), genes, samples, lab, train, cfg)
+            if world > 1:
+                # every rank read the CSV; it keeps its own block of samples: normalisation runs sample-sharded and the voom
+                # prefilter gene-sharded (stats/sharded.py), every rank ends up with the same DEG cohort
+                from ..parallel.dist import shard_bounds
+                lo, hi = shard_bounds(len(samples), world, rank)
+                co = pipeline.cohort_from_counts_sharded(counts[:, lo:hi].contiguous().to(dev), genes, samples, lab, train, cfg)
+            else:
+                co = pipeline.cohort_from_counts(counts.to(dev), genes, samples, lab, train, cfg)
             summary = pipeline.run(cfg, co)
         else:
             co = pipeline.multiclass_cohort_from_counts(counts.to(dev), genes, samples, lab, train, cfg)
             summary = pipeline.run_multiclass(cfg, co, class_names={i: str(v) for i, v in enumerate(levels)})
-        print(json.dumps(summary, indent=1, default=str))
+        say(json.dumps(summary, indent=1, default=str))
         return 0
     if args.command == "lasso":
         from .. import consensus, datasets

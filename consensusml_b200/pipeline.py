@@ -155,6 +155,30 @@ def build_tasks(cfg: Config, cohort: Cohort, dev: torch.device, store: Optional[
         # the exclusion chain is sequential (each replicate removes the genes the previous ones selected): one task
         add("lasso", 4.0 + 0.75 * cfg.lasso.exclusion_reps, lasso_task, "lasso")
 
+    if cfg.lasso.enabled and cfg.lasso.stability_boot > 0:
+        # stability selection (north-star config 5): bootstrap replicates x alpha grid, each replicate a full 100-lambda path.
+        # Replicates are independent: fixed chunks of them are tasks, their selection counts add up.
+        from .ops import lasso as KL
+        lam_grid = KL.default_lambda_grid()
+        chunk = max(1, int(cfg.lasso.stability_chunk))
+        for ai, a in enumerate(cfg.lasso.stability_alphas):
+            for c0 in range(0, cfg.lasso.stability_boot, chunk):
+                nb = min(chunk, cfg.lasso.stability_boot - c0)
+
+                def stab_task(ai=ai, a=a, c0=c0, nb=nb):
+                    from .ops.replicate import replicate_weights
+                    xtr, ytr, _, _ = data()
+                    n, p = xtr.shape
+                    on_dev = KL._native.on_device(xtr)
+                    packed = KL.pack_design(xtr) if on_dev else None
+                    n_pad = packed[1] if on_dev else n
+                    freq = torch.zeros(len(lam_grid), p, dtype=torch.float32, device=dev)
+                    w = replicate_weights(nb, n, mode="bootstrap", seed=cfg.lasso.seed + 7919 * ai, device=dev, n_pad=n_pad, rep0=c0)
+                    KL.lognet_path(xtr, ytr, w[:, :n], lam_grid, alpha=float(a), want_eta=False, packed=packed, freq_out=freq,
+                                   padded_weights=w if on_dev else None, want_coef=False)
+                    return {"counts": _host(freq), "n": nb}
+                add(f"stab_a{ai}_b{c0}", 0.12 * nb / 250.0, stab_task, f"stab_a{ai}")
+
     if cfg.svm.enabled:
         k = 0
         for kern in cfg.svm.kernels:
@@ -267,6 +291,24 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
         importances["lasso"] = st.df["lasso_coef_rep1"].to_numpy()
         summary["lasso"] = {**lr["rep1"], "n_genes": [len(nz) for nz in lr["nonzero"]], "test_errors": lr["test_error"],
                             "jerr": lr["jerr"][0], "genes_rep1": sorted(lr["nonzero"][0])}
+    if cfg.lasso.enabled and cfg.lasso.stability_boot > 0:
+        maxf = np.zeros(len(genes))
+        per_alpha = {}
+        for ai, a in enumerate(cfg.lasso.stability_alphas):
+            names = [t.name for t in tasks if t.group == f"stab_a{ai}"]
+            if not all(ok(nm) for nm in names):
+                continue
+            cnt = sum(results[nm]["counts"] for nm in names)
+            nrep = sum(results[nm]["n"] for nm in names)
+            f = (cnt / max(nrep, 1)).max(0)                          # max over the lambda grid of the selection frequency
+            per_alpha[str(a)] = int((f >= cfg.lasso.stability_threshold).sum())
+            maxf = np.maximum(maxf, f)
+        if per_alpha:
+            st.add("stability_max_freq", maxf)
+            importances["stability"] = maxf
+            summary["stability"] = {"n_boot": cfg.lasso.stability_boot, "alphas": list(cfg.lasso.stability_alphas),
+                                    "stable_genes_per_alpha": per_alpha, "stable_genes": int((maxf >= cfg.lasso.stability_threshold).sum()),
+                                    "threshold": cfg.lasso.stability_threshold}
     if cfg.svm.enabled:
         k = 0
         for kern in cfg.svm.kernels:

@@ -52,7 +52,10 @@ class LassoConfig:
     nfolds: Optional[int] = None           # None = leave-one-out (SEA:100)
     exclusion_reps: int = 15              # SEA:728-773 ran 15 replicates
     seed: int = 2019
-    stability_boot: int = 0
+    stability_boot: int = 0                # > 0: stability selection with this many bootstrap replicates per alpha (BASELINE config 5)
+    stability_alphas: List[float] = field(default_factory=lambda: [1.0, 0.5])
+    stability_chunk: int = 250             # bootstraps per scheduler task (fixed: results do not depend on the world size)
+    stability_threshold: float = 0.6       # a gene is "stable" when its maximal selection frequency reaches this
 
 
 @dataclass

@@ -19,7 +19,7 @@ def main():
     out = sys.argv[1]
     cuda = "--cuda" in sys.argv
     rank, world, dev = D.init(None if cuda else "gloo")
-    ov = ["lasso.exclusion_reps=2", "rf.n_trees=[90, 150]", "rf.chunk=40", "rf.proximity=true",
+    ov = ["lasso.exclusion_reps=2", "lasso.stability_boot=6", "lasso.stability_chunk=2", "rf.n_trees=[90, 150]", "rf.chunk=40", "rf.proximity=true",
           'gbm.reps=[{"max_depth": 2, "nrounds": 2}, {"max_depth": 3, "nrounds": 3}]', "mlp.enabled=true", "mlp.epochs=20",
           "mlp.hidden=[8]", "mlp.lr=[0.003]", "resume=false", "checkpoint=false", "device=" + ("cuda" if cuda else "cpu")]
     cfg = C.load(None, ov + ["io.out_dir=" + os.path.join(out, "dist")])
@@ -44,6 +44,7 @@ def main():
                 if f in sa:
                     assert abs(sa[f] - sb[f]) < 1e-9, (k, f, sa[f], sb[f])
         assert det["summary"]["consensus"]["top"] == ref["summary"]["consensus"]["top"]
+        assert det["summary"]["stability"] == ref["summary"]["stability"] and det["summary"]["stability"]["stable_genes"] > 0
         assert os.path.exists(os.path.join(out, "dist", "standouttable.csv"))
         print("PIPELINE DIST OK", sched["critical"], flush=True)
     dist.barrier()
