@@ -30,8 +30,27 @@ from ..parallel.dist import all_reduce_
 
 def quantile_bin(x_local: torch.Tensor, nbins: int = 256, sample: int = 200000):
     """Quantile cut points from (a subsample of) this rank's rows, averaged across ranks, and the uint8 bins
-    [p, n_pad] of the local rows.  Returns (bins, cuts [p, nbins-1])."""
+    [p, n_pad] of the local rows.  Returns (bins, cuts [p, nbins-1]).
+
+    On the kernel path the cut points are a ``models.trees.Binner``: rank 0 sorts (a strided sample of) each gene's values
+    in shared memory (``cml_quantile_edges`` - torch.quantile cannot take a 125k x 20k shard), its edge table is broadcast,
+    and every rank bins its own rows against it (``cml_apply_bins``), so all ranks share one binning."""
     n, p = x_local.shape
+    if _native.on_device(x_local) and n > 256:
+        from .trees import Binner
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        if world == 1 or dist.get_rank() == 0:
+            binner, bins = Binner.fit(x_local, max_bin=nbins)
+            edges, n_edges = binner.edges, binner.n_edges
+        else:
+            edges = torch.empty(p, 256, dtype=torch.float32, device=x_local.device)
+            n_edges = torch.empty(p, dtype=torch.int32, device=x_local.device)
+        if world > 1:
+            dist.broadcast(edges, src=0)
+            dist.broadcast(n_edges, src=0)
+            binner = Binner(edges, n_edges, max(2, int(n_edges.max().item())))
+            bins = binner.transform(x_local)
+        return bins, binner
     sub = x_local if n <= sample else x_local[(torch.arange(sample, device=x_local.device) * n) // sample]    # deterministic stride
     qs = torch.linspace(0, 1, nbins + 1, device=x_local.device)[1:-1]
     cuts = torch.quantile(sub.float(), qs, dim=0).t().contiguous()            # [p, nbins-1]
@@ -43,7 +62,9 @@ def quantile_bin(x_local: torch.Tensor, nbins: int = 256, sample: int = 200000):
     return bins, cuts
 
 
-def apply_cuts(x: torch.Tensor, cuts: torch.Tensor) -> torch.Tensor:
+def apply_cuts(x: torch.Tensor, cuts) -> torch.Tensor:
+    if hasattr(cuts, "transform"):                 # a Binner (kernel path)
+        return cuts.transform(x)
     n, p = x.shape
     n_pad = (n + 3) // 4 * 4
     bins = torch.zeros(p, n_pad, dtype=torch.uint8, device=x.device)

@@ -330,7 +330,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
                 continue
             parts = [results[t.name] for t in tasks if t.group == f"rf_{tag}"]         # task order = tree order
             rf = RandomForest(n_trees=nt, proximity=cfg.rf.proximity, seed=cfg.rf.seed)
-            rf._bins, rf._yf = torch.zeros(1), ytr_t.float()                            # merge on the host
+            rf._bins, rf._yf = torch.zeros(1), ytr_t.float().cpu()                      # merge on the host (parts are host arrays)
             rf.finish(parts)
             imp = rf.importance_.numpy()
             st.add(f"rfnb_{tag}_MeanDecNodeImp", imp)
