@@ -1128,6 +1128,7 @@ int launch_team(const LognetParams& P, int grid, cudaStream_t st) {
   const size_t per_slot = (size_t)P.n_pad * 4 + 8;
   int cap = base + 16 < budget ? (int)((budget - base - 16) / per_slot) : 0;
   if (cap > 32767) cap = 32767;
+  if (const char* e = getenv("CML_LASSO_TEAM_CAP")) cap = min(cap, max(0, atoi(e)));      // tests: force the cache to overflow
   const size_t smem = base + (size_t)cap * per_slot + 16;
   CML_CUDA(cudaFuncSetAttribute(lognet_path_cta_kernel<NPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   lognet_path_cta_kernel<NPL><<<grid, 32 * kTeamWarps, smem, st>>>(P, cap);

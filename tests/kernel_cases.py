@@ -286,7 +286,15 @@ def case_lasso_cta_per_fit_kernel_is_bit_identical_to_the_warp_kernel(be):
     lam = np.geomspace(0.3, 0.02, 14)
     old = os.environ.get("CML_LASSO_TEAM")
     try:
-        for kw in (dict(), dict(alpha=0.5, intercept=True), dict(modified_newton=True)):
+        # the last variant shrinks the column cache to 5 slots: most screened features then stay in global memory and the
+        # solver mixes cached and uncached coordinates
+        for kw in (dict(), dict(alpha=0.5, intercept=True), dict(modified_newton=True), dict(_cap="5")):
+            kw = dict(kw)
+            cap = kw.pop("_cap", None)
+            if cap is None:
+                os.environ.pop("CML_LASSO_TEAM_CAP", None)
+            else:
+                os.environ["CML_LASSO_TEAM_CAP"] = cap
             res = {}
             for mode in ("0", "1"):
                 os.environ["CML_LASSO_TEAM"] = mode
@@ -303,6 +311,7 @@ def case_lasso_cta_per_fit_kernel_is_bit_identical_to_the_warp_kernel(be):
             for i in range(B):
                 assert torch.equal(_h(a.dense(i)), _h(b_.dense(i))), (kw, i)
     finally:
+        os.environ.pop("CML_LASSO_TEAM_CAP", None)
         if old is None:
             os.environ.pop("CML_LASSO_TEAM", None)
         else:

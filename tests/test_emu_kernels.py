@@ -290,3 +290,38 @@ import kernel_cases as KC
 @pytest.mark.parametrize("case", [n for n in dir(KC) if n.startswith("case_")])
 def test_round2_kernel_on_the_host_execution_model(case):
     getattr(KC, case)(KC.EmuBackend())
+
+
+def test_path_kernels_reproduce_the_stored_glmnet_path_on_the_real_cohort(aml, glmnet_oracle):
+    """The reference's own training matrix (93 x 1984) and lambda grid through BOTH path kernels on the host execution
+    model, against the coefficient path stored in the reference's lasso_resultslist.rda: same 999 passes as glmnet, the same
+    support at lambda.min, coefficients to 1e-5 (fp32 kernel vs float64 Fortran)."""
+    import os
+    tr, _ = aml.split()
+    x, y = tr.design(torch.float32), tr.labels()
+    w = torch.ones(2, x.shape[0])
+    w[1, 0] = 0                                                       # a leave-one-out fold next to the full fit
+    lam = glmnet_oracle["rep1_lambda"]
+    ref = np.zeros((1984, 100))
+    ref[glmnet_oracle["rep1_train_rows"]] = glmnet_oracle["rep1_train_beta"]
+    ref = ref.T
+    old = os.environ.get("CML_LASSO_TEAM")
+    out = {}
+    try:
+        for mode in ("0", "1"):
+            os.environ["CML_LASSO_TEAM"] = mode
+            with _native.emulation(sms=2):
+                out[mode] = K.lognet_path(x, y, w, lam)
+    finally:
+        if old is None:
+            os.environ.pop("CML_LASSO_TEAM", None)
+        else:
+            os.environ["CML_LASSO_TEAM"] = old
+    for mode, pb in out.items():
+        beta = pb.dense(0).double().numpy()
+        assert int(pb.jerr.abs().max()) == 0 and int(pb.npasses[0]) == 999, (mode, pb.npasses)
+        assert np.abs(beta - ref).max() < 1e-5
+        assert set(np.flatnonzero(beta[89])) == set(np.flatnonzero(ref[89]))
+        assert np.abs(pb.dev_ratio[0].double().numpy() - glmnet_oracle["rep1_train_dev_ratio"]).max() < 1e-5
+    a, b = out["0"], out["1"]
+    assert torch.equal(a.npasses, b.npasses) and torch.equal(a.eta, b.eta) and torch.equal(a.dense(1), b.dense(1))
