@@ -191,3 +191,22 @@ def test_failed_stage_is_reported_not_fatal_when_fail_fast_is_off(tmp_path, monk
     assert len(s["consensus"]["top"]) == 50
     with pytest.raises(RuntimeError, match="injected fault"):
         pipeline.run(C.load(None, ov))
+
+
+@pytest.mark.slow
+def test_pipeline_on_the_kernel_path_under_emulation(tmp_path):
+    """pipeline.run with every stage on the kernel code paths (lasso path kernel in latency mode, SMO, tree level kernels,
+    metrics, MLP tail / Adam, replicate weights, stability selection), executed by the host execution model."""
+    from consensusml_b200 import _native
+    cfg = C.load(None, ["io.out_dir=" + str(tmp_path), "device=cpu", "lasso.exclusion_reps=1", "lasso.nfolds=4", "lasso.stability_boot=4",
+                        "lasso.stability_chunk=2", "rf.n_trees=[60]", "rf.chunk=30", 'gbm.reps=[{"max_depth": 2, "nrounds": 2}]',
+                        'svm.kernels=["linear"]', "svm.weightfilt=[null, 0.5]", "mlp.enabled=true", "mlp.epochs=15", "mlp.hidden=[8]",
+                        "mlp.lr=[0.003]", "mlp.weight_decay=[0.0]", "checkpoint=false"])
+    with _native.emulation(seed=1, sms=8):
+        s = pipeline.run(cfg)
+    assert "failed_tasks" not in s
+    assert len(s["lasso"]["genes_rep1"]) == 13 and s["lasso"]["auc"] > 0.95           # 4-fold CV picks a neighbouring lambda
+    assert s["xgb1"]["n_genes"] == 6 and abs(s["xgb1"]["train_error"] - 0.010753) < 1e-5 + 0.02
+    assert s["rf_60"]["oob_error"] < 0.2 and s["svm1"]["auc"] > 0.9 and s["svm2"]["auc"] > 0.9 and s["mlp"]["auc"] > 0.85
+    assert s["stability"]["stable_genes"] > 5 and len(s["consensus"]["top"]) == 50
+    assert os.path.exists(tmp_path / "standouttable.csv")
