@@ -218,15 +218,17 @@ def build_emu(force: bool = False) -> Path:
     gxx = shutil.which("g++") or "g++"
     flags = ["-O1", "-g", "-std=c++17", "-fPIC", "-DCML_EMU=1", "-fno-fast-math", "-ffp-contract=off", "-Wno-unknown-pragmas",
              "-Wno-attributes", "-I", str(INCLUDE), "-I", str(CSRC), "-I", str(CSRC / "emu"), "-include", str(CSRC / "emu" / "cuda_emu.h")]
-    if os.environ.get("CML_EMU_SANITIZE"):
-        flags += ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"]
+    san = os.environ.get("CML_EMU_SANITIZE")          # "1" / "address" = ASan + UBSan (needs LD_PRELOAD of libasan), "undefined" = UBSan only
+    san_flags = ["-fsanitize=undefined", "-fno-sanitize-recover=undefined"] if san == "undefined" else (["-fsanitize=address,undefined"] if san else [])
+    if san:
+        flags += san_flags + ["-fno-omit-frame-pointer"]
     objs = _compile_objects(gen, [gxx], flags, "emu", force)
     LIBDIR.mkdir(parents=True, exist_ok=True)
     newest = max(o.stat().st_mtime for o in objs)
     if force or not EMU_LIB.exists() or EMU_LIB.stat().st_mtime < newest:
         link = [gxx, "-shared", "-o", str(EMU_LIB)] + [str(o) for o in objs] + ["-lpthread"]
-        if os.environ.get("CML_EMU_SANITIZE"):
-            link += ["-fsanitize=address,undefined"]
+        if san:
+            link += san_flags
         _run(link, OBJDIR / "link_emu.log")
     return EMU_LIB
 

@@ -228,7 +228,7 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()
   g_rng = 0x9e3779b97f4a7c15ull ^ (seed * 0xbf58476d1ce4e5b9ull);
   if (g_rng == 0) g_rng = 1;
   if ((int)g_fibers.size() < nthreads) g_fibers.resize(nthreads);
-  g_smem.resize(smem_bytes + 64);
+  g_smem.resize(smem_bytes ? smem_bytes : 1);          // exact size: under ASan an access past the launch's dynamic shared memory is an error
   g_body = &body;
   g_blockDim = block;
   g_gridDim = grid;
