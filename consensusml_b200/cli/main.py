@@ -5,6 +5,8 @@ The reference has no CLI - its entry points are "open the notebook and run the c
   run         the full ensemble + consensus pipeline (default cohort: bundled TARGET-AML; with --counts/--groups: normalise,
               DE-prefilter and model your own two-group cohort, the Differential_Expression_and_Lasso.Rmd flow)
   multiclass  one-vs-rest ensemble + pan-class consensus on a counts CSV with a multi-level group column
+  acquire     query the GDC for the TARGET HTSeq count files, write id map + manifest, download, verify, build the counts CSV
+              (GDC_Data_Download.Rmd; --endpoint selects the API server, --clinical adds the clinical tables)
   concat      per-sample HTSeq count files -> one genes x samples counts CSV (Cat_Expn_Data.r)
   lasso       the reference's headline model only (runLasso + gene CSV)
   de          limma-voom DE on a counts CSV: writes the DEG table in the reference's format
@@ -22,11 +24,13 @@ import sys
 
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="consensusml_b200", description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
-    ap.add_argument("command", choices=["run", "multiclass", "concat", "lasso", "de", "normalize", "build", "config"])
+    ap.add_argument("command", choices=["run", "multiclass", "acquire", "concat", "lasso", "de", "normalize", "build", "config"])
     ap.add_argument("--config", default=None)
     ap.add_argument("--counts", default=None, help="genes x samples counts CSV")
     ap.add_argument("--groups", default=None, help="CSV with columns sample,group (1 = non-reference level)")
     ap.add_argument("--files", default=None, help="concat: glob pattern of the per-sample count files (sample id = file name up to the first dot)")
+    ap.add_argument("--endpoint", default=None, help="acquire: GDC API base URL (default https://api.gdc.cancer.gov)")
+    ap.add_argument("--clinical", action="store_true", help="acquire: also fetch the per-case clinical tables and the clinical supplements")
     ap.add_argument("--train-frac", type=float, default=2.0 / 3.0, help="run/multiclass on counts: stratified training fraction")
     ap.add_argument("overrides", nargs="*", help="section.key=value")
     args = ap.parse_intermixed_args(argv)
@@ -39,6 +43,20 @@ def main(argv=None) -> int:
         from .. import _build
         _build.build_all()
         print(_build.ptxas_report())
+        return 0
+    if args.command == "acquire":
+        from ..io import gdc
+        url = args.endpoint or gdc.GDC_API
+        counts, idmap = gdc.acquire(cfg.io.out_dir, url)
+        path = os.path.join(cfg.io.out_dir, "TARGET_HTSeq_Counts.csv")
+        counts.to_csv(path)
+        out = {"files": int(len(idmap)), "genes": int(counts.shape[0]), "samples": int(counts.shape[1]), "csv": path}
+        if args.clinical:
+            full = gdc.clinical(gdc.case_ids("TARGET-AML", url), url)
+            full.to_csv(os.path.join(cfg.io.out_dir, "TARGET_AML_clinical_GDC.csv"), index=False)
+            sup = gdc.clinical_supplements(os.path.join(cfg.io.out_dir, "Clinical_Data"), url)
+            out.update(clinical_rows=int(len(full)), clinical_supplements=len(sup))
+        print(json.dumps(out))
         return 0
     import numpy as np
     import pandas as pd
