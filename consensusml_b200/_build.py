@@ -33,9 +33,9 @@ HOST_LIB = LIBDIR / "libcml_host.so"
 EMU_LIB = LIBDIR / "libcml_emu.so"
 EMUDIR = ROOT / "build" / "emu"
 
-# kernels that only need warp / block primitives run under the host execution model (csrc/emu/cuda_emu.h);
-# the tcgen05 / TMA GEMMs (gemm_tcgen05.cu, gemm_rs.cu) do not
-EMU_EXCLUDE = {"gemm_tcgen05.cu", "gemm_rs.cu"}
+# every kernel source is also built for the host execution model (csrc/emu/): warp / block primitives in cuda_emu.h, the
+# asynchronous units the tcgen05 / TMA GEMMs drive (mbarrier, TMA, TMEM, tcgen05.mma) in async_emu.cpp
+EMU_EXCLUDE: set = set()
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -215,6 +215,7 @@ def build_emu(force: bool = False) -> Path:
             dst.write_text(text)
         gen.append(dst)
     gen.append(CSRC / "emu" / "cuda_emu.cpp")
+    gen.append(CSRC / "emu" / "async_emu.cpp")
     gxx = shutil.which("g++") or "g++"
     flags = ["-O1", "-g", "-std=c++17", "-fPIC", "-DCML_EMU=1", "-fno-fast-math", "-ffp-contract=off", "-Wno-unknown-pragmas",
              "-Wno-attributes", "-I", str(INCLUDE), "-I", str(CSRC), "-I", str(CSRC / "emu"), "-include", str(CSRC / "emu" / "cuda_emu.h")]

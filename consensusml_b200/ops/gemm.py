@@ -45,7 +45,7 @@ def to_bf16_rows(x: torch.Tensor, *, shift: float = 0.0, col_shift: Optional[tor
                  norm_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """Row-major fp32 [rows, cols] -> (bf16 [rows, pad8(cols)] zero padded, squared norms of the rounded rows).
     Optional per-column centring / scaling is fused (z-scoring for e1071's ``scale = TRUE``)."""
-    assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    assert _native.on_device(x) and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
     rows, cols = x.shape
     ld = _pad8(cols)
     y = out if out is not None else torch.empty(rows, ld, dtype=torch.bfloat16, device=x.device)
@@ -124,7 +124,7 @@ MIN_K = 64
 def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optional[float] = None) -> torch.Tensor:
     """K(i, j) = exp(-gamma |x_i - z_j|^2); gamma defaults to 1/p as in e1071."""
     gamma = 1.0 / x.shape[1] if gamma is None else gamma
-    if not x.is_cuda or x.shape[1] < MIN_K:
+    if not _native.on_device(x) or x.shape[1] < MIN_K:
         zz = x if z is None else z
         d2 = torch.cdist(x.double(), zz.double()) ** 2
         return torch.exp(-gamma * d2).to(x.dtype)
@@ -138,7 +138,7 @@ def rbf_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, gamma: Optiona
 
 
 def linear_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, scale: float = 1.0) -> torch.Tensor:
-    if not x.is_cuda or x.shape[1] < MIN_K:
+    if not _native.on_device(x) or x.shape[1] < MIN_K:
         zz = x if z is None else z
         return (scale * (x.double() @ zz.double().t())).to(x.dtype)
     xa, _ = to_bf16_rows(x.float())
@@ -147,7 +147,7 @@ def linear_kernel(x: torch.Tensor, z: Optional[torch.Tensor] = None, scale: floa
 
 
 def sq_dists(x: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
-    if not x.is_cuda or x.shape[1] < MIN_K:
+    if not _native.on_device(x) or x.shape[1] < MIN_K:
         return (torch.cdist(x.double(), z.double()) ** 2).to(x.dtype)
     xa, na = to_bf16_rows(x.float())
     xb, nb = to_bf16_rows(z.float())

@@ -1,6 +1,9 @@
-// Fiber scheduler behind csrc/emu/cuda_emu.h: runs the blocks of an emulated launch one after the other, each block's
-// threads as ucontext fibers that switch only at barriers and warp collectives.
-#include "cuda_emu.h"
+// Fiber scheduler behind csrc/emu/cuda_emu.h.  A launch runs in waves of resident blocks: one block at a time for ordinary
+// kernels, the whole grid at once for kernels that ask for it (thread-block clusters, CTAs that wait for each other through
+// global memory).  Every CUDA thread of a resident block is a fiber that switches only at barriers, warp collectives and
+// polls.  When no fiber can run, one pending operation of the asynchronous units (async_emu.cpp) completes; when there is
+// none either, the launch is deadlocked and the process stops with a message.
+#include "emu_internal.h"
 
 #include <sys/mman.h>
 
@@ -35,6 +38,8 @@ cml_emu_switch:
 #include <ucontext.h>
 #endif
 
+
+#include <memory>
 #include <vector>
 
 namespace cml_emu {
@@ -44,8 +49,14 @@ dim3 g_blockDim(1, 1, 1), g_gridDim(1, 1, 1);
 
 namespace {
 
+using detail::AsyncOp;
+using detail::BlockState;
+using detail::Cluster;
+using detail::OpRef;
+
 constexpr size_t kStackBytes = 256 * 1024;
 constexpr int kMaxThreads = 1024;
+constexpr size_t kMaxResident = 256;
 
 struct Warp {
   unsigned live = 0, arrived = 0, gen = 0, mask = 0xffffffffu;   // mask: the one the waiting lanes passed
@@ -78,32 +89,47 @@ inline void make_context(Context& c, void* stack, size_t bytes, void (*entry)())
 }
 #endif
 
+struct Block;
+
 struct Fiber {
   Context ctx;
   void* stack = nullptr;
   uint3 tid{0, 0, 0};
   int linear = 0;
-  bool done = true;
+  bool done = true, spinning = false;
+  Block* blk = nullptr;
   // a blocked fiber waits for *wait_word to move away from wait_val
   const unsigned* wait_word = nullptr;
   unsigned wait_val = 0;
+  std::vector<OpRef> stores;                 // bulk-group operations this thread has issued and not yet waited for
 };
 
 struct Block {
+  BlockState st;
   int nthreads = 0, live = 0;
   unsigned bar_arrived = 0, bar_gen = 0;
   std::vector<Warp> warps;
+  std::vector<Fiber> fibers;
+  ~Block() {
+    std::free(st.smem);
+    for (Fiber& f : fibers)
+      if (f.stack) munmap(f.stack, kStackBytes);
+  }
 };
 
-std::vector<Fiber> g_fibers;
-Block g_block;
+std::vector<std::unique_ptr<Block>> g_resident;      // blocks of the running wave (kept between launches: stacks are reused)
+size_t g_wave = 0;                                   // how many of them are in use
+std::vector<Cluster> g_clusters;
+Block* g_blk = nullptr;
 Context g_sched;
 Fiber* g_cur = nullptr;
 const std::function<void()>* g_body = nullptr;
-std::vector<unsigned char> g_smem;
 long long g_tick = 0;
 uint64_t g_rng = 0x9e3779b97f4a7c15ull;
-bool g_shuffle = false;
+bool g_shuffle = false, g_progress = false, g_lazy = true;
+int g_next_cluster = 1;
+bool g_next_resident = false;
+std::vector<OpRef> g_pending;
 
 uint64_t rng_next() {
   g_rng ^= g_rng << 13;
@@ -123,11 +149,11 @@ void* alloc_stack() {
   return p;
 }
 
-void release_barrier_if_complete() {
-  Block& b = g_block;
+void release_barrier_if_complete(Block& b) {
   if (b.bar_arrived > 0 && (int)b.bar_arrived >= b.live) {
     b.bar_arrived = 0;
     ++b.bar_gen;
+    g_progress = true;
   }
 }
 
@@ -136,18 +162,36 @@ void release_warp_if_complete(Warp& w, unsigned mask) {
   if (w.arrived != 0u && (w.arrived & expected) == expected) {
     w.arrived = 0u;
     ++w.gen;
+    g_progress = true;
+  }
+}
+
+void release_cluster_if_complete(Cluster& c) {
+  if (c.arrived > 0 && (int)c.arrived >= c.live) {
+    c.arrived = 0;
+    ++c.gen;
+    g_progress = true;
   }
 }
 
 void fiber_exit() {
   Fiber* f = g_cur;
+  Block& b = *f->blk;
+  for (const OpRef& op : f->stores)
+    if (op->next < 1) trap("a thread returned while a bulk store it issued had not yet read its shared-memory source (missing cp.async.bulk.wait_group)");
+  f->stores.clear();
   f->done = true;
-  --g_block.live;
-  Warp& w = g_block.warps[f->linear >> 5];
+  if (--b.live == 0) b.st.exited = true;
+  Warp& w = b.warps[f->linear >> 5];
   w.live &= ~(1u << (f->linear & 31));
   // a thread that returns no longer takes part in barriers: those already waiting may now be complete
-  release_barrier_if_complete();
+  release_barrier_if_complete(b);
   release_warp_if_complete(w, w.mask);
+  if (b.st.cluster) {
+    --b.st.cluster->live;
+    release_cluster_if_complete(*b.st.cluster);
+  }
+  g_progress = true;
   switch_to(f->ctx, g_sched);
   trap("a finished fiber was resumed");
 }
@@ -165,11 +209,36 @@ void yield_until_changed(const unsigned* word, unsigned val) {
   f->wait_word = nullptr;
 }
 
+bool async_step() {
+  // drop what forced completion has already finished
+  size_t w = 0;
+  for (size_t i = 0; i < g_pending.size(); ++i)
+    if (g_pending[i]->next < g_pending[i]->phases) g_pending[w++] = g_pending[i];
+  g_pending.resize(w);
+  if (g_pending.empty()) return false;
+  // eligible: the first pending op of every ordered stream, and every unordered op
+  size_t pick = 0;
+  if (g_shuffle) {
+    std::vector<size_t> ok;
+    for (size_t i = 0; i < g_pending.size(); ++i) {
+      bool first = true;
+      if (g_pending[i]->key != 0)
+        for (size_t j = 0; j < i && first; ++j) first = g_pending[j]->key != g_pending[i]->key;
+      if (first) ok.push_back(i);
+    }
+    pick = ok[rng_next() % ok.size()];
+  }
+  OpRef op = g_pending[pick];
+  op->run(op->next++);
+  g_progress = true;
+  return true;
+}
+
 }  // namespace
 
 int lane_id() { return g_cur ? (g_cur->linear & 31) : 0; }
 long long tick() { return g_tick += 1000000; }          // every look at the clock is a millisecond: spin time-outs fire at once
-void* dyn_smem() { return g_smem.data(); }
+void* dyn_smem() { return g_blk->st.smem + g_blk->st.dyn_off; }
 int sm_count_emulated() {
   const char* s = std::getenv("CML_EMU_SMS");
   const int v = s ? std::atoi(s) : 4;
@@ -182,16 +251,21 @@ int sm_count_emulated() {
   std::abort();
 }
 
+void next_launch(int cluster, bool resident) {
+  g_next_cluster = cluster > 0 ? cluster : 1;
+  g_next_resident = resident || cluster > 1;
+}
+
 void sync_block() {
-  Block& b = g_block;
+  Block& b = *g_blk;
   const unsigned gen = b.bar_gen;
   ++b.bar_arrived;
-  release_barrier_if_complete();
+  release_barrier_if_complete(b);
   if (b.bar_gen == gen) yield_until_changed(&b.bar_gen, gen);
 }
 
 void sync_warp(unsigned mask) {
-  Warp& w = g_block.warps[g_cur->linear >> 5];
+  Warp& w = g_blk->warps[g_cur->linear >> 5];
   const unsigned gen = w.gen;
   w.arrived |= 1u << (g_cur->linear & 31);
   w.mask = mask;
@@ -199,8 +273,25 @@ void sync_warp(unsigned mask) {
   if (w.gen == gen) yield_until_changed(&w.gen, gen);
 }
 
+void sync_cluster() {
+  Cluster* c = g_blk->st.cluster;
+  if (!c) {                                  // a launch without clusters: the cluster is the block
+    sync_block();
+    return;
+  }
+  const unsigned gen = c->gen;
+  ++c->arrived;
+  release_cluster_if_complete(*c);
+  if (c->gen == gen) yield_until_changed(&c->gen, gen);
+}
+
+void wait_word_change(const unsigned* word, unsigned val) {
+  if (*word == val) yield_until_changed(word, val);
+  g_progress = true;
+}
+
 uint64_t warp_exchange(unsigned mask, uint64_t v, int src_lane) {
-  Warp& w = g_block.warps[g_cur->linear >> 5];
+  Warp& w = g_blk->warps[g_cur->linear >> 5];
   const int lane = g_cur->linear & 31, par = w.gen & 1u;
   const unsigned taking_part = mask & w.live;
   w.slot[par][lane] = v;
@@ -210,7 +301,7 @@ uint64_t warp_exchange(unsigned mask, uint64_t v, int src_lane) {
 }
 
 unsigned warp_ballot(unsigned mask, bool pred) {
-  Warp& w = g_block.warps[g_cur->linear >> 5];
+  Warp& w = g_blk->warps[g_cur->linear >> 5];
   const int lane = g_cur->linear & 31, par = w.gen & 1u;
   if (w.arrived == 0u) w.ballot[par] = 0u;          // first arrival of this collective
   if (pred) w.ballot[par] |= 1u << lane;
@@ -218,65 +309,165 @@ unsigned warp_ballot(unsigned mask, bool pred) {
   return w.ballot[par] & mask;
 }
 
+namespace detail {
+BlockState* cur_block() { return &g_blk->st; }
+BlockState* block_of_slot(int slot) {
+  if (slot < 0 || (size_t)slot >= g_wave) trap("shared-memory address does not belong to a resident block");
+  return &g_resident[slot]->st;
+}
+uint64_t cur_fiber_key() { return ((uint64_t)(g_blk->st.slot + 1) << 32) | (uint64_t)(g_cur->linear + 1); }
+int cur_warp_in_block() { return g_cur->linear >> 5; }
+std::vector<OpRef>& cur_fiber_stores() { return g_cur->stores; }
+uint64_t rng() { return rng_next(); }
+bool shuffled() { return g_shuffle; }
+void note_progress() { g_progress = true; }
+
+void spin_yield() {
+  Fiber* f = g_cur;
+  f->spinning = true;                        // resuming it is not progress by itself: it only looks at its flag again
+  switch_to(f->ctx, g_sched);
+  f->spinning = false;
+}
+
+OpRef async_submit(uint64_t key, int phases, std::function<void(int)> fn) {
+  OpRef op = std::make_shared<AsyncOp>();
+  op->key = key;
+  op->phases = phases;
+  op->run = std::move(fn);
+  if (!g_lazy) {
+    while (op->next < op->phases) op->run(op->next++);
+  } else {
+    g_pending.push_back(op);
+  }
+  return op;
+}
+
+void async_force(const OpRef& op, int upto_phase) {
+  while (op->next < upto_phase && op->next < op->phases) op->run(op->next++);
+}
+}  // namespace detail
+
 void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()>& body) {
   if (g_cur != nullptr) trap("nested launch from inside a kernel");
+  const int cluster = g_next_cluster;
+  const bool resident = g_next_resident;
+  g_next_cluster = 1;
+  g_next_resident = false;
   const int nthreads = (int)(block.x * block.y * block.z);
   if (nthreads <= 0 || nthreads > kMaxThreads) trap("block size out of range");
-  if ((size_t)grid.x * grid.y * grid.z == 0) return;
+  const size_t nblocks = (size_t)grid.x * grid.y * grid.z;
+  if (nblocks == 0) return;
+  if (cluster > 1 && (grid.x % (unsigned)cluster != 0 || cluster > 16)) trap("grid.x is not a multiple of the cluster size");
+  if (resident && nblocks > kMaxResident) trap("a launch that needs all its blocks resident is larger than the emulated machine");
   const uint64_t seed = seed_from_env();
   g_shuffle = seed != 0;
   g_rng = 0x9e3779b97f4a7c15ull ^ (seed * 0xbf58476d1ce4e5b9ull);
   if (g_rng == 0) g_rng = 1;
-  if ((int)g_fibers.size() < nthreads) g_fibers.resize(nthreads);
-  g_smem.resize(smem_bytes ? smem_bytes : 1);          // exact size: under ASan an access past the launch's dynamic shared memory is an error
+  {
+    const char* a = std::getenv("CML_EMU_ASYNC");
+    g_lazy = !(a && a[0] == 'e');             // "eager": asynchronous operations complete at issue; default: as late as possible
+  }
   g_body = &body;
   g_blockDim = block;
   g_gridDim = grid;
-  std::vector<int> order(nthreads);
-  for (unsigned bz = 0; bz < grid.z; ++bz)
-    for (unsigned by = 0; by < grid.y; ++by)
-      for (unsigned bx = 0; bx < grid.x; ++bx) {
-        g_blockIdx = uint3{bx, by, bz};
-        // dynamic shared memory starts out as garbage that depends on the seed (it is never zero on hardware either)
-        // (CML_EMU_POISON=ff makes every stale float a NaN and every stale int -1; =00 gives the zeroes that hide such bugs)
-        {
-          const char* poison = std::getenv("CML_EMU_POISON");
-          if (poison && (poison[0] == 'f' || poison[0] == '0')) std::memset(g_smem.data(), poison[0] == 'f' ? 0xff : 0x00, g_smem.size());
-          else for (size_t i = 0; i < g_smem.size(); ++i) g_smem[i] = (unsigned char)(rng_next() >> 56);
-        }
-        Block& b = g_block;
-        b.nthreads = b.live = nthreads;
-        b.bar_arrived = 0;
-        b.bar_gen = 0;
-        b.warps.assign((nthreads + 31) / 32, Warp());
-        for (int t = 0; t < nthreads; ++t) {
-          Fiber& f = g_fibers[t];
-          if (!f.stack) f.stack = alloc_stack();
-          f.linear = t;
-          f.tid = uint3{(unsigned)t % block.x, ((unsigned)t / block.x) % block.y, (unsigned)t / (block.x * block.y)};
-          f.done = false;
-          f.wait_word = nullptr;
-          b.warps[t >> 5].live |= 1u << (t & 31);
-          make_context(f.ctx, f.stack, kStackBytes, trampoline);
-          order[t] = t;
-        }
-        while (b.live > 0) {
-          if (g_shuffle)
-            for (int i = nthreads - 1; i > 0; --i) std::swap(order[i], order[rng_next() % (uint64_t)(i + 1)]);
-          bool progressed = false;
-          for (int oi = 0; oi < nthreads; ++oi) {
-            Fiber& f = g_fibers[order[oi]];
-            if (f.done) continue;
-            if (f.wait_word && *f.wait_word == f.wait_val) continue;      // still blocked
-            progressed = true;
-            g_cur = &f;
-            g_threadIdx = f.tid;
-            switch_to(g_sched, f.ctx);
-            g_cur = nullptr;
-          }
-          if (!progressed) trap("deadlock: live threads are all waiting at a barrier or warp collective that cannot complete");
-        }
+  const size_t wave = resident ? nblocks : 1;
+  // ordinary launches keep the layout they always had (window offset 0); resident ones start the dynamic shared memory
+  // 16 bytes into the window, as hardware does not promise more alignment than that
+  const uint32_t dyn_off = resident ? 16u : 0u;
+  if (g_resident.size() < wave) g_resident.resize(wave);
+  g_wave = wave;
+  std::vector<std::pair<int, int>> order;
+  for (size_t first = 0; first < nblocks; first += wave) {
+    g_clusters.assign(cluster > 1 ? wave / (size_t)cluster : 0, Cluster());
+    for (size_t s = 0; s < wave; ++s) {
+      if (!g_resident[s]) g_resident[s] = std::make_unique<Block>();
+      Block& b = *g_resident[s];
+      const size_t lin = first + s;
+      b.st.slot = (int)s;
+      b.st.bidx = uint3{(unsigned)(lin % grid.x), (unsigned)((lin / grid.x) % grid.y), (unsigned)(lin / ((size_t)grid.x * grid.y))};
+      const size_t need = dyn_off + (smem_bytes ? smem_bytes : 1);
+      if (b.st.smem_alloc != need) {           // exact size: under ASan an access past the launch's dynamic shared memory is an error
+        std::free(b.st.smem);
+        void* p = nullptr;
+        if (posix_memalign(&p, 1024, need) != 0) trap("cannot allocate the shared memory of a block");
+        b.st.smem = static_cast<uint8_t*>(p);
+        b.st.smem_alloc = need;
       }
+      b.st.dyn_off = dyn_off;
+      b.st.dyn_bytes = smem_bytes;
+      b.st.bars.clear();
+      b.st.exited = false;
+      b.st.tmem_cols.clear();
+      // dynamic shared memory starts out as garbage that depends on the seed (it is never zero on hardware either)
+      // (CML_EMU_POISON=ff makes every stale float a NaN and every stale int -1; =00 gives the zeroes that hide such bugs)
+      {
+        const char* poison = std::getenv("CML_EMU_POISON");
+        if (poison && (poison[0] == 'f' || poison[0] == '0')) std::memset(b.st.smem, poison[0] == 'f' ? 0xff : 0x00, need);
+        else for (size_t i = 0; i < need; ++i) b.st.smem[i] = (unsigned char)(rng_next() >> 56);
+      }
+      if (cluster > 1) {
+        Cluster& c = g_clusters[s / (size_t)cluster];
+        c.size = cluster;
+        c.cta[s % (size_t)cluster] = &b.st;
+        c.live += nthreads;
+        b.st.cluster = &c;
+        b.st.cta_rank = (int)(s % (size_t)cluster);
+      } else {
+        b.st.cluster = nullptr;
+        b.st.cta_rank = 0;
+      }
+      b.nthreads = b.live = nthreads;
+      b.bar_arrived = 0;
+      b.bar_gen = 0;
+      b.warps.assign((nthreads + 31) / 32, Warp());
+      if ((int)b.fibers.size() < nthreads) b.fibers.resize(nthreads);
+      for (int t = 0; t < nthreads; ++t) {
+        Fiber& f = b.fibers[t];
+        if (!f.stack) f.stack = alloc_stack();
+        f.linear = t;
+        f.tid = uint3{(unsigned)t % block.x, ((unsigned)t / block.x) % block.y, (unsigned)t / (block.x * block.y)};
+        f.done = false;
+        f.spinning = false;
+        f.blk = &b;
+        f.wait_word = nullptr;
+        f.stores.clear();
+        b.warps[t >> 5].live |= 1u << (t & 31);
+        make_context(f.ctx, f.stack, kStackBytes, trampoline);
+      }
+    }
+    order.clear();
+    for (size_t s = 0; s < wave; ++s)
+      for (int t = 0; t < nthreads; ++t) order.emplace_back((int)s, t);
+    for (;;) {
+      size_t live = 0;
+      for (size_t s = 0; s < wave; ++s) live += (size_t)g_resident[s]->live;
+      if (live == 0) break;
+      if (g_shuffle)
+        for (size_t i = order.size() - 1; i > 0; --i) std::swap(order[i], order[rng_next() % (uint64_t)(i + 1)]);
+      g_progress = false;
+      for (const auto& st : order) {
+        Block& b = *g_resident[st.first];
+        Fiber& f = b.fibers[st.second];
+        if (f.done) continue;
+        if (f.wait_word && *f.wait_word == f.wait_val) continue;      // still blocked
+        if (!f.spinning) g_progress = true;                           // first run, or what it waited for has happened
+        g_blk = &b;
+        g_cur = &f;
+        g_threadIdx = f.tid;
+        g_blockIdx = b.st.bidx;
+        switch_to(g_sched, f.ctx);
+        g_cur = nullptr;
+      }
+      if (!g_progress && !async_step())
+        trap("deadlock: every live thread waits at a barrier, a warp collective, an mbarrier or a flag that nothing can complete");
+    }
+    while (async_step()) {
+    }                                              // operations nobody waited for still complete (a store without wait_group, ...)
+    for (size_t s = 0; s < wave; ++s)
+      for (uint8_t used : g_resident[s]->st.tmem_cols)
+        if (used) trap("a CTA exited with tensor memory still allocated (missing tcgen05.dealloc)");
+  }
+  g_blk = nullptr;
   g_body = nullptr;
 }
 

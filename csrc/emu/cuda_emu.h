@@ -10,13 +10,18 @@
 // threads run between synchronisation points is shuffled by the same seed, so a read of uninitialised shared memory or a
 // missing __syncwarp/__syncthreads shows up as a result that depends on CML_EMU_SEED.
 //
-// Model: one OS thread.  Every CUDA thread of a block is a fiber (ucontext); blocks run one after the other.  A fiber
-// runs until it reaches a block barrier or a warp collective and is resumed when all participants have arrived.
+// Model: one OS thread.  Every CUDA thread of a block is a fiber; blocks run one after the other unless the launch asks
+// for the whole grid to be resident (cml_emu::next_launch: clusters, CTAs that wait for each other).  A fiber runs until
+// it reaches a barrier, a warp collective, an mbarrier wait or a poll and is resumed when that can complete.
 // Atomics are therefore plain read-modify-writes, __threadfence is a no-op, and a spin on memory that only a later
 // launch would write is a deadlock (clock64() jumps ahead so time-outs fire at once).
+// The asynchronous units of sm_100 - TMA tensor / bulk copies, tcgen05 MMA into TMEM, tcgen05.commit, bulk groups - are
+// modelled in emu/async_emu.cpp behind the wrappers of sm100.cuh: each operation is queued when issued and completes as
+// LATE as the program allows (when no thread can run), in a seed-dependent order among the operations that hardware
+// leaves unordered, so a consumer that does not wait for its mbarrier reads stale shared memory or TMEM here too.
 //
-// Not modelled: tcgen05 / TMEM / TMA / mbarrier / clusters (those kernels are not part of the emulated build), textures,
-// cooperative groups, independent progress of divergent lanes inside *_sync collectives with differing masks.
+// Not modelled: textures, cooperative groups, independent progress of divergent lanes inside *_sync collectives with
+// differing masks; tensor maps other than 2-D tiled / 128B swizzle; MMA kinds other than f16 (bf16 in, fp32 out).
 #pragma once
 #ifndef CML_EMU
 #define CML_EMU 1
@@ -29,7 +34,12 @@
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <memory>
+#include <mutex>
+#include <string>
 #include <type_traits>
+#include <unordered_map>
+#include <vector>     // (the standard headers come first: libstdc++ spells attributes the way the macros below do)
 
 // ---- qualifiers --------------------------------------------------------------------------------------------------
 #define __global__
@@ -42,6 +52,7 @@
 #define __constant__ static
 #define __align__(n) __attribute__((aligned(n)))
 #define __grid_constant__
+#define __cluster_dims__(...)
 
 // ---- vector types ------------------------------------------------------------------------------------------------
 struct uint3 { unsigned x, y, z; };
@@ -72,6 +83,11 @@ namespace cml_emu {
 extern uint3 g_threadIdx, g_blockIdx;
 extern dim3 g_blockDim, g_gridDim;
 void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()>& body);
+// Options of the NEXT launch only.  cluster: CTAs per thread-block cluster along x (the host model cannot see
+// __cluster_dims__); resident: run all blocks of the grid at the same time (kernels whose CTAs wait for each other).
+void next_launch(int cluster, bool resident);
+void sync_cluster();
+void wait_word_change(const unsigned* word, unsigned val);          // block this thread until *word != val
 void* dyn_smem();
 void sync_block();
 void sync_warp(unsigned mask);

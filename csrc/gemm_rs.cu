@@ -186,19 +186,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) xtr_gem
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rr[c & 1][j]) * P.alpha;
         if (P.use_tma) {
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          if (lane == 0) bulk_wait_group_read0();
           __syncwarp();
           float4* dst = reinterpret_cast<float4*>(stage_gen + lane * 128);
 #pragma unroll
           for (int q = 0; q < 8; ++q) dst[q ^ (lane & 7)] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                             reinterpret_cast<uint64_t>(&P.map_out[owner])),
-                         "r"(stage_u32), "r"(ocol0), "r"(lrow0)
-                         : "memory");
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            tma_reduce_add_2d(&P.map_out[owner], stage_u32, ocol0, lrow0);
+            bulk_commit_group();
           }
         } else if (row_warp0 + lane < P.p) {
           float* dst = P.out[owner] + (size_t)(lrow0 + lane) * P.ldo + ocol0;
@@ -211,7 +208,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) xtr_gem
       if (lane == 0) mbar_arrive_cluster(mapa_cluster(tempty_bar(acc), 0));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-    if (P.use_tma && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");     // reductions performed, not just read
+    if (P.use_tma && lane == 0) bulk_wait_group0();     // reductions performed, not just read
     __threadfence_system();
   }
   tc_fence_before();
@@ -280,6 +277,9 @@ int cml_xtr_gemm_reduce_scatter(int p, int N, int B, int K, const void* xt_bf16,
   CML_CUDA(cudaFuncSetAttribute(xtr_gemm_rs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
   const int items = P.tiles_m * P.tiles_n * P.ksplit;
   const int grid = 2 * (items < pairs ? items : pairs);
+#ifdef CML_EMU
+  cml_emu::next_launch(2, true);                    // host model: it cannot see __cluster_dims__
+#endif
   xtr_gemm_rs_kernel<<<grid, kThreads, kSmemTotal, static_cast<cudaStream_t>(stream)>>>(P);
   CML_LAUNCH_CHECK();
   return 0;

@@ -138,19 +138,6 @@ struct SmemLayout {
   static_assert(kTotal <= 227 * 1024, "shared memory budget");
 };
 
-__device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
-               "l"(gsrc), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_store_s2g(void* gdst, uint32_t smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 // Wait until a copier CTA of this grid has flagged a staged tile.  The copiers and the GEMM CTAs are co-resident by
 // construction (grid = SM count), but an SM held by another stream's kernel, or a copier that faulted on a bad peer
 // pointer, would otherwise leave this loop spinning for ever and the device unusable: back off after a short spin and
@@ -159,7 +146,7 @@ constexpr long long kFlagTimeoutCycles = 40000000000LL;
 __device__ __forceinline__ void wait_tile_flag(const unsigned* flag, unsigned epoch) {
   unsigned spins = 0;
   long long t0 = 0;
-  while (ld_acquire_gpu(flag) != epoch) {
+  while (sm100::ld_acquire_gpu(flag) != epoch) {
     if (++spins == 64u) t0 = clock64();
     if (spins > 64u) {
       __nanosleep(128);
@@ -200,7 +187,7 @@ __device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
         for (int c = 0; c < nchunks + (kSlots - 1); ++c) {
           if (c < nchunks) {
             const uint32_t slot = issued % kSlots;
-            if (issued >= kSlots) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // slot's previous store has left smem
+            if (issued >= kSlots) bulk_wait_group_read0();   // slot's previous store has left smem
             const uint32_t bytes = (uint32_t)min((size_t)kChunk, total - (size_t)c * kChunk);
             mbar_arrive_expect_tx(bar0 + 8u * slot, bytes);
             bulk_load_g2s(base + slot * kChunk, gsrc + (size_t)c * kChunk, bytes, bar0 + 8u * slot);
@@ -212,12 +199,12 @@ __device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
             mbar_wait(bar0 + 8u * slot, (drained / kSlots) & 1u);
             const uint32_t bytes = (uint32_t)min((size_t)kChunk, total - (size_t)d * kChunk);
             bulk_store_s2g(gdst + (size_t)d * kChunk, base + slot * kChunk, bytes);
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            bulk_commit_group();
             ++drained;
           }
         }
-        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // stores complete (written, not just read)
-        asm volatile("fence.proxy.async;" ::: "memory");
+        bulk_wait_group0();       // stores complete (written, not just read)
+        fence_proxy_async();
       } else if (P.peer_norm[src] && P.stage_norm) {
         for (int r = r0 + (int)threadIdx.x - 1; r < r1; r += (int)blockDim.x - 1)
           P.stage_norm[(size_t)src * P.rows_per_src + r] = P.peer_norm[src][r];
@@ -226,7 +213,7 @@ __device__ void copier_role(const GemmParams& P, uint8_t* smem_raw) {
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0)
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.flags + (size_t)src * P.tiles_n_per_src + n_loc), "r"(P.epoch) : "memory");
+      st_release_gpu(P.flags + (size_t)src * P.tiles_n_per_src + n_loc, P.epoch);
   }
 }
 
@@ -269,13 +256,6 @@ __device__ __forceinline__ void tile_to_mn_src(const GemmParams& P, int tile, in
     tile_to_mn(tile - si * per_src, P.tiles_m, P.tiles_n_per_src, true, m_blk, n_loc);
     n_blk = si * P.tiles_n_per_src + n_loc;
   }
-}
-
-// 2^x on the SFU without the denormal pre/post scaling of exp2f (results below 2^-126 flush to zero)
-__device__ __forceinline__ float ex2_ftz(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
 }
 
 template <int BN, int EPI>
@@ -331,19 +311,16 @@ __device__ __forceinline__ void epilogue_tile_impl(const GemmParams& P, uint32_t
     const int ccol = src * P.rows_per_src + cs;
     if (P.c_tma && nvalid == 32 && (ccol & 3) == 0) {       // TMA stores need a 16-byte aligned start in global memory
       constexpr uint32_t buf = 0;
-      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous store has left the buffer
+      if (lane == 0) bulk_wait_group_read0();   // the previous store has left the buffer
       __syncwarp();
       float4* dst = reinterpret_cast<float4*>(stage_gen + buf + lane * 128);
 #pragma unroll
       for (int q = 0; q < 8; ++q) dst[q ^ (lane & 7)] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                         reinterpret_cast<uint64_t>(&P.map_c)),
-                     "r"(stage_u32 + buf), "r"(ccol), "r"(row_warp0)
-                     : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        tma_store_2d(&P.map_c, stage_u32 + buf, ccol, row_warp0);
+        bulk_commit_group();
       }
     } else if (row < P.M) {
       float* out = P.c + (size_t)row * P.ldc + ccol;
@@ -427,7 +404,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
         if (staged) {
           const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
           wait_tile_flag(flag, P.epoch);
-          asm volatile("fence.proxy.async;" ::: "memory");          // staged bytes were written through the async proxy
+          fence_proxy_async();          // staged bytes were written through the async proxy
         }
         const int brow = staged ? src * P.rows_per_src + n_loc * BN : n_loc * BN;
         const CUtensorMap* mapb = staged ? &P.map_b[0] : &P.map_b[src];
@@ -493,7 +470,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
       if (lane == 0) mbar_arrive(tempty_bar(acc));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // C tiles are written before the CTA exits
+    if (lane == 0) bulk_wait_group0();   // C tiles are written before the CTA exits
   }
   tc_fence_before();
   __syncthreads();
@@ -511,6 +488,9 @@ int launch_gemm(const GemmParams& P, cudaStream_t st) {
   const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
   int grid = tiles < sm_count() ? tiles : sm_count();
   if (P.n_copiers > 0) grid = sm_count();          // copier CTAs + GEMM CTAs must all be co-resident (flags are spun on)
+#ifdef CML_EMU
+  cml_emu::next_launch(1, true);                   // host model: whole grid resident
+#endif
   kern<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;
@@ -597,7 +577,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
         if (staged) {
           const unsigned* flag = P.flags + (size_t)src * P.tiles_n_per_src + n_loc;
           wait_tile_flag(flag, P.epoch);
-          asm volatile("fence.proxy.async;" ::: "memory");
+          fence_proxy_async();
         }
         const int arow = m_blk * BM2 + (int)cta * 128;
         const int brow = (staged ? src * P.rows_per_src : 0) + n_loc * BN + (int)cta * 128;
@@ -667,7 +647,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
       if (lane == 0) mbar_arrive_cluster(mapa_cluster(tempty_bar(acc), 0));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (lane == 0) bulk_wait_group0();
   }
   tc_fence_before();
   cluster_sync_all();                                        // neither CTA leaves while the other may still touch it
@@ -686,6 +666,9 @@ int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
   const int pairs = sm_count() / 2;
   int grid = 2 * (tiles < pairs ? tiles : pairs);
   if (P.n_copiers > 0) grid = 2 * pairs;             // copier clusters + GEMM clusters must all be co-resident (flags are spun on)
+#ifdef CML_EMU
+  cml_emu::next_launch(2, true);                     // host model: it cannot see __cluster_dims__
+#endif
   kern<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;

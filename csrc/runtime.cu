@@ -30,6 +30,9 @@ int current_device() {
 }
 
 int sm_count() {
+#ifdef CML_EMU
+  return cml_emu::sm_count_emulated();       // CML_EMU_SMS may change between launches
+#endif
   static int cache[64];
   static std::once_flag once;
   std::call_once(once, [] { memset(cache, 0, sizeof(cache)); });

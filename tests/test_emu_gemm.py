@@ -1,0 +1,194 @@
+"""The tcgen05 / TMA kernels on the host model of the asynchronous units (csrc/emu/async_emu.cpp).
+
+gemm_tcgen05.cu is the calibration: it ran on hardware in round 1, so a model that disagreed with the hardware about
+descriptors, the 128B swizzle, TMEM layout or mbarrier phases would fail here.  gemm_rs.cu has never run on hardware; the same
+model executes it below (register-reduce and TMA-reduce landing, hi / lo split, split-K, several owners and ranks).
+Asynchronous operations complete as late as possible and in a seed-dependent order, so a missing wait shows up as stale or
+poisoned data: the last test removes single waits from the kernel and checks that the result breaks."""
+import ctypes
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from consensusml_b200 import _native
+from consensusml_b200.ops import gemm as G
+from consensusml_b200.parallel import fused as F
+
+
+def _bf16_pad(x):
+    rows, k = x.shape
+    ld = (k + 7) // 8 * 8
+    y = torch.zeros(rows, ld, dtype=torch.bfloat16)
+    y[:, :k] = x.bfloat16()
+    return y
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("M,N,K,seed", [(100, 90, 128, 0), (300, 520, 200, 3), (257, 769, 72, 11), (130, 1000, 328, 5)])
+def test_gemm_epilogues(variant, M, N, K, seed):
+    torch.manual_seed(seed)
+    x, z = torch.randn(M, K), torch.randn(N, K)
+    with _native.emulation(seed=seed):
+        G.set_variant(variant)
+        try:
+            xa, na = G.to_bf16_rows(x)
+            xb, nb = G.to_bf16_rows(z)
+            c = G.gemm_tn(xa, [xb], N, epilogue=G.EPI_SCALE, alpha=0.5)
+            d = G.gemm_tn(xa, [xb], N, epilogue=G.EPI_SQDIST, norm_a=na, norm_b=[nb])
+            r = G.gemm_tn(xa, [xb], N, epilogue=G.EPI_RBF, alpha=1.0 / K, norm_a=na, norm_b=[nb])
+        finally:
+            G.set_variant(0)
+    prod = xa.float() @ xb.float().t()
+    d2 = (na[:, None] + nb[None, :] - 2 * prod).clamp_min(0)
+    assert (c - 0.5 * prod).abs().max() < 1e-4
+    assert (d - d2).abs().max() < 2e-4
+    assert (r - torch.exp(-d2 / K)).abs().max() < 1e-5
+    assert (na - xa.float().square().sum(1)).abs().max() < 1e-3
+
+
+def test_gemm_unaligned_output_takes_register_stores():
+    """A C whose pitch TMA cannot address (ldc % 4 != 0 is impossible through gemm_tn, so: an out view offset by one float)."""
+    torch.manual_seed(2)
+    x, z = torch.randn(140, 96), torch.randn(75, 96)
+    with _native.emulation(seed=4):
+        xa, _ = G.to_bf16_rows(x)
+        xb, _ = G.to_bf16_rows(z)
+        buf = torch.zeros(140 * 76 + 1)
+        out = buf[1:].view(140, 76)                       # 4-byte aligned only
+        c = G.gemm_tn(xa, [xb], 75, out=out)
+    assert (c - xa.float() @ xb.float().t()).abs().max() < 1e-4
+
+
+def test_gemm_many_sources_direct():
+    """B spread over three row blocks (the direct all-gather form: one tensor map per source, ragged last block)."""
+    torch.manual_seed(3)
+    x = torch.randn(150, 136)
+    blocks = [torch.randn(200, 136), torch.randn(200, 136), torch.randn(117, 136)]
+    with _native.emulation(seed=6):
+        xa, na = G.to_bf16_rows(x)
+        bs = [G.to_bf16_rows(b) for b in blocks]
+        c = G.gemm_tn(xa, [b[0] for b in bs], 517, epilogue=G.EPI_SQDIST, norm_a=na, norm_b=[b[1] for b in bs])
+    zb = torch.cat([b[0].float() for b in bs])
+    nb = torch.cat([b[1] for b in bs])
+    ref = (na[:, None] + nb[None, :] - 2 * xa.float() @ zb.t()).clamp_min(0)
+    assert (c - ref).abs().max() < 2e-4
+
+
+@pytest.mark.parametrize("variant,n_src,rank,grouped", [(1, 2, 0, 0), (2, 3, 1, 0), (2, 2, 1, 1), (1, 3, 2, 1)])
+def test_gemm_staged_all_gather(variant, n_src, rank, grouped):
+    """Copier CTAs pull the source blocks into the staging buffer and flag tiles; GEMM CTAs of the same launch consume them."""
+    torch.manual_seed(10 + n_src)
+    M, K, rows = 260, 200, 300
+    N = n_src * rows - 37                                   # ragged last source
+    x = torch.randn(M, K)
+    with _native.emulation(seed=variant + rank, sms=8):
+        G.set_variant(variant)
+        G.set_staged_grouping(bool(grouped))
+        try:
+            xa, na = G.to_bf16_rows(x)
+            srcs = [G.to_bf16_rows(torch.randn(rows, K)) for _ in range(n_src)]
+            ldb = srcs[0][0].shape[1]
+            stage = torch.full((n_src * rows, ldb), float("nan"), dtype=torch.bfloat16)
+            stage_norm = torch.full((n_src * rows,), float("nan"))
+            n_flags = _native.cuda().cml_gemm_staged_flags(n_src, rows)
+            flags = torch.zeros(n_flags, dtype=torch.int32)
+            for epoch in (1, 2):                              # flags are compared for equality: the second call must not reuse the first's
+                if epoch == 2:
+                    stage.fill_(float("nan"))
+                c = G.gemm_tn_staged(xa, [s[0].data_ptr() for s in srcs], N, rows, ldb, stage, stage_norm, flags, epoch, rank,
+                                     epilogue=G.EPI_SQDIST, norm_a=na, peer_norm_ptrs=[s[1].data_ptr() for s in srcs], n_copiers=2).clone()
+                zb = torch.cat([s[0].float() for s in srcs])[:N]
+                nb = torch.cat([s[1] for s in srcs])[:N]
+                ref = (na[:, None] + nb[None, :] - 2 * xa.float() @ zb.t()).clamp_min(0)
+                assert (c - ref).abs().max() < 2e-4
+                assert bool((flags == epoch).all())
+        finally:
+            G.set_variant(0)
+            G.set_staged_grouping(False)
+
+
+def _run_gemm_rs(p, B, K, world, use_tma, split, seed, sms=None):
+    g = torch.Generator().manual_seed(seed + 1)
+    xts = [_bf16_pad(torch.randn(p, K, generator=g)) for _ in range(world)]
+    rfs = [torch.randn(B, K, generator=g) for _ in range(world)]
+    ld = xts[0].shape[1]
+    rts = []
+    for rf in rfs:
+        pad = torch.zeros(B, ld)
+        pad[:, :K] = rf
+        rts.append(F.split_bf16(pad) if split else pad.bfloat16())
+    gpr = ((p + world - 1) // world + 31) // 32 * 32
+    outs = [torch.zeros(gpr, B) for _ in range(world)]
+    sigs = [torch.zeros(256, dtype=torch.int32) for _ in range(world)]
+    arr = lambda ts: (ctypes.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    with _native.emulation(seed=seed, sms=sms):
+        for r in range(world):
+            done = torch.zeros(4, dtype=torch.int32)
+            rc = _native.cuda().cml_xtr_gemm_reduce_scatter(p, rts[r].shape[0], B, ld, _native.ptr(xts[r]), ld, _native.ptr(rts[r]), ld, arr(outs), B,
+                                                            gpr, arr(sigs), r, world, _native.ptr(done), 7, F.SIG_GEMM_RS, 0.5, int(use_tma),
+                                                            _native.stream_ptr())
+            _native.check(rc, "cml_xtr_gemm_reduce_scatter")
+            assert int(done[0]) == 0                          # the last CTA re-arms the counter
+    ref = sum(0.5 * (xts[r].float() @ (rts[r].float()[:B] + (rts[r].float()[B:] if split else 0)).t()) for r in range(world))
+    exact = sum(0.5 * (xts[r].float()[:, :K] @ rfs[r].t()) for r in range(world))
+    return outs, sigs, ref, exact, gpr
+
+
+@pytest.mark.parametrize("p,B,K,world,use_tma,split,seed,sms", [
+    (512, 256, 300, 1, 0, 0, 0, None), (512, 256, 300, 1, 1, 0, 2, None), (1000, 128, 520, 3, 0, 0, 5, None),
+    (1000, 128, 2100, 2, 1, 1, 9, None), (300, 64, 4000, 2, 0, 1, 0, 8), (777, 96, 1300, 4, 1, 0, 13, 6)])
+def test_gemm_reduce_scatter(p, B, K, world, use_tma, split, seed, sms):
+    outs, sigs, ref, exact, gpr = _run_gemm_rs(p, B, K, world, use_tma, split, seed, sms)
+    scale = float(ref.abs().max())
+    for d in range(world):
+        lo, hi = min(p, d * gpr), min(p, (d + 1) * gpr)
+        assert (outs[d][: hi - lo] - ref[lo:hi]).abs().max() < 2e-5 * scale          # same bf16 operands, fp32 accumulation
+        assert float(outs[d][hi - lo:].abs().max()) == 0.0 if hi - lo < gpr else True   # rows past the owner's genes stay untouched
+        assert [int(sigs[d][F.SIG_GEMM_RS + r]) for r in range(world)] == [7] * world     # every rank signalled every owner
+        if split:                                                                         # hi + lo carries the fp32 residuals
+            assert (outs[d][: hi - lo] - exact[lo:hi]).abs().max() < 3e-4 * scale
+
+
+def test_gemm_eager_completion_mode(monkeypatch):
+    monkeypatch.setenv("CML_EMU_ASYNC", "eager")
+    outs, _, ref, _, gpr = _run_gemm_rs(512, 128, 300, 2, 1, 0, 1)
+    assert (torch.cat(outs)[:512] - ref).abs().max() < 2e-5 * float(ref.abs().max())
+
+
+def test_high_level_ops_use_the_kernel_under_emulation():
+    torch.manual_seed(5)
+    x, z = torch.randn(93, 200), torch.randn(44, 200)
+    with _native.emulation(seed=1):
+        _native.reset_calls()
+        k = G.rbf_kernel(x, z)
+        assert _native.calls.get("cml_gemm_tn_bf16", 0) == 1
+    ref = torch.exp(-torch.cdist(x.double(), z.double()) ** 2 / 200).float()
+    assert (k - ref).abs().max() < 5e-3                    # bf16 operands
+
+
+_FAULT = r"""
+import sys, torch
+root = %r
+sys.path[:0] = [root, root + "/tests"]
+from test_emu_gemm import _run_gemm_rs
+outs, _, ref, _, gpr = _run_gemm_rs(512, 256, 300, 1, %d, 0, 0)
+bad = not bool(((outs[0][:512] - ref).abs().max() < 1e-3).item())
+print("RESULT", "wrong" if bad else "right")
+"""
+
+
+@pytest.mark.parametrize("n,use_tma", [(1, 0), (300, 0), (560, 1), (800, 1)])
+def test_a_removed_wait_is_detected(n, use_tma):
+    """Remove the n-th mbarrier wait (these four are epilogue / MMA-issuer / producer waits that would have blocked): the
+    late-completion model must turn that into a wrong result or a rule violation, never into a pass."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CML_EMU_FAULT=f"skip_wait:{n}", CML_EMU_FAULT_VERBOSE="1")
+    res = subprocess.run([sys.executable, "-c", _FAULT % (root, use_tma)], env=env, capture_output=True, text=True, timeout=600, cwd=root)
+    assert "skipped wait" in res.stderr
+    line = [l for l in res.stderr.splitlines() if "skipped wait" in l][0]
+    parity, phase = int(line.split("parity ")[1].split()[0]), int(line.split("phase now ")[1].split(")")[0])
+    assert parity == phase, "test premise: the removed wait would have blocked"
+    assert res.returncode != 0 or "RESULT wrong" in res.stdout
