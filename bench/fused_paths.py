@@ -223,7 +223,26 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
             emit(path="xtr_gemm_reduce_scatter", tma_reduce=use_tma, rows_per_gpu=n, genes=p, B=B, ms=ms, tflops=flops / ms / 1e9,
                  hbm_gbs=byts / ms / 1e6, frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link)
             del op
-        del xt, rt
+        # ---- the whole replicate-batched iteration built on it: eta product (tcgen05), residual split, GEMM -> reduce-scatter
+        # gradient, proximal step + all-gather of the bf16 rows of v (models/lasso_large.BatchedLassoLarge), B = 256 lanes
+        from consensusml_b200.models import lasso_large as LL
+        ldp = (p + 7) // 8 * 8
+        xb = torch.randn(n, ldp, device=dev, dtype=torch.bfloat16)
+        S = LL.BatchedLassoLarge(None, torch.randint(0, 2, (n,), device=dev).float(), [1e-3] * B, n_total=n * world, step=1e-3,
+                                 prepared=(xb, xt))
+
+        def it():
+            S.phase_a(False)
+            S.phase_b()
+        it()
+        ms = timed(it, args.reps, flush)
+        flops = 8.0 * B * n * p                                   # two products, each with hi / lo rows
+        byts = 2.0 * (n * ldp + p * ld) + 2 * B * n * 4 * 2.0
+        link = 4.0 * p * B * (world - 1) / world + 4.0 * B * p * (world - 1) / world
+        t_roof = max(flops / (tf * 1e12), byts / (hbm * 1e9), link / (NVLINK_GBS * 1e9))
+        emit(path="lasso_batched_iteration", rows_per_gpu=n, genes=p, lanes=B, ms=ms, tflops=flops / ms / 1e9,
+             frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, lane_iterations_per_s=B / ms * 1e3)
+        del S, xb, xt, rt
         if world > 1 and "gram" not in args.skip:
             from consensusml_b200.ops import gemm as G
             m = args.gram_rows

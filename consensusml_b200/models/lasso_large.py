@@ -218,3 +218,237 @@ def fit_path(x_local: torch.Tensor, y_local: torch.Tensor, lams=None, *, n_lambd
         beta = f.beta
         fits.append(f)
     return lams, fits
+
+
+# ------------------------------------------------------------------------------------------------ replicate-batched form
+_I, _LL, _Fc, _Pc, _U = ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_void_p, ctypes.c_uint
+_native.register_signature("cml_batched_residual", [_Pc, _LL, _I, _I, _Pc, _Pc, _LL, _Pc, _LL, _Pc, _Pc])
+_native.register_signature("cml_batched_prox_allgather", [_Pc, _LL, _I, _I, _I, _Pc, _Fc, _Fc, _Fc, _Fc, _Pc, _Pc, _LL, _Pc, _LL, _Pc, _I, _I,
+                                                            _Pc, _U, _I, _Pc, _Pc])
+SIG_VHL = 48                    # signal-pad words 48..55 (fused.py: 0..23, transpose: 24..31, gemm_rs: 32..39)
+
+
+@dataclass
+class BatchedFit:
+    beta: torch.Tensor          # [B, p]
+    iterations: int
+    objective: torch.Tensor     # [B] at the last check
+    delta: torch.Tensor         # [B] largest coefficient change of the last checked iteration
+    step: float
+    history: list
+
+
+class BatchedLassoLarge:
+    """B lanes of the sample-sharded proximal-gradient solver advancing together - lane = (observation weights, lambda): the
+    bootstrap replicates x lambda grid of a stability selection, or the lambda path of one fit, on a cohort that is
+    streamed rather than cached.  With B in the hundreds both products of an iteration are tensor-core GEMMs:
+
+        Eta^T = Vhl . X_r^T            ``ops.gemm.gemm_tn``  (tcgen05, bf16 hi / lo rows of v -> fp32-accurate eta)
+        Rt    = split(W o (y - sigmoid(Eta)))                ``cml_batched_residual``
+        G_own = sum_ranks Xt_r . Rt_r^T [owned genes]        ``XtrGemmReduceScatter`` (tcgen05 GEMM + reduce-scatter, one kernel)
+        prox step on the owned genes, new Vhl rows stored to every rank   ``cml_batched_prox_allgather``
+
+    The iteration is split into ``phase_a`` (local products, gradient launch) and ``phase_b`` (wait, proximal step, all-gather)
+    so that several ranks can be played in one process (``symm.LocalGroup``: host execution model, single-GPU tests);
+    ``run`` is the normal driver.  ``backend="unfused"`` is the torch / ``torch.distributed`` comparator and CPU path."""
+
+    def __init__(self, x_local: torch.Tensor, y_local: torch.Tensor, lams, *, weights: Optional[torch.Tensor] = None,
+                 n_total: Optional[int] = None, alpha: float = 1.0, step: Optional[float] = None, use_tma_reduce: bool = False,
+                 rank: Optional[int] = None, world: Optional[int] = None, shared: Optional[dict] = None, prepared=None):
+        """``prepared=(xb, xt)``: the two bf16 layouts of this rank's rows already on the device ([n_r, pad8(p)] sample-major and
+        [p, pad8(n_r)] gene-major) - then ``x_local`` may be None and ``step`` must be given."""
+        self.world = world if world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
+        self.rank = rank if rank is not None else (dist.get_rank() if dist.is_initialized() else 0)
+        if prepared is not None:
+            dev, n_r, p = prepared[0].device, prepared[0].shape[0], prepared[1].shape[0]
+        else:
+            dev = x_local.device
+            n_r, p = x_local.shape
+        self.n_r, self.p, self.dev, self.alpha = n_r, p, dev, float(alpha)
+        lams = torch.as_tensor(np.asarray(lams, dtype=np.float32)).reshape(-1)
+        self.B = int(lams.numel())
+        self.Bp = (self.B + 31) // 32 * 32
+        if n_total is None:
+            t = torch.tensor([n_r], dtype=torch.float64, device=dev)
+            all_reduce_(t)
+            n_total = int(t.item())
+        self.n_total = n_total
+        if step is None and prepared is not None:
+            raise ValueError("prepared operands need an explicit step")
+        self.step = float(step) if step is not None else 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
+        lam_pad = torch.full((self.Bp,), float("inf"))
+        lam_pad[: self.B] = lams * self.alpha                     # padding lanes: infinite threshold, coefficients stay zero
+        self.lam_l1 = lam_pad.to(dev)
+        self.lams = lams.to(dev)
+        self.shrink = 1.0                                         # per-lane ridge would need a vector; one alpha for all lanes
+        if self.alpha < 1.0:
+            if float(lams.max() - lams.min()) != 0.0:
+                raise ValueError("elastic-net lanes must share one lambda (the ridge shrink factor is a scalar of the kernel)")
+            self.shrink = 1.0 / (1.0 + self.step * float(lams[0]) * (1.0 - self.alpha))
+        if prepared is not None:
+            self.xb, self.xt = prepared
+        else:
+            xf = x_local.float()
+            self.xb = F.to_bf16_padded(xf)                        # [n_r, ldp] sample-major: B operand of the eta product
+            self.xt = F.to_bf16_padded(xf.t().contiguous())       # [p, ldn] gene-major: A operand of the gradient product
+        self.ldp, self.ldn = self.xb.shape[1], self.xt.shape[1]
+        self.y = y_local.float().contiguous()
+        self.W = None
+        if weights is not None:
+            assert weights.shape == (self.B, n_r)
+            self.W = torch.ones(self.Bp, n_r, dtype=torch.float32, device=dev)
+            self.W[: self.B] = weights.float()
+        gpr = F.XtrGemmReduceScatter.genes_per_rank_for(p, self.world)
+        if shared is None:
+            self.vhl = symm.alloc((2 * self.Bp, self.ldp), torch.bfloat16, dev)
+            rs_bufs = None
+        else:
+            self.vhl, rs_bufs = shared["vhl"][self.rank], [b[self.rank] for b in shared["rs"]]
+        self.rs = F.XtrGemmReduceScatter(p, self.Bp, dev, use_tma_reduce=use_tma_reduce, rank=self.rank, world=self.world, bufs=rs_bufs)
+        go = self.rs.genes_owned
+        self.ldo = max(go, 1)
+        self.beta = torch.zeros(self.Bp, self.ldo, dtype=torch.float32, device=dev)
+        self.v = torch.zeros(self.Bp, self.ldo, dtype=torch.float32, device=dev)
+        self.lde = (n_r + 3) // 4 * 4
+        self.eta2 = torch.empty(2 * self.Bp, self.lde, dtype=torch.float32, device=dev)
+        self.rt = torch.zeros(2 * self.Bp, self.ldn, dtype=torch.bfloat16, device=dev)
+        self.loss = torch.zeros(self.Bp, dtype=torch.float64, device=dev)
+        self.dmax = torch.zeros(self.Bp, dtype=torch.float32, device=dev)
+        self.done = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.tk = 1.0
+        self.it = 0
+
+    @staticmethod
+    def shared_buffers(group: "symm.LocalGroup", p: int, n_lanes: int) -> dict:
+        """The symmetric buffers of a ``LocalGroup`` run (one entry per rank in every list)."""
+        Bp = (n_lanes + 31) // 32 * 32
+        ldp = (p + 7) // 8 * 8
+        gpr = F.XtrGemmReduceScatter.genes_per_rank_for(p, group.world)
+        return {"vhl": group.alloc((2 * Bp, ldp), torch.bfloat16), "rs": [group.alloc((gpr, Bp), torch.float32) for _ in range(2)]}
+
+    # ---- one iteration, in the two halves between which the other ranks have to have caught up
+    def phase_a(self, check: bool) -> None:
+        lb, P, st = _native.cuda(), _native.ptr, _native.stream_ptr
+        self.it += 1
+        if self.it > 1:      # every owner's new rows of v have landed in this rank's Vhl
+            _native.check(lb.cml_wait_signals(ctypes.c_void_p(self.vhl.signal_ptrs[self.rank]), SIG_VHL, self.world, self.it - 1, st()),
+                          "cml_wait_signals")
+        from ..ops import gemm as G
+        G.gemm_tn(self.vhl.local, [self.xb], self.n_r, out=self.eta2)
+        if check:
+            self.loss.zero_()
+            self.dmax.zero_()
+        _native.check(lb.cml_batched_residual(P(self.eta2), self.lde, self.Bp, self.n_r, P(self.y), P(self.W) if self.W is not None else None,
+                                              self.n_r, P(self.rt), self.ldn, P(self.loss) if check else None, st()), "cml_batched_residual")
+        self.rs.launch(self.xt, self.rt)
+
+    def phase_b(self) -> None:
+        lb, P, st = _native.cuda(), _native.ptr, _native.stream_ptr
+        self.rs.wait()
+        tk1 = (1.0 + np.sqrt(1.0 + 4.0 * self.tk * self.tk)) / 2.0
+        mom = (self.tk - 1.0) / tk1
+        self.tk = tk1
+        grad = self.rs.bufs[self.rs.epoch & 1].local
+        _native.check(lb.cml_batched_prox_allgather(P(grad), self.Bp, self.rs.genes_owned, self.rs.gene0, self.Bp, P(self.lam_l1), self.step,
+                                                    1.0 / self.n_total, mom, self.shrink, P(self.beta), P(self.v), self.ldo,
+                                                    F._ptr_array(self.vhl.peer_ptrs), self.ldp, F._ptr_array(self.vhl.signal_ptrs), self.rank,
+                                                    self.world, P(self.done), self.it, SIG_VHL, P(self.dmax), st()),
+                      "cml_batched_prox_allgather")
+
+    def wait_all_gather(self) -> None:
+        _native.check(_native.cuda().cml_wait_signals(ctypes.c_void_p(self.vhl.signal_ptrs[self.rank]), SIG_VHL, self.world, self.it,
+                                                      _native.stream_ptr()), "cml_wait_signals")
+
+    def penalty_owned(self) -> torch.Tensor:
+        """[B]: lambda (alpha |b|_1 + (1 - alpha)/2 |b|^2) over the genes this rank owns."""
+        b = self.beta[: self.B, : self.rs.genes_owned].double()
+        return self.lams.double() * (self.alpha * b.abs().sum(1) + 0.5 * (1.0 - self.alpha) * (b * b).sum(1))
+
+    def coefficients(self) -> torch.Tensor:
+        """[B, p] on every rank (one all-gather of the owned slices)."""
+        own = torch.zeros(self.B, self.rs.genes_per_rank, dtype=torch.float32, device=self.dev)
+        own[:, : self.rs.genes_owned] = self.beta[: self.B, : self.rs.genes_owned]
+        if self.world > 1 and dist.is_initialized():
+            parts = [torch.empty_like(own) for _ in range(self.world)]
+            dist.all_gather(parts, own)
+            own = torch.cat(parts, 1)
+        return own[:, : self.p].contiguous()
+
+    def run(self, max_iter: int = 200, tol: float = 1e-5, check_every: int = 10) -> BatchedFit:
+        history = []
+        obj = torch.full((self.B,), float("nan"), dtype=torch.float64)
+        d = torch.full((self.B,), float("inf"))
+        for it in range(1, max_iter + 1):
+            check = (it % check_every == 0) or it == max_iter
+            self.phase_a(check)
+            self.phase_b()
+            if check:
+                dm = self.dmax[: self.B].double().clone()
+                s = self.loss[: self.B].clone() / self.n_total + self.penalty_owned()
+                all_reduce_(dm, dist.ReduceOp.MAX)
+                all_reduce_(s)
+                obj, d = s.cpu(), dm.float().cpu()
+                history.append((it, float(obj.mean()), float(d.max())))
+                if float(d.max()) < tol:
+                    break
+        self.wait_all_gather()
+        if self.dev.type == "cuda":
+            torch.cuda.synchronize()
+        self.vhl.barrier()
+        return BatchedFit(self.coefficients(), self.it, obj, d, self.step, history)
+
+
+def fit_batched(x_local: torch.Tensor, y_local: torch.Tensor, lams, *, weights: Optional[torch.Tensor] = None, n_total: Optional[int] = None,
+                max_iter: int = 200, tol: float = 1e-5, backend: str = "auto", alpha: float = 1.0, step: Optional[float] = None,
+                check_every: int = 10, use_tma_reduce: bool = False) -> BatchedFit:
+    """All lanes ``(weights[b], lams[b])`` of the sample-sharded lasso at once; every rank returns ``beta`` [B, p].
+    ``backend``: "fused" (tensor-core products, in-kernel reduce-scatter and all-gather; CUDA or the host execution model),
+    "unfused" (torch matmul + ``torch.distributed`` all-reduce: the comparator and the plain CPU path)."""
+    if backend == "auto":
+        backend = "fused" if _native.on_device(x_local) else "unfused"
+    if backend == "fused":
+        return BatchedLassoLarge(x_local, y_local, lams, weights=weights, n_total=n_total, alpha=alpha, step=step,
+                                 use_tma_reduce=use_tma_reduce).run(max_iter, tol, check_every)
+    dev = x_local.device
+    lam = torch.as_tensor(np.asarray(lams, dtype=np.float32)).reshape(-1).to(dev)
+    B, (n_r, p) = int(lam.numel()), x_local.shape
+    if n_total is None:
+        t = torch.tensor([n_r], dtype=torch.float64, device=dev)
+        all_reduce_(t)
+        n_total = int(t.item())
+    if step is None:
+        step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
+    xf, yf = x_local.float(), y_local.float()
+    W = weights.float() if weights is not None else torch.ones(B, n_r, device=dev)
+    beta = torch.zeros(B, p, device=dev)
+    v = beta.clone()
+    tk, history = 1.0, []
+    obj = torch.full((B,), float("nan"), dtype=torch.float64)
+    d = torch.full((B,), float("inf"))
+    it = 0
+    shrink = 1.0 / (1.0 + step * lam * (1.0 - alpha))
+    for it in range(1, max_iter + 1):
+        eta = v @ xf.t()                                          # [B, n_r]
+        r = W * (yf[None, :] - torch.sigmoid(eta))
+        g = r @ xf                                                # [B, p]
+        all_reduce_(g)
+        z = v + step * g / n_total
+        thr = (step * lam * alpha)[:, None]
+        bnew = torch.sign(z) * (z.abs() - thr).clamp_min(0) * shrink[:, None]
+        tk1 = (1.0 + np.sqrt(1.0 + 4.0 * tk * tk)) / 2.0
+        mom = (tk - 1.0) / tk1
+        tk = tk1
+        dd = (bnew - beta).abs().amax(1)
+        v = bnew + mom * (bnew - beta)
+        beta = bnew
+        if it % check_every == 0 or it == max_iter:
+            sp = torch.where(eta > 0, eta + torch.log1p(torch.exp(-eta)), torch.log1p(torch.exp(eta)))
+            s = (W * (sp - yf[None, :] * eta)).double().sum(1)
+            all_reduce_(s)
+            bd = beta.double()
+            obj = (s / n_total + lam.double() * (alpha * bd.abs().sum(1) + 0.5 * (1.0 - alpha) * (bd * bd).sum(1))).cpu()
+            d = dd.cpu()
+            history.append((it, float(obj.mean()), float(d.max())))
+            if float(d.max()) < tol:
+                break
+    return BatchedFit(beta, it, obj, d, step, history)

@@ -428,8 +428,9 @@ def best_splits_torch(hist: torch.Tensor, lam: float = 1.0, gamma: float = 0.0, 
 
 
 # ------------------------------------------------------------------------------------------------ path 2b
-# Replicate-batched gradient as a tcgen05 GEMM fused with its reduce-scatter (csrc/gemm_rs.cu).  EXPERIMENTAL: the kernel
-# compiles for sm_100a and has a GPU test, but it has not run on hardware yet - nothing in the package calls it by default.
+# Replicate-batched gradient as a tcgen05 GEMM fused with its reduce-scatter (csrc/gemm_rs.cu).  Executed on the host model
+# of the asynchronous units (tests/test_emu_gemm.py) and by models/lasso_large.BatchedLassoLarge; its first hardware run is
+# tests/test_yy_gemm_rs_gpu.py.
 SIG_GEMM_RS = 32
 _native.register_signature("cml_xtr_gemm_reduce_scatter",
                            [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p,
@@ -452,17 +453,24 @@ class XtrGemmReduceScatter:
     residuals ([B, ld] or the [2B, ld] hi/lo split).  Results alternate between two symmetric buffers; the one returned by
     ``result()`` stays valid until the next ``launch``."""
 
-    def __init__(self, p: int, B: int, device, use_tma_reduce: bool = False):
+    def __init__(self, p: int, B: int, device, use_tma_reduce: bool = False, *, rank: Optional[int] = None, world: Optional[int] = None,
+                 bufs=None):
+        """``rank`` / ``world`` / ``bufs`` (two SymmBuffers of shape ``(genes_per_rank(p, world), B)``) override the process
+        group: that is how several ranks are played in one process (``symm.LocalGroup``)."""
         assert B % 32 == 0, "B must be a multiple of 32"
-        self.world = dist.get_world_size() if dist.is_initialized() else 1
-        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world = world if world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
+        self.rank = rank if rank is not None else (dist.get_rank() if dist.is_initialized() else 0)
         self.p, self.B, self.use_tma = p, B, use_tma_reduce
-        self.genes_per_rank = ((p + self.world - 1) // self.world + 31) // 32 * 32
+        self.genes_per_rank = self.genes_per_rank_for(p, self.world)
         self.gene0 = min(p, self.rank * self.genes_per_rank)
         self.genes_owned = max(0, min(p, self.gene0 + self.genes_per_rank) - self.gene0)
-        self.bufs = [symm.alloc((self.genes_per_rank, B), torch.float32, device) for _ in range(2)]
+        self.bufs = bufs if bufs is not None else [symm.alloc((self.genes_per_rank, B), torch.float32, device) for _ in range(2)]
         self.done = torch.zeros(4, dtype=torch.int32, device=device)
         self.epoch = 0
+
+    @staticmethod
+    def genes_per_rank_for(p: int, world: int) -> int:
+        return ((p + world - 1) // world + 31) // 32 * 32
 
     def launch(self, xt: torch.Tensor, rt: torch.Tensor, alpha: float = 1.0) -> None:
         assert xt.dtype == torch.bfloat16 and rt.dtype == torch.bfloat16 and xt.shape[1] == rt.shape[1] and xt.shape[1] % 8 == 0

@@ -69,3 +69,22 @@ def alloc(shape, dtype, device) -> SymmBuffer:
     buf = SymmBuffer(t, [int(p) for p in h.buffer_ptrs], [int(p) for p in hs.buffer_ptrs], mc, rank, world, h)
     buf._pad, buf._pad_handle = sig, hs
     return buf
+
+
+class LocalGroup:
+    """``world`` ranks played inside ONE process: every "rank" gets a plain tensor and the addresses of all of them, which is
+    all the fused kernels need.  For the host execution model (several emulated ranks on the CPU) and for single-GPU
+    multi-rank tests; a real multi-GPU run uses ``alloc``."""
+
+    def __init__(self, world: int, device="cpu"):
+        self.world, self.device = world, device
+        self.pads = [torch.zeros(_SIGNAL_PAD_WORDS, dtype=torch.int32, device=device) for _ in range(world)]
+
+    def alloc(self, shape, dtype) -> List[SymmBuffer]:
+        ts = [torch.zeros(shape, dtype=dtype, device=self.device) for _ in range(self.world)]
+        out = []
+        for r in range(self.world):
+            buf = SymmBuffer(ts[r], [t.data_ptr() for t in ts], [q.data_ptr() for q in self.pads], 0, r, self.world, None)
+            buf._keep = (ts, self.pads)
+            out.append(buf)
+        return out

@@ -14,8 +14,10 @@
 //                       halves add up to an fp32-accurate product.
 //   out_d fp32 [genes_per_rank][ldo] on owner d (symmetric memory, zero before the epoch starts); genes_per_rank % 32 == 0.
 // Completion: signal word (sig_base + rank) of every destination == epoch, released by the last CTA to finish.
-// STATUS: compiled for sm_100a and covered by tests/test_gemm_rs_gpu.py, which has not been run on hardware yet (GPU access
-// was closed when this was written); parallel/fused.py keeps the streaming kernel as the default gradient path.
+// STATUS: compiled for sm_100a; executed on the host model of the asynchronous units (csrc/emu/async_emu.cpp,
+// tests/test_emu_gemm.py: both landings, hi/lo split, split-K, several owners) - not yet on hardware (GPU access was closed
+// while it was written; tests/test_yy_gemm_rs_gpu.py is its first hardware run).  parallel/fused.py keeps the streaming
+// kernel as the default gradient path.
 #include <cuda_bf16.h>
 
 #include <cstring>

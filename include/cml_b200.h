@@ -273,7 +273,7 @@ int cml_prox_allgather_enet(float* grad_owned, int genes_owned, int gene0, const
 int cml_shard_transpose(const void* x, long long ldx, int rows_local, int cols, const int* col_start, const void* const* out_bufs,
     long long ldy, int row0, const void* const* peer_sigs, int rank, int world, unsigned* done_count,
     unsigned epoch, int sig_base, void* stream);
-/* Path 2b (EXPERIMENTAL - compiled, not yet run on hardware): replicate-batched gradient G = alpha * Xt . Rt^T as a CTA-pair
+/* Path 2b (executed on the host model of the asynchronous units, not yet on hardware): replicate-batched gradient G = alpha * Xt . Rt^T as a CTA-pair
  * tcgen05 GEMM whose epilogue reduces each tile into the owning rank's buffer over NVLink (register red.add.v4.f32, or a
  * TMA tensor reduce with use_tma_reduce = 1); split-K over the samples comes for free because the landing is an atomic add.
  * xt bf16 [p][ldxt] gene-major, rt bf16 [N][ldrt] with N = B or 2B (hi/lo split, column n lands in n % B); out_bufs[d]:
@@ -282,6 +282,17 @@ int cml_xtr_gemm_reduce_scatter(int p, int N, int B, int K, const void* xt_bf16,
                                 const void* const* out_bufs, long long ldo, int genes_per_rank, const void* const* peer_sigs,
                                 int rank, int world, unsigned* done_count, unsigned epoch, int sig_base, float alpha,
                                 int use_tma_reduce, void* stream);
+/* Elementwise halves of the replicate-batched sharded lasso iteration (csrc/lasso_batched.cu; reference call site: the repeated
+ * cv.glmnet fits of cml_targetaml_seanalysis.Rmd:94-101,728-773).  cml_batched_residual: rt[2B][ldn] (bf16 hi / lo rows) =
+ * split(W o (y - sigmoid(eta2[b] + eta2[B + b]))), loss[b] += weighted log-loss when loss != NULL.  cml_batched_prox_allgather:
+ * soft-threshold step of every lane on the owned genes (grad gene-major [genes_owned][ldg]; beta, v lane-major [B][ldo]) and
+ * peer stores of the new bf16 hi / lo rows of v into every rank's [2B][ldp] buffer; signal word (sig_base + rank) == epoch. */
+int cml_batched_residual(const float* eta2, long long lde, int B, int n, const float* y, const float* W, long long ldw, void* rt_bf16,
+                         long long ldn, double* loss, void* stream);
+int cml_batched_prox_allgather(const float* grad, long long ldg, int genes_owned, int gene0, int B, const float* lam, float step,
+                               float inv_n, float momentum, float shrink, float* beta, float* v, long long ldo,
+                               const void* const* vhl_bufs, long long ldp, const void* const* peer_sigs, int rank, int world,
+                               unsigned* done_count, unsigned epoch, int sig_base, float* delta_max, void* stream);
 int cml_xb_residual(const void* x_bf16, long long ldx, int n, int p, const float* v, float b0, const float* y, const float* w,
     float* R, float* eta_out, double* loss_sum, void* stream);
 size_t cml_hist_scratch_bytes(int p, int ft);

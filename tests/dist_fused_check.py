@@ -270,6 +270,15 @@ def main():
         err = float((fu.beta - un.beta).abs().max())
         print(f"[{rank}] EXPERIMENTAL elastic-net (alpha 0.5) fused vs unfused beta max diff {err:.2e}", flush=True)
         xok &= err < 2e-3
+        # replicate-batched sharded lasso: both products on tensor cores, the gradient through the fused GEMM -> reduce-scatter
+        lmax = LL.lambda_max(xl, yl, n)
+        lams = np.geomspace(lmax * 0.8, lmax * 0.1, 40)
+        xr = xl.bfloat16().float()
+        bu = LL.fit_batched(xr, yl, lams, n_total=n, max_iter=40, tol=0.0, backend="unfused")
+        bf = LL.fit_batched(xr, yl, lams, n_total=n, max_iter=40, tol=0.0, backend="fused", step=bu.step)
+        err = float((bf.beta - bu.beta).abs().max())
+        print(f"[{rank}] EXPERIMENTAL batched sharded lasso (40 lanes) fused vs unfused beta max diff {err:.2e}", flush=True)
+        xok &= err < 5e-4
         print(f"[{rank}] EXPERIMENTAL verdict: {'OK' if xok else 'FAILED'}", flush=True)
     t = torch.tensor([1.0 if ok else 0.0], device=dev)
     if world > 1:

@@ -192,3 +192,76 @@ def test_a_removed_wait_is_detected(n, use_tma):
     parity, phase = int(line.split("parity ")[1].split()[0]), int(line.split("phase now ")[1].split(")")[0])
     assert parity == phase, "test premise: the removed wait would have blocked"
     assert res.returncode != 0 or "RESULT wrong" in res.stdout
+
+
+def _batched_problem(n, p, B, seed):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, p, generator=g).bfloat16().float()          # bf16-exact design: both backends see the same numbers
+    bt = torch.zeros(p)
+    bt[:8] = torch.randn(8, generator=g) * 1.5
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ bt)).float()
+    from consensusml_b200.models import lasso_large as LL
+    lmax = LL.lambda_max(x, y, n)
+    import numpy as np
+    lams = np.geomspace(lmax * 0.9, lmax * 0.1, B)
+    W = torch.poisson(torch.ones(B, n), generator=g)
+    return x, y, lams, W
+
+
+@pytest.mark.parametrize("use_tma", [False, True])
+def test_batched_sharded_lasso_single_rank(use_tma):
+    """The replicate-batched iteration end to end on the kernels: tcgen05 eta product, residual split, fused GEMM ->
+    reduce-scatter gradient, proximal step + all-gather; against the torch iteration of the same lanes."""
+    from consensusml_b200.models import lasso_large as LL
+    x, y, lams, W = _batched_problem(150, 260, 20, 0)
+    ref = LL.fit_batched(x, y, lams, weights=W, backend="unfused", max_iter=40, tol=0.0)
+    with _native.emulation(seed=3):
+        got = LL.BatchedLassoLarge(x, y, lams, weights=W, step=ref.step, use_tma_reduce=use_tma).run(40, 0.0, 10)
+    assert got.iterations == ref.iterations == 40
+    assert (got.beta - ref.beta).abs().max() < 2e-4
+    assert (got.objective - ref.objective).abs().max() < 1e-5
+    assert torch.equal((got.beta.abs() > 1e-4).sum(1), (ref.beta.abs() > 1e-4).sum(1))
+    assert len(got.history) == 4 and got.history[-1][1] < got.history[0][1]
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_batched_sharded_lasso_several_ranks_in_one_process(world):
+    """Ranks played one after the other on the host model (symm.LocalGroup): every rank's gradient kernel reduces into the
+    owners' buffers, every owner's proximal kernel stores its rows of v into all ranks' copies."""
+    from consensusml_b200.models import lasso_large as LL
+    from consensusml_b200.parallel import symm
+    n, p, B = 210, 300, 12
+    x, y, lams, W = _batched_problem(n, p, B, world)
+    ref = LL.fit_batched(x, y, lams, weights=W, backend="unfused", max_iter=25, tol=0.0)
+    bounds = [n * r // world for r in range(world + 1)]
+    with _native.emulation(seed=world, sms=6):
+        group = symm.LocalGroup(world)
+        shared = LL.BatchedLassoLarge.shared_buffers(group, p, B)
+        ranks = [LL.BatchedLassoLarge(x[bounds[r]:bounds[r + 1]], y[bounds[r]:bounds[r + 1]], lams, weights=W[:, bounds[r]:bounds[r + 1]],
+                                      n_total=n, step=ref.step, rank=r, world=world, shared=shared) for r in range(world)]
+        for it in range(1, 26):
+            for s in ranks:
+                s.phase_a(check=(it == 25))
+            for s in ranks:
+                s.phase_b()
+        for s in ranks:
+            s.wait_all_gather()
+        beta = torch.cat([s.beta[:B, : s.rs.genes_owned] for s in ranks], 1)
+        loss = sum(s.loss[:B] for s in ranks) / n + sum(s.penalty_owned() for s in ranks)
+        vhl = [s.vhl.local.float() for s in ranks]
+    assert beta.shape == (B, p) and (beta - ref.beta).abs().max() < 2e-4
+    assert all(torch.equal(vhl[0], v) for v in vhl[1:])              # every rank holds the same extrapolated point
+    # the loss of iteration 25 is taken at its extrapolated point v, the comparator reports the objective at the same iteration
+    assert (loss - ref.objective).abs().max() < 5e-3
+
+
+def test_batched_solver_accepts_prepared_operands():
+    from consensusml_b200.models import lasso_large as LL
+    x, y, lams, W = _batched_problem(96, 130, 5, 4)
+    with _native.emulation(seed=2):
+        a = LL.BatchedLassoLarge(x, y, lams, weights=W, step=0.5)
+        b = LL.BatchedLassoLarge(None, y, lams, weights=W, step=0.5, n_total=96, prepared=(a.xb, a.xt))
+        ra, rb = a.run(6, 0.0, 3), b.run(6, 0.0, 3)
+    assert torch.equal(ra.beta, rb.beta)
+    with pytest.raises(ValueError):
+        LL.BatchedLassoLarge(None, y, lams, prepared=(a.xb, a.xt), n_total=96)
