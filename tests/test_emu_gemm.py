@@ -77,6 +77,27 @@ def test_gemm_many_sources_direct():
     assert (c - ref).abs().max() < 2e-4
 
 
+def test_gemm_staged_unaligned_source_blocks():
+    """8 sources of 750 rows: output column starts that are not 16-byte aligned (3000 B).  This is the shape whose TMA-store
+    epilogue faulted on the 8-GPU run of round 1; the chunks that cannot be TMA-stored must take the register path (the
+    model stops on a TMA store with an unaligned innermost coordinate, as the hardware did)."""
+    torch.manual_seed(8)
+    M, K, rows, n_src = 140, 72, 750, 8
+    N = n_src * rows
+    with _native.emulation(seed=5, sms=8):
+        xa, na = G.to_bf16_rows(torch.randn(M, K))
+        srcs = [G.to_bf16_rows(torch.randn(rows, K)) for _ in range(n_src)]
+        ldb = srcs[0][0].shape[1]
+        stage = torch.zeros(n_src * rows, ldb, dtype=torch.bfloat16)
+        stage_norm = torch.zeros(n_src * rows)
+        flags = torch.zeros(_native.cuda().cml_gemm_staged_flags(n_src, rows), dtype=torch.int32)
+        c = G.gemm_tn_staged(xa, [s[0].data_ptr() for s in srcs], N, rows, ldb, stage, stage_norm, flags, 1, 3, epilogue=G.EPI_SQDIST,
+                             norm_a=na, peer_norm_ptrs=[s[1].data_ptr() for s in srcs], n_copiers=2)
+    zb = torch.cat([s[0].float() for s in srcs])
+    nb = torch.cat([s[1] for s in srcs])
+    assert (c - (na[:, None] + nb[None, :] - 2 * xa.float() @ zb.t()).clamp_min(0)).abs().max() < 2e-4
+
+
 @pytest.mark.parametrize("variant,n_src,rank,grouped", [(1, 2, 0, 0), (2, 3, 1, 0), (2, 2, 1, 1), (1, 3, 2, 1)])
 def test_gemm_staged_all_gather(variant, n_src, rank, grouped):
     """Copier CTAs pull the source blocks into the staging buffer and flag tiles; GEMM CTAs of the same launch consume them."""
