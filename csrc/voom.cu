@@ -220,54 +220,113 @@ __global__ void voom_wls_kernel(const WlsArgs A) {
     for (int b = 0; b < KMAX; ++b)
       if (b >= a) M[a][b] = warp_sum(M[a][b]);
   }
+  double beta[KMAX], inv_diag[KMAX], cvc = 0.0;
+  if constexpr (KMAX <= 4) {
+    // small designs: invert the k x k normal matrix redundantly on every lane (Gauss-Jordan with partial pivoting)
 #pragma unroll
-  for (int a = 0; a < KMAX; ++a)
+    for (int a = 0; a < KMAX; ++a)
 #pragma unroll
-    for (int b = 0; b < KMAX; ++b)
-      if (b < a) M[a][b] = M[b][a];
-  // invert the k x k normal matrix (Gauss-Jordan with partial pivoting, redundantly on every lane)
-  double inv[KMAX][KMAX];
+      for (int b = 0; b < KMAX; ++b)
+        if (b < a) M[a][b] = M[b][a];
+    double inv[KMAX][KMAX];
 #pragma unroll
-  for (int a = 0; a < KMAX; ++a)
+    for (int a = 0; a < KMAX; ++a)
 #pragma unroll
-    for (int b = 0; b < KMAX; ++b) {
-      inv[a][b] = (a == b) ? 1.0 : 0.0;
-      if (a >= k || b >= k) M[a][b] = (a == b) ? 1.0 : 0.0;
-    }
+      for (int b = 0; b < KMAX; ++b) {
+        inv[a][b] = (a == b) ? 1.0 : 0.0;
+        if (a >= k || b >= k) M[a][b] = (a == b) ? 1.0 : 0.0;
+      }
 #pragma unroll
-  for (int c = 0; c < KMAX; ++c) {
-    int piv = c;
-    double best = fabs(M[c][c]);
+    for (int c = 0; c < KMAX; ++c) {
+      int piv = c;
+      double best = fabs(M[c][c]);
 #pragma unroll
-    for (int r2 = 0; r2 < KMAX; ++r2)
-      if (r2 > c && fabs(M[r2][c]) > best) { best = fabs(M[r2][c]); piv = r2; }
+      for (int r2 = 0; r2 < KMAX; ++r2)
+        if (r2 > c && fabs(M[r2][c]) > best) { best = fabs(M[r2][c]); piv = r2; }
 #pragma unroll
-    for (int r2 = 0; r2 < KMAX; ++r2) {
-      if (r2 == piv && piv != c) {
+      for (int r2 = 0; r2 < KMAX; ++r2) {
+        if (r2 == piv && piv != c) {
 #pragma unroll
-        for (int b = 0; b < KMAX; ++b) {
-          double t = M[c][b]; M[c][b] = M[r2][b]; M[r2][b] = t;
-          t = inv[c][b]; inv[c][b] = inv[r2][b]; inv[r2][b] = t;
+          for (int b = 0; b < KMAX; ++b) {
+            double t = M[c][b]; M[c][b] = M[r2][b]; M[r2][b] = t;
+            t = inv[c][b]; inv[c][b] = inv[r2][b]; inv[r2][b] = t;
+          }
         }
       }
+      const double d = 1.0 / M[c][c];
+#pragma unroll
+      for (int b = 0; b < KMAX; ++b) { M[c][b] *= d; inv[c][b] *= d; }
+#pragma unroll
+      for (int r2 = 0; r2 < KMAX; ++r2) {
+        if (r2 == c) continue;
+        const double f = M[r2][c];
+#pragma unroll
+        for (int b = 0; b < KMAX; ++b) { M[r2][b] -= f * M[c][b]; inv[r2][b] -= f * inv[c][b]; }
+      }
     }
-    const double d = 1.0 / M[c][c];
 #pragma unroll
-    for (int b = 0; b < KMAX; ++b) { M[c][b] *= d; inv[c][b] *= d; }
+    for (int a = 0; a < KMAX; ++a) {
+      beta[a] = 0.0;
+      inv_diag[a] = inv[a][a];
 #pragma unroll
-    for (int r2 = 0; r2 < KMAX; ++r2) {
-      if (r2 == c) continue;
-      const double f = M[r2][c];
-#pragma unroll
-      for (int b = 0; b < KMAX; ++b) { M[r2][b] -= f * M[c][b]; inv[r2][b] -= f * inv[c][b]; }
+      for (int b = 0; b < KMAX; ++b) beta[a] += inv[a][b] * rhs[b];
     }
-  }
-  double beta[KMAX];
+    if (A.contrast) {
 #pragma unroll
-  for (int a = 0; a < KMAX; ++a) {
-    beta[a] = 0.0;
+      for (int a = 0; a < KMAX; ++a) {
+        if (a >= k) continue;
 #pragma unroll
-    for (int b = 0; b < KMAX; ++b) beta[a] += inv[a][b] * rhs[b];
+        for (int b = 0; b < KMAX; ++b)
+          if (b < k) cvc += A.contrast[a] * inv[a][b] * A.contrast[b];
+      }
+    }
+  } else {
+    // wide designs: the augmented matrix [M | I] does not fit one lane's registers (2 * 64 doubles spilled 1 KB per thread).
+    // Its 2 * KMAX columns are spread over the lanes instead - lane c < KMAX holds M[:, c], lane KMAX + b holds e_b - and the
+    // same Gauss-Jordan runs with the pivot column broadcast by shuffles; every lane touches only its own KMAX doubles.
+    static_assert(2 * KMAX <= 32, "one column per lane");
+    constexpr unsigned kFull = 0xffffffffu;
+    double col[KMAX];
+#pragma unroll
+    for (int a = 0; a < KMAX; ++a) {
+      col[a] = (lane - KMAX == a) ? 1.0 : 0.0;
+#pragma unroll
+      for (int c = 0; c < KMAX; ++c)
+        if (lane == c) col[a] = (a >= k || c >= k) ? (a == c ? 1.0 : 0.0) : (a <= c ? M[a][c] : M[c][a]);
+    }
+#pragma unroll
+    for (int c = 0; c < KMAX; ++c) {
+      int piv = c;
+      double best = fabs(col[c]);
+#pragma unroll
+      for (int r2 = 0; r2 < KMAX; ++r2)
+        if (r2 > c && fabs(col[r2]) > best) { best = fabs(col[r2]); piv = r2; }
+      piv = __shfl_sync(kFull, piv, c);                       // the choice of the lane that owns column c
+#pragma unroll
+      for (int r2 = 0; r2 < KMAX; ++r2)
+        if (r2 > c && r2 == piv) { const double t = col[c]; col[c] = col[r2]; col[r2] = t; }
+      const double d = 1.0 / __shfl_sync(kFull, col[c], c);
+      col[c] *= d;
+#pragma unroll
+      for (int r2 = 0; r2 < KMAX; ++r2) {
+        if (r2 == c) continue;
+        const double f = __shfl_sync(kFull, col[r2], c);      // M[r2][c] before this step's update
+        col[r2] -= f * col[c];
+      }
+    }
+    // lane KMAX + b now holds inv[:, b]
+    double rb = 0.0, cb_ = 0.0;
+#pragma unroll
+    for (int b = 0; b < KMAX; ++b)
+      if (lane == KMAX + b) { rb = rhs[b]; cb_ = (A.contrast && b < k) ? A.contrast[b] : 0.0; }
+    double ca = 0.0;
+#pragma unroll
+    for (int a = 0; a < KMAX; ++a) {
+      beta[a] = warp_sum(col[a] * rb);
+      inv_diag[a] = __shfl_sync(kFull, col[a], KMAX + a);
+      if (A.contrast && a < k) ca += A.contrast[a] * col[a];
+    }
+    cvc = warp_sum(ca * cb_);
   }
   double rss = 0.0;
   for (int s = lane; s < A.S; s += 32) {
@@ -285,19 +344,14 @@ __global__ void voom_wls_kernel(const WlsArgs A) {
     for (int j = 0; j < KMAX; ++j)
       if (j < k) {
         A.coef[(size_t)g * k + j] = beta[j];
-        A.stdev_unscaled[(size_t)g * k + j] = sqrt(inv[j][j]);
+        A.stdev_unscaled[(size_t)g * k + j] = sqrt(inv_diag[j]);
       }
     A.sigma[g] = sqrt(rss / (double)(A.S - k));
     if (A.contrast) {
-      double cb = 0.0, cvc = 0.0;
+      double cb = 0.0;
 #pragma unroll
-      for (int a = 0; a < KMAX; ++a) {
-        if (a >= k) continue;
-        cb += A.contrast[a] * beta[a];
-#pragma unroll
-        for (int b = 0; b < KMAX; ++b)
-          if (b < k) cvc += A.contrast[a] * inv[a][b] * A.contrast[b];
-      }
+      for (int a = 0; a < KMAX; ++a)
+        if (a < k) cb += A.contrast[a] * beta[a];
       A.coef_c[g] = cb;
       A.su_c[g] = sqrt(cvc);
     }

@@ -325,3 +325,24 @@ def test_path_kernels_reproduce_the_stored_glmnet_path_on_the_real_cohort(aml, g
         assert np.abs(pb.dev_ratio[0].double().numpy() - glmnet_oracle["rep1_train_dev_ratio"]).max() < 1e-5
     a, b = out["0"], out["1"]
     assert torch.equal(a.npasses, b.npasses) and torch.equal(a.eta, b.eta) and torch.equal(a.dense(1), b.dense(1))
+
+
+@pytest.mark.parametrize("k", [3, 6, 8])
+def test_voom_wls_with_wide_designs(k):
+    """Designs beyond two columns: k = 3 takes the in-register inverse (KMAX = 4), k = 6 / 8 the lane-distributed Gauss-Jordan
+    (KMAX = 8, one column of [M | I] per lane).  Oracle: the float64 host restatement of the same voom + lmFit + contrast."""
+    from consensusml_b200.stats import de as DE
+    c, g = nb_counts(400, 40, seed=20 + k, n_de=60)
+    rng = np.random.default_rng(k)
+    X = np.column_stack([np.ones(40), np.asarray(g, dtype=np.float64)] + [rng.normal(size=40) for _ in range(k - 2)])
+    cvec = np.zeros(k)
+    cvec[1] = 1.0
+    cvec[k - 1] = -0.5
+    ref = DE.voom_de(torch.from_numpy(c), g, design=X, contrast=cvec)                  # CPU: oracle path
+    with _native.emulation(seed=2):
+        res = DE.voom_de(torch.from_numpy(c), g, design=X, contrast=cvec)
+    assert np.array_equal(np.asarray(res.keep), np.asarray(ref.keep))
+    assert np.abs(np.asarray(res.logFC) - np.asarray(ref.logFC)).max() < 2e-3
+    t_a, t_b = np.asarray(res.t), np.asarray(ref.t)
+    assert (np.abs(t_a - t_b) / np.maximum(1.0, np.abs(t_b))).max() < 1e-2
+    assert abs(res.s2_prior - ref.s2_prior) / ref.s2_prior < 5e-3
