@@ -54,35 +54,25 @@ def dispersion_moments(counts: torch.Tensor, sf: torch.Tensor) -> torch.Tensor:
     return ((var - mu * (1.0 / sf).mean()) / (mu * mu).clamp_min(1e-12)).clamp_min(0)
 
 
-def deseq_vst(counts: torch.Tensor, sf: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Variance-stabilising transform with a parametric dispersion trend alpha(mu) = a1/mu + a0 fitted by least
-    squares to the moment estimates (closed-form VST of DESeq2 for that trend), log2 scale."""
-    sf = deseq_size_factors(counts) if sf is None else sf
-    q = counts.double() / sf[None, :]
-    mu = q.mean(1)
-    disp = dispersion_moments(counts, sf)
-    use = (mu > 1) & (disp > 0)
-    if int(use.sum()) >= 3:
-        A = torch.stack([1.0 / mu[use], torch.ones_like(mu[use])], 1)
-        sol = torch.linalg.lstsq(A, disp[use, None]).solution.flatten()
-        a1, a0 = float(sol[0].clamp_min(1e-8)), float(sol[1].clamp_min(1e-8))
+def deseq_vst(counts: torch.Tensor, sf: Optional[torch.Tensor] = None, *, fit=None, fit_type: str = "parametric", return_fit: bool = False):
+    """DESeq2's ``varianceStabilizingTransformation`` (blind design): gene-wise dispersions by the Cox-Reid adjusted profile
+    likelihood, parametric trend by the Gamma GLM, closed-form transform (``models.deseq``; kernels in csrc/deseq.cu).
+    ``fit`` = a training set's ``DispersionFit``: transform new samples with its geometric means and dispersion function."""
+    from . import deseq as DQ
+    out, fit = DQ.vst(counts, fit, sf=sf, fit_type=fit_type)
+    return (out, fit) if return_fit else out
+
+
+def deseq_rlog(counts: torch.Tensor, sf: Optional[torch.Tensor] = None, *, frozen=None, return_fit: bool = False):
+    """DESeq2's ``rlog`` (blind design): ridge NB GLM with one coefficient per sample, prior variance by weighted quantile
+    matching, dispersions from the fitted trend (``models.deseq``).  ``frozen`` = a training set's ``RlogFit``: new samples are
+    fitted against its intercepts, trend and prior variance."""
+    from . import deseq as DQ
+    if frozen is not None:
+        r = DQ.rlog(counts, frozen=frozen)
     else:
-        a1, a0 = 1.0, 0.01
-    return torch.log((1 + a1 + 2 * a0 * q + 2 * torch.sqrt(a0 * q * (1 + a1 + a0 * q))) / (4 * a0)) / np.log(2)
-
-
-def deseq_rlog(counts: torch.Tensor, sf: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Regularised log: log2 normalised counts shrunk towards the gene's mean with a strength that grows as the count
-    (hence the information) shrinks - a ridge approximation of DESeq2's rlog."""
-    sf = deseq_size_factors(counts) if sf is None else sf
-    q = counts.double() / sf[None, :]
-    lq = torch.log2(q + 0.5)
-    base = torch.log2(q.mean(1, keepdim=True) + 0.5)
-    disp = dispersion_moments(counts, sf)[:, None]
-    var_obs = (1.0 / (q + 0.5) + disp) / np.log(2) ** 2           # delta-method variance of log2 count
-    prior = (lq - base).var(1, unbiased=True).median().clamp_min(1e-6)
-    shrink = prior / (prior + var_obs)
-    return base + shrink * (lq - base)
+        r = DQ.rlog(counts, DQ.estimate_dispersions(counts, sf, None, "parametric"))
+    return (r.values, r) if return_fit else r.values
 
 
 # ------------------------------------------------------------------------------------------------ classifiers
@@ -328,13 +318,14 @@ _TRANSFORMED = {"svmRadial": _svm_radial, "LogitBoost": _logitboost, "blackboost
 class _TransformedModel:
     """A learner trained on VST / rlog values; ``predict`` takes raw counts (genes x samples) like the count models."""
 
-    def __init__(self, model, pre, size_factors_train):
-        self.model, self.pre = model, pre
-        self.geo_ref_ = None
+    def __init__(self, model, pre, train_fit):
+        self.model, self.pre, self.train_fit = model, pre, train_fit
 
     def _transform(self, counts):
-        sf = deseq_size_factors(counts)
-        return (deseq_vst(counts, sf) if self.pre == "deseq-vst" else deseq_rlog(counts, sf)).float().t().contiguous()
+        # new samples against the TRAINING set's geometric means, dispersion function, rlog intercepts and prior variance
+        # (MLSeq: estimateSizeFactors(geoMeans = ), dispersionFunction<-, rlog(intercept = , betaPriorVar = ))
+        t = deseq_vst(counts, fit=self.train_fit) if self.pre == "deseq-vst" else deseq_rlog(counts, frozen=self.train_fit)
+        return t.float().t().contiguous()
 
     def predict(self, counts: torch.Tensor) -> torch.Tensor:
         return self.model.predict(self._transform(counts))
@@ -376,10 +367,10 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
             return _TRANSFORMED[method](param, seed)
         return NearestShrunkenCentroids(threshold=float(param))
 
-    transformed = None
-    if method in _TRANSFORMED:                                    # caret-trained learners on the VST / rlog matrix
-        sf = deseq_size_factors(counts_train)
-        transformed = (deseq_vst(counts_train, sf) if pre == "deseq-vst" else deseq_rlog(counts_train, sf)).float()
+    transformed = train_fit = None
+    if method in _TRANSFORMED or method == "pam":                 # learners on the VST / rlog matrix
+        transformed, train_fit = deseq_vst(counts_train, return_fit=True) if pre == "deseq-vst" else deseq_rlog(counts_train, return_fit=True)
+        transformed = transformed.float() if method in _TRANSFORMED else transformed
 
     def fit_predict(param, tr, te):
         ctr, cte, ytr = counts_train[:, tr], counts_train[:, te], y_train[tr]
@@ -389,9 +380,7 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
         if method in ("PLDA", "PLDA2", "NBLDA"):
             return mdl.fit(ctr, ytr, n_classes).predict(cte)
         if method == "pam":
-            sf = deseq_size_factors(counts_train)
-            t = deseq_vst(counts_train, sf) if pre == "deseq-vst" else deseq_rlog(counts_train, sf)
-            return mdl.fit(t[:, tr], ytr, n_classes).predict(t[:, te])
+            return mdl.fit(transformed[:, tr], ytr, n_classes).predict(transformed[:, te])
         e, w = _voom_transform(ctr, ytr, n_classes)
         mdl.fit(e, ytr, n_classes, weights=w)
         lib = cte.double().sum(0)
@@ -411,13 +400,11 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
     best = max(table, key=lambda k: (table[k], k))
     mdl = make(best)
     if method in _TRANSFORMED:
-        mdl = _TransformedModel(mdl.fit(transformed.t().contiguous(), y_train), pre, sf)
+        mdl = _TransformedModel(mdl.fit(transformed.t().contiguous(), y_train), pre, train_fit)
     elif method in ("PLDA", "PLDA2", "NBLDA"):
         mdl.fit(counts_train, y_train, n_classes)
     elif method == "pam":
-        sf = deseq_size_factors(counts_train)
-        t = deseq_vst(counts_train, sf) if pre == "deseq-vst" else deseq_rlog(counts_train, sf)
-        mdl.fit(t, y_train, n_classes)
+        mdl.fit(transformed, y_train, n_classes)
     else:
         e, w = _voom_transform(counts_train, y_train, n_classes)
         mdl.fit(e, y_train, n_classes, weights=w)

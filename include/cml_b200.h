@@ -233,6 +233,13 @@ int cml_mlp_adam(float* const* state, const float* gw1, long long ldg, const flo
 /* ---- K14: count-based discriminants (csrc/discriminant.cu) - MLSeq classify() zoo, VikasP/AML.R:167-264.
  * DESeq median-of-ratios size factors of a genes x samples matrix; Poisson-LDA scores out [B][n][k] for B fitted models. */
 int cml_deseq_size_factors(const double* counts, int G, int S, double* loggeo_scratch, double* sf, void* stream);
+/* DESeq2's per-gene fits (csrc/deseq.cu; reference: VikasP/AML.R:174-264, MLSeq deseq-vst / deseq-rlog pre-processing): gene-wise NB
+ * dispersion = maximum of the Cox-Reid adjusted profile likelihood (group-indicator design; group NULL = one group), and the
+ * regularised log transform (ridge NB GLM with one coefficient per sample), out[G][S] in log2. */
+int cml_nb_dispersion(const double* counts, int G, int S, const double* sf, const int* group, int n_groups, double min_disp,
+                      double max_disp, double* base_mean, double* base_var, double* disp, int* iters, void* stream);
+int cml_rlog(const double* counts, int G, int S, const double* sf, const double* alpha, const double* base_mean, const double* intercept,
+             double lambda, double lambda0, double tol, int maxit, double* out, double* intercept_out, int* iters, void* stream);
 int cml_plda_scores(const double* x, int G, int n, int k, int B, const double* logd, const double* gd, const double* s,
                     const double* logprior, double* out, void* stream);
 
