@@ -52,6 +52,7 @@ class DispersionFit:
     coefs: Tuple[float, float]       # (asymptDisp, extraPois) for "parametric", (mean, 0) for "mean"
     iters: torch.Tensor              # [G] line-search iterations
     trend: Optional[tuple] = None    # "local": (log mean grid, log dispersion on it)
+    vst_table: Optional[tuple] = None  # "local": the integrated transform tabulated on the data it was fitted to (asinh grid, values, scale, shift)
 
     def dispersion_at(self, mu: torch.Tensor) -> torch.Tensor:
         if self.fit_type == "parametric":
@@ -291,18 +292,24 @@ def vst(counts: torch.Tensor, fit: Optional[DispersionFit] = None, *, sf: Option
         out = (2 * torch.asinh(torch.sqrt(al * q)) - np.log(al) - np.log(4.0)) / ln2
     else:
         # numerical integration of 1 / sqrt(mu + alpha(mu) mu^2) on a grid that is uniform in asinh, then rescaled so that
-        # the transform agrees with log2 for large counts (DESeq2 getVarianceStabilizedData, local fit)
-        qmax = float(q.max())
-        xg = torch.sinh(torch.linspace(float(np.arcsinh(0.0)), float(np.arcsinh(max(qmax, 1.0))), 1000, dtype=torch.float64))[1:]
-        xg = xg.to(q.device)
-        integrand = 1.0 / torch.sqrt(xg + fit.dispersion_at(xg) * xg * xg)
-        splf_x = torch.asinh((xg[1:] + xg[:-1]) / 2)
-        splf_y = torch.cumsum((xg[1:] - xg[:-1]) * (integrand[1:] + integrand[:-1]) / 2, 0)
-        h1, h2 = torch.quantile(q.mean(1), torch.tensor([0.95, 0.999], dtype=torch.float64, device=q.device))
-        e1, e2 = _interp(torch.asinh(h1)[None], splf_x, splf_y)[0], _interp(torch.asinh(h2)[None], splf_x, splf_y)[0]
-        eta = (torch.log2(h2) - torch.log2(h1)) / (e2 - e1)
-        xi = torch.log2(h1) - eta * e1
-        out = eta * _interp(torch.asinh(q).flatten(), splf_x, splf_y).reshape(q.shape) + xi
+        # the transform agrees with log2 for large counts (DESeq2 getVarianceStabilizedData, local fit).  The table and its
+        # scaling are made once, from the data the trend was fitted to, and reused for new samples.
+        if fit.vst_table is None:
+            qmax = float(q.max()) * 8.0
+            xg = torch.sinh(torch.linspace(0.0, float(np.arcsinh(max(qmax, 1.0))), 2000, dtype=torch.float64))[1:].to(q.device)
+            integrand = 1.0 / torch.sqrt(xg + fit.dispersion_at(xg) * xg * xg)
+            splf_x = torch.asinh((xg[1:] + xg[:-1]) / 2)
+            splf_y = torch.cumsum((xg[1:] - xg[:-1]) * (integrand[1:] + integrand[:-1]) / 2, 0)
+            h1, h2 = torch.quantile(q.mean(1), torch.tensor([0.95, 0.999], dtype=torch.float64, device=q.device))
+            e1, e2 = _interp(torch.asinh(h1)[None], splf_x, splf_y)[0], _interp(torch.asinh(h2)[None], splf_x, splf_y)[0]
+            eta = (torch.log2(h2) - torch.log2(h1)) / (e2 - e1)
+            fit.vst_table = (splf_x, splf_y, float(eta), float(torch.log2(h1) - eta * e1))
+        splf_x, splf_y, eta, xi = fit.vst_table
+        aq = torch.asinh(q).flatten()
+        out = eta * _interp(aq, splf_x, splf_y) + xi
+        beyond = aq > splf_x[-1]                                    # past the table: the transform runs parallel to log2 there
+        out = torch.where(beyond, eta * splf_y[-1] + xi + (torch.log2(torch.sinh(aq).clamp_min(1e-300)) - torch.log2(torch.sinh(splf_x[-1]))), out)
+        out = out.reshape(q.shape)
     return out, fit
 
 
