@@ -331,6 +331,33 @@ def main():
     except Exception as exc:
         mc = {"error": repr(exc)}
 
+    # ---------------- secondary: the same pipeline with this rank's stages overlapped on CUDA streams (dist.task_streams) ----------------
+    # opt-in mode (parallel/tasks.py): timed here so that the first hardware run also says what it is worth; never part of `value`
+    overlap = None
+    try:
+        if not on_gpu:
+            raise RuntimeError("skipped in the CPU dry run")
+        cfg_ov = C.load(None, base + ["write_outputs=false", "dist.task_streams=4"])
+        pipeline.run(cfg_ov, resident)
+        tms = []
+        s_ov = None
+        for _ in range(2):
+            flush()
+            barrier()
+            a, b = Stamp(), Stamp()
+            a.record()
+            s_ov = pipeline.run(cfg_ov, resident)
+            b.record()
+            barrier()
+            tms.append(a.elapsed_time(b))
+        tt = torch.tensor(tms, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        overlap = {"task_streams": 4, "wall_s": float(tt.mean().item()) / 1e3, "same_lasso_result": s_ov.get("lasso") == summary.get("lasso"),
+                   "same_top50": s_ov["consensus"]["top"] == summary["consensus"]["top"], "failed_tasks": s_ov.get("failed_tasks")}
+    except Exception as exc:
+        overlap = {"error": repr(exc)}
+
     # ---------------- secondary (N > 1): fused compute + collective paths ----------------
     fused = None
     if world > 1 and not args.no_fused:
@@ -366,7 +393,7 @@ def main():
                                  "kernel of ours); counted in consensusml_b200._native.check; torch's own kernels excluded",
             "gpu_launches_rank0_by_entry": calls,
             "accuracy": acc, "schedule": sched, "step_ms": ms, "failed_tasks": summary.get("failed_tasks"),
-            "secondary": {"fits": fits, "model_comp": mc, "fused_paths": fused},
+            "secondary": {"fits": fits, "model_comp": mc, "overlapped_stages": overlap, "fused_paths": fused},
         }, default=float))
     if world > 1:
         dist.destroy_process_group()

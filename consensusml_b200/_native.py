@@ -162,7 +162,8 @@ def reset_calls() -> None:
 
 
 def check(code: int, what: str) -> None:
-    calls[what] = calls.get(what, 0) + 1
+    with _lock:                                    # tasks may run on several host threads (parallel/tasks.py)
+        calls[what] = calls.get(what, 0) + 1
     if code != 0:
         msg = cuda().cml_last_error().decode(errors="replace")
         raise NativeError(f"{what} failed with code {code}: {msg}")

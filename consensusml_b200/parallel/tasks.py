@@ -13,6 +13,10 @@ Design rules
     communication, no work stealing: the run is a second long, a dynamic queue would cost more than it saves).
   * Results are small (per-gene vectors, n x n proximity sums); one ``all_gather_object`` at the end gives every rank
     every result.  Device time per task is recorded so the limiting task can be named.
+  * Stage overlap inside a rank (``streams > 1``): the rank's tasks run on a small pool of host threads, each with its own
+    CUDA stream, heaviest first.  The sequential lasso chain is latency bound (one CTA per fit, at most 94 of 148 SMs, long
+    dependent launches) - the forest chunks, SVMs and boosting runs fill the rest of the machine meanwhile.  Tasks only read
+    the shared cohort tensors and return host results, so they need no synchronisation among themselves.
 """
 from __future__ import annotations
 
@@ -69,8 +73,63 @@ class TaskError:
         return f"TaskError({self.name!r}, {self.error!r})"
 
 
-def run_tasks(tasks: List[Task], *, enabled: bool = True, fail_fast: bool = True) -> tuple[Dict[str, Any], TaskReport]:
+def _run_one(t: Task, fail_fast: bool, stream) -> tuple:
+    """(result, seconds) of one task, run on ``stream`` when given (device work is complete on return)."""
+    t0 = time.perf_counter()
+    try:
+        if stream is not None:
+            with torch.cuda.stream(stream):
+                out = t.fn()
+            stream.synchronize()
+        else:
+            out = t.fn()
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+    except Exception as exc:                           # noqa: BLE001 - reported, not swallowed
+        if fail_fast:
+            raise
+        out = TaskError(t.name, exc)
+    return out, time.perf_counter() - t0
+
+
+def _run_overlapped(mine: List[Task], streams: int, fail_fast: bool, local: Dict[str, Any], secs: Dict[str, float]) -> None:
+    import threading
+    from concurrent.futures import ThreadPoolExecutor
+    use_cuda = torch.cuda.is_available()
+    tls = threading.local()
+    main = torch.cuda.current_stream() if use_cuda else None
+    made: List[Any] = []
+    lock = threading.Lock()
+    dev = torch.cuda.current_device() if use_cuda else None
+
+    def work(t: Task):
+        if use_cuda and not hasattr(tls, "stream"):
+            torch.cuda.set_device(dev)                 # a new host thread starts on device 0
+            tls.stream = torch.cuda.Stream()
+            tls.stream.wait_stream(main)               # everything queued before the stage started is visible
+            with lock:
+                made.append(tls.stream)
+        return _run_one(t, fail_fast, getattr(tls, "stream", None))
+
+    order = sorted(range(len(mine)), key=lambda i: (-mine[i].cost, i))
+    with ThreadPoolExecutor(max_workers=streams, thread_name_prefix="cml-task") as pool:
+        futs = {mine[i].name: pool.submit(work, mine[i]) for i in order}
+        err = None
+        for name, f in futs.items():
+            try:
+                local[name], secs[name] = f.result()
+            except Exception as exc:                   # noqa: BLE001 - first failure is re-raised once every thread has finished
+                err = err or exc
+    for s in made:
+        main.wait_stream(s)
+    if err is not None:
+        raise err
+
+
+def run_tasks(tasks: List[Task], *, enabled: bool = True, fail_fast: bool = True, streams: int = 1) -> tuple[Dict[str, Any], TaskReport]:
     """Run every task on the rank it is assigned to and return ``{task name: result}`` complete on every rank.
+    ``streams > 1``: this rank's tasks overlap on that many CUDA streams (host threads); ``seconds`` are then wall times of
+    overlapping intervals and ``rank_seconds`` the wall time of the whole stage.
     Results must be picklable and live on the host (tasks copy what they return off the device).
     ``fail_fast=False`` turns an exception inside a task into a ``TaskError`` result instead of aborting the run (every rank
     still reaches the gather, so a failed stage cannot leave the other ranks waiting)."""
@@ -82,30 +141,29 @@ def run_tasks(tasks: List[Task], *, enabled: bool = True, fail_fast: bool = True
     amap = assign(tasks, world)
     local: Dict[str, Any] = {}
     secs: Dict[str, float] = {}
-    for t in tasks:
-        if amap[t.name] != rank:
-            continue
-        if torch.cuda.is_available():
-            torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        try:
-            local[t.name] = t.fn()
-            if torch.cuda.is_available():
-                torch.cuda.synchronize()
-        except Exception as exc:                       # noqa: BLE001 - reported, not swallowed
-            if fail_fast:
-                raise
-            local[t.name] = TaskError(t.name, exc)
-        secs[t.name] = time.perf_counter() - t0
+    mine = [t for t in tasks if amap[t.name] == rank]
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+    stage0 = time.perf_counter()
+    from .. import _native
+    if streams > 1 and len(mine) > 1 and not _native.emulating():      # the host execution model is single-threaded by design
+        _run_overlapped(mine, int(streams), fail_fast, local, secs)
+    else:
+        for t in mine:
+            local[t.name], secs[t.name] = _run_one(t, fail_fast, None)
+    stage_s = time.perf_counter() - stage0
     if world > 1:
         gathered: List[Optional[tuple]] = [None] * world
-        dist.all_gather_object(gathered, (local, secs))
+        dist.all_gather_object(gathered, (local, secs, stage_s))
         results: Dict[str, Any] = {}
         all_secs: Dict[str, float] = {}
-        for part, s in gathered:
+        stage = []
+        for part, s, st in gathered:
             results.update(part)
             all_secs.update(s)
+            stage.append(st)
     else:
-        results, all_secs = local, secs
-    rep = TaskReport(amap, all_secs, [sum(v for k, v in all_secs.items() if amap[k] == r) for r in range(world)])
+        results, all_secs, stage = local, secs, [stage_s]
+    rank_s = stage if streams > 1 else [sum(v for k, v in all_secs.items() if amap[k] == r) for r in range(world)]
+    rep = TaskReport(amap, all_secs, rank_s)
     return {n: results[n] for n in names}, rep

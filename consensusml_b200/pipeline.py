@@ -269,7 +269,7 @@ def run(cfg: Config, cohort: Optional[Cohort] = None, log: Optional[RunLog] = No
     # a checkpoint is only reused for the same configuration AND the same data (ids, labels, split and assay content)
     key = cfg.hash(["lasso", "svm", "rf", "gbm", "mlp", "split"]) + ":" + fp
     tasks = build_tasks(cfg, cohort, dev, store, key, log)
-    results, report = run_tasks(tasks, enabled=cfg.dist.enabled, fail_fast=cfg.fail_fast)
+    results, report = run_tasks(tasks, enabled=cfg.dist.enabled, fail_fast=cfg.fail_fast, streams=cfg.dist.task_streams)
     from .parallel.tasks import TaskError
     failed = {n: r.error for n, r in results.items() if isinstance(r, TaskError)}
     for t in tasks:

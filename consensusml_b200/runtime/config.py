@@ -106,6 +106,7 @@ class DistConfig:
     enabled: bool = True                   # under torchrun: spread the independent stages over the ranks (parallel/tasks.py)
     backend: str = "auto"                  # nccl on GPUs, gloo on CPU (parallel.dist.init)
     fused: bool = True                     # large sample-sharded cohorts: in-kernel collectives (models/lasso_large, gbm_large)
+    task_streams: int = 1                  # > 1: the stages a rank owns run concurrently, each on its own CUDA stream (opt-in: not yet timed on hardware)
 
 
 @dataclass

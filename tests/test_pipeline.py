@@ -210,3 +210,39 @@ def test_pipeline_on_the_kernel_path_under_emulation(tmp_path):
     assert s["rf_60"]["oob_error"] < 0.2 and s["svm1"]["auc"] > 0.9 and s["svm2"]["auc"] > 0.9 and s["mlp"]["auc"] > 0.85
     assert s["stability"]["stable_genes"] > 5 and len(s["consensus"]["top"]) == 50
     assert os.path.exists(tmp_path / "standouttable.csv")
+
+
+def test_overlapped_stages_give_the_same_tables(tmp_path):
+    """dist.task_streams > 1: the rank's tasks run on a pool of host threads (one CUDA stream each on a GPU); every task draws its
+    randomness from its own identity, so the result files are those of the sequential run."""
+    import pandas as pd
+    ov = ["device=cpu", "lasso.exclusion_reps=2", "rf.n_trees=[60, 90]", "rf.chunk=30", "rf.proximity=false", "checkpoint=false",
+          'gbm.reps=[{"max_depth": 2, "nrounds": 2}, {"max_depth": 3, "nrounds": 2}]', 'svm.kernels=["linear", "radial"]', "svm.weightfilt=[null]"]
+    a = pipeline.run(C.load(None, ov + ["io.out_dir=" + str(tmp_path / "seq")]))
+    b = pipeline.run(C.load(None, ov + ["io.out_dir=" + str(tmp_path / "par"), "dist.task_streams=3"]))
+    assert a["lasso"] == b["lasso"] and a["consensus"]["top"] == b["consensus"]["top"]
+    ta, tb = pd.read_csv(tmp_path / "seq" / "standouttable.csv"), pd.read_csv(tmp_path / "par" / "standouttable.csv")
+    pd.testing.assert_frame_equal(ta, tb)
+    assert b["schedule"]["rank_seconds"][0] > 0 and set(b["schedule"]["group_seconds"]) == set(a["schedule"]["group_seconds"])
+
+
+def test_overlapped_task_runner_propagates_failures():
+    import time as _t
+    from consensusml_b200.parallel.tasks import Task, TaskError, run_tasks
+    seen = []
+
+    def ok(i):
+        def f():
+            _t.sleep(0.02)
+            seen.append(i)
+            return i
+        return f
+
+    def bad():
+        raise ValueError("boom")
+    tasks = [Task(f"t{i}", float(i), ok(i)) for i in range(6)] + [Task("bad", 10.0, bad)]
+    res, rep = run_tasks(tasks, fail_fast=False, streams=3)
+    assert [res[f"t{i}"] for i in range(6)] == list(range(6)) and isinstance(res["bad"], TaskError) and sorted(seen) == list(range(6))
+    assert rep.rank_seconds[0] < sum(rep.seconds.values())            # the intervals overlapped
+    with pytest.raises(ValueError, match="boom"):
+        run_tasks(tasks, fail_fast=True, streams=3)

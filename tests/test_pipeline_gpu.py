@@ -39,3 +39,17 @@ def test_counts_to_cohort_gpu():
     ia = [co_g.gene_ids.index(i) for i in common[:200]]
     ib = [co_c.gene_ids.index(i) for i in common[:200]]
     assert (co_g.assay[ia].cpu() - co_c.assay[ib]).abs().max() < 2e-3
+
+
+@pytest.mark.gpu
+def test_overlapped_stages_on_cuda_streams(tmp_path):
+    """dist.task_streams: the stages of one rank on concurrent CUDA streams (host threads) - same lasso result, same genes on top."""
+    from consensusml_b200 import pipeline
+    from consensusml_b200.runtime import config as C
+    ov = ["device=cuda:0", "lasso.exclusion_reps=3", "rf.n_trees=[500, 1000]", "checkpoint=false", "write_outputs=false",
+          'gbm.reps=[{"max_depth": 2, "nrounds": 20}, {"max_depth": 3, "nrounds": 20}]']
+    a = pipeline.run(C.load(None, ov + ["io.out_dir=" + str(tmp_path / "seq")]))
+    b = pipeline.run(C.load(None, ov + ["io.out_dir=" + str(tmp_path / "par"), "dist.task_streams=4"]))
+    assert "failed_tasks" not in a and "failed_tasks" not in b
+    assert a["lasso"] == b["lasso"]
+    assert len(set(a["consensus"]["top"]) & set(b["consensus"]["top"])) >= 45      # forests use float atomics: order of ties may move
