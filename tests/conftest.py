@@ -16,9 +16,17 @@ def pytest_configure(config):
     _build.build_host()
 
 
+# GPU run order: the files whose kernels have the longest hardware record first, whole-pipeline and multi-GPU tests after the
+# single-kernel ones (a fault in a new kernel then fails its own small test, not the pipeline's), first-time-on-hardware code
+# next to last, the allocation-free entry point last.  (-x stops at the first failure: what is proven should get to run.)
+_LATE = ["test_y_kernels_gpu.py", "test_pipeline_gpu.py", "test_x_fused.py", "test_yy_gemm_rs_gpu.py", "test_zz_no_alloc.py"]
+
+
 def pytest_collection_modifyitems(config, items):
     import torch
     if torch.cuda.is_available():
+        rank = {name: i + 1 for i, name in enumerate(_LATE)}
+        items.sort(key=lambda it: rank.get(os.path.basename(str(it.fspath)), 0))      # stable: collection order inside a class
         return
     skip = pytest.mark.skip(reason="no CUDA device")
     for item in items:
