@@ -367,3 +367,68 @@ def case_forest_proximity_as_one_hot_gemm(be):
         p2, q2 = TR.proximity_gemm(be.dev(leaf), None, max_nodes)
     assert torch.equal(_h(p1), want_p) and torch.equal(_h(q1), both.float().sum(0))
     assert torch.equal(_h(p2), (leaf[:, :, None] == leaf[:, None, :]).float().sum(0)) and float(_h(q2).min()) == T
+
+
+def case_deseq_dispersion_and_rlog_kernels_follow_the_float64_path(be):
+    """csrc/deseq.cu against the vectorised float64 restatement of the same DESeq2 steps (models/deseq.py)."""
+    from consensusml_b200.models import deseq as DQ
+    rng = np.random.default_rng(31)
+    G, S = 180, 45
+    mu = np.exp(rng.normal(4, 1.5, G))
+    disp = 0.05 + 2.0 / mu
+    sf0 = np.exp(rng.normal(0, 0.3, S))
+    c = torch.from_numpy(rng.negative_binomial(1 / disp[:, None], 1 / (1 + disp[:, None] * mu[:, None] * sf0[None, :])).astype(np.float64))
+    c[3] = 0
+    groups = torch.from_numpy(np.arange(S) % 3)
+    ref = DQ.estimate_dispersions(c, groups=groups)                 # CPU tensors outside emulation: the torch path
+    rr = DQ.rlog(c, ref)
+    fr = DQ.rlog(c[:, :6], frozen=rr)
+    with be.ctx(seed=5):
+        got = DQ.estimate_dispersions(be.dev(c), groups=be.dev(groups))
+        gr = DQ.rlog(be.dev(c), got)
+        gf = DQ.rlog(be.dev(c[:, :6]), frozen=gr)
+    ok = torch.isfinite(ref.disp_gene)
+    assert torch.equal(torch.isfinite(_h(got.disp_gene)), ok)
+    di = (_h(got.iters) - ref.iters).abs()
+    assert int(di.max()) <= 2 and float((di == 0).float().mean()) > 0.9
+    rel = (_h(got.disp_gene)[ok] - ref.disp_gene[ok]).abs() / ref.disp_gene[ok]
+    assert float(rel.max()) < 5e-3 and float(rel.median()) < 1e-6
+    assert got.fit_type == ref.fit_type and np.allclose(got.coefs, ref.coefs, rtol=1e-3)
+    assert (_h(gr.values) - rr.values).abs().max() < 2e-3 and (_h(gf.values) - fr.values).abs().max() < 2e-3
+    assert abs(gr.beta_prior_var - rr.beta_prior_var) < 1e-3 * rr.beta_prior_var
+
+
+def case_voom_wls_wide_design_on_the_lane_distributed_inverse(be):
+    from consensusml_b200.stats import de as DE
+    c, g = nb_counts(300, 36, seed=26, n_de=40)
+    rng = np.random.default_rng(6)
+    k = 6
+    X = np.column_stack([np.ones(36), np.asarray(g, dtype=np.float64)] + [rng.normal(size=36) for _ in range(k - 2)])
+    cvec = np.zeros(k)
+    cvec[1] = 1.0
+    ref = DE.voom_de(torch.from_numpy(c), g, design=X, contrast=cvec)
+    with be.ctx(seed=2):
+        res = DE.voom_de(be.dev(torch.from_numpy(c)), g, design=X, contrast=cvec)
+    assert np.array_equal(np.asarray(_h(torch.as_tensor(res.keep))), np.asarray(ref.keep))
+    assert np.abs(np.asarray(res.logFC) - np.asarray(ref.logFC)).max() < 2e-3
+    t_a, t_b = np.asarray(res.t), np.asarray(ref.t)
+    assert (np.abs(t_a - t_b) / np.maximum(1.0, np.abs(t_b))).max() < 1e-2
+
+
+def case_batched_sharded_lasso_iteration_on_the_tensor_core_kernels(be):
+    """BatchedLassoLarge on one rank: tcgen05 eta product, residual split, fused GEMM -> reduce-scatter, proximal step + all-gather."""
+    from consensusml_b200.models import lasso_large as LL
+    g = torch.Generator().manual_seed(4)
+    n, p, B = 140, 200, 10
+    x = torch.randn(n, p, generator=g).bfloat16().float()
+    bt = torch.zeros(p)
+    bt[:6] = torch.randn(6, generator=g) * 1.5
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ bt)).float()
+    lmax = LL.lambda_max(x, y, n)
+    lams = np.geomspace(lmax * 0.9, lmax * 0.1, B)
+    W = torch.poisson(torch.ones(B, n), generator=g)
+    ref = LL.fit_batched(x, y, lams, weights=W, backend="unfused", max_iter=30, tol=0.0)
+    with be.ctx(seed=3):
+        got = LL.BatchedLassoLarge(be.dev(x), be.dev(y), lams, weights=be.dev(W), step=ref.step).run(30, 0.0, 10)
+    assert (_h(got.beta) - ref.beta).abs().max() < be.tol(2e-4, 5e-4)
+    assert (got.objective - ref.objective).abs().max() < 1e-4
