@@ -405,6 +405,7 @@ def classify(counts_train: torch.Tensor, y_train: torch.Tensor, method: str = "P
         mdl.fit(counts_train, y_train, n_classes)
     elif method == "pam":
         mdl.fit(transformed, y_train, n_classes)
+        mdl.train_fit_, mdl.pre_ = train_fit, pre                 # new samples go through the training set's transform
     else:
         e, w = _voom_transform(counts_train, y_train, n_classes)
         mdl.fit(e, y_train, n_classes, weights=w)
