@@ -136,8 +136,8 @@ def wilms_glmboost(df: pd.DataFrame, *, target: str = "Event.Free.Survival.Time.
     at ``cutoff`` days (:78-108).  Writes ``feature_list.csv`` (gene, coeff of the selected base learners) and the scatter data."""
     genes = list(gene_cols) if gene_cols is not None else list(df.columns[first_gene_col:])
     dev = torch.device(device) if device is not None else torch.device("cpu")
-    y = torch.as_tensor(df[target].to_numpy(dtype=np.float64), device=dev)
-    x = torch.as_tensor(df[genes].to_numpy(dtype=np.float64), device=dev)
+    y = torch.as_tensor(np.array(df[target].to_numpy(dtype=np.float64)), device=dev)
+    x = torch.as_tensor(np.array(df[genes].to_numpy(dtype=np.float64)), device=dev)
     early = y <= split_days
     keep = GB.mean_difference_filter(x, early, threshold)
     xs = x[:, keep]

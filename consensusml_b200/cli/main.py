@@ -11,6 +11,9 @@ The reference has no CLI - its entry points are "open the notebook and run the c
   lasso       the reference's headline model only (runLasso + gene CSV)
   de          limma-voom DE on a counts CSV: writes the DEG table in the reference's format
   normalize   TMM log2-CPM of a counts CSV
+  mlseq       the MLSeq / DESeq2 classifier zoo on raw counts (VikasP/AML.R): --counts, --degs, --clinical -> DEG_*.csv + test statistics
+  glmboost    glmboost on event-free survival (Ryan/Feature_selection_GLMTrain_WT_TARGET.R): --table -> feature_list.csv
+  kmsvm       k-means + GLM / SVM weight tails / QDA (BuieRProj/KM_WHATEVER.Rmd): --features and/or --expr -> output/High*.csv, low*.csv
   build       compile the native libraries
   config      print the resolved configuration
 """
@@ -24,11 +27,18 @@ import sys
 
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="consensusml_b200", description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
-    ap.add_argument("command", choices=["run", "multiclass", "acquire", "concat", "lasso", "de", "normalize", "build", "config"])
+    ap.add_argument("command", choices=["run", "multiclass", "acquire", "concat", "lasso", "de", "normalize", "mlseq", "glmboost", "kmsvm", "build", "config"])
     ap.add_argument("--config", default=None)
     ap.add_argument("--counts", default=None, help="genes x samples counts CSV")
     ap.add_argument("--groups", default=None, help="CSV with columns sample,group (1 = non-reference level)")
     ap.add_argument("--files", default=None, help="concat: glob pattern of the per-sample count files (sample id = file name up to the first dot)")
+    ap.add_argument("--degs", default=None, help="mlseq: DEG table CSV (first column = gene ids)")
+    ap.add_argument("--clinical-csv", default=None, help="mlseq: clinical table with TARGET.USI and Risk.group columns")
+    ap.add_argument("--table", default=None, help="glmboost: samples x (clinical + genes) CSV with the survival column")
+    ap.add_argument("--first-gene-col", type=int, default=41, help="glmboost: 0-based position of the first gene column (the script's column 42)")
+    ap.add_argument("--honest", action="store_true", help="glmboost: predict the rows that were NOT used for fitting (the script predicts its training rows)")
+    ap.add_argument("--features", default=None, help="kmsvm: patients x binary features CSV with a 'risk' column (0 / 1)")
+    ap.add_argument("--expr", default=None, help="kmsvm: samples x genes CSV with 'risk' (0 / 1) and 'train' (1 = fit on it) columns")
     ap.add_argument("--endpoint", default=None, help="acquire: GDC API base URL (default https://api.gdc.cancer.gov)")
     ap.add_argument("--clinical", action="store_true", help="acquire: also fetch the per-case clinical tables and the clinical supplements")
     ap.add_argument("--train-frac", type=float, default=2.0 / 3.0, help="run/multiclass on counts: stratified training fraction")
@@ -125,6 +135,35 @@ def main(argv=None) -> int:
         consensus.write_lasso_gene_csv(res.nonzero_coef, path)
         print(json.dumps({"lambda_min": res.cv.lambda_min, "test_error": res.test_error, "auc": res.test_auc,
                           "confusion": res.confusion.tolist(), "genes": len(res.nonzero_coef), "csv": path}))
+        return 0
+    if args.command in ("mlseq", "glmboost", "kmsvm"):
+        from ..api import side_analyses as SA
+        if args.command == "mlseq":
+            if not (args.counts and args.degs and args.clinical_csv):
+                ap.error("'mlseq' needs --counts, --degs and --clinical-csv")
+            counts_df = pd.read_csv(args.counts, index_col=0)
+            prep = SA.mlseq_prepare(counts_df, pd.read_csv(args.degs).iloc[:, 0].astype(str).tolist(), pd.read_csv(args.clinical_csv))
+            out = SA.mlseq_zoo(prep, cfg.io.out_dir, device=dev)
+            print(json.dumps({m: {"best_param": r["best_param"], "cv_accuracy": r["cv_accuracy"], **r["test"], "n_selected": len(r["selected_genes"])}
+                              for m, r in out["methods"].items()}, indent=1, default=float))
+        elif args.command == "glmboost":
+            if not args.table:
+                ap.error("'glmboost' needs --table")
+            out = SA.wilms_glmboost(pd.read_csv(args.table), first_gene_col=args.first_gene_col, honest_test=args.honest, out_dir=cfg.io.out_dir, device=dev)
+            print(json.dumps({k: v for k, v in out.items() if k != "features"} | {"n_features": len(out["features"])}, default=float))
+        else:
+            if not (args.features or args.expr):
+                ap.error("'kmsvm' needs --features and/or --expr")
+            kw = {}
+            if args.features:
+                f = pd.read_csv(args.features)
+                kw.update(binary_features=f.drop(columns=["risk"]), risk=f["risk"].to_numpy())
+            if args.expr:
+                e = pd.read_csv(args.expr)
+                kw.update(expression=e.drop(columns=["risk", "train"]), expr_risk=e["risk"].to_numpy(), train_flag=e["train"].to_numpy())
+            out = SA.km_whatever(out_dir=cfg.io.out_dir, device=dev, **kw)
+            print(json.dumps({"kmeans": out["kmeans"].to_dict("records") if "kmeans" in out else None, "svm": out.get("svm"), "qda": out.get("qda")},
+                             default=float))
         return 0
     if args.counts is None:
         ap.error(f"'{args.command}' needs --counts")

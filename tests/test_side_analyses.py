@@ -99,3 +99,43 @@ def test_km_whatever_three_aims(tmp_path):
     assert len(open(tmp_path / "output" / "low1000.csv").read().splitlines()) - 1 == out["svm"]["tail_sizes"][0.001][1]
     assert sorted(os.listdir(tmp_path / "output")) == sorted([f"{a}{b}.csv" for a in ("High", "low") for b in ("4", "10", "20", "100", "1000")])
     assert out["qda"]["test_accuracy"] > 0.8
+
+
+def test_cli_entry_points(tmp_path, capsys):
+    import json
+    from consensusml_b200.cli.main import main
+    rng = np.random.default_rng(4)
+    n, p = 80, 60
+    x = rng.normal(size=(n, p))
+    df = pd.DataFrame({f"clin{i}": rng.integers(0, 3, n) for i in range(40)})
+    df["Event.Free.Survival.Time.in.Days"] = np.clip(500 + 300 * x[:, 0] + rng.normal(scale=50, size=n), 5, None)
+    df = pd.concat([df, pd.DataFrame(x, columns=[f"g{i}" for i in range(p)])], axis=1)
+    df.to_csv(tmp_path / "wt.csv", index=False)
+    assert main(["glmboost", "--table", str(tmp_path / "wt.csv"), f"io.out_dir={tmp_path}", "device=cpu"]) == 0
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert out["n_train"] == 40 and (tmp_path / "feature_list.csv").exists()
+    y = rng.integers(0, 2, 90)
+    e = pd.DataFrame(rng.normal(size=(90, 50)) + 1.2 * y[:, None] * (np.arange(50) < 5), columns=[f"g{i}" for i in range(50)])
+    e["risk"], e["train"] = y, (np.arange(90) % 2)
+    e.to_csv(tmp_path / "expr.csv", index=False)
+    assert main(["kmsvm", "--expr", str(tmp_path / "expr.csv"), f"io.out_dir={tmp_path}", "device=cpu"]) == 0
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert out["svm"]["auc"] > 0.8 and (tmp_path / "output" / "High4.csv").exists()
+    counts, deg_ids, clinical, _, _ = _aml_counts(n_pat=40, n_deg=50, seed=6)
+    counts.to_csv(tmp_path / "counts.csv")
+    pd.DataFrame({"X": deg_ids}).to_csv(tmp_path / "degs.csv", index=False)
+    clinical.to_csv(tmp_path / "clin.csv", index=False)
+    SA.MLSEQ_METHODS_BACKUP = dict(SA.MLSEQ_METHODS)
+    try:
+        SA.MLSEQ_METHODS.clear()
+        SA.MLSEQ_METHODS.update({"PLDA": None, "voomNSC": None})       # two quick members of the zoo
+        import consensusml_b200.models.discriminant as DC
+        orig = DC.classify
+        DC.classify = lambda *a, **k: orig(*a, **{**k, "repeats": 1, "folds": 3})
+        assert main(["mlseq", "--counts", str(tmp_path / "counts.csv"), "--degs", str(tmp_path / "degs.csv"), "--clinical-csv", str(tmp_path / "clin.csv"),
+                     f"io.out_dir={tmp_path}", "device=cpu"]) == 0
+    finally:
+        DC.classify = orig
+        SA.MLSEQ_METHODS.clear()
+        SA.MLSEQ_METHODS.update(SA.MLSEQ_METHODS_BACKUP)
+    assert (tmp_path / "DEG_plda.csv").exists() and (tmp_path / "DEG_voomnsc.csv").exists()
