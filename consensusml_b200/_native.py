@@ -61,6 +61,11 @@ class emulation:
     uninitialised read.  ``sms`` sets the multiprocessor count the launchers see (grid sizing)."""
 
     def __init__(self, seed: Optional[int] = None, sms: Optional[int] = None):
+        # CML_EMU_SEED_SHIFT moves every seed a test passes: a sweep over it re-runs the suite under other thread orders,
+        # other shared-memory garbage and other completion orders of the asynchronous units (tools/emu_seed_sweep.sh)
+        shift = int(os.environ.get("CML_EMU_SEED_SHIFT", "0"))
+        if shift:
+            seed = (seed or 0) + shift
         self.env = {"CML_EMU_SEED": seed, "CML_EMU_SMS": sms}
         self.saved = {}
 
