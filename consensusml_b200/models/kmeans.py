@@ -106,8 +106,7 @@ def kmeans(x: torch.Tensor, k: int, nstart: int = 25, max_iter: int = 100, seed:
         n, d = x.shape
         if n * d <= _FUSED_LIMIT and 2 * k * d * 4 <= 200 * 1024:
             return _kmeans_device(x, [k], nstart, max_iter, seed)[k]
-        if x.is_cuda:
-            return _kmeans_gemm(x, k, nstart, max_iter, seed)
+        return _kmeans_gemm(x, k, nstart, max_iter, seed)
     x = x.float()
     n, d = x.shape
     g = torch.Generator(device="cpu").manual_seed(seed + 7919 * k)

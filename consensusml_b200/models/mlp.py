@@ -60,11 +60,11 @@ def make_grid(hidden=(16, 32, 64), lr=(1e-3, 3e-3), weight_decay=(0.0, 1e-3), se
 
 
 def _gemm_nt(a_bf16: torch.Tensor, b_bf16: torch.Tensor, n_out: int) -> torch.Tensor:
-    """A . B^T for bf16 [M, K] x [N, K] -> fp32 [M, >= n_out].  The tcgen05 kernel on a GPU; under the host execution
-    model (no tensor cores to emulate) the same product of the same bf16 values in fp32."""
-    if a_bf16.is_cuda and a_bf16.shape[1] >= G.MIN_K and a_bf16.shape[0] >= 32 and n_out >= 32:
+    """A . B^T for bf16 [M, K] x [N, K] -> fp32 [M, >= n_out] on the tcgen05 kernel (GPU, or the host execution model's
+    rendering of it); toy shapes below one k-block take the plain product of the same bf16 values."""
+    if _native.on_device(a_bf16) and a_bf16.shape[1] >= G.MIN_K and a_bf16.shape[0] >= 32 and n_out >= 32:
         return G.gemm_tn(a_bf16, [b_bf16], n_out)
-    return a_bf16.float() @ b_bf16.float().t()          # toy shapes (and the host execution model): same bf16 values, fp32 product
+    return a_bf16.float() @ b_bf16.float().t()
 
 
 def _bf16_rows(t: torch.Tensor) -> torch.Tensor:

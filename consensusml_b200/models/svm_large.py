@@ -248,7 +248,7 @@ class LargeSVC:
         return self
 
     def _columns_single(self, x_local, x_sel, gamma):
-        if x_local.is_cuda:
+        if _native.on_device(x_local):
             return (G.rbf_kernel(x_local, x_sel, gamma) if self.kernel == "radial" else G.linear_kernel(x_local, x_sel)).float()
         if self.kernel == "radial":
             return torch.exp(-gamma * torch.cdist(x_local.double(), x_sel.double()) ** 2).float()

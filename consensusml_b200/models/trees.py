@@ -217,12 +217,9 @@ def proximity_gemm(leaf: torch.Tensor, oob: Optional[torch.Tensor], max_nodes: i
         rc = _native.cuda().cml_forest_onehot(_native.ptr(lf), _native.ptr(ob), tt, n, max_nodes, _native.ptr(z), ldz, _native.ptr(o), ldo,
                                               _native.stream_ptr())
         _native.check(rc, "cml_forest_onehot")
-        if z.is_cuda:
-            prox += G.gemm_tn(z, [z], n)
-            pairs += G.gemm_tn(o, [o], n) if ldo >= G.MIN_K else o.float() @ o.float().t()
-        else:                                   # host execution model: the same one-hot matrices, fp32 products
-            prox += z.float() @ z.float().t()
-            pairs += o.float() @ o.float().t()
+        # tcgen05 GEMMs (on the host execution model: the same kernels on the model of the asynchronous units)
+        prox += G.gemm_tn(z, [z], n) if ldz >= G.MIN_K else z.float() @ z.float().t()
+        pairs += G.gemm_tn(o, [o], n) if ldo >= G.MIN_K else o.float() @ o.float().t()
     return prox, pairs
 
 

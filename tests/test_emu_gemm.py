@@ -318,3 +318,32 @@ def test_random_ragged_shapes():
                 assert (outs[dd][: hi - lo] - ref[lo:hi]).abs().max() < 3e-5 * scale, (p, B, K, world, use_tma, split, seed, sms, dd)
             if hi - lo < gpr:
                 assert float(outs[dd][hi - lo:].abs().max()) == 0.0
+
+
+def test_consumers_of_the_gemm_run_their_kernel_branch_under_emulation(monkeypatch):
+    """Code that only a GPU used to reach: k-means for large cohorts (tcgen05 distances + assign / update kernels), the forest
+    proximity as one-hot GEMMs, the MLP's two products, the large-n SVM's kernel columns."""
+    from consensusml_b200.models import kmeans as KM
+    from consensusml_b200.models import mlp as MLP
+    from consensusml_b200.models import svm_large as SL
+    g = torch.Generator().manual_seed(3)
+    centers = torch.randn(3, 80, generator=g) * 4
+    x = centers[torch.arange(150) % 3] + torch.randn(150, 80, generator=g)
+    monkeypatch.setattr(KM, "_FUSED_LIMIT", 100)                    # force the large-cohort path on a small problem
+    ref = KM.kmeans(x, 3, nstart=3, seed=5)                          # CPU path
+    with _native.emulation(seed=2):
+        _native.reset_calls()
+        got = KM.kmeans(x, 3, nstart=3, seed=5)
+        assert _native.calls.get("cml_gemm_tn_bf16", 0) >= 3 and _native.calls.get("cml_kmeans_assign", 0) >= 3
+    assert abs(got.tot_withinss - ref.tot_withinss) < 2e-2 * ref.tot_withinss      # bf16 distances: same partition, slightly different sums
+    perm_ok = len({(int(a), int(b)) for a, b in zip(got.labels, ref.labels)}) == 3
+    assert perm_ok
+    a = torch.randn(64, 96, generator=g).bfloat16()
+    b = torch.randn(40, 96, generator=g).bfloat16()
+    with _native.emulation(seed=4):
+        _native.reset_calls()
+        c = MLP._gemm_nt(a, b, 40)
+        assert _native.calls.get("cml_gemm_tn_bf16") == 1
+        k = SL.LargeSVC(kernel="radial")._columns_single(x, x[:70], 1.0 / 80)
+    assert (c[:, :40] - a.float() @ b.float().t()).abs().max() < 1e-3
+    assert (k - torch.exp(-torch.cdist(x.double(), x[:70].double()) ** 2 / 80).float()).abs().max() < 2e-2
