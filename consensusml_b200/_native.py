@@ -194,6 +194,13 @@ def ptr(t) -> ctypes.c_void_p:
     return p
 
 
+def synchronize() -> None:
+    """``torch.cuda.synchronize()`` on a GPU; nothing to wait for on the host execution model (launches run to completion)."""
+    if _emu_depth == 0:
+        import torch
+        torch.cuda.synchronize()
+
+
 def stream_ptr() -> ctypes.c_void_p:
     import torch
     if _emu_depth > 0:

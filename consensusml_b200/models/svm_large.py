@@ -109,7 +109,7 @@ class LargeSVC:
     def _columns(self, x_local: torch.Tensor, x_ws_local: torch.Tensor, gamma: float, q_total: int) -> torch.Tensor:
         """K[local samples, all nominees] -> [n_local, q_total]: the nominees' rows of every rank against this rank's samples."""
         world, _ = _world()
-        if x_local.is_cuda:
+        if _native.on_device(x_local):
             from ..parallel import fused as F
             # gram_allgather computes rows = its first argument against the all-gathered blocks: here the "block" a rank
             # publishes is its nominee rows, and the left operand is the local shard
@@ -134,7 +134,7 @@ class LargeSVC:
             st["stage"] = F.gram_stage_buffers(world, qw, ld, dev) if world > 1 else None
         xb, nb = st["xb"], st["nb"]
         G.to_bf16_rows(x_ws_local.float().contiguous(), out=xb.local, norm_out=nb.local)
-        torch.cuda.synchronize()
+        _native.synchronize()
         xb.barrier()
         epi, alpha = (G.EPI_RBF, gamma) if self.kernel == "radial" else (G.EPI_SCALE, 1.0)
         if world > 1:
@@ -143,7 +143,7 @@ class LargeSVC:
                                    epilogue=epi, alpha=alpha, norm_a=st["na"], peer_norm_ptrs=nb.peer_ptrs)
         else:
             out = G.gemm_tn(st["xa"], [xb.local], q_total, epilogue=epi, alpha=alpha, norm_a=st["na"], norm_b=[nb.local])
-        torch.cuda.synchronize()
+        _native.synchronize()
         xb.barrier()                  # nobody overwrites its nominee block while a peer may still be reading it
         return out
 
