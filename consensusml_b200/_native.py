@@ -71,6 +71,9 @@ class emulation:
 
     def __enter__(self):
         global _emu_depth
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            # several emulated ranks as processes (torchrun): a kernel that waits for a peer's signal needs a real clock
+            os.environ.setdefault("CML_EMU_REALTIME", "1")
         for k, v in self.env.items():
             if v is not None:
                 self.saved[k] = os.environ.get(k)
@@ -192,6 +195,14 @@ def ptr(t) -> ctypes.c_void_p:
     p = _KeepAlivePtr(t.data_ptr())
     p._keep = t
     return p
+
+
+def sm_count() -> int:
+    """Multiprocessors the launchers size their grids for (the emulated count inside ``emulation()``)."""
+    if _emu_depth > 0:
+        return max(1, int(os.environ.get("CML_EMU_SMS", "4")))
+    import torch
+    return torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
 
 
 def synchronize() -> None:

@@ -72,7 +72,7 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
         all_reduce_(t)
         n_total = int(t.item())
     if backend == "auto":
-        backend = "fused" if x_local.is_cuda else "unfused"
+        backend = "fused" if _native.on_device(x_local) else "unfused"
     if step is None:
         step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12)
     if backend == "unfused":
@@ -96,7 +96,7 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
     loss = torch.zeros(1, dtype=torch.float64, device=dev)
     done = torch.zeros(4, dtype=torch.int32, device=dev)
     dmax = torch.zeros(1, dtype=torch.float32, device=dev)
-    torch.cuda.synchronize()
+    _native.synchronize()
     beta.barrier()
     bptr, vptr, sptr = F._ptr_array(beta.peer_ptrs), F._ptr_array(v.peer_ptrs), F._ptr_array(rs.grad.signal_ptrs)
     my_pad = ctypes.c_void_p(rs.grad.signal_ptrs[rank])
@@ -141,10 +141,10 @@ def fit(x_local: torch.Tensor, y_local: torch.Tensor, lam: float, *, n_total: Op
             if float(d.item()) < tol:
                 break
     _native.check(lb.cml_wait_signals(my_pad, F.SIG_BETA, world, it, st()), "cml_wait_signals")
-    torch.cuda.synchronize()
+    _native.synchronize()
     beta.barrier()
     out = beta.local[:p].clone()
-    torch.cuda.synchronize()
+    _native.synchronize()
     beta.barrier()
     return LargeFit(out, it, obj, step, history)
 
@@ -392,8 +392,7 @@ class BatchedLassoLarge:
                 if float(d.max()) < tol:
                     break
         self.wait_all_gather()
-        if self.dev.type == "cuda":
-            torch.cuda.synchronize()
+        _native.synchronize()
         self.vhl.barrier()
         return BatchedFit(self.coefficients(), self.it, obj, d, self.step, history)
 

@@ -103,6 +103,7 @@ def gemm_tn_staged(a_bf16: torch.Tensor, peer_ptrs: Sequence[int], n_total: int,
     of the same kernel stage the blocks into ``stage`` while the GEMM CTAs consume the tiles that have arrived."""
     M, K = a_bf16.shape
     n_src = len(peer_ptrs)
+    n_copiers = max(1, min(n_copiers, _native.sm_count() // 2 - 1))      # the copiers must leave most of the machine to the GEMM
     ldc = (n_total + 3) // 4 * 4
     c = out if out is not None else torch.empty(M, ldc, dtype=torch.float32, device=a_bf16.device)
     arr_b = (ctypes.c_void_p * n_src)(*peer_ptrs)

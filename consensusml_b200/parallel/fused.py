@@ -169,7 +169,7 @@ def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Opti
         xb.local[n_local:].zero_()
         nrm.local[n_local:].zero_()
     G.to_bf16_rows(x_local.float().contiguous(), shift=shift, out=xb.local[:n_local], norm_out=nrm.local[:n_local])
-    torch.cuda.synchronize()
+    _native.synchronize()
     xb.barrier()
     gamma = 1.0 / p if gamma is None else gamma
     epi, alpha = (G.EPI_RBF, gamma) if kernel == "radial" else (G.EPI_SCALE, 1.0)
@@ -184,7 +184,7 @@ def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Opti
     else:
         out = G.gemm_tn(xb.local[:n_local], None, n_total, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
                         b_ptrs=xb.peer_ptrs, norm_b_ptrs=nrm.peer_ptrs, rows_per_src=rows, ldb=ld)
-    torch.cuda.synchronize()
+    _native.synchronize()
     xb.barrier()                     # nobody frees / rewrites its block while a peer may still be reading it
     if cache is not None:
         cache["xb"], cache["nrm"] = xb, nrm
@@ -268,10 +268,10 @@ class HistAllReduce:
 
     def clear(self, n_nodes: int) -> None:
         """Zero the reduced histogram for the next level - after every rank has finished reading it."""
-        torch.cuda.synchronize()
+        _native.synchronize()
         self.hist.barrier()
         self.hist.local[: n_nodes * self.p * self.nbins * 2].zero_()
-        torch.cuda.synchronize()
+        _native.synchronize()
         self.hist.barrier()
 
 

@@ -33,17 +33,65 @@ class SymmBuffer:
     def peer_view(self, r: int) -> torch.Tensor:
         """Tensor view of rank r's copy (for tests / un-fused fallbacks)."""
         if self.handle is None:
-            return self.local
+            views = getattr(self, "_peer_views", None)
+            return views[r] if views is not None else self.local
         return self.handle.get_buffer(r, tuple(self.local.shape), self.local.dtype)
 
 
 _SIGNAL_PAD_WORDS = 256
 
 
+_SHM_SEQ = 0
+
+
+def _alloc_host_shared(shape, dtype, world: int, rank: int) -> SymmBuffer:
+    """Several PROCESSES on the host execution model (torchrun + gloo + ``_native.emulation()``): every rank backs its buffer
+    and its signal pad with a POSIX shared-memory file and maps all of its peers' files, so the "peer pointers" the kernels get
+    are real addresses of the other processes' buffers - the in-kernel stores, reductions and signals of the fused paths then
+    cross process boundaries the way they cross NVLink.  (tests/dist_fused_check.py --emu.)"""
+    import mmap
+    import os
+    global _SHM_SEQ
+    _SHM_SEQ += 1
+    token = [f"{os.getpid()}_{_SHM_SEQ}"]
+    dist.broadcast_object_list(token, src=0)
+    numel = 1
+    for d in (shape if isinstance(shape, (tuple, list)) else (shape,)):
+        numel *= int(d)
+    esize = torch.empty(0, dtype=dtype).element_size()
+    sizes = {"buf": max(4096, (numel * esize + 4095) // 4096 * 4096), "pad": 4096}
+    path = lambda kind, r: f"/dev/shm/cml_symm_{token[0]}_{kind}_{r}"
+    for kind, size in sizes.items():
+        with open(path(kind, rank), "wb") as fh:
+            fh.truncate(size)                                   # zero pages
+    dist.barrier()
+    maps, tens = {}, {}
+    for kind, size in sizes.items():
+        for r in range(world):
+            fd = os.open(path(kind, r), os.O_RDWR)
+            mm = mmap.mmap(fd, size)
+            os.close(fd)
+            maps[(kind, r)] = mm
+            tens[(kind, r)] = torch.frombuffer(mm, dtype=torch.uint8, count=size)
+    dist.barrier()
+    for kind in sizes:
+        os.unlink(path(kind, rank))                             # the mappings keep the memory alive
+    view = lambda r: tens[("buf", r)][: numel * esize].view(dtype).view(shape)
+    buf = SymmBuffer(view(rank), [tens[("buf", r)].data_ptr() for r in range(world)], [tens[("pad", r)].data_ptr() for r in range(world)], 0,
+                     rank, world, None)
+    buf._keep = (maps, tens)
+    buf._peer_views = [view(r) for r in range(world)]
+    buf._pad = tens[("pad", rank)].view(torch.int32)
+    return buf
+
+
 def alloc(shape, dtype, device) -> SymmBuffer:
     """Collective: every rank calls with the same shape / dtype."""
+    from .. import _native
     world = dist.get_world_size() if dist.is_initialized() else 1
     rank = dist.get_rank() if dist.is_initialized() else 0
+    if world > 1 and torch.device(device).type != "cuda" and _native.emulating():
+        return _alloc_host_shared(shape, dtype, world, rank)
     if world == 1 or torch.device(device).type != "cuda":
         t = torch.zeros(shape, dtype=dtype, device=device)
         pad = torch.zeros(_SIGNAL_PAD_WORDS, dtype=torch.int32, device=device)

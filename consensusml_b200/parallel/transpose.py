@@ -56,7 +56,7 @@ class ShardTranspose:
         self.epoch = 0
 
     def __call__(self, x_local: torch.Tensor) -> torch.Tensor:
-        assert x_local.is_cuda and x_local.dtype == self.dtype and x_local.dim() == 2 and x_local.stride(1) == 1
+        assert _native.on_device(x_local) and x_local.dtype == self.dtype and x_local.dim() == 2 and x_local.stride(1) == 1
         assert x_local.shape == (self.row1 - self.row0, self.cols), (tuple(x_local.shape), self.row1 - self.row0, self.cols)
         self.epoch += 1
         buf = self.out[self.epoch & 1]
@@ -92,7 +92,7 @@ def shard_transpose_unfused(x_local: torch.Tensor, rows_total: int) -> torch.Ten
 
 def to_gene_shards(x_local: torch.Tensor, rows_total: int, plan: Optional[ShardTranspose] = None) -> torch.Tensor:
     """samples x genes (row block) -> genes x samples (gene block); fused on CUDA, all_to_all otherwise."""
-    if x_local.is_cuda and _native.cuda_available():
+    if (x_local.is_cuda and _native.cuda_available()) or _native.emulating():
         plan = plan or ShardTranspose(rows_total, x_local.shape[1], x_local.device, x_local.dtype)
         return plan(x_local)
     return shard_transpose_unfused(x_local, rows_total)

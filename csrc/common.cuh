@@ -111,17 +111,28 @@ __host__ __device__ __forceinline__ int ceil_div(int a, int b) { return (a + b -
 __host__ __device__ __forceinline__ long long ceil_div(long long a, long long b) { return (a + b - 1) / b; }
 
 // ---- cache-hint and system-scope PTX shared by several kernels -------------------------------------------------------
-// Under the host execution model (CML_EMU, csrc/emu/cuda_emu.h) these are plain accesses: one OS thread runs every
-// emulated thread, so there is nothing to order; a multicast (multimem) address does not exist there and traps.
+// Under the host execution model (CML_EMU, csrc/emu/cuda_emu.h) the local ones are plain accesses (one OS thread runs every
+// emulated thread of a process); a multicast (multimem) address does not exist there and traps.
 #ifdef CML_EMU
 inline int4 ld_stream(const int4* p) { return *p; }
 inline float ld_stream_f32(const float* p) { return *p; }
 inline void prefetch_l1(const void*) {}
-inline void red_add_v4_sys(float* addr, float4 v) { addr[0] += v.x; addr[1] += v.y; addr[2] += v.z; addr[3] += v.w; }
-inline void red_add_sys(float* addr, float v) { *addr += v; }
+// The operations that reach PEER memory are real atomics / ordered accesses: with several emulated ranks as separate processes
+// (shared-memory "symmetric" buffers, parallel/symm.py) the peers do run concurrently.
+inline void red_add_sys(float* addr, float v) {
+  unsigned* w = reinterpret_cast<unsigned*>(addr);
+  unsigned old = __atomic_load_n(w, __ATOMIC_RELAXED), neu;
+  do {
+    float f;
+    std::memcpy(&f, &old, 4);
+    f += v;
+    std::memcpy(&neu, &f, 4);
+  } while (!__atomic_compare_exchange_n(w, &old, neu, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED));
+}
+inline void red_add_v4_sys(float* addr, float4 v) { red_add_sys(addr, v.x); red_add_sys(addr + 1, v.y); red_add_sys(addr + 2, v.z); red_add_sys(addr + 3, v.w); }
 inline void multimem_red_add_v4(float*, float4) { ::cml_emu::trap("multimem.red is not available under the host execution model"); }
-inline void st_release_sys(unsigned* addr, unsigned v) { *addr = v; }
-inline unsigned ld_acquire_sys(const unsigned* addr) { return *addr; }
+inline void st_release_sys(unsigned* addr, unsigned v) { __atomic_store_n(addr, v, __ATOMIC_RELEASE); }
+inline unsigned ld_acquire_sys(const unsigned* addr) { return __atomic_load_n(addr, __ATOMIC_ACQUIRE); }
 #else
 // 128-bit streaming loads that do not pollute L1 (single-use data).
 __device__ __forceinline__ int4 ld_stream(const int4* p) {

@@ -210,11 +210,16 @@ void box_copy(const TensorMapEmu& t, int c0, int c1, uint8_t* smem_win, uint32_t
           std::memcpy(g, staging + lin, t.esize);
         } else {
           if (t.dtype != CU_TENSOR_MAP_DATA_TYPE_FLOAT32) trap("tensor reduce-add is modelled for fp32 only");
-          float a, b;
-          std::memcpy(&a, g, 4);
+          float b;                                           // the destination may be another process's buffer: atomic add
           std::memcpy(&b, staging + lin, 4);
-          a += b;
-          std::memcpy(g, &a, 4);
+          unsigned* w = reinterpret_cast<unsigned*>(g);
+          unsigned old = __atomic_load_n(w, __ATOMIC_RELAXED), neu;
+          do {
+            float a;
+            std::memcpy(&a, &old, 4);
+            a += b;
+            std::memcpy(&neu, &a, 4);
+          } while (!__atomic_compare_exchange_n(w, &old, neu, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED));
         }
       }
     }

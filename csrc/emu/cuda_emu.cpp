@@ -6,6 +6,7 @@
 #include "emu_internal.h"
 
 #include <sys/mman.h>
+#include <time.h>
 
 // Context switch: a dozen instructions of our own on x86-64 (swapcontext makes a signal-mask system call per switch,
 // which dominates kernels that shuffle a lot); ucontext elsewhere and in sanitizer builds (ASan tracks its switches).
@@ -237,7 +238,15 @@ bool async_step() {
 }  // namespace
 
 int lane_id() { return g_cur ? (g_cur->linear & 31) : 0; }
-long long tick() { return g_tick += 1000000; }          // every look at the clock is a millisecond: spin time-outs fire at once
+long long tick() {
+  // one process: nothing but this launch can change what a spin waits for, so every look at the clock is a millisecond and
+  // time-outs fire at once.  CML_EMU_REALTIME=1 (several emulated ranks as processes): cycles of a 2 GHz clock.
+  static const bool realtime = [] { const char* s = std::getenv("CML_EMU_REALTIME"); return s && s[0] == '1'; }();
+  if (!realtime) return g_tick += 1000000;
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (long long)ts.tv_sec * 2000000000LL + (long long)ts.tv_nsec * 2LL;
+}
 void* dyn_smem() { return g_blk->st.smem + g_blk->st.dyn_off; }
 int sm_count_emulated() {
   const char* s = std::getenv("CML_EMU_SMS");

@@ -1,5 +1,7 @@
 """Multi-rank checks of the fused compute+collective paths against their un-fused comparators.
-Run under torchrun (NCCL, one rank per GPU) or with --cpu (gloo, un-fused logic only).  Prints 'ALL OK' on rank 0."""
+Run under torchrun: NCCL, one rank per GPU (default); ``--cpu``: gloo, un-fused logic only; ``--emu``: gloo, one PROCESS per
+rank with the kernels on the host execution model and the symmetric buffers in shared memory - the fused paths, their signal
+protocol and the Python orchestration around them, really concurrent, without a GPU.  Prints 'ALL OK' on rank 0."""
 import os
 import sys
 
@@ -24,10 +26,20 @@ def synth(n, p, seed=0):
 
 def main():
     cpu = "--cpu" in sys.argv
+    emu = "--emu" in sys.argv
     import faulthandler
-    faulthandler.dump_traceback_later(90, exit=True)      # a hung collective must not hold the GPU box
+    faulthandler.dump_traceback_later(900 if emu else 90, exit=True)      # a hung collective must not hold the GPU box
+    from consensusml_b200 import _native
     from consensusml_b200.models import lasso_large as LL
-    n, p = (3000, 120) if cpu else (6000, 2500)
+    if emu:
+        os.environ["CML_EMU_REALTIME"] = "1"              # waits on other processes need a real clock
+        os.environ.setdefault("CML_WAIT_TIMEOUT_S", "120")
+        ctx = _native.emulation(seed=int(os.environ.get("RANK", "0")) + 1, sms=8)
+        ctx.__enter__()
+    sync = _native.synchronize
+    n, p = (3000, 120) if cpu else ((640, 200) if emu else (6000, 2500))
+    if emu:
+        n = n // int(os.environ.get("WORLD_SIZE", "1")) * int(os.environ.get("WORLD_SIZE", "1"))     # gloo's gather (the comparator) wants equal blocks
     x, y = synth(n, p)
     ref_single = None
     if cpu:      # single-process answer first, while no process group exists (its all-reduces are then no-ops)
@@ -37,7 +49,7 @@ def main():
         sx = x[:800, :16]
         sx = (sx - sx.mean(0)) / sx.std(0, unbiased=True)
         svm_single = LargeSVC(kernel="radial", q=64).fit(sx, y[:800])
-    rank, world, dev = D.init("gloo" if cpu else None)
+    rank, world, dev = D.init("gloo" if (cpu or emu) else None)
     lo, hi = shard_bounds(n, world, rank)
     xl, yl = x[lo:hi].to(dev), y[lo:hi].to(dev)
     ok = True
@@ -51,11 +63,11 @@ def main():
         plan = TR.ShardTranspose(n, p, dev)
         for rep in range(3):                                  # alternating output buffers, increasing epochs
             got_f = plan(xl * (rep + 1))
-            torch.cuda.synchronize()
+            sync()
             ok &= bool(torch.equal(got_f.cpu(), want * (rep + 1)))
         back = TR.ShardTranspose(p, n, dev)                   # and back: gene-sharded -> sample-sharded
         again = back(got_u.contiguous())
-        torch.cuda.synchronize()
+        sync()
         ok &= bool(torch.equal(again.cpu(), x[lo:hi]))
         print(f"[{rank}] shard_transpose fused == all_to_all: {ok}", flush=True)
     if cpu:
@@ -102,13 +114,13 @@ def main():
             for rep in range(2):                      # twice: the scratch cleans itself
                 rs.launch(xb, R)
                 rs.wait()
-                torch.cuda.synchronize()
+                sync()
                 got = rs.result().clone()
                 ref = F.xtr_reduce_scatter_unfused(xb[:, :p], R, p)
                 err = float((got - ref).abs().max() / ref.abs().max())
-                torch.cuda.synchronize(); rs.grad.barrier()
+                sync(); rs.grad.barrier()
                 rs.grad.local.zero_()
-                torch.cuda.synchronize(); rs.grad.barrier()
+                sync(); rs.grad.barrier()
                 print(f"[{rank}] xtr_rs nb={nb} rep={rep} rel err {err:.2e}", flush=True)
                 ok &= err < 1e-4
         # ---- path 3: all-gather -> tcgen05 Gram
@@ -136,9 +148,9 @@ def main():
         bins, node, gh = bins.to(dev), node_full[lo:hi].contiguous().to(dev), gh_full[lo:hi].contiguous().to(dev)
         H = F.HistAllReduce(pf, nbins, 8, dev)
         ref = F.hist_unfused(bins, nl, node, gh, n_nodes, pf, nbins)
-        for mc in (True, False):
+        for mc in ((False,) if emu else (True, False)):          # no multicast address on the host model
             got = H.build(bins, nl, node, gh, n_nodes, use_multicast=mc).clone()
-            torch.cuda.synchronize()
+            sync()
             err = float((got - ref).abs().max() / ref.abs().max())
             print(f"[{rank}] hist_allreduce multicast={mc} rel err {err:.2e}", flush=True)
             ok &= err < 1e-4
@@ -151,15 +163,15 @@ def main():
         f0, f1 = E.feat0, min(pf, E.feat0 + E.fpr)
         for rep in range(2):
             E.build(bins, nl, node, gh, slot_of, 2, gb_, hb_)
-            torch.cuda.synchronize()
+            sync()
             got = E.landing.local[: 2 * E.cells].view(2, E.fpr, nbins, 2).clone()
             if f1 > f0:
                 err = float((got[:, : f1 - f0] - ref[1:3, f0:f1]).abs().max() / ref.abs().max())
                 print(f"[{rank}] hist reduce-scatter landing rep={rep} features [{f0}, {f1}) rel err {err:.2e}", flush=True)
                 ok &= err < 1e-4
-            torch.cuda.synchronize(); E.landing.barrier()
+            sync(); E.landing.barrier()
             E.landing.local.zero_()
-            torch.cuda.synchronize(); E.landing.barrier()
+            sync(); E.landing.barrier()
         gain, feat, b = F.best_splits(ref)
         hh = ref.double()
         cg, ch = hh[..., 0].cumsum(-1), hh[..., 1].cumsum(-1)
@@ -179,12 +191,13 @@ def main():
         # ---- sharded GBM on the fused histogram path: identical trees on every rank, sensible accuracy
         from consensusml_b200.models.gbm_large import GBMLarge
         from consensusml_b200.ops.metrics import auc
-        gx, gy = synth(4000, 64, seed=3)
-        glo, ghi = shard_bounds(4000, world, rank)
+        gn_ = 600 if emu else 4000
+        gx, gy = synth(gn_, 64, seed=3)
+        glo, ghi = shard_bounds(gn_, world, rank)
         from consensusml_b200.models.gbm_large import quantile_bin
         gbins, gcuts = quantile_bin(gx[glo:ghi].to(dev), 64)
-        gb = GBMLarge(n_estimators=8, max_depth=3, nbins=64).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
-        gu = GBMLarge(n_estimators=8, max_depth=3, nbins=64, backend="unfused", sibling_subtraction=True).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
+        gb = GBMLarge(n_estimators=3 if emu else 8, max_depth=3, nbins=64).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
+        gu = GBMLarge(n_estimators=3 if emu else 8, max_depth=3, nbins=64, backend="unfused", sibling_subtraction=True).fit(None, gy[glo:ghi].to(dev), bins=gbins, cuts=gcuts)
         same_trees = all(torch.equal(s_.feat, t_.feat) and torch.equal(s_.thr[s_.feat >= 0], t_.thr[t_.feat >= 0]) for s_, t_ in zip(gb.trees, gu.trees))
         print(f"[{rank}] gbm_large kernel level loop (reduce-scatter landing, sibling subtraction) == torch + NCCL path: {same_trees}", flush=True)
         ok &= same_trees
@@ -198,20 +211,20 @@ def main():
         # ---- large-n SVM: working-set decomposition whose kernel columns come from the all-gather -> tcgen05 Gram kernel
         from consensusml_b200.models import svm as SV
         from consensusml_b200.models.svm_large import LargeSVC
-        sn = 4096 // world * world
-        sx = x[:sn, :512]
+        sn = (256 if emu else 4096) // world * world
+        sx = x[:sn, : (64 if emu else 512)]
         sx = ((sx - sx.mean(0)) / sx.std(0, unbiased=True)).contiguous()
         slo, shi = shard_bounds(sn, world, rank)
-        big = LargeSVC(kernel="radial", q=256).fit(sx[slo:shi].to(dev), y[:sn][slo:shi].to(dev))
+        big = LargeSVC(kernel="radial", q=32 if emu else 256).fit(sx[slo:shi].to(dev), y[:sn][slo:shi].to(dev))
         small = SV.SVC(kernel="radial", scale=False).fit(sx.to(dev), y[:sn].to(dev))          # full-matrix single-CTA SMO
         ypm = (2 * y[:sn] - 1).to(dev)
-        o_small = float(0.5 * (small.coef_ @ (SV.G.rbf_kernel(sx.to(dev), None, 1.0 / 512).float() @ small.coef_)) - small.coef_.abs().sum())
+        o_small = float(0.5 * (small.coef_ @ (SV.G.rbf_kernel(sx.to(dev), None, 1.0 / sx.shape[1]).float() @ small.coef_)) - small.coef_.abs().sum())
         rel = abs(big.objective_ - o_small) / abs(o_small)
         print(f"[{rank}] svm_large objective {big.objective_:.5f} vs full-matrix SMO {o_small:.5f} (rel {rel:.2e}) outer iters {big.outer_iters_} gap {big.gap_:.2e}", flush=True)
         ok &= rel < 5e-3 and big.gap_ < 1e-3
         print(f"[{rank}] gbm_large auc {a:.4f} trees identical across ranks: {same} top genes {torch.argsort(-gb.importance_gain_)[:4].tolist()}", flush=True)
-        ok &= a > 0.85 and same
-    if not cpu and os.environ.get("CML_EXPERIMENTAL") == "1":
+        ok &= a > (0.75 if emu else 0.85) and same
+    if not cpu and (emu or os.environ.get("CML_EXPERIMENTAL") == "1"):
         # ---- opt-in: kernels / modes written while the GPUs were closed (not part of the default verdict until proven)
         from consensusml_b200.ops import gemm as G
         from consensusml_b200.models.gbm_large import GBMLarge
@@ -229,13 +242,13 @@ def main():
             for rt in (rt32.bfloat16(), F.split_bf16(rt32)):
                 op.launch(xt, rt)
                 op.wait()
-                torch.cuda.synchronize()
+                sync()
                 got = op.result().clone()
                 ref = F.xtr_gemm_rs_unfused(xt, rt, p, B, op.genes_per_rank)
-                err = float((got - ref).abs().max() / ref.abs().max())
+                err = float((got - ref).abs().max() / ref.abs().max()) if got.numel() else 0.0       # a rank may own no gene
                 print(f"[{rank}] EXPERIMENTAL gemm_rs tma={use_tma} rows={rt.shape[0]} rel err {err:.2e}", flush=True)
                 xok &= err < 2e-3
-                torch.cuda.synchronize(); op.bufs[0].barrier()
+                sync(); op.bufs[0].barrier()
         # deterministic reduce-scatter: two launches give the same bits, and agree with the atomic form
         g = torch.Generator().manual_seed(77)
         Rd = torch.randn(n, 4, generator=g)[lo:hi].contiguous().to(dev)
@@ -245,9 +258,9 @@ def main():
         for rep in range(2):
             rsd.launch(xbd, Rd)
             rsd.wait()
-            torch.cuda.synchronize()
+            sync()
             outs.append(rsd.result().clone())
-            torch.cuda.synchronize(); rsd.grad.barrier()
+            sync(); rsd.grad.barrier()
         refd = F.xtr_reduce_scatter_unfused(xbd[:, :p], Rd, p)
         errd = float((outs[0] - refd).abs().max() / refd.abs().max())
         print(f"[{rank}] EXPERIMENTAL deterministic xtr_rs: bit-equal across launches {bool(torch.equal(outs[0], outs[1]))}, rel err {errd:.2e}", flush=True)
@@ -258,8 +271,8 @@ def main():
         got_p = F.gram_allgather(xl, kernel="radial", n_total=n)
         xok &= bool(torch.equal(got_g, got_p))
         print(f"[{rank}] EXPERIMENTAL staged grouped order equals plain order: {bool(torch.equal(got_g, got_p))}", flush=True)
-        gx, gy = synth(4000, 64, seed=3)
-        glo, ghi = shard_bounds(4000, world, rank)
+        gx, gy = synth(600 if emu else 4000, 64, seed=3)
+        glo, ghi = shard_bounds(600 if emu else 4000, world, rank)
         a = GBMLarge(n_estimators=4, max_depth=3, nbins=64, sibling_subtraction=False).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
         b = GBMLarge(n_estimators=4, max_depth=3, nbins=64, sibling_subtraction=True).fit(gx[glo:ghi].to(dev), gy[glo:ghi].to(dev))
         same = all(torch.equal(s_.feat, t_.feat) and torch.equal(s_.thr, t_.thr) for s_, t_ in zip(a.trees, b.trees))
@@ -272,7 +285,7 @@ def main():
         xok &= err < 2e-3
         # replicate-batched sharded lasso: both products on tensor cores, the gradient through the fused GEMM -> reduce-scatter
         lmax = LL.lambda_max(xl, yl, n)
-        lams = np.geomspace(lmax * 0.8, lmax * 0.1, 40)
+        lams = np.geomspace(lmax * 0.8, lmax * 0.1, 12 if emu else 40)
         xr = xl.bfloat16().float()
         bu = LL.fit_batched(xr, yl, lams, n_total=n, max_iter=40, tol=0.0, backend="unfused")
         bf = LL.fit_batched(xr, yl, lams, n_total=n, max_iter=40, tol=0.0, backend="fused", step=bu.step)

@@ -1,0 +1,25 @@
+"""The multi-GPU check of the fused compute + collective paths (tests/dist_fused_check.py) WITHOUT GPUs: one process per rank
+under torchrun / gloo, every kernel on the host execution model, the symmetric buffers in POSIX shared memory that all ranks
+map (parallel/symm.py), so the in-kernel peer stores, reductions and release / acquire signals really cross process
+boundaries and the ranks really run concurrently.  Covers the Python orchestration around the kernels as well:
+ShardTranspose, XtrReduceScatter (atomic and deterministic), the staged / direct all-gather Gram, HistAllReduce and the
+HistEngine reduce-scatter landing, lasso_large (lasso, elastic net, batched lanes through the fused GEMM reduce-scatter),
+GBMLarge's kernel level loop, the working-set SVM."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("world,port", [(2, 29671), (3, 29672), (8, 29678)])
+def test_fused_paths_between_emulated_ranks(world, port):
+    if world > (os.cpu_count() or 1):
+        pytest.skip("fewer cores than ranks")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "dist_fused_check.py"), "--emu"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600"})
+    assert r.returncode == 0 and "ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("EXPERIMENTAL verdict: OK") == world
