@@ -33,16 +33,39 @@ def peaks():
         return 6650.0, 1590.0, "fallback"
 
 
+class _Stamp:
+    """CUDA event on a GPU; host clock on the host execution model (a smoke run of this file, not a measurement)."""
+
+    def __init__(self):
+        self.ev = None if _native.emulating() else torch.cuda.Event(enable_timing=True)
+        self.t = 0.0
+
+    def record(self):
+        if self.ev is not None:
+            self.ev.record()
+        else:
+            import time
+            self.t = time.perf_counter()
+
+    def elapsed_time(self, other):
+        return self.ev.elapsed_time(other.ev) if self.ev is not None else (other.t - self.t) * 1e3
+
+
+def _empty_cache():
+    if not _native.emulating():
+        torch.cuda.empty_cache()
+
+
 def timed(fn, reps, flush):
     ms = []
     for _ in range(reps):
         flush()
         D.barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a, b = _Stamp(), _Stamp()
         a.record()
         fn()
         b.record()
-        torch.cuda.synchronize()
+        _native.synchronize()
         ms.append(a.elapsed_time(b))
     ms.sort()
     return D.max_over_ranks(ms[len(ms) // 2])
@@ -76,7 +99,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
                                  experimental=experimental)
     hbm, tf, how = peaks()
     lib = _native.cuda()
-    fb = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    fb = torch.empty((256 << 20) if not _native.emulating() else 4096, dtype=torch.uint8, device=dev)
     flush = lambda: lib.cml_l2_flush(_native.ptr(fb), fb.numel(), _native.stream_ptr())
     n, p = args.rows, args.genes
     out = []
@@ -103,7 +126,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
             def run():
                 rs.launch(xb, R)
                 rs.wait()
-            run(); torch.cuda.synchronize(); rs.grad.barrier(); rs.grad.local.zero_(); torch.cuda.synchronize(); rs.grad.barrier()
+            run(); _native.synchronize(); rs.grad.barrier(); rs.grad.local.zero_(); _native.synchronize(); rs.grad.barrier()
             ms = timed(run, args.reps, flush)
             bytes_hbm = n * ld * 2 + n * nb * 4
             link_bytes = p * nb * 4 * (world - 1) / world
@@ -122,7 +145,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
                     emit(path="xtr_unfused_torch_nccl", nb=nb, ms=timed(run_un, args.reps, flush))
             del rs, R
         del xb
-        torch.cuda.empty_cache()
+        _empty_cache()
     # ------------------------------------------------------------------ path 1: histogram + all-reduce
     if "hist" not in args.skip:
         n_pad = (n + 3) // 4 * 4
@@ -137,8 +160,8 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
             ms_list = []
             for _ in range(args.reps):
                 flush(); D.barrier()
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a.record(); run(); b.record(); torch.cuda.synchronize()
+                a, b = _Stamp(), _Stamp()
+                a.record(); run(); b.record(); _native.synchronize()
                 ms_list.append(a.elapsed_time(b)); H.clear(args.nodes)
             ms_list.sort()
             ms = D.max_over_ranks(ms_list[len(ms_list) // 2])
@@ -148,7 +171,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
             emit(path="hist_allreduce", multicast=mc, rows_per_gpu=n, genes=p, bins=args.bins, nodes=args.nodes, ms=ms,
                  frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, smem_atomics=2.0 * n * p, atomics_per_s=2.0 * n * p / ms * 1e3)
         del H
-        torch.cuda.empty_cache()
+        _empty_cache()
         # the reduce-scatter-by-feature landing with sibling subtraction: a level with 2 * nodes open nodes histograms only the
         # `nodes` smaller children (half of the samples), lands 1 / world of the bytes per rank, then derives + scores on the owner
         E = F.HistEngine(p, args.bins, args.nodes, 2 * args.nodes, dev)
@@ -171,7 +194,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
              frac_of_roofline=t_roof / (ms / 1e3), nvlink_bytes=link, smem_atomics=1.0 * n * p, atomics_per_s=1.0 * n * p / ms * 1e3,
              includes="build (half of the samples) + peer landing + wait + sibling derivation + split scoring of the owned features")
         del bins, E
-        torch.cuda.empty_cache()
+        _empty_cache()
     # ------------------------------------------------------------------ path 3: all-gather -> tcgen05 Gram (RBF)
     if "gram" not in args.skip:
         m = args.gram_rows
@@ -257,7 +280,7 @@ def measure(rank, world, dev, rows_per_gpu=125000, genes=20000, gram_rows=8192, 
     if "transpose" not in args.skip:
         # ---- path 4: sample-shard -> gene-shard transpose, 32768 samples per GPU x 20k genes fp32 (2.6 GB per GPU)
         from consensusml_b200.parallel import transpose as TR
-        m, p = 32768, args.genes
+        m, p = (32768 if not _native.emulating() else 64), args.genes
         x = torch.randn(m, p, device=dev)
         plan = TR.ShardTranspose(m * world, p, dev)
         plan(x)

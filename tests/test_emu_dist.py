@@ -23,3 +23,11 @@ def test_fused_paths_between_emulated_ranks(world, port):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600"})
     assert r.returncode == 0 and "ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("EXPERIMENTAL verdict: OK") == world
+
+
+def test_fused_paths_bench_runs_on_emulated_ranks():
+    """bench/fused_paths.py::measure (every path, opt-in ones included) as two emulated ranks: the bench code itself is exercised."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29683", os.path.join(ROOT, "tests", "dist_bench_smoke.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600"})
+    assert r.returncode == 0 and "BENCH SMOKE OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
