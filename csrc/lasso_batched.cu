@@ -75,47 +75,62 @@ __global__ void __launch_bounds__(256) batched_residual_kernel(const float* __re
   }
 }
 
-// 32 genes x 32 lanes per block: the gradient tile is read along lanes (its contiguous direction), transposed through shared
-// memory, and everything lane-major (beta, v, the bf16 rows of every rank) is accessed along genes.
+// 64 genes x 32 lanes per block: the gradient tile is read along lanes (its contiguous direction), transposed through shared
+// memory, and everything lane-major (beta, v, the bf16 rows of every rank) is accessed along genes - two adjacent genes per
+// thread, so that a warp's store to a peer is one full 128-byte line of bf16 pairs.
 //   grad  fp32 [genes_owned][ldg]  gene-major (output of gemm_rs.cu), columns = lanes
 //   beta, v  fp32 [B][ldo]         this rank's owned genes only
-//   Vhl peers bf16 [2B][ldp]       hi rows [0, B), lo rows [B, 2B), all genes
+//   Vhl peers bf16 [2B][ldp]       hi rows [0, B), lo rows [B, 2B), all genes; gene0 and ldp even (4-byte aligned pairs)
 __global__ void __launch_bounds__(256) batched_prox_allgather_kernel(const float* __restrict__ grad, long long ldg, int genes_owned, int gene0,
                                                                      int B, const float* __restrict__ lam, float step, float inv_n,
                                                                      float momentum, float shrink, float* __restrict__ beta,
                                                                      float* __restrict__ v, long long ldo, PeersBf16 P, long long ldp,
                                                                      unsigned* __restrict__ done_count, unsigned epoch, int sig_base,
                                                                      float* __restrict__ delta_max) {
-  __shared__ float tile[32][33];
-  const int j0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
+  __shared__ float tile[64][33];
+  const int j0 = blockIdx.x * 64, b0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;      // 8 warps
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
+  for (int k = 0; k < 8; ++k) {
     const int jl = j0 + ty + 8 * k, b = b0 + tx;
     tile[ty + 8 * k][tx] = (jl < genes_owned && b < B) ? __ldcg(grad + (size_t)jl * ldg + b) : 0.f;
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const int b = b0 + ty + 8 * k, jl = j0 + tx;
+    const int b = b0 + ty + 8 * k, jl = j0 + 2 * tx;
     float d = 0.f;
     if (b < B && jl < genes_owned) {
-      const float g = tile[tx][ty + 8 * k];
-      const size_t o = (size_t)b * ldo + jl;
-      const float bold = beta[o], vold = v[o];
-      const float z = vold + step * g * inv_n;
       const float thr = step * lam[b];
-      const float bnew = (z > thr ? z - thr : (z < -thr ? z + thr : 0.f)) * shrink;
-      const float vnew = bnew + momentum * (bnew - bold);
-      beta[o] = bnew;
-      v[o] = vnew;
-      d = fabsf(bnew - bold);
-      const __nv_bfloat16 hi = __float2bfloat16_rn(vnew);
-      const __nv_bfloat16 lo = __float2bfloat16_rn(vnew - __bfloat162float(hi));
+      float vn[2] = {0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (jl + q >= genes_owned) continue;
+        const float g = tile[2 * tx + q][ty + 8 * k];
+        const size_t o = (size_t)b * ldo + jl + q;
+        const float bold = beta[o], vold = v[o];
+        const float z = vold + step * g * inv_n;
+        const float bnew = (z > thr ? z - thr : (z < -thr ? z + thr : 0.f)) * shrink;
+        vn[q] = bnew + momentum * (bnew - bold);
+        beta[o] = bnew;
+        v[o] = vn[q];
+        d = fmaxf(d, fabsf(bnew - bold));
+      }
+      __nv_bfloat162 hi, lo;
+      hi.x = __float2bfloat16_rn(vn[0]);
+      hi.y = __float2bfloat16_rn(vn[1]);
+      lo.x = __float2bfloat16_rn(vn[0] - __bfloat162float(hi.x));
+      lo.y = __float2bfloat16_rn(vn[1] - __bfloat162float(hi.y));
       const size_t ph = (size_t)b * ldp + gene0 + jl, pl = (size_t)(B + b) * ldp + gene0 + jl;
+      const bool pair = jl + 1 < genes_owned;                    // the odd tail writes its single element
       for (int r = 0; r < P.world; ++r) {
-        P.buf[r][ph] = hi;
-        P.buf[r][pl] = lo;
+        if (pair) {
+          *reinterpret_cast<__nv_bfloat162*>(P.buf[r] + ph) = hi;
+          *reinterpret_cast<__nv_bfloat162*>(P.buf[r] + pl) = lo;
+        } else {
+          P.buf[r][ph] = hi.x;
+          P.buf[r][pl] = lo.x;
+        }
       }
     }
     d = warp_max(d);                                             // one lane b per warp row
@@ -171,7 +186,8 @@ int cml_batched_prox_allgather(const float* grad, long long ldg, int genes_owned
   }
   P.rank = rank;
   P.world = world;
-  dim3 grid(max(1, ceil_div(genes_owned, 32)), ceil_div(B, 32));
+  CML_REQUIRE((gene0 & 1) == 0 && (ldp & 1) == 0, CML_EINVAL, "cml_batched_prox_allgather: gene0=%d and ldp=%lld must be even (bf16 pairs)", gene0, ldp);
+  dim3 grid(max(1, ceil_div(genes_owned, 64)), ceil_div(B, 32));
   batched_prox_allgather_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad, ldg, genes_owned, gene0, B, lam, step, inv_n, momentum,
                                                                                   shrink, beta, v, ldo, P, ldp, done_count, epoch,
                                                                                   sig_base, delta_max);
