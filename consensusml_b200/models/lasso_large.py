@@ -451,3 +451,45 @@ def fit_batched(x_local: torch.Tensor, y_local: torch.Tensor, lams, *, weights: 
             if float(d.max()) < tol:
                 break
     return BatchedFit(beta, it, obj, d, step, history)
+
+
+def stability_selection_large(x_local: torch.Tensor, y_local: torch.Tensor, lams, n_boot: int = 64, *, row0: Optional[int] = None,
+                              n_total: Optional[int] = None, seed: int = 0, max_iter: int = 150, tol: float = 1e-4, backend: str = "auto",
+                              alpha: float = 1.0, lanes_per_batch: int = 256, threshold: float = 1e-6) -> dict:
+    """Stability selection on a sample-sharded cohort: ``n_boot`` bootstrap replicates x the lambda grid, all (replicate, lambda)
+    pairs fitted as lanes of the batched solver, ``lanes_per_batch`` at a time.  The bootstrap is the Poisson(1) weighting of the
+    samples, drawn per replicate from a generator keyed by (seed, replicate) over the GLOBAL sample index, so every sharding of
+    the cohort sees the same replicates.  Returns the selection frequency of every gene at every lambda ([n_lambda, p]) and
+    its maximum over the grid (the reference's bootstraps x alpha grid, models.lasso.stability_selection, at cohort sizes where
+    the design matrix is streamed)."""
+    lams = np.asarray(lams, dtype=np.float64).reshape(-1)
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    n_r, p = x_local.shape
+    dev = x_local.device
+    if n_total is None or row0 is None:
+        counts = torch.zeros(world, dtype=torch.float64, device=dev)
+        counts[rank] = n_r
+        all_reduce_(counts)
+        n_total = int(counts.sum().item())
+        row0 = int(counts[:rank].sum().item())
+    W = torch.empty(n_boot, n_r, dtype=torch.float32)
+    for b in range(n_boot):
+        g = torch.Generator().manual_seed(seed * 1000003 + b)
+        W[b] = torch.poisson(torch.ones(n_total), generator=g)[row0: row0 + n_r]
+    W = W.to(dev)
+    step = 1.0 / max(lipschitz_estimate(x_local, n_total), 1e-12) / 2.0          # bootstrap weights up to ~2x the curvature bound
+    pairs = [(b, l) for b in range(n_boot) for l in range(len(lams))]
+    freq = torch.zeros(len(lams), p, dtype=torch.float64, device=dev)
+    iters = []
+    for s in range(0, len(pairs), lanes_per_batch):
+        chunk = pairs[s: s + lanes_per_batch]
+        wts = W[[b for b, _ in chunk]]
+        ls = lams[[l for _, l in chunk]]
+        fit = fit_batched(x_local, y_local, ls, weights=wts, n_total=n_total, max_iter=max_iter, tol=tol, backend=backend, alpha=alpha, step=step)
+        sel = (fit.beta.abs() > threshold).double()
+        idx = torch.as_tensor([l for _, l in chunk], device=dev)
+        freq.index_add_(0, idx, sel)
+        iters.append(fit.iterations)
+    freq /= n_boot
+    return {"frequency": freq, "max_frequency": freq.max(0).values, "lambdas": lams, "iterations": iters, "step": step, "n_total": n_total}

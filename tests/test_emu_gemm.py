@@ -347,3 +347,20 @@ def test_consumers_of_the_gemm_run_their_kernel_branch_under_emulation(monkeypat
         k = SL.LargeSVC(kernel="radial")._columns_single(x, x[:70], 1.0 / 80)
     assert (c[:, :40] - a.float() @ b.float().t()).abs().max() < 1e-3
     assert (k - torch.exp(-torch.cdist(x.double(), x[:70].double()) ** 2 / 80).float()).abs().max() < 2e-2
+
+
+def test_stability_selection_on_the_batched_solver():
+    """Bootstrap x lambda lanes through the batched sharded solver: the informative genes are selected in (almost) every
+    replicate, the noise genes are not; the kernel path agrees with the torch path lane for lane."""
+    from consensusml_b200.models import lasso_large as LL
+    x, y, _, _ = _batched_problem(160, 96, 4, 11)
+    lmax = LL.lambda_max(x, y, 160)
+    lams = [0.35 * lmax, 0.15 * lmax]
+    ref = LL.stability_selection_large(x, y, lams, n_boot=10, seed=3, max_iter=60, tol=0.0, backend="unfused")
+    assert ref["frequency"].shape == (2, 96) and ref["n_total"] == 160
+    top = torch.argsort(ref["max_frequency"], descending=True)[:4]
+    assert set(top.tolist()) <= set(range(8)) and float(ref["max_frequency"][top].min()) >= 0.8
+    assert float(ref["max_frequency"][20:].mean()) < 0.35
+    with _native.emulation(seed=6):
+        got = LL.stability_selection_large(x, y, lams, n_boot=10, seed=3, max_iter=60, tol=0.0, backend="fused")
+    assert (got["frequency"] - ref["frequency"]).abs().max() <= 0.1 + 1e-9       # a coefficient at the threshold may flip in one replicate
