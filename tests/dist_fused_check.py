@@ -49,6 +49,8 @@ def main():
         sx = x[:800, :16]
         sx = (sx - sx.mean(0)) / sx.std(0, unbiased=True)
         svm_single = LargeSVC(kernel="radial", q=64).fit(sx, y[:800])
+        lm = LL.lambda_max(x[:600, :60], y[:600], 600)
+        stab_single = LL.stability_selection_large(x[:600, :60], y[:600], [0.4 * lm, 0.2 * lm], n_boot=6, seed=2, max_iter=40, tol=0.0, backend="unfused")
     rank, world, dev = D.init("gloo" if (cpu or emu) else None)
     lo, hi = shard_bounds(n, world, rank)
     xl, yl = x[lo:hi].to(dev), y[lo:hi].to(dev)
@@ -98,6 +100,13 @@ def main():
         if rank == 0:
             print("gloo sharded working-set SVM: objective", sv.objective_, "single process", svm_single.objective_, "ok", ok_svm)
         ok &= ok_svm
+        # stability selection: the bootstrap replicates are keyed by the global sample index, so the sharded run selects the same genes
+        qlo, qhi = shard_bounds(600, world, rank)
+        stab = LL.stability_selection_large(x[qlo:qhi, :60], y[qlo:qhi], [0.4 * lm, 0.2 * lm], n_boot=6, seed=2, max_iter=40, tol=0.0, backend="unfused")
+        ok_stab = float((stab["frequency"] - stab_single["frequency"]).abs().max()) < 1e-9 and stab["n_total"] == 600
+        if rank == 0:
+            print("gloo sharded stability selection equals the single-process frequencies:", ok_stab)
+        ok &= ok_stab
         fit = LL.fit(xl, yl, 0.02, n_total=n, max_iter=150, backend="unfused", step=step0)
         if rank == 0:
             err = float((fit.beta - ref_single.beta).abs().max())
