@@ -15,6 +15,8 @@ echo "== lasso latency (team vs warp kernel)"
 for M in 0 1; do CML_LASSO_TEAM=$M timeout 200 python tools/time_lasso_reps.py 2>&1 | tail -2 | sed "s/^/team=$M /" | tee -a $O/lasso_latency.txt; done
 echo "== pipeline bench";           timeout 400 python bench/pipeline_bench.py 2>/dev/null | tail -1 | tee $O/pipeline.json | cut -c1-600
 echo "== fused paths (1 GPU)";      timeout 400 python bench/fused_paths.py --reps 4 2>/dev/null | grep '^{' | tee $O/fused_1gpu.jsonl | cut -c1-300
+echo "== fused paths, opt-in ones (1 GPU): GEMM -> reduce-scatter both landings, the batched lasso iteration"
+timeout 400 python bench/fused_paths.py --reps 3 --experimental --skip xtr,hist,gram,transpose 2>/dev/null | grep '^{' | tee $O/fused_optin_1gpu.jsonl | cut -c1-300
 echo "== stability bench";          timeout 300 python bench/stability_bench.py 2>&1 | tail -1 | tee $O/stability.json | cut -c1-600
 echo "== pan-cancer bench";         timeout 600 python bench/pancancer_bench.py 2>&1 | tail -1 | tee $O/pancancer.json | cut -c1-600
 echo "== gemm bench";               timeout 200 python bench/gemm_bench.py 2>/dev/null | tee $O/gemm_bench.jsonl | cut -c1-250
