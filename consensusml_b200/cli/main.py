@@ -33,7 +33,7 @@ def main(argv=None) -> int:
     ap.add_argument("--groups", default=None, help="CSV with columns sample,group (1 = non-reference level)")
     ap.add_argument("--files", default=None, help="concat: glob pattern of the per-sample count files (sample id = file name up to the first dot)")
     ap.add_argument("--degs", default=None, help="mlseq: DEG table CSV (first column = gene ids)")
-    ap.add_argument("--clinical-csv", default=None, help="mlseq: clinical table with TARGET.USI and Risk.group columns")
+    ap.add_argument("--clinical-csv", default=None, help="mlseq: clinical table (.csv or .xlsx) with TARGET.USI and Risk.group columns")
     ap.add_argument("--table", default=None, help="glmboost: samples x (clinical + genes) CSV with the survival column")
     ap.add_argument("--first-gene-col", type=int, default=41, help="glmboost: 0-based position of the first gene column (the script's column 42)")
     ap.add_argument("--honest", action="store_true", help="glmboost: predict the rows that were NOT used for fitting (the script predicts its training rows)")
@@ -142,7 +142,7 @@ def main(argv=None) -> int:
             if not (args.counts and args.degs and args.clinical_csv):
                 ap.error("'mlseq' needs --counts, --degs and --clinical-csv")
             counts_df = pd.read_csv(args.counts, index_col=0)
-            prep = SA.mlseq_prepare(counts_df, pd.read_csv(args.degs).iloc[:, 0].astype(str).tolist(), pd.read_csv(args.clinical_csv))
+            prep = SA.mlseq_prepare(counts_df, pd.read_csv(args.degs).iloc[:, 0].astype(str).tolist(), __import__("consensusml_b200.io.xlsx", fromlist=["read_table"]).read_table(args.clinical_csv))
             out = SA.mlseq_zoo(prep, cfg.io.out_dir, device=dev)
             print(json.dumps({m: {"best_param": r["best_param"], "cv_accuracy": r["cv_accuracy"], **r["test"], "n_selected": len(r["selected_genes"])}
                               for m, r in out["methods"].items()}, indent=1, default=float))
