@@ -211,3 +211,28 @@ def km_whatever(binary_features: Optional[pd.DataFrame] = None, risk: Optional[S
         q = DC.QDA(shrink=qda_shrinkage).fit(xe[tr][:, top].double(), ye[tr])
         out["qda"] = {"genes": [genes[i] for i in top.cpu().tolist()], "test_accuracy": float((q.predict(xe[te][:, top].double()) == ye[te]).float().mean())}
     return out
+
+
+# columns of the TARGET-AML clinical sheet that are NOT cytogenetic / mutation indicators (BUI:86-124, R's dotted names undone)
+_NON_PHENOTYPE = ["Gender", "Race", "Ethnicity", "Age at Diagnosis in Days", "First Event", "FLT3/ITD allelic ratio", "Event Free Survival Time in Days",
+                  "Vital Status", "Overall Survival Time in Days", "Year of Diagnosis", "Year of Last Follow Up", "Protocol", "WBC at Diagnosis",
+                  "Bone marrow leukemic blast percentage (%)", "Peripheral blasts (%)", "CNS disease", "Chloroma", "FAB Category", "Cytogenetic Code Other",
+                  "Cytogenetic Complexity", "Primary Cytogenetic Code", "ISCN", "MRD at end of course 1", "MRD % at end of course 1", "MRD at end of course 2",
+                  "MRD % at end of course 2", "CR status at end of course 1", "CR status at end of course 2", "Risk group", "SCT in 1st CR",
+                  "Bone Marrow Site of Relapse/Induction Failure", "CNS Site of Relapse/Induction Failure", "Chloroma Site of Relapse/Induction Failure",
+                  "Cytogenetic Site of Relapse/Induction Failure", "Other Site of Relapse/Induction Failure", "Comment",
+                  "Refractory Timepoint sent for Induction Failure Project"]
+
+
+def phenotype_matrix(clinical: pd.DataFrame, id_col: str = "TARGET USI") -> pd.DataFrame:
+    """BUI:83-130: the patients x {translocations, deletions, monosomies / trisomies, gene mutations} indicator matrix the k-means of
+    aim 1 runs on.  Non-phenotype columns are dropped, ``Unknown`` / ``N/A`` / ``Not done`` / ``No`` become 0 and ``Yes`` 1, anything
+    that is not numeric afterwards - and every missing value, which the notebook reads as "not tested, so not expected" - is 0."""
+    keep = [c for c in clinical.columns if c not in _NON_PHENOTYPE and c != id_col]
+    m = clinical[keep].copy()
+    rec = {"unknown": 0, "n/a": 0, "not done": 0, "no": 0, "yes": 1}
+    for c in keep:
+        col = m[c].map(lambda v: rec.get(v.strip().lower(), v) if isinstance(v, str) else v)
+        m[c] = pd.to_numeric(col, errors="coerce").fillna(0.0)
+    m.index = clinical[id_col].astype(str).to_numpy()
+    return m.astype(np.float32)

@@ -37,7 +37,7 @@ def main(argv=None) -> int:
     ap.add_argument("--table", default=None, help="glmboost: samples x (clinical + genes) CSV with the survival column")
     ap.add_argument("--first-gene-col", type=int, default=41, help="glmboost: 0-based position of the first gene column (the script's column 42)")
     ap.add_argument("--honest", action="store_true", help="glmboost: predict the rows that were NOT used for fitting (the script predicts its training rows)")
-    ap.add_argument("--features", default=None, help="kmsvm: patients x binary features CSV with a 'risk' column (0 / 1)")
+    ap.add_argument("--features", default=None, help="kmsvm: patients x binary features CSV with a 'risk' column (0 / 1), or the TARGET-AML clinical .xlsx")
     ap.add_argument("--expr", default=None, help="kmsvm: samples x genes CSV with 'risk' (0 / 1) and 'train' (1 = fit on it) columns")
     ap.add_argument("--endpoint", default=None, help="acquire: GDC API base URL (default https://api.gdc.cancer.gov)")
     ap.add_argument("--clinical", action="store_true", help="acquire: also fetch the per-case clinical tables and the clinical supplements")
@@ -156,8 +156,13 @@ def main(argv=None) -> int:
                 ap.error("'kmsvm' needs --features and/or --expr")
             kw = {}
             if args.features:
-                f = pd.read_csv(args.features)
-                kw.update(binary_features=f.drop(columns=["risk"]), risk=f["risk"].to_numpy())
+                from ..io.xlsx import read_table
+                if args.features.lower().endswith(".xlsx"):      # the TARGET clinical workbook itself: the notebook's recoding
+                    clin = read_table(args.features, keep_default_na=False)
+                    kw.update(binary_features=SA.phenotype_matrix(clin), risk=(clin["Risk group"].astype(str) != "Low").astype(int).to_numpy())
+                else:
+                    f = read_table(args.features)
+                    kw.update(binary_features=f.drop(columns=["risk"]), risk=f["risk"].to_numpy())
             if args.expr:
                 e = pd.read_csv(args.expr)
                 kw.update(expression=e.drop(columns=["risk", "train"]), expr_risk=e["risk"].to_numpy(), train_flag=e["train"].to_numpy())

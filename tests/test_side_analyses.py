@@ -139,3 +139,24 @@ def test_cli_entry_points(tmp_path, capsys):
         SA.MLSEQ_METHODS.clear()
         SA.MLSEQ_METHODS.update(SA.MLSEQ_METHODS_BACKUP)
     assert (tmp_path / "DEG_plda.csv").exists() and (tmp_path / "DEG_voomnsc.csv").exists()
+
+
+def test_phenotype_matrix_on_the_reference_workbook():
+    """The real TARGET-AML clinical sheet (993 patients) through io.xlsx and the notebook's recoding, then its k-means for k = 4, 2."""
+    from conftest import REFERENCE_DIR
+    path = os.path.join(REFERENCE_DIR, "BuieRProj", "data", "TARGET_AML_ClinicalData_20160714.xlsx")
+    if not os.path.exists(path):
+        pytest.skip("reference tree not mounted")
+    from consensusml_b200.io import xlsx as X
+    clin = X.read_xlsx(path, keep_default_na=False)
+    m = SA.phenotype_matrix(clin)
+    assert m.shape == (993, 25) and set(np.unique(m.to_numpy())) <= {0.0, 1.0}
+    assert {"t(8;21)", "inv(16)", "MLL", "FLT3/ITD positive?", "NPM mutation", "CEBPA mutation", "c-Kit Mutation Exon 17"} <= set(m.columns)
+    assert 100 < m["t(8;21)"].sum() < 200 and 80 < m["inv(16)"].sum() < 200         # core-binding-factor AML: roughly a quarter of paediatric cases
+    risk = (clin["Risk group"].astype(str) != "Low").astype(int).to_numpy()
+    out = SA.km_whatever(m, risk, ks=(4, 2), nstart=5)
+    km = out["kmeans"].set_index("k")
+    assert km.loc[4, "tot_withinss"] < km.loc[2, "tot_withinss"] and km.loc[4, "deviance"] < km.loc[2, "deviance"] + 1e-9
+    # the low-risk definition of the protocol IS cytogenetic (t(8;21), inv(16), NPM / CEBPA without FLT3-ITD): clusters must carry signal
+    null_dev = -2 * (risk.sum() * np.log(risk.mean()) + (len(risk) - risk.sum()) * np.log(1 - risk.mean()))
+    assert km.loc[4, "deviance"] < 0.8 * null_dev
