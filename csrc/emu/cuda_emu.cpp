@@ -364,6 +364,10 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()
   g_next_resident = false;
   const int nthreads = (int)(block.x * block.y * block.z);
   if (nthreads <= 0 || nthreads > kMaxThreads) trap("block size out of range");
+  // the launch limits of the real device: a configuration beyond them is a launch failure there
+  if (grid.y > 65535u || grid.z > 65535u || grid.x > 2147483647u) trap("grid dimension beyond the device limit (x <= 2^31 - 1, y / z <= 65535)");
+  if (block.z > 64u) trap("blockDim.z beyond the device limit (64)");
+  if (smem_bytes > 227u * 1024u) trap("dynamic shared memory beyond the 227 KB a CTA can opt into");
   const size_t nblocks = (size_t)grid.x * grid.y * grid.z;
   if (nblocks == 0) return;
   if (cluster > 1 && (grid.x % (unsigned)cluster != 0 || cluster > 16)) trap("grid.x is not a multiple of the cluster size");
