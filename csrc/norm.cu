@@ -256,14 +256,15 @@ __global__ void logcpm_kernel(const int* __restrict__ counts, int G, int S, cons
                               const double* __restrict__ lib_eff, double prior, double mean_lib,
                               float* __restrict__ out, float* __restrict__ out_t, long long ld_t) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i = blockIdx.y;
-  if (s >= S || i >= n_rows) return;
-  const int g = rows ? rows[i] : i;
+  if (s >= S) return;
   const double l = lib_eff[s];
   const double pcs = l / mean_lib * prior;
-  const double v = log2(((double)counts[(size_t)g * S + s] + pcs) / (l + 2.0 * pcs) * 1e6);
-  if (out) out[(size_t)i * S + s] = (float)v;
-  if (out_t) out_t[(size_t)s * ld_t + i] = (float)v;
+  for (int i = blockIdx.y; i < n_rows; i += gridDim.y) {        // grid.y is capped at the device limit: rows beyond it wrap around
+    const int g = rows ? rows[i] : i;
+    const double v = log2(((double)counts[(size_t)g * S + s] + pcs) / (l + 2.0 * pcs) * 1e6);
+    if (out) out[(size_t)i * S + s] = (float)v;
+    if (out_t) out_t[(size_t)s * ld_t + i] = (float)v;
+  }
 }
 
 __global__ void rowmask_kernel(const int* __restrict__ counts, int G, int S, unsigned char* __restrict__ mask) {
@@ -329,7 +330,7 @@ int cml_logcpm(const int* counts, int G, int S, const int* rows, int n_rows, con
                double mean_lib, float* out, float* out_t, long long ld_t, void* stream) {
   using namespace cml;
   CML_REQUIRE(n_rows > 0 && (out || out_t), CML_EINVAL, "cml_logcpm: nothing to do");
-  dim3 grid(ceil_div(S, 128), n_rows);
+  dim3 grid(ceil_div(S, 128), n_rows < 65535 ? n_rows : 65535);
   logcpm_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(counts, G, S, rows, n_rows, lib_eff, prior,
                                                                     mean_lib, out, out_t, ld_t);
   CML_LAUNCH_CHECK();

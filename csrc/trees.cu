@@ -368,18 +368,19 @@ __global__ void rank_bins_kernel(const float* __restrict__ xt, int p, int n, int
 // goes left at threshold b iff v < midpoint(e[b], e[b+1]), so its bin is the number of midpoints <= v.
 __global__ void apply_bins_kernel(const float* __restrict__ xt, int p, int m, int ld, const float* __restrict__ edges,
                                   const int* __restrict__ n_edges, unsigned char* __restrict__ bins, int m_pad) {
-  const int f = blockIdx.y;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m_pad) return;
-  if (i >= m) { bins[(size_t)f * m_pad + i] = 0; return; }
-  const float v = xt[(size_t)f * ld + i];
-  const float* e = edges + (size_t)f * 256;
-  int lo = 0, hi = n_edges[f] - 1;            // midpoints exist for b in [0, ne-2]
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (0.5f * (e[mid] + e[mid + 1]) <= v) lo = mid + 1; else hi = mid;
+  for (int f = blockIdx.y; f < p; f += gridDim.y) {           // grid.y is capped at the device limit: features beyond it wrap around
+    if (i >= m) { bins[(size_t)f * m_pad + i] = 0; continue; }
+    const float v = xt[(size_t)f * ld + i];
+    const float* e = edges + (size_t)f * 256;
+    int lo = 0, hi = n_edges[f] - 1;            // midpoints exist for b in [0, ne-2]
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (0.5f * (e[mid] + e[mid + 1]) <= v) lo = mid + 1; else hi = mid;
+    }
+    bins[(size_t)f * m_pad + i] = (unsigned char)lo;
   }
-  bins[(size_t)f * m_pad + i] = (unsigned char)lo;
 }
 
 }  // namespace
@@ -400,7 +401,7 @@ int cml_rank_bins(const float* xt, int p, int n, int ld, unsigned char* bins, in
 int cml_apply_bins(const float* xt, int p, int m, int ld, const float* edges, const int* n_edges, unsigned char* bins,
                    int m_pad, void* stream) {
   using namespace cml;
-  dim3 grid(ceil_div(m_pad, 128), p);
+  dim3 grid(ceil_div(m_pad, 128), p < 65535 ? p : 65535);
   apply_bins_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(xt, p, m, ld, edges, n_edges, bins, m_pad);
   CML_LAUNCH_CHECK();
   return 0;

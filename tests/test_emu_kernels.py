@@ -346,3 +346,17 @@ def test_voom_wls_with_wide_designs(k):
     t_a, t_b = np.asarray(res.t), np.asarray(ref.t)
     assert (np.abs(t_a - t_b) / np.maximum(1.0, np.abs(t_b))).max() < 1e-2
     assert abs(res.s2_prior - ref.s2_prior) / ref.s2_prior < 5e-3
+
+
+def test_log_cpm_beyond_the_grid_y_limit():
+    """More rows than gridDim.y can hold (65,535): the kernel wraps around instead of failing to launch (a transcript-level
+    matrix has several hundred thousand rows; the host model enforces the device's launch limits)."""
+    from consensusml_b200.stats import normalize as N
+    rng = np.random.default_rng(3)
+    c = torch.from_numpy(rng.poisson(5, (70001, 3)).astype(np.int32))
+    lib = c.sum(0).double()
+    ref = N.log_cpm(c, lib)
+    with _native.emulation():
+        got = N.log_cpm(c, lib)
+        got_t = N.log_cpm(c, lib, sample_major=True)
+    assert got.shape == (70001, 3) and (got - ref).abs().max() < 1e-5 and torch.equal(got_t.t().contiguous(), got)
