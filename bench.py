@@ -154,8 +154,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--fits", type=int, default=8880, help="bootstrap path fits per GPU for the secondary fits/s number (0 = skip)")
     ap.add_argument("--no-fused", action="store_true", help="skip the fused-path block (N > 1)")
-    ap.add_argument("--device", default="cuda", choices=["cuda", "cpu"],
-                    help="cpu = dry run of this script's own logic on the CPU oracles (tests/test_api.py); its line is marked invalid")
+    ap.add_argument("--device", default="cuda", choices=["cuda", "cpu", "emu"],
+                    help="cpu = dry run of this script's own logic on the CPU oracles; emu = dry run with the kernels on the host "
+                         "execution model (same entry points and launch counts as on a GPU); both lines are marked invalid")
     ap.add_argument("overrides", nargs="*", help="section.key=value overrides of the pipeline configuration")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -176,6 +177,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     on_gpu = args.device == "cuda"
+    if args.device == "emu":
+        _emu_ctx = _native.emulation(seed=1)                # stays entered for the life of the process
+        _emu_ctx.__enter__()
     if on_gpu and not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device")
     if on_gpu:
@@ -373,7 +377,7 @@ def main():
         acc = _accuracy(summary, cpu_arm, genes13)
         sched = summary["schedule"]
         print(json.dumps({
-            **({} if on_gpu else {"invalid": "CPU dry run of bench.py (--device cpu): not a measurement"}),
+            **({} if on_gpu else {"invalid": f"dry run of bench.py without a GPU (--device {args.device}): not a measurement"}),
             "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": value / CPU_ARM_WALL_S,
