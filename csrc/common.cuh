@@ -129,7 +129,10 @@ inline void red_add_sys(float* addr, float v) {
     std::memcpy(&neu, &f, 4);
   } while (!__atomic_compare_exchange_n(w, &old, neu, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED));
 }
-inline void red_add_v4_sys(float* addr, float4 v) { red_add_sys(addr, v.x); red_add_sys(addr + 1, v.y); red_add_sys(addr + 2, v.z); red_add_sys(addr + 3, v.w); }
+inline void red_add_v4_sys(float* addr, float4 v) {
+  if (reinterpret_cast<uintptr_t>(addr) & 15u) ::cml_emu::trap("red.add.v4.f32 to an address that is not 16-byte aligned (misaligned-address fault on the device)");
+  red_add_sys(addr, v.x); red_add_sys(addr + 1, v.y); red_add_sys(addr + 2, v.z); red_add_sys(addr + 3, v.w);
+}
 inline void multimem_red_add_v4(float*, float4) { ::cml_emu::trap("multimem.red is not available under the host execution model"); }
 inline void st_release_sys(unsigned* addr, unsigned v) { __atomic_store_n(addr, v, __ATOMIC_RELEASE); }
 inline unsigned ld_acquire_sys(const unsigned* addr) { return __atomic_load_n(addr, __ATOMIC_ACQUIRE); }
