@@ -139,6 +139,9 @@ class LargeSVC:
         epi, alpha = (G.EPI_RBF, gamma) if self.kernel == "radial" else (G.EPI_SCALE, 1.0)
         if world > 1:
             sg = st["stage"]
+            if symm.poison_enabled():          # debug mode: stale nominee rows of the previous outer iteration must never be read
+                symm.poison_(sg["stage"])
+                symm.poison_(sg["norm"])
             out = G.gemm_tn_staged(st["xa"], xb.peer_ptrs, q_total, qw, ld, sg["stage"], sg["norm"], sg["flags"], sg.next_epoch(), rank,
                                    epilogue=epi, alpha=alpha, norm_a=st["na"], peer_norm_ptrs=nb.peer_ptrs)
         else:

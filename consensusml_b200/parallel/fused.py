@@ -176,6 +176,9 @@ def gram_allgather(x_local: torch.Tensor, *, kernel: str = "radial", gamma: Opti
     use_stage = (world > 1) if staged is None else staged
     if use_stage:
         st = gram_stage_buffers(world, rows, ld, dev)
+        if symm.poison_enabled():              # nothing of an earlier call may be read: tiles become valid only through this epoch's flags
+            symm.poison_(st["stage"])
+            symm.poison_(st["norm"])
         out = G.gemm_tn_staged(xb.local[:n_local], xb.peer_ptrs, n_total, rows, ld, st["stage"], st["norm"], st["flags"],
                                st.next_epoch(), rank, epilogue=epi, alpha=alpha, norm_a=nrm.local[:n_local],
                                peer_norm_ptrs=nrm.peer_ptrs)

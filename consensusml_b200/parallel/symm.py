@@ -41,6 +41,22 @@ class SymmBuffer:
 _SIGNAL_PAD_WORDS = 256
 
 
+def poison_enabled() -> bool:
+    """``CML_SYMM_POISON=1``: debug mode of the fused paths - buffers whose contents are dead between two epochs
+    (the idle half of a double-buffered landing area, a staging buffer before its copiers run) are filled with NaN, so that a
+    consumer that reads before its producer's flag / signal for THIS epoch has arrived returns NaN instead of last epoch's
+    plausible numbers.  Accumulation targets cannot be poisoned (they must be zero); they are checked by their own tests."""
+    import os
+    return os.environ.get("CML_SYMM_POISON", "0") == "1"
+
+
+def poison_(t: torch.Tensor) -> None:
+    if t.dtype.is_floating_point:
+        t.fill_(float("nan"))
+    else:
+        t.fill_(-1)
+
+
 _SHM_SEQ = 0
 
 

@@ -16,11 +16,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.mark.parametrize("world,port", [(2, 29671), (3, 29672), (8, 29678)])
 def test_fused_paths_between_emulated_ranks(world, port):
+    """(The 3-rank run also switches on CML_SYMM_POISON: staging buffers are NaN until this epoch's copiers have flagged them.)"""
     if world > (os.cpu_count() or 1):
         pytest.skip("fewer cores than ranks")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "tests", "dist_fused_check.py"), "--emu"]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600"})
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600", "CML_SYMM_POISON": "1" if world == 3 else "0"})
     assert r.returncode == 0 and "ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("EXPERIMENTAL verdict: OK") == world
 

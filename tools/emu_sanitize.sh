@@ -12,8 +12,8 @@ mkdir -p profiles
 OUT=profiles/sanitizer_emu.txt
 echo "# tools/emu_sanitize.sh  $(date -u +%Y-%m-%dT%H:%MZ)  g++ $(g++ -dumpversion)" > $OUT
 echo "== UBSan (-fsanitize=undefined -fno-sanitize-recover)" | tee -a $OUT
-CML_EMU_SANITIZE=undefined python -m pytest tests/test_emu_kernels.py tests/test_emu_fused.py tests/test_emu_gemm.py -x -q 2>&1 | tail -2 | tee -a $OUT
+CML_EMU_SANITIZE=undefined python -m pytest tests/test_emu_kernels.py tests/test_emu_fused.py tests/test_emu_gemm.py tests/test_deseq.py -x -q 2>&1 | tail -2 | tee -a $OUT
 echo "== ASan + UBSan (-fsanitize=address,undefined)" | tee -a $OUT
 CML_EMU_SANITIZE=address LD_PRELOAD=$(gcc -print-file-name=libasan.so) ASAN_OPTIONS=detect_leaks=0:detect_stack_use_after_return=0:verify_asan_link_order=0 \
-  python -m pytest tests/test_emu_kernels.py tests/test_emu_fused.py tests/test_emu_gemm.py -x -q 2>&1 | tail -2 | tee -a $OUT
+  python -m pytest tests/test_emu_kernels.py tests/test_emu_fused.py tests/test_emu_gemm.py tests/test_deseq.py -x -q 2>&1 | tail -2 | tee -a $OUT
 python -c "from consensusml_b200 import _build; _build.build_emu()"      # back to the plain build
