@@ -32,3 +32,15 @@ def test_fused_paths_bench_runs_on_emulated_ranks():
            "--master-port", "29683", os.path.join(ROOT, "tests", "dist_bench_smoke.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, cwd=ROOT, env={**os.environ, "CML_DIST_TIMEOUT_S": "600"})
     assert r.returncode == 0 and "BENCH SMOKE OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_a_silent_peer_makes_the_wait_kernel_trap():
+    """Failure detection: a rank that never signals turns into an error on the waiting rank after CML_WAIT_TIMEOUT_S, not a hang."""
+    import time
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29713", os.path.join(ROOT, "tests", "dist_fault_check.py")]
+    t0 = time.time()
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    out = r.stdout + r.stderr
+    assert r.returncode != 0 and "__trap() reached" in out and "WAIT RETURNED" not in out, out[-3000:]
+    assert "waiting for a peer that will never push" in out and time.time() - t0 < 120
