@@ -71,6 +71,24 @@ class emulation:
 
     def __enter__(self):
         global _emu_depth
+        if os.environ.get("CML_EMU_POISON_EMPTY") == "1" and _emu_depth == 0:
+            # fresh host pages are zero, device memory from torch.empty is not: fill every "empty" tensor with NaN / large integers
+            # so that a kernel (or its wrapper) relying on zero-initialised scratch fails here as it would on a GPU
+            import torch
+            self._orig_empty = (torch.empty, torch.empty_like)
+
+            def _fill(t):
+                if t.numel():
+                    if t.dtype.is_floating_point or t.dtype.is_complex:
+                        t.fill_(float("nan"))
+                    elif t.dtype == torch.bool:
+                        t.fill_(True)
+                    else:
+                        t.fill_(torch.iinfo(t.dtype).max // 3)
+                return t
+            oe, oel = self._orig_empty
+            torch.empty = lambda *a, **k: _fill(oe(*a, **k))
+            torch.empty_like = lambda *a, **k: _fill(oel(*a, **k))
         if int(os.environ.get("WORLD_SIZE", "1")) > 1:
             # several emulated ranks as processes (torchrun): a kernel that waits for a peer's signal needs a real clock
             os.environ.setdefault("CML_EMU_REALTIME", "1")
@@ -84,6 +102,10 @@ class emulation:
     def __exit__(self, *a):
         global _emu_depth
         _emu_depth -= 1
+        if getattr(self, "_orig_empty", None) is not None:
+            import torch
+            torch.empty, torch.empty_like = self._orig_empty
+            self._orig_empty = None
         for k, old in self.saved.items():
             if old is None:
                 os.environ.pop(k, None)

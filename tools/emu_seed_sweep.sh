@@ -11,6 +11,8 @@ for s in ${@:-101 202 303}; do
   echo "== CML_EMU_SEED_SHIFT=$s" | tee -a $OUT
   CML_EMU_SEED_SHIFT=$s python -m pytest $FILES -x -q -p no:cacheprovider 2>&1 | tail -1 | tee -a $OUT
 done
+echo "== CML_EMU_POISON_EMPTY=1 (torch.empty returns NaN / large integers, as device memory is not zero)" | tee -a $OUT
+CML_EMU_POISON_EMPTY=1 python -m pytest $FILES tests/test_emu_dist.py -x -q -p no:cacheprovider 2>&1 | tail -1 | tee -a $OUT
 for p in ff 00; do
   echo "== CML_EMU_POISON=$p CML_EMU_SEED_SHIFT=17" | tee -a $OUT
   CML_EMU_POISON=$p CML_EMU_SEED_SHIFT=17 python -m pytest $FILES -x -q -p no:cacheprovider 2>&1 | tail -1 | tee -a $OUT
