@@ -432,3 +432,29 @@ def case_batched_sharded_lasso_iteration_on_the_tensor_core_kernels(be):
         got = LL.BatchedLassoLarge(be.dev(x), be.dev(y), lams, weights=be.dev(W), step=ref.step).run(30, 0.0, 10)
     assert (_h(got.beta) - ref.beta).abs().max() < be.tol(2e-4, 5e-4)
     assert (got.objective - ref.objective).abs().max() < 1e-4
+
+
+def case_lasso_path_results_do_not_depend_on_the_launch(be):
+    """The same batch three times (on the host model: under three thread orders / shared-memory garbage patterns): pass counts,
+    active sets and coefficients must be EQUAL - the round-1 kernel differed "by a sweep or two" on a first launch because its
+    convergence test read a shared-memory slot nobody had written."""
+    from consensusml_b200.ops import lasso as K
+    g = torch.Generator().manual_seed(8)
+    n, p, B = 75, 300, 6
+    x = torch.randn(n, p, generator=g)
+    bt = torch.zeros(p)
+    bt[:6] = torch.tensor([1.0, -1.0, 0.8, -0.8, 0.5, 0.5])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ bt)).float()
+    w = torch.ones(B, n)
+    for b in range(1, B):
+        w[b, torch.randperm(n, generator=g)[:7]] = 0
+    lam = 10.0 ** np.linspace(-0.3, -2.0, 40)
+    runs = []
+    for seed in (1, 2, 3):
+        with be.ctx(seed=seed):
+            pb = K.lognet_path(be.dev(x), be.dev(y), be.dev(w), lam)
+            runs.append((_h(pb.npasses).clone(), _h(pb.kin).clone(), _h(pb.dense(0)).clone(), _h(pb.dense(B - 1)).clone()))
+    for r in runs[1:]:
+        for a, b in zip(runs[0], r):
+            assert torch.equal(a, b)
+    assert int(runs[0][0].min()) > 40
