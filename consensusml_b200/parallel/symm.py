@@ -76,7 +76,9 @@ def _alloc_host_shared(shape, dtype, world: int, rank: int) -> SymmBuffer:
         numel *= int(d)
     esize = torch.empty(0, dtype=dtype).element_size()
     sizes = {"buf": max(4096, (numel * esize + 4095) // 4096 * 4096), "pad": 4096}
-    path = lambda kind, r: f"/dev/shm/cml_symm_{token[0]}_{kind}_{r}"
+    import tempfile
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()   # any shared mapping will do
+    path = lambda kind, r: os.path.join(base, f"cml_symm_{token[0]}_{kind}_{r}")
     for kind, size in sizes.items():
         with open(path(kind, rank), "wb") as fh:
             fh.truncate(size)                                   # zero pages
