@@ -111,6 +111,8 @@ def lognet_path(x: torch.Tensor, y: torch.Tensor, weights: torch.Tensor, lam, *,
     if freq_out is not None and (tuple(freq_out.shape) != (L, p) or freq_out.dtype != torch.float32):
         raise ValueError("freq_out must be a float32 [L, p] tensor")
     if _native.on_device(x):
+        if x.is_cuda:
+            _latency_kernel_canary(x.device)
         return _path_cuda(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
                           feature_mask, penalty_factor, want_eta, packed, freq_out, padded_weights, want_coef)
     out = _path_host(x, y, weights, lam_np, alpha, intercept, modified_newton, thresh, maxit, nx,
@@ -118,6 +120,47 @@ def lognet_path(x: torch.Tensor, y: torch.Tensor, weights: torch.Tensor, lam, *,
     if freq_out is not None:
         freq_out += (out._dense_all != 0).sum(0).to(freq_out.dtype)
     return out
+
+
+_CANARY_DONE: dict = {}
+
+
+def _latency_kernel_canary(device) -> None:
+    """Once per process and device: a small batch through BOTH path kernels.  The one-CTA-per-fit kernel (latency mode, chosen
+    for batches of at most one fit per SM) was developed on the host execution model, where it is bit-identical to the
+    one-warp kernel; this makes the same comparison on the actual device before the pipeline relies on it.  A mismatch
+    switches latency mode off for the process (``CML_LASSO_TEAM=0``) and says so - results then come from the kernel with
+    the hardware record.  An explicit ``CML_LASSO_TEAM`` setting is respected and skips the check."""
+    import os
+    import warnings
+    key = str(device)
+    if key in _CANARY_DONE or "CML_LASSO_TEAM" in os.environ:
+        return
+    _CANARY_DONE[key] = True
+    g = torch.Generator().manual_seed(11)
+    n, p, B = 60, 200, 4
+    x = torch.randn(n, p, generator=g)
+    bt = torch.zeros(p)
+    bt[:5] = torch.tensor([1.0, -1.0, 0.8, -0.6, 0.5])
+    y = (torch.rand(n, generator=g) < torch.sigmoid(x @ bt)).float()
+    w = torch.ones(B, n)
+    for b in range(1, B):
+        w[b, torch.randperm(n, generator=g)[:6]] = 0
+    lam = 10.0 ** np.linspace(-0.4, -1.8, 25)
+    outs = []
+    try:
+        for mode in ("0", "1"):
+            os.environ["CML_LASSO_TEAM"] = mode
+            pb = _path_cuda(x.to(device), y.to(device), w.to(device), lam, 1.0, False, False, 1e-7, 100000, min(p, 256), None, None, False, None)
+            outs.append((pb.npasses.cpu(), pb.kin.cpu(), torch.stack([pb.dense(b).cpu() for b in range(B)]), pb.jerr.cpu()))
+    finally:
+        os.environ.pop("CML_LASSO_TEAM", None)
+    same = all(torch.equal(a, b) for a, b in zip(*outs)) and int(outs[0][3].abs().max()) == 0
+    if not same:
+        os.environ["CML_LASSO_TEAM"] = "0"
+        warnings.warn("consensusml_b200: the latency-mode lasso kernel disagreed with the one-warp kernel on this device; "
+                      "latency mode is switched off for this process (CML_LASSO_TEAM=0)")
+    _CANARY_DONE[key] = "ok" if same else "disabled"
 
 
 def _path_cuda(x, y, weights, lam_np, alpha, intercept, kopt, thresh, maxit, nx, fmask, vp, want_eta, packed,

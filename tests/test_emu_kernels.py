@@ -360,3 +360,34 @@ def test_log_cpm_beyond_the_grid_y_limit():
         got = N.log_cpm(c, lib)
         got_t = N.log_cpm(c, lib, sample_major=True)
     assert got.shape == (70001, 3) and (got - ref).abs().max() < 1e-5 and torch.equal(got_t.t().contiguous(), got)
+
+
+def test_latency_kernel_canary_logic(monkeypatch):
+    """ops.lasso runs a small batch through both path kernels once per device before latency mode is relied on; here on the host
+    model: equal -> 'ok' and no environment left behind; a forced disagreement -> latency mode switched off with a warning."""
+    import os
+    import warnings
+    from consensusml_b200.ops import lasso as K
+    monkeypatch.delenv("CML_LASSO_TEAM", raising=False)
+    K._CANARY_DONE.clear()
+    with _native.emulation(seed=2):
+        K._latency_kernel_canary(torch.device("cpu"))
+        assert K._CANARY_DONE == {"cpu": "ok"} and "CML_LASSO_TEAM" not in os.environ
+        K._CANARY_DONE.clear()
+        real = K._path_cuda
+        calls = []
+
+        def skewed(*a, **k):
+            pb = real(*a, **k)
+            calls.append(os.environ.get("CML_LASSO_TEAM"))
+            if calls[-1] == "1":
+                pb.npasses += 1
+            return pb
+        monkeypatch.setattr(K, "_path_cuda", skewed)
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            K._latency_kernel_canary(torch.device("cpu"))
+        assert calls == ["0", "1"] and K._CANARY_DONE == {"cpu": "disabled"} and os.environ.get("CML_LASSO_TEAM") == "0"
+        assert any("latency-mode lasso kernel disagreed" in str(w.message) for w in rec)
+    monkeypatch.delenv("CML_LASSO_TEAM", raising=False)
+    K._CANARY_DONE.clear()
