@@ -23,6 +23,23 @@ _native.register_signature("cml_binary_metrics", [ctypes.c_void_p, ctypes.c_long
 _KERNEL_MAX_N = 8192
 
 
+_KERNEL_STATE: dict = {}
+_FORCE_CHECK = False            # tests: run the first-use comparison on the host execution model too
+
+
+def _batch_metrics_torch(scores: torch.Tensor, truth: torch.Tensor, threshold: float, is_prob: bool) -> torch.Tensor:
+    B = scores.shape[0]
+    out = torch.empty(B, 8, dtype=torch.float64, device=scores.device)
+    for b in range(B):
+        t = truth if truth.dim() == 1 else truth[b]
+        cm = _confusion_torch((scores[b] > threshold), t)
+        out[b, 0] = _auc_torch(scores[b], t)
+        out[b, 1] = _log_loss_torch(t, scores[b]) if is_prob else float("nan")
+        out[b, 2:6] = cm.flatten().double()
+        out[b, 6], out[b, 7] = cm[:, 1].sum(), cm[:, 0].sum()
+    return out
+
+
 def batch_metrics(scores: torch.Tensor, truth: torch.Tensor, threshold: float = 0.0, is_prob: bool = False) -> Dict[str, torch.Tensor]:
     """Metrics of B score vectors at once.  scores [B, n]; truth [n] or [B, n] in {0, 1}; class 1 iff score > threshold
     (0 for decision values / link scale, 0.5 for probabilities).  Returns float64 tensors of length B:
@@ -30,22 +47,27 @@ def batch_metrics(scores: torch.Tensor, truth: torch.Tensor, threshold: float = 
     if scores.dim() == 1:
         scores = scores[None, :]
     B, n = scores.shape
-    if _native.on_device(scores) and n <= _KERNEL_MAX_N:
+    if _native.on_device(scores) and n <= _KERNEL_MAX_N and _KERNEL_STATE.get("use", True):
         sc = scores.float().contiguous()
         tr = truth.to(device=sc.device, dtype=torch.float32).contiguous()
         out = torch.empty(B, 8, dtype=torch.float64, device=sc.device)
         rc = _native.cuda().cml_binary_metrics(_native.ptr(sc), sc.stride(0), B, n, _native.ptr(tr), n if tr.dim() == 2 else 0,
                                                float(threshold), int(is_prob), _native.ptr(out), _native.stream_ptr())
         _native.check(rc, "cml_binary_metrics")
+        if (scores.is_cuda or _FORCE_CHECK) and "checked" not in _KERNEL_STATE:
+            # first use on a real device: this kernel has run on the host execution model only - hold its first answer against
+            # the torch restatement, and fall back to that (loudly) if they disagree
+            _KERNEL_STATE["checked"] = True
+            ref = _batch_metrics_torch(scores, truth, threshold, is_prob)
+            same = torch.allclose(out[:, 0], ref[:, 0], atol=1e-6, equal_nan=True) and torch.equal(out[:, 2:6], ref[:, 2:6]) and \
+                torch.allclose(out[:, 1], ref[:, 1], rtol=1e-5, atol=1e-6, equal_nan=True)
+            if not same:
+                import warnings
+                warnings.warn("consensusml_b200: cml_binary_metrics disagreed with the torch restatement on this device; using the latter")
+                _KERNEL_STATE["use"] = False
+                out = ref
     else:
-        out = torch.empty(B, 8, dtype=torch.float64, device=scores.device)
-        for b in range(B):
-            t = truth if truth.dim() == 1 else truth[b]
-            cm = _confusion_torch((scores[b] > threshold), t)
-            out[b, 0] = _auc_torch(scores[b], t)
-            out[b, 1] = _log_loss_torch(t, scores[b]) if is_prob else float("nan")
-            out[b, 2:6] = cm.flatten().double()
-            out[b, 6], out[b, 7] = cm[:, 1].sum(), cm[:, 0].sum()
+        out = _batch_metrics_torch(scores, truth, threshold, is_prob)
     return {"auc": out[:, 0], "logloss": out[:, 1], "tn": out[:, 2], "fn": out[:, 3], "fp": out[:, 4], "tp": out[:, 5],
             "error": (out[:, 3] + out[:, 4]) / n}
 

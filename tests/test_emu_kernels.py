@@ -391,3 +391,29 @@ def test_latency_kernel_canary_logic(monkeypatch):
         assert any("latency-mode lasso kernel disagreed" in str(w.message) for w in rec)
     monkeypatch.delenv("CML_LASSO_TEAM", raising=False)
     K._CANARY_DONE.clear()
+
+
+def test_metrics_kernel_first_use_check(monkeypatch):
+    """The first answer of cml_binary_metrics on a device is held against the torch restatement; a disagreement makes the
+    restatement the implementation for the rest of the process."""
+    import warnings
+    from consensusml_b200.ops import metrics as M
+    g = torch.Generator().manual_seed(2)
+    s = torch.randn(3, 50, generator=g)
+    t = (torch.rand(50, generator=g) < 0.5).float()
+    monkeypatch.setattr(M, "_FORCE_CHECK", True)
+    monkeypatch.setattr(M, "_KERNEL_STATE", {})
+    with _native.emulation(seed=1):
+        _native.reset_calls()
+        a = M.batch_metrics(s, t)
+        assert M._KERNEL_STATE == {"checked": True} and _native.calls.get("cml_binary_metrics") == 1
+        monkeypatch.setattr(M, "_KERNEL_STATE", {})
+        real = M._batch_metrics_torch
+        monkeypatch.setattr(M, "_batch_metrics_torch", lambda *a_, **k: real(*a_, **k) + torch.tensor([0.01, 0, 0, 0, 0, 0, 0, 0], dtype=torch.float64))
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            b = M.batch_metrics(s, t)
+        assert M._KERNEL_STATE.get("use") is False and any("disagreed" in str(w.message) for w in rec)
+        assert torch.allclose(b["auc"], a["auc"] + 0.01)
+        c = M.batch_metrics(s, t)                               # from now on: the restatement, no kernel call
+        assert _native.calls.get("cml_binary_metrics") == 2 and torch.allclose(c["auc"], b["auc"])
