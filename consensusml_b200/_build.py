@@ -194,7 +194,8 @@ def emu_translate(src: str) -> str:
         a1 = _match_paren(src, a0)
         args = src[a0:a1]
         out.append(src[pos:j])
-        out.append(f"::cml_emu::launch(dim3({cfg[0]}), dim3({cfg[1]}), (size_t)({cfg[2]}), [&]() {{ {name}{args}; }})")
+        label = name.replace('"', "").replace("\\", "")
+        out.append(f"(::cml_emu::launch_name(\"{label}\"), ::cml_emu::launch(dim3({cfg[0]}), dim3({cfg[1]}), (size_t)({cfg[2]}), [&]() {{ {name}{args}; }}))")
         pos = a1
     text = "".join(out)
     text = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?([\w:]+(?:\s+[\w:]+)*?)\s+(\w+)\[\];",

@@ -260,6 +260,9 @@ int sm_count_emulated() {
   std::abort();
 }
 
+namespace { const char* g_next_name = "?"; }
+void launch_name(const char* kernel) { g_next_name = kernel; }
+
 void next_launch(int cluster, bool resident) {
   g_next_cluster = cluster > 0 ? cluster : 1;
   g_next_resident = resident || cluster > 1;
@@ -369,6 +372,13 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()
   if (block.z > 64u) trap("blockDim.z beyond the device limit (64)");
   if (smem_bytes > 227u * 1024u) trap("dynamic shared memory beyond the 227 KB a CTA can opt into");
   const size_t nblocks = (size_t)grid.x * grid.y * grid.z;
+  if (const char* tr = std::getenv("CML_EMU_TRACE")) {        // launch list: kernel, grid, block, dynamic shared memory, cluster
+    if (FILE* fh = std::fopen(tr, "a")) {
+      std::fprintf(fh, "%s,%u,%u,%u,%u,%u,%u,%zu,%d\n", g_next_name, grid.x, grid.y, grid.z, block.x, block.y, block.z, smem_bytes, cluster);
+      std::fclose(fh);
+    }
+  }
+  g_next_name = "?";
   if (nblocks == 0) return;
   if (cluster > 1 && (grid.x % (unsigned)cluster != 0 || cluster > 16)) trap("grid.x is not a multiple of the cluster size");
   if (resident && nblocks > kMaxResident) trap("a launch that needs all its blocks resident is larger than the emulated machine");

@@ -86,6 +86,7 @@ void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function<void()
 // Options of the NEXT launch only.  cluster: CTAs per thread-block cluster along x (the host model cannot see
 // __cluster_dims__); resident: run all blocks of the grid at the same time (kernels whose CTAs wait for each other).
 void next_launch(int cluster, bool resident);
+void launch_name(const char* kernel);                               // name of the kernel the next launch() runs (for CML_EMU_TRACE)
 void sync_cluster();
 void wait_word_change(const unsigned* word, unsigned val);          // block this thread until *word != val
 void* dyn_smem();

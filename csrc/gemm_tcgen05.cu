@@ -483,15 +483,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_kernel(const __grid_const
 template <int BN, int STAGES>
 int launch_gemm(const GemmParams& P, cudaStream_t st) {
   using L = SmemLayout<BN, STAGES>;
-  auto kern = gemm_tn_kernel<BN, STAGES>;
-  CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+  auto gemm_tn_kernel_inst = gemm_tn_kernel<BN, STAGES>;
+  CML_CUDA(cudaFuncSetAttribute(gemm_tn_kernel_inst, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
   int grid = tiles < sm_count() ? tiles : sm_count();
   if (P.n_copiers > 0) grid = sm_count();          // copier CTAs + GEMM CTAs must all be co-resident (flags are spun on)
 #ifdef CML_EMU
   cml_emu::next_launch(1, true);                   // host model: whole grid resident
 #endif
-  kern<<<grid, kThreads, L::kTotal, st>>>(P);
+  gemm_tn_kernel_inst<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;
 }
@@ -660,8 +660,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) gemm_tn
 template <int STAGES>
 int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
   using L = PairLayout<STAGES>;
-  auto kern = gemm_tn_pair_kernel<STAGES>;
-  CML_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+  auto gemm_tn_pair_kernel_inst = gemm_tn_pair_kernel<STAGES>;
+  CML_CUDA(cudaFuncSetAttribute(gemm_tn_pair_kernel_inst, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   const int tiles = P.tiles_m * P.tiles_n_per_src * P.n_src;
   const int pairs = sm_count() / 2;
   int grid = 2 * (tiles < pairs ? tiles : pairs);
@@ -669,7 +669,7 @@ int launch_gemm_pair(const GemmParams& P, cudaStream_t st) {
 #ifdef CML_EMU
   cml_emu::next_launch(2, true);                     // host model: it cannot see __cluster_dims__
 #endif
-  kern<<<grid, kThreads, L::kTotal, st>>>(P);
+  gemm_tn_pair_kernel_inst<<<grid, kThreads, L::kTotal, st>>>(P);
   CML_LAUNCH_CHECK();
   return 0;
 }
