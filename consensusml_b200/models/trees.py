@@ -554,7 +554,8 @@ class GradientBoosting:
             self.trees.append(tb)
             _, val = predict_leaves(tb, bins, n)
             margin = margin + val[0]
-            self.train_error_.append(float(((margin > 0).float() != yf).float().mean()))
+            self.train_error_.append(((margin > 0).float() != yf).float().mean())      # stays on the device: no host sync per round
+        self.train_error_ = torch.stack(self.train_error_).cpu().tolist() if self.train_error_ else []
         tot = {k: float(v.sum()) for k, v in imp.items()}
         self.importance_ = {"gain": imp["gain"] / max(tot["gain"], 1e-30), "cover": imp["cover"] / max(tot["cover"], 1e-30),
                             "frequency": imp["freq"] / max(tot["freq"], 1e-30)}
