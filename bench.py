@@ -146,6 +146,9 @@ def _accuracy(summary, cpu_arm, genes13):
     return out
 
 
+SECONDARY_LIMIT_S = 900          # the secondary measurements (after the two timed arms) may take this long, then the line is printed without them
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -253,6 +256,7 @@ def main():
     ncalls = torch.tensor([sum(calls.values())], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(ncalls)                             # launches of all ranks
+    n_launches = int(ncalls.item())                         # read now: nothing after the timed arms may stand between this number and the line
     ms = [a.elapsed_time(b) for a, b in ev]
     t = torch.tensor(ms, dtype=torch.float64, device=dev)
     if world > 1:
@@ -279,9 +283,64 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = float(te.mean().item())
 
+    line = None
+    if rank == 0:
+        cpu_arm = None
+        try:
+            cpu_arm = json.load(open(datasets.path("cpu_arm_summary.json")))
+        except OSError:
+            pass
+        genes13 = set(pd.read_csv(datasets.path("lasso13_gene_symbols_biomart.csv")).iloc[:, 0].astype(str))
+        acc = _accuracy(summary, cpu_arm, genes13)
+        sched = summary["schedule"]
+        line = {
+            **({} if on_gpu else {"invalid": f"dry run of bench.py without a GPU (--device {args.device}): not a measurement"}),
+            "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": value / CPU_ARM_WALL_S,
+            "vs_baseline_note": "value / 45.4 s = wall-clock of the same pipeline stages on one CPU core with compiled CPU libraries "
+            "(BASELINE.md section 4 row 1, bench/pipeline_bench.py cpu_arm; the reference publishes no pipeline timing of its own); lower is better",
+            "dtype": "fp32 solvers (lasso, trees, SMO) + bf16 tensor-core Gram with fp32 accumulate; reference is float64 - "
+                     "accuracy gates in this line", "data": "real: bundled TARGET-AML DEG cohort (1984 genes x 137 samples, reference split 93/44)",
+            "config": {"model": "TARGET-AML risk-group consensus pipeline: lasso x15 exclusion reps (LOOCV, 100 lambda) + SVM x4 + "
+                                "RF 2k/5k/10k (proximity) + xgboost-mode GBM x5 + rank aggregation",
+                       "global_batch": 93, "seq_len": 1984, "parallelism": f"stage/task-parallel x{world} (parallel/tasks.py), one all_gather_object",
+                       "l2": "flushed (256 MiB write) before every timed step; inputs < L2", "overrides": list(args.overrides)},
+            "clocks": clk.summary(),
+            "e2e": {"value": e2e_value, "unit": "s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "includes": "pinned-host -> device copy of the assay, all stages, D2H of importances / scores, CSV + report files written"},
+            "gpu_launches": n_launches,
+            "gpu_launches_note": "calls of libcml_b200.so entry points inside the timed region, all ranks (each launches at least one "
+                                 "kernel of ours); counted in consensusml_b200._native.check; torch's own kernels excluded",
+            "gpu_launches_rank0_by_entry": calls,
+            "accuracy": acc, "schedule": sched, "step_ms": ms, "failed_tasks": summary.get("failed_tasks"),
+        }
+
+    emitted = []
+
+    def emit(secondary):
+        """The ONE line of the contract.  Built from the two timed arms above; whatever happens in the secondary measurements
+        below (an exception, a hang in a collective) cannot lose it: a watchdog thread prints it and ends the process."""
+        if rank == 0 and not emitted:
+            emitted.append(True)
+            print(json.dumps({**line, "secondary": secondary}, default=float), flush=True)
+
+    watchdog = None
+    if on_gpu:
+        import threading
+
+        def _give_up():
+            emit({"aborted": f"secondary measurements did not finish within {SECONDARY_LIMIT_S} s"})
+            os._exit(0)
+        watchdog = threading.Timer(SECONDARY_LIMIT_S, _give_up)
+        watchdog.daemon = True
+        watchdog.start()
+
     # ---------------- secondary: lasso path fits per second (replicate-parallel stability selection) ----------------
     fits = None
-    if args.fits > 0:
+    try:
+        if args.fits <= 0:
+            raise RuntimeError("skipped (--fits 0)")
         from consensusml_b200.models import lasso
         from consensusml_b200.ops import lasso as K
         tr, _ = resident.split()
@@ -309,6 +368,8 @@ def main():
         fits = {"lasso_path_fits_per_s": world * args.fits * 3 / (float(tf.item()) / 1e3), "fits_per_gpu_per_step": args.fits,
                 "shape": "93 x 1984 x 100 lambda (real training matrix), fp32 kernel vs float64 glmnet: coefficients agree to 2e-3",
                 "scaling": "weak"}
+    except Exception as exc:
+        fits = {"error": repr(exc)}
 
     # ---------------- secondary: the reference's model_comp() through our API (like for like with --impl reference) ----------------
     mc = None
@@ -367,38 +428,10 @@ def main():
     if world > 1 and not args.no_fused:
         fused = _fused_block(rank, world, dev)
 
+    if watchdog is not None:
+        watchdog.cancel()
     if rank == 0:
-        cpu_arm = None
-        try:
-            cpu_arm = json.load(open(datasets.path("cpu_arm_summary.json")))
-        except OSError:
-            pass
-        genes13 = set(pd.read_csv(datasets.path("lasso13_gene_symbols_biomart.csv")).iloc[:, 0].astype(str))
-        acc = _accuracy(summary, cpu_arm, genes13)
-        sched = summary["schedule"]
-        print(json.dumps({
-            **({} if on_gpu else {"invalid": f"dry run of bench.py without a GPU (--device {args.device}): not a measurement"}),
-            "metric": METRIC, "value": value, "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong",
-            "vs_baseline": value / CPU_ARM_WALL_S,
-            "vs_baseline_note": "value / 45.4 s = wall-clock of the same pipeline stages on one CPU core with compiled CPU libraries "
-            "(BASELINE.md section 4 row 1, bench/pipeline_bench.py cpu_arm; the reference publishes no pipeline timing of its own); lower is better",
-            "dtype": "fp32 solvers (lasso, trees, SMO) + bf16 tensor-core Gram with fp32 accumulate; reference is float64 - "
-                     "accuracy gates in this line", "data": "real: bundled TARGET-AML DEG cohort (1984 genes x 137 samples, reference split 93/44)",
-            "config": {"model": "TARGET-AML risk-group consensus pipeline: lasso x15 exclusion reps (LOOCV, 100 lambda) + SVM x4 + "
-                                "RF 2k/5k/10k (proximity) + xgboost-mode GBM x5 + rank aggregation",
-                       "global_batch": 93, "seq_len": 1984, "parallelism": f"stage/task-parallel x{world} (parallel/tasks.py), one all_gather_object",
-                       "l2": "flushed (256 MiB write) before every timed step; inputs < L2", "overrides": list(args.overrides)},
-            "clocks": clk.summary(),
-            "e2e": {"value": e2e_value, "unit": "s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "includes": "pinned-host -> device copy of the assay, all stages, D2H of importances / scores, CSV + report files written"},
-            "gpu_launches": int(ncalls.item()),
-            "gpu_launches_note": "calls of libcml_b200.so entry points inside the timed region, all ranks (each launches at least one "
-                                 "kernel of ours); counted in consensusml_b200._native.check; torch's own kernels excluded",
-            "gpu_launches_rank0_by_entry": calls,
-            "accuracy": acc, "schedule": sched, "step_ms": ms, "failed_tasks": summary.get("failed_tasks"),
-            "secondary": {"fits": fits, "model_comp": mc, "overlapped_stages": overlap, "fused_paths": fused},
-        }, default=float))
+        emit({"fits": fits, "model_comp": mc, "overlapped_stages": overlap, "fused_paths": fused})
     if world > 1:
         dist.destroy_process_group()
     return 0
