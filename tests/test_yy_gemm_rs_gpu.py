@@ -114,3 +114,22 @@ def test_batched_sharded_lasso_on_the_kernels(use_tma):
     """BatchedLassoLarge (tcgen05 eta product, residual split, fused GEMM -> reduce-scatter, proximal step + all-gather)
     against the torch iteration of the same 96 lanes."""
     _child(_BATCHED % use_tma, timeout=400)
+
+
+@pytest.mark.parametrize("nproc", [1, 2, 8])
+def test_opt_in_fused_paths_on_gpus(nproc):
+    """The section of tests/dist_fused_check.py that was written without hardware (fused GEMM -> reduce-scatter across ranks, the
+    deterministic reduce-scatter, grouped staged order, sibling subtraction on the fused histogram path, elastic net, the
+    batched sharded lasso) - passed with 2 - 8 emulated ranks; here on real GPUs, in its own process group and its own test."""
+    import torch
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    script = os.path.join(ROOT, "tests", "dist_fused_check.py")
+    cmd = ([sys.executable, script, "--only-experimental"] if nproc == 1 else
+           [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
+            "--master-port", str(29570 + nproc), script, "--only-experimental"])
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    except subprocess.TimeoutExpired as exc:
+        pytest.fail(f"did not finish within 600 s: {(exc.stdout or b'')[-2000:]!r}")
+    assert r.returncode == 0 and "ALL OK" in r.stdout and "EXPERIMENTAL verdict: OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
