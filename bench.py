@@ -121,6 +121,9 @@ def reference_arm(args):
                                                              "predict time is measured and EXCLUDED from value",
                                      "standin_seconds_excluded_per_step": float(np.mean(inside))},
                    "install": "verbatim copy of /root/reference/scripts (pip install fails: no setup.py / pyproject.toml)"},
+        "value_scope": "the ensemble stage the reference can run here (model_comp), NOT the whole consensus pipeline that `value` of our arm "
+                       "times; the like-for-like number in our line is secondary.model_comp.model_comp_wall_s (same three models, same "
+                       "hyper-parameters, same cohort and split, through api.model_comp)",
         "log_loss": ll, "rf_auc": auc_rf, "gpu_launches": 0,
         "e2e": {"value": val, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -392,7 +395,8 @@ def main():
         if not tm:
             raise RuntimeError("skipped in the CPU dry run")
         mc = {"model_comp_wall_s": float(np.mean(tm[1:])), "note": "api.model_comp: same three models, hyper-parameters and printed "
-              "log-losses as scripts/model_comp.py:6-34, host DataFrames in, fitted on this rank's GPU"}
+              "log-losses as scripts/model_comp.py:6-34, host DataFrames in, fitted on this rank's GPU; THIS is the number to hold against "
+              "`value` of `bench.py --impl reference` (which times the reference's model_comp, xgboost stand-in excluded)"}
     except Exception as exc:
         mc = {"error": repr(exc)}
 
