@@ -31,13 +31,26 @@ def model_comp(X_train, X_test, y_train, y_test, device=None, verbose: bool = Tr
     .25) and RF(300 trees, depth 3), average their class-1 probabilities, print the four log-losses and
     return ``(xgboost_model, random_forest_model)`` like the reference (model_comp.py:6-34).  The fitted
     gradient-boosting model and the losses are attached to the returned xgboost model as ``.extras``."""
+    import time
     dev = _dev(device)
     xtr, xte, ytr, yte = _t(X_train, dev), _t(X_test, dev), _t(y_train, dev), _t(y_test, dev)
-    xgb = GradientBoosting(n_estimators=700, learning_rate=0.01, max_depth=3, mode="xgboost", seed=8).fit(xtr, ytr)
-    gb = GradientBoosting(n_estimators=280, learning_rate=0.01, max_depth=4, max_features="log2", min_samples_leaf=4,
-                          subsample=0.25, mode="sklearn", seed=8).fit(xtr, ytr)
-    rf = RandomForest(n_trees=300, max_depth=3, seed=8).fit(xtr, ytr)
-    p_rf, p_gb, p_xgb = rf.predict_proba_mean(xte), gb.predict_proba(xte), xgb.predict_proba(xte)
+
+    def timed(fn):
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = fn()
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        return out, time.perf_counter() - t0
+    seconds = {}
+    (xgb, p_xgb), seconds["xgboost"] = timed(lambda: (lambda m: (m, m.predict_proba(xte)))(
+        GradientBoosting(n_estimators=700, learning_rate=0.01, max_depth=3, mode="xgboost", seed=8).fit(xtr, ytr)))
+    (gb, p_gb), seconds["gradient_boost"] = timed(lambda: (lambda m: (m, m.predict_proba(xte)))(
+        GradientBoosting(n_estimators=280, learning_rate=0.01, max_depth=4, max_features="log2", min_samples_leaf=4,
+                         subsample=0.25, mode="sklearn", seed=8).fit(xtr, ytr)))
+    (rf, p_rf), seconds["random_forest"] = timed(lambda: (lambda m: (m, m.predict_proba_mean(xte)))(
+        RandomForest(n_trees=300, max_depth=3, seed=8).fit(xtr, ytr)))
     ens = (p_rf + p_gb + p_xgb) / 3
     losses = {"ensemble": log_loss(yte, ens), "gradient_boost": log_loss(yte, p_gb), "random_forest": log_loss(yte, p_rf),
               "xgboost": log_loss(yte, p_xgb)}
@@ -46,7 +59,7 @@ def model_comp(X_train, X_test, y_train, y_test, device=None, verbose: bool = Tr
         print("Gradient Boost Log Loss " + str(losses["gradient_boost"]))
         print("Random Forest Log Loss " + str(losses["random_forest"]))
         print("XGBoost Log Loss " + str(losses["xgboost"]))
-    xgb.extras = {"gradient_boost_model": gb, "log_loss": losses, "ensemble_proba": ens}
+    xgb.extras = {"gradient_boost_model": gb, "log_loss": losses, "ensemble_proba": ens, "seconds": seconds}
     return xgb, rf
 
 
