@@ -108,8 +108,8 @@ def reference_arm(args):
     from sklearn.metrics import roc_auc_score
     auc_rf = float(roc_auc_score(yte, rf_m.predict_proba(Xte)[:, 1]))
     val = float(np.mean(times))
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": val, "unit": "s", "n_gpus": world, "steps": steps, "warmup": warm,
+    partial = {
+        "metric": "model_comp_wall_s", "value": val, "unit": "s", "n_gpus": world, "steps": steps, "warmup": warm,
         "ms_per_step": val * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "fp64",
         "data": "real: bundled TARGET-AML DEG cohort (1984 genes x 137 samples, reference split 93/44)",
         "config": {"model": "reference scripts/model_comp.py::model_comp (XGBClassifier 700 + GradientBoosting 280 + RandomForest 300, "
@@ -126,7 +126,15 @@ def reference_arm(args):
                        "hyper-parameters, same cohort and split, through api.model_comp)",
         "log_loss": ll, "rf_auc": auc_rf, "gpu_launches": 0,
         "e2e": {"value": val, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    }
+    # The metric of BASELINE.json is the whole consensus pipeline (glmnet LOOCV x15, e1071 SVM x4, randomForest 17k trees, xgboost x5:
+    # R notebooks), which cannot run here: no R, no xgboost.  Only the reference's Python ensemble stage runs; a number for that stage
+    # under the pipeline's metric name would invite a ratio between two different amounts of work, so the line says "unavailable" for
+    # the headline and carries the stage's measurement - with its like-for-like counterpart named - under "partial".
+    print(json.dumps({"impl": "reference",
+                      "unavailable": "the reference's consensus pipeline is R (glmnet / e1071 / randomForest / xgboost notebooks) and R is not "
+                                     "installed; its Python ensemble stage (scripts/model_comp.py, unmodified, from baseline/_ref) does run: see partial",
+                      "metric": METRIC, "partial": partial}))
     return 0
 
 

@@ -43,10 +43,11 @@ def test_reference_arm_runs_the_unmodified_reference_or_says_why():
     assert r.returncode == 0, r.stderr[-2000:]
     d = _line(r.stdout)
     assert d["impl"] == "reference"
-    if "unavailable" in d:
-        assert isinstance(d["unavailable"], str) and d["unavailable"]
+    assert isinstance(d["unavailable"], str) and d["unavailable"] and "value" not in d      # no number under the pipeline's metric name
+    if "partial" not in d:
         return
-    assert d["metric"] == "consensus_pipeline_wall_s" and d["value"] > 0 and "substitutions" in d["config"]
+    pr = d["partial"]
+    assert pr["metric"] == "model_comp_wall_s" and pr["value"] > 0 and "substitutions" in pr["config"] and "value_scope" in pr
     ref_src = os.path.join(os.environ.get("CML_REFERENCE_DIR", "/root/reference"), "scripts", "model_comp.py")
     if os.path.exists(ref_src):                                        # the installed copy is byte-identical to the reference's file
         assert open(ref_src, "rb").read() == open(os.path.join(ROOT, "baseline", "_ref", "scripts", "model_comp.py"), "rb").read()
