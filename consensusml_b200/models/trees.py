@@ -28,6 +28,10 @@ _native.register_signature("cml_apply_bins", [_P, _I, _I, _I, _P, _P, _P, _I, _P
 _native.register_signature("cml_forest_level", [_P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P,
                                                 _P, _P, _P, _P, _P, _P, _I, _I, _F, _F, _F, _F, _F, _F, _ULL, _P, _P, _P,
                                                 _P, _P])
+# (n_frontier_dev, frontier_bound) first; then cml_forest_level's arguments without its host-side n_frontier
+_native.register_signature("cml_forest_level_dev", [_P, _I, _P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P,
+                                                    _P, _P, _P, _P, _P, _P, _I, _I, _F, _F, _F, _F, _F, _F, _ULL, _P, _P, _P,
+                                                    _P, _P])
 _native.register_signature("cml_forest_predict", [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P])
 _native.register_signature("cml_forest_proximity", [_P, _P, _I, _I, _P, _P, _P])
 _native.register_signature("cml_forest_onehot", [_P, _P, _I, _I, _I, _P, ctypes.c_longlong, _P, ctypes.c_longlong, _P])
@@ -160,6 +164,24 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     fm = feature_mask.to(device=dev, dtype=torch.uint8).contiguous() if feature_mask is not None else None
     imp = importance or {}
     depth = 0
+    if max_depth <= SYNC_FREE_MAX_DEPTH and T * (2 ** max_depth) <= SYNC_FREE_MAX_BLOCKS:
+        # Shallow trees (the boosting rounds of model_comp: depth 3 / 4, one tree per launch): the frontier size of level d is
+        # bounded by T * 2^d, so every level is launched with that bound and reads the true size on the device (the previous level's
+        # counter) - no host synchronisation, no counter reset and no frontier compaction between levels.
+        counts = torch.zeros(max_depth + 2, **i32)
+        for depth in range(max_depth + 1):
+            bound = min(T * (2 ** depth), T * max_nodes)
+            nxt = torch.empty(2 * bound, 7, **i32)
+            rc = lb.cml_forest_level_dev(P(counts[depth:]) if depth > 0 else None, bound, P(bins), p, n, n_pad, max_bin, P(s0), P(s1), P(s2c), T,
+                                         max_nodes, max_depth, P(order), P(order2), P(frontier), P(nxt), P(counts[depth + 1:]), P(node_count),
+                                         P(feat), P(thr), P(left), P(value), P(gain), P(cover), criterion, int(mtry), float(lam), float(gamma),
+                                         float(min_child_weight), float(min_samples_leaf), float(min_samples_split), float(eta),
+                                         seed & (2**64 - 1), P(fm), P(imp.get("gain")), P(imp.get("cover")), P(imp.get("freq")),
+                                         _native.stream_ptr())
+            _native.check(rc, "cml_forest_level_dev")
+            frontier = nxt
+            order, order2 = order2, order
+        return TreeBatch(feat, thr, left, value, gain, cover, node_count)
     while nf > 0 and depth <= max_depth:
         nxt = torch.empty(2 * nf, 7, **i32)
         next_count.zero_()
@@ -191,6 +213,8 @@ def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):
     return leaf, val
 
 
+SYNC_FREE_MAX_DEPTH = 8         # grow(): trees this shallow are grown without a host synchronisation per level ...
+SYNC_FREE_MAX_BLOCKS = 1 << 15  # ... as long as the widest level's upper bound stays a modest grid
 PROXIMITY_GEMM_MIN_N = 256      # below this the O(n^2 T) comparison kernel is one cheap launch; above it the GEMM form wins
 
 

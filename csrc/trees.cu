@@ -38,7 +38,8 @@ struct ForestArgs {
   const float* s0; const float* s1; const float* s2;   // [T][n]; s2 may be null
   int T, max_nodes, max_depth;
   int* order_in; int* order_out;                       // [T][n] sample ids grouped by node (ping-pong)
-  const Frontier* frontier; int n_frontier;
+  const Frontier* frontier; int n_frontier;            // n_frontier: entries, or their upper bound when n_frontier_dev is given
+  const int* n_frontier_dev;                           // device-side entry count (the previous level's next_count), or null
   Frontier* next_frontier; int* next_count;
   int* node_count;                                     // [T]
   int* feat; int* thr; int* left; float* value; float* gain; float* cover;   // [T][max_nodes]
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(kWarps * 32) forest_level_kernel(const ForestA
   __shared__ int warp_left[kWarps], warp_tot[kWarps];
 
   const int fi = blockIdx.x;
-  if (fi >= A.n_frontier) return;
+  if (fi >= (A.n_frontier_dev ? *A.n_frontier_dev : A.n_frontier)) return;
   const Frontier F = A.frontier[fi];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const size_t tb = (size_t)F.tree * A.n;
@@ -270,7 +271,7 @@ __global__ void __launch_bounds__(kWarps * 32) forest_level_kernel(const ForestA
 // Nodes that stay leaves copy their samples through, so that the ping-pong buffers stay interchangeable.
 __global__ void forest_copy_unsplit_kernel(const ForestArgs A) {
   const int fi = blockIdx.x;
-  if (fi >= A.n_frontier) return;
+  if (fi >= (A.n_frontier_dev ? *A.n_frontier_dev : A.n_frontier)) return;
   const Frontier F = A.frontier[fi];
   if (A.feat[(size_t)F.tree * A.max_nodes + F.node] >= 0) return;
   const size_t tb = (size_t)F.tree * A.n + F.start;
@@ -407,7 +408,9 @@ int cml_apply_bins(const float* xt, int p, int m, int ld, const float* edges, co
   return 0;
 }
 
-int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max_bin, const float* s0, const float* s1,
+}  // extern "C"
+
+static int forest_level_impl(const int* n_frontier_dev, const unsigned char* bins, int p, int n, int n_pad, int max_bin, const float* s0, const float* s1,
                      const float* s2, int T, int max_nodes, int max_depth, int* order_in, int* order_out,
                      const int* frontier, int n_frontier, int* next_frontier, int* next_count, int* node_count,
                      int* feat, int* thr, int* left, float* value, float* gain, float* cover, int criterion, int mtry,
@@ -419,7 +422,7 @@ int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max
   CML_REQUIRE(max_bin >= 2 && max_bin <= 256, CML_EINVAL, "cml_forest_level: max_bin=%d out of range 2..256", max_bin);
   CML_REQUIRE(mtry <= kMaxMtry || mtry >= p, CML_E2BIG, "cml_forest_level: mtry=%d exceeds the sampled-candidate limit %d", mtry, kMaxMtry);
   ForestArgs A{bins, p, n, n_pad, max_bin, s0, s1, s2, T, max_nodes, max_depth, order_in, order_out,
-               reinterpret_cast<const Frontier*>(frontier), n_frontier, reinterpret_cast<Frontier*>(next_frontier),
+               reinterpret_cast<const Frontier*>(frontier), n_frontier, n_frontier_dev, reinterpret_cast<Frontier*>(next_frontier),
                next_count, node_count, feat, thr, left, value, gain, cover, criterion, mtry, lambda, gamma,
                min_child_weight, min_samples_leaf, min_samples_split, eta, seed, feature_mask, imp_gain, imp_cover, imp_freq};
   const size_t smem = (size_t)kWarps * 2 * max_bin * sizeof(float) + kMaxMtry * sizeof(int);
@@ -429,6 +432,36 @@ int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max
   forest_copy_unsplit_kernel<<<n_frontier, 128, 0, st>>>(A);
   CML_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" {
+
+int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max_bin, const float* s0, const float* s1,
+                     const float* s2, int T, int max_nodes, int max_depth, int* order_in, int* order_out,
+                     const int* frontier, int n_frontier, int* next_frontier, int* next_count, int* node_count,
+                     int* feat, int* thr, int* left, float* value, float* gain, float* cover, int criterion, int mtry,
+                     float lambda, float gamma, float min_child_weight, float min_samples_leaf, float min_samples_split,
+                     float eta, unsigned long long seed, const unsigned char* feature_mask, float* imp_gain,
+                     float* imp_cover, float* imp_freq, void* stream) {
+  return forest_level_impl(nullptr, bins, p, n, n_pad, max_bin, s0, s1, s2, T, max_nodes, max_depth, order_in, order_out, frontier, n_frontier,
+                           next_frontier, next_count, node_count, feat, thr, left, value, gain, cover, criterion, mtry, lambda, gamma,
+                           min_child_weight, min_samples_leaf, min_samples_split, eta, seed, feature_mask, imp_gain, imp_cover, imp_freq,
+                           stream);
+}
+
+// The same level with the number of frontier entries read on the DEVICE (the previous level's next_count): the grid is sized by
+// the caller's upper bound `frontier_bound` and surplus blocks leave at once.  A shallow tree (boosting rounds of depth 2 - 8) is
+// then grown without one host synchronisation per level.
+int cml_forest_level_dev(const int* n_frontier_dev, int frontier_bound, const unsigned char* bins, int p, int n, int n_pad, int max_bin,
+                         const float* s0, const float* s1, const float* s2, int T, int max_nodes, int max_depth, int* order_in,
+                         int* order_out, const int* frontier, int* next_frontier, int* next_count, int* node_count, int* feat, int* thr,
+                         int* left, float* value, float* gain, float* cover, int criterion, int mtry, float lambda, float gamma,
+                         float min_child_weight, float min_samples_leaf, float min_samples_split, float eta, unsigned long long seed,
+                         const unsigned char* feature_mask, float* imp_gain, float* imp_cover, float* imp_freq, void* stream) {
+  return forest_level_impl(n_frontier_dev, bins, p, n, n_pad, max_bin, s0, s1, s2, T, max_nodes, max_depth, order_in, order_out, frontier,
+                           frontier_bound, next_frontier, next_count, node_count, feat, thr, left, value, gain, cover, criterion, mtry, lambda,
+                           gamma, min_child_weight, min_samples_leaf, min_samples_split, eta, seed, feature_mask, imp_gain, imp_cover,
+                           imp_freq, stream);
 }
 
 int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int max_nodes, const int* feat, const int* thr,

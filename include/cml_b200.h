@@ -167,6 +167,14 @@ int cml_forest_level(const unsigned char* bins, int p, int n, int n_pad, int max
                      float lambda, float gamma, float min_child_weight, float min_samples_leaf, float min_samples_split,
                      float eta, unsigned long long seed, const unsigned char* feature_mask, float* imp_gain,
                      float* imp_cover, float* imp_freq, void* stream);
+/* The same level with the frontier size read on the device (previous level's next_count) and the grid sized by an upper bound:
+ * no host synchronisation per level for shallow trees (boosting rounds; reference: scripts/model_comp.py:7-8). */
+int cml_forest_level_dev(const int* n_frontier_dev, int frontier_bound, const unsigned char* bins, int p, int n, int n_pad, int max_bin,
+                         const float* s0, const float* s1, const float* s2, int T, int max_nodes, int max_depth, int* order_in,
+                         int* order_out, const int* frontier, int* next_frontier, int* next_count, int* node_count, int* feat, int* thr,
+                         int* left, float* value, float* gain, float* cover, int criterion, int mtry, float lambda, float gamma,
+                         float min_child_weight, float min_samples_leaf, float min_samples_split, float eta, unsigned long long seed,
+                         const unsigned char* feature_mask, float* imp_gain, float* imp_cover, float* imp_freq, void* stream);
 int cml_forest_predict(const unsigned char* bins, int m, int m_pad, int T, int max_nodes, const int* feat, const int* thr,
                        const int* left, const float* value, int* leaf_out, float* value_out, void* stream);
 int cml_forest_proximity(const int* leaf, const unsigned char* oob, int T, int n, float* prox, float* pairs, void* stream);

@@ -458,3 +458,40 @@ def case_lasso_path_results_do_not_depend_on_the_launch(be):
         for a, b in zip(runs[0], r):
             assert torch.equal(a, b)
     assert int(runs[0][0].min()) > 40
+
+
+def case_shallow_trees_grown_without_host_syncs_equal_the_synchronised_growth(be):
+    """grow() for max_depth <= 8 launches every level with an upper bound on the frontier and reads the true size on the device;
+    the trees (boosting rounds in both modes, a depth-3 forest) must be the ones the level-by-level synchronised loop grows."""
+    from consensusml_b200.models import trees as TR
+    g = torch.Generator().manual_seed(6)
+    n, p = 120, 40
+    x = torch.randn(n, p, generator=g)
+    y = ((x[:, 0] - 0.7 * x[:, 1] + 0.4 * torch.randn(n, generator=g)) > 0).float()
+
+    def fit_all():
+        a = TR.GradientBoosting(n_estimators=6, learning_rate=0.3, max_depth=3, mode="xgboost", seed=8).fit(be.dev(x), be.dev(y))
+        b = TR.GradientBoosting(n_estimators=6, learning_rate=0.1, max_depth=4, max_features="log2", min_samples_leaf=4, subsample=0.5, mode="sklearn",
+                                seed=8).fit(be.dev(x), be.dev(y))
+        c = TR.RandomForest(n_trees=20, max_depth=3, seed=8).fit(be.dev(x), be.dev(y))
+        return a, b, c
+    with be.ctx(seed=4):
+        _native.reset_calls()
+        fast = fit_all()
+        assert _native.calls.get("cml_forest_level_dev", 0) > 0 and _native.calls.get("cml_forest_level", 0) == 0
+        old = TR.SYNC_FREE_MAX_DEPTH
+        TR.SYNC_FREE_MAX_DEPTH = -1
+        try:
+            slow = fit_all()
+        finally:
+            TR.SYNC_FREE_MAX_DEPTH = old
+    for f, s in zip(fast[:2], slow[:2]):
+        assert len(f.trees) == len(s.trees)
+        for tf, ts in zip(f.trees, s.trees):
+            if be.name == "emu":       # (on a GPU the children of one level get their node ids in atomic order: compare what the trees compute)
+                assert torch.equal(_h(tf.feat), _h(ts.feat)) and torch.equal(_h(tf.thr), _h(ts.thr)) and torch.equal(_h(tf.left), _h(ts.left))
+                assert torch.allclose(_h(tf.value), _h(ts.value), atol=1e-6)
+            assert int(_h(tf.node_count).sum()) == int(_h(ts.node_count).sum())
+        assert torch.allclose(_h(f.predict_proba(be.dev(x))), _h(s.predict_proba(be.dev(x))), atol=1e-6)
+    assert abs(fast[2].oob_error_ - slow[2].oob_error_) < 1e-9
+    assert torch.allclose(_h(fast[2].importance_), _h(slow[2].importance_), atol=1e-6)
