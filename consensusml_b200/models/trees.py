@@ -164,12 +164,16 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     fm = feature_mask.to(device=dev, dtype=torch.uint8).contiguous() if feature_mask is not None else None
     imp = importance or {}
     depth = 0
-    if max_depth <= SYNC_FREE_MAX_DEPTH and T * (2 ** max_depth) <= SYNC_FREE_MAX_BLOCKS:
-        # Shallow trees (the boosting rounds of model_comp: depth 3 / 4, one tree per launch): the frontier size of level d is
-        # bounded by T * 2^d, so every level is launched with that bound and reads the true size on the device (the previous level's
-        # counter) - no host synchronisation, no counter reset and no frontier compaction between levels.
-        counts = torch.zeros(max_depth + 2, **i32)
-        for depth in range(max_depth + 1):
+    # The first levels are launched WITHOUT host synchronisation: the frontier of level d has at most T * 2^d entries, so each of
+    # them gets that bound as its grid and reads the true size on the device (the previous level's counter); no counter reset, no
+    # frontier compaction.  Shallow trees (boosting rounds of depth 2 - 8) finish here; deeper ones pay their first host round trip
+    # only at the level where the bound would exceed a modest grid, and continue with the synchronised, compacted loop below.
+    free_levels = 0
+    while free_levels <= min(max_depth, SYNC_FREE_MAX_DEPTH) and T * (2 ** free_levels) <= SYNC_FREE_MAX_BLOCKS:
+        free_levels += 1
+    if free_levels > 0:
+        counts = torch.zeros(free_levels + 1, **i32)
+        for depth in range(free_levels):
             bound = min(T * (2 ** depth), T * max_nodes)
             nxt = torch.empty(2 * bound, 7, **i32)
             rc = lb.cml_forest_level_dev(P(counts[depth:]) if depth > 0 else None, bound, P(bins), p, n, n_pad, max_bin, P(s0), P(s1), P(s2c), T,
@@ -181,7 +185,11 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
             _native.check(rc, "cml_forest_level_dev")
             frontier = nxt
             order, order2 = order2, order
-        return TreeBatch(feat, thr, left, value, gain, cover, node_count)
+        depth = free_levels
+        if depth > max_depth:
+            return TreeBatch(feat, thr, left, value, gain, cover, node_count)
+        nf = int(counts[free_levels].item())
+        frontier = frontier[:nf].contiguous()
     while nf > 0 and depth <= max_depth:
         nxt = torch.empty(2 * nf, 7, **i32)
         next_count.zero_()

@@ -474,11 +474,13 @@ def case_shallow_trees_grown_without_host_syncs_equal_the_synchronised_growth(be
         b = TR.GradientBoosting(n_estimators=6, learning_rate=0.1, max_depth=4, max_features="log2", min_samples_leaf=4, subsample=0.5, mode="sklearn",
                                 seed=8).fit(be.dev(x), be.dev(y))
         c = TR.RandomForest(n_trees=20, max_depth=3, seed=8).fit(be.dev(x), be.dev(y))
-        return a, b, c
+        d = TR.RandomForest(n_trees=12, seed=8).fit(be.dev(x), be.dev(y))                       # unlimited depth: bounded levels first, then the compacted loop
+        e = TR.GradientBoosting(n_estimators=3, learning_rate=0.3, max_depth=12, mode="xgboost", seed=8).fit(be.dev(x), be.dev(y))
+        return a, b, c, d, e
     with be.ctx(seed=4):
         _native.reset_calls()
         fast = fit_all()
-        assert _native.calls.get("cml_forest_level_dev", 0) > 0 and _native.calls.get("cml_forest_level", 0) == 0
+        assert _native.calls.get("cml_forest_level_dev", 0) > 0 and _native.calls.get("cml_forest_level", 0) > 0
         old = TR.SYNC_FREE_MAX_DEPTH
         TR.SYNC_FREE_MAX_DEPTH = -1
         try:
@@ -493,5 +495,7 @@ def case_shallow_trees_grown_without_host_syncs_equal_the_synchronised_growth(be
                 assert torch.allclose(_h(tf.value), _h(ts.value), atol=1e-6)
             assert int(_h(tf.node_count).sum()) == int(_h(ts.node_count).sum())
         assert torch.allclose(_h(f.predict_proba(be.dev(x))), _h(s.predict_proba(be.dev(x))), atol=1e-6)
-    assert abs(fast[2].oob_error_ - slow[2].oob_error_) < 1e-9
-    assert torch.allclose(_h(fast[2].importance_), _h(slow[2].importance_), atol=1e-6)
+    for k in (2, 3):
+        assert abs(fast[k].oob_error_ - slow[k].oob_error_) < 1e-9
+        assert torch.allclose(_h(fast[k].importance_), _h(slow[k].importance_), atol=1e-6)
+    assert torch.allclose(_h(fast[4].predict_proba(be.dev(x))), _h(slow[4].predict_proba(be.dev(x))), atol=1e-6)
