@@ -137,6 +137,8 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
     if not _native.on_device(bins):
         return _grow_numpy(bins, n, s0, s1, s2, criterion, mtry, max_depth, max_nodes, max_bin, lam, gamma, min_child_weight,
                            min_samples_leaf, min_samples_split, eta, seed, feature_mask, importance, in_tree)
+    if bins.is_cuda or _FORCE_CANARY:
+        _sync_free_canary(dev)
     i32 = dict(dtype=torch.int32, device=dev)
     f32 = dict(dtype=torch.float32, device=dev)
     if in_tree is None:
@@ -205,6 +207,43 @@ def grow(bins: torch.Tensor, n: int, s0: torch.Tensor, s1: torch.Tensor, *, s2: 
         order, order2 = order2, order
         depth += 1
     return TreeBatch(feat, thr, left, value, gain, cover, node_count)
+
+
+_CANARY_STATE: dict = {}
+_FORCE_CANARY = False           # tests: run the first-use comparison on the host execution model too
+
+
+def _sync_free_canary(dev) -> None:
+    """Once per process and device, before the first real growth: a small forest grown with the bounded, synchronisation-free
+    levels and with the synchronised loop.  The former has run on the host execution model only; if the leaf values the two
+    assign to the training samples differ on this device, it is switched off for the process (loudly)."""
+    global SYNC_FREE_MAX_DEPTH
+    key = str(dev)
+    if key in _CANARY_STATE or SYNC_FREE_MAX_DEPTH < 0:
+        return
+    _CANARY_STATE[key] = "running"                       # grow() below re-enters this function
+    g = torch.Generator().manual_seed(5)
+    n, p, T = 64, 12, 6
+    xb = torch.randint(0, 16, (p, n), generator=g, dtype=torch.uint8).to(dev)
+    yv = (torch.rand(T, n, generator=g) < 0.5).float().to(dev)
+    w = torch.ones(T, n, device=dev)
+    outs = []
+    keep = SYNC_FREE_MAX_DEPTH
+    try:
+        for mode in (keep, -1):
+            SYNC_FREE_MAX_DEPTH = mode
+            tb = grow(xb, n, w * yv, w, criterion=GINI, mtry=4, max_depth=5, max_bin=16, seed=3)
+            outs.append(predict_leaves(tb, xb, n)[1].cpu())
+    finally:
+        SYNC_FREE_MAX_DEPTH = keep
+    if torch.allclose(outs[0], outs[1], atol=1e-6):
+        _CANARY_STATE[key] = "ok"
+    else:
+        import warnings
+        warnings.warn("consensusml_b200: tree growth without per-level synchronisation disagreed with the synchronised loop on this "
+                      "device; it is switched off for this process")
+        SYNC_FREE_MAX_DEPTH = -1
+        _CANARY_STATE[key] = "disabled"
 
 
 def predict_leaves(trees: TreeBatch, bins: torch.Tensor, m: int):

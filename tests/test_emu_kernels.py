@@ -417,3 +417,31 @@ def test_metrics_kernel_first_use_check(monkeypatch):
         assert torch.allclose(b["auc"], a["auc"] + 0.01)
         c = M.batch_metrics(s, t)                               # from now on: the restatement, no kernel call
         assert _native.calls.get("cml_binary_metrics") == 2 and torch.allclose(c["auc"], b["auc"])
+
+
+def test_tree_growth_first_use_check(monkeypatch):
+    from consensusml_b200.models import trees as TR
+    monkeypatch.setattr(TR, "_FORCE_CANARY", True)
+    monkeypatch.setattr(TR, "_CANARY_STATE", {})
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(80, 10, generator=g)
+    y = (x[:, 0] > 0).float()
+    with _native.emulation(seed=2):
+        TR.RandomForest(n_trees=4, max_depth=3, seed=1).fit(x, y)
+        assert TR._CANARY_STATE == {"cpu": "ok"} and TR.SYNC_FREE_MAX_DEPTH == 8
+        # a device on which the two growth modes disagree: the bounded levels are switched off
+        monkeypatch.setattr(TR, "_CANARY_STATE", {})
+        real = TR.predict_leaves
+        n_calls = []
+
+        def skew(tb, bins, m):
+            leaf, val = real(tb, bins, m)
+            n_calls.append(1)
+            return leaf, val + (0.5 if len(n_calls) == 2 else 0.0)
+        monkeypatch.setattr(TR, "predict_leaves", skew)
+        import warnings
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            TR._sync_free_canary(torch.device("cpu"))
+        assert TR._CANARY_STATE == {"cpu": "disabled"} and TR.SYNC_FREE_MAX_DEPTH == -1 and any("switched off" in str(w.message) for w in rec)
+    monkeypatch.setattr(TR, "SYNC_FREE_MAX_DEPTH", 8)
