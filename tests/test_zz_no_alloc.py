@@ -106,7 +106,11 @@ def _dense(o, b, p):
     return out
 
 
-def test_static_scratch_entry_matches_regular_entry_twice():
+def test_static_scratch_entry_matches_regular_entry_twice(monkeypatch):
+    # the regular entry would give a batch of at most one fit per SM to the one-CTA-per-fit kernel (round 2); this test is about
+    # the allocation-free entry, so both sides are pinned to the kernel they share (the two kernels are compared with each other
+    # in tests/kernel_cases.py::case_lasso_cta_per_fit_*)
+    monkeypatch.setenv("CML_LASSO_TEAM", "0")
     lib = _lib()
     assert lib.cml_lognet_static_scratch_bytes() == 8 << 20
     # p chosen so that fewer replicates fit in the built-in array than the batch holds: 8 MiB / (12 * 3000) = 233 < 300,
