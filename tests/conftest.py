@@ -19,14 +19,17 @@ def pytest_configure(config):
 # GPU run order: the files whose kernels have the longest hardware record first, whole-pipeline and multi-GPU tests after the
 # single-kernel ones (a fault in a new kernel then fails its own small test, not the pipeline's), first-time-on-hardware code
 # next to last, the allocation-free entry point last.  (-x stops at the first failure: what is proven should get to run.)
-_LATE = ["test_y_kernels_gpu.py", "test_pipeline_gpu.py", "test_x_fused.py", "test_yy_gemm_rs_gpu.py", "test_zz_no_alloc.py"]
+_LATE = ["test_gemm_gpu.py",                                   # device code byte-identical to the build that ran in round 1
+         "test_lasso_gpu.py", "test_normalize.py", "test_stats.py", "test_svm.py",      # small round-2 changes to round-1 kernels
+         "test_de.py", "test_trees.py", "test_models_misc.py",                          # larger round-2 changes / new kernels
+         "test_y_kernels_gpu.py", "test_pipeline_gpu.py", "test_x_fused.py", "test_yy_gemm_rs_gpu.py", "test_zz_no_alloc.py"]
 
 
 def pytest_collection_modifyitems(config, items):
     import torch
     if torch.cuda.is_available():
         rank = {name: i + 1 for i, name in enumerate(_LATE)}
-        items.sort(key=lambda it: rank.get(os.path.basename(str(it.fspath)), 0))      # stable: collection order inside a class
+        items.sort(key=lambda it: rank.get(os.path.basename(str(it.fspath)), 1.5))    # stable; unlisted files right after the GEMM tests
         return
     skip = pytest.mark.skip(reason="no CUDA device")
     for item in items:
